@@ -1,0 +1,304 @@
+#!/usr/bin/env python
+"""Benchmark of the GenSeg hot path on B200: U-Net (1 -> 2 classes, bilinear) 256x256 bf16 training step
+(forward + CE+Dice loss + backward + RMSprop), global batch 64, data-parallel over N GPUs.
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (one JSON line on rank 0)
+    python bench.py --impl reference --steps K --warmup W    # the CPU oracle port on the host cores
+
+See the module docstrings of semantic_segmentation_b200 and DESIGN.md for what is timed.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+GLOBAL_BATCH = 64
+H = W = 256
+N_CLASSES = 2
+# algorithmic FLOPs per image: U-Net(1,2,bilinear) fwd 79.818 GF, training step 239.38 GF
+TRAIN_GF_PER_IMG = 239.38
+METRIC = "U-Net train images/sec @256^2 (1->2 classes, bilinear, bf16, global batch 64)"
+
+
+def synthetic_batch(n, seed=4321):
+    """JSRT-shaped synthetic batch: image in [0,1), mask = two filled ellipses (~27% foreground)."""
+    g = torch.Generator().manual_seed(seed)
+    x = torch.rand(n, 1, H, W, generator=g)
+    yy, xx = torch.meshgrid(torch.arange(H, dtype=torch.float32), torch.arange(W, dtype=torch.float32), indexing="ij")
+    m = (((xx - 80) / 48) ** 2 + ((yy - 128) / 90) ** 2 < 1) | (((xx - 176) / 48) ** 2 + ((yy - 128) / 90) ** 2 < 1)
+    y = m.long()[None].repeat(n, 1, 1).contiguous()
+    return x, y
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [t.strip() for t in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("bf16_tflops", 1590.0), d.get("bf16_tflops_sustained", 1400.0), d.get("hbm_gbs", 6650.0), "measured"
+    return 1590.0, 1400.0, 6650.0, "fallback"
+
+
+def cpu_oracle_step_time(batch: int, steps: int, warmup: int):
+    """Time the CPU oracle (port of the reference's path) on a bounded sample: fwd + CE+Dice + bwd."""
+    from oracle import genseg_oracle as O
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    st = O.seeded_state(O.unet_state_spec(1, N_CLASSES, True), 1234)
+    params = {k: v.clone().requires_grad_(True) for k, v in st.items() if v.dtype.is_floating_point and "running" not in k}
+    work = dict(st)
+    work.update(params)
+    x, y = synthetic_batch(batch)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        logits = O.unet_forward(work, x, True, training=True, update_running=True)
+        loss, _, _ = O.seg_loss(logits, y)
+        grads = torch.autograd.grad(loss, list(params.values()))
+        del grads
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    times.sort()
+    return times[len(times) // 2], threads
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    batch = 4
+    steps = max(1, min(args.steps, 5))
+    warm = max(1, min(args.warmup, 2))
+    t, threads = cpu_oracle_step_time(batch, steps, warm)
+    v = batch / t
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "images/s", "n_gpus": args.gpus, "steps": steps,
+            "warmup": warm, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "U-Net(1,2,bilinear) 256x256 fwd+CE+Dice+bwd, CPU oracle port of the reference path",
+                       "global_batch": GLOBAL_BATCH, "parallelism": "host cores"},
+            "cpu_baseline": {"value": v, "unit": "images/s", "cores": threads, "kind": "port",
+                             "sample": "batch %d x %d steps of the 64-image workload (median)" % (batch, steps)},
+            "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def time_kernel(fn, iters=10, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(iters):
+        fn()
+    e.record()
+    torch.cuda.synchronize()
+    return s.elapsed_time(e) / iters * 1e-3
+
+
+def dominant_kernel_roofline(per_gpu_batch: int):
+    """Time the heaviest conv layer of the step (up4.conv[0]: 128 -> 64 ch, 3x3, 256x256; 9.66 GF/img per pass)
+    alone, per pass (fprop / dgrad / wgrad), with CUDA events on the launching stream."""
+    from semantic_segmentation_b200 import ops
+    from semantic_segmentation_b200._lib import MODE_CONV, MODE_CONVT, view_nhwc
+    dev = torch.device("cuda")
+    b = per_gpu_batch
+    cin, cout = 128, 64
+    x = torch.randn(b, H, W, cin, device=dev, dtype=torch.bfloat16)
+    w = torch.randn(cout, cin, 3, 3, device=dev) * 0.03
+    wp, wpb = ops.pack_weight(w, True, torch.bfloat16), ops.pack_weight(w, False, torch.bfloat16)
+    y = torch.empty(b, H, W, cout, device=dev, dtype=torch.bfloat16)
+    dx = torch.empty_like(x)
+    dwp = torch.zeros(9, cout, cin, device=dev, dtype=torch.float32)
+    xv, yv, dxv = view_nhwc(x), view_nhwc(y), view_nhwc(dx)
+    flops = 2.0 * b * H * W * 9 * cin * cout
+    out = {}
+    out["fprop"] = flops / time_kernel(lambda: ops.conv_gather(xv, wp, None, yv, MODE_CONV, 3, 1, 1, use_tc=1, want_stats=True))
+    out["dgrad"] = flops / time_kernel(lambda: ops.conv_gather(yv, wpb, None, dxv, MODE_CONVT, 3, 1, 1, use_tc=1))
+    out["wgrad"] = flops / time_kernel(lambda: ops.conv_wgrad_into(xv, yv, dwp, MODE_CONV, 3, 1, 1, use_tc=1))
+    return {k: v / 1e12 for k, v in out.items()}, flops
+
+
+def run_ours(args):
+    import semantic_segmentation_b200 as S
+    from oracle import genseg_oracle as O
+    from semantic_segmentation_b200 import _lib, parallel
+    from semantic_segmentation_b200.optim import RMSprop
+    from semantic_segmentation_b200.unet import UNet
+    from semantic_segmentation_b200.util.dice_score import seg_loss
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        parallel.init_data_parallel(sync_bn=not args.no_sync_bn)
+    rank = parallel.rank()
+    lib = _lib.load()
+    S.set_precision("bf16")
+    if GLOBAL_BATCH % world != 0:
+        raise SystemExit("global batch 64 must be divisible by the number of GPUs")
+    per = args.per_gpu_batch or GLOBAL_BATCH // world
+    net = UNet(1, N_CLASSES, True)
+    net.load_state_dict(O.seeded_state(O.unet_state_spec(1, N_CLASSES, True), 1234))
+    net = net.to(dev).train()
+    params = list(net.parameters())
+    opt = RMSprop(params, lr=1e-4, weight_decay=1e-8, momentum=0.9)
+    opt.grad_scale = 1.0 / world
+    xg, yg = synthetic_batch(per * world)
+    lo, hi = rank * per, (rank + 1) * per
+    x_host, y_host = xg[lo:hi].contiguous().pin_memory(), yg[lo:hi].contiguous().pin_memory()
+    x_dev, y_dev = x_host.to(dev), y_host.to(dev)
+
+    def step(x, y):
+        opt.zero_grad(set_to_none=True)
+        loss = seg_loss(net(x), y)
+        loss.backward()
+        parallel.allreduce_gradients(params)
+        opt.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(steps):
+            fn()
+        e.record()
+        barrier()
+        t = torch.tensor([s.elapsed_time(e) * 1e-3], device=dev, dtype=torch.float64)
+        if world > 1:
+            torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(max(args.warmup, 3)):
+        step(x_dev, y_dev)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    l0 = lib.gsb_launch_count()
+    t_dev = timed(lambda: step(x_dev, y_dev), args.steps)
+    launches = int(lib.gsb_launch_count() - l0)
+    clocks = sampler.stop() if rank == 0 else None
+
+    def e2e_step():
+        xd = x_host.to(dev, non_blocking=True)
+        yd = y_host.to(dev, non_blocking=True)
+        return float(step(xd, yd).item())      # device -> host read of the step's loss
+
+    e2e_step()
+    t_e2e = timed(e2e_step, args.steps)
+    images = per * world * args.steps
+    value, e2e = images / t_dev, images / t_e2e
+    if rank != 0:
+        return
+    burst, sustained, hbm, src = peaks()
+    kern, flops = dominant_kernel_roofline(per)
+    step_tf = TRAIN_GF_PER_IMG * 1e9 * per * args.steps / t_dev / 1e12
+    line = {"metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True,
+            "scaling": "strong" if not args.per_gpu_batch else "weak", "vs_baseline": None, "dtype": "bf16",
+            "data": "synthetic",
+            "config": {"workload": "U-Net(n_channels=1,n_classes=2,bilinear) 256x256 train step: fwd + CE+Dice + bwd + RMSprop",
+                       "global_batch": per * world, "per_gpu_batch": per, "parallelism": "dp%d" % world,
+                       "sync_bn": bool(world > 1 and not args.no_sync_bn),
+                       "l2": "per-step working set (activations+gradients, >1 GB per GPU) exceeds the 126 MB L2; no flush needed"},
+            "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": int(x_host.numel() * 4 + y_host.numel() * 8) * world,
+                    "d2h_bytes_per_step": 4 * world},
+            "gpu_launches": launches, "clocks": clocks,
+            "roofline": {"bound": "tensor", "kernel": "conv_tc_fprop_kernel<64> (up4.conv[0] 128->64 3x3 @256^2)",
+                         "achieved": kern["fprop"], "peak": burst, "unit": "TFLOP/s", "frac": kern["fprop"] / burst,
+                         "traffic": None, "peak_source": src, "flops_per_launch": flops,
+                         "other_kernels_tflops": {"dgrad<128>": kern["dgrad"], "wgrad<64>": kern["wgrad"]},
+                         "whole_step_tflops_per_gpu": step_tf, "whole_step_frac_of_sustained": step_tf / sustained}}
+    if world == 1 and not args.no_cpu_baseline:
+        t, threads = cpu_oracle_step_time(4, 3, 1)
+        line["cpu_baseline"] = {"value": 4 / t, "unit": "images/s", "cores": threads, "kind": "port",
+                                "sample": "batch 4 x 3 steps (median) of the same U-Net step on the host cores"}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--per-gpu-batch", type=int, default=0, help="override 64/N (weak scaling experiments)")
+    ap.add_argument("--no-sync-bn", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 path has no CPU fallback (use --impl reference)")
+    run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

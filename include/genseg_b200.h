@@ -1,0 +1,182 @@
+/* genseg_b200 -- C ABI of the B200-native GenSeg hot path (libgenseg_b200.so).
+ *
+ * The reference (importZL/semantic_segmentation) has no FFI/plugin seam: its hot path is
+ * Python nn.Modules calling torch.nn layers.  This header is the
+ * boundary a maintainer binds instead of those library calls; every entry point cites the
+ * reference line(s) whose arithmetic it replaces.  Plain pointers and sizes only; the caller
+ * owns every buffer; all functions enqueue on the caller's CUDA stream and return
+ * 0 on success, <0 on error (message via gsb_last_error()).  There is no CPU fallback.
+ */
+#ifndef GENSEG_B200_H
+#define GENSEG_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSB_F32 0
+#define GSB_BF16 1
+
+#define GSB_ACT_NONE 0
+#define GSB_ACT_RELU 1
+#define GSB_ACT_LRELU 2 /* negative slope 0.2, networks.py:583,640 */
+#define GSB_ACT_TANH 3
+
+#define GSB_MODE_CONV 0  /* gather: iy = oy*stride - pad + ky           (nn.Conv2d) */
+#define GSB_MODE_CONVT 1 /* gather: iy = (oy + pad - ky)/stride if exact (nn.ConvTranspose2d) */
+
+/* A 4-D activation view with element strides (NHWC buffers, channel slices of concat
+ * buffers and NCHW fp32 tensors at the API edge are all expressible). */
+typedef struct {
+  void* ptr;
+  int32_t dtype; /* GSB_F32 | GSB_BF16 */
+  int32_t n, h, w, c;
+  int64_t sn, sh, sw, sc; /* strides in elements */
+} gsb_view;
+
+typedef struct {
+  int32_t mode; /* GSB_MODE_* */
+  int32_t kh, kw, stride, pad;
+} gsb_conv_geom;
+
+typedef void* gsb_stream; /* cudaStream_t */
+
+int gsb_version(void);
+const char* gsb_last_error(void);
+/* 1 if the running device is sm_100 and the tcgen05 kernels can launch. */
+int gsb_tc_available(void);
+/* Number of kernels this library has launched in the calling process (bench evidence). */
+unsigned long long gsb_launch_count(void);
+
+/* ---- layout / packing -------------------------------------------------------------- */
+/* dst <- cast(src) element-wise over (n,h,w,c) with arbitrary strides (NCHW<->NHWC, dtype). */
+int gsb_copy_view(const gsb_view* src, const gsb_view* dst, gsb_stream s);
+/* Pack a torch weight into the GEMM operand layout Wp[tap][rows][cols] (cols contiguous).
+ * src is fp32 [d0][d1][kh][kw] (Conv2d: OIHW, unet_parts.py:16; ConvTranspose2d: IOHW,
+ * operations.py:18).  rows_from_d0 != 0 -> rows = d0, cols = d1; else rows = d1, cols = d0. */
+int gsb_pack_weight(const float* src, int d0, int d1, int kh, int kw, int rows_from_d0, void* dst,
+                    int dst_dtype, gsb_stream s);
+/* Inverse for gradients: dWp fp32 [tap][rows][cols] -> torch layout fp32 [d0][d1][kh][kw];
+ * accumulate != 0 adds into dst. */
+int gsb_unpack_wgrad(const float* src, int d0, int d1, int kh, int kw, int rows_from_d0, float* dst,
+                     int accumulate, gsb_stream s);
+/* Mixed transposed-conv cell (networks.py:495-511, operations.py:14-39): softmax(alpha[3])-
+ * weighted, zero-padded sum of the IOHW k4/k6/k8 weights -> one IOHW 8x8 fp32 weight, and
+ * merged bias (nullable).  SURVEY fact 4. */
+int gsb_merge_upconv(const float* w4, const float* w6, const float* w8, const float* b4, const float* b6,
+                     const float* b8, const float* alpha, int cin, int cout, float* w_merged,
+                     float* b_merged, gsb_stream s);
+/* Backward of gsb_merge_upconv: given dW (8x8 IOHW fp32) and db (nullable), produce
+ * dW4/dW6/dW8 (+db4/6/8) and ACCUMULATE dalpha[3] (through the softmax Jacobian). */
+int gsb_unmerge_upconv(const float* dw_merged, const float* db_merged, const float* w4, const float* w6,
+                       const float* w8, const float* b4, const float* b6, const float* b8,
+                       const float* alpha, int cin, int cout, float* dw4, float* dw6, float* dw8,
+                       float* db4, float* db6, float* db8, float* dalpha, void* workspace,
+                       size_t workspace_bytes, gsb_stream s);
+
+/* ---- convolution (replaces cuDNN behind nn.Conv2d / nn.ConvTranspose2d) ------------- */
+/* out = act(gather-conv(in, Wp) + bias).  Wp = [kh*kw][cout][cin], dtype wdtype.
+ * Forward and data-gradient of both Conv2d and ConvTranspose2d are this one primitive
+ * (mode + packing choose which).  use_tc: 0 = SIMT kernel (any shape, fp32 or bf16),
+ * 1 = tcgen05/TMEM/TMA implicit GEMM (bf16 NHWC, cin%64==0, cout%64==0), 2 = auto.
+ * stats_partial (nullable, TC path only): fp32 [m_tiles][2][cout] per-CTA sum / sum-of-squares
+ * of the bf16-rounded outputs for BatchNorm; *stats_rows receives m_tiles.
+ * accumulate != 0: out += result (SIMT path only). */
+int gsb_conv_gather(const gsb_view* in, const void* wp, int wdtype, const float* bias, const gsb_view* out,
+                    const gsb_conv_geom* g, int act, int accumulate, int use_tc, float* stats_partial,
+                    int* stats_rows, gsb_stream s);
+size_t gsb_conv_stats_rows(const gsb_view* out, const gsb_conv_geom* g);
+/* dWp[tap][cout][cin] (fp32, ACCUMULATED into -- caller zeroes) =
+ * sum_pixels dout[pix][cout] * in[pix@tap][cin], with the forward op's gather mode. */
+int gsb_conv_wgrad(const gsb_view* in, const gsb_view* dout, float* dwp, const gsb_conv_geom* g, int use_tc,
+                   gsb_stream s);
+/* Per-channel sum over pixels (conv bias gradient), fp32 accumulate into db[c]. */
+int gsb_bias_grad(const gsb_view* dout, float* db, gsb_stream s);
+
+/* ---- BatchNorm2d (+ activation, dropout) -- unet_parts.py:17-21, networks.py:584-607 -- */
+/* sums[2][c] (fp64) <- sum x, sum x^2 over (n,h,w); workspace >= gsb_bn_workspace_bytes. */
+size_t gsb_bn_workspace_bytes(const gsb_view* x);
+int gsb_bn_reduce(const gsb_view* x, double* sums, void* workspace, size_t workspace_bytes, gsb_stream s);
+/* Reduce TC-conv per-CTA partials [rows][2][c] fp32 -> sums[2][c] fp64. */
+int gsb_bn_reduce_partials(const float* partial, int rows, int c, double* sums, gsb_stream s);
+/* Training finalize: mean/biased var from sums & count -> scale = g*invstd, shift = b - mean*scale,
+ * saves mean/invstd; running stats updated with momentum and UNBIASED var; nbt += 1 (all nullable
+ * except sums/scale/shift).  Eval: pass sums = NULL -> scale/shift from running stats. */
+int gsb_bn_finalize(const double* sums, double count, const float* gamma, const float* beta,
+                    float* running_mean, float* running_var, int64_t* num_batches_tracked, float momentum,
+                    float eps, int c, float* scale, float* shift, float* mean, float* invstd, gsb_stream s);
+/* out1 = act1(drop(x*scale+shift)); out2 (nullable) = act2(x*scale+shift).
+ * scale/shift nullable (identity).  Dropout(0.5) on the out1 path: explicit keep-mask drop_mask
+ * (uint8 dense NHWC, nullable) or, if drop_seed != 0, a stateless Philox4x32-10 mask keyed by
+ * (drop_seed, logical element index) that backward recomputes. */
+int gsb_bn_act(const gsb_view* x, const float* scale, const float* shift, int act1, const gsb_view* out1,
+               int act2, const gsb_view* out2, uint64_t drop_seed, const uint8_t* drop_mask, gsb_stream s);
+/* Backward.  dy = act1'(z)*drop*dA1 + act2'(z)*dA2 (dA2 nullable), z = x*scale+shift.
+ * reduce: sums[2][c] fp64 <- sum dy, sum dy*xhat.   apply (has_bn): dx = scale*(dy - s0/cnt - xhat*s1/cnt);
+ * (no bn: pass mean = NULL -> dx = dy).  dgamma/dbeta accumulate (nullable). */
+int gsb_bn_bwd_reduce(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
+                      const float* shift, const float* mean, const float* invstd, int act1, int act2,
+                      uint64_t drop_seed, const uint8_t* drop_mask, double* sums, void* workspace,
+                      size_t workspace_bytes, gsb_stream s);
+int gsb_bn_bwd_apply(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
+                     const float* shift, const float* mean, const float* invstd, int act1, int act2,
+                     uint64_t drop_seed, const uint8_t* drop_mask, const double* sums, double count,
+                     const gsb_view* dx, float* dgamma, float* dbeta, gsb_stream s);
+
+/* ---- pooling / resampling -- unet_parts.py:34,50,57-67 -------------------------------- */
+int gsb_maxpool2_fwd(const gsb_view* x, const gsb_view* y, gsb_stream s);
+/* dx (+)= route(dy) to the first maximum of each 2x2 window of x (PyTorch tie rule). */
+int gsb_maxpool2_bwd(const gsb_view* x, const gsb_view* dy, const gsb_view* dx, int accumulate,
+                     gsb_stream s);
+/* Bilinear x2 upsample (align_corners=True) of x written at offset (pad_top, pad_left) inside
+ * out (rest of out's window zero-filled): nn.Upsample + F.pad + the cat slice write. */
+int gsb_upsample2_fwd(const gsb_view* x, const gsb_view* out, int pad_top, int pad_left, gsb_stream s);
+int gsb_upsample2_bwd(const gsb_view* dout, const gsb_view* dx, int pad_top, int pad_left, gsb_stream s);
+
+/* ---- segmentation losses / metrics -- util/dice_score.py, train_end2end_jsrt.py:136,182 -- */
+/* logits: fp32 NCHW [n][c][h][w]; labels int64 [n][h][w] (values < max(c,2)).
+ * sums (fp64[4]): CE (or BCE) sum, sum p*t, sum p, sum t over the local batch.  The caller may
+ * all-reduce sums across ranks before finalize (global-batch Dice). */
+int gsb_seg_loss_reduce(const float* logits, const int64_t* labels, int n, int c, int h, int w, double* sums,
+                        void* workspace, size_t workspace_bytes, gsb_stream s);
+size_t gsb_seg_loss_workspace_bytes(int n, int c, int h, int w);
+/* out[3] fp32: total, ce, dice_loss.  count = global n*h*w. */
+int gsb_seg_loss_finalize(const double* sums, double count, float* out, gsb_stream s);
+/* dlogits = gscale * d(total)/dlogits. */
+int gsb_seg_loss_bwd(const float* logits, const int64_t* labels, int n, int c, int h, int w,
+                     const double* sums, double count, const float* gscale, float* dlogits, gsb_stream s);
+/* evaluate(): mask = sigmoid(x)>0.5 (c==1) or argmax (first max wins); integer counts per
+ * (image, class>=1): counts[n][max(c-1,1)][3] int64 = inter, pred, true.  unet/evaluate.py:29-40. */
+int gsb_eval_counts(const float* logits, const int64_t* labels, int n, int c, int h, int w, uint8_t* mask,
+                    int64_t* counts, gsb_stream s);
+/* dice_coeff pieces: per-slice sums[slices][3] fp64 = sum a*b, sum a, sum b over `inner` elements. */
+int gsb_dice_sums(const float* a, const float* b, int64_t slices, int64_t inner, double* sums, gsb_stream s);
+
+/* ---- GAN / L1 losses -- networks.py:263-281, pix2pix_model.py:73,127 -------------------- */
+/* mode 0 vanilla (BCE-with-logits vs constant label), 1 lsgan (MSE), 2 wgangp (+-mean).
+ * loss[0] (fp32) = mean; dpred (nullable) = gscale * dloss/dpred. */
+int gsb_gan_loss(const float* pred, int64_t numel, int mode, float label, float* loss, const float* gscale,
+                 float* dpred, void* workspace /* 8 bytes, needed when loss != NULL */, gsb_stream s);
+int gsb_l1_loss(const float* a, const float* b, int64_t numel, float* loss, const float* gscale, float* da,
+                void* workspace /* 8 bytes, needed when loss != NULL */, gsb_stream s);
+
+/* dx = dout * act'(.) from the activation OUTPUT (contiguous fp32; the Tanh of the generator's
+ * outermost block, networks.py:592). */
+int gsb_act_bwd(const float* out, const float* dout, int act, float* dx, int64_t numel, gsb_stream s);
+
+/* ---- optimisers -- train_end2end_jsrt.py:71-72, pix2pix_model.py:75-78 ------ */
+/* torch.optim.RMSprop(momentum, weight_decay, alpha, eps, centered=False) over a flat fp32 range. */
+int gsb_rmsprop_step(float* p, const float* g, float* square_avg, float* mom_buf, int64_t numel, float lr,
+                     float alpha, float eps, float weight_decay, float momentum, float grad_scale,
+                     gsb_stream s);
+/* torch.optim.Adam (no amsgrad). step = 1-based step count. */
+int gsb_adam_step(float* p, const float* g, float* exp_avg, float* exp_avg_sq, int64_t numel, float lr,
+                  float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,
+                  gsb_stream s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GENSEG_B200_H */

@@ -1,0 +1,53 @@
+// Error plumbing, version and device queries of libgenseg_b200.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace gsb {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+static unsigned long long g_launches = 0;
+unsigned long long launch_count() { return g_launches; }
+
+int check_launch(const char* what, int n) {
+  g_launches += (unsigned long long)n;
+  cudaError_t e = cudaPeekAtLastError();
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    set_error("%s: CUDA error: %s", what, cudaGetErrorString(e));
+    return -3;
+  }
+  return 0;
+}
+
+int num_sms() {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+        sms <= 0)
+      sms = 148;
+  }
+  return sms;
+}
+
+}  // namespace gsb
+
+extern "C" unsigned long long gsb_launch_count(void) { return gsb::launch_count(); }
+extern "C" int gsb_version(void) { return 100; }
+extern "C" const char* gsb_last_error(void) { return gsb::g_err; }
+extern "C" int gsb_tc_available(void) {
+  int dev = 0, major = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return 0;
+  return major == 10 ? 1 : 0;
+}

@@ -1,0 +1,67 @@
+// C-ABI dispatch for the convolution primitives: tcgen05 path when the shape allows, SIMT otherwise.
+#include "common.cuh"
+
+namespace gsb {
+int conv_gather_direct(const gsb_view* in, const void* wp, int wdtype, const float* bias, const gsb_view* out,
+                       const gsb_conv_geom* g, int act, int accumulate, cudaStream_t st);
+int conv_wgrad_direct(const gsb_view* in, const gsb_view* dout, float* dwp, const gsb_conv_geom* g, cudaStream_t st);
+bool conv_tc_supported(const gsb_view* in, const gsb_view* out, const gsb_conv_geom* g);
+int conv_gather_tc(const gsb_view* in, const void* wp, const float* bias, const gsb_view* out, const gsb_conv_geom* g, int act,
+                   float* stats, int* stats_rows, cudaStream_t st);
+int conv_wgrad_tc(const gsb_view* in, const gsb_view* dout, float* dwp, const gsb_conv_geom* g, cudaStream_t st);
+int conv_tc_m_tiles(const gsb_view* out);
+
+static int out_extent(int mode, int in, int k, int stride, int pad) {
+  return mode == GSB_MODE_CONV ? (in + 2 * pad - k) / stride + 1 : (in - 1) * stride - 2 * pad + k;
+}
+}  // namespace gsb
+
+using namespace gsb;
+
+static int check_geom(const gsb_conv_geom* g) {
+  GSB_REQUIRE(g != nullptr, "conv: null geometry");
+  GSB_REQUIRE(g->mode == GSB_MODE_CONV || g->mode == GSB_MODE_CONVT, "conv: bad mode %d", g->mode);
+  GSB_REQUIRE(g->kh >= 1 && g->kw >= 1 && g->stride >= 1 && g->pad >= 0, "conv: bad geometry");
+  return 0;
+}
+
+extern "C" size_t gsb_conv_stats_rows(const gsb_view* out, const gsb_conv_geom* g) {
+  (void)g;
+  return (size_t)conv_tc_m_tiles(out);
+}
+
+extern "C" int gsb_conv_gather(const gsb_view* in, const void* wp, int wdtype, const float* bias, const gsb_view* out,
+                               const gsb_conv_geom* g, int act, int accumulate, int use_tc, float* stats_partial,
+                               int* stats_rows, gsb_stream s) {
+  if (check_geom(g)) return -1;
+  GSB_REQUIRE(in && out && wp && in->ptr && out->ptr, "conv_gather: null argument");
+  GSB_REQUIRE(in->n == out->n, "conv_gather: batch mismatch");
+  // gather-conv: `in` is the source; the source->destination relation is (mode, stride, pad)
+  if (g->mode == GSB_MODE_CONV) {
+    GSB_REQUIRE(out->h == out_extent(GSB_MODE_CONV, in->h, g->kh, g->stride, g->pad) &&
+                    out->w == out_extent(GSB_MODE_CONV, in->w, g->kw, g->stride, g->pad),
+                "conv_gather: output extent %dx%d does not match conv of %dx%d", out->h, out->w, in->h, in->w);
+  } else {
+    // transposed gather: any out extent whose forward conv gives back `in` is legal (output_padding)
+    GSB_REQUIRE(out_extent(GSB_MODE_CONV, out->h, g->kh, g->stride, g->pad) == in->h &&
+                    out_extent(GSB_MODE_CONV, out->w, g->kw, g->stride, g->pad) == in->w,
+                "conv_gather: output extent %dx%d does not match transposed conv of %dx%d", out->h, out->w, in->h, in->w);
+  }
+  if (stats_rows) *stats_rows = 0;
+  bool tc_ok = wdtype == GSB_BF16 && !accumulate && gsb_tc_available() && conv_tc_supported(in, out, g);
+  if (use_tc == 1) GSB_REQUIRE(tc_ok, "conv_gather: tcgen05 path requested but shape/dtype unsupported");
+  if (use_tc != 0 && tc_ok) return conv_gather_tc(in, wp, bias, out, g, act, stats_partial, stats_rows, gsb::to_stream(s));
+  GSB_REQUIRE(stats_partial == nullptr || use_tc != 1, "conv_gather: stats need the tcgen05 path");
+  return conv_gather_direct(in, wp, wdtype, bias, out, g, act, accumulate, gsb::to_stream(s));
+}
+
+extern "C" int gsb_conv_wgrad(const gsb_view* in, const gsb_view* dout, float* dwp, const gsb_conv_geom* g, int use_tc,
+                              gsb_stream s) {
+  if (check_geom(g)) return -1;
+  GSB_REQUIRE(in && dout && dwp && in->ptr && dout->ptr, "conv_wgrad: null argument");
+  GSB_REQUIRE(in->n == dout->n, "conv_wgrad: batch mismatch");
+  bool tc_ok = gsb_tc_available() && conv_tc_supported(in, dout, g);
+  if (use_tc == 1) GSB_REQUIRE(tc_ok, "conv_wgrad: tcgen05 path requested but shape/dtype unsupported");
+  if (use_tc != 0 && tc_ok) return conv_wgrad_tc(in, dout, dwp, g, gsb::to_stream(s));
+  return conv_wgrad_direct(in, dout, dwp, g, gsb::to_stream(s));
+}

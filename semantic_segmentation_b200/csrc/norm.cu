@@ -1,0 +1,379 @@
+// BatchNorm2d statistics / apply / backward fused with activation and dropout.
+// Replaces nn.BatchNorm2d + nn.ReLU / nn.LeakyReLU(0.2) / nn.Dropout(0.5) of
+// unet/unet_parts.py:17-21 and models_pix2pix/networks.py:583-607,648-657.
+//
+// All kernels are HBM-bound: every thread owns 8 consecutive channels (one 128-bit access in
+// bf16) of a pixel and a fixed channel group, so per-channel parameters live in registers.
+// Algorithmic bytes: reduce = 1 read; act = 1 read + 1 (or 2) writes; bwd_reduce = 2 (3) reads;
+// bwd_apply = 2 (3) reads + 1 write -- at the storage dtype.
+#include "common.cuh"
+
+namespace gsb {
+
+constexpr int kThreads = 256;
+
+struct PixView {  // pixel-linear view
+  void* ptr;
+  int64_t ld;
+};
+
+template <typename T>
+__device__ __forceinline__ void load8(const PixView& v, int64_t p, int c0, float (&f)[8]) {
+  Vec8<T>::load(reinterpret_cast<const T*>(v.ptr) + p * v.ld + c0, f);
+}
+template <typename T>
+__device__ __forceinline__ void store8(const PixView& v, int64_t p, int c0, const float (&f)[8]) {
+  Vec8<T>::store(reinterpret_cast<T*>(v.ptr) + p * v.ld + c0, f);
+}
+
+__device__ __forceinline__ void load_param8(const float* p, int c0, float (&f)[8], float dflt) {
+  if (p == nullptr) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) f[i] = dflt;
+  } else {
+    float4 a = __ldg(reinterpret_cast<const float4*>(p + c0));
+    float4 b = __ldg(reinterpret_cast<const float4*>(p + c0 + 4));
+    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w;
+    f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+  }
+}
+
+// keep bits for the 8 channels of (pixel p, channel group c0); logical index = p*C + c0
+__device__ __forceinline__ uint32_t keep_bits(uint64_t seed, const uint8_t* mask, int64_t p, int C, int c0) {
+  if (mask != nullptr) {
+    const uint8_t* m = mask + p * C + c0;
+    uint2 r = *reinterpret_cast<const uint2*>(m);
+    uint32_t bits = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      bits |= ((r.x >> (8 * i)) & 0xFFu ? 1u : 0u) << i;
+      bits |= ((r.y >> (8 * i)) & 0xFFu ? 1u : 0u) << (4 + i);
+    }
+    return bits;
+  }
+  if (seed != 0) return dropout_keep8(seed, (uint64_t)p * (uint64_t)C + (uint64_t)c0);
+  return 0xFFu;
+}
+
+// ---------------------------------------------------------------------------------------
+// Per-channel reductions.  MODE 0: sum x, sum x^2.   MODE 1: sum dy, sum dy*xhat.
+// Block partials -> partial[block][2][C] fp32; second kernel reduces blocks in fp64.
+// ---------------------------------------------------------------------------------------
+template <typename T, int MODE>
+__global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
+    PixView x, PixView dA1, PixView dA2, int64_t P, int C, const float* __restrict__ scale,
+    const float* __restrict__ shift, const float* __restrict__ mean, const float* __restrict__ invstd, int act1,
+    int act2, uint64_t drop_seed, const uint8_t* __restrict__ drop_mask, float* __restrict__ partial) {
+  extern __shared__ float red[];  // [lanes][2][C]
+  const int G = C >> 3;
+  const int lanes = kThreads / G;
+  const int g = threadIdx.x % G, lane = threadIdx.x / G;
+  const int c0 = g * 8;
+  float s0[8], s1[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s0[i] = s1[i] = 0.f;
+  float sc[8], sh[8], mu[8], is[8];
+  if (MODE == 1) {
+    load_param8(scale, c0, sc, 1.f);
+    load_param8(shift, c0, sh, 0.f);
+    load_param8(mean, c0, mu, 0.f);
+    load_param8(invstd, c0, is, 1.f);
+  }
+  const bool has_drop = (drop_seed != 0) || (drop_mask != nullptr);
+  for (int64_t p = (int64_t)blockIdx.x * lanes + lane; p < P; p += (int64_t)gridDim.x * lanes) {
+    float v[8];
+    load8<T>(x, p, c0, v);
+    if (MODE == 0) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        s0[i] += v[i];
+        s1[i] = fmaf(v[i], v[i], s1[i]);
+      }
+    } else {
+      float a[8], b[8];
+      load8<T>(dA1, p, c0, a);
+      if (dA2.ptr != nullptr) load8<T>(dA2, p, c0, b);
+      uint32_t keep = has_drop ? keep_bits(drop_seed, drop_mask, p, C, c0) : 0xFFu;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float z = fmaf(v[i], sc[i], sh[i]);
+        float dm = has_drop ? (((keep >> i) & 1u) ? 2.f : 0.f) : 1.f;
+        float dy = a[i] * dm * act_grad(z * dm, act1);
+        if (dA2.ptr != nullptr) dy += b[i] * act_grad(z, act2);
+        float xh = (v[i] - mu[i]) * is[i];
+        s0[i] += dy;
+        s1[i] = fmaf(dy, xh, s1[i]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    red[(lane * 2 + 0) * C + c0 + i] = s0[i];
+    red[(lane * 2 + 1) * C + c0 + i] = s1[i];
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < 2 * C; j += kThreads) {
+    float acc = 0.f;
+    for (int l = 0; l < lanes; ++l) acc += red[l * 2 * C + j];
+    partial[(int64_t)blockIdx.x * 2 * C + j] = acc;
+  }
+}
+
+__global__ void reduce_partials_kernel(const float* __restrict__ partial, int rows, int n, double* __restrict__ sums) {
+  // one warp per output column j in [0, n): fixed summation order -> deterministic
+  int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= n) return;
+  double acc = 0.0;
+  for (int r = lane; r < rows; r += 32) acc += (double)partial[(int64_t)r * n + warp];
+  acc = warp_sum_d(acc);
+  if (lane == 0) sums[warp] = acc;
+}
+
+__global__ void bn_finalize_kernel(const double* __restrict__ sums, double count, const float* __restrict__ gamma,
+                                   const float* __restrict__ beta, float* running_mean, float* running_var,
+                                   int64_t* nbt, float momentum, float eps, int C, float* scale, float* shift,
+                                   float* mean_out, float* invstd_out) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c == 0 && nbt != nullptr && sums != nullptr) *nbt += 1;
+  if (c >= C) return;
+  float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
+  float m, is;
+  if (sums != nullptr) {
+    double mu = sums[c] / count;
+    double var = sums[C + c] / count - mu * mu;
+    if (var < 0.0) var = 0.0;
+    m = (float)mu;
+    is = (float)(1.0 / sqrt(var + (double)eps));
+    if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * m;
+    if (running_var) {
+      double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
+      running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+    }
+  } else {
+    m = running_mean[c];
+    is = 1.f / sqrtf(running_var[c] + eps);
+  }
+  float sc = g * is;
+  scale[c] = sc;
+  shift[c] = b - m * sc;
+  if (mean_out) mean_out[c] = m;
+  if (invstd_out) invstd_out[c] = is;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, int C, const float* __restrict__ scale,
+                                                         const float* __restrict__ shift, int act1, PixView out1,
+                                                         int act2, PixView out2, uint64_t drop_seed,
+                                                         const uint8_t* __restrict__ drop_mask) {
+  const int G = C >> 3;
+  const int lanes = kThreads / G;
+  const int g = threadIdx.x % G, lane = threadIdx.x / G;
+  const int c0 = g * 8;
+  float sc[8], sh[8];
+  load_param8(scale, c0, sc, 1.f);
+  load_param8(shift, c0, sh, 0.f);
+  const bool has_drop = (drop_seed != 0) || (drop_mask != nullptr);
+  for (int64_t p = (int64_t)blockIdx.x * lanes + lane; p < P; p += (int64_t)gridDim.x * lanes) {
+    float v[8], o1[8], o2[8];
+    load8<T>(x, p, c0, v);
+    uint32_t keep = has_drop ? keep_bits(drop_seed, drop_mask, p, C, c0) : 0xFFu;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float z = fmaf(v[i], sc[i], sh[i]);
+      float dm = has_drop ? (((keep >> i) & 1u) ? 2.f : 0.f) : 1.f;
+      o1[i] = act_fwd(z * dm, act1);
+      o2[i] = act_fwd(z, act2);
+    }
+    store8<T>(out1, p, c0, o1);
+    if (out2.ptr != nullptr) store8<T>(out2, p, c0, o2);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
+    PixView x, PixView dA1, PixView dA2, int64_t P, int C, const float* __restrict__ scale,
+    const float* __restrict__ shift, const float* __restrict__ mean, const float* __restrict__ invstd, int act1,
+    int act2, uint64_t drop_seed, const uint8_t* __restrict__ drop_mask, const double* __restrict__ sums,
+    double inv_count, PixView dx) {
+  const int G = C >> 3;
+  const int lanes = kThreads / G;
+  const int g = threadIdx.x % G, lane = threadIdx.x / G;
+  const int c0 = g * 8;
+  float sc[8], sh[8], mu[8], is[8], m0[8], m1[8];
+  load_param8(scale, c0, sc, 1.f);
+  load_param8(shift, c0, sh, 0.f);
+  const bool has_bn = mean != nullptr;
+  load_param8(mean, c0, mu, 0.f);
+  load_param8(invstd, c0, is, 1.f);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    m0[i] = has_bn ? (float)(sums[c0 + i] * inv_count) : 0.f;
+    m1[i] = has_bn ? (float)(sums[C + c0 + i] * inv_count) : 0.f;
+  }
+  const bool has_drop = (drop_seed != 0) || (drop_mask != nullptr);
+  for (int64_t p = (int64_t)blockIdx.x * lanes + lane; p < P; p += (int64_t)gridDim.x * lanes) {
+    float v[8], a[8], b[8], o[8];
+    load8<T>(x, p, c0, v);
+    load8<T>(dA1, p, c0, a);
+    if (dA2.ptr != nullptr) load8<T>(dA2, p, c0, b);
+    uint32_t keep = has_drop ? keep_bits(drop_seed, drop_mask, p, C, c0) : 0xFFu;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float z = fmaf(v[i], sc[i], sh[i]);
+      float dm = has_drop ? (((keep >> i) & 1u) ? 2.f : 0.f) : 1.f;
+      float dy = a[i] * dm * act_grad(z * dm, act1);
+      if (dA2.ptr != nullptr) dy += b[i] * act_grad(z, act2);
+      if (has_bn) {
+        float xh = (v[i] - mu[i]) * is[i];
+        o[i] = sc[i] * (dy - m0[i] - xh * m1[i]);
+      } else {
+        o[i] = dy * sc[i];
+      }
+    }
+    store8<T>(dx, p, c0, o);
+  }
+}
+
+__global__ void bn_param_grad_kernel(const double* __restrict__ sums, int C, float* dgamma, float* dbeta) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  if (dbeta) dbeta[c] += (float)sums[c];
+  if (dgamma) dgamma[c] += (float)sums[C + c];
+}
+
+static int grid_for(int64_t P, int lanes) {
+  int64_t want = (P + lanes - 1) / lanes;
+  int64_t cap = (int64_t)num_sms() * 8;
+  return (int)(want < cap ? (want > 0 ? want : 1) : cap);
+}
+
+static int check_vec_view(const gsb_view* v, const char* name) {
+  GSB_REQUIRE(v != nullptr && v->ptr != nullptr, "%s: null view", name);
+  GSB_REQUIRE(vec8_ok(v), "%s: view must be pixel-linear NHWC with c%%8==0, ld%%8==0, 16B-aligned", name);
+  GSB_REQUIRE(v->c >= 8 && kThreads % (v->c / 8) == 0, "%s: channel count %d unsupported (c/8 must divide 256)",
+              name, v->c);
+  return 0;
+}
+static PixView pv(const gsb_view* v) { return v ? PixView{v->ptr, v->sw} : PixView{nullptr, 0}; }
+
+}  // namespace gsb
+
+using namespace gsb;
+
+extern "C" size_t gsb_bn_workspace_bytes(const gsb_view* x) {
+  return (size_t)num_sms() * 8 * 2 * (size_t)x->c * sizeof(float);
+}
+
+extern "C" int gsb_bn_reduce(const gsb_view* x, double* sums, void* workspace, size_t workspace_bytes, gsb_stream s) {
+  if (check_vec_view(x, "bn_reduce.x")) return -1;
+  const int C = x->c, lanes = kThreads / (C / 8);
+  const int64_t P = num_pixels(x);
+  int grid = grid_for(P, lanes);
+  GSB_REQUIRE(workspace_bytes >= (size_t)grid * 2 * C * sizeof(float), "bn_reduce: workspace too small");
+  size_t smem = (size_t)lanes * 2 * C * sizeof(float);
+  float* partial = reinterpret_cast<float*>(workspace);
+  PixView nul{nullptr, 0};
+  if (x->dtype == GSB_BF16)
+    bn_reduce_kernel<__nv_bfloat16, 0><<<grid, kThreads, smem, to_stream(s)>>>(pv(x), nul, nul, P, C, nullptr, nullptr,
+                                                                              nullptr, nullptr, 0, 0, 0, nullptr, partial);
+  else
+    bn_reduce_kernel<float, 0><<<grid, kThreads, smem, to_stream(s)>>>(pv(x), nul, nul, P, C, nullptr, nullptr, nullptr,
+                                                                      nullptr, 0, 0, 0, nullptr, partial);
+  int n = 2 * C;
+  reduce_partials_kernel<<<(n * 32 + 255) / 256, 256, 0, to_stream(s)>>>(partial, grid, n, sums);
+  return check_launch("bn_reduce", 2);
+}
+
+extern "C" int gsb_bn_reduce_partials(const float* partial, int rows, int c, double* sums, gsb_stream s) {
+  int n = 2 * c;
+  reduce_partials_kernel<<<(n * 32 + 255) / 256, 256, 0, to_stream(s)>>>(partial, rows, n, sums);
+  return check_launch("bn_reduce_partials");
+}
+
+extern "C" int gsb_bn_finalize(const double* sums, double count, const float* gamma, const float* beta,
+                               float* running_mean, float* running_var, int64_t* num_batches_tracked, float momentum,
+                               float eps, int c, float* scale, float* shift, float* mean, float* invstd, gsb_stream s) {
+  GSB_REQUIRE(scale && shift, "bn_finalize: scale/shift required");
+  GSB_REQUIRE(sums != nullptr || (running_mean && running_var), "bn_finalize: eval mode needs running stats");
+  bn_finalize_kernel<<<(c + 127) / 128, 128, 0, to_stream(s)>>>(sums, count, gamma, beta, running_mean, running_var,
+                                                               num_batches_tracked, momentum, eps, c, scale, shift,
+                                                               mean, invstd);
+  return check_launch("bn_finalize");
+}
+
+extern "C" int gsb_bn_act(const gsb_view* x, const float* scale, const float* shift, int act1, const gsb_view* out1,
+                          int act2, const gsb_view* out2, uint64_t drop_seed, const uint8_t* drop_mask, gsb_stream s) {
+  if (check_vec_view(x, "bn_act.x") || check_vec_view(out1, "bn_act.out1")) return -1;
+  if (out2 && out2->ptr && check_vec_view(out2, "bn_act.out2")) return -1;
+  GSB_REQUIRE(out1->dtype == x->dtype && out1->c == x->c && num_pixels(out1) == num_pixels(x), "bn_act: out1 mismatch");
+  if (out2 && out2->ptr)
+    GSB_REQUIRE(out2->dtype == x->dtype && out2->c == x->c && num_pixels(out2) == num_pixels(x), "bn_act: out2 mismatch");
+  const int C = x->c, lanes = kThreads / (C / 8);
+  const int64_t P = num_pixels(x);
+  int grid = grid_for(P, lanes * 4);
+  PixView o2 = (out2 && out2->ptr) ? pv(out2) : PixView{nullptr, 0};
+  if (x->dtype == GSB_BF16)
+    bn_act_kernel<__nv_bfloat16><<<grid, kThreads, 0, to_stream(s)>>>(pv(x), P, C, scale, shift, act1, pv(out1), act2, o2,
+                                                                      drop_seed, drop_mask);
+  else
+    bn_act_kernel<float><<<grid, kThreads, 0, to_stream(s)>>>(pv(x), P, C, scale, shift, act1, pv(out1), act2, o2,
+                                                              drop_seed, drop_mask);
+  return check_launch("bn_act");
+}
+
+static int check_bwd_views(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2) {
+  if (check_vec_view(x, "bn_bwd.x") || check_vec_view(dA1, "bn_bwd.dA1")) return -1;
+  GSB_REQUIRE(dA1->dtype == x->dtype && dA1->c == x->c && num_pixels(dA1) == num_pixels(x), "bn_bwd: dA1 mismatch");
+  if (dA2 && dA2->ptr) {
+    if (check_vec_view(dA2, "bn_bwd.dA2")) return -1;
+    GSB_REQUIRE(dA2->dtype == x->dtype && dA2->c == x->c && num_pixels(dA2) == num_pixels(x), "bn_bwd: dA2 mismatch");
+  }
+  return 0;
+}
+
+extern "C" int gsb_bn_bwd_reduce(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
+                                 const float* shift, const float* mean, const float* invstd, int act1, int act2,
+                                 uint64_t drop_seed, const uint8_t* drop_mask, double* sums, void* workspace,
+                                 size_t workspace_bytes, gsb_stream s) {
+  if (check_bwd_views(x, dA1, dA2)) return -1;
+  const int C = x->c, lanes = kThreads / (C / 8);
+  const int64_t P = num_pixels(x);
+  int grid = grid_for(P, lanes);
+  GSB_REQUIRE(workspace_bytes >= (size_t)grid * 2 * C * sizeof(float), "bn_bwd_reduce: workspace too small");
+  size_t smem = (size_t)lanes * 2 * C * sizeof(float);
+  float* partial = reinterpret_cast<float*>(workspace);
+  PixView d2 = (dA2 && dA2->ptr) ? pv(dA2) : PixView{nullptr, 0};
+  if (x->dtype == GSB_BF16)
+    bn_reduce_kernel<__nv_bfloat16, 1><<<grid, kThreads, smem, to_stream(s)>>>(
+        pv(x), pv(dA1), d2, P, C, scale, shift, mean, invstd, act1, act2, drop_seed, drop_mask, partial);
+  else
+    bn_reduce_kernel<float, 1><<<grid, kThreads, smem, to_stream(s)>>>(pv(x), pv(dA1), d2, P, C, scale, shift, mean,
+                                                                      invstd, act1, act2, drop_seed, drop_mask, partial);
+  int n = 2 * C;
+  reduce_partials_kernel<<<(n * 32 + 255) / 256, 256, 0, to_stream(s)>>>(partial, grid, n, sums);
+  return check_launch("bn_bwd_reduce", 2);
+}
+
+extern "C" int gsb_bn_bwd_apply(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
+                                const float* shift, const float* mean, const float* invstd, int act1, int act2,
+                                uint64_t drop_seed, const uint8_t* drop_mask, const double* sums, double count,
+                                const gsb_view* dx, float* dgamma, float* dbeta, gsb_stream s) {
+  if (check_bwd_views(x, dA1, dA2) || check_vec_view(dx, "bn_bwd.dx")) return -1;
+  GSB_REQUIRE(dx->dtype == x->dtype && dx->c == x->c && num_pixels(dx) == num_pixels(x), "bn_bwd_apply: dx mismatch");
+  GSB_REQUIRE(mean == nullptr || sums != nullptr, "bn_bwd_apply: sums required with BN");
+  const int C = x->c, lanes = kThreads / (C / 8);
+  const int64_t P = num_pixels(x);
+  int grid = grid_for(P, lanes * 4);
+  PixView d2 = (dA2 && dA2->ptr) ? pv(dA2) : PixView{nullptr, 0};
+  double inv = count > 0 ? 1.0 / count : 0.0;
+  if (x->dtype == GSB_BF16)
+    bn_bwd_apply_kernel<__nv_bfloat16><<<grid, kThreads, 0, to_stream(s)>>>(pv(x), pv(dA1), d2, P, C, scale, shift, mean,
+                                                                            invstd, act1, act2, drop_seed, drop_mask,
+                                                                            sums, inv, pv(dx));
+  else
+    bn_bwd_apply_kernel<float><<<grid, kThreads, 0, to_stream(s)>>>(pv(x), pv(dA1), d2, P, C, scale, shift, mean, invstd,
+                                                                    act1, act2, drop_seed, drop_mask, sums, inv, pv(dx));
+  if (mean != nullptr && (dgamma || dbeta))
+    bn_param_grad_kernel<<<(C + 127) / 128, 128, 0, to_stream(s)>>>(sums, C, dgamma, dbeta);
+  return check_launch("bn_bwd_apply", (mean != nullptr && (dgamma || dbeta)) ? 2 : 1);
+}

@@ -1,0 +1,260 @@
+// MaxPool2d(2) and bilinear x2 upsample (+pad, +concat-slice write): bandwidth kernels.
+// Replaces unet/unet_parts.py:34 (nn.MaxPool2d(2)) and :50,57-67 (nn.Upsample(scale_factor=2,
+// 'bilinear', align_corners=True) -> F.pad -> torch.cat).  128-bit NHWC accesses; the upsample
+// writes straight into the upper channel half of the concat buffer, so no cat copy exists.
+// Algorithmic bytes: pool fwd = 1 read + 1/4 write; upsample fwd = 1/4 read + 1 write.
+#include "common.cuh"
+
+namespace gsb {
+
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool2_fwd_kernel(const T* __restrict__ x, int64_t xld, int N, int H, int W, int C,
+                                                          T* __restrict__ y, int64_t yld) {
+  const int G = C >> 3, OH = H >> 1, OW = W >> 1;
+  const int64_t total = (int64_t)N * OH * OW * G;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int g = (int)(i % G);
+    int64_t p = i / G;
+    int ox = (int)(p % OW);
+    int64_t r = p / OW;
+    int oy = (int)(r % OH);
+    int n = (int)(r / OH);
+    const T* base = x + (((int64_t)n * H + 2 * oy) * W + 2 * ox) * xld + g * 8;
+    float m[8], v[8];
+    Vec8<T>::load(base, m);
+#pragma unroll
+    for (int t = 1; t < 4; ++t) {
+      Vec8<T>::load(base + ((t >> 1) * (int64_t)W + (t & 1)) * xld, v);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (v[k] > m[k] || v[k] != v[k]) m[k] = v[k];
+    }
+    Vec8<T>::store(y + p * yld + g * 8, m);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool2_bwd_kernel(const T* __restrict__ x, int64_t xld, int N, int H, int W, int C,
+                                                          const T* __restrict__ dy, int64_t dyld, T* __restrict__ dx,
+                                                          int64_t dxld, int accumulate) {
+  const int G = C >> 3, OH = H >> 1, OW = W >> 1;
+  const int WH = (H + 1) >> 1, WW = (W + 1) >> 1;  // windows incl. the ragged last row/col
+  const int64_t total = (int64_t)N * WH * WW * G;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int g = (int)(i % G);
+    int64_t p = i / G;
+    int ox = (int)(p % WW);
+    int64_t r = p / WW;
+    int oy = (int)(r % WH);
+    int n = (int)(r / WH);
+    const int64_t pix0 = ((int64_t)n * H + 2 * oy) * W + 2 * ox;
+    if (oy >= OH || ox >= OW) {  // not a pooling window: gradient is zero there
+      if (!accumulate) {
+        float z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (int t = 0; t < 4; ++t) {
+          int yy = 2 * oy + (t >> 1), xx = 2 * ox + (t & 1);
+          if (yy < H && xx < W) Vec8<T>::store(dx + (pix0 + (t >> 1) * (int64_t)W + (t & 1)) * dxld + g * 8, z);
+        }
+      }
+      continue;
+    }
+    float v[4][8], gr[8];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) Vec8<T>::load(x + (pix0 + (t >> 1) * (int64_t)W + (t & 1)) * xld + g * 8, v[t]);
+    Vec8<T>::load(dy + (((int64_t)n * OH + oy) * OW + ox) * dyld + g * 8, gr);
+    int arg[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float m = v[0][k];
+      int a = 0;
+#pragma unroll
+      for (int t = 1; t < 4; ++t)
+        if (v[t][k] > m || v[t][k] != v[t][k]) { m = v[t][k]; a = t; }
+      arg[k] = a;
+    }
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      T* d = dx + (pix0 + (t >> 1) * (int64_t)W + (t & 1)) * dxld + g * 8;
+      float o[8];
+      if (accumulate) Vec8<T>::load(d, o);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float c = arg[k] == t ? gr[k] : 0.f;
+        o[k] = accumulate ? o[k] + c : c;
+      }
+      Vec8<T>::store(d, o);
+    }
+  }
+}
+
+struct Lerp {
+  int i0, i1;
+  float l0, l1;
+};
+// PyTorch align_corners=True source index (ATen UpSample.h: area_pixel_compute_scale /
+// guard_index_and_lambda), all in fp32.
+__device__ __forceinline__ Lerp lerp_for(int o, int in, int out) {
+  float scale = out > 1 ? (float)(in - 1) / (float)(out - 1) : 0.f;
+  float real = scale * (float)o;
+  int i0 = (int)real;
+  if (i0 > in - 1) i0 = in - 1;
+  float l1 = real - (float)i0;
+  l1 = fminf(fmaxf(l1, 0.f), 1.f);
+  Lerp L;
+  L.i0 = i0;
+  L.i1 = i0 + ((i0 + 1 > in - 1) ? 0 : 1);
+  L.l1 = l1;
+  L.l0 = 1.f - l1;
+  return L;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) upsample2_fwd_kernel(const T* __restrict__ x, int64_t xld, int N, int h, int w, int C,
+                                                           T* __restrict__ out, int64_t old, int OH, int OW, int pad_top,
+                                                           int pad_left) {
+  const int G = C >> 3;
+  const int64_t total = (int64_t)N * OH * OW * G;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int g = (int)(i % G);
+    int64_t p = i / G;
+    int ox = (int)(p % OW);
+    int64_t r = p / OW;
+    int oy = (int)(r % OH);
+    int n = (int)(r / OH);
+    int uy = oy - pad_top, ux = ox - pad_left;
+    float o[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (uy >= 0 && uy < 2 * h && ux >= 0 && ux < 2 * w) {
+      Lerp ly = lerp_for(uy, h, 2 * h), lx = lerp_for(ux, w, 2 * w);
+      const T* b = x + (int64_t)n * h * w * xld + g * 8;
+      float v00[8], v01[8], v10[8], v11[8];
+      Vec8<T>::load(b + ((int64_t)ly.i0 * w + lx.i0) * xld, v00);
+      Vec8<T>::load(b + ((int64_t)ly.i0 * w + lx.i1) * xld, v01);
+      Vec8<T>::load(b + ((int64_t)ly.i1 * w + lx.i0) * xld, v10);
+      Vec8<T>::load(b + ((int64_t)ly.i1 * w + lx.i1) * xld, v11);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        o[k] = ly.l0 * (lx.l0 * v00[k] + lx.l1 * v01[k]) + ly.l1 * (lx.l0 * v10[k] + lx.l1 * v11[k]);
+    }
+    Vec8<T>::store(out + p * old + g * 8, o);
+  }
+}
+
+// dx[iy][ix] = sum over upsampled pixels whose lerp touches (iy,ix): exact transpose of the forward.
+template <typename T>
+__global__ void __launch_bounds__(256) upsample2_bwd_kernel(const T* __restrict__ dout, int64_t dld, int N, int OH, int OW,
+                                                           int C, T* __restrict__ dx, int64_t xld, int h, int w, int pad_top,
+                                                           int pad_left) {
+  const int G = C >> 3;
+  const int64_t total = (int64_t)N * h * w * G;
+  const float sy = 2 * h > 1 ? (float)(h - 1) / (float)(2 * h - 1) : 0.f;
+  const float sx = 2 * w > 1 ? (float)(w - 1) / (float)(2 * w - 1) : 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int g = (int)(i % G);
+    int64_t p = i / G;
+    int ix = (int)(p % w);
+    int64_t r = p / w;
+    int iy = (int)(r % h);
+    int n = (int)(r / h);
+    int ylo = 0, yhi = 2 * h - 1, xlo = 0, xhi = 2 * w - 1;
+    if (sy > 0.f) {
+      ylo = max(0, (int)floorf((float)(iy - 1) / sy) - 1);
+      yhi = min(2 * h - 1, (int)ceilf((float)(iy + 1) / sy) + 1);
+    }
+    if (sx > 0.f) {
+      xlo = max(0, (int)floorf((float)(ix - 1) / sx) - 1);
+      xhi = min(2 * w - 1, (int)ceilf((float)(ix + 1) / sx) + 1);
+    }
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int uy = ylo; uy <= yhi; ++uy) {
+      Lerp ly = lerp_for(uy, h, 2 * h);
+      float wy = (ly.i0 == iy ? ly.l0 : 0.f) + (ly.i1 == iy ? ly.l1 : 0.f);
+      if (wy == 0.f) continue;
+      int oy = uy + pad_top;
+      if (oy < 0 || oy >= OH) continue;
+      for (int ux = xlo; ux <= xhi; ++ux) {
+        Lerp lx = lerp_for(ux, w, 2 * w);
+        float wx = (lx.i0 == ix ? lx.l0 : 0.f) + (lx.i1 == ix ? lx.l1 : 0.f);
+        if (wx == 0.f) continue;
+        int ox = ux + pad_left;
+        if (ox < 0 || ox >= OW) continue;
+        float v[8];
+        Vec8<T>::load(dout + (((int64_t)n * OH + oy) * OW + ox) * dld + g * 8, v);
+        float wgt = wy * wx;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = fmaf(wgt, v[k], acc[k]);
+      }
+    }
+    Vec8<T>::store(dx + p * xld + g * 8, acc);
+  }
+}
+
+static int ew_grid(int64_t total) {
+  int64_t b = (total + 255) / 256;
+  int64_t cap = (int64_t)num_sms() * 16;
+  return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+static int chk(const gsb_view* v, const char* nm) {
+  GSB_REQUIRE(v && v->ptr, "%s: null view", nm);
+  GSB_REQUIRE(vec8_ok(v), "%s: view must be pixel-linear NHWC, c%%8==0, 16B aligned", nm);
+  return 0;
+}
+
+}  // namespace gsb
+
+using namespace gsb;
+
+#define DISPATCH_T(dtype, ...)                 \
+  if ((dtype) == GSB_BF16) {                   \
+    using T = __nv_bfloat16;                   \
+    __VA_ARGS__;                               \
+  } else {                                     \
+    using T = float;                           \
+    __VA_ARGS__;                               \
+  }
+
+extern "C" int gsb_maxpool2_fwd(const gsb_view* x, const gsb_view* y, gsb_stream s) {
+  if (chk(x, "maxpool.x") || chk(y, "maxpool.y")) return -1;
+  GSB_REQUIRE(y->n == x->n && y->h == x->h / 2 && y->w == x->w / 2 && y->c == x->c && y->dtype == x->dtype,
+              "maxpool2_fwd: shape mismatch");
+  int64_t total = num_pixels(y) * (x->c / 8);
+  if (total == 0) return 0;
+  DISPATCH_T(x->dtype, maxpool2_fwd_kernel<T><<<ew_grid(total), 256, 0, to_stream(s)>>>(
+                           (const T*)x->ptr, x->sw, x->n, x->h, x->w, x->c, (T*)y->ptr, y->sw));
+  return check_launch("maxpool2_fwd");
+}
+
+extern "C" int gsb_maxpool2_bwd(const gsb_view* x, const gsb_view* dy, const gsb_view* dx, int accumulate, gsb_stream s) {
+  if (chk(x, "maxpool_bwd.x") || chk(dy, "maxpool_bwd.dy") || chk(dx, "maxpool_bwd.dx")) return -1;
+  GSB_REQUIRE(dy->n == x->n && dy->h == x->h / 2 && dy->w == x->w / 2 && dy->c == x->c && dy->dtype == x->dtype,
+              "maxpool2_bwd: dy mismatch");
+  GSB_REQUIRE(dx->n == x->n && dx->h == x->h && dx->w == x->w && dx->c == x->c && dx->dtype == x->dtype,
+              "maxpool2_bwd: dx mismatch");
+  int64_t total = (int64_t)x->n * ((x->h + 1) / 2) * ((x->w + 1) / 2) * (x->c / 8);
+  if (total == 0) return 0;
+  DISPATCH_T(x->dtype, maxpool2_bwd_kernel<T><<<ew_grid(total), 256, 0, to_stream(s)>>>(
+                           (const T*)x->ptr, x->sw, x->n, x->h, x->w, x->c, (const T*)dy->ptr, dy->sw, (T*)dx->ptr, dx->sw,
+                           accumulate));
+  return check_launch("maxpool2_bwd");
+}
+
+extern "C" int gsb_upsample2_fwd(const gsb_view* x, const gsb_view* out, int pad_top, int pad_left, gsb_stream s) {
+  if (chk(x, "upsample.x") || chk(out, "upsample.out")) return -1;
+  GSB_REQUIRE(out->n == x->n && out->c == x->c && out->dtype == x->dtype, "upsample2_fwd: mismatch");
+  int64_t total = num_pixels(out) * (x->c / 8);
+  if (total == 0) return 0;
+  DISPATCH_T(x->dtype, upsample2_fwd_kernel<T><<<ew_grid(total), 256, 0, to_stream(s)>>>(
+                           (const T*)x->ptr, x->sw, x->n, x->h, x->w, x->c, (T*)out->ptr, out->sw, out->h, out->w, pad_top,
+                           pad_left));
+  return check_launch("upsample2_fwd");
+}
+
+extern "C" int gsb_upsample2_bwd(const gsb_view* dout, const gsb_view* dx, int pad_top, int pad_left, gsb_stream s) {
+  if (chk(dout, "upsample_bwd.dout") || chk(dx, "upsample_bwd.dx")) return -1;
+  GSB_REQUIRE(dout->n == dx->n && dout->c == dx->c && dout->dtype == dx->dtype, "upsample2_bwd: mismatch");
+  int64_t total = num_pixels(dx) * (dx->c / 8);
+  if (total == 0) return 0;
+  DISPATCH_T(dx->dtype, upsample2_bwd_kernel<T><<<ew_grid(total), 256, 0, to_stream(s)>>>(
+                            (const T*)dout->ptr, dout->sw, dout->n, dout->h, dout->w, dout->c, (T*)dx->ptr, dx->sw, dx->h,
+                            dx->w, pad_top, pad_left));
+  return check_launch("upsample2_bwd");
+}

@@ -1,0 +1,261 @@
+"""Layer executor of the B200 hot path: explicit forward / backward over NHWC device buffers.
+
+Autograd sees ONE node per network call (see ``functions.py``); inside it every kernel launch,
+saved activation and gradient buffer is managed here, so skip gradients accumulate in place,
+concat buffers are written by their producers, and nothing runs through ATen / cuDNN.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from . import ops
+from ._lib import (ACT_LRELU, ACT_NONE, ACT_RELU, ACT_TANH, MODE_CONV, MODE_CONVT, GsbView, view_nchw, view_nhwc)
+
+BN_EPS = 1e-5
+BN_MOMENTUM = 0.1
+
+_CONFIG = {"dtype": torch.bfloat16, "use_tc": 2, "fused_stats": True}
+
+
+def set_precision(mode: str) -> None:
+    """'bf16' (production: bf16 activations/weights, fp32 accumulate, tcgen05 kernels) or
+    'fp32' (validation mode: fp32 activations/weights through the SIMT kernels)."""
+    if mode == "bf16":
+        _CONFIG["dtype"] = torch.bfloat16
+    elif mode == "fp32":
+        _CONFIG["dtype"] = torch.float32
+    else:
+        raise ValueError("precision must be 'bf16' or 'fp32'")
+
+
+def get_precision() -> str:
+    return "bf16" if _CONFIG["dtype"] == torch.bfloat16 else "fp32"
+
+
+def set_tensor_core_mode(use_tc: int, fused_stats: bool = True) -> None:
+    """0 = SIMT kernels only, 1 = require tcgen05 where requested, 2 = auto (default)."""
+    _CONFIG["use_tc"] = int(use_tc)
+    _CONFIG["fused_stats"] = bool(fused_stats)
+
+
+def act_dtype() -> torch.dtype:
+    return _CONFIG["dtype"]
+
+
+# --- cross-rank reductions (sync-BN / global Dice); installed by parallel.py ----------------------
+_REDUCER = {"fn": None, "world": 1, "sync_bn": False}
+
+
+def install_reducer(fn, world: int, sync_bn: bool) -> None:
+    _REDUCER.update(fn=fn, world=int(world), sync_bn=bool(sync_bn))
+
+
+def _sync_stats(sums: torch.Tensor, count: float) -> Tuple[torch.Tensor, float]:
+    if _REDUCER["sync_bn"] and _REDUCER["fn"] is not None and _REDUCER["world"] > 1:
+        _REDUCER["fn"](sums)
+        return sums, count * _REDUCER["world"]
+    return sums, count
+
+
+@dataclass
+class ConvSpec:
+    """kind 'conv' = nn.Conv2d (weight [cout,cin,k,k]); 'convT' = nn.ConvTranspose2d (weight [cin,cout,k,k])."""
+    kind: str
+    cin: int
+    cout: int
+    k: int
+    stride: int
+    pad: int
+
+    @property
+    def fwd_mode(self) -> int:
+        return MODE_CONV if self.kind == "conv" else MODE_CONVT
+
+    @property
+    def bwd_mode(self) -> int:
+        return MODE_CONVT if self.kind == "conv" else MODE_CONV
+
+    def out_hw(self, h: int, w: int) -> Tuple[int, int]:
+        if self.kind == "conv":
+            return (h + 2 * self.pad - self.k) // self.stride + 1, (w + 2 * self.pad - self.k) // self.stride + 1
+        return (h - 1) * self.stride - 2 * self.pad + self.k, (w - 1) * self.stride - 2 * self.pad + self.k
+
+    def pack_fwd(self, weight: torch.Tensor) -> torch.Tensor:
+        return ops.pack_weight(weight.detach().contiguous(), self.kind == "conv", act_dtype())
+
+    def pack_bwd(self, weight: torch.Tensor) -> torch.Tensor:
+        return ops.pack_weight(weight.detach().contiguous(), self.kind != "conv", act_dtype())
+
+    def weight_shape(self) -> Tuple[int, int, int, int]:
+        if self.kind == "conv":
+            return (self.cout, self.cin, self.k, self.k)
+        return (self.cin, self.cout, self.k, self.k)
+
+
+@dataclass
+class Saved:
+    """What one conv(+BN+act) layer keeps for backward."""
+    x_view: Optional[GsbView] = None
+    x_keep: Optional[torch.Tensor] = None     # keeps x's storage alive
+    y: Optional[torch.Tensor] = None          # raw conv output (pre-BN), NHWC
+    scale: Optional[torch.Tensor] = None
+    shift: Optional[torch.Tensor] = None
+    mean: Optional[torch.Tensor] = None
+    invstd: Optional[torch.Tensor] = None
+    count: float = 0.0
+    weight: Optional[torch.Tensor] = None     # fp32 weight in torch layout as used in forward
+    drop_seed: int = 0
+    drop_mask: Optional[torch.Tensor] = None
+    extra: Dict[str, object] = field(default_factory=dict)
+
+
+def _nhwc_empty(n: int, h: int, w: int, c: int, device, dtype=None, zero: bool = False) -> torch.Tensor:
+    f = torch.zeros if zero else torch.empty
+    return f((n, h, w, c), device=device, dtype=dtype or act_dtype())
+
+
+class ConvBNAct:
+    """conv (+bias) -> [BatchNorm2d] -> act1(dropout(.)) [-> second output act2(.)].
+
+    Covers DoubleConv's halves (unet/unet_parts.py:16-21), the generator's down / up steps
+    (networks.py:582-607) and the discriminator blocks (networks.py:640-657).
+    """
+
+    def __init__(self, spec: ConvSpec, has_bn: bool, act1: int, act2: Optional[int] = None, dropout: bool = False):
+        self.spec, self.has_bn, self.act1, self.act2, self.dropout = spec, has_bn, act1, act2, dropout
+
+    # x_view: GsbView of the input (NHWC act buffer or the NCHW fp32 network input)
+    def forward(self, x_view: GsbView, x_keep, n: int, h: int, w: int, device, weight, bias, bn, training: bool,
+                out1: Optional[torch.Tensor] = None, out2: Optional[torch.Tensor] = None, save: bool = True,
+                drop_seed: int = 0, drop_mask: Optional[torch.Tensor] = None):
+        s = self.spec
+        oh, ow = s.out_hw(h, w)
+        wp = s.pack_fwd(weight)
+        y = _nhwc_empty(n, oh, ow, s.cout, device)
+        want_stats = self.has_bn and training and _CONFIG["fused_stats"]
+        stats, rows = ops.conv_gather(x_view, wp, bias, view_nhwc(y), s.fwd_mode, s.k, s.stride, s.pad,
+                                      use_tc=_CONFIG["use_tc"], want_stats=want_stats)
+        sv = Saved()
+        count = float(n * oh * ow)
+        scale = shift = mean = invstd = None
+        if self.has_bn:
+            gamma, beta, rm, rv, nbt = bn
+            if training:
+                sums = ops.bn_reduce_partials(stats, rows, s.cout) if stats is not None else ops.bn_reduce(y)
+                sums, count = _sync_stats(sums, count)
+                scale, shift, mean, invstd = ops.bn_finalize(sums, count, gamma, beta, rm, rv, nbt, BN_MOMENTUM, BN_EPS,
+                                                             s.cout, device)
+            else:
+                scale, shift, mean, invstd = ops.bn_finalize(None, count, gamma, beta, rm, rv, None, BN_MOMENTUM,
+                                                             BN_EPS, s.cout, device)
+        if out1 is None:
+            out1 = _nhwc_empty(n, oh, ow, s.cout, device)
+        use_drop = self.dropout and training
+        ops.bn_act(y, scale, shift, self.act1, out1, self.act2 if self.act2 is not None else ACT_NONE,
+                   out2 if self.act2 is not None else None, drop_seed if use_drop else 0,
+                   drop_mask if use_drop else None)
+        if save:
+            sv.x_view, sv.x_keep, sv.y = x_view, x_keep, y
+            sv.scale, sv.shift, sv.mean, sv.invstd, sv.count = scale, shift, mean, invstd, count
+            sv.weight = weight
+            sv.drop_seed = drop_seed if use_drop else 0
+            sv.drop_mask = drop_mask if use_drop else None
+            sv.extra["train_bn"] = self.has_bn and training
+        return out1, sv
+
+    def backward(self, sv: Saved, dA1: torch.Tensor, dA2: Optional[torch.Tensor], need_dx: bool, need_dw: bool,
+                 need_bn: bool, need_db: bool, dx_out: Optional[torch.Tensor] = None, dx_view: Optional[GsbView] = None):
+        """Returns (dx, dweight, dbias, dgamma, dbeta).  dx is written to dx_out / dx_view when given."""
+        s = self.spec
+        y = sv.y
+        n, oh, ow, _ = y.shape
+        device = y.device
+        train_bn = bool(sv.extra.get("train_bn"))
+        dY = torch.empty_like(y)
+        dgamma = dbeta = None
+        act2 = self.act2 if self.act2 is not None else ACT_NONE
+        sums = None
+        mean = invstd = None
+        if train_bn:
+            sums = ops.bn_bwd_reduce(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2,
+                                     sv.drop_seed, sv.drop_mask)
+            sums, _ = _sync_stats(sums, 0.0)
+            mean, invstd = sv.mean, sv.invstd
+            if need_bn:
+                dgamma = torch.zeros(s.cout, device=device, dtype=torch.float32)
+                dbeta = torch.zeros(s.cout, device=device, dtype=torch.float32)
+        ops.bn_bwd_apply(y, dA1, dA2, sv.scale, sv.shift, mean, invstd, self.act1, act2, sums, sv.count, dY,
+                         dgamma, dbeta, sv.drop_seed, sv.drop_mask)
+        dyv = view_nhwc(dY)
+        dweight = dbias = None
+        if need_dw:
+            dwp = torch.zeros((s.k * s.k, s.cout, s.cin), device=device, dtype=torch.float32)
+            ops.conv_wgrad_into(sv.x_view, dyv, dwp, s.fwd_mode, s.k, s.stride, s.pad, use_tc=_CONFIG["use_tc"])
+            dweight = ops.unpack_wgrad(dwp, s.weight_shape(), s.kind == "conv")
+        if need_db:
+            dbias = torch.zeros(s.cout, device=device, dtype=torch.float32)
+            ops.bias_grad(dyv, dbias)
+        dx = None
+        if need_dx:
+            wpb = s.pack_bwd(sv.weight)
+            if dx_view is None:
+                if dx_out is None:
+                    xv = sv.x_view
+                    dx_out = _nhwc_empty(xv.n, xv.h, xv.w, xv.c, device)
+                dx_view = view_nhwc(dx_out)
+            ops.conv_gather(dyv, wpb, None, dx_view, s.bwd_mode, s.k, s.stride, s.pad, use_tc=_CONFIG["use_tc"])
+            dx = dx_out
+        return dx, dweight, dbias, dgamma, dbeta
+
+
+class EdgeConv:
+    """conv (+bias) -> act, written straight to an NCHW fp32 tensor (network outputs with 1..3
+    channels: OutConv unet_parts.py:71-77, the discriminator's last conv networks.py:660, the
+    generator's outermost up-cell + Tanh networks.py:590-592)."""
+
+    def __init__(self, spec: ConvSpec, act: int = ACT_NONE):
+        self.spec, self.act = spec, act
+
+    def forward(self, x: torch.Tensor, weight, bias, save: bool = True):
+        s = self.spec
+        n, h, w, _ = x.shape
+        oh, ow = s.out_hw(h, w)
+        out = torch.empty((n, s.cout, oh, ow), device=x.device, dtype=torch.float32)
+        wp = s.pack_fwd(weight)
+        ops.conv_gather(view_nhwc(x), wp, bias, view_nchw(out), s.fwd_mode, s.k, s.stride, s.pad, act=self.act,
+                        use_tc=0)
+        sv = Saved()
+        if save:
+            sv.x_view, sv.x_keep, sv.weight = view_nhwc(x), x, weight
+            sv.extra["out"] = out if self.act != ACT_NONE else None
+        return out, sv
+
+    def backward(self, sv: Saved, dout: torch.Tensor, need_dx: bool, need_dw: bool, need_db: bool,
+                 dx_out: Optional[torch.Tensor] = None):
+        s = self.spec
+        dout = dout.contiguous()
+        if dout.dtype != torch.float32:
+            raise RuntimeError("genseg_b200: gradient of an fp32 output must be fp32")
+        if self.act != ACT_NONE:
+            dout = ops.act_bwd(sv.extra["out"], dout, self.act)
+        dv = view_nchw(dout)
+        device = dout.device
+        dweight = dbias = dx = None
+        if need_dw:
+            dwp = torch.zeros((s.k * s.k, s.cout, s.cin), device=device, dtype=torch.float32)
+            ops.conv_wgrad_into(sv.x_view, dv, dwp, s.fwd_mode, s.k, s.stride, s.pad, use_tc=0)
+            dweight = ops.unpack_wgrad(dwp, s.weight_shape(), s.kind == "conv")
+        if need_db:
+            dbias = torch.zeros(s.cout, device=device, dtype=torch.float32)
+            ops.bias_grad(dv, dbias)
+        if need_dx:
+            xv = sv.x_view
+            if dx_out is None:
+                dx_out = _nhwc_empty(xv.n, xv.h, xv.w, xv.c, device)
+            wpb = s.pack_bwd(sv.weight)
+            ops.conv_gather(dv, wpb, None, view_nhwc(dx_out), s.bwd_mode, s.k, s.stride, s.pad, use_tc=0)
+            dx = dx_out
+        return dx, dweight, dbias

@@ -1,0 +1,64 @@
+"""torch.autograd glue: ONE autograd node per network call.
+
+``ProgramFunction.apply(program, module_buffers, training, x, *params)`` runs the program's explicit
+forward on the CUDA kernels and keeps its tape; backward runs the explicit backward.  It supports
+loss.backward(), torch.autograd.grad(..., allow_unused=True), retain_graph=True (the tape is never
+mutated by backward), torch.no_grad() (nothing saved) and requires_grad_(False) parameters (their
+wgrad kernels are skipped) -- the autograd contract of SURVEY.md section 8b.
+"""
+from __future__ import annotations
+
+from typing import Dict, List
+
+import torch
+
+from ._lib import require_cuda
+
+
+class ProgramFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, program, buffers: Dict[str, torch.Tensor], training: bool, extra, n_in: int, *tensors):
+        xs, params = tensors[:n_in], tensors[n_in:]
+        for x in xs:
+            require_cuda(x, "input")
+        names: List[str] = program.param_names
+        if len(params) != len(names):
+            raise RuntimeError("genseg_b200: expected %d parameters, got %d" % (len(names), len(params)))
+        P = {k: v.detach() for k, v in zip(names, params)}
+        for k, v in P.items():
+            require_cuda(v, k)
+        need_any = torch.is_grad_enabled() and any(t.requires_grad for t in tensors)
+        xin = xs[0].detach() if n_in == 1 else tuple(x.detach() for x in xs)
+        out, tape = program.forward(xin, P, buffers, training, need_any, extra)
+        ctx.program = program
+        ctx.tape = tape if need_any else None
+        ctx.names = names
+        ctx.n_in = n_in
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        if ctx.tape is None:
+            raise RuntimeError("genseg_b200: backward called but no tape was saved")
+        n_in = ctx.n_in
+        need_in = ctx.needs_input_grad  # (program, buffers, training, extra, n_in, *inputs, *params)
+        need = {k: bool(need_in[5 + n_in + i]) for i, k in enumerate(ctx.names)}
+        need_x = [bool(need_in[5 + i]) for i in range(n_in)]
+        dx, G = ctx.program.backward(ctx.tape, dout, need, need_x[0] if n_in == 1 else need_x)
+        dxs = (dx,) if n_in == 1 else tuple(dx)
+        dxs = tuple(d if nx else None for d, nx in zip(dxs, need_x))
+        grads = [G.get(k) if need[k] else None for k in ctx.names]
+        return (None, None, None, None, None, *dxs, *grads)
+
+
+def run_program(program, module: torch.nn.Module, x, extra=None):
+    """Collect the module's parameters/buffers by state_dict name and run the program."""
+    xs = x if isinstance(x, (tuple, list)) else (x,)
+    for t in xs:
+        if not t.is_cuda:
+            raise RuntimeError("genseg_b200: the B200 hot path needs CUDA tensors; there is no CPU fallback "
+                               "(got a %s tensor)" % t.device.type)
+    pd = dict(module.named_parameters())
+    bd = dict(module.named_buffers())
+    params = [pd[k] for k in program.param_names]
+    return ProgramFunction.apply(program, bd, module.training, extra, len(xs), *xs, *params)

@@ -1,0 +1,294 @@
+"""Python wrappers over the C ABI (one function per entry point family).
+
+Tensors are torch CUDA tensors used as typed device buffers; activations inside the engine are
+NHWC ([N,H,W,C], bf16 in production / fp32 in validation mode), possibly channel slices of
+concat buffers.  Everything is enqueued on torch's current CUDA stream.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib as L
+from ._lib import (ACT_LRELU, ACT_NONE, ACT_RELU, ACT_TANH, MODE_CONV, MODE_CONVT, GsbConvGeom, GsbView, check,
+                   load, ptr, stream_ptr, view_nchw, view_nhwc)
+
+__all__ = ["ACT_NONE", "ACT_RELU", "ACT_LRELU", "ACT_TANH", "MODE_CONV", "MODE_CONVT"]
+
+
+def _s(t: torch.Tensor) -> int:
+    return stream_ptr(t.device)
+
+
+def _ref(v: Optional[GsbView]):
+    return C.byref(v) if v is not None else None
+
+
+# ---- layout ---------------------------------------------------------------------------------
+
+def nchw_to_nhwc(x: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    n, c, h, w = x.shape
+    out = torch.empty((n, h, w, c), device=x.device, dtype=dtype)
+    check(load().gsb_copy_view(_ref(view_nchw(x)), _ref(view_nhwc(out)), _s(x)), "copy_view")
+    return out
+
+
+def nhwc_to_nchw(x: torch.Tensor, dtype: torch.dtype = torch.float32) -> torch.Tensor:
+    n, h, w, c = x.shape
+    out = torch.empty((n, c, h, w), device=x.device, dtype=dtype)
+    check(load().gsb_copy_view(_ref(view_nhwc(x)), _ref(view_nchw(out)), _s(x)), "copy_view")
+    return out
+
+
+def copy_view(src: GsbView, dst: GsbView, stream: int) -> None:
+    check(load().gsb_copy_view(_ref(src), _ref(dst), stream), "copy_view")
+
+
+def pack_weight(w: torch.Tensor, rows_from_d0: bool, dtype: torch.dtype) -> torch.Tensor:
+    """fp32 [d0,d1,kh,kw] -> [kh*kw, rows, cols] in `dtype` (cols contiguous)."""
+    assert w.dtype == torch.float32 and w.is_contiguous()
+    d0, d1, kh, kw = w.shape
+    rows, cols = (d0, d1) if rows_from_d0 else (d1, d0)
+    out = torch.empty((kh * kw, rows, cols), device=w.device, dtype=dtype)
+    check(load().gsb_pack_weight(ptr(w), d0, d1, kh, kw, int(rows_from_d0), ptr(out), L.dtype_code(dtype), _s(w)),
+          "pack_weight")
+    return out
+
+
+def unpack_wgrad(dwp: torch.Tensor, shape: Tuple[int, int, int, int], rows_from_d0: bool,
+                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    d0, d1, kh, kw = shape
+    acc = out is not None
+    if out is None:
+        out = torch.empty(shape, device=dwp.device, dtype=torch.float32)
+    check(load().gsb_unpack_wgrad(ptr(dwp), d0, d1, kh, kw, int(rows_from_d0), ptr(out), int(acc), _s(dwp)),
+          "unpack_wgrad")
+    return out
+
+
+def merge_upconv(w4, w6, w8, b4, b6, b8, alpha_row: torch.Tensor):
+    cin, cout = w8.shape[0], w8.shape[1]
+    wm = torch.empty_like(w8)
+    bm = torch.empty_like(b8) if b8 is not None else None
+    check(load().gsb_merge_upconv(ptr(w4), ptr(w6), ptr(w8), ptr(b4), ptr(b6), ptr(b8), ptr(alpha_row), cin, cout,
+                                  ptr(wm), ptr(bm), _s(w8)), "merge_upconv")
+    return wm, bm
+
+
+def unmerge_upconv(dwm, dbm, w4, w6, w8, b4, b6, b8, alpha_row, dalpha_row):
+    cin, cout = w8.shape[0], w8.shape[1]
+    dw4, dw6, dw8 = torch.empty_like(w4), torch.empty_like(w6), torch.empty_like(w8)
+    db4 = db6 = db8 = None
+    if dbm is not None:
+        db4, db6, db8 = torch.empty_like(b4), torch.empty_like(b6), torch.empty_like(b8)
+    ws = torch.empty(4, device=w8.device, dtype=torch.float64)
+    check(load().gsb_unmerge_upconv(ptr(dwm), ptr(dbm), ptr(w4), ptr(w6), ptr(w8), ptr(b4), ptr(b6), ptr(b8),
+                                    ptr(alpha_row), cin, cout, ptr(dw4), ptr(dw6), ptr(dw8), ptr(db4), ptr(db6),
+                                    ptr(db8), ptr(dalpha_row), ptr(ws), ws.numel() * 8, _s(w8)), "unmerge_upconv")
+    return dw4, dw6, dw8, db4, db6, db8
+
+
+# ---- convolution ----------------------------------------------------------------------------
+
+def conv_gather(inp: GsbView, wp: torch.Tensor, bias: Optional[torch.Tensor], out: GsbView, mode: int, k: int,
+                stride: int, pad: int, act: int = ACT_NONE, accumulate: bool = False, use_tc: int = 2,
+                want_stats: bool = False, stream: Optional[int] = None):
+    """Returns (stats_partial, rows) when want_stats and the tcgen05 path ran, else (None, 0)."""
+    lib = load()
+    g = GsbConvGeom(mode, k, k, stride, pad)
+    stats = None
+    rows = C.c_int(0)
+    if want_stats and use_tc != 0 and wp.dtype == torch.bfloat16:
+        nrows = lib.gsb_conv_stats_rows(_ref(out), C.byref(g))
+        stats = torch.empty((nrows, 2, out.c), device=wp.device, dtype=torch.float32)
+    check(lib.gsb_conv_gather(_ref(inp), ptr(wp), L.dtype_code(wp.dtype), ptr(bias), _ref(out), C.byref(g), act,
+                              int(accumulate), use_tc, ptr(stats), C.byref(rows),
+                              stream if stream is not None else _s(wp)), "conv_gather")
+    if stats is not None and rows.value > 0:
+        return stats, rows.value
+    return None, 0
+
+
+def conv_wgrad_into(inp: GsbView, dout: GsbView, dwp: torch.Tensor, mode: int, k: int, stride: int, pad: int,
+                    use_tc: int = 2) -> None:
+    g = GsbConvGeom(mode, k, k, stride, pad)
+    check(load().gsb_conv_wgrad(_ref(inp), _ref(dout), ptr(dwp), C.byref(g), use_tc, _s(dwp)), "conv_wgrad")
+
+
+def bias_grad(dout: GsbView, db: torch.Tensor) -> None:
+    check(load().gsb_bias_grad(_ref(dout), ptr(db), _s(db)), "bias_grad")
+
+
+# ---- batch norm -----------------------------------------------------------------------------
+
+def _bn_ws(v: GsbView, device) -> torch.Tensor:
+    nbytes = load().gsb_bn_workspace_bytes(_ref(v))
+    return torch.empty(nbytes // 4, device=device, dtype=torch.float32)
+
+
+def bn_reduce(x: torch.Tensor) -> torch.Tensor:
+    v = view_nhwc(x)
+    ws = _bn_ws(v, x.device)
+    sums = torch.empty(2 * v.c, device=x.device, dtype=torch.float64)
+    check(load().gsb_bn_reduce(_ref(v), ptr(sums), ptr(ws), ws.numel() * 4, _s(x)), "bn_reduce")
+    return sums
+
+
+def bn_reduce_partials(partial: torch.Tensor, rows: int, c: int) -> torch.Tensor:
+    sums = torch.empty(2 * c, device=partial.device, dtype=torch.float64)
+    check(load().gsb_bn_reduce_partials(ptr(partial), rows, c, ptr(sums), _s(partial)), "bn_reduce_partials")
+    return sums
+
+
+def bn_finalize(sums: Optional[torch.Tensor], count: float, gamma, beta, running_mean, running_var, nbt,
+                momentum: float, eps: float, c: int, device, want_saved: bool = True):
+    scale = torch.empty(c, device=device, dtype=torch.float32)
+    shift = torch.empty(c, device=device, dtype=torch.float32)
+    mean = torch.empty(c, device=device, dtype=torch.float32) if want_saved else None
+    invstd = torch.empty(c, device=device, dtype=torch.float32) if want_saved else None
+    check(load().gsb_bn_finalize(ptr(sums), float(count), ptr(gamma), ptr(beta), ptr(running_mean), ptr(running_var),
+                                 ptr(nbt), float(momentum), float(eps), c, ptr(scale), ptr(shift), ptr(mean),
+                                 ptr(invstd), stream_ptr(device)), "bn_finalize")
+    return scale, shift, mean, invstd
+
+
+def bn_act(x: torch.Tensor, scale, shift, act1: int, out1: torch.Tensor, act2: int = ACT_NONE,
+           out2: Optional[torch.Tensor] = None, drop_seed: int = 0, drop_mask: Optional[torch.Tensor] = None) -> None:
+    v2 = view_nhwc(out2) if out2 is not None else None
+    check(load().gsb_bn_act(_ref(view_nhwc(x)), ptr(scale), ptr(shift), act1, _ref(view_nhwc(out1)), act2, _ref(v2),
+                            int(drop_seed), ptr(drop_mask), _s(x)), "bn_act")
+
+
+def bn_bwd_reduce(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, drop_seed=0, drop_mask=None) -> torch.Tensor:
+    v = view_nhwc(x)
+    ws = _bn_ws(v, x.device)
+    sums = torch.empty(2 * v.c, device=x.device, dtype=torch.float64)
+    v2 = view_nhwc(dA2) if dA2 is not None else None
+    check(load().gsb_bn_bwd_reduce(_ref(v), _ref(view_nhwc(dA1)), _ref(v2), ptr(scale), ptr(shift), ptr(mean),
+                                   ptr(invstd), act1, act2, int(drop_seed), ptr(drop_mask), ptr(sums), ptr(ws),
+                                   ws.numel() * 4, _s(x)), "bn_bwd_reduce")
+    return sums
+
+
+def bn_bwd_apply(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, sums, count, dx, dgamma=None, dbeta=None,
+                 drop_seed=0, drop_mask=None) -> None:
+    v2 = view_nhwc(dA2) if dA2 is not None else None
+    check(load().gsb_bn_bwd_apply(_ref(view_nhwc(x)), _ref(view_nhwc(dA1)), _ref(v2), ptr(scale), ptr(shift),
+                                  ptr(mean), ptr(invstd), act1, act2, int(drop_seed), ptr(drop_mask), ptr(sums),
+                                  float(count), _ref(view_nhwc(dx)), ptr(dgamma), ptr(dbeta), _s(x)), "bn_bwd_apply")
+
+
+# ---- pooling / resampling -------------------------------------------------------------------
+
+def maxpool2_fwd(x: torch.Tensor) -> torch.Tensor:
+    n, h, w, c = x.shape
+    y = torch.empty((n, h // 2, w // 2, c), device=x.device, dtype=x.dtype)
+    check(load().gsb_maxpool2_fwd(_ref(view_nhwc(x)), _ref(view_nhwc(y)), _s(x)), "maxpool2_fwd")
+    return y
+
+
+def maxpool2_bwd(x: torch.Tensor, dy: torch.Tensor, dx: torch.Tensor, accumulate: bool) -> None:
+    check(load().gsb_maxpool2_bwd(_ref(view_nhwc(x)), _ref(view_nhwc(dy)), _ref(view_nhwc(dx)), int(accumulate),
+                                  _s(x)), "maxpool2_bwd")
+
+
+def upsample2_fwd(x: torch.Tensor, out: torch.Tensor, pad_top: int, pad_left: int) -> None:
+    check(load().gsb_upsample2_fwd(_ref(view_nhwc(x)), _ref(view_nhwc(out)), pad_top, pad_left, _s(x)),
+          "upsample2_fwd")
+
+
+def upsample2_bwd(dout: torch.Tensor, dx: torch.Tensor, pad_top: int, pad_left: int) -> None:
+    check(load().gsb_upsample2_bwd(_ref(view_nhwc(dout)), _ref(view_nhwc(dx)), pad_top, pad_left, _s(dx)),
+          "upsample2_bwd")
+
+
+# ---- losses ---------------------------------------------------------------------------------
+
+def seg_loss_reduce(logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+    n, c, h, w = logits.shape
+    lib = load()
+    nbytes = lib.gsb_seg_loss_workspace_bytes(n, c, h, w)
+    ws = torch.empty(nbytes // 8, device=logits.device, dtype=torch.float64)
+    sums = torch.empty(4, device=logits.device, dtype=torch.float64)
+    check(lib.gsb_seg_loss_reduce(ptr(logits), ptr(labels), n, c, h, w, ptr(sums), ptr(ws), nbytes, _s(logits)),
+          "seg_loss_reduce")
+    return sums
+
+
+def seg_loss_finalize(sums: torch.Tensor, count: float) -> torch.Tensor:
+    out = torch.empty(3, device=sums.device, dtype=torch.float32)
+    check(load().gsb_seg_loss_finalize(ptr(sums), float(count), ptr(out), _s(sums)), "seg_loss_finalize")
+    return out
+
+
+def seg_loss_bwd(logits, labels, sums, count: float, gscale: torch.Tensor) -> torch.Tensor:
+    n, c, h, w = logits.shape
+    d = torch.empty_like(logits)
+    check(load().gsb_seg_loss_bwd(ptr(logits), ptr(labels), n, c, h, w, ptr(sums), float(count), ptr(gscale), ptr(d),
+                                  _s(logits)), "seg_loss_bwd")
+    return d
+
+
+def eval_counts(logits: torch.Tensor, labels: torch.Tensor, want_mask: bool = True):
+    n, c, h, w = logits.shape
+    k = max(c - 1, 1)
+    counts = torch.empty((n, k, 3), device=logits.device, dtype=torch.int64)
+    mask = torch.empty((n, h, w), device=logits.device, dtype=torch.uint8) if want_mask else None
+    check(load().gsb_eval_counts(ptr(logits), ptr(labels), n, c, h, w, ptr(mask), ptr(counts), _s(logits)),
+          "eval_counts")
+    return counts, mask
+
+
+def dice_sums(a: torch.Tensor, b: torch.Tensor, slices: int, inner: int) -> torch.Tensor:
+    sums = torch.empty((slices, 3), device=a.device, dtype=torch.float64)
+    check(load().gsb_dice_sums(ptr(a), ptr(b), slices, inner, ptr(sums), _s(a)), "dice_sums")
+    return sums
+
+
+def gan_loss_fwd(pred: torch.Tensor, mode: int, label: float) -> torch.Tensor:
+    loss = torch.empty((), device=pred.device, dtype=torch.float32)
+    ws = torch.empty(1, device=pred.device, dtype=torch.float64)
+    check(load().gsb_gan_loss(ptr(pred), pred.numel(), mode, float(label), ptr(loss), None, None, ptr(ws), _s(pred)),
+          "gan_loss")
+    return loss
+
+
+def gan_loss_bwd(pred: torch.Tensor, mode: int, label: float, gscale: torch.Tensor) -> torch.Tensor:
+    d = torch.empty_like(pred)
+    check(load().gsb_gan_loss(ptr(pred), pred.numel(), mode, float(label), None, ptr(gscale), ptr(d), None, _s(pred)),
+          "gan_loss")
+    return d
+
+
+def l1_loss_fwd(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    loss = torch.empty((), device=a.device, dtype=torch.float32)
+    ws = torch.empty(1, device=a.device, dtype=torch.float64)
+    check(load().gsb_l1_loss(ptr(a), ptr(b), a.numel(), ptr(loss), None, None, ptr(ws), _s(a)), "l1_loss")
+    return loss
+
+
+def l1_loss_bwd(a: torch.Tensor, b: torch.Tensor, gscale: torch.Tensor) -> torch.Tensor:
+    d = torch.empty_like(a)
+    check(load().gsb_l1_loss(ptr(a), ptr(b), a.numel(), None, ptr(gscale), ptr(d), None, _s(a)), "l1_loss")
+    return d
+
+
+def act_bwd(out: torch.Tensor, dout: torch.Tensor, act: int) -> torch.Tensor:
+    """dx = dout * act'(.) evaluated from the activation OUTPUT (contiguous fp32)."""
+    dx = torch.empty_like(out)
+    check(load().gsb_act_bwd(ptr(out), ptr(dout), act, ptr(dx), out.numel(), _s(out)), "act_bwd")
+    return dx
+
+
+# ---- optimisers -----------------------------------------------------------------------------
+
+def rmsprop_step(p, g, square_avg, mom_buf, lr, alpha, eps, weight_decay, momentum, grad_scale=1.0) -> None:
+    check(load().gsb_rmsprop_step(ptr(p), ptr(g), ptr(square_avg), ptr(mom_buf), p.numel(), lr, alpha, eps,
+                                  weight_decay, momentum, grad_scale, _s(p)), "rmsprop_step")
+
+
+def adam_step(p, g, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0) -> None:
+    check(load().gsb_adam_step(ptr(p), ptr(g), ptr(exp_avg), ptr(exp_avg_sq), p.numel(), lr, beta1, beta2, eps,
+                               weight_decay, int(step), grad_scale, _s(p)), "adam_step")

@@ -1,0 +1,290 @@
+"""GPU parity tests of the individual C-ABI ops against the same torch CPU functionals the oracle uses."""
+import math
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from semantic_segmentation_b200 import ops  # noqa: E402
+from semantic_segmentation_b200._lib import (ACT_LRELU, ACT_NONE, ACT_RELU, ACT_TANH, MODE_CONV, MODE_CONVT,  # noqa: E402
+                                              view_nchw, view_nhwc)
+
+DEV = "cuda"
+
+
+def rel(a, b):
+    a = a.detach().double().cpu().flatten()
+    b = b.detach().double().cpu().flatten()
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def nhwc(x, dtype):
+    return x.permute(0, 2, 3, 1).contiguous().to(DEV, dtype)
+
+
+def from_nhwc(x):
+    return x.float().cpu().permute(0, 3, 1, 2).contiguous()
+
+
+GEOMS = [  # kind, k, stride, pad, cin, cout, n, h, w
+    ("conv", 3, 1, 1, 64, 64, 2, 16, 16),
+    ("conv", 3, 1, 1, 128, 64, 1, 24, 40),
+    ("conv", 3, 1, 1, 64, 128, 3, 9, 11),
+    ("conv", 4, 2, 1, 64, 128, 2, 32, 32),
+    ("conv", 4, 1, 1, 128, 64, 2, 31, 31),
+    ("conv", 1, 1, 0, 64, 64, 2, 8, 8),
+    ("convT", 2, 2, 0, 128, 64, 2, 8, 8),
+    ("convT", 4, 2, 1, 64, 64, 2, 8, 8),
+    ("convT", 8, 2, 3, 128, 64, 2, 4, 4),
+    ("convT", 8, 2, 3, 64, 64, 3, 1, 1),
+    ("conv", 4, 2, 1, 64, 64, 5, 2, 2),
+]
+
+
+def conv_case(kind, k, stride, pad, cin, cout, n, h, w, dtype, use_tc, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(n, cin, h, w, generator=g)
+    wshape = (cout, cin, k, k) if kind == "conv" else (cin, cout, k, k)
+    wt = torch.randn(wshape, generator=g) / math.sqrt(cin * k * k)
+    if dtype == torch.bfloat16:
+        x = x.bfloat16().float()
+        wt = wt.bfloat16().float()
+    x.requires_grad_(True)
+    wt.requires_grad_(True)
+    y = F.conv2d(x, wt, None, stride=stride, padding=pad) if kind == "conv" else \
+        F.conv_transpose2d(x, wt, None, stride=stride, padding=pad)
+    dy = torch.randn(y.shape, generator=g)
+    if dtype == torch.bfloat16:
+        dy = dy.bfloat16().float()
+    y.backward(dy)
+    fwd_mode = MODE_CONV if kind == "conv" else MODE_CONVT
+    bwd_mode = MODE_CONVT if kind == "conv" else MODE_CONV
+    xd = nhwc(x.detach(), dtype)
+    wd = wt.detach().to(DEV)
+    wp = ops.pack_weight(wd, kind == "conv", dtype)
+    wpb = ops.pack_weight(wd, kind != "conv", dtype)
+    oh, ow = y.shape[2], y.shape[3]
+    yd = torch.empty((n, oh, ow, cout), device=DEV, dtype=dtype)
+    stats, rows = ops.conv_gather(view_nhwc(xd), wp, None, view_nhwc(yd), fwd_mode, k, stride, pad, use_tc=use_tc,
+                                  want_stats=(use_tc == 1 and not (kind == "convT" and stride > 1)))
+    dyd = nhwc(dy, dtype)
+    dxd = torch.empty_like(xd)
+    ops.conv_gather(view_nhwc(dyd), wpb, None, view_nhwc(dxd), bwd_mode, k, stride, pad, use_tc=use_tc)
+    dwp = torch.zeros((k * k, cout, cin), device=DEV, dtype=torch.float32)
+    ops.conv_wgrad_into(view_nhwc(xd), view_nhwc(dyd), dwp, fwd_mode, k, stride, pad, use_tc=use_tc)
+    dw = ops.unpack_wgrad(dwp, wshape, kind == "conv")
+    torch.cuda.synchronize()
+    res = dict(fwd=rel(from_nhwc(yd), y), dgrad=rel(from_nhwc(dxd), x.grad), wgrad=rel(dw, wt.grad))
+    if stats is not None:
+        sums = ops.bn_reduce_partials(stats, rows, cout).cpu()
+        yq = from_nhwc(yd).double()
+        ref = torch.cat([yq.sum((0, 2, 3)), (yq * yq).sum((0, 2, 3))])
+        res["stats"] = rel(sums, ref)
+    return res
+
+
+@pytest.mark.parametrize("geom", GEOMS, ids=[f"{g[0]}k{g[1]}s{g[2]}_{g[4]}to{g[5]}_{g[7]}x{g[8]}" for g in GEOMS])
+def test_conv_direct_fp32(geom):
+    res = conv_case(*geom, dtype=torch.float32, use_tc=0)
+    assert res["fwd"] < 1e-5 and res["dgrad"] < 1e-5 and res["wgrad"] < 2e-5, res
+
+
+@pytest.mark.parametrize("geom", GEOMS, ids=[f"{g[0]}k{g[1]}s{g[2]}_{g[4]}to{g[5]}_{g[7]}x{g[8]}" for g in GEOMS])
+def test_conv_direct_bf16(geom):
+    res = conv_case(*geom, dtype=torch.bfloat16, use_tc=0)
+    assert res["fwd"] < 6e-3 and res["dgrad"] < 6e-3 and res["wgrad"] < 1e-4, res
+
+
+@pytest.mark.parametrize("geom", GEOMS, ids=[f"{g[0]}k{g[1]}s{g[2]}_{g[4]}to{g[5]}_{g[7]}x{g[8]}" for g in GEOMS])
+def test_conv_tcgen05_bf16(geom):
+    """tcgen05/TMEM/TMA path: operands are exact bf16, accumulation fp32 -> only the bf16 rounding of the
+    stored output separates it from the fp32 reference (rel-L2 <= 1e-2 per BASELINE north_star)."""
+    res = conv_case(*geom, dtype=torch.bfloat16, use_tc=1)
+    assert res["fwd"] < 6e-3 and res["dgrad"] < 6e-3 and res["wgrad"] < 1e-4, res
+    if "stats" in res:
+        assert res["stats"] < 1e-5, res
+
+
+def test_edge_strided_views_direct():
+    """NCHW fp32 network edges (Cin=1 input, Cout=2 output with bias+tanh) through the SIMT kernel."""
+    g = torch.Generator().manual_seed(3)
+    x = torch.rand(2, 1, 20, 28, generator=g)
+    w = torch.randn(64, 1, 3, 3, generator=g)
+    y = F.conv2d(x, w, None, padding=1)
+    xd, wd = x.to(DEV), w.to(DEV)
+    yd = torch.empty((2, 20, 28, 64), device=DEV, dtype=torch.float32)
+    ops.conv_gather(view_nchw(xd), ops.pack_weight(wd, True, torch.float32), None, view_nhwc(yd), MODE_CONV, 3, 1, 1,
+                    use_tc=0)
+    assert rel(from_nhwc(yd), y) < 1e-5
+    w2 = torch.randn(2, 64, 1, 1, generator=g) * 0.1
+    b2 = torch.randn(2, generator=g)
+    z = torch.tanh(F.conv2d(y, w2, b2))
+    zd = torch.empty((2, 2, 20, 28), device=DEV, dtype=torch.float32)
+    ops.conv_gather(view_nhwc(yd), ops.pack_weight(w2.to(DEV), True, torch.float32), b2.to(DEV), view_nchw(zd), MODE_CONV,
+                    1, 1, 0, act=ACT_TANH, use_tc=0)
+    assert rel(zd, z) < 1e-5
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("c", [64, 128, 1024])
+def test_bn_act_fwd_bwd(dtype, c):
+    g = torch.Generator().manual_seed(c)
+    n, h, w = 3, 10, 6
+    x = torch.randn(n, c, h, w, generator=g) * 1.5 + 0.3
+    if dtype == torch.bfloat16:
+        x = x.bfloat16().float()
+    gamma = 1 + 0.1 * torch.randn(c, generator=g)
+    beta = 0.1 * torch.randn(c, generator=g)
+    rm, rv = torch.zeros(c), torch.ones(c)
+    xr = x.clone().requires_grad_(True)
+    gr, br = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    rm_ref, rv_ref = rm.clone(), rv.clone()
+    z = F.batch_norm(xr, rm_ref, rv_ref, gr, br, training=True, momentum=0.1, eps=1e-5)
+    a1, a2 = F.leaky_relu(z, 0.2), F.relu(z)
+    d1, d2 = torch.randn(a1.shape, generator=g), torch.randn(a1.shape, generator=g)
+    if dtype == torch.bfloat16:
+        d1, d2 = d1.bfloat16().float(), d2.bfloat16().float()
+    (a1 * d1 + a2 * d2).sum().backward()
+    xd = nhwc(x, dtype)
+    sums = ops.bn_reduce(xd)
+    rmd, rvd = rm.to(DEV), rv.to(DEV)
+    nbt = torch.zeros((), dtype=torch.int64, device=DEV)
+    scale, shift, mean, invstd = ops.bn_finalize(sums, n * h * w, gamma.to(DEV), beta.to(DEV), rmd, rvd, nbt, 0.1, 1e-5,
+                                                 c, torch.device(DEV))
+    o1, o2 = torch.empty_like(xd), torch.empty_like(xd)
+    ops.bn_act(xd, scale, shift, ACT_LRELU, o1, ACT_RELU, o2)
+    tol = 1e-5 if dtype == torch.float32 else 6e-3
+    assert rel(from_nhwc(o1), a1) < tol and rel(from_nhwc(o2), a2) < tol
+    assert rel(rmd, rm_ref) < 1e-5 and rel(rvd, rv_ref) < 1e-5 and int(nbt) == 1
+    d1d, d2d = nhwc(d1, dtype), nhwc(d2, dtype)
+    bs = ops.bn_bwd_reduce(xd, d1d, d2d, scale, shift, mean, invstd, ACT_LRELU, ACT_RELU)
+    dx = torch.empty_like(xd)
+    dg, db = torch.zeros(c, device=DEV), torch.zeros(c, device=DEV)
+    ops.bn_bwd_apply(xd, d1d, d2d, scale, shift, mean, invstd, ACT_LRELU, ACT_RELU, bs, n * h * w, dx, dg, db)
+    tolg = 2e-5 if dtype == torch.float32 else 8e-3
+    assert rel(from_nhwc(dx), xr.grad) < tolg
+    assert rel(dg, gr.grad) < 1e-4 and rel(db, br.grad) < 1e-4
+
+
+def test_bn_eval_and_dropout_mask():
+    g = torch.Generator().manual_seed(9)
+    c, n, h, w = 64, 2, 4, 4
+    x = torch.randn(n, c, h, w, generator=g)
+    gamma, beta = torch.rand(c, generator=g) + 0.5, torch.randn(c, generator=g)
+    rm, rv = torch.randn(c, generator=g), torch.rand(c, generator=g) + 0.5
+    z = F.batch_norm(x, rm, rv, gamma, beta, training=False, eps=1e-5)
+    mask = (torch.rand(n, c, h, w, generator=g) > 0.5)
+    ref = F.relu(z * mask * 2.0)
+    xd = nhwc(x, torch.float32)
+    scale, shift, _, _ = ops.bn_finalize(None, 1.0, gamma.to(DEV), beta.to(DEV), rm.to(DEV), rv.to(DEV), None, 0.1, 1e-5,
+                                         c, torch.device(DEV))
+    o = torch.empty_like(xd)
+    md = mask.permute(0, 2, 3, 1).contiguous().to(DEV, torch.uint8)
+    ops.bn_act(xd, scale, shift, ACT_RELU, o, drop_mask=md)
+    assert rel(from_nhwc(o), ref) < 1e-5
+    # Philox mask: ~half kept, identical when recomputed
+    o1, o2 = torch.empty_like(xd), torch.empty_like(xd)
+    ops.bn_act(xd, None, None, ACT_NONE, o1, drop_seed=1234)
+    ops.bn_act(xd, None, None, ACT_NONE, o2, drop_seed=1234)
+    assert torch.equal(o1, o2)
+    kept = (o1 != 0).float().mean().item()
+    assert 0.4 < kept < 0.6
+    assert torch.allclose(o1[o1 != 0], (2 * xd)[o1 != 0])
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("hw", [(8, 8), (9, 7)])
+def test_maxpool(dtype, hw):
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(2, 64, *hw, generator=g)
+    x[0, :, :2, :2] = 0.0  # ties: first max wins
+    if dtype == torch.bfloat16:
+        x = x.bfloat16().float()
+    xr = x.clone().requires_grad_(True)
+    y = F.max_pool2d(xr, 2)
+    dy = torch.randn(y.shape, generator=g)
+    y.backward(dy)
+    xd = nhwc(x, dtype)
+    yd = ops.maxpool2_fwd(xd)
+    assert torch.equal(from_nhwc(yd), y.detach())
+    dxd = torch.full_like(xd, 7.0)
+    ops.maxpool2_bwd(xd, nhwc(dy, dtype), dxd, accumulate=False)
+    assert rel(from_nhwc(dxd), xr.grad) < (1e-6 if dtype == torch.float32 else 5e-3)
+    base = torch.ones_like(xd)
+    ops.maxpool2_bwd(xd, nhwc(dy, dtype), base, accumulate=True)
+    assert rel(from_nhwc(base), xr.grad + 1) < (1e-6 if dtype == torch.float32 else 5e-3)
+
+
+@pytest.mark.parametrize("hw,out_hw", [((4, 4), (8, 8)), ((4, 5), (9, 11)), ((1, 3), (2, 6)), ((16, 16), (32, 32))])
+def test_upsample_into_concat_slice(hw, out_hw):
+    g = torch.Generator().manual_seed(2)
+    n, c = 2, 64
+    x = torch.randn(n, c, *hw, generator=g)
+    xr = x.clone().requires_grad_(True)
+    up = F.interpolate(xr, scale_factor=2, mode="bilinear", align_corners=True)
+    dy_, dx_ = out_hw[0] - up.shape[2], out_hw[1] - up.shape[3]
+    ref = F.pad(up, [dx_ // 2, dx_ - dx_ // 2, dy_ // 2, dy_ - dy_ // 2])
+    dref = torch.randn(ref.shape, generator=g)
+    ref.backward(dref)
+    xd = nhwc(x, torch.float32)
+    cat = torch.full((n, out_hw[0], out_hw[1], 2 * c), 5.0, device=DEV)
+    ops.upsample2_fwd(xd, cat[..., c:], dy_ // 2, dx_ // 2)
+    assert rel(from_nhwc(cat[..., c:]), ref) < 1e-6
+    assert (cat[..., :c] == 5.0).all()
+    dcat = torch.zeros_like(cat)
+    dcat[..., c:] = nhwc(dref, torch.float32)
+    dxd = torch.empty_like(xd)
+    ops.upsample2_bwd(dcat[..., c:], dxd, dy_ // 2, dx_ // 2)
+    assert rel(from_nhwc(dxd), xr.grad) < 1e-5
+
+
+def test_merge_unmerge_upconv():
+    from oracle import genseg_oracle as O
+    g = torch.Generator().manual_seed(5)
+    cin, cout = 6, 5
+    st = {f"c._ops._ops.{i}.op.weight": torch.randn(cin, cout, k, k, generator=g) for i, k in enumerate((4, 6, 8))}
+    st.update({f"c._ops._ops.{i}.op.bias": torch.randn(cout, generator=g) for i in range(3)})
+    leaves = {k: v.clone().requires_grad_(True) for k, v in st.items()}
+    alpha = torch.randn(3, generator=g).requires_grad_(True)
+    W, b = O.merged_upconv_weight(leaves, "c", alpha, bias=True)
+    gW, gb = torch.randn(W.shape, generator=g), torch.randn(b.shape, generator=g)
+    ((W * gW).sum() + (b * gb).sum()).backward()
+    d = {k: v.to(DEV) for k, v in st.items()}
+    ws = [d[f"c._ops._ops.{i}.op.weight"] for i in range(3)]
+    bs = [d[f"c._ops._ops.{i}.op.bias"] for i in range(3)]
+    ad = alpha.detach().to(DEV)
+    wm, bm = ops.merge_upconv(*ws, *bs, ad)
+    assert rel(wm, W) < 1e-6 and rel(bm, b) < 1e-6
+    dal = torch.zeros(3, device=DEV)
+    outs = ops.unmerge_upconv(gW.to(DEV), gb.to(DEV), *ws, *bs, ad, dal)
+    for i in range(3):
+        assert rel(outs[i], leaves[f"c._ops._ops.{i}.op.weight"].grad) < 1e-6
+        assert rel(outs[3 + i], leaves[f"c._ops._ops.{i}.op.bias"].grad) < 1e-6
+    assert rel(dal, alpha.grad) < 1e-5
+
+
+def test_optimizers_match_torch():
+    g = torch.Generator().manual_seed(4)
+    p0 = torch.randn(10007, generator=g)
+    grads = [torch.randn(10007, generator=g) for _ in range(3)]
+    pr = p0.clone().requires_grad_(True)
+    opt = torch.optim.RMSprop([pr], lr=1e-3, weight_decay=1e-8, momentum=0.9)
+    pd = p0.to(DEV)
+    sq, mb = torch.zeros_like(pd), torch.zeros_like(pd)
+    for gr in grads:
+        pr.grad = gr.clone()
+        opt.step()
+        ops.rmsprop_step(pd, gr.to(DEV), sq, mb, 1e-3, 0.99, 1e-8, 1e-8, 0.9)
+    assert rel(pd, pr) < 1e-6
+    pr = p0.clone().requires_grad_(True)
+    opt = torch.optim.Adam([pr], lr=2e-4, betas=(0.5, 0.999))
+    pd = p0.to(DEV)
+    m, v = torch.zeros_like(pd), torch.zeros_like(pd)
+    for t, gr in enumerate(grads, 1):
+        pr.grad = gr.clone()
+        opt.step()
+        ops.adam_step(pd, gr.to(DEV), m, v, 2e-4, 0.5, 0.999, 1e-8, 0.0, t)
+    assert rel(pd, pr) < 1e-6
