@@ -115,11 +115,25 @@ def require_cuda(t: torch.Tensor, name: str = "tensor") -> None:
         raise RuntimeError("genseg_b200: %s must be a CUDA tensor (the hot path has no CPU fallback)" % name)
 
 
+def _canon(n, h, w, c, sn, sh, sw, sc):
+    """Strides of size-1 dimensions are arbitrary in torch; replace them by the values that keep the view
+    pixel-linear (sh = w*sw, sn = h*sh) so the kernels' layout checks see a canonical description."""
+    if c == 1:
+        sc = 1
+    if w == 1:
+        sw = sh if h > 1 else (sn if n > 1 else c * sc)
+    if h == 1:
+        sh = w * sw
+    if n == 1:
+        sn = h * sh
+    return sn, sh, sw, sc
+
+
 def view_nhwc(t: torch.Tensor) -> GsbView:
     """View of a [N,H,W,C]-shaped tensor (any strides: NHWC buffers and their channel slices)."""
     require_cuda(t)
     n, h, w, c = t.shape
-    sn, sh, sw, sc = t.stride()
+    sn, sh, sw, sc = _canon(n, h, w, c, *t.stride())
     return GsbView(t.data_ptr(), dtype_code(t.dtype), n, h, w, c, sn, sh, sw, sc)
 
 
@@ -128,6 +142,7 @@ def view_nchw(t: torch.Tensor) -> GsbView:
     require_cuda(t)
     n, c, h, w = t.shape
     sn, sc, sh, sw = t.stride()
+    sn, sh, sw, sc = _canon(n, h, w, c, sn, sh, sw, sc)
     return GsbView(t.data_ptr(), dtype_code(t.dtype), n, h, w, c, sn, sh, sw, sc)
 
 

@@ -27,7 +27,7 @@ class ProgramFunction(torch.autograd.Function):
         P = {k: v.detach() for k, v in zip(names, params)}
         for k, v in P.items():
             require_cuda(v, k)
-        need_any = torch.is_grad_enabled() and any(t.requires_grad for t in tensors)
+        need_any = any(ctx.needs_input_grad)
         xin = xs[0].detach() if n_in == 1 else tuple(x.detach() for x in xs)
         out, tape = program.forward(xin, P, buffers, training, need_any, extra)
         ctx.program = program
