@@ -92,6 +92,18 @@ size_t gsb_conv_stats_rows(const gsb_view* out, const gsb_conv_geom* g);
  * sum_pixels dout[pix][cout] * in[pix@tap][cin], with the forward op's gather mode. */
 int gsb_conv_wgrad(const gsb_view* in, const gsb_view* dout, float* dwp, const gsb_conv_geom* g, int use_tc,
                    gsb_stream s);
+/* Network-edge convolutions as bandwidth kernels (one side has 1..4 / 1..8 channels).
+ * stem: Conv2d(cin<=4 -> y.c, k x k, stride, pad) from the fp32 NCHW input x[n][cin][h][w] with the torch OIHW fp32
+ *       weight (unet_model.py:14 / unet_parts.py:16; networks.py:582 outermost, :640); wgrad writes dweight (OIHW).
+ * head: 1x1 Conv2d(x.c -> c<=8) + bias to fp32 NCHW logits (OutConv, unet_parts.py:71-77); backward writes
+ *       dx (nullable), dweight[c][x.c] and dbias[c] (nullable; zeroed by the callee). */
+int gsb_stem_conv_fwd(const float* x, int n, int cin, int h, int w, const float* weight, const float* bias,
+                      const gsb_view* y, int k, int stride, int pad, int act, gsb_stream s);
+int gsb_stem_conv_wgrad(const float* x, int n, int cin, int h, int w, const gsb_view* dy, int k, int stride, int pad,
+                        float* dweight, gsb_stream s);
+int gsb_head_conv_fwd(const gsb_view* x, const float* weight, const float* bias, int c, float* logits, gsb_stream s);
+int gsb_head_conv_bwd(const gsb_view* x, const float* weight, int c, const float* dlogits, const gsb_view* dx,
+                      float* dweight, float* dbias, gsb_stream s);
 /* Per-channel sum over pixels (conv bias gradient), fp32 accumulate into db[c]. */
 int gsb_bias_grad(const gsb_view* dout, float* db, gsb_stream s);
 

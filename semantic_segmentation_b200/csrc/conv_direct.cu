@@ -252,7 +252,7 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(DView in, DView dout, f
 __global__ void bias_grad_kernel(DView d, float* __restrict__ db) {
   const int c = blockIdx.x;
   const int64_t P = (int64_t)d.N * d.H * d.W;
-  float acc = 0.f;
+  double acc = 0.0;   // bias gradients are cancellation-heavy sums: accumulate in fp64
   for (int64_t p = (int64_t)blockIdx.y * blockDim.x + threadIdx.x; p < P; p += (int64_t)gridDim.y * blockDim.x) {
     int x = (int)(p % d.W);
     int64_t r = p / d.W;
@@ -260,14 +260,14 @@ __global__ void bias_grad_kernel(DView d, float* __restrict__ db) {
     int n = (int)(r / d.H);
     acc += ld_elem(d.ptr, (int64_t)n * d.sn + (int64_t)y * d.sh + (int64_t)x * d.sw + (int64_t)c * d.sc, d.dtype);
   }
-  __shared__ float red[8];
-  acc = warp_sum(acc);
+  __shared__ double red[8];
+  acc = warp_sum_d(acc);
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
   __syncthreads();
   if (threadIdx.x < 32) {
-    float v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
-    v = warp_sum(v);
-    if (threadIdx.x == 0) atomicAdd(db + c, v);
+    double v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.0;
+    v = warp_sum_d(v);
+    if (threadIdx.x == 0) atomicAdd(db + c, (float)v);
   }
 }
 

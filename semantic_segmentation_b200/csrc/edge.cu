@@ -1,0 +1,330 @@
+// Bandwidth kernels for the network-edge convolutions, where one side has 1..4 channels and a 128-wide
+// tensor-core tile cannot be filled:
+//   * "stem": Conv2d(Cin<=4 -> Cout, k x k, stride, pad) reading the fp32 NCHW network input and writing the
+//     NHWC activation (unet/unet_model.py:14 via unet_parts.py:16; networks.py:582 outermost, :640), forward
+//     and weight gradient;
+//   * "head": the 1x1 OutConv (unet_parts.py:71-77) K -> C<=8 classes, reading the NHWC activation and writing
+//     fp32 NCHW logits; backward fuses dX, dW and db in one pass over (x, dlogits).
+// All four are HBM-bound; algorithmic bytes: stem fwd = N*H*W*(4 Cin + Cout*esz); stem wgrad = one read of dY
+// per 16-tap pass + x; head fwd = N*H*W*(K*esz + 4C); head bwd = N*H*W*(2 K*esz + 4C).
+#include "common.cuh"
+
+namespace gsb {
+
+constexpr int kStemMaxTaps = 64;   // k*k*Cin
+
+// ---------------------------------------------------------------------------------------------------------
+// stem forward: thread = (output pixel, 8-channel group)
+// ---------------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) stem_fwd_kernel(const float* __restrict__ x, int N, int Cin, int H, int W,
+                                                      const float* __restrict__ w /*[Cout][Cin][k][k]*/,
+                                                      const float* __restrict__ bias, T* __restrict__ y, int64_t yld, int OH,
+                                                      int OW, int Cout, int k, int stride, int pad, int act) {
+  extern __shared__ float sw[];  // [taps][Cout]
+  const int taps = Cin * k * k;
+  for (int i = threadIdx.x; i < taps * Cout; i += blockDim.x) {
+    int t = i / Cout, co = i % Cout;
+    sw[i] = w[(int64_t)co * taps + t];
+  }
+  __syncthreads();
+  const int G = Cout >> 3;
+  const int64_t total = (int64_t)N * OH * OW * G;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int g = (int)(i % G);
+    const int64_t p = i / G;
+    const int ox = (int)(p % OW);
+    const int64_t r = p / OW;
+    const int oy = (int)(r % OH), n = (int)(r / OH);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = bias ? bias[g * 8 + j] : 0.f;
+    int t = 0;
+    for (int ci = 0; ci < Cin; ++ci) {
+      const float* xp = x + ((int64_t)n * Cin + ci) * H * W;
+      for (int ky = 0; ky < k; ++ky) {
+        const int iy = oy * stride - pad + ky;
+        for (int kx = 0; kx < k; ++kx, ++t) {
+          const int ix = ox * stride - pad + kx;
+          float v = (iy >= 0 && iy < H && ix >= 0 && ix < W) ? __ldg(xp + (int64_t)iy * W + ix) : 0.f;
+          const float4 w0 = *reinterpret_cast<const float4*>(sw + t * Cout + g * 8);
+          const float4 w1 = *reinterpret_cast<const float4*>(sw + t * Cout + g * 8 + 4);
+          acc[0] = fmaf(v, w0.x, acc[0]); acc[1] = fmaf(v, w0.y, acc[1]);
+          acc[2] = fmaf(v, w0.z, acc[2]); acc[3] = fmaf(v, w0.w, acc[3]);
+          acc[4] = fmaf(v, w1.x, acc[4]); acc[5] = fmaf(v, w1.y, acc[5]);
+          acc[6] = fmaf(v, w1.z, acc[6]); acc[7] = fmaf(v, w1.w, acc[7]);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = act_fwd(acc[j], act);
+    Vec8<T>::store(y + p * yld + g * 8, acc);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// stem weight gradient: dw[co][tap] += sum_pix dY[pix][co] * x[pix@tap]; TP taps per pass kept in registers
+// ---------------------------------------------------------------------------------------------------------
+template <typename T, int TP>
+__global__ void __launch_bounds__(256) stem_wgrad_kernel(const float* __restrict__ x, int N, int Cin, int H, int W,
+                                                        const T* __restrict__ dy, int64_t dld, int OH, int OW, int Cout,
+                                                        int k, int stride, int pad, int tap0, float* __restrict__ dw) {
+  extern __shared__ float sacc[];  // [G][TP][8]
+  __shared__ int s_ci[TP], s_ky[TP], s_kx[TP];
+  const int taps = Cin * k * k;
+  if (threadIdx.x < TP) {
+    const int tap = tap0 + threadIdx.x;
+    s_ci[threadIdx.x] = tap / (k * k);
+    s_ky[threadIdx.x] = (tap % (k * k)) / k;
+    s_kx[threadIdx.x] = tap % k;
+  }
+  const int G = Cout >> 3;
+  const int lanes = blockDim.x / G;
+  const int g = threadIdx.x % G, lane = threadIdx.x / G;
+  for (int i = threadIdx.x; i < G * TP * 8; i += blockDim.x) sacc[i] = 0.f;
+  __syncthreads();
+  float acc[TP][8];
+#pragma unroll
+  for (int t = 0; t < TP; ++t)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[t][j] = 0.f;
+  const int64_t P = (int64_t)N * OH * OW;
+  for (int64_t p = (int64_t)blockIdx.x * lanes + lane; p < P; p += (int64_t)gridDim.x * lanes) {
+    const int ox = (int)(p % OW);
+    const int64_t r = p / OW;
+    const int oy = (int)(r % OH), n = (int)(r / OH);
+    float d[8];
+    Vec8<T>::load(dy + p * dld + g * 8, d);
+#pragma unroll
+    for (int t = 0; t < TP; ++t) {
+      const int tap = tap0 + t;
+      if (tap < taps) {
+        const int ci = s_ci[t];
+        const int iy = oy * stride - pad + s_ky[t], ix = ox * stride - pad + s_kx[t];
+        float v = (iy >= 0 && iy < H && ix >= 0 && ix < W) ? __ldg(x + (((int64_t)n * Cin + ci) * H + iy) * W + ix) : 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[t][j] = fmaf(v, d[j], acc[t][j]);
+      }
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < TP; ++t)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) atomicAdd(&sacc[(g * TP + t) * 8 + j], acc[t][j]);
+  __syncthreads();
+  for (int i = threadIdx.x; i < G * TP * 8; i += blockDim.x) {
+    const int j = i % 8, t = (i / 8) % TP, gg = i / (8 * TP);
+    const int tap = tap0 + t;
+    if (tap < taps) atomicAdd(dw + (int64_t)(gg * 8 + j) * taps + tap, sacc[i]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// head forward: 8 lanes per pixel, each lane a contiguous 1/8 of the K channels; 3 shuffles per class
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kHeadMaxC = 8;
+
+template <typename T>
+__global__ void __launch_bounds__(256) head_fwd_kernel(const T* __restrict__ x, int64_t xld, int64_t P, int64_t HW, int K, int C,
+                                                      const float* __restrict__ w /*[C][K]*/, const float* __restrict__ bias,
+                                                      float* __restrict__ out /*[N][C][HW]*/) {
+  extern __shared__ float sw[];  // [C][K]
+  for (int i = threadIdx.x; i < C * K; i += blockDim.x) sw[i] = w[i];
+  __syncthreads();
+  const int sub = threadIdx.x & 7;
+  const int chunks = K >> 6;  // K multiple of 64: each lane handles 8 channels per 64-channel chunk
+  const int64_t stride_p = ((int64_t)gridDim.x * blockDim.x) >> 3;
+  // warp-uniform trip count (the shuffles below need all 32 lanes): iterate on the warp's first pixel
+  for (int64_t pw = ((int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31)) >> 3; pw < P; pw += stride_p) {
+    const int64_t p = pw + ((threadIdx.x & 31) >> 3);
+    const bool valid = p < P;
+    float acc[kHeadMaxC];
+#pragma unroll
+    for (int c = 0; c < kHeadMaxC; ++c) acc[c] = 0.f;
+    if (valid) {
+      for (int ch = 0; ch < chunks; ++ch) {
+        float v[8];
+        const int k0 = ch * 64 + sub * 8;
+        Vec8<T>::load(x + p * xld + k0, v);
+#pragma unroll
+        for (int c = 0; c < kHeadMaxC; ++c)
+          if (c < C) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[c] = fmaf(v[j], sw[c * K + k0 + j], acc[c]);
+          }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < kHeadMaxC; ++c)
+      if (c < C) {
+        acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 1);
+        acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 2);
+        acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 4);
+      }
+    if (valid && sub == 0) {
+      const int64_t n = p / HW, r = p - n * HW;
+#pragma unroll
+      for (int c = 0; c < kHeadMaxC; ++c)
+        if (c < C) out[(n * C + c) * HW + r] = acc[c] + (bias ? bias[c] : 0.f);
+    }
+  }
+}
+
+// head backward: dx[p][k] = sum_c d[p][c] w[c][k];  dw[c][k] += sum_p d[p][c] x[p][k];  db[c] += sum_p d[p][c]
+template <typename T>
+__global__ void __launch_bounds__(256) head_bwd_kernel(const T* __restrict__ x, int64_t xld, int64_t P, int64_t HW, int K, int C,
+                                                      const float* __restrict__ w, const float* __restrict__ dout,
+                                                      T* __restrict__ dx, int64_t dxld, float* __restrict__ dw,
+                                                      float* __restrict__ db) {
+  extern __shared__ float sm[];  // sw[C][K] | sdw[C][K] | sdb[C]
+  float* sw = sm;
+  float* sdw = sm + C * K;
+  float* sdb = sdw + C * K;
+  for (int i = threadIdx.x; i < C * K; i += blockDim.x) {
+    sw[i] = w[i];
+    sdw[i] = 0.f;
+  }
+  if (threadIdx.x < C) sdb[threadIdx.x] = 0.f;
+  __syncthreads();
+  const int G = K >> 3;                 // 8-channel groups
+  const int lanes = blockDim.x / G;
+  const int g = threadIdx.x % G, lane = threadIdx.x / G;
+  float aw[kHeadMaxC][8], ab[kHeadMaxC];
+#pragma unroll
+  for (int c = 0; c < kHeadMaxC; ++c) {
+    ab[c] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) aw[c][j] = 0.f;
+  }
+  for (int64_t p = (int64_t)blockIdx.x * lanes + lane; p < P; p += (int64_t)gridDim.x * lanes) {
+    const int64_t n = p / HW, r = p - n * HW;
+    float d[kHeadMaxC];
+#pragma unroll
+    for (int c = 0; c < kHeadMaxC; ++c) d[c] = c < C ? __ldg(dout + (n * C + c) * HW + r) : 0.f;
+    float v[8], o[8];
+    if (dw != nullptr) Vec8<T>::load(x + p * xld + g * 8, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = 0.f;
+#pragma unroll
+    for (int c = 0; c < kHeadMaxC; ++c)
+      if (c < C) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          o[j] = fmaf(d[c], sw[c * K + g * 8 + j], o[j]);
+          if (dw != nullptr) aw[c][j] = fmaf(d[c], v[j], aw[c][j]);
+        }
+        ab[c] += d[c];
+      }
+    if (dx != nullptr) Vec8<T>::store(dx + p * dxld + g * 8, o);
+  }
+  if (dw != nullptr) {
+#pragma unroll
+    for (int c = 0; c < kHeadMaxC; ++c)
+      if (c < C) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) atomicAdd(&sdw[c * K + g * 8 + j], aw[c][j]);
+      }
+  }
+  if (db != nullptr && g == 0) {
+#pragma unroll
+    for (int c = 0; c < kHeadMaxC; ++c)
+      if (c < C) atomicAdd(&sdb[c], ab[c]);
+  }
+  __syncthreads();
+  if (dw != nullptr)
+    for (int i = threadIdx.x; i < C * K; i += blockDim.x) atomicAdd(dw + i, sdw[i]);
+  if (db != nullptr && threadIdx.x < C) atomicAdd(db + threadIdx.x, sdb[threadIdx.x]);
+}
+
+static int grid_cap(int64_t want, int per_sm) {
+  int64_t cap = (int64_t)num_sms() * per_sm;
+  return (int)(want < 1 ? 1 : (want > cap ? cap : want));
+}
+
+}  // namespace gsb
+
+using namespace gsb;
+
+#define EDGE_DISPATCH_T(dtype, ...) \
+  if ((dtype) == GSB_BF16) {        \
+    using T = __nv_bfloat16;        \
+    __VA_ARGS__;                    \
+  } else {                          \
+    using T = float;                \
+    __VA_ARGS__;                    \
+  }
+
+static int stem_check(const float* x, const gsb_view* y, int cin, int k) {
+  GSB_REQUIRE(x && y && y->ptr, "stem: null argument");
+  GSB_REQUIRE(vec8_ok(y), "stem: output must be a pixel-linear NHWC view with c%%8==0");
+  GSB_REQUIRE(cin * k * k <= kStemMaxTaps && y->c <= 256 && 256 % (y->c / 8) == 0, "stem: unsupported shape (cin=%d k=%d cout=%d)", cin, k, y->c);
+  return 0;
+}
+
+extern "C" int gsb_stem_conv_fwd(const float* x, int n, int cin, int h, int w, const float* weight, const float* bias,
+                                 const gsb_view* y, int k, int stride, int pad, int act, gsb_stream s) {
+  if (stem_check(x, y, cin, k)) return -1;
+  GSB_REQUIRE(weight && y->n == n && y->h == (h + 2 * pad - k) / stride + 1 && y->w == (w + 2 * pad - k) / stride + 1,
+              "stem_conv_fwd: shape mismatch");
+  const int cout = y->c;
+  int64_t total = num_pixels(y) * (cout / 8);
+  size_t smem = (size_t)cin * k * k * cout * sizeof(float);
+  int grid = grid_cap((total + 255) / 256, 16);
+  EDGE_DISPATCH_T(y->dtype, stem_fwd_kernel<T><<<grid, 256, smem, to_stream(s)>>>(x, n, cin, h, w, weight, bias, (T*)y->ptr, y->sw,
+                                                                                   y->h, y->w, cout, k, stride, pad, act));
+  return check_launch("stem_conv_fwd");
+}
+
+extern "C" int gsb_stem_conv_wgrad(const float* x, int n, int cin, int h, int w, const gsb_view* dy, int k, int stride, int pad,
+                                   float* dweight, gsb_stream s) {
+  if (stem_check(x, dy, cin, k)) return -1;
+  GSB_REQUIRE(dweight && dy->n == n, "stem_conv_wgrad: bad argument");
+  const int cout = dy->c, taps = cin * k * k;
+  constexpr int TP = 9;
+  cudaMemsetAsync(dweight, 0, (size_t)cout * taps * sizeof(float), to_stream(s));
+  const int G = cout / 8, lanes = 256 / G;
+  int grid = grid_cap((num_pixels(dy) + lanes - 1) / lanes, 4);
+  size_t smem = (size_t)G * TP * 8 * sizeof(float);
+  int launches = 0;
+  for (int tap0 = 0; tap0 < taps; tap0 += TP, ++launches) {
+    EDGE_DISPATCH_T(dy->dtype, stem_wgrad_kernel<T, TP><<<grid, 256, smem, to_stream(s)>>>(
+                                   x, n, cin, h, w, (const T*)dy->ptr, dy->sw, dy->h, dy->w, cout, k, stride, pad, tap0, dweight));
+  }
+  return check_launch("stem_conv_wgrad", launches);
+}
+
+static int head_check(const gsb_view* x, int c) {
+  GSB_REQUIRE(x && x->ptr, "head: null view");
+  GSB_REQUIRE(vec8_ok(x) && x->c % 64 == 0 && x->c <= 256, "head: input must be pixel-linear NHWC with c in {64,128,192,256}");
+  GSB_REQUIRE(c >= 1 && c <= kHeadMaxC, "head: n_classes %d unsupported by the fused 1x1 kernel (max %d)", c, kHeadMaxC);
+  return 0;
+}
+
+extern "C" int gsb_head_conv_fwd(const gsb_view* x, const float* weight, const float* bias, int c, float* logits, gsb_stream s) {
+  if (head_check(x, c)) return -1;
+  GSB_REQUIRE(weight && logits, "head_conv_fwd: null pointer");
+  const int64_t P = num_pixels(x), HW = (int64_t)x->h * x->w;
+  int grid = grid_cap((P * 8 + 255) / 256, 16);
+  size_t smem = (size_t)c * x->c * sizeof(float);
+  EDGE_DISPATCH_T(x->dtype, head_fwd_kernel<T><<<grid, 256, smem, to_stream(s)>>>((const T*)x->ptr, x->sw, P, HW, x->c, c, weight,
+                                                                                   bias, logits));
+  return check_launch("head_conv_fwd");
+}
+
+extern "C" int gsb_head_conv_bwd(const gsb_view* x, const float* weight, int c, const float* dlogits, const gsb_view* dx,
+                                 float* dweight, float* dbias, gsb_stream s) {
+  if (head_check(x, c)) return -1;
+  GSB_REQUIRE(weight && dlogits, "head_conv_bwd: null pointer");
+  if (dx && dx->ptr)
+    GSB_REQUIRE(vec8_ok(dx) && dx->c == x->c && num_pixels(dx) == num_pixels(x) && dx->dtype == x->dtype, "head_conv_bwd: dx mismatch");
+  const int64_t P = num_pixels(x), HW = (int64_t)x->h * x->w;
+  const int K = x->c, G = K / 8, lanes = 256 / G;
+  if (dweight) cudaMemsetAsync(dweight, 0, (size_t)c * K * sizeof(float), to_stream(s));
+  if (dbias) cudaMemsetAsync(dbias, 0, (size_t)c * sizeof(float), to_stream(s));
+  int grid = grid_cap((P + lanes - 1) / lanes, 4);
+  size_t smem = (size_t)(2 * c * K + c) * sizeof(float);
+  EDGE_DISPATCH_T(x->dtype, head_bwd_kernel<T><<<grid, 256, smem, to_stream(s)>>>(
+                                (const T*)x->ptr, x->sw, P, HW, K, c, weight, dlogits, (dx && dx->ptr) ? (T*)dx->ptr : nullptr,
+                                dx ? dx->sw : 0, dweight, dbias));
+  return check_launch("head_conv_bwd");
+}

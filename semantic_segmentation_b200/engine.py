@@ -117,6 +117,13 @@ def _nhwc_empty(n: int, h: int, w: int, c: int, device, dtype=None, zero: bool =
     return f((n, h, w, c), device=device, dtype=dtype or act_dtype())
 
 
+def _is_stem(s: "ConvSpec", x_view: GsbView, x_keep) -> bool:
+    return (s.kind == "conv" and s.cin <= 4 and s.cin * s.k * s.k <= 64 and s.cout % 8 == 0 and s.cout <= 256
+            and 256 % (s.cout // 8) == 0 and isinstance(x_keep, torch.Tensor) and x_keep.dim() == 4
+            and x_keep.dtype == torch.float32 and x_keep.is_contiguous() and x_keep.shape[1] == s.cin
+            and x_view.sc == x_view.h * x_view.w and x_view.sw == 1)
+
+
 class ConvBNAct:
     """conv (+bias) -> [BatchNorm2d] -> act1(dropout(.)) [-> second output act2(.)].
 
@@ -133,11 +140,16 @@ class ConvBNAct:
                 drop_seed: int = 0, drop_mask: Optional[torch.Tensor] = None):
         s = self.spec
         oh, ow = s.out_hw(h, w)
-        wp = s.pack_fwd(weight)
         y = _nhwc_empty(n, oh, ow, s.cout, device)
-        want_stats = self.has_bn and training and _CONFIG["fused_stats"]
-        stats, rows = ops.conv_gather(x_view, wp, bias, view_nhwc(y), s.fwd_mode, s.k, s.stride, s.pad,
-                                      use_tc=_CONFIG["use_tc"], want_stats=want_stats)
+        stem = _is_stem(s, x_view, x_keep)
+        if stem:   # fp32 NCHW network input with 1..4 channels: bandwidth kernel, torch-layout fp32 weights
+            ops.stem_conv_fwd(x_keep, weight.detach().contiguous(), bias, y, s.k, s.stride, s.pad)
+            stats, rows = None, 0
+        else:
+            wp = s.pack_fwd(weight)
+            want_stats = self.has_bn and training and _CONFIG["fused_stats"]
+            stats, rows = ops.conv_gather(x_view, wp, bias, view_nhwc(y), s.fwd_mode, s.k, s.stride, s.pad,
+                                          use_tc=_CONFIG["use_tc"], want_stats=want_stats)
         sv = Saved()
         count = float(n * oh * ow)
         scale = shift = mean = invstd = None
@@ -164,6 +176,7 @@ class ConvBNAct:
             sv.drop_seed = drop_seed if use_drop else 0
             sv.drop_mask = drop_mask if use_drop else None
             sv.extra["train_bn"] = self.has_bn and training
+            sv.extra["stem"] = stem
         return out1, sv
 
     def backward(self, sv: Saved, dA1: torch.Tensor, dA2: Optional[torch.Tensor], need_dx: bool, need_dw: bool,
@@ -191,7 +204,9 @@ class ConvBNAct:
                          dgamma, dbeta, sv.drop_seed, sv.drop_mask)
         dyv = view_nhwc(dY)
         dweight = dbias = None
-        if need_dw:
+        if need_dw and sv.extra.get("stem"):
+            dweight = ops.stem_conv_wgrad(sv.x_keep, dY, s.k, s.stride, s.pad)
+        elif need_dw:
             dwp = torch.zeros((s.k * s.k, s.cout, s.cin), device=device, dtype=torch.float32)
             ops.conv_wgrad_into(sv.x_view, dyv, dwp, s.fwd_mode, s.k, s.stride, s.pad, use_tc=_CONFIG["use_tc"])
             dweight = ops.unpack_wgrad(dwp, s.weight_shape(), s.kind == "conv")
@@ -223,15 +238,26 @@ class EdgeConv:
         s = self.spec
         n, h, w, _ = x.shape
         oh, ow = s.out_hw(h, w)
-        out = torch.empty((n, s.cout, oh, ow), device=x.device, dtype=torch.float32)
-        wp = s.pack_fwd(weight)
-        ops.conv_gather(view_nhwc(x), wp, bias, view_nchw(out), s.fwd_mode, s.k, s.stride, s.pad, act=self.act,
-                        use_tc=0)
+        head = self._is_head(x)
+        if head:
+            out = ops.head_conv_fwd(x, weight.detach().contiguous(), bias)
+        else:
+            out = torch.empty((n, s.cout, oh, ow), device=x.device, dtype=torch.float32)
+            wp = s.pack_fwd(weight)
+            ops.conv_gather(view_nhwc(x), wp, bias, view_nchw(out), s.fwd_mode, s.k, s.stride, s.pad, act=self.act,
+                            use_tc=0)
         sv = Saved()
         if save:
             sv.x_view, sv.x_keep, sv.weight = view_nhwc(x), x, weight
             sv.extra["out"] = out if self.act != ACT_NONE else None
+            sv.extra["head"] = head
         return out, sv
+
+    def _is_head(self, x: torch.Tensor) -> bool:
+        s = self.spec
+        return (s.kind == "conv" and s.k == 1 and s.stride == 1 and s.pad == 0 and self.act == ACT_NONE
+                and s.cout <= 8 and s.cin % 64 == 0 and s.cin <= 256 and x.stride(3) == 1
+                and x.stride(2) % 8 == 0 and x.stride(1) == x.shape[2] * x.stride(2))
 
     def backward(self, sv: Saved, dout: torch.Tensor, need_dx: bool, need_dw: bool, need_db: bool,
                  dx_out: Optional[torch.Tensor] = None):
@@ -244,6 +270,8 @@ class EdgeConv:
         dv = view_nchw(dout)
         device = dout.device
         dweight = dbias = dx = None
+        if sv.extra.get("head") and dx_out is None:
+            return ops.head_conv_bwd(sv.x_keep, sv.weight.detach().contiguous(), dout, need_dx, need_dw, need_db)
         if need_dw:
             dwp = torch.zeros((s.k * s.k, s.cout, s.cin), device=device, dtype=torch.float32)
             ops.conv_wgrad_into(sv.x_view, dv, dwp, s.fwd_mode, s.k, s.stride, s.pad, use_tc=0)

@@ -117,6 +117,40 @@ def conv_wgrad_into(inp: GsbView, dout: GsbView, dwp: torch.Tensor, mode: int, k
     check(load().gsb_conv_wgrad(_ref(inp), _ref(dout), ptr(dwp), C.byref(g), use_tc, _s(dwp)), "conv_wgrad")
 
 
+def stem_conv_fwd(x: torch.Tensor, weight: torch.Tensor, bias, y: torch.Tensor, k: int, stride: int, pad: int,
+                  act: int = ACT_NONE) -> None:
+    n, cin, h, w = x.shape
+    check(load().gsb_stem_conv_fwd(ptr(x), n, cin, h, w, ptr(weight), ptr(bias), _ref(view_nhwc(y)), k, stride, pad, act,
+                                   _s(x)), "stem_conv_fwd")
+
+
+def stem_conv_wgrad(x: torch.Tensor, dy: torch.Tensor, k: int, stride: int, pad: int) -> torch.Tensor:
+    n, cin, h, w = x.shape
+    dw = torch.empty((dy.shape[3], cin, k, k), device=x.device, dtype=torch.float32)
+    check(load().gsb_stem_conv_wgrad(ptr(x), n, cin, h, w, _ref(view_nhwc(dy)), k, stride, pad, ptr(dw), _s(x)),
+          "stem_conv_wgrad")
+    return dw
+
+
+def head_conv_fwd(x: torch.Tensor, weight: torch.Tensor, bias) -> torch.Tensor:
+    n, h, w, _ = x.shape
+    c = weight.shape[0]
+    out = torch.empty((n, c, h, w), device=x.device, dtype=torch.float32)
+    check(load().gsb_head_conv_fwd(_ref(view_nhwc(x)), ptr(weight), ptr(bias), c, ptr(out), _s(x)), "head_conv_fwd")
+    return out
+
+
+def head_conv_bwd(x: torch.Tensor, weight: torch.Tensor, dlogits: torch.Tensor, need_dx: bool, need_dw: bool,
+                  need_db: bool):
+    c = weight.shape[0]
+    dx = torch.empty_like(x) if need_dx else None
+    dw = torch.empty_like(weight) if need_dw else None
+    db = torch.empty(c, device=x.device, dtype=torch.float32) if need_db else None
+    check(load().gsb_head_conv_bwd(_ref(view_nhwc(x)), ptr(weight), c, ptr(dlogits), _ref(view_nhwc(dx)) if need_dx else None,
+                                   ptr(dw), ptr(db), _s(x)), "head_conv_bwd")
+    return dx, dw, db
+
+
 def bias_grad(dout: GsbView, db: torch.Tensor) -> None:
     check(load().gsb_bias_grad(_ref(dout), ptr(db), _s(db)), "bias_grad")
 

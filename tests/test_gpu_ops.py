@@ -288,3 +288,49 @@ def test_optimizers_match_torch():
         opt.step()
         ops.adam_step(pd, gr.to(DEV), m, v, 2e-4, 0.5, 0.999, 1e-8, 0.0, t)
     assert rel(pd, pr) < 1e-6
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("cfg", [(1, 64, 3, 1, 1, 2, 20, 28), (3, 64, 3, 1, 1, 2, 17, 16), (1, 64, 4, 2, 1, 2, 32, 32),
+                                 (2, 64, 4, 2, 1, 3, 16, 24)])
+def test_stem_conv(dtype, cfg):
+    cin, cout, k, s, p, n, h, w = cfg
+    g = torch.Generator().manual_seed(11)
+    x = torch.rand(n, cin, h, w, generator=g)
+    wt = torch.randn(cout, cin, k, k, generator=g) * 0.3
+    b = torch.randn(cout, generator=g)
+    wr = wt.clone().requires_grad_(True)
+    y = F.conv2d(x, wr, b, stride=s, padding=p)
+    dy = torch.randn(y.shape, generator=g)
+    if dtype == torch.bfloat16:
+        dy = dy.bfloat16().float()
+    y.backward(dy)
+    yd = torch.empty((n, y.shape[2], y.shape[3], cout), device=DEV, dtype=dtype)
+    ops.stem_conv_fwd(x.to(DEV), wt.to(DEV), b.to(DEV), yd, k, s, p)
+    assert rel(from_nhwc(yd), y) < (1e-5 if dtype == torch.float32 else 4e-3)
+    dw = ops.stem_conv_wgrad(x.to(DEV), nhwc(dy, dtype), k, s, p)
+    assert rel(dw, wr.grad) < 2e-5
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("c", [1, 2, 3])
+def test_head_conv(dtype, c):
+    g = torch.Generator().manual_seed(12)
+    n, h, w, k = 2, 19, 23, 64
+    x = torch.randn(n, k, h, w, generator=g)
+    if dtype == torch.bfloat16:
+        x = x.bfloat16().float()
+    wt = torch.randn(c, k, 1, 1, generator=g) * 0.2
+    b = torch.randn(c, generator=g)
+    xr, wr, br = x.clone().requires_grad_(True), wt.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    y = F.conv2d(xr, wr, br)
+    dy = torch.randn(y.shape, generator=g)
+    y.backward(dy)
+    cat = torch.zeros((n, h, w, 2 * k), device=DEV, dtype=dtype)     # strided (channel-slice) input view
+    xd = cat[..., k:]
+    xd.copy_(nhwc(x, dtype))
+    out = ops.head_conv_fwd(xd, wt.to(DEV), b.to(DEV))
+    assert rel(out, y) < 1e-5
+    dx, dw, db = ops.head_conv_bwd(xd, wt.to(DEV), dy.to(DEV), True, True, True)
+    assert rel(from_nhwc(dx), xr.grad) < (1e-5 if dtype == torch.float32 else 4e-3)
+    assert rel(dw, wr.grad) < 2e-5 and rel(db, br.grad) < 1e-5
