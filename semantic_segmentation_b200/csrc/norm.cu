@@ -11,6 +11,7 @@
 namespace gsb {
 
 constexpr int kThreads = 256;
+constexpr int kUnroll = 1;  // pixels in flight per thread (memory-level parallelism)
 
 struct PixView {  // pixel-linear view
   void* ptr;
@@ -80,29 +81,41 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
     load_param8(invstd, c0, is, 1.f);
   }
   const bool has_drop = (drop_seed != 0) || (drop_mask != nullptr);
-  for (int64_t p = (int64_t)blockIdx.x * lanes + lane; p < P; p += (int64_t)gridDim.x * lanes) {
-    float v[8];
-    load8<T>(x, p, c0, v);
-    if (MODE == 0) {
+  const bool two = dA2.ptr != nullptr;
+  const int64_t step = (int64_t)gridDim.x * lanes;
+  for (int64_t p0 = (int64_t)blockIdx.x * lanes + lane; p0 < P; p0 += step * kUnroll) {
+    float v[kUnroll][8], a[kUnroll][8], b[kUnroll][8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        s0[i] += v[i];
-        s1[i] = fmaf(v[i], v[i], s1[i]);
+    for (int u = 0; u < kUnroll; ++u)
+      if (p0 + u * step < P) {
+        load8<T>(x, p0 + u * step, c0, v[u]);
+        if (MODE == 1) {
+          load8<T>(dA1, p0 + u * step, c0, a[u]);
+          if (two) load8<T>(dA2, p0 + u * step, c0, b[u]);
+        }
       }
-    } else {
-      float a[8], b[8];
-      load8<T>(dA1, p, c0, a);
-      if (dA2.ptr != nullptr) load8<T>(dA2, p, c0, b);
-      uint32_t keep = has_drop ? keep_bits(drop_seed, drop_mask, p, C, c0) : 0xFFu;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        float z = fmaf(v[i], sc[i], sh[i]);
-        float dm = has_drop ? (((keep >> i) & 1u) ? 2.f : 0.f) : 1.f;
-        float dy = a[i] * dm * act_grad(z * dm, act1);
-        if (dA2.ptr != nullptr) dy += b[i] * act_grad(z, act2);
-        float xh = (v[i] - mu[i]) * is[i];
-        s0[i] += dy;
-        s1[i] = fmaf(dy, xh, s1[i]);
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t p = p0 + u * step;
+      if (p >= P) break;
+      if (MODE == 0) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          s0[i] += v[u][i];
+          s1[i] = fmaf(v[u][i], v[u][i], s1[i]);
+        }
+      } else {
+        uint32_t keep = has_drop ? keep_bits(drop_seed, drop_mask, p, C, c0) : 0xFFu;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float z = fmaf(v[u][i], sc[i], sh[i]);
+          float dm = has_drop ? (((keep >> i) & 1u) ? 2.f : 0.f) : 1.f;
+          float dy = a[u][i] * dm * act_grad(z * dm, act1);
+          if (two) dy += b[u][i] * act_grad(z, act2);
+          float xh = (v[u][i] - mu[i]) * is[i];
+          s0[i] += dy;
+          s1[i] = fmaf(dy, xh, s1[i]);
+        }
       }
     }
   }
@@ -173,19 +186,28 @@ __global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, 
   load_param8(scale, c0, sc, 1.f);
   load_param8(shift, c0, sh, 0.f);
   const bool has_drop = (drop_seed != 0) || (drop_mask != nullptr);
-  for (int64_t p = (int64_t)blockIdx.x * lanes + lane; p < P; p += (int64_t)gridDim.x * lanes) {
-    float v[8], o1[8], o2[8];
-    load8<T>(x, p, c0, v);
-    uint32_t keep = has_drop ? keep_bits(drop_seed, drop_mask, p, C, c0) : 0xFFu;
+  const int64_t step = (int64_t)gridDim.x * lanes;
+  for (int64_t p0 = (int64_t)blockIdx.x * lanes + lane; p0 < P; p0 += step * kUnroll) {
+    float v[kUnroll][8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      float z = fmaf(v[i], sc[i], sh[i]);
-      float dm = has_drop ? (((keep >> i) & 1u) ? 2.f : 0.f) : 1.f;
-      o1[i] = act_fwd(z * dm, act1);
-      o2[i] = act_fwd(z, act2);
+    for (int u = 0; u < kUnroll; ++u)
+      if (p0 + u * step < P) load8<T>(x, p0 + u * step, c0, v[u]);
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t p = p0 + u * step;
+      if (p >= P) break;
+      float o1[8], o2[8];
+      uint32_t keep = has_drop ? keep_bits(drop_seed, drop_mask, p, C, c0) : 0xFFu;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float z = fmaf(v[u][i], sc[i], sh[i]);
+        float dm = has_drop ? (((keep >> i) & 1u) ? 2.f : 0.f) : 1.f;
+        o1[i] = act_fwd(z * dm, act1);
+        o2[i] = act_fwd(z, act2);
+      }
+      store8<T>(out1, p, c0, o1);
+      if (out2.ptr != nullptr) store8<T>(out2, p, c0, o2);
     }
-    store8<T>(out1, p, c0, o1);
-    if (out2.ptr != nullptr) store8<T>(out2, p, c0, o2);
   }
 }
 
@@ -211,26 +233,38 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
     m1[i] = has_bn ? (float)(sums[C + c0 + i] * inv_count) : 0.f;
   }
   const bool has_drop = (drop_seed != 0) || (drop_mask != nullptr);
-  for (int64_t p = (int64_t)blockIdx.x * lanes + lane; p < P; p += (int64_t)gridDim.x * lanes) {
-    float v[8], a[8], b[8], o[8];
-    load8<T>(x, p, c0, v);
-    load8<T>(dA1, p, c0, a);
-    if (dA2.ptr != nullptr) load8<T>(dA2, p, c0, b);
-    uint32_t keep = has_drop ? keep_bits(drop_seed, drop_mask, p, C, c0) : 0xFFu;
+  const bool two = dA2.ptr != nullptr;
+  const int64_t step = (int64_t)gridDim.x * lanes;
+  for (int64_t p0 = (int64_t)blockIdx.x * lanes + lane; p0 < P; p0 += step * kUnroll) {
+    float v[kUnroll][8], a[kUnroll][8], b[kUnroll][8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      float z = fmaf(v[i], sc[i], sh[i]);
-      float dm = has_drop ? (((keep >> i) & 1u) ? 2.f : 0.f) : 1.f;
-      float dy = a[i] * dm * act_grad(z * dm, act1);
-      if (dA2.ptr != nullptr) dy += b[i] * act_grad(z, act2);
-      if (has_bn) {
-        float xh = (v[i] - mu[i]) * is[i];
-        o[i] = sc[i] * (dy - m0[i] - xh * m1[i]);
-      } else {
-        o[i] = dy * sc[i];
+    for (int u = 0; u < kUnroll; ++u)
+      if (p0 + u * step < P) {
+        load8<T>(x, p0 + u * step, c0, v[u]);
+        load8<T>(dA1, p0 + u * step, c0, a[u]);
+        if (two) load8<T>(dA2, p0 + u * step, c0, b[u]);
       }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t p = p0 + u * step;
+      if (p >= P) break;
+      float o[8];
+      uint32_t keep = has_drop ? keep_bits(drop_seed, drop_mask, p, C, c0) : 0xFFu;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float z = fmaf(v[u][i], sc[i], sh[i]);
+        float dm = has_drop ? (((keep >> i) & 1u) ? 2.f : 0.f) : 1.f;
+        float dy = a[u][i] * dm * act_grad(z * dm, act1);
+        if (two) dy += b[u][i] * act_grad(z, act2);
+        if (has_bn) {
+          float xh = (v[u][i] - mu[i]) * is[i];
+          o[i] = sc[i] * (dy - m0[i] - xh * m1[i]);
+        } else {
+          o[i] = dy * sc[i];
+        }
+      }
+      store8<T>(dx, p, c0, o);
     }
-    store8<T>(dx, p, c0, o);
   }
 }
 

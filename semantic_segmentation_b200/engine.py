@@ -121,7 +121,7 @@ def _is_stem(s: "ConvSpec", x_view: GsbView, x_keep) -> bool:
     return (s.kind == "conv" and s.cin <= 4 and s.cin * s.k * s.k <= 64 and s.cout % 8 == 0 and s.cout <= 256
             and 256 % (s.cout // 8) == 0 and isinstance(x_keep, torch.Tensor) and x_keep.dim() == 4
             and x_keep.dtype == torch.float32 and x_keep.is_contiguous() and x_keep.shape[1] == s.cin
-            and x_view.sc == x_view.h * x_view.w and x_view.sw == 1)
+            and x_view.sw == 1 and x_view.dtype == 0)
 
 
 class ConvBNAct:
@@ -147,7 +147,8 @@ class ConvBNAct:
             stats, rows = None, 0
         else:
             wp = s.pack_fwd(weight)
-            want_stats = self.has_bn and training and _CONFIG["fused_stats"]
+            want_stats = (self.has_bn and training and _CONFIG["fused_stats"]
+                          and not (s.kind == "convT" and s.stride > 1))
             stats, rows = ops.conv_gather(x_view, wp, bias, view_nhwc(y), s.fwd_mode, s.k, s.stride, s.pad,
                                           use_tc=_CONFIG["use_tc"], want_stats=want_stats)
         sv = Saved()
@@ -200,8 +201,13 @@ class ConvBNAct:
             if need_bn:
                 dgamma = torch.zeros(s.cout, device=device, dtype=torch.float32)
                 dbeta = torch.zeros(s.cout, device=device, dtype=torch.float32)
+        elif self.has_bn and need_bn:
+            # eval-mode BatchNorm (running statistics are constants): dgamma = sum dy*xhat_running, dbeta = sum dy
+            es = ops.bn_bwd_reduce(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2,
+                                   sv.drop_seed, sv.drop_mask)
+            dbeta, dgamma = es[:s.cout].float(), es[s.cout:].float()
         ops.bn_bwd_apply(y, dA1, dA2, sv.scale, sv.shift, mean, invstd, self.act1, act2, sums, sv.count, dY,
-                         dgamma, dbeta, sv.drop_seed, sv.drop_mask)
+                         dgamma if train_bn else None, dbeta if train_bn else None, sv.drop_seed, sv.drop_mask)
         dyv = view_nhwc(dY)
         dweight = dbias = None
         if need_dw and sv.extra.get("stem"):

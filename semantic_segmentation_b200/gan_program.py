@@ -1,0 +1,253 @@
+"""Forward/backward schedules of the Pix2Pix generator (unet_256 with mixed transposed-conv cells,
+models_pix2pix/networks.py:476-617) and the 70x70 PatchGAN discriminator (networks.py:620-665).
+
+Generator notes
+  * every up-convolution is the reference's softmax(alpha)-weighted sum of ConvTranspose2d k4/k6/k8 (s2,
+    p=(k-2)/2); the three kernels are concentric, so they are merged into ONE 8x8/s2/p3 transposed conv each
+    forward (gsb_merge_upconv) and the gradient is un-merged into dW4/dW6/dW8/dalpha;
+  * the in-place LeakyReLU of networks.py:583 makes every skip carry lrelu(e); the parent's ReLU over the
+    concat then yields relu(e).  One BN pass therefore writes lrelu(BN(y)) (next down conv) AND relu(BN(y))
+    (lower half of the concat buffer); the up path writes relu(dropout(BN(y))) into the upper half.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional
+
+import torch
+
+from . import ops
+from ._lib import ACT_LRELU, ACT_NONE, ACT_RELU, ACT_TANH, view_nchw, view_nhwc
+from .engine import ConvBNAct, ConvSpec, EdgeConv, Saved, _nhwc_empty, act_dtype
+from .unet_program import _put
+
+ARCH_KEY = "__upconv_arch__"
+
+
+def _block_prefix(level: int) -> str:
+    """state_dict prefix of the UnetSkipConnectionBlock whose down conv produces e_level (level 1 = outermost)."""
+    return "model.model" if level == 1 else "model.model.1" + ".model.3" * (level - 2)
+
+
+class GeneratorProgram:
+    def __init__(self, input_nc: int, output_nc: int, ngf: int = 64, use_dropout: bool = False):
+        self.input_nc, self.output_nc, self.ngf, self.use_dropout = input_nc, output_nc, ngf, use_dropout
+        c = [None, ngf, ngf * 2, ngf * 4, ngf * 8, ngf * 8, ngf * 8, ngf * 8, ngf * 8]  # channels of e_1..e_8
+        self.c = c
+        self.down: List[Optional[ConvBNAct]] = [None]
+        for L in range(1, 9):
+            cin = input_nc if L == 1 else c[L - 1]
+            spec = ConvSpec("conv", cin, c[L], 4, 2, 1)
+            if L == 8:
+                self.down.append(ConvBNAct(spec, False, ACT_RELU))
+            else:
+                self.down.append(ConvBNAct(spec, L != 1, ACT_LRELU, ACT_RELU))
+        self.up: List[Optional[ConvBNAct]] = [None] * 8
+        for L in range(7, 0, -1):
+            cin = c[8] if L == 7 else 2 * c[L + 1]
+            self.up[L] = ConvBNAct(ConvSpec("convT", cin, c[L], 8, 2, 3), True, ACT_RELU,
+                                   dropout=use_dropout and L in (4, 5, 6))
+        self.outer = EdgeConv(ConvSpec("convT", 2 * c[1], output_nc, 8, 2, 3), ACT_TANH)
+        names: List[str] = ["model.model.0.weight"]
+        for L in range(2, 9):
+            q = _block_prefix(L)
+            names.append(q + ".model.1.weight")
+            if L != 8:
+                names += [q + ".model.2.weight", q + ".model.2.bias"]
+        for L in range(7, 0, -1):
+            q = _block_prefix(L + 1)
+            ui, bi = (3, 4) if L == 7 else (5, 6)
+            names += [f"{q}.model.{ui}._ops._ops.{i}.op.weight" for i in range(3)]
+            names += [f"{q}.model.{bi}.weight", f"{q}.model.{bi}.bias"]
+        names += [f"model.model.3._ops._ops.{i}.op.weight" for i in range(3)]
+        names += [f"model.model.3._ops._ops.{i}.op.bias" for i in range(3)]
+        names.append(ARCH_KEY)
+        self.param_names = names
+        self._calls = 0
+
+    @staticmethod
+    def _bn(P, B, p: str):
+        return (P[p + ".weight"], P[p + ".bias"], B[p + ".running_mean"], B[p + ".running_var"],
+                B[p + ".num_batches_tracked"])
+
+    def _up_names(self, L: int):
+        q = _block_prefix(L + 1)
+        ui, bi = (3, 4) if L == 7 else (5, 6)
+        return [f"{q}.model.{ui}._ops._ops.{i}.op.weight" for i in range(3)], f"{q}.model.{bi}"
+
+    def forward(self, x: torch.Tensor, P, B, training: bool, save: bool, extra=None):
+        x = x.contiguous()
+        if x.dtype != torch.float32:
+            x = x.float()
+        n, cin, h, w = x.shape
+        if cin != self.input_nc or h % 256 != 0 or w % 256 != 0:
+            raise RuntimeError("UnetGenerator(unet_256): expected input [N,%d,256k,256k], got %s" % (self.input_nc, tuple(x.shape)))
+        dev = x.device
+        arch = P[ARCH_KEY]
+        if arch.dtype != torch.float32 or tuple(arch.shape) != (8, 3):
+            raise RuntimeError("upconv_arch must be a float32 [8,3] tensor")
+        arch = arch.contiguous()
+        self._calls += 1
+        masks = (extra or {}).get("drop_masks")
+        base_seed = int((extra or {}).get("drop_seed", 0)) or (torch.initial_seed() * 1000003 + self._calls) % (1 << 62) + 1
+        tape: Dict[str, object] = {"x": x, "arch": arch}
+        c = self.c
+        sizes = [(h, w)] + [(h >> L, w >> L) for L in range(1, 9)]      # sizes[L] = spatial of e_L
+        cats = [None] + [_nhwc_empty(n, sizes[L][0], sizes[L][1], 2 * c[L], dev) for L in range(1, 8)]
+        # ---- encoder
+        cur_view, cur_keep, ch, cw = view_nchw(x), x, h, w
+        for L in range(1, 9):
+            q = _block_prefix(L)
+            wname = "model.model.0.weight" if L == 1 else q + ".model.1.weight"
+            bn = self._bn(P, B, q + ".model.2") if 1 < L < 8 else None
+            out2 = cats[L][..., :c[L]] if L < 8 else None
+            s, sv = self.down[L].forward(cur_view, cur_keep, n, ch, cw, dev, P[wname], None, bn, training, out2=out2,
+                                         save=save)
+            tape[f"down{L}"] = sv
+            cur_view, cur_keep, (ch, cw) = view_nhwc(s), s, sizes[L]
+        # ---- decoder
+        cur = cur_keep                                   # u = relu(e_8)
+        for L in range(7, 0, -1):
+            wn, bnp = self._up_names(L)
+            wm, _ = ops.merge_upconv(P[wn[0]], P[wn[1]], P[wn[2]], None, None, None, arch[7 - L])
+            hh, ww = cur.shape[1], cur.shape[2]
+            drop = self.up[L].dropout and training
+            mask = masks[L - 4] if (drop and masks is not None) else None
+            seed = (base_seed + 7919 * L) if (drop and masks is None) else 0
+            _, sv = self.up[L].forward(view_nhwc(cur), cur, n, hh, ww, dev, wm, None, self._bn(P, B, bnp), training,
+                                       out1=cats[L][..., c[L]:], save=save, drop_seed=seed, drop_mask=mask)
+            tape[f"up{L}"] = sv
+            cur = cats[L]
+        wo = [f"model.model.3._ops._ops.{i}.op.weight" for i in range(3)]
+        bo = [f"model.model.3._ops._ops.{i}.op.bias" for i in range(3)]
+        wm, bm = ops.merge_upconv(P[wo[0]], P[wo[1]], P[wo[2]], P[bo[0]], P[bo[1]], P[bo[2]], arch[7])
+        out, sv = self.outer.forward(cur, wm, bm, save)
+        tape["outer"] = sv
+        tape["P"] = P if save else None
+        tape["sizes"], tape["n"] = sizes, n
+        return out, tape
+
+    def backward(self, tape, dout: torch.Tensor, need: Dict[str, bool], need_dx: bool):
+        G: Dict[str, torch.Tensor] = {}
+        P = tape["P"]
+        arch = tape["arch"]
+        dev = dout.device
+        c, sizes, n = self.c, tape["sizes"], tape["n"]
+        dalpha = torch.zeros_like(arch)
+
+        def unmerge(dwm, dbm, wn, bn_, row):
+            ws = [P[k] for k in wn]
+            bs = [P[k] for k in bn_] if bn_ else [None, None, None]
+            o = ops.unmerge_upconv(dwm, dbm, ws[0], ws[1], ws[2], bs[0], bs[1], bs[2], arch[row], dalpha[row])
+            for i in range(3):
+                if need.get(wn[i], False):
+                    G[wn[i]] = o[i]
+                if bn_ and need.get(bn_[i], False):
+                    G[bn_[i]] = o[3 + i]
+
+        wo = [f"model.model.3._ops._ops.{i}.op.weight" for i in range(3)]
+        bo = [f"model.model.3._ops._ops.{i}.op.bias" for i in range(3)]
+        need_arch = need.get(ARCH_KEY, False)
+        need_wo = need_arch or any(need.get(k, False) for k in wo + bo)
+        dcat, dwm, dbm = self.outer.backward(tape["outer"], dout, True, need_wo, need_wo)
+        if need_wo:
+            unmerge(dwm, dbm, wo, bo, 7)
+        dskips: List[Optional[torch.Tensor]] = [None] * 9
+        for L in range(1, 8):
+            wn, bnp = self._up_names(L)
+            nw = need_arch or any(need.get(k, False) for k in wn)
+            nb = need.get(bnp + ".weight", False) or need.get(bnp + ".bias", False)
+            dskips[L] = dcat[..., :c[L]]
+            dnext, dwm, _, dg, db = self.up[L].backward(tape[f"up{L}"], dcat[..., c[L]:], None, True, nw, nb, False)
+            if nw:
+                unmerge(dwm, None, wn, None, 7 - L)
+            _put(G, bnp + ".weight", dg)
+            _put(G, bnp + ".bias", db)
+            dcat = dnext            # gradient of cat_{L+1} (or of u for L == 7)
+        ds = dcat
+        dx = None
+        for L in range(8, 0, -1):
+            q = _block_prefix(L)
+            wname = "model.model.0.weight" if L == 1 else q + ".model.1.weight"
+            nb = (need.get(q + ".model.2.weight", False) or need.get(q + ".model.2.bias", False)) if 1 < L < 8 else False
+            want_dx = True if L > 1 else need_dx
+            dxo = dxv = None
+            if L == 1 and need_dx:
+                dxo = torch.empty_like(tape["x"])
+                dxv = view_nchw(dxo)
+            ds, dw, _, dg, db = self.down[L].backward(tape[f"down{L}"], ds, dskips[L] if L < 8 else None, want_dx,
+                                                      need.get(wname, False), nb, False, dx_out=dxo, dx_view=dxv)
+            _put(G, wname, dw)
+            if 1 < L < 8:
+                _put(G, q + ".model.2.weight", dg)
+                _put(G, q + ".model.2.bias", db)
+            if L == 1:
+                dx = ds
+        if need_arch:
+            G[ARCH_KEY] = dalpha
+        return dx, G
+
+
+class DiscriminatorProgram:
+    """NLayerDiscriminator(input_nc, ndf, n_layers=3, BatchNorm2d)."""
+
+    def __init__(self, input_nc: int, ndf: int = 64, n_layers: int = 3):
+        if n_layers != 3:
+            raise NotImplementedError("genseg_b200: only the 'basic' 3-layer PatchGAN is on the B200 path")
+        self.input_nc = input_nc
+        self.l0 = ConvBNAct(ConvSpec("conv", input_nc, ndf, 4, 2, 1), False, ACT_LRELU)
+        self.mid = [(2, ConvBNAct(ConvSpec("conv", ndf, ndf * 2, 4, 2, 1), True, ACT_LRELU)),
+                    (5, ConvBNAct(ConvSpec("conv", ndf * 2, ndf * 4, 4, 2, 1), True, ACT_LRELU)),
+                    (8, ConvBNAct(ConvSpec("conv", ndf * 4, ndf * 8, 4, 1, 1), True, ACT_LRELU))]
+        self.last = EdgeConv(ConvSpec("conv", ndf * 8, 1, 4, 1, 1), ACT_NONE)
+        names = ["model.0.weight", "model.0.bias"]
+        for idx, _ in self.mid:
+            names += [f"model.{idx}.weight", f"model.{idx + 1}.weight", f"model.{idx + 1}.bias"]
+        names += ["model.11.weight", "model.11.bias"]
+        self.param_names = names
+
+    def forward(self, x: torch.Tensor, P, B, training: bool, save: bool, extra=None):
+        x = x.contiguous()
+        if x.dtype != torch.float32:
+            x = x.float()
+        n, cin, h, w = x.shape
+        if cin != self.input_nc:
+            raise RuntimeError("NLayerDiscriminator: expected %d input channels, got %d" % (self.input_nc, cin))
+        dev = x.device
+        tape: Dict[str, object] = {"x": x}
+        a, sv = self.l0.forward(view_nchw(x), x, n, h, w, dev, P["model.0.weight"], P["model.0.bias"], None, training,
+                                save=save)
+        tape["l0"] = sv
+        for idx, layer in self.mid:
+            p = f"model.{idx + 1}"
+            bn = (P[p + ".weight"], P[p + ".bias"], B[p + ".running_mean"], B[p + ".running_var"],
+                  B[p + ".num_batches_tracked"])
+            a, sv = layer.forward(view_nhwc(a), a, n, a.shape[1], a.shape[2], dev, P[f"model.{idx}.weight"], None, bn,
+                                  training, save=save)
+            tape[f"l{idx}"] = sv
+        out, sv = self.last.forward(a, P["model.11.weight"], P["model.11.bias"], save)
+        tape["last"] = sv
+        return out, tape
+
+    def backward(self, tape, dout, need: Dict[str, bool], need_dx: bool):
+        G: Dict[str, torch.Tensor] = {}
+        d, dw, db = self.last.backward(tape["last"], dout, True, need.get("model.11.weight", False),
+                                       need.get("model.11.bias", False))
+        _put(G, "model.11.weight", dw)
+        _put(G, "model.11.bias", db)
+        for idx, layer in reversed(self.mid):
+            p = f"model.{idx + 1}"
+            nb = need.get(p + ".weight", False) or need.get(p + ".bias", False)
+            d, dw, _, dg, dbb = layer.backward(tape[f"l{idx}"], d, None, True, need.get(f"model.{idx}.weight", False), nb,
+                                               False)
+            _put(G, f"model.{idx}.weight", dw)
+            _put(G, p + ".weight", dg)
+            _put(G, p + ".bias", dbb)
+        dx = dxv = None
+        if need_dx:
+            dx = torch.empty_like(tape["x"])
+            dxv = view_nchw(dx)
+        _, dw, db, _, _ = self.l0.backward(tape["l0"], d, None, need_dx, need.get("model.0.weight", False), False,
+                                           need.get("model.0.bias", False), dx_out=dx, dx_view=dxv)
+        _put(G, "model.0.weight", dw)
+        _put(G, "model.0.bias", db)
+        return dx, G
