@@ -1,7 +1,7 @@
 """Data parallelism: one process per GPU, NCCL over NVLink 5 / NVSwitch (torch.distributed plumbing).
 
 The path shards by batch with three exchange steps, all sums:
-  1. gradient all-reduce (coalesced NCCL group launch over the per-parameter gradients);
+  1. gradient all-reduce (asynchronous NCCL all-reduces over the per-parameter gradients, enqueued back to back);
   2. BatchNorm batch statistics, forward [sum x, sum x^2] and backward [sum dy, sum dy*xhat] (fp64, <= 16 KB),
      when sync_bn is on -- an n-rank run then equals the 1-rank run at the same global batch;
   3. the CE / Dice sums of the fused loss (global-batch Dice ratio).
@@ -74,14 +74,9 @@ def allreduce_gradients(params: Iterable[torch.Tensor]) -> None:
     grads = [p.grad for p in params if p.grad is not None]
     if not grads:
         return
-    try:
-        from torch.distributed.distributed_c10d import _coalescing_manager
-        with _coalescing_manager(group=_GROUP["pg"], device=grads[0].device, async_ops=False):
-            for g in grads:
-                dist.all_reduce(g, op=dist.ReduceOp.SUM, group=_GROUP["pg"])
-    except Exception:  # older/newer torch without the coalescing manager: plain per-tensor all-reduce
-        for g in grads:
-            dist.all_reduce(g, op=dist.ReduceOp.SUM, group=_GROUP["pg"])
+    works = [dist.all_reduce(g, op=dist.ReduceOp.SUM, group=_GROUP["pg"], async_op=True) for g in grads]
+    for w in works:
+        w.wait()
 
 
 def broadcast_parameters(module: torch.nn.Module, src: int = 0) -> None:

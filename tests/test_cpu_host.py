@@ -1,0 +1,120 @@
+"""CPU-side tests: the C-ABI library loads and exports every symbol of include/genseg_b200.h, the drop-in modules
+keep the reference's state_dict layout, the product path refuses to run without CUDA, and the data-parallel host
+logic works over gloo with world_size 2."""
+import os
+import re
+import subprocess
+import sys
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _header_symbols():
+    txt = open(os.path.join(ROOT, "include", "genseg_b200.h")).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(gsb_[a-z0-9_]+)\s*\(", txt)))
+
+
+def test_library_exports_every_header_symbol():
+    import __graft_entry__ as g
+    g.build()
+    from semantic_segmentation_b200 import _lib
+    lib = _lib.load()
+    syms = _header_symbols()
+    assert len(syms) >= 35
+    for s in syms:
+        assert hasattr(lib, s), "missing export " + s
+        assert s in _lib.SIGNATURES, "no ctypes signature for " + s
+    assert lib.gsb_version() >= 100
+    assert set(_lib.SIGNATURES) <= set(syms)
+
+
+def test_state_dict_layout_matches_reference_spec():
+    from oracle import genseg_oracle as O
+    from semantic_segmentation_b200.models_pix2pix import networks
+    from semantic_segmentation_b200.unet import UNet
+    for nch, ncls, bil in ((1, 2, True), (1, 1, False), (3, 3, False)):
+        net = UNet(nch, ncls, bil)
+        spec = O.unet_state_spec(nch, ncls, bil)
+        sd = net.state_dict()
+        assert list(sd.keys()) == list(spec.keys())
+        assert all(tuple(sd[k].shape) == tuple(spec[k]) for k in spec)
+        assert set(net._program.param_names) == set(dict(net.named_parameters()).keys())
+        assert (net.n_channels, net.n_classes, net.bilinear) == (nch, ncls, bil)
+    G = networks.define_G(1, 1, 64, "unet_256", "batch", True, "normal", 0.02, [])
+    D = networks.define_D(2, 64, "basic", 3, "batch", "normal", 0.02, [])
+    assert list(G.state_dict().keys()) == list(O.generator_state_spec(1, 1, 64).keys())
+    assert list(D.state_dict().keys()) == list(O.discriminator_state_spec(2, 64).keys())
+    assert networks.arch_parameters()[0] is networks.upconv_arch and tuple(networks.upconv_arch.shape) == (8, 3)
+    assert networks.upconv_arch.requires_grad
+    # init rule of networks.py:84-101: conv weights N(0, 0.02), BN weight N(1, 0.02)
+    w = G.state_dict()["model.model.1.model.1.weight"]
+    assert abs(w.std().item() - 0.02) < 2e-3
+    with pytest.raises(NotImplementedError):
+        networks.define_G(1, 1, 64, "resnet_9blocks")
+
+
+def test_no_cpu_fallback():
+    from semantic_segmentation_b200.models_pix2pix import networks
+    from semantic_segmentation_b200.unet import UNet
+    from semantic_segmentation_b200.util.dice_score import dice_loss, seg_loss
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        UNet(1, 2, True)(torch.zeros(1, 1, 32, 32))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        seg_loss(torch.zeros(2, 2, 8, 8), torch.zeros(2, 8, 8, dtype=torch.long))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        dice_loss(torch.zeros(2, 8, 8), torch.zeros(2, 8, 8))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        networks.GANLoss("vanilla")(torch.zeros(1, 1, 30, 30), True)
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "semantic_segmentation_b200")
+    for dp, _, fs in os.walk(pkg):
+        for f in fs:
+            if f.endswith(".py"):
+                src = open(os.path.join(dp, f)).read()
+                assert "oracle" not in src, os.path.join(dp, f)
+
+
+def test_shard_batch():
+    from semantic_segmentation_b200 import parallel
+    assert [parallel.shard_batch(64, r, 8) for r in range(8)] == [(8 * r, 8 * r + 8) for r in range(8)]
+    with pytest.raises(ValueError):
+        parallel.shard_batch(10, 0, 4)
+
+
+WORKER = r'''
+import os, sys, torch
+sys.path.insert(0, %r)
+from semantic_segmentation_b200 import engine, parallel
+world = parallel.init_data_parallel(sync_bn=True, backend="gloo")
+r = parallel.rank()
+assert world == 2 and parallel.shard_batch(64) == (32 * r, 32 * r + 32)
+sums = torch.tensor([1.0 + r, 10.0 * (r + 1)], dtype=torch.float64)
+s2, cnt = engine._sync_stats(sums, 100.0)             # BatchNorm statistics: summed over ranks, count scaled
+assert s2.tolist() == [3.0, 30.0] and cnt == 200.0
+p = torch.nn.Parameter(torch.zeros(3)); p.grad = torch.full((3,), float(r + 1))
+parallel.allreduce_gradients([p])                      # gradient sum (1/world folded into the optimiser)
+assert p.grad.tolist() == [3.0, 3.0, 3.0]
+m = torch.nn.Linear(2, 2)
+with torch.no_grad():
+    m.weight.fill_(float(r))
+parallel.broadcast_parameters(m)
+assert float(m.weight.sum()) == 0.0
+parallel.shutdown()
+print("rank", r, "ok")
+'''
+
+
+def test_data_parallel_host_logic_gloo_world2(tmp_path):
+    script = tmp_path / "w.py"
+    script.write_text(WORKER % ROOT)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29533", str(script)],
+                       capture_output=True, text=True, timeout=240)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.count("ok") == 2
