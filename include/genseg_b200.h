@@ -137,6 +137,10 @@ int gsb_bn_bwd_apply(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2
                      uint64_t drop_seed, const uint8_t* drop_mask, const double* sums, double count,
                      const gsb_view* dx, float* dgamma, float* dbeta, gsb_stream s);
 
+/* dbeta[c] (+)= sums[c], dgamma[c] (+)= sums[c + C]: parameter gradients from the LOCAL backward sums (under
+ * sync-BN the sums are all-reduced afterwards; the gradient all-reduce then adds the other ranks' parts). */
+int gsb_bn_param_grad(const double* sums, int c, float* dgamma, float* dbeta, int accumulate, gsb_stream s);
+
 /* ---- pooling / resampling -- unet_parts.py:34,50,57-67 -------------------------------- */
 int gsb_maxpool2_fwd(const gsb_view* x, const gsb_view* y, gsb_stream s);
 /* dx (+)= route(dy) to the first maximum of each 2x2 window of x (PyTorch tie rule). */

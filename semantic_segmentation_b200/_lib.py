@@ -58,6 +58,7 @@ SIGNATURES = {
     "gsb_bn_act": (_i, [_VP, _p, _p, _i, _VP, _i, _VP, _u64, _p, _p]),
     "gsb_bn_bwd_reduce": (_i, [_VP, _VP, _VP, _p, _p, _p, _p, _i, _i, _u64, _p, _p, _p, _sz, _p]),
     "gsb_bn_bwd_apply": (_i, [_VP, _VP, _VP, _p, _p, _p, _p, _i, _i, _u64, _p, _p, _d, _VP, _p, _p, _p]),
+    "gsb_bn_param_grad": (_i, [_p, _i, _p, _p, _i, _p]),
     "gsb_maxpool2_fwd": (_i, [_VP, _VP, _p]),
     "gsb_maxpool2_bwd": (_i, [_VP, _VP, _VP, _i, _p]),
     "gsb_upsample2_fwd": (_i, [_VP, _VP, _i, _i, _p]),

@@ -268,11 +268,11 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
   }
 }
 
-__global__ void bn_param_grad_kernel(const double* __restrict__ sums, int C, float* dgamma, float* dbeta) {
+__global__ void bn_param_grad_kernel(const double* __restrict__ sums, int C, float* dgamma, float* dbeta, int accumulate = 1) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
-  if (dbeta) dbeta[c] += (float)sums[c];
-  if (dgamma) dgamma[c] += (float)sums[C + c];
+  if (dbeta) dbeta[c] = (accumulate ? dbeta[c] : 0.f) + (float)sums[c];
+  if (dgamma) dgamma[c] = (accumulate ? dgamma[c] : 0.f) + (float)sums[C + c];
 }
 
 static int grid_for(int64_t P, int lanes) {
@@ -410,4 +410,10 @@ extern "C" int gsb_bn_bwd_apply(const gsb_view* x, const gsb_view* dA1, const gs
   if (mean != nullptr && (dgamma || dbeta))
     bn_param_grad_kernel<<<(C + 127) / 128, 128, 0, to_stream(s)>>>(sums, C, dgamma, dbeta);
   return check_launch("bn_bwd_apply", (mean != nullptr && (dgamma || dbeta)) ? 2 : 1);
+}
+
+extern "C" int gsb_bn_param_grad(const double* sums, int c, float* dgamma, float* dbeta, int accumulate, gsb_stream s) {
+  GSB_REQUIRE(sums != nullptr, "bn_param_grad: null sums");
+  bn_param_grad_kernel<<<(c + 127) / 128, 128, 0, to_stream(s)>>>(sums, c, dgamma, dbeta, accumulate);
+  return check_launch("bn_param_grad");
 }

@@ -196,18 +196,17 @@ class ConvBNAct:
         if train_bn:
             sums = ops.bn_bwd_reduce(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2,
                                      sv.drop_seed, sv.drop_mask)
+            if need_bn:   # parameter gradients from the LOCAL sums (the gradient all-reduce adds the other ranks)
+                dgamma, dbeta = ops.bn_param_grad(sums, s.cout)
             sums, _ = _sync_stats(sums, 0.0)
             mean, invstd = sv.mean, sv.invstd
-            if need_bn:
-                dgamma = torch.zeros(s.cout, device=device, dtype=torch.float32)
-                dbeta = torch.zeros(s.cout, device=device, dtype=torch.float32)
         elif self.has_bn and need_bn:
             # eval-mode BatchNorm (running statistics are constants): dgamma = sum dy*xhat_running, dbeta = sum dy
             es = ops.bn_bwd_reduce(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2,
                                    sv.drop_seed, sv.drop_mask)
-            dbeta, dgamma = es[:s.cout].float(), es[s.cout:].float()
+            dgamma, dbeta = ops.bn_param_grad(es, s.cout)
         ops.bn_bwd_apply(y, dA1, dA2, sv.scale, sv.shift, mean, invstd, self.act1, act2, sums, sv.count, dY,
-                         dgamma if train_bn else None, dbeta if train_bn else None, sv.drop_seed, sv.drop_mask)
+                         None, None, sv.drop_seed, sv.drop_mask)
         dyv = view_nhwc(dY)
         dweight = dbias = None
         if need_dw and sv.extra.get("stem"):

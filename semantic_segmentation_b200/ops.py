@@ -214,6 +214,13 @@ def bn_bwd_apply(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, sums, coun
                                   float(count), _ref(view_nhwc(dx)), ptr(dgamma), ptr(dbeta), _s(x)), "bn_bwd_apply")
 
 
+def bn_param_grad(sums: torch.Tensor, c: int):
+    dgamma = torch.empty(c, device=sums.device, dtype=torch.float32)
+    dbeta = torch.empty(c, device=sums.device, dtype=torch.float32)
+    check(load().gsb_bn_param_grad(ptr(sums), c, ptr(dgamma), ptr(dbeta), 0, _s(sums)), "bn_param_grad")
+    return dgamma, dbeta
+
+
 # ---- pooling / resampling -------------------------------------------------------------------
 
 def maxpool2_fwd(x: torch.Tensor) -> torch.Tensor:
