@@ -1,0 +1,573 @@
+// Halo-stationary tcgen05 implicit-GEMM convolution (fprop / dgrad) for sm_100a.
+//
+// Why a second kernel: the shifted-window kernel of conv_tc.cu re-loads the full 128-pixel activation box for
+// every filter tap, i.e. 24 KB of TMA traffic per 128x64x64 MMA block.  ncu (profiles/r01_*) shows the tensor
+// pipe 14-29 % busy with the L2->SM operand feed as the limiter.  Here one CTA owns a 16x16 output-pixel tile
+// (two M=128 accumulators, 8x16 pixels each) and, per 64-channel block, loads the input window ONCE PER
+// HORIZONTAL TAP OFFSET with a vertical halo:  box = 64 ch x 16 px x (16 + ndy - 1) rows.  All vertical taps are
+// then plain row shifts of that box: +dy rows = +dy*16*128 B, a multiple of the 1024 B swizzle atom, so the UMMA
+// shared-memory descriptor of tap (dx, dy) / M-tile m is simply
+//      start = slot + m*1024 + dy*2048,  SBO = 2048 (next pixel row),  SWIZZLE_128B, K-major
+// and stays canonical (no base-offset games).  A 3x3 convolution therefore moves 3 boxes of 36 KB per 64-channel
+// block for 256 output pixels instead of 18 boxes of 16 KB, and every weight tile (BN x 64) is used by two
+// M-tiles: 2.4x less operand traffic per FLOP at BN=128.
+//
+// Roles (192 threads): warp 0 = TMA producer (activation ring + weight ring, separate mbarrier pairs),
+// warp 1 = tcgen05.mma issuer (accumulators double-buffered in TMEM: 2 buffers x 2 M-tiles x BN columns),
+// warps 2-5 = epilogue (tcgen05.ld -> bias/act -> bf16 -> swizzled smem -> TMA store, fused BN sum / sum-sq).
+//
+// Covers every stride-1 window structure whose taps, for a fixed (parity map, dx), have consecutive dy:
+// 3x3 s1 (unet/unet_parts.py:16,19 fwd + dgrad), 4x4 s1/s2 and the parity phases of transposed convs
+// (models_pix2pix/networks.py:582,647,655; architecture_pix2pix/operations.py:14-39).
+#include <stdlib.h>
+
+#include "tc_common.cuh"
+
+namespace gsb {
+
+constexpr int kHaloMaxGroups = 16;
+constexpr int kHaloMaxDy = 4;
+struct HaloPlan {
+  int ngroups;
+  int8_t map[kHaloMaxGroups], dx[kHaloMaxGroups], dy0[kHaloMaxGroups], ndy[kHaloMaxGroups];
+  uint8_t wtap[kHaloMaxGroups][kHaloMaxDy];
+};
+struct HaloParams {
+  int tiles_x, tiles_y;  // 16x16 tiles per image
+  int W, H, N;           // extents of the tiled (output) space
+  int cin, cout, n_tiles, num_tiles;
+  int nA, nB, a_bytes;   // ring depths and activation slot size (16 x boxh x 128 B)
+  int act;
+  const float* bias;
+  float* stats;          // [2*spatial_tiles][2][cout] or null
+};
+
+template <int BN>
+__global__ void __launch_bounds__(192, 1)
+conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ HaloPlan plan, const HaloParams p) {
+  constexpr int B_BYTES = BN * 128;
+  constexpr int OUT_BYTES = 128 * BN * 2;
+  constexpr int RED_BYTES = 4 * 2 * BN * 4;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + p.nA * p.a_bytes;
+  uint8_t* s_out = sB + p.nB * B_BYTES;
+  float* s_red = reinterpret_cast<float*>(s_out + OUT_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_out + OUT_BYTES + RED_BYTES);
+  uint64_t* fullA = bars;
+  uint64_t* emptyA = bars + 4;
+  uint64_t* fullB = bars + 8;
+  uint64_t* emptyB = bars + 16;
+  uint64_t* tfull = bars + 24;
+  uint64_t* tempty = bars + 26;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(bars + 28);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 4; ++i) {
+      mbar_init(&fullA[i], 1);
+      mbar_init(&emptyA[i], 1);
+    }
+    for (int i = 0; i < 8; ++i) {
+      mbar_init(&fullB[i], 1);
+      mbar_init(&emptyB[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tfull[i], 1);
+      mbar_init(&tempty[i], 128);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    prefetch_tmap(&maps.w);
+    prefetch_tmap(&maps.out);
+    prefetch_tmap(&maps.in[0]);
+  }
+  __syncthreads();
+  if (warp == 1) tmem_alloc(tmem_holder, 4 * BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+  const int kblocks = p.cin >> 6;
+  const int per_img = p.tiles_x * p.tiles_y;
+
+  if (warp == 0) {
+    if (lane == 0) {  // ---------------- TMA producer ----------------
+      int sa = 0, sb = 0;
+      uint32_t pa = 0, pb = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        const int nt = tile % p.n_tiles, st = tile / p.n_tiles;
+        const int n = st / per_img, r = st % per_img;
+        const int x0 = (r % p.tiles_x) * 16, y0 = (r / p.tiles_x) * 16;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          for (int g = 0; g < plan.ngroups; ++g) {
+            mbar_wait(&emptyA[sa], pa ^ 1u);
+            mbar_expect_tx(&fullA[sa], (uint32_t)p.a_bytes);
+            tma_load_4d(&maps.in[plan.map[g]], &fullA[sa], sA + sa * p.a_bytes, kb * 64, x0 + plan.dx[g], y0 + plan.dy0[g], n);
+            if (++sa == p.nA) { sa = 0; pa ^= 1u; }
+            const int nd = plan.ndy[g];
+            for (int j = 0; j < nd; ++j) {
+              mbar_wait(&emptyB[sb], pb ^ 1u);
+              mbar_expect_tx(&fullB[sb], B_BYTES);
+              tma_load_2d(&maps.w, &fullB[sb], sB + sb * B_BYTES, kb * 64, (int)plan.wtap[g][j] * p.cout + nt * BN);
+              if (++sb == p.nB) { sb = 0; pb ^= 1u; }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {  // ---------------- MMA issuer ----------------
+      constexpr uint32_t idesc = umma_idesc(128, BN, 0, 0);
+      int sa = 0, sb = 0;
+      uint32_t pa = 0, pb = 0, acc = 0, acc_phase = 0;
+      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+        mbar_wait(&tempty[acc], acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d0 = tmem_base + acc * (2 * BN);
+        uint32_t accum = 0;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          for (int g = 0; g < plan.ngroups; ++g) {
+            mbar_wait(&fullA[sa], pa);
+            tc_fence_after();
+            const uint32_t a_base = smem_u32(sA + sa * p.a_bytes);
+            const int nd = plan.ndy[g];
+            for (int j = 0; j < nd; ++j) {
+              mbar_wait(&fullB[sb], pb);
+              tc_fence_after();
+              const uint64_t bdesc = umma_desc(smem_u32(sB + sb * B_BYTES), 16, 1024);
+#pragma unroll
+              for (int m = 0; m < 2; ++m) {
+                const uint64_t adesc = umma_desc(a_base + m * 1024 + j * 2048, 16, 2048);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_bf16(d0 + m * BN, adesc + 2 * k, bdesc + 2 * k, idesc, accum | (uint32_t)k);
+              }
+              accum = 1;
+              umma_commit(&emptyB[sb]);
+              if (++sb == p.nB) { sb = 0; pb ^= 1u; }
+            }
+            umma_commit(&emptyA[sa]);
+            if (++sa == p.nA) { sa = 0; pa ^= 1u; }
+          }
+        }
+        umma_commit(&tfull[acc]);
+        acc ^= 1u;
+        if (acc == 0) acc_phase ^= 1u;
+      }
+    }
+  } else {  // ---------------- epilogue warps 2..5 ----------------
+    const int q = warp & 3;         // TMEM lane quarter this warp may access
+    const int row = q * 32 + lane;  // accumulator row: pixel (row % 8, row / 8) of the 8x16 M-tile
+    const int et = threadIdx.x - 64;
+    const float slope = p.act == GSB_ACT_RELU ? 0.f : (p.act == GSB_ACT_LRELU ? 0.2f : 1.f);
+    const bool is_tanh = p.act == GSB_ACT_TANH;
+    uint32_t acc = 0, acc_phase = 0;
+    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      const int nt = tile % p.n_tiles, st = tile / p.n_tiles;
+      const int n = st / per_img, r = st % per_img;
+      const int x0 = (r % p.tiles_x) * 16, y0 = (r / p.tiles_x) * 16;
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+#pragma unroll 1
+      for (int m = 0; m < 2; ++m) {
+        const bool valid = (x0 + m * 8 + (row & 7) < p.W) && (y0 + (row >> 3) < p.H);
+        if (et == 0) tma_store_wait_read();  // the previous store has finished reading s_out
+        named_bar_sync(1, 128);
+#pragma unroll 1
+        for (int ch = 0; ch < BN / 32; ++ch) {
+          uint32_t v[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * (2 * BN) + m * BN + ch * 32, v);
+          const int cbase = nt * BN + ch * 32;
+          uint8_t* slab = s_out + (ch >> 1) * (128 * 128) + row * 128;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint32_t pk[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              float f0 = __uint_as_float(v[g * 8 + 2 * e]), f1 = __uint_as_float(v[g * 8 + 2 * e + 1]);
+              if (p.bias != nullptr) {
+                f0 += __ldg(p.bias + cbase + g * 8 + 2 * e);
+                f1 += __ldg(p.bias + cbase + g * 8 + 2 * e + 1);
+              }
+              if (is_tanh) {
+                f0 = tanhf(f0);
+                f1 = tanhf(f1);
+              } else {
+                f0 = f0 > 0.f ? f0 : f0 * slope;
+                f1 = f1 > 0.f ? f1 : f1 * slope;
+              }
+              if (!valid) f0 = f1 = 0.f;
+              __nv_bfloat162 h = __floats2bfloat162_rn(f0, f1);
+              pk[e] = *reinterpret_cast<uint32_t*>(&h);
+            }
+            const int c16 = (ch & 1) * 4 + g;  // 16-byte chunk inside the 128-byte row
+            *reinterpret_cast<uint4*>(slab + ((c16 ^ (row & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+          }
+        }
+        if (m == 1) {
+          tc_fence_before();
+          mbar_arrive(&tempty[acc]);  // both accumulators drained: the MMA warp may start the tile after next
+        }
+        fence_proxy_async();
+        named_bar_sync(1, 128);
+        if (et == 0) {
+#pragma unroll
+          for (int s = 0; s < BN / 64; ++s) tma_store_4d(&maps.out, s_out + s * (128 * 128), nt * BN + s * 64, x0 + m * 8, y0, n);
+          tma_store_commit();
+        }
+        if (p.stats != nullptr) {
+          // per-channel sum / sum-of-squares of the bf16 values just staged (invalid rows hold zeros)
+          const int w = et & 31, rg = et >> 5;
+#pragma unroll
+          for (int s = 0; s < BN / 64; ++s) {
+            float s0a = 0.f, s0b = 0.f, s1a = 0.f, s1b = 0.f;
+            const uint8_t* slab = s_out + s * (128 * 128);
+#pragma unroll 8
+            for (int i = 0; i < 32; ++i) {
+              const int rr = rg * 32 + i;
+              uint32_t u = *reinterpret_cast<const uint32_t*>(slab + rr * 128 + (((w >> 2) ^ (rr & 7)) << 4) + (w & 3) * 4);
+              float2 f = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u));
+              s0a += f.x; s0b += f.y;
+              s1a = fmaf(f.x, f.x, s1a); s1b = fmaf(f.y, f.y, s1b);
+            }
+            float* rd = s_red + rg * (2 * BN);
+            rd[s * 64 + 2 * w] = s0a;
+            rd[s * 64 + 2 * w + 1] = s0b;
+            rd[BN + s * 64 + 2 * w] = s1a;
+            rd[BN + s * 64 + 2 * w + 1] = s1b;
+          }
+          named_bar_sync(2, 128);
+          const int64_t mrow = (int64_t)st * 2 + m;
+          for (int j = et; j < 2 * BN; j += 128) {
+            float a = s_red[j] + s_red[2 * BN + j] + s_red[4 * BN + j] + s_red[6 * BN + j];
+            const int which = j / BN, c = j % BN;
+            p.stats[(mrow * 2 + which) * p.cout + nt * BN + c] = a;
+          }
+          named_bar_sync(2, 128);
+        }
+      }
+      acc ^= 1u;
+      if (acc == 0) acc_phase ^= 1u;
+    }
+    if (et == 0) tma_store_wait_read();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 4 * BN);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Weight gradient, halo-stationary:  dWp[tap][co][ci] = sum_pix dY[pix][co] * X[pix @ tap][ci]
+//
+// GEMM with K = pixels, so both operands are MN-major in the TMA boxes (64 channels x 128 B rows of pixels).
+// One CTA owns: an M-tile = two 64-channel blocks of the SHIFTED tensor (each tied to a (parity map, dx) group),
+// an N-tile = BN channels of the TILED tensor, and a range of 8x16-pixel boxes (split-K).  The shifted boxes are
+// loaded with a vertical halo (8 x (16+ndy-1) pixels); the ndy vertical taps are K-row shifts of +1024 B and
+// accumulate into ndy separate TMEM accumulators, so one pass over the pixels produces all vertical taps:
+// 3x less operand traffic than one (tap, block) pair per CTA.  Epilogue: fp32 red.global.add into dWp.
+// ------------------------------------------------------------------------------------------------------
+struct WgHaloParams {
+  int tiles_x, tiles_y;  // 8x16 pixel boxes per image
+  int boxes, boxes_per_split;
+  int a_blocks, a_cblocks;  // (group, 64-channel) blocks of the shifted side; channel blocks per group
+  int n_tiles, ndy;
+  int a_is_in;              // 1: shifted side is the forward input (rows = ci), 0: it is dY (rows = co)
+  int cin, cout;
+  int a_block_bytes, nstages;
+  float* dwp;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(192, 1)
+conv_tc_wgrad_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ HaloPlan plan, const WgHaloParams p) {
+  constexpr int B_BYTES = (BN / 64) * 16384;
+  constexpr int TMEM_COLS = BN == 128 ? 512 : 256;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int stage_bytes = 2 * p.a_block_bytes + B_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.nstages * stage_bytes);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + 8;
+  uint64_t* tfull = bars + 16;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(bars + 17);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 8; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    mbar_init(tfull, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    prefetch_tmap(&maps.w);
+    prefetch_tmap(&maps.in[0]);
+  }
+  __syncthreads();
+  if (warp == 1) tmem_alloc(tmem_holder, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+
+  const int mt = blockIdx.x / p.n_tiles, nt = blockIdx.x % p.n_tiles;
+  const int blk0 = mt * 2, blk1 = (mt * 2 + 1 < p.a_blocks) ? mt * 2 + 1 : mt * 2;
+  const int box_begin = blockIdx.y * p.boxes_per_split;
+  const int box_end = min(box_begin + p.boxes_per_split, p.boxes);
+  const int nsteps = box_end - box_begin;
+  const int per_img = p.tiles_x * p.tiles_y;
+
+  if (warp == 0) {
+    if (lane == 0 && nsteps > 0) {
+      const int g0 = blk0 / p.a_cblocks, c0 = (blk0 % p.a_cblocks) * 64;
+      const int g1 = blk1 / p.a_cblocks, c1 = (blk1 % p.a_cblocks) * 64;
+      const void* m0 = &maps.in[plan.map[g0]];
+      const void* m1 = &maps.in[plan.map[g1]];
+      const int dx0 = plan.dx[g0], dy0 = plan.dy0[g0], dx1 = plan.dx[g1], dy1 = plan.dy0[g1];
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int b = box_begin; b < box_end; ++b) {
+        const int n = b / per_img, r = b % per_img;
+        const int x0 = (r % p.tiles_x) * 8, y0 = (r / p.tiles_x) * 16;
+        mbar_wait(&empty[stage], phase ^ 1u);
+        mbar_expect_tx(&full[stage], (uint32_t)stage_bytes);
+        uint8_t* sa = smem + stage * stage_bytes;
+        tma_load_4d(m0, &full[stage], sa, c0, x0 + dx0, y0 + dy0, n);
+        tma_load_4d(m1, &full[stage], sa + p.a_block_bytes, c1, x0 + dx1, y0 + dy1, n);
+#pragma unroll
+        for (int j = 0; j < BN / 64; ++j)
+          tma_load_4d(&maps.w, &full[stage], sa + 2 * p.a_block_bytes + j * 16384, nt * BN + j * 64, x0, y0, n);
+        if (++stage == p.nstages) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && nsteps > 0) {
+      constexpr uint32_t idesc = umma_idesc(128, BN, 1, 1);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int s = 0; s < nsteps; ++s) {
+        mbar_wait(&full[stage], phase);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + stage * stage_bytes);
+        const uint64_t adesc = umma_desc(sa, (uint32_t)p.a_block_bytes, 1024);
+        const uint64_t bdesc = umma_desc(sa + 2 * p.a_block_bytes, 16384, 1024);
+        for (int j = 0; j < p.ndy; ++j) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)  // 16 pixels (two 8-pixel rows) per MMA; vertical tap j = +j rows
+            umma_bf16(tmem_base + j * BN, adesc + (uint64_t)(64 * j + 128 * k), bdesc + (uint64_t)(128 * k), idesc,
+                      (uint32_t)(s | k));
+        }
+        umma_commit(&empty[stage]);
+        if (++stage == p.nstages) { stage = 0; phase ^= 1u; }
+      }
+      umma_commit(tfull);
+    }
+  } else if (nsteps > 0) {
+    const int q = warp & 3, row = q * 32 + lane;
+    const int blk = mt * 2 + (row >> 6);
+    const bool rvalid = blk < p.a_blocks;
+    const int g = rvalid ? blk / p.a_cblocks : 0;
+    const int a_ch = rvalid ? (blk % p.a_cblocks) * 64 + (row & 63) : 0;
+    mbar_wait(tfull, 0);
+    tc_fence_after();
+#pragma unroll 1
+    for (int j = 0; j < p.ndy; ++j) {
+      const int tap = (int)plan.wtap[g][j];
+#pragma unroll 1
+      for (int ch = 0; ch < BN / 32; ++ch) {
+        uint32_t v[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + j * BN + ch * 32, v);
+        if (rvalid) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int b_ch = nt * BN + ch * 32 + i;
+            const int64_t idx = p.a_is_in ? ((int64_t)tap * p.cout + b_ch) * p.cin + a_ch
+                                          : ((int64_t)tap * p.cout + a_ch) * p.cin + b_ch;
+            atomicAdd(p.dwp + idx, __uint_as_float(v[i]));
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Host side
+// ------------------------------------------------------------------------------------------------------
+static bool halo_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("GSB_TC_HALO");
+    v = (e != nullptr && e[0] == '0') ? 0 : 1;
+  }
+  return v != 0;
+}
+
+// Group the taps by (parity map, dx); inside a group dy must be consecutive.  Returns false when the structure
+// does not fit (caller falls back to the shifted-window kernel).
+static bool build_halo_plan(const TcTaps& taps, HaloPlan& plan, int& max_ndy, bool& uniform) {
+  memset(&plan, 0, sizeof(plan));
+  int dys[kHaloMaxGroups][kMaxTaps], wts[kHaloMaxGroups][kMaxTaps], cnt[kHaloMaxGroups];
+  for (int t = 0; t < taps.ntaps; ++t) {
+    int g = -1;
+    for (int i = 0; i < plan.ngroups; ++i)
+      if (plan.map[i] == taps.map[t] && plan.dx[i] == taps.dx[t]) g = i;
+    if (g < 0) {
+      if (plan.ngroups == kHaloMaxGroups) return false;
+      g = plan.ngroups++;
+      plan.map[g] = taps.map[t];
+      plan.dx[g] = taps.dx[t];
+      cnt[g] = 0;
+    }
+    dys[g][cnt[g]] = taps.dy[t];
+    wts[g][cnt[g]] = taps.wtap[t];
+    cnt[g]++;
+  }
+  max_ndy = 1;
+  uniform = true;
+  for (int g = 0; g < plan.ngroups; ++g) {
+    if (cnt[g] > kHaloMaxDy) return false;
+    for (int a = 0; a < cnt[g]; ++a)  // insertion sort by dy
+      for (int b = a + 1; b < cnt[g]; ++b)
+        if (dys[g][b] < dys[g][a]) {
+          int t0 = dys[g][a]; dys[g][a] = dys[g][b]; dys[g][b] = t0;
+          t0 = wts[g][a]; wts[g][a] = wts[g][b]; wts[g][b] = t0;
+        }
+    for (int a = 1; a < cnt[g]; ++a)
+      if (dys[g][a] != dys[g][a - 1] + 1) return false;
+    plan.dy0[g] = (int8_t)dys[g][0];
+    plan.ndy[g] = (int8_t)cnt[g];
+    for (int a = 0; a < cnt[g]; ++a) plan.wtap[g][a] = (uint8_t)wts[g][a];
+    if (cnt[g] > max_ndy) max_ndy = cnt[g];
+    if (cnt[g] != cnt[0]) uniform = false;
+  }
+  return plan.ngroups > 0;
+}
+
+bool conv_halo_applicable(const SubView& outv) { return halo_enabled() && outv.W >= 16 && outv.H >= 16; }
+int conv_halo_m_tiles(int w, int h, int n) { return ((w + 15) / 16) * ((h + 15) / 16) * n * 2; }
+
+// Returns 1 when the launch was issued, 0 when the tap structure does not fit (caller falls back), -1 on error.
+int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, const TcTaps& taps, const void* wp, int taps_total,
+                    int cin, int cout, const float* bias, int act, float* stats, int* stats_rows, cudaStream_t st) {
+  if (!conv_halo_applicable(outv)) return 0;
+  HaloPlan plan;
+  int max_ndy;
+  bool uniform;
+  if (!build_halo_plan(taps, plan, max_ndy, uniform)) return 0;
+  const int boxh = 16 + max_ndy - 1;
+  TcMaps maps;
+  memset(&maps, 0, sizeof(maps));
+  for (int i = 0; i < nmaps; ++i)
+    if (make_act_map(&maps.in[i], shifted[i], 16, boxh, 1)) return -1;
+  for (int i = nmaps; i < 4; ++i) maps.in[i] = maps.in[0];
+  if (make_act_map(&maps.out, outv, 8, 16, 1)) return -1;
+  const int BN = (cout % 128 == 0) ? 128 : 64;
+  if (make_w_map(&maps.w, wp, (int64_t)taps_total * cout, cin, BN)) return -1;
+  HaloParams p;
+  p.tiles_x = ((int)outv.W + 15) / 16;
+  p.tiles_y = ((int)outv.H + 15) / 16;
+  p.W = (int)outv.W; p.H = (int)outv.H; p.N = (int)outv.N;
+  p.cin = cin; p.cout = cout;
+  p.n_tiles = cout / BN;
+  p.num_tiles = p.tiles_x * p.tiles_y * p.N * p.n_tiles;
+  p.a_bytes = 16 * boxh * 128;
+  const int b_bytes = BN * 128;
+  const int fixed = 1024 + 128 * BN * 2 + 4 * 2 * BN * 4 + 256;
+  p.nB = BN == 64 ? 6 : 4;
+  int nA = (232448 - fixed - p.nB * b_bytes) / p.a_bytes;
+  p.nA = nA > 4 ? 4 : nA;
+  GSB_REQUIRE(p.nA >= 2, "conv_halo: shared memory budget");
+  p.act = act; p.bias = bias; p.stats = stats;
+  if (stats_rows) *stats_rows = conv_halo_m_tiles(p.W, p.H, p.N);
+  const int smem = fixed + p.nA * p.a_bytes + p.nB * b_bytes;
+  const int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+  cudaError_t e;
+  if (BN == 128) {
+    e = cudaFuncSetAttribute(conv_tc_halo_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    GSB_REQUIRE(e == cudaSuccess, "cudaFuncSetAttribute(smem=%d) failed: %s", smem, cudaGetErrorString(e));
+    conv_tc_halo_kernel<128><<<grid, 192, smem, st>>>(maps, plan, p);
+  } else {
+    e = cudaFuncSetAttribute(conv_tc_halo_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    GSB_REQUIRE(e == cudaSuccess, "cudaFuncSetAttribute(smem=%d) failed: %s", smem, cudaGetErrorString(e));
+    conv_tc_halo_kernel<64><<<grid, 192, smem, st>>>(maps, plan, p);
+  }
+  if (check_launch("conv_tc_halo launch")) return -1;
+  return 1;
+}
+
+// Weight gradient through the halo kernel.  Returns 1 when launched, 0 when not applicable, -1 on error.
+int conv_halo_wgrad(const SubView& tiled, const SubView* shifted, int nmaps, const TcTaps& taps, int shifted_c, int a_is_in,
+                    int cin, int cout, float* dwp, cudaStream_t st) {
+  if (!halo_enabled() || tiled.W < 8 || tiled.H < 16) return 0;
+  HaloPlan plan;
+  int max_ndy;
+  bool uniform;
+  if (!build_halo_plan(taps, plan, max_ndy, uniform) || !uniform) return 0;
+  const int BN = (tiled.C % 128 == 0) ? 128 : 64;
+  if (max_ndy * BN > (BN == 128 ? 512 : 256)) return 0;
+  const int boxh = 16 + max_ndy - 1;
+  TcMaps maps;
+  memset(&maps, 0, sizeof(maps));
+  for (int i = 0; i < nmaps; ++i)
+    if (make_act_map(&maps.in[i], shifted[i], 8, boxh, 1)) return -1;
+  for (int i = nmaps; i < 4; ++i) maps.in[i] = maps.in[0];
+  if (make_act_map(&maps.w, tiled, 8, 16, 1)) return -1;
+  maps.out = maps.w;
+  WgHaloParams p;
+  p.tiles_x = ((int)tiled.W + 7) / 8;
+  p.tiles_y = ((int)tiled.H + 15) / 16;
+  p.boxes = p.tiles_x * p.tiles_y * (int)tiled.N;
+  p.a_cblocks = shifted_c / 64;
+  p.a_blocks = plan.ngroups * p.a_cblocks;
+  p.n_tiles = (int)tiled.C / BN;
+  p.ndy = max_ndy;
+  p.a_is_in = a_is_in;
+  p.cin = cin; p.cout = cout;
+  p.a_block_bytes = 8 * boxh * 128;
+  p.dwp = dwp;
+  const int stage_bytes = 2 * p.a_block_bytes + (BN / 64) * 16384;
+  int nst = (232448 - 1024 - 256) / stage_bytes;
+  p.nstages = nst > 8 ? 8 : nst;
+  GSB_REQUIRE(p.nstages >= 2, "conv_halo_wgrad: shared memory budget");
+  const int m_tiles = (p.a_blocks + 1) / 2;
+  const int base = m_tiles * p.n_tiles;
+  // split-K over the pixel boxes: fill whole waves of SMs, keep >= 2 boxes per CTA
+  const int sms = num_sms();
+  int max_split = p.boxes / 2 > 0 ? p.boxes / 2 : 1;
+  int best = 1;
+  double best_eff = 0.0;
+  for (int sp = 1; sp <= max_split && sp <= 4 * sms; ++sp) {
+    const long long ctas = (long long)base * sp;
+    const long long waves = (ctas + sms - 1) / sms;
+    const double eff = (double)ctas / (double)(waves * sms);
+    if (eff > best_eff + 1e-9) { best_eff = eff; best = sp; }
+    if (eff >= 0.95 && ctas >= sms) { best = sp; break; }
+  }
+  p.boxes_per_split = (p.boxes + best - 1) / best;
+  const int split = (p.boxes + p.boxes_per_split - 1) / p.boxes_per_split;
+  GSB_REQUIRE(split <= 65535, "conv_halo_wgrad: split too large");
+  const int smem = 1024 + 256 + p.nstages * stage_bytes;
+  cudaError_t e;
+  if (BN == 128) {
+    e = cudaFuncSetAttribute(conv_tc_wgrad_halo_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    GSB_REQUIRE(e == cudaSuccess, "cudaFuncSetAttribute(smem=%d) failed: %s", smem, cudaGetErrorString(e));
+    conv_tc_wgrad_halo_kernel<128><<<dim3(base, split), 192, smem, st>>>(maps, plan, p);
+  } else {
+    e = cudaFuncSetAttribute(conv_tc_wgrad_halo_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    GSB_REQUIRE(e == cudaSuccess, "cudaFuncSetAttribute(smem=%d) failed: %s", smem, cudaGetErrorString(e));
+    conv_tc_wgrad_halo_kernel<64><<<dim3(base, split), 192, smem, st>>>(maps, plan, p);
+  }
+  if (check_launch("conv_tc_wgrad_halo launch")) return -1;
+  return 1;
+}
+
+}  // namespace gsb

@@ -41,6 +41,13 @@ GEOMS = [  # kind, k, stride, pad, cin, cout, n, h, w
     ("convT", 8, 2, 3, 128, 64, 2, 4, 4),
     ("convT", 8, 2, 3, 64, 64, 3, 1, 1),
     ("conv", 4, 2, 1, 64, 64, 5, 2, 2),
+    # halo-stationary tcgen05 kernel (tiled space >= 16x16): full / partial tiles, 2 N-tiles, 4x4 windows, parity phases
+    ("conv", 3, 1, 1, 128, 128, 2, 32, 48),
+    ("conv", 3, 1, 1, 64, 256, 1, 16, 16),
+    ("conv", 3, 1, 1, 192, 64, 1, 20, 17),
+    ("convT", 8, 2, 3, 64, 64, 1, 16, 16),
+    ("convT", 2, 2, 0, 128, 64, 2, 16, 16),
+    ("conv", 4, 2, 1, 128, 128, 1, 64, 64),
 ]
 
 
