@@ -97,8 +97,12 @@ int gsb_conv_wgrad(const gsb_view* in, const gsb_view* dout, float* dwp, const g
  *       weight (unet_model.py:14 / unet_parts.py:16; networks.py:582 outermost, :640); wgrad writes dweight (OIHW).
  * head: 1x1 Conv2d(x.c -> c<=8) + bias to fp32 NCHW logits (OutConv, unet_parts.py:71-77); backward writes
  *       dx (nullable), dweight[c][x.c] and dbias[c] (nullable; zeroed by the callee). */
+/* stats_partial (optional): [gsb_stem_stats_rows()][2][y.c] fp32 per-block BatchNorm sum / sum-of-squares of the stored
+ * values; *stats_rows receives the rows written (0 when the shape ran through the kernel without fused statistics). */
+int gsb_stem_stats_rows(void);
 int gsb_stem_conv_fwd(const float* x, int n, int cin, int h, int w, const float* weight, const float* bias,
-                      const gsb_view* y, int k, int stride, int pad, int act, gsb_stream s);
+                      const gsb_view* y, int k, int stride, int pad, int act, float* stats_partial, int* stats_rows,
+                      gsb_stream s);
 int gsb_stem_conv_wgrad(const float* x, int n, int cin, int h, int w, const gsb_view* dy, int k, int stride, int pad,
                         float* dweight, gsb_stream s);
 int gsb_head_conv_fwd(const gsb_view* x, const float* weight, const float* bias, int c, float* logits, gsb_stream s);

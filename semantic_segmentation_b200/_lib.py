@@ -46,7 +46,8 @@ SIGNATURES = {
     "gsb_conv_gather": (_i, [_VP, _p, _i, _p, _VP, _GP, _i, _i, _i, _p, _p, _p]),
     "gsb_conv_stats_rows": (_sz, [_VP, _GP]),
     "gsb_conv_wgrad": (_i, [_VP, _VP, _p, _GP, _i, _p]),
-    "gsb_stem_conv_fwd": (_i, [_p, _i, _i, _i, _i, _p, _p, _VP, _i, _i, _i, _i, _p]),
+    "gsb_stem_stats_rows": (_i, []),
+    "gsb_stem_conv_fwd": (_i, [_p, _i, _i, _i, _i, _p, _p, _VP, _i, _i, _i, _i, _p, _p, _p]),
     "gsb_stem_conv_wgrad": (_i, [_p, _i, _i, _i, _i, _VP, _i, _i, _i, _p, _p]),
     "gsb_head_conv_fwd": (_i, [_VP, _p, _p, _i, _p, _p]),
     "gsb_head_conv_bwd": (_i, [_VP, _p, _i, _p, _VP, _p, _p, _p]),

@@ -42,12 +42,34 @@ struct HaloParams {
   float* stats;          // [2*spatial_tiles][2][cout] or null
 };
 
-template <int BN>
+// multicast variants (thread-block cluster of CL CTAs working on CL spatial tiles with the same weights)
+__device__ __forceinline__ void tma_load_2d_mc(const void* map, uint64_t* bar, void* dst, int c0, int c1, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// BN = output channels per tile (64 / 128 double-buffered accumulators, 256 single-buffered);
+// CL = cluster size: the CL CTAs of a cluster own CL different 16x16 tiles with the SAME weight tile, each
+// loads 1/CL of every weight slot and multicasts it to all of them (L2 weight reads / CL).
+template <int BN, int CL>
 __global__ void __launch_bounds__(192, 1)
 conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ HaloPlan plan, const HaloParams p) {
   constexpr int B_BYTES = BN * 128;
-  constexpr int OUT_BYTES = 128 * BN * 2;
-  constexpr int RED_BYTES = 4 * 2 * BN * 4;
+  constexpr int OUT_COLS = BN > 128 ? 128 : BN;
+  constexpr int OUT_BYTES = 128 * OUT_COLS * 2;
+  constexpr int RED_BYTES = 4 * 2 * OUT_COLS * 4;
+  constexpr int NBUF = BN > 128 ? 1 : 2;
+  constexpr int TMEM_COLS = NBUF * 2 * BN;
+  constexpr uint16_t kMask = (uint16_t)((1u << CL) - 1u);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem;
@@ -71,7 +93,7 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
     }
     for (int i = 0; i < 8; ++i) {
       mbar_init(&fullB[i], 1);
-      mbar_init(&emptyB[i], 1);
+      mbar_init(&emptyB[i], CL);  // every CTA of the cluster reads the slot its peers multicast into
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
@@ -83,21 +105,26 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
     prefetch_tmap(&maps.in[0]);
   }
   __syncthreads();
-  if (warp == 1) tmem_alloc(tmem_holder, 4 * BN);
+  if (warp == 1) tmem_alloc(tmem_holder, TMEM_COLS);
   tc_fence_before();
-  __syncthreads();
+  if (CL > 1) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
   const int kblocks = p.cin >> 6;
   const int per_img = p.tiles_x * p.tiles_y;
+  const int spatial = per_img * p.N;
+  const int rank = CL > 1 ? (int)(blockIdx.x % CL) : 0;
+  const int cluster_id = (int)(blockIdx.x / CL), nclusters = (int)(gridDim.x / CL);
+  const int num_ctiles = ((spatial + CL - 1) / CL) * p.n_tiles;  // cluster tiles: CL spatial tiles x one weight tile
 
   if (warp == 0) {
     if (lane == 0) {  // ---------------- TMA producer ----------------
       int sa = 0, sb = 0;
       uint32_t pa = 0, pb = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-        const int nt = tile % p.n_tiles, st = tile / p.n_tiles;
-        const int n = st / per_img, r = st % per_img;
+      for (int tile = cluster_id; tile < num_ctiles; tile += nclusters) {
+        const int nt = tile % p.n_tiles, st = (tile / p.n_tiles) * CL + rank;
+        const bool ghost = st >= spatial;  // odd tail: out-of-range image index -> zero-filled loads, no stores
+        const int n = ghost ? p.N : st / per_img, r = ghost ? 0 : st % per_img;
         const int x0 = (r % p.tiles_x) * 16, y0 = (r / p.tiles_x) * 16;
         for (int kb = 0; kb < kblocks; ++kb) {
           for (int g = 0; g < plan.ngroups; ++g) {
@@ -109,7 +136,11 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
             for (int j = 0; j < nd; ++j) {
               mbar_wait(&emptyB[sb], pb ^ 1u);
               mbar_expect_tx(&fullB[sb], B_BYTES);
-              tma_load_2d(&maps.w, &fullB[sb], sB + sb * B_BYTES, kb * 64, (int)plan.wtap[g][j] * p.cout + nt * BN);
+              const int wrow = (int)plan.wtap[g][j] * p.cout + nt * BN;
+              if (CL > 1)
+                tma_load_2d_mc(&maps.w, &fullB[sb], sB + sb * B_BYTES + rank * (B_BYTES / CL), kb * 64, wrow + rank * (BN / CL), kMask);
+              else
+                tma_load_2d(&maps.w, &fullB[sb], sB + sb * B_BYTES, kb * 64, wrow);
               if (++sb == p.nB) { sb = 0; pb ^= 1u; }
             }
           }
@@ -121,7 +152,7 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
       constexpr uint32_t idesc = umma_idesc(128, BN, 0, 0);
       int sa = 0, sb = 0;
       uint32_t pa = 0, pb = 0, acc = 0, acc_phase = 0;
-      for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
+      for (int tile = cluster_id; tile < num_ctiles; tile += nclusters) {
         mbar_wait(&tempty[acc], acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d0 = tmem_base + acc * (2 * BN);
@@ -143,7 +174,7 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
                 for (int k = 0; k < 4; ++k) umma_bf16(d0 + m * BN, adesc + 2 * k, bdesc + 2 * k, idesc, accum | (uint32_t)k);
               }
               accum = 1;
-              umma_commit(&emptyB[sb]);
+              if (CL > 1) umma_commit_mc(&emptyB[sb], kMask); else umma_commit(&emptyB[sb]);
               if (++sb == p.nB) { sb = 0; pb ^= 1u; }
             }
             umma_commit(&emptyA[sa]);
@@ -151,8 +182,7 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
           }
         }
         umma_commit(&tfull[acc]);
-        acc ^= 1u;
-        if (acc == 0) acc_phase ^= 1u;
+        if (++acc == NBUF) { acc = 0; acc_phase ^= 1u; }
       }
     }
   } else {  // ---------------- epilogue warps 2..5 ----------------
@@ -162,22 +192,24 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
     const float slope = p.act == GSB_ACT_RELU ? 0.f : (p.act == GSB_ACT_LRELU ? 0.2f : 1.f);
     const bool is_tanh = p.act == GSB_ACT_TANH;
     uint32_t acc = 0, acc_phase = 0;
-    for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-      const int nt = tile % p.n_tiles, st = tile / p.n_tiles;
-      const int n = st / per_img, r = st % per_img;
+    for (int tile = cluster_id; tile < num_ctiles; tile += nclusters) {
+      const int nt = tile % p.n_tiles, st = (tile / p.n_tiles) * CL + rank;
+      const bool ghost = st >= spatial;
+      const int n = ghost ? p.N : st / per_img, r = ghost ? 0 : st % per_img;
       const int x0 = (r % p.tiles_x) * 16, y0 = (r / p.tiles_x) * 16;
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
 #pragma unroll 1
-      for (int m = 0; m < 2; ++m) {
-        const bool valid = (x0 + m * 8 + (row & 7) < p.W) && (y0 + (row >> 3) < p.H);
+      for (int mh = 0; mh < 2 * (BN / OUT_COLS); ++mh) {
+        const int m = mh / (BN / OUT_COLS), h = mh % (BN / OUT_COLS);  // M-tile, 128-column half
+        const bool valid = !ghost && (x0 + m * 8 + (row & 7) < p.W) && (y0 + (row >> 3) < p.H);
         if (et == 0) tma_store_wait_read();  // the previous store has finished reading s_out
         named_bar_sync(1, 128);
 #pragma unroll 1
-        for (int ch = 0; ch < BN / 32; ++ch) {
+        for (int ch = 0; ch < OUT_COLS / 32; ++ch) {
           uint32_t v[32];
-          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * (2 * BN) + m * BN + ch * 32, v);
-          const int cbase = nt * BN + ch * 32;
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * (2 * BN) + m * BN + h * OUT_COLS + ch * 32, v);
+          const int cbase = nt * BN + h * OUT_COLS + ch * 32;
           uint8_t* slab = s_out + (ch >> 1) * (128 * 128) + row * 128;
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
@@ -197,29 +229,30 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
                 f1 = f1 > 0.f ? f1 : f1 * slope;
               }
               if (!valid) f0 = f1 = 0.f;
-              __nv_bfloat162 h = __floats2bfloat162_rn(f0, f1);
-              pk[e] = *reinterpret_cast<uint32_t*>(&h);
+              __nv_bfloat162 hh = __floats2bfloat162_rn(f0, f1);
+              pk[e] = *reinterpret_cast<uint32_t*>(&hh);
             }
             const int c16 = (ch & 1) * 4 + g;  // 16-byte chunk inside the 128-byte row
             *reinterpret_cast<uint4*>(slab + ((c16 ^ (row & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
           }
         }
-        if (m == 1) {
+        if (mh == 2 * (BN / OUT_COLS) - 1) {
           tc_fence_before();
-          mbar_arrive(&tempty[acc]);  // both accumulators drained: the MMA warp may start the tile after next
+          mbar_arrive(&tempty[acc]);  // accumulators drained: the MMA warp may reuse this TMEM buffer
         }
         fence_proxy_async();
         named_bar_sync(1, 128);
-        if (et == 0) {
+        if (et == 0 && !ghost) {
 #pragma unroll
-          for (int s = 0; s < BN / 64; ++s) tma_store_4d(&maps.out, s_out + s * (128 * 128), nt * BN + s * 64, x0 + m * 8, y0, n);
+          for (int s = 0; s < OUT_COLS / 64; ++s)
+            tma_store_4d(&maps.out, s_out + s * (128 * 128), nt * BN + h * OUT_COLS + s * 64, x0 + m * 8, y0, n);
           tma_store_commit();
         }
-        if (p.stats != nullptr) {
+        if (p.stats != nullptr && !ghost) {
           // per-channel sum / sum-of-squares of the bf16 values just staged (invalid rows hold zeros)
           const int w = et & 31, rg = et >> 5;
 #pragma unroll
-          for (int s = 0; s < BN / 64; ++s) {
+          for (int s = 0; s < OUT_COLS / 64; ++s) {
             float s0a = 0.f, s0b = 0.f, s1a = 0.f, s1b = 0.f;
             const uint8_t* slab = s_out + s * (128 * 128);
 #pragma unroll 8
@@ -230,32 +263,31 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
               s0a += f.x; s0b += f.y;
               s1a = fmaf(f.x, f.x, s1a); s1b = fmaf(f.y, f.y, s1b);
             }
-            float* rd = s_red + rg * (2 * BN);
+            float* rd = s_red + rg * (2 * OUT_COLS);
             rd[s * 64 + 2 * w] = s0a;
             rd[s * 64 + 2 * w + 1] = s0b;
-            rd[BN + s * 64 + 2 * w] = s1a;
-            rd[BN + s * 64 + 2 * w + 1] = s1b;
+            rd[OUT_COLS + s * 64 + 2 * w] = s1a;
+            rd[OUT_COLS + s * 64 + 2 * w + 1] = s1b;
           }
           named_bar_sync(2, 128);
           const int64_t mrow = (int64_t)st * 2 + m;
-          for (int j = et; j < 2 * BN; j += 128) {
-            float a = s_red[j] + s_red[2 * BN + j] + s_red[4 * BN + j] + s_red[6 * BN + j];
-            const int which = j / BN, c = j % BN;
-            p.stats[(mrow * 2 + which) * p.cout + nt * BN + c] = a;
+          for (int j = et; j < 2 * OUT_COLS; j += 128) {
+            float a = s_red[j] + s_red[2 * OUT_COLS + j] + s_red[4 * OUT_COLS + j] + s_red[6 * OUT_COLS + j];
+            const int which = j / OUT_COLS, c = j % OUT_COLS;
+            p.stats[(mrow * 2 + which) * p.cout + nt * BN + h * OUT_COLS + c] = a;
           }
           named_bar_sync(2, 128);
         }
       }
-      acc ^= 1u;
-      if (acc == 0) acc_phase ^= 1u;
+      if (++acc == NBUF) { acc = 0; acc_phase ^= 1u; }
     }
     if (et == 0) tma_store_wait_read();
   }
   tc_fence_before();
-  __syncthreads();
+  if (CL > 1) cluster_sync_all(); else __syncthreads();  // no CTA may exit while a peer still multicasts into it
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 4 * BN);
+    tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
@@ -452,6 +484,22 @@ static bool build_halo_plan(const TcTaps& taps, HaloPlan& plan, int& max_ndy, bo
   return plan.ngroups > 0;
 }
 
+static bool env_flag(const char* name, bool dflt) {
+  const char* e = getenv(name);
+  if (e == nullptr || e[0] == 0) return dflt;
+  return e[0] != '0';
+}
+static bool cluster_enabled() {
+  static int v = -1;
+  if (v < 0) v = env_flag("GSB_TC_CLUSTER", true) ? 1 : 0;
+  return v != 0;
+}
+static bool bn256_enabled() {
+  static int v = -1;
+  if (v < 0) v = env_flag("GSB_TC_BN256", true) ? 1 : 0;
+  return v != 0;
+}
+
 bool conv_halo_applicable(const SubView& outv) { return halo_enabled() && outv.W >= 16 && outv.H >= 16; }
 int conv_halo_m_tiles(int w, int h, int n) { return ((w + 15) / 16) * ((h + 15) / 16) * n * 2; }
 
@@ -470,36 +518,51 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
     if (make_act_map(&maps.in[i], shifted[i], 16, boxh, 1)) return -1;
   for (int i = nmaps; i < 4; ++i) maps.in[i] = maps.in[0];
   if (make_act_map(&maps.out, outv, 8, 16, 1)) return -1;
-  const int BN = (cout % 128 == 0) ? 128 : 64;
-  if (make_w_map(&maps.w, wp, (int64_t)taps_total * cout, cin, BN)) return -1;
+  const int spatial = (((int)outv.W + 15) / 16) * (((int)outv.H + 15) / 16) * (int)outv.N;
+  const int CL = (cluster_enabled() && spatial >= 2) ? 2 : 1;
+  // 256-column tiles (single-buffered accumulators) pay off once the K loop dwarfs the un-overlapped epilogue
+  const int BN = (cout % 256 == 0 && cin >= 128 && bn256_enabled()) ? 256 : ((cout % 128 == 0) ? 128 : 64);
+  if (make_w_map(&maps.w, wp, (int64_t)taps_total * cout, cin, BN / CL)) return -1;
   HaloParams p;
   p.tiles_x = ((int)outv.W + 15) / 16;
   p.tiles_y = ((int)outv.H + 15) / 16;
   p.W = (int)outv.W; p.H = (int)outv.H; p.N = (int)outv.N;
   p.cin = cin; p.cout = cout;
   p.n_tiles = cout / BN;
-  p.num_tiles = p.tiles_x * p.tiles_y * p.N * p.n_tiles;
+  p.num_tiles = ((spatial + CL - 1) / CL) * p.n_tiles;  // cluster tiles
   p.a_bytes = 16 * boxh * 128;
   const int b_bytes = BN * 128;
-  const int fixed = 1024 + 128 * BN * 2 + 4 * 2 * BN * 4 + 256;
-  p.nB = BN == 64 ? 6 : 4;
+  const int out_cols = BN > 128 ? 128 : BN;
+  const int fixed = 1024 + 128 * out_cols * 2 + 4 * 2 * out_cols * 4 + 256;
+  p.nB = BN == 64 ? 6 : (BN == 128 ? 4 : 3);
   int nA = (232448 - fixed - p.nB * b_bytes) / p.a_bytes;
   p.nA = nA > 4 ? 4 : nA;
   GSB_REQUIRE(p.nA >= 2, "conv_halo: shared memory budget");
   p.act = act; p.bias = bias; p.stats = stats;
   if (stats_rows) *stats_rows = conv_halo_m_tiles(p.W, p.H, p.N);
   const int smem = fixed + p.nA * p.a_bytes + p.nB * b_bytes;
-  const int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
-  cudaError_t e;
-  if (BN == 128) {
-    e = cudaFuncSetAttribute(conv_tc_halo_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    GSB_REQUIRE(e == cudaSuccess, "cudaFuncSetAttribute(smem=%d) failed: %s", smem, cudaGetErrorString(e));
-    conv_tc_halo_kernel<128><<<grid, 192, smem, st>>>(maps, plan, p);
-  } else {
-    e = cudaFuncSetAttribute(conv_tc_halo_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    GSB_REQUIRE(e == cudaSuccess, "cudaFuncSetAttribute(smem=%d) failed: %s", smem, cudaGetErrorString(e));
-    conv_tc_halo_kernel<64><<<grid, 192, smem, st>>>(maps, plan, p);
-  }
+  const int max_clusters = num_sms() / CL;
+  const int grid = (p.num_tiles < max_clusters ? p.num_tiles : max_clusters) * CL;
+  void (*kern)(TcMaps, HaloPlan, HaloParams) = nullptr;
+  if (CL == 2) kern = BN == 256 ? conv_tc_halo_kernel<256, 2> : (BN == 128 ? conv_tc_halo_kernel<128, 2> : conv_tc_halo_kernel<64, 2>);
+  else kern = BN == 256 ? conv_tc_halo_kernel<256, 1> : (BN == 128 ? conv_tc_halo_kernel<128, 1> : conv_tc_halo_kernel<64, 1>);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  GSB_REQUIRE(e == cudaSuccess, "cudaFuncSetAttribute(smem=%d) failed: %s", smem, cudaGetErrorString(e));
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(192);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CL;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  e = cudaLaunchKernelEx(&cfg, kern, maps, plan, p);
+  GSB_REQUIRE(e == cudaSuccess, "conv_tc_halo launch failed: %s", cudaGetErrorString(e));
   if (check_launch("conv_tc_halo launch")) return -1;
   return 1;
 }

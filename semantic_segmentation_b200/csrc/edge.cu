@@ -120,12 +120,187 @@ __global__ void __launch_bounds__(256) stem_wgrad_kernel(const float* __restrict
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Fast stem kernels (K x K, stride S known at compile time): every thread owns PX consecutive output pixels of
+// one 8-channel group, so the input row segment is loaded once per (ci, ky) and reused by all K horizontal taps,
+// the weight vectors are read once per tap for PX pixels, and the index arithmetic (32-bit) is paid once per PX
+// pixels.  The generic kernels above are issue-bound (~480 instructions per 16-byte store, ncu profiles/r01b).
+// The forward optionally accumulates the BatchNorm sum / sum-of-squares of the STORED (rounded) values.
+// ---------------------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ float stored_value(float v) { return v; }
+template <>
+__device__ __forceinline__ float stored_value<__nv_bfloat16>(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+
+template <typename T, int PX, int K, int S>
+__global__ void __launch_bounds__(256) stem_fwd_fast_kernel(const float* __restrict__ x, int N, int Cin, int H, int W,
+                                                           const float* __restrict__ w, const float* __restrict__ bias,
+                                                           T* __restrict__ y, int64_t yld, int OH, int OW, int Cout, int pad,
+                                                           int act, float* __restrict__ stats) {
+  extern __shared__ float sw[];  // [taps][Cout] | red[2][Cout]
+  const int taps = Cin * K * K;
+  float* red = sw + taps * Cout;
+  for (int i = threadIdx.x; i < taps * Cout; i += blockDim.x) {
+    int t = i / Cout, co = i % Cout;
+    sw[i] = w[(int64_t)co * taps + t];
+  }
+  if (stats != nullptr)
+    for (int i = threadIdx.x; i < 2 * Cout; i += blockDim.x) red[i] = 0.f;
+  __syncthreads();
+  constexpr int SPAN = (PX - 1) * S + K;
+  const unsigned G = (unsigned)Cout >> 3, XQ = (unsigned)(OW + PX - 1) / PX;
+  const unsigned total = (unsigned)N * (unsigned)OH * XQ * G;
+  const unsigned g = threadIdx.x % G;  // fixed per thread: the grid stride is a multiple of G
+  float s0[8], s1[8], b8[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    s0[j] = s1[j] = 0.f;
+    b8[j] = bias ? bias[g * 8 + j] : 0.f;
+  }
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const unsigned q = i / G;
+    const unsigned xq = q % XQ, row = q / XQ;
+    const int oy = (int)(row % (unsigned)OH), n = (int)(row / (unsigned)OH);
+    const int ox0 = (int)xq * PX;
+    float acc[PX][8];
+#pragma unroll
+    for (int px = 0; px < PX; ++px)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[px][j] = b8[j];
+    for (int ci = 0; ci < Cin; ++ci) {
+#pragma unroll
+      for (int ky = 0; ky < K; ++ky) {
+        const int iy = oy * S - pad + ky;
+        if (iy < 0 || iy >= H) continue;
+        const float* xr = x + (((int64_t)n * Cin + ci) * H + iy) * W;
+        float xv[SPAN];
+        const int ixb = ox0 * S - pad;
+#pragma unroll
+        for (int e = 0; e < SPAN; ++e) {
+          const int ix = ixb + e;
+          xv[e] = (ix >= 0 && ix < W) ? __ldg(xr + ix) : 0.f;
+        }
+        const float* wr = sw + ((ci * K + ky) * K) * Cout + g * 8;
+#pragma unroll
+        for (int kx = 0; kx < K; ++kx) {
+          const float4 w0 = *reinterpret_cast<const float4*>(wr + kx * Cout);
+          const float4 w1 = *reinterpret_cast<const float4*>(wr + kx * Cout + 4);
+#pragma unroll
+          for (int px = 0; px < PX; ++px) {
+            const float v = xv[px * S + kx];
+            acc[px][0] = fmaf(v, w0.x, acc[px][0]); acc[px][1] = fmaf(v, w0.y, acc[px][1]);
+            acc[px][2] = fmaf(v, w0.z, acc[px][2]); acc[px][3] = fmaf(v, w0.w, acc[px][3]);
+            acc[px][4] = fmaf(v, w1.x, acc[px][4]); acc[px][5] = fmaf(v, w1.y, acc[px][5]);
+            acc[px][6] = fmaf(v, w1.z, acc[px][6]); acc[px][7] = fmaf(v, w1.w, acc[px][7]);
+          }
+        }
+      }
+    }
+    const int64_t pbase = ((int64_t)n * OH + oy) * OW + ox0;
+#pragma unroll
+    for (int px = 0; px < PX; ++px) {
+      if (ox0 + px < OW) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[px][j] = act_fwd(acc[px][j], act);
+        Vec8<T>::store(y + (pbase + px) * yld + g * 8, acc[px]);
+        if (stats != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float r = stored_value<T>(acc[px][j]);
+            s0[j] += r;
+            s1[j] = fmaf(r, r, s1[j]);
+          }
+        }
+      }
+    }
+  }
+  if (stats != nullptr) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(&red[g * 8 + j], s0[j]);
+      atomicAdd(&red[Cout + g * 8 + j], s1[j]);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 2 * Cout; i += blockDim.x) stats[(int64_t)blockIdx.x * 2 * Cout + i] = red[i];
+  }
+}
+
+// dw[co][ci][ky][kx] += sum_pix dY[pix][co] * x[pix @ (ky,kx)]; blockIdx.y = ci; all K*K taps of 8 channels in registers
+template <typename T, int PX, int K, int S>
+__global__ void __launch_bounds__(256) stem_wgrad_fast_kernel(const float* __restrict__ x, int N, int Cin, int H, int W,
+                                                             const T* __restrict__ dy, int64_t dld, int OH, int OW, int Cout,
+                                                             int pad, float* __restrict__ dw) {
+  extern __shared__ float sacc[];  // [G][K*K][8]
+  constexpr int SPAN = (PX - 1) * S + K;
+  const int ci = blockIdx.y;
+  const unsigned G = (unsigned)Cout >> 3, XQ = (unsigned)(OW + PX - 1) / PX;
+  const unsigned lanes = blockDim.x / G;
+  const unsigned g = threadIdx.x % G, lane = threadIdx.x / G;
+  for (int i = threadIdx.x; i < (int)G * K * K * 8; i += blockDim.x) sacc[i] = 0.f;
+  __syncthreads();
+  float acc[K * K][8];
+#pragma unroll
+  for (int t = 0; t < K * K; ++t)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[t][j] = 0.f;
+  const unsigned items = (unsigned)N * (unsigned)OH * XQ;
+  for (unsigned q = blockIdx.x * lanes + lane; q < items; q += gridDim.x * lanes) {
+    const unsigned xq = q % XQ, row = q / XQ;
+    const int oy = (int)(row % (unsigned)OH), n = (int)(row / (unsigned)OH);
+    const int ox0 = (int)xq * PX;
+    const int64_t pbase = ((int64_t)n * OH + oy) * OW + ox0;
+    float d[PX][8];
+#pragma unroll
+    for (int px = 0; px < PX; ++px) {
+      if (ox0 + px < OW) {
+        Vec8<T>::load(dy + (pbase + px) * dld + g * 8, d[px]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) d[px][j] = 0.f;
+      }
+    }
+#pragma unroll
+    for (int ky = 0; ky < K; ++ky) {
+      const int iy = oy * S - pad + ky;
+      if (iy < 0 || iy >= H) continue;
+      const float* xr = x + (((int64_t)n * Cin + ci) * H + iy) * W;
+      float xv[SPAN];
+      const int ixb = ox0 * S - pad;
+#pragma unroll
+      for (int e = 0; e < SPAN; ++e) {
+        const int ix = ixb + e;
+        xv[e] = (ix >= 0 && ix < W) ? __ldg(xr + ix) : 0.f;
+      }
+#pragma unroll
+      for (int kx = 0; kx < K; ++kx)
+#pragma unroll
+        for (int px = 0; px < PX; ++px) {
+          const float v = xv[px * S + kx];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[ky * K + kx][j] = fmaf(v, d[px][j], acc[ky * K + kx][j]);
+        }
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < K * K; ++t)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) atomicAdd(&sacc[(g * K * K + t) * 8 + j], acc[t][j]);
+  __syncthreads();
+  const int taps = Cin * K * K;
+  for (int i = threadIdx.x; i < (int)G * K * K * 8; i += blockDim.x) {
+    const int j = i % 8, t = (i / 8) % (K * K), gg = i / (8 * K * K);
+    atomicAdd(dw + (int64_t)(gg * 8 + j) * taps + ci * K * K + t, sacc[i]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // head forward: 8 lanes per pixel, each lane a contiguous 1/8 of the K channels; 3 shuffles per class
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kHeadMaxC = 8;
 
-template <typename T>
-__global__ void __launch_bounds__(256) head_fwd_kernel(const T* __restrict__ x, int64_t xld, int64_t P, int64_t HW, int K, int C,
+// CT = compile-time bound on the class count (2 or 8): weights of the lane's 8 channels live in registers when
+// K == 64 (OutConv of the U-Net), pixel arithmetic is 32-bit.
+template <typename T, int CT>
+__global__ void __launch_bounds__(256) head_fwd_kernel(const T* __restrict__ x, int64_t xld, unsigned P, unsigned HW, int K, int C,
                                                       const float* __restrict__ w /*[C][K]*/, const float* __restrict__ bias,
                                                       float* __restrict__ out /*[N][C][HW]*/) {
   extern __shared__ float sw[];  // [C][K]
@@ -133,21 +308,31 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(const T* __restrict__ x, 
   __syncthreads();
   const int sub = threadIdx.x & 7;
   const int chunks = K >> 6;  // K multiple of 64: each lane handles 8 channels per 64-channel chunk
-  const int64_t stride_p = ((int64_t)gridDim.x * blockDim.x) >> 3;
+  float wr[CT][8];
+#pragma unroll
+  for (int c = 0; c < CT; ++c)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) wr[c][j] = c < C ? sw[c * K + sub * 8 + j] : 0.f;
+  const unsigned stride_p = (gridDim.x * blockDim.x) >> 3;
   // warp-uniform trip count (the shuffles below need all 32 lanes): iterate on the warp's first pixel
-  for (int64_t pw = ((int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31)) >> 3; pw < P; pw += stride_p) {
-    const int64_t p = pw + ((threadIdx.x & 31) >> 3);
+  for (unsigned pw = (blockIdx.x * blockDim.x + (threadIdx.x & ~31u)) >> 3; pw < P; pw += stride_p) {
+    const unsigned p = pw + ((threadIdx.x & 31) >> 3);
     const bool valid = p < P;
-    float acc[kHeadMaxC];
+    float acc[CT];
 #pragma unroll
-    for (int c = 0; c < kHeadMaxC; ++c) acc[c] = 0.f;
+    for (int c = 0; c < CT; ++c) acc[c] = 0.f;
     if (valid) {
-      for (int ch = 0; ch < chunks; ++ch) {
-        float v[8];
-        const int k0 = ch * 64 + sub * 8;
-        Vec8<T>::load(x + p * xld + k0, v);
+      float v[8];
+      Vec8<T>::load(x + (int64_t)p * xld + sub * 8, v);
 #pragma unroll
-        for (int c = 0; c < kHeadMaxC; ++c)
+      for (int c = 0; c < CT; ++c)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[c] = fmaf(v[j], wr[c][j], acc[c]);
+      for (int ch = 1; ch < chunks; ++ch) {
+        const int k0 = ch * 64 + sub * 8;
+        Vec8<T>::load(x + (int64_t)p * xld + k0, v);
+#pragma unroll
+        for (int c = 0; c < CT; ++c)
           if (c < C) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) acc[c] = fmaf(v[j], sw[c * K + k0 + j], acc[c]);
@@ -155,24 +340,23 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(const T* __restrict__ x, 
       }
     }
 #pragma unroll
-    for (int c = 0; c < kHeadMaxC; ++c)
-      if (c < C) {
-        acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 1);
-        acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 2);
-        acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 4);
-      }
+    for (int c = 0; c < CT; ++c) {
+      acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 1);
+      acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 2);
+      acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 4);
+    }
     if (valid && sub == 0) {
-      const int64_t n = p / HW, r = p - n * HW;
+      const unsigned n = p / HW, r = p - n * HW;
 #pragma unroll
-      for (int c = 0; c < kHeadMaxC; ++c)
-        if (c < C) out[(n * C + c) * HW + r] = acc[c] + (bias ? bias[c] : 0.f);
+      for (int c = 0; c < CT; ++c)
+        if (c < C) out[((int64_t)n * C + c) * HW + r] = acc[c] + (bias ? bias[c] : 0.f);
     }
   }
 }
 
 // head backward: dx[p][k] = sum_c d[p][c] w[c][k];  dw[c][k] += sum_p d[p][c] x[p][k];  db[c] += sum_p d[p][c]
-template <typename T>
-__global__ void __launch_bounds__(256) head_bwd_kernel(const T* __restrict__ x, int64_t xld, int64_t P, int64_t HW, int K, int C,
+template <typename T, int CT>
+__global__ void __launch_bounds__(256) head_bwd_kernel(const T* __restrict__ x, int64_t xld, unsigned P, unsigned HW, int K, int C,
                                                       const float* __restrict__ w, const float* __restrict__ dout,
                                                       T* __restrict__ dx, int64_t dxld, float* __restrict__ dw,
                                                       float* __restrict__ db) {
@@ -186,40 +370,42 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(const T* __restrict__ x, 
   }
   if (threadIdx.x < C) sdb[threadIdx.x] = 0.f;
   __syncthreads();
-  const int G = K >> 3;                 // 8-channel groups
-  const int lanes = blockDim.x / G;
-  const int g = threadIdx.x % G, lane = threadIdx.x / G;
-  float aw[kHeadMaxC][8], ab[kHeadMaxC];
+  const unsigned G = (unsigned)K >> 3;  // 8-channel groups
+  const unsigned lanes = blockDim.x / G;
+  const unsigned g = threadIdx.x % G, lane = threadIdx.x / G;
+  float aw[CT][8], ab[CT], wr[CT][8];
 #pragma unroll
-  for (int c = 0; c < kHeadMaxC; ++c) {
+  for (int c = 0; c < CT; ++c) {
     ab[c] = 0.f;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) aw[c][j] = 0.f;
+    for (int j = 0; j < 8; ++j) {
+      aw[c][j] = 0.f;
+      wr[c][j] = c < C ? sw[c * K + g * 8 + j] : 0.f;
+    }
   }
-  for (int64_t p = (int64_t)blockIdx.x * lanes + lane; p < P; p += (int64_t)gridDim.x * lanes) {
-    const int64_t n = p / HW, r = p - n * HW;
-    float d[kHeadMaxC];
+  for (unsigned p = blockIdx.x * lanes + lane; p < P; p += gridDim.x * lanes) {
+    const unsigned n = p / HW, r = p - n * HW;
+    float d[CT];
 #pragma unroll
-    for (int c = 0; c < kHeadMaxC; ++c) d[c] = c < C ? __ldg(dout + (n * C + c) * HW + r) : 0.f;
+    for (int c = 0; c < CT; ++c) d[c] = c < C ? __ldg(dout + ((int64_t)n * C + c) * HW + r) : 0.f;
     float v[8], o[8];
-    if (dw != nullptr) Vec8<T>::load(x + p * xld + g * 8, v);
+    if (dw != nullptr) Vec8<T>::load(x + (int64_t)p * xld + g * 8, v);
 #pragma unroll
     for (int j = 0; j < 8; ++j) o[j] = 0.f;
 #pragma unroll
-    for (int c = 0; c < kHeadMaxC; ++c)
-      if (c < C) {
+    for (int c = 0; c < CT; ++c) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          o[j] = fmaf(d[c], sw[c * K + g * 8 + j], o[j]);
-          if (dw != nullptr) aw[c][j] = fmaf(d[c], v[j], aw[c][j]);
-        }
-        ab[c] += d[c];
+      for (int j = 0; j < 8; ++j) {
+        o[j] = fmaf(d[c], wr[c][j], o[j]);
+        if (dw != nullptr) aw[c][j] = fmaf(d[c], v[j], aw[c][j]);
       }
-    if (dx != nullptr) Vec8<T>::store(dx + p * dxld + g * 8, o);
+      ab[c] += d[c];
+    }
+    if (dx != nullptr) Vec8<T>::store(dx + (int64_t)p * dxld + g * 8, o);
   }
   if (dw != nullptr) {
 #pragma unroll
-    for (int c = 0; c < kHeadMaxC; ++c)
+    for (int c = 0; c < CT; ++c)
       if (c < C) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) atomicAdd(&sdw[c * K + g * 8 + j], aw[c][j]);
@@ -227,7 +413,7 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(const T* __restrict__ x, 
   }
   if (db != nullptr && g == 0) {
 #pragma unroll
-    for (int c = 0; c < kHeadMaxC; ++c)
+    for (int c = 0; c < CT; ++c)
       if (c < C) atomicAdd(&sdb[c], ab[c]);
   }
   __syncthreads();
@@ -261,13 +447,33 @@ static int stem_check(const float* x, const gsb_view* y, int cin, int k) {
   return 0;
 }
 
+extern "C" int gsb_stem_stats_rows(void) { return num_sms() * 8; }
+
 extern "C" int gsb_stem_conv_fwd(const float* x, int n, int cin, int h, int w, const float* weight, const float* bias,
-                                 const gsb_view* y, int k, int stride, int pad, int act, gsb_stream s) {
+                                 const gsb_view* y, int k, int stride, int pad, int act, float* stats_partial, int* stats_rows,
+                                 gsb_stream s) {
   if (stem_check(x, y, cin, k)) return -1;
   GSB_REQUIRE(weight && y->n == n && y->h == (h + 2 * pad - k) / stride + 1 && y->w == (w + 2 * pad - k) / stride + 1,
               "stem_conv_fwd: shape mismatch");
   const int cout = y->c;
   int64_t total = num_pixels(y) * (cout / 8);
+  if (stats_rows) *stats_rows = 0;
+  const bool k3 = (k == 3 && stride == 1), k4 = (k == 4 && stride == 2);
+  if ((k3 || k4) && total < (int64_t)1 << 31) {
+    constexpr int PX = 4;
+    const int64_t items = (int64_t)y->n * y->h * ((y->w + PX - 1) / PX) * (cout / 8);
+    int grid = grid_cap((items + 255) / 256, 8);
+    size_t smem = ((size_t)cin * k * k * cout + 2 * cout) * sizeof(float);
+    if (k3) {
+      EDGE_DISPATCH_T(y->dtype, stem_fwd_fast_kernel<T, PX, 3, 1><<<grid, 256, smem, to_stream(s)>>>(
+                                    x, n, cin, h, w, weight, bias, (T*)y->ptr, y->sw, y->h, y->w, cout, pad, act, stats_partial));
+    } else {
+      EDGE_DISPATCH_T(y->dtype, stem_fwd_fast_kernel<T, PX, 4, 2><<<grid, 256, smem, to_stream(s)>>>(
+                                    x, n, cin, h, w, weight, bias, (T*)y->ptr, y->sw, y->h, y->w, cout, pad, act, stats_partial));
+    }
+    if (stats_partial && stats_rows) *stats_rows = grid;
+    return check_launch("stem_conv_fwd");
+  }
   size_t smem = (size_t)cin * k * k * cout * sizeof(float);
   int grid = grid_cap((total + 255) / 256, 16);
   EDGE_DISPATCH_T(y->dtype, stem_fwd_kernel<T><<<grid, 256, smem, to_stream(s)>>>(x, n, cin, h, w, weight, bias, (T*)y->ptr, y->sw,
@@ -283,6 +489,15 @@ extern "C" int gsb_stem_conv_wgrad(const float* x, int n, int cin, int h, int w,
   constexpr int TP = 9;
   cudaMemsetAsync(dweight, 0, (size_t)cout * taps * sizeof(float), to_stream(s));
   const int G = cout / 8, lanes = 256 / G;
+  if (k == 3 && stride == 1 && num_pixels(dy) < (int64_t)1 << 31) {
+    constexpr int PX = 4;
+    const int64_t items = (int64_t)dy->n * dy->h * ((dy->w + PX - 1) / PX);
+    int gx = grid_cap((items + lanes - 1) / lanes, 4);
+    size_t smem = (size_t)G * 9 * 8 * sizeof(float);
+    EDGE_DISPATCH_T(dy->dtype, stem_wgrad_fast_kernel<T, PX, 3, 1><<<dim3(gx, cin), 256, smem, to_stream(s)>>>(
+                                   x, n, cin, h, w, (const T*)dy->ptr, dy->sw, dy->h, dy->w, cout, pad, dweight));
+    return check_launch("stem_conv_wgrad");
+  }
   int grid = grid_cap((num_pixels(dy) + lanes - 1) / lanes, 4);
   size_t smem = (size_t)G * TP * 8 * sizeof(float);
   int launches = 0;
@@ -306,8 +521,14 @@ extern "C" int gsb_head_conv_fwd(const gsb_view* x, const float* weight, const f
   const int64_t P = num_pixels(x), HW = (int64_t)x->h * x->w;
   int grid = grid_cap((P * 8 + 255) / 256, 16);
   size_t smem = (size_t)c * x->c * sizeof(float);
-  EDGE_DISPATCH_T(x->dtype, head_fwd_kernel<T><<<grid, 256, smem, to_stream(s)>>>((const T*)x->ptr, x->sw, P, HW, x->c, c, weight,
-                                                                                   bias, logits));
+  GSB_REQUIRE(P < ((int64_t)1 << 28), "head_conv_fwd: too many pixels");
+  if (c <= 2) {
+    EDGE_DISPATCH_T(x->dtype, head_fwd_kernel<T, 2><<<grid, 256, smem, to_stream(s)>>>((const T*)x->ptr, x->sw, (unsigned)P, (unsigned)HW,
+                                                                                        x->c, c, weight, bias, logits));
+  } else {
+    EDGE_DISPATCH_T(x->dtype, head_fwd_kernel<T, 8><<<grid, 256, smem, to_stream(s)>>>((const T*)x->ptr, x->sw, (unsigned)P, (unsigned)HW,
+                                                                                        x->c, c, weight, bias, logits));
+  }
   return check_launch("head_conv_fwd");
 }
 
@@ -323,8 +544,15 @@ extern "C" int gsb_head_conv_bwd(const gsb_view* x, const float* weight, int c, 
   if (dbias) cudaMemsetAsync(dbias, 0, (size_t)c * sizeof(float), to_stream(s));
   int grid = grid_cap((P + lanes - 1) / lanes, 4);
   size_t smem = (size_t)(2 * c * K + c) * sizeof(float);
-  EDGE_DISPATCH_T(x->dtype, head_bwd_kernel<T><<<grid, 256, smem, to_stream(s)>>>(
-                                (const T*)x->ptr, x->sw, P, HW, K, c, weight, dlogits, (dx && dx->ptr) ? (T*)dx->ptr : nullptr,
-                                dx ? dx->sw : 0, dweight, dbias));
+  GSB_REQUIRE(P < ((int64_t)1 << 31), "head_conv_bwd: too many pixels");
+  if (c <= 2) {
+    EDGE_DISPATCH_T(x->dtype, head_bwd_kernel<T, 2><<<grid, 256, smem, to_stream(s)>>>(
+                                  (const T*)x->ptr, x->sw, (unsigned)P, (unsigned)HW, K, c, weight, dlogits,
+                                  (dx && dx->ptr) ? (T*)dx->ptr : nullptr, dx ? dx->sw : 0, dweight, dbias));
+  } else {
+    EDGE_DISPATCH_T(x->dtype, head_bwd_kernel<T, 8><<<grid, 256, smem, to_stream(s)>>>(
+                                  (const T*)x->ptr, x->sw, (unsigned)P, (unsigned)HW, K, c, weight, dlogits,
+                                  (dx && dx->ptr) ? (T*)dx->ptr : nullptr, dx ? dx->sw : 0, dweight, dbias));
+  }
   return check_launch("head_conv_bwd");
 }

@@ -143,8 +143,8 @@ class ConvBNAct:
         y = _nhwc_empty(n, oh, ow, s.cout, device)
         stem = _is_stem(s, x_view, x_keep)
         if stem:   # fp32 NCHW network input with 1..4 channels: bandwidth kernel, torch-layout fp32 weights
-            ops.stem_conv_fwd(x_keep, weight.detach().contiguous(), bias, y, s.k, s.stride, s.pad)
-            stats, rows = None, 0
+            stats, rows = ops.stem_conv_fwd(x_keep, weight.detach().contiguous(), bias, y, s.k, s.stride, s.pad,
+                                            want_stats=self.has_bn and training and _CONFIG["fused_stats"])
         else:
             wp = s.pack_fwd(weight)
             want_stats = (self.has_bn and training and _CONFIG["fused_stats"]

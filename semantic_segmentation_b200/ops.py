@@ -118,10 +118,19 @@ def conv_wgrad_into(inp: GsbView, dout: GsbView, dwp: torch.Tensor, mode: int, k
 
 
 def stem_conv_fwd(x: torch.Tensor, weight: torch.Tensor, bias, y: torch.Tensor, k: int, stride: int, pad: int,
-                  act: int = ACT_NONE) -> None:
+                  act: int = ACT_NONE, want_stats: bool = False):
+    """Returns (stats_partial, rows) when want_stats and the fused-statistics kernel ran, else (None, 0)."""
     n, cin, h, w = x.shape
-    check(load().gsb_stem_conv_fwd(ptr(x), n, cin, h, w, ptr(weight), ptr(bias), _ref(view_nhwc(y)), k, stride, pad, act,
-                                   _s(x)), "stem_conv_fwd")
+    lib = load()
+    stats = None
+    rows = C.c_int(0)
+    if want_stats:
+        stats = torch.empty((lib.gsb_stem_stats_rows(), 2, y.shape[3]), device=x.device, dtype=torch.float32)
+    check(lib.gsb_stem_conv_fwd(ptr(x), n, cin, h, w, ptr(weight), ptr(bias), _ref(view_nhwc(y)), k, stride, pad, act,
+                                ptr(stats), C.byref(rows), _s(x)), "stem_conv_fwd")
+    if stats is not None and rows.value > 0:
+        return stats, rows.value
+    return None, 0
 
 
 def stem_conv_wgrad(x: torch.Tensor, dy: torch.Tensor, k: int, stride: int, pad: int) -> torch.Tensor:
