@@ -77,6 +77,7 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
   uint8_t* s_out = sB + p.nB * B_BYTES;
   float* s_red = reinterpret_cast<float*>(s_out + OUT_BYTES);
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_out + OUT_BYTES + RED_BYTES);
+  float* s_acc = reinterpret_cast<float*>(bars + 32);  // [2][cout] running BN sums of this CTA (only when p.stats)
   uint64_t* fullA = bars;
   uint64_t* emptyA = bars + 4;
   uint64_t* fullB = bars + 8;
@@ -192,6 +193,10 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
     const float slope = p.act == GSB_ACT_RELU ? 0.f : (p.act == GSB_ACT_LRELU ? 0.2f : 1.f);
     const bool is_tanh = p.act == GSB_ACT_TANH;
     uint32_t acc = 0, acc_phase = 0;
+    if (p.stats != nullptr) {
+      for (int j = et; j < 2 * p.cout; j += 128) s_acc[j] = 0.f;
+      named_bar_sync(2, 128);
+    }
     for (int tile = cluster_id; tile < num_ctiles; tile += nclusters) {
       const int nt = tile % p.n_tiles, st = (tile / p.n_tiles) * CL + rank;
       const bool ghost = st >= spatial;
@@ -270,17 +275,18 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
             rd[OUT_COLS + s * 64 + 2 * w + 1] = s1b;
           }
           named_bar_sync(2, 128);
-          const int64_t mrow = (int64_t)st * 2 + m;
-          for (int j = et; j < 2 * OUT_COLS; j += 128) {
+          for (int j = et; j < 2 * OUT_COLS; j += 128) {  // (which, channel) -> always the same thread: no race
             float a = s_red[j] + s_red[2 * OUT_COLS + j] + s_red[4 * OUT_COLS + j] + s_red[6 * OUT_COLS + j];
             const int which = j / OUT_COLS, c = j % OUT_COLS;
-            p.stats[(mrow * 2 + which) * p.cout + nt * BN + h * OUT_COLS + c] = a;
+            s_acc[which * p.cout + nt * BN + h * OUT_COLS + c] += a;
           }
           named_bar_sync(2, 128);
         }
       }
       if (++acc == NBUF) { acc = 0; acc_phase ^= 1u; }
     }
+    if (p.stats != nullptr)  // one statistics row per CTA (CTAs without tiles write zeros)
+      for (int j = et; j < 2 * p.cout; j += 128) p.stats[(int64_t)blockIdx.x * 2 * p.cout + j] = s_acc[j];
     if (et == 0) tma_store_wait_read();
   }
   tc_fence_before();
@@ -501,7 +507,10 @@ static bool bn256_enabled() {
 }
 
 bool conv_halo_applicable(const SubView& outv) { return halo_enabled() && outv.W >= 16 && outv.H >= 16; }
-int conv_halo_m_tiles(int w, int h, int n) { return ((w + 15) / 16) * ((h + 15) / 16) * n * 2; }
+int conv_halo_m_tiles(int w, int h, int n) {  // upper bound on the statistics rows (one per CTA)
+  (void)w; (void)h; (void)n;
+  return num_sms();
+}
 
 // Returns 1 when the launch was issued, 0 when the tap structure does not fit (caller falls back), -1 on error.
 int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, const TcTaps& taps, const void* wp, int taps_total,
@@ -533,16 +542,16 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
   p.a_bytes = 16 * boxh * 128;
   const int b_bytes = BN * 128;
   const int out_cols = BN > 128 ? 128 : BN;
-  const int fixed = 1024 + 128 * out_cols * 2 + 4 * 2 * out_cols * 4 + 256;
+  const int fixed = 1024 + 128 * out_cols * 2 + 4 * 2 * out_cols * 4 + 256 + (stats ? 2 * cout * 4 : 0);
   p.nB = BN == 64 ? 6 : (BN == 128 ? 4 : 3);
   int nA = (232448 - fixed - p.nB * b_bytes) / p.a_bytes;
   p.nA = nA > 4 ? 4 : nA;
   GSB_REQUIRE(p.nA >= 2, "conv_halo: shared memory budget");
   p.act = act; p.bias = bias; p.stats = stats;
-  if (stats_rows) *stats_rows = conv_halo_m_tiles(p.W, p.H, p.N);
   const int smem = fixed + p.nA * p.a_bytes + p.nB * b_bytes;
   const int max_clusters = num_sms() / CL;
   const int grid = (p.num_tiles < max_clusters ? p.num_tiles : max_clusters) * CL;
+  if (stats_rows) *stats_rows = grid;  // one row of running sums per CTA
   void (*kern)(TcMaps, HaloPlan, HaloParams) = nullptr;
   if (CL == 2) kern = BN == 256 ? conv_tc_halo_kernel<256, 2> : (BN == 128 ? conv_tc_halo_kernel<128, 2> : conv_tc_halo_kernel<64, 2>);
   else kern = BN == 256 ? conv_tc_halo_kernel<256, 1> : (BN == 128 ? conv_tc_halo_kernel<128, 1> : conv_tc_halo_kernel<64, 1>);

@@ -136,14 +136,24 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
   }
 }
 
-__global__ void reduce_partials_kernel(const float* __restrict__ partial, int rows, int n, double* __restrict__ sums) {
-  // one warp per output column j in [0, n): fixed summation order -> deterministic
-  int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= n) return;
+// partial[rows][n] fp32 -> sums[n] fp64.  Block = 32 columns x 8 row lanes: coalesced 128-byte row segments,
+// fp64 accumulation, fixed summation order (deterministic).
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ partial, int rows, int n,
+                                                             double* __restrict__ sums) {
+  __shared__ double red[8][33];
+  const int c = threadIdx.x & 31, l = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + c;
   double acc = 0.0;
-  for (int r = lane; r < rows; r += 32) acc += (double)partial[(int64_t)r * n + warp];
-  acc = warp_sum_d(acc);
-  if (lane == 0) sums[warp] = acc;
+  if (col < n)
+    for (int r = l; r < rows; r += 8) acc += (double)partial[(int64_t)r * n + col];
+  red[l][c] = acc;
+  __syncthreads();
+  if (l == 0 && col < n) {
+    double t = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += red[i][c];
+    sums[col] = t;
+  }
 }
 
 __global__ void bn_finalize_kernel(const double* __restrict__ sums, double count, const float* __restrict__ gamma,
@@ -354,13 +364,13 @@ extern "C" int gsb_bn_reduce(const gsb_view* x, double* sums, void* workspace, s
     bn_reduce_kernel<float, 0, false><<<grid, kThreads, smem, to_stream(s)>>>(pv(x), nul, nul, P, C, nullptr, nullptr, nullptr,
                                                                              nullptr, 0, 0, 0, nullptr, partial);
   int n = 2 * C;
-  reduce_partials_kernel<<<(n * 32 + 255) / 256, 256, 0, to_stream(s)>>>(partial, grid, n, sums);
+  reduce_partials_kernel<<<(n + 31) / 32, 256, 0, to_stream(s)>>>(partial, grid, n, sums);
   return check_launch("bn_reduce", 2);
 }
 
 extern "C" int gsb_bn_reduce_partials(const float* partial, int rows, int c, double* sums, gsb_stream s) {
   int n = 2 * c;
-  reduce_partials_kernel<<<(n * 32 + 255) / 256, 256, 0, to_stream(s)>>>(partial, rows, n, sums);
+  reduce_partials_kernel<<<(n + 31) / 32, 256, 0, to_stream(s)>>>(partial, rows, n, sums);
   return check_launch("bn_reduce_partials");
 }
 
@@ -437,7 +447,7 @@ extern "C" int gsb_bn_bwd_reduce(const gsb_view* x, const gsb_view* dA1, const g
                                                                              invstd, act1, act2, drop_seed, drop_mask, partial);
   }
   int n = 2 * C;
-  reduce_partials_kernel<<<(n * 32 + 255) / 256, 256, 0, to_stream(s)>>>(partial, grid, n, sums);
+  reduce_partials_kernel<<<(n + 31) / 32, 256, 0, to_stream(s)>>>(partial, grid, n, sums);
   return check_launch("bn_bwd_reduce", 2);
 }
 
