@@ -36,7 +36,9 @@ struct HaloParams {
   int tiles_x, tiles_y;  // 16x16 tiles per image
   int W, H, N;           // extents of the tiled (output) space
   int cin, cout, n_tiles, num_tiles;
-  int nA, nB, a_bytes;   // ring depths and activation slot size (16 x boxh x 128 B)
+  int nA, nB, a_bytes;   // ring depths and activation box bytes (pw x boxh x 128 B)
+  int a_stride;          // activation slot stride (a_bytes rounded up to 1024)
+  int pw, full;          // box width in pixels; full = 1: ONE box per 64-channel block serves every (dx, dy) tap
   int act;
   const float* bias;
   float* stats;          // [2*spatial_tiles][2][cout] or null
@@ -53,6 +55,22 @@ __device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t mask) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
                ::"r"(smem_u32(bar)), "h"(mask) : "memory");
 }
+__device__ __forceinline__ void sts_128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ void sts_f32(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
@@ -61,19 +79,19 @@ __device__ __forceinline__ void cluster_sync_all() {
 // CL = cluster size: the CL CTAs of a cluster own CL different 16x16 tiles with the SAME weight tile, each
 // loads 1/CL of every weight slot and multicasts it to all of them (L2 weight reads / CL).
 template <int BN, int CL>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(320, 1)
 conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ HaloPlan plan, const HaloParams p) {
   constexpr int B_BYTES = BN * 128;
   constexpr int OUT_COLS = BN > 128 ? 128 : BN;
   constexpr int OUT_BYTES = 128 * OUT_COLS * 2;
-  constexpr int RED_BYTES = 4 * 2 * OUT_COLS * 4;
+  constexpr int RED_BYTES = 8 * 2 * OUT_COLS * 4;
   constexpr int NBUF = BN > 128 ? 1 : 2;
   constexpr int TMEM_COLS = NBUF * 2 * BN;
   constexpr uint16_t kMask = (uint16_t)((1u << CL) - 1u);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem;
-  uint8_t* sB = sA + p.nA * p.a_bytes;
+  uint8_t* sB = sA + p.nA * p.a_stride;
   uint8_t* s_out = sB + p.nB * B_BYTES;
   float* s_red = reinterpret_cast<float*>(s_out + OUT_BYTES);
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_out + OUT_BYTES + RED_BYTES);
@@ -98,7 +116,7 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], 128);
+      mbar_init(&tempty[i], 256);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     prefetch_tmap(&maps.w);
@@ -129,10 +147,12 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
         const int x0 = (r % p.tiles_x) * 16, y0 = (r / p.tiles_x) * 16;
         for (int kb = 0; kb < kblocks; ++kb) {
           for (int g = 0; g < plan.ngroups; ++g) {
-            mbar_wait(&emptyA[sa], pa ^ 1u);
-            mbar_expect_tx(&fullA[sa], (uint32_t)p.a_bytes);
-            tma_load_4d(&maps.in[plan.map[g]], &fullA[sa], sA + sa * p.a_bytes, kb * 64, x0 + plan.dx[g], y0 + plan.dy0[g], n);
-            if (++sa == p.nA) { sa = 0; pa ^= 1u; }
+            if (!p.full || g == 0) {
+              mbar_wait(&emptyA[sa], pa ^ 1u);
+              mbar_expect_tx(&fullA[sa], (uint32_t)p.a_bytes);
+              tma_load_4d(&maps.in[plan.map[g]], &fullA[sa], sA + sa * p.a_stride, kb * 64, x0 + plan.dx[g], y0 + plan.dy0[g], n);
+              if (++sa == p.nA) { sa = 0; pa ^= 1u; }
+            }
             const int nd = plan.ndy[g];
             for (int j = 0; j < nd; ++j) {
               mbar_wait(&emptyB[sb], pb ^ 1u);
@@ -160,9 +180,14 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
         uint32_t accum = 0;
         for (int kb = 0; kb < kblocks; ++kb) {
           for (int g = 0; g < plan.ngroups; ++g) {
-            mbar_wait(&fullA[sa], pa);
-            tc_fence_after();
-            const uint32_t a_base = smem_u32(sA + sa * p.a_bytes);
+            if (!p.full || g == 0) {
+              mbar_wait(&fullA[sa], pa);
+              tc_fence_after();
+            }
+            // full mode: horizontal taps are pixel (= 128 B row) shifts inside the one box; the swizzle XOR acts on
+            // absolute shared-memory address bits, so a row-shifted start stays consistent with what TMA wrote
+            const uint32_t a_base = smem_u32(sA + sa * p.a_stride) + (p.full ? (uint32_t)(plan.dx[g] - plan.dx[0]) * 128u : 0u);
+            const uint32_t row_bytes = (uint32_t)p.pw * 128u;
             const int nd = plan.ndy[g];
             for (int j = 0; j < nd; ++j) {
               mbar_wait(&fullB[sb], pb);
@@ -170,7 +195,7 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
               const uint64_t bdesc = umma_desc(smem_u32(sB + sb * B_BYTES), 16, 1024);
 #pragma unroll
               for (int m = 0; m < 2; ++m) {
-                const uint64_t adesc = umma_desc(a_base + m * 1024 + j * 2048, 16, 2048);
+                const uint64_t adesc = umma_desc(a_base + m * 1024 + j * row_bytes, 16, row_bytes);
 #pragma unroll
                 for (int k = 0; k < 4; ++k) umma_bf16(d0 + m * BN, adesc + 2 * k, bdesc + 2 * k, idesc, accum | (uint32_t)k);
               }
@@ -178,30 +203,40 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
               if (CL > 1) umma_commit_mc(&emptyB[sb], kMask); else umma_commit(&emptyB[sb]);
               if (++sb == p.nB) { sb = 0; pb ^= 1u; }
             }
-            umma_commit(&emptyA[sa]);
-            if (++sa == p.nA) { sa = 0; pa ^= 1u; }
+            if (!p.full || g == plan.ngroups - 1) {
+              umma_commit(&emptyA[sa]);
+              if (++sa == p.nA) { sa = 0; pa ^= 1u; }
+            }
           }
         }
         umma_commit(&tfull[acc]);
         if (++acc == NBUF) { acc = 0; acc_phase ^= 1u; }
       }
     }
-  } else {  // ---------------- epilogue warps 2..5 ----------------
-    const int q = warp & 3;         // TMEM lane quarter this warp may access
-    const int row = q * 32 + lane;  // accumulator row: pixel (row % 8, row / 8) of the 8x16 M-tile
-    const int et = threadIdx.x - 64;
+  } else {  // ---------------- epilogue warps 2..9 ----------------
+    // Eight warps: two per TMEM lane quarter, each taking half of the columns of a staging pass.  With four warps
+    // (one per scheduler, no ILP) the epilogue ran at IPC ~0.24 and the MMA warp waited on `tempty` for the
+    // small-K layers (ncu profiles/r01e: 10.1 k cycles per tile against 2.3 k cycles of MMA at K = 576).
+    const int q = warp & 3;              // TMEM lane quarter this warp may access
+    const int half = (warp - 2) >> 2;    // column half of the staging pass
+    const int row = q * 32 + lane;       // accumulator row: pixel (row % 8, row / 8) of the 8x16 M-tile
+    const int et = threadIdx.x - 64;     // 0..255
+    constexpr int CPW = OUT_COLS / 64;   // 32-column chunks per warp and staging pass
     const float slope = p.act == GSB_ACT_RELU ? 0.f : (p.act == GSB_ACT_LRELU ? 0.2f : 1.f);
     const bool is_tanh = p.act == GSB_ACT_TANH;
+    const bool simple = p.bias == nullptr && p.act == GSB_ACT_NONE;
+    const uint32_t so = smem_u32(s_out), sr = smem_u32(s_red), sacc = smem_u32(s_acc);
     uint32_t acc = 0, acc_phase = 0;
     if (p.stats != nullptr) {
-      for (int j = et; j < 2 * p.cout; j += 128) s_acc[j] = 0.f;
-      named_bar_sync(2, 128);
+      for (int j = et; j < 2 * p.cout; j += 256) sts_f32(sacc + 4 * j, 0.f);
+      named_bar_sync(2, 256);
     }
     for (int tile = cluster_id; tile < num_ctiles; tile += nclusters) {
       const int nt = tile % p.n_tiles, st = (tile / p.n_tiles) * CL + rank;
       const bool ghost = st >= spatial;
       const int n = ghost ? p.N : st / per_img, r = ghost ? 0 : st % per_img;
       const int x0 = (r % p.tiles_x) * 16, y0 = (r / p.tiles_x) * 16;
+      const bool plain = simple && !ghost && (x0 + 16 <= p.W) && (y0 + 16 <= p.H);  // no bias / act / masking
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
 #pragma unroll 1
@@ -209,36 +244,50 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
         const int m = mh / (BN / OUT_COLS), h = mh % (BN / OUT_COLS);  // M-tile, 128-column half
         const bool valid = !ghost && (x0 + m * 8 + (row & 7) < p.W) && (y0 + (row >> 3) < p.H);
         if (et == 0) tma_store_wait_read();  // the previous store has finished reading s_out
-        named_bar_sync(1, 128);
-#pragma unroll 1
-        for (int ch = 0; ch < OUT_COLS / 32; ++ch) {
+        named_bar_sync(1, 256);
+#pragma unroll
+        for (int cc = 0; cc < CPW; ++cc) {
+          const int ch = half * CPW + cc;
           uint32_t v[32];
           tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * (2 * BN) + m * BN + h * OUT_COLS + ch * 32, v);
-          const int cbase = nt * BN + h * OUT_COLS + ch * 32;
-          uint8_t* slab = s_out + (ch >> 1) * (128 * 128) + row * 128;
+          const uint32_t slab = so + (ch >> 1) * (128 * 128) + row * 128;
+          if (plain) {
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            uint32_t pk[4];
+            for (int g = 0; g < 4; ++g) {
+              uint32_t pk[4];
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              float f0 = __uint_as_float(v[g * 8 + 2 * e]), f1 = __uint_as_float(v[g * 8 + 2 * e + 1]);
-              if (p.bias != nullptr) {
-                f0 += __ldg(p.bias + cbase + g * 8 + 2 * e);
-                f1 += __ldg(p.bias + cbase + g * 8 + 2 * e + 1);
+              for (int e = 0; e < 4; ++e) {
+                __nv_bfloat162 hh = __floats2bfloat162_rn(__uint_as_float(v[g * 8 + 2 * e]), __uint_as_float(v[g * 8 + 2 * e + 1]));
+                pk[e] = *reinterpret_cast<uint32_t*>(&hh);
               }
-              if (is_tanh) {
-                f0 = tanhf(f0);
-                f1 = tanhf(f1);
-              } else {
-                f0 = f0 > 0.f ? f0 : f0 * slope;
-                f1 = f1 > 0.f ? f1 : f1 * slope;
-              }
-              if (!valid) f0 = f1 = 0.f;
-              __nv_bfloat162 hh = __floats2bfloat162_rn(f0, f1);
-              pk[e] = *reinterpret_cast<uint32_t*>(&hh);
+              const int c16 = (ch & 1) * 4 + g;  // 16-byte chunk inside the 128-byte row
+              sts_128(slab + ((c16 ^ (row & 7)) << 4), pk[0], pk[1], pk[2], pk[3]);
             }
-            const int c16 = (ch & 1) * 4 + g;  // 16-byte chunk inside the 128-byte row
-            *reinterpret_cast<uint4*>(slab + ((c16 ^ (row & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+          } else {
+            const int cbase = nt * BN + h * OUT_COLS + ch * 32;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              uint32_t pk[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                float f0 = __uint_as_float(v[g * 8 + 2 * e]), f1 = __uint_as_float(v[g * 8 + 2 * e + 1]);
+                if (p.bias != nullptr) {
+                  f0 += __ldg(p.bias + cbase + g * 8 + 2 * e);
+                  f1 += __ldg(p.bias + cbase + g * 8 + 2 * e + 1);
+                }
+                if (is_tanh) {
+                  f0 = tanhf(f0);
+                  f1 = tanhf(f1);
+                } else {
+                  f0 = f0 > 0.f ? f0 : f0 * slope;
+                  f1 = f1 > 0.f ? f1 : f1 * slope;
+                }
+                __nv_bfloat162 hh = __floats2bfloat162_rn(f0, f1);
+                pk[e] = valid ? *reinterpret_cast<uint32_t*>(&hh) : 0u;
+              }
+              const int c16 = (ch & 1) * 4 + g;
+              sts_128(slab + ((c16 ^ (row & 7)) << 4), pk[0], pk[1], pk[2], pk[3]);
+            }
           }
         }
         if (mh == 2 * (BN / OUT_COLS) - 1) {
@@ -246,7 +295,7 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
           mbar_arrive(&tempty[acc]);  // accumulators drained: the MMA warp may reuse this TMEM buffer
         }
         fence_proxy_async();
-        named_bar_sync(1, 128);
+        named_bar_sync(1, 256);
         if (et == 0 && !ghost) {
 #pragma unroll
           for (int s = 0; s < OUT_COLS / 64; ++s)
@@ -254,39 +303,44 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
           tma_store_commit();
         }
         if (p.stats != nullptr && !ghost) {
-          // per-channel sum / sum-of-squares of the bf16 values just staged (invalid rows hold zeros)
+          // per-channel sum / sum-of-squares of the bf16 values just staged (masked rows hold zeros):
+          // thread = (channel pair w, row group rg of 16 rows)
           const int w = et & 31, rg = et >> 5;
 #pragma unroll
           for (int s = 0; s < OUT_COLS / 64; ++s) {
             float s0a = 0.f, s0b = 0.f, s1a = 0.f, s1b = 0.f;
-            const uint8_t* slab = s_out + s * (128 * 128);
-#pragma unroll 8
-            for (int i = 0; i < 32; ++i) {
-              const int rr = rg * 32 + i;
-              uint32_t u = *reinterpret_cast<const uint32_t*>(slab + rr * 128 + (((w >> 2) ^ (rr & 7)) << 4) + (w & 3) * 4);
-              float2 f = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u));
-              s0a += f.x; s0b += f.y;
-              s1a = fmaf(f.x, f.x, s1a); s1b = fmaf(f.y, f.y, s1b);
+            const uint32_t slab = so + s * (128 * 128);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const int rr = rg * 16 + i;
+              const uint32_t u = lds_32(slab + rr * 128 + (((w >> 2) ^ (rr & 7)) << 4) + (w & 3) * 4);
+              const float fx = __uint_as_float(u << 16), fy = __uint_as_float(u & 0xffff0000u);
+              s0a += fx; s0b += fy;
+              s1a = fmaf(fx, fx, s1a); s1b = fmaf(fy, fy, s1b);
             }
-            float* rd = s_red + rg * (2 * OUT_COLS);
-            rd[s * 64 + 2 * w] = s0a;
-            rd[s * 64 + 2 * w + 1] = s0b;
-            rd[OUT_COLS + s * 64 + 2 * w] = s1a;
-            rd[OUT_COLS + s * 64 + 2 * w + 1] = s1b;
+            const uint32_t rd = sr + rg * (2 * OUT_COLS) * 4;
+            sts_f32(rd + (s * 64 + 2 * w) * 4, s0a);
+            sts_f32(rd + (s * 64 + 2 * w + 1) * 4, s0b);
+            sts_f32(rd + (OUT_COLS + s * 64 + 2 * w) * 4, s1a);
+            sts_f32(rd + (OUT_COLS + s * 64 + 2 * w + 1) * 4, s1b);
           }
-          named_bar_sync(2, 128);
-          for (int j = et; j < 2 * OUT_COLS; j += 128) {  // (which, channel) -> always the same thread: no race
-            float a = s_red[j] + s_red[2 * OUT_COLS + j] + s_red[4 * OUT_COLS + j] + s_red[6 * OUT_COLS + j];
+          named_bar_sync(2, 256);
+          if (et < 2 * OUT_COLS) {  // (which, channel) -> always the same thread: no race on s_acc
+            const int j = et;
+            float a = 0.f;
+#pragma unroll
+            for (int g8 = 0; g8 < 8; ++g8) a += lds_f32(sr + (g8 * 2 * OUT_COLS + j) * 4);
             const int which = j / OUT_COLS, c = j % OUT_COLS;
-            s_acc[which * p.cout + nt * BN + h * OUT_COLS + c] += a;
+            const uint32_t dst = sacc + (which * p.cout + nt * BN + h * OUT_COLS + c) * 4;
+            sts_f32(dst, lds_f32(dst) + a);
           }
-          named_bar_sync(2, 128);
+          named_bar_sync(2, 256);
         }
       }
       if (++acc == NBUF) { acc = 0; acc_phase ^= 1u; }
     }
     if (p.stats != nullptr)  // one statistics row per CTA (CTAs without tiles write zeros)
-      for (int j = et; j < 2 * p.cout; j += 128) p.stats[(int64_t)blockIdx.x * 2 * p.cout + j] = s_acc[j];
+      for (int j = et; j < 2 * p.cout; j += 256) p.stats[(int64_t)blockIdx.x * 2 * p.cout + j] = lds_f32(sacc + 4 * j);
     if (et == 0) tma_store_wait_read();
   }
   tc_fence_before();
@@ -487,6 +541,19 @@ static bool build_halo_plan(const TcTaps& taps, HaloPlan& plan, int& max_ndy, bo
     if (cnt[g] > max_ndy) max_ndy = cnt[g];
     if (cnt[g] != cnt[0]) uniform = false;
   }
+  // order the groups by (map, dx): the full-halo mode wants dx ascending from the box origin
+  for (int a = 0; a < plan.ngroups; ++a)
+    for (int b = a + 1; b < plan.ngroups; ++b)
+      if (plan.map[b] < plan.map[a] || (plan.map[b] == plan.map[a] && plan.dx[b] < plan.dx[a])) {
+        int8_t t8;
+        t8 = plan.map[a]; plan.map[a] = plan.map[b]; plan.map[b] = t8;
+        t8 = plan.dx[a]; plan.dx[a] = plan.dx[b]; plan.dx[b] = t8;
+        t8 = plan.dy0[a]; plan.dy0[a] = plan.dy0[b]; plan.dy0[b] = t8;
+        t8 = plan.ndy[a]; plan.ndy[a] = plan.ndy[b]; plan.ndy[b] = t8;
+        for (int j = 0; j < kHaloMaxDy; ++j) {
+          uint8_t u8 = plan.wtap[a][j]; plan.wtap[a][j] = plan.wtap[b][j]; plan.wtap[b][j] = u8;
+        }
+      }
   return plan.ngroups > 0;
 }
 
@@ -498,6 +565,11 @@ static bool env_flag(const char* name, bool dflt) {
 static bool cluster_enabled() {
   static int v = -1;
   if (v < 0) v = env_flag("GSB_TC_CLUSTER", true) ? 1 : 0;
+  return v != 0;
+}
+static bool fullhalo_enabled() {
+  static int v = -1;
+  if (v < 0) v = env_flag("GSB_TC_FULLHALO", true) ? 1 : 0;
   return v != 0;
 }
 static bool bn256_enabled() {
@@ -521,10 +593,16 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
   bool uniform;
   if (!build_halo_plan(taps, plan, max_ndy, uniform)) return 0;
   const int boxh = 16 + max_ndy - 1;
+  // full-halo mode: one parity map, every group spans the same rows, dx consecutive -> a single box per channel block
+  int full = fullhalo_enabled() && uniform && nmaps == 1 && plan.ngroups > 1 ? 1 : 0;
+  for (int g = 0; full && g < plan.ngroups; ++g)
+    if (plan.dy0[g] != plan.dy0[0] || plan.dx[g] != plan.dx[0] + g) full = 0;
+  const int pw = full ? 16 + plan.ngroups - 1 : 16;
+  if (pw > 24) full = 0;
   TcMaps maps;
   memset(&maps, 0, sizeof(maps));
   for (int i = 0; i < nmaps; ++i)
-    if (make_act_map(&maps.in[i], shifted[i], 16, boxh, 1)) return -1;
+    if (make_act_map(&maps.in[i], shifted[i], full ? pw : 16, boxh, 1)) return -1;
   for (int i = nmaps; i < 4; ++i) maps.in[i] = maps.in[0];
   if (make_act_map(&maps.out, outv, 8, 16, 1)) return -1;
   const int spatial = (((int)outv.W + 15) / 16) * (((int)outv.H + 15) / 16) * (int)outv.N;
@@ -539,16 +617,19 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
   p.cin = cin; p.cout = cout;
   p.n_tiles = cout / BN;
   p.num_tiles = ((spatial + CL - 1) / CL) * p.n_tiles;  // cluster tiles
-  p.a_bytes = 16 * boxh * 128;
+  p.pw = full ? pw : 16;
+  p.full = full;
+  p.a_bytes = p.pw * boxh * 128;
+  p.a_stride = (p.a_bytes + 1023) & ~1023;
   const int b_bytes = BN * 128;
   const int out_cols = BN > 128 ? 128 : BN;
-  const int fixed = 1024 + 128 * out_cols * 2 + 4 * 2 * out_cols * 4 + 256 + (stats ? 2 * cout * 4 : 0);
+  const int fixed = 1024 + 128 * out_cols * 2 + 8 * 2 * out_cols * 4 + 256 + (stats ? 2 * cout * 4 : 0);
   p.nB = BN == 64 ? 6 : (BN == 128 ? 4 : 3);
-  int nA = (232448 - fixed - p.nB * b_bytes) / p.a_bytes;
+  int nA = (232448 - fixed - p.nB * b_bytes) / p.a_stride;
   p.nA = nA > 4 ? 4 : nA;
   GSB_REQUIRE(p.nA >= 2, "conv_halo: shared memory budget");
   p.act = act; p.bias = bias; p.stats = stats;
-  const int smem = fixed + p.nA * p.a_bytes + p.nB * b_bytes;
+  const int smem = fixed + p.nA * p.a_stride + p.nB * b_bytes;
   const int max_clusters = num_sms() / CL;
   const int grid = (p.num_tiles < max_clusters ? p.num_tiles : max_clusters) * CL;
   if (stats_rows) *stats_rows = grid;  // one row of running sums per CTA
@@ -560,7 +641,7 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(192);
+  cfg.blockDim = dim3(320);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];

@@ -132,7 +132,7 @@ template <>
 __device__ __forceinline__ float stored_value<__nv_bfloat16>(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
 
 template <typename T, int PX, int K, int S>
-__global__ void __launch_bounds__(256) stem_fwd_fast_kernel(const float* __restrict__ x, int N, int Cin, int H, int W,
+__global__ void __launch_bounds__(256, 2) stem_fwd_fast_kernel(const float* __restrict__ x, int N, int Cin, int H, int W,
                                                            const float* __restrict__ w, const float* __restrict__ bias,
                                                            T* __restrict__ y, int64_t yld, int OH, int OW, int Cout, int pad,
                                                            int act, float* __restrict__ stats) {
@@ -226,7 +226,7 @@ __global__ void __launch_bounds__(256) stem_fwd_fast_kernel(const float* __restr
 
 // dw[co][ci][ky][kx] += sum_pix dY[pix][co] * x[pix @ (ky,kx)]; blockIdx.y = ci; all K*K taps of 8 channels in registers
 template <typename T, int PX, int K, int S>
-__global__ void __launch_bounds__(256) stem_wgrad_fast_kernel(const float* __restrict__ x, int N, int Cin, int H, int W,
+__global__ void __launch_bounds__(256, 2) stem_wgrad_fast_kernel(const float* __restrict__ x, int N, int Cin, int H, int W,
                                                              const T* __restrict__ dy, int64_t dld, int OH, int OW, int Cout,
                                                              int pad, float* __restrict__ dw) {
   extern __shared__ float sacc[];  // [G][K*K][8]

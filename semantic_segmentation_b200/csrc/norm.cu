@@ -136,22 +136,29 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
   }
 }
 
-// partial[rows][n] fp32 -> sums[n] fp64.  Block = 32 columns x 8 row lanes: coalesced 128-byte row segments,
-// fp64 accumulation, fixed summation order (deterministic).
-__global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ partial, int rows, int n,
-                                                             double* __restrict__ sums) {
-  __shared__ double red[8][33];
+// partial[rows][n] fp32 -> sums[n] fp64.  Block = 32 columns x 32 row lanes: coalesced 128-byte row segments,
+// four independent loads in flight per thread, fp64 accumulation, fixed summation order (deterministic).
+__global__ void __launch_bounds__(1024) reduce_partials_kernel(const float* __restrict__ partial, int rows, int n,
+                                                              double* __restrict__ sums) {
+  __shared__ double red[32][33];
   const int c = threadIdx.x & 31, l = threadIdx.x >> 5;
   const int col = blockIdx.x * 32 + c;
-  double acc = 0.0;
-  if (col < n)
-    for (int r = l; r < rows; r += 8) acc += (double)partial[(int64_t)r * n + col];
-  red[l][c] = acc;
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+  if (col < n) {
+    int r = l;
+    for (; r + 96 < rows; r += 128) {
+      const float v0 = partial[(int64_t)r * n + col], v1 = partial[(int64_t)(r + 32) * n + col];
+      const float v2 = partial[(int64_t)(r + 64) * n + col], v3 = partial[(int64_t)(r + 96) * n + col];
+      a0 += (double)v0; a1 += (double)v1; a2 += (double)v2; a3 += (double)v3;
+    }
+    for (; r < rows; r += 32) a0 += (double)partial[(int64_t)r * n + col];
+  }
+  red[l][c] = (a0 + a1) + (a2 + a3);
   __syncthreads();
   if (l == 0 && col < n) {
     double t = 0.0;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) t += red[i][c];
+    for (int i = 0; i < 32; ++i) t += red[i][c];
     sums[col] = t;
   }
 }
@@ -364,13 +371,13 @@ extern "C" int gsb_bn_reduce(const gsb_view* x, double* sums, void* workspace, s
     bn_reduce_kernel<float, 0, false><<<grid, kThreads, smem, to_stream(s)>>>(pv(x), nul, nul, P, C, nullptr, nullptr, nullptr,
                                                                              nullptr, 0, 0, 0, nullptr, partial);
   int n = 2 * C;
-  reduce_partials_kernel<<<(n + 31) / 32, 256, 0, to_stream(s)>>>(partial, grid, n, sums);
+  reduce_partials_kernel<<<(n + 31) / 32, 1024, 0, to_stream(s)>>>(partial, grid, n, sums);
   return check_launch("bn_reduce", 2);
 }
 
 extern "C" int gsb_bn_reduce_partials(const float* partial, int rows, int c, double* sums, gsb_stream s) {
   int n = 2 * c;
-  reduce_partials_kernel<<<(n + 31) / 32, 256, 0, to_stream(s)>>>(partial, rows, n, sums);
+  reduce_partials_kernel<<<(n + 31) / 32, 1024, 0, to_stream(s)>>>(partial, rows, n, sums);
   return check_launch("bn_reduce_partials");
 }
 
@@ -447,7 +454,7 @@ extern "C" int gsb_bn_bwd_reduce(const gsb_view* x, const gsb_view* dA1, const g
                                                                              invstd, act1, act2, drop_seed, drop_mask, partial);
   }
   int n = 2 * C;
-  reduce_partials_kernel<<<(n + 31) / 32, 256, 0, to_stream(s)>>>(partial, grid, n, sums);
+  reduce_partials_kernel<<<(n + 31) / 32, 1024, 0, to_stream(s)>>>(partial, grid, n, sums);
   return check_launch("bn_bwd_reduce", 2);
 }
 

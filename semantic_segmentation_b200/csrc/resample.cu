@@ -7,18 +7,43 @@
 
 namespace gsb {
 
+// (group, x, y, n) of flat item i = ((n*OH + oy)*OW + ox)*G + g; 32-bit divisions whenever the index fits
+struct ItemIdx {
+  int g, ox, oy, n;
+  int64_t p;
+};
+__device__ __forceinline__ ItemIdx decode_item(int64_t i, int G, int OW, int OH) {
+  ItemIdx r;
+  if ((i >> 32) == 0) {
+    const unsigned u = (unsigned)i;
+    const unsigned p = u / (unsigned)G;
+    r.g = (int)(u - p * (unsigned)G);
+    const unsigned row = p / (unsigned)OW;
+    r.ox = (int)(p - row * (unsigned)OW);
+    const unsigned n = row / (unsigned)OH;
+    r.oy = (int)(row - n * (unsigned)OH);
+    r.n = (int)n;
+    r.p = (int64_t)p;
+  } else {
+    r.g = (int)(i % G);
+    r.p = i / G;
+    r.ox = (int)(r.p % OW);
+    const int64_t row = r.p / OW;
+    r.oy = (int)(row % OH);
+    r.n = (int)(row / OH);
+  }
+  return r;
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) maxpool2_fwd_kernel(const T* __restrict__ x, int64_t xld, int N, int H, int W, int C,
                                                           T* __restrict__ y, int64_t yld) {
   const int G = C >> 3, OH = H >> 1, OW = W >> 1;
   const int64_t total = (int64_t)N * OH * OW * G;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    int g = (int)(i % G);
-    int64_t p = i / G;
-    int ox = (int)(p % OW);
-    int64_t r = p / OW;
-    int oy = (int)(r % OH);
-    int n = (int)(r / OH);
+    const ItemIdx it = decode_item(i, G, OW, OH);
+    const int g = it.g, ox = it.ox, oy = it.oy, n = it.n;
+    const int64_t p = it.p;
     const T* base = x + (((int64_t)n * H + 2 * oy) * W + 2 * ox) * xld + g * 8;
     float m[8], v[8];
     Vec8<T>::load(base, m);
@@ -41,12 +66,8 @@ __global__ void __launch_bounds__(256) maxpool2_bwd_kernel(const T* __restrict__
   const int WH = (H + 1) >> 1, WW = (W + 1) >> 1;  // windows incl. the ragged last row/col
   const int64_t total = (int64_t)N * WH * WW * G;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    int g = (int)(i % G);
-    int64_t p = i / G;
-    int ox = (int)(p % WW);
-    int64_t r = p / WW;
-    int oy = (int)(r % WH);
-    int n = (int)(r / WH);
+    const ItemIdx it = decode_item(i, G, WW, WH);
+    const int g = it.g, ox = it.ox, oy = it.oy, n = it.n;
     const int64_t pix0 = ((int64_t)n * H + 2 * oy) * W + 2 * ox;
     if (oy >= OH || ox >= OW) {  // not a pooling window: gradient is zero there
       if (!accumulate) {
@@ -115,12 +136,9 @@ __global__ void __launch_bounds__(256) upsample2_fwd_kernel(const T* __restrict_
   const int G = C >> 3;
   const int64_t total = (int64_t)N * OH * OW * G;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    int g = (int)(i % G);
-    int64_t p = i / G;
-    int ox = (int)(p % OW);
-    int64_t r = p / OW;
-    int oy = (int)(r % OH);
-    int n = (int)(r / OH);
+    const ItemIdx it = decode_item(i, G, OW, OH);
+    const int g = it.g, ox = it.ox, oy = it.oy, n = it.n;
+    const int64_t p = it.p;
     int uy = oy - pad_top, ux = ox - pad_left;
     float o[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (uy >= 0 && uy < 2 * h && ux >= 0 && ux < 2 * w) {
@@ -149,12 +167,9 @@ __global__ void __launch_bounds__(256) upsample2_bwd_kernel(const T* __restrict_
   const float sy = 2 * h > 1 ? (float)(h - 1) / (float)(2 * h - 1) : 0.f;
   const float sx = 2 * w > 1 ? (float)(w - 1) / (float)(2 * w - 1) : 0.f;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    int g = (int)(i % G);
-    int64_t p = i / G;
-    int ix = (int)(p % w);
-    int64_t r = p / w;
-    int iy = (int)(r % h);
-    int n = (int)(r / h);
+    const ItemIdx it = decode_item(i, G, w, h);
+    const int g = it.g, ix = it.ox, iy = it.oy, n = it.n;
+    const int64_t p = it.p;
     int ylo = 0, yhi = 2 * h - 1, xlo = 0, xhi = 2 * w - 1;
     if (sy > 0.f) {
       ylo = max(0, (int)floorf((float)(iy - 1) / sy) - 1);
@@ -164,6 +179,21 @@ __global__ void __launch_bounds__(256) upsample2_bwd_kernel(const T* __restrict_
       xlo = max(0, (int)floorf((float)(ix - 1) / sx) - 1);
       xhi = min(2 * w - 1, (int)ceilf((float)(ix + 1) / sx) + 1);
     }
+    // separable: the (<= 4) contributing output columns and their weights are found once, not once per row
+    constexpr int kMaxC = 6;
+    int cx[kMaxC];
+    float cw[kMaxC];
+    int ncx = 0;
+    for (int ux = xlo; ux <= xhi && ncx < kMaxC; ++ux) {
+      Lerp lx = lerp_for(ux, w, 2 * w);
+      float wx = (lx.i0 == ix ? lx.l0 : 0.f) + (lx.i1 == ix ? lx.l1 : 0.f);
+      int ox = ux + pad_left;
+      if (wx != 0.f && ox >= 0 && ox < OW) {
+        cx[ncx] = ox;
+        cw[ncx] = wx;
+        ++ncx;
+      }
+    }
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (int uy = ylo; uy <= yhi; ++uy) {
       Lerp ly = lerp_for(uy, h, 2 * h);
@@ -171,17 +201,16 @@ __global__ void __launch_bounds__(256) upsample2_bwd_kernel(const T* __restrict_
       if (wy == 0.f) continue;
       int oy = uy + pad_top;
       if (oy < 0 || oy >= OH) continue;
-      for (int ux = xlo; ux <= xhi; ++ux) {
-        Lerp lx = lerp_for(ux, w, 2 * w);
-        float wx = (lx.i0 == ix ? lx.l0 : 0.f) + (lx.i1 == ix ? lx.l1 : 0.f);
-        if (wx == 0.f) continue;
-        int ox = ux + pad_left;
-        if (ox < 0 || ox >= OW) continue;
-        float v[8];
-        Vec8<T>::load(dout + (((int64_t)n * OH + oy) * OW + ox) * dld + g * 8, v);
-        float wgt = wy * wx;
+      const T* rowp = dout + ((int64_t)n * OH + oy) * OW * dld + g * 8;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) acc[k] = fmaf(wgt, v[k], acc[k]);
+      for (int c = 0; c < kMaxC; ++c) {
+        if (c < ncx) {
+          float v[8];
+          Vec8<T>::load(rowp + (int64_t)cx[c] * dld, v);
+          float wgt = wy * cw[c];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] = fmaf(wgt, v[k], acc[k]);
+        }
       }
     }
     Vec8<T>::store(dx + p * xld + g * 8, acc);
