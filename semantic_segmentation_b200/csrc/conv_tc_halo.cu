@@ -71,6 +71,15 @@ __device__ __forceinline__ uint32_t lds_32(uint32_t addr) {
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
   return v;
 }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
+      "elect.sync rx|px, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, px;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
@@ -169,49 +178,59 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {  // ---------------- MMA issuer ----------------
-      constexpr uint32_t idesc = umma_idesc(128, BN, 0, 0);
-      int sa = 0, sb = 0;
-      uint32_t pa = 0, pb = 0, acc = 0, acc_phase = 0;
-      for (int tile = cluster_id; tile < num_ctiles; tile += nclusters) {
-        mbar_wait(&tempty[acc], acc_phase ^ 1u);
-        tc_fence_after();
-        const uint32_t d0 = tmem_base + acc * (2 * BN);
-        uint32_t accum = 0;
-        for (int kb = 0; kb < kblocks; ++kb) {
-          for (int g = 0; g < plan.ngroups; ++g) {
-            if (!p.full || g == 0) {
-              mbar_wait(&fullA[sa], pa);
-              tc_fence_after();
-            }
-            // full mode: horizontal taps are pixel (= 128 B row) shifts inside the one box; the swizzle XOR acts on
-            // absolute shared-memory address bits, so a row-shifted start stays consistent with what TMA wrote
-            const uint32_t a_base = smem_u32(sA + sa * p.a_stride) + (p.full ? (uint32_t)(plan.dx[g] - plan.dx[0]) * 128u : 0u);
-            const uint32_t row_bytes = (uint32_t)p.pw * 128u;
-            const int nd = plan.ndy[g];
-            for (int j = 0; j < nd; ++j) {
-              mbar_wait(&fullB[sb], pb);
-              tc_fence_after();
-              const uint64_t bdesc = umma_desc(smem_u32(sB + sb * B_BYTES), 16, 1024);
+    // ---------------- MMA issuer ----------------
+    // The WHOLE warp runs the loop (warp-uniform control flow and operands, so descriptors and barrier addresses stay
+    // in uniform registers); one elected lane issues.  With `if (lane == 0)` around the loop every tcgen05.mma cost
+    // ~20 dependent per-thread instructions (~120 cycles, ncu profiles/r01e) against 32-128 cycles of tensor time.
+    constexpr uint32_t idesc = umma_idesc(128, BN, 0, 0);
+    int sa = 0, sb = 0;
+    uint32_t pa = 0, pb = 0, acc = 0, acc_phase = 0;
+    const uint32_t row_bytes = (uint32_t)p.pw * 128u;
+    const uint64_t desc_hi_a = umma_desc(0, 16, row_bytes), desc_hi_b = umma_desc(0, 16, 1024);
+    const uint32_t sA_u = smem_u32(sA), sB_u = smem_u32(sB);
+    for (int tile = cluster_id; tile < num_ctiles; tile += nclusters) {
+      mbar_wait(&tempty[acc], acc_phase ^ 1u);
+      tc_fence_after();
+      const uint32_t d0 = tmem_base + acc * (2 * BN);
+      uint32_t accum = 0;
+      for (int kb = 0; kb < kblocks; ++kb) {
+        for (int g = 0; g < plan.ngroups; ++g) {
+          if (!p.full || g == 0) {
+            mbar_wait(&fullA[sa], pa);
+            tc_fence_after();
+          }
+          // full mode: horizontal taps are pixel (= 128 B row) shifts inside the one box; the swizzle XOR acts on
+          // absolute shared-memory address bits, so a row-shifted start stays consistent with what TMA wrote
+          const uint32_t a_base = sA_u + sa * p.a_stride + (p.full ? (uint32_t)(plan.dx[g] - plan.dx[0]) * 128u : 0u);
+          const int nd = plan.ndy[g];
+          for (int j = 0; j < nd; ++j) {
+            mbar_wait(&fullB[sb], pb);
+            tc_fence_after();
+            const uint64_t bdesc = desc_hi_b | (uint64_t)(((sB_u + sb * B_BYTES) & 0x3FFFFu) >> 4);
+            const uint64_t adesc = desc_hi_a | (uint64_t)(((a_base + j * row_bytes) & 0x3FFFFu) >> 4);
+            if (elect_one()) {
 #pragma unroll
               for (int m = 0; m < 2; ++m) {
-                const uint64_t adesc = umma_desc(a_base + m * 1024 + j * row_bytes, 16, row_bytes);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) umma_bf16(d0 + m * BN, adesc + 2 * k, bdesc + 2 * k, idesc, accum | (uint32_t)k);
+                for (int k = 0; k < 4; ++k)
+                  umma_bf16(d0 + m * BN, adesc + (uint64_t)(64 * m + 2 * k), bdesc + (uint64_t)(2 * k), idesc, accum | (uint32_t)k);
               }
-              accum = 1;
               if (CL > 1) umma_commit_mc(&emptyB[sb], kMask); else umma_commit(&emptyB[sb]);
-              if (++sb == p.nB) { sb = 0; pb ^= 1u; }
             }
-            if (!p.full || g == plan.ngroups - 1) {
-              umma_commit(&emptyA[sa]);
-              if (++sa == p.nA) { sa = 0; pa ^= 1u; }
-            }
+            __syncwarp();
+            accum = 1;
+            if (++sb == p.nB) { sb = 0; pb ^= 1u; }
+          }
+          if (!p.full || g == plan.ngroups - 1) {
+            if (elect_one()) umma_commit(&emptyA[sa]);
+            __syncwarp();
+            if (++sa == p.nA) { sa = 0; pa ^= 1u; }
           }
         }
-        umma_commit(&tfull[acc]);
-        if (++acc == NBUF) { acc = 0; acc_phase ^= 1u; }
       }
+      if (elect_one()) umma_commit(&tfull[acc]);
+      __syncwarp();
+      if (++acc == NBUF) { acc = 0; acc_phase ^= 1u; }
     }
   } else {  // ---------------- epilogue warps 2..9 ----------------
     // Eight warps: two per TMEM lane quarter, each taking half of the columns of a staging pass.  With four warps
@@ -435,26 +454,32 @@ conv_tc_wgrad_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_cons
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && nsteps > 0) {
+    if (nsteps > 0) {  // whole warp runs the loop (uniform operands), one elected lane issues
       constexpr uint32_t idesc = umma_idesc(128, BN, 1, 1);
       int stage = 0;
       uint32_t phase = 0;
+      const uint64_t hi_a = umma_desc(0, (uint32_t)p.a_block_bytes, 1024), hi_b = umma_desc(0, 16384, 1024);
+      const uint32_t s0 = smem_u32(smem);
       for (int s = 0; s < nsteps; ++s) {
         mbar_wait(&full[stage], phase);
         tc_fence_after();
-        const uint32_t sa = smem_u32(smem + stage * stage_bytes);
-        const uint64_t adesc = umma_desc(sa, (uint32_t)p.a_block_bytes, 1024);
-        const uint64_t bdesc = umma_desc(sa + 2 * p.a_block_bytes, 16384, 1024);
-        for (int j = 0; j < p.ndy; ++j) {
+        const uint32_t sa = s0 + stage * stage_bytes;
+        const uint64_t adesc = hi_a | (uint64_t)((sa & 0x3FFFFu) >> 4);
+        const uint64_t bdesc = hi_b | (uint64_t)(((sa + 2 * p.a_block_bytes) & 0x3FFFFu) >> 4);
+        if (elect_one()) {
+          for (int j = 0; j < p.ndy; ++j) {
 #pragma unroll
-          for (int k = 0; k < 8; ++k)  // 16 pixels (two 8-pixel rows) per MMA; vertical tap j = +j rows
-            umma_bf16(tmem_base + j * BN, adesc + (uint64_t)(64 * j + 128 * k), bdesc + (uint64_t)(128 * k), idesc,
-                      (uint32_t)(s | k));
+            for (int k = 0; k < 8; ++k)  // 16 pixels (two 8-pixel rows) per MMA; vertical tap j = +j rows
+              umma_bf16(tmem_base + j * BN, adesc + (uint64_t)(64 * j + 128 * k), bdesc + (uint64_t)(128 * k), idesc,
+                        (uint32_t)(s | k));
+          }
+          umma_commit(&empty[stage]);
         }
-        umma_commit(&empty[stage]);
+        __syncwarp();
         if (++stage == p.nstages) { stage = 0; phase ^= 1u; }
       }
-      umma_commit(tfull);
+      if (elect_one()) umma_commit(tfull);
+      __syncwarp();
     }
   } else if (nsteps > 0) {
     const int q = warp & 3, row = q * 32 + lane;
