@@ -38,6 +38,7 @@ struct HaloParams {
   int cin, cout, n_tiles, num_tiles;
   int nA, nB, a_bytes;   // ring depths and activation box bytes (pw x boxh x 128 B)
   int a_stride;          // activation slot stride (a_bytes rounded up to 1024)
+  int tb;                // vertical taps per weight slot (1, or ndy for the short N=64 MMAs: fewer barrier round trips)
   int pw, full;          // box width in pixels; full = 1: ONE box per 64-channel block serves every (dx, dy) tap
   int act;
   const float* bias;
@@ -101,7 +102,7 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem;
   uint8_t* sB = sA + p.nA * p.a_stride;
-  uint8_t* s_out = sB + p.nB * B_BYTES;
+  uint8_t* s_out = sB + p.nB * p.tb * B_BYTES;
   float* s_red = reinterpret_cast<float*>(s_out + OUT_BYTES);
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_out + OUT_BYTES + RED_BYTES);
   float* s_acc = reinterpret_cast<float*>(bars + 32);  // [2][cout] running BN sums of this CTA (only when p.stats)
@@ -163,14 +164,18 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
               if (++sa == p.nA) { sa = 0; pa ^= 1u; }
             }
             const int nd = plan.ndy[g];
-            for (int j = 0; j < nd; ++j) {
+            for (int j0 = 0; j0 < nd; j0 += p.tb) {
+              const int nt_ = nd - j0 < p.tb ? nd - j0 : p.tb;
               mbar_wait(&emptyB[sb], pb ^ 1u);
-              mbar_expect_tx(&fullB[sb], B_BYTES);
-              const int wrow = (int)plan.wtap[g][j] * p.cout + nt * BN;
-              if (CL > 1)
-                tma_load_2d_mc(&maps.w, &fullB[sb], sB + sb * B_BYTES + rank * (B_BYTES / CL), kb * 64, wrow + rank * (BN / CL), kMask);
-              else
-                tma_load_2d(&maps.w, &fullB[sb], sB + sb * B_BYTES, kb * 64, wrow);
+              mbar_expect_tx(&fullB[sb], (uint32_t)(nt_ * B_BYTES));
+              for (int t = 0; t < nt_; ++t) {
+                const int wrow = (int)plan.wtap[g][j0 + t] * p.cout + nt * BN;
+                uint8_t* dst = sB + (sb * p.tb + t) * B_BYTES;
+                if (CL > 1)
+                  tma_load_2d_mc(&maps.w, &fullB[sb], dst + rank * (B_BYTES / CL), kb * 64, wrow + rank * (BN / CL), kMask);
+                else
+                  tma_load_2d(&maps.w, &fullB[sb], dst, kb * 64, wrow);
+              }
               if (++sb == p.nB) { sb = 0; pb ^= 1u; }
             }
           }
@@ -203,17 +208,21 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
           // absolute shared-memory address bits, so a row-shifted start stays consistent with what TMA wrote
           const uint32_t a_base = sA_u + sa * p.a_stride + (p.full ? (uint32_t)(plan.dx[g] - plan.dx[0]) * 128u : 0u);
           const int nd = plan.ndy[g];
-          for (int j = 0; j < nd; ++j) {
+          for (int j0 = 0; j0 < nd; j0 += p.tb) {
+            const int nt_ = nd - j0 < p.tb ? nd - j0 : p.tb;
             mbar_wait(&fullB[sb], pb);
             tc_fence_after();
-            const uint64_t bdesc = desc_hi_b | (uint64_t)(((sB_u + sb * B_BYTES) & 0x3FFFFu) >> 4);
-            const uint64_t adesc = desc_hi_a | (uint64_t)(((a_base + j * row_bytes) & 0x3FFFFu) >> 4);
+            const uint64_t bdesc0 = desc_hi_b | (uint64_t)(((sB_u + sb * p.tb * B_BYTES) & 0x3FFFFu) >> 4);
+            const uint64_t adesc0 = desc_hi_a | (uint64_t)(((a_base + j0 * row_bytes) & 0x3FFFFu) >> 4);
             if (elect_one()) {
+              for (int t = 0; t < nt_; ++t) {
+                const uint64_t adesc = adesc0 + (uint64_t)(t * (row_bytes >> 4)), bdesc = bdesc0 + (uint64_t)(t * (B_BYTES >> 4));
 #pragma unroll
-              for (int m = 0; m < 2; ++m) {
+                for (int m = 0; m < 2; ++m) {
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
-                  umma_bf16(d0 + m * BN, adesc + (uint64_t)(64 * m + 2 * k), bdesc + (uint64_t)(2 * k), idesc, accum | (uint32_t)k);
+                  for (int k = 0; k < 4; ++k)
+                    umma_bf16(d0 + m * BN, adesc + (uint64_t)(64 * m + 2 * k), bdesc + (uint64_t)(2 * k), idesc, accum | (uint32_t)(t | k));
+                }
               }
               if (CL > 1) umma_commit_mc(&emptyB[sb], kMask); else umma_commit(&emptyB[sb]);
             }
@@ -649,12 +658,13 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
   const int b_bytes = BN * 128;
   const int out_cols = BN > 128 ? 128 : BN;
   const int fixed = 1024 + 128 * out_cols * 2 + 8 * 2 * out_cols * 4 + 256 + (stats ? 2 * cout * 4 : 0);
-  p.nB = BN == 64 ? 6 : (BN == 128 ? 4 : 3);
-  int nA = (232448 - fixed - p.nB * b_bytes) / p.a_stride;
+  p.tb = (BN == 64 && uniform) ? max_ndy : 1;
+  p.nB = BN == 64 ? (p.tb > 1 ? 3 : 6) : (BN == 128 ? 4 : 3);
+  int nA = (232448 - fixed - p.nB * p.tb * b_bytes) / p.a_stride;
   p.nA = nA > 4 ? 4 : nA;
   GSB_REQUIRE(p.nA >= 2, "conv_halo: shared memory budget");
   p.act = act; p.bias = bias; p.stats = stats;
-  const int smem = fixed + p.nA * p.a_stride + p.nB * b_bytes;
+  const int smem = fixed + p.nA * p.a_stride + p.nB * p.tb * b_bytes;
   const int max_clusters = num_sms() / CL;
   const int grid = (p.num_tiles < max_clusters ? p.num_tiles : max_clusters) * CL;
   if (stats_rows) *stats_rows = grid;  // one row of running sums per CTA
