@@ -62,6 +62,11 @@ int gsb_pack_weight(const float* src, int d0, int d1, int kh, int kw, int rows_f
  * accumulate != 0 adds into dst. */
 int gsb_unpack_wgrad(const float* src, int d0, int d1, int kh, int kw, int rows_from_d0, float* dst,
                      int accumulate, gsb_stream s);
+/* Batched forms of the two calls above: n (layer) jobs in one launch; taps = kh*kw; host arrays. */
+int gsb_pack_weight_multi(int n, const void* const* src, void* const* dst, const int* d0, const int* d1, const int* taps,
+                          const int* rows_from_d0, int dst_dtype, gsb_stream s);
+int gsb_unpack_wgrad_multi(int n, const void* const* src, void* const* dst, const int* d0, const int* d1, const int* taps,
+                           const int* rows_from_d0, int accumulate, gsb_stream s);
 /* Mixed transposed-conv cell (networks.py:495-511, operations.py:14-39): softmax(alpha[3])-
  * weighted, zero-padded sum of the IOHW k4/k6/k8 weights -> one IOHW 8x8 fp32 weight, and
  * merged bias (nullable).  SURVEY fact 4. */
@@ -195,6 +200,13 @@ int gsb_rmsprop_step(float* p, const float* g, float* square_avg, float* mom_buf
 int gsb_adam_step(float* p, const float* g, float* exp_avg, float* exp_avg_sq, int64_t numel, float lr,
                   float beta1, float beta2, float eps, float weight_decay, int64_t step, float grad_scale,
                   gsb_stream s);
+/* Multi-tensor forms: n tensors in one launch (host arrays of device pointers / element counts). */
+int gsb_rmsprop_step_multi(int n, float* const* p, const float* const* g, float* const* square_avg, float* const* mom_buf,
+                           const int64_t* numel, float lr, float alpha, float eps, float weight_decay, float momentum,
+                           float grad_scale, gsb_stream s);
+int gsb_adam_step_multi(int n, float* const* p, const float* const* g, float* const* exp_avg, float* const* exp_avg_sq,
+                        const int64_t* numel, float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
+                        float grad_scale, gsb_stream s);
 
 #ifdef __cplusplus
 }

@@ -41,6 +41,8 @@ SIGNATURES = {
     "gsb_copy_view": (_i, [_VP, _VP, _p]),
     "gsb_pack_weight": (_i, [_p, _i, _i, _i, _i, _i, _p, _i, _p]),
     "gsb_unpack_wgrad": (_i, [_p, _i, _i, _i, _i, _i, _p, _i, _p]),
+    "gsb_pack_weight_multi": (_i, [_i, _p, _p, _p, _p, _p, _p, _i, _p]),
+    "gsb_unpack_wgrad_multi": (_i, [_i, _p, _p, _p, _p, _p, _p, _i, _p]),
     "gsb_merge_upconv": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _p, _p, _p]),
     "gsb_unmerge_upconv": (_i, [_p] * 9 + [_i, _i] + [_p] * 7 + [_p, _sz, _p]),
     "gsb_conv_gather": (_i, [_VP, _p, _i, _p, _VP, _GP, _i, _i, _i, _p, _p, _p]),
@@ -75,6 +77,8 @@ SIGNATURES = {
     "gsb_act_bwd": (_i, [_p, _p, _i, _p, _i64, _p]),
     "gsb_rmsprop_step": (_i, [_p, _p, _p, _p, _i64, _f, _f, _f, _f, _f, _f, _p]),
     "gsb_adam_step": (_i, [_p, _p, _p, _p, _i64, _f, _f, _f, _f, _f, _i64, _f, _p]),
+    "gsb_rmsprop_step_multi": (_i, [_i, _p, _p, _p, _p, _p, _f, _f, _f, _f, _f, _f, _p]),
+    "gsb_adam_step_multi": (_i, [_i, _p, _p, _p, _p, _p, _f, _f, _f, _f, _f, _i64, _f, _p]),
 }
 
 _lib: Optional[C.CDLL] = None

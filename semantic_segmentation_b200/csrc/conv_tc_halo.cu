@@ -661,6 +661,15 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
   p.tb = (BN == 64 && uniform) ? max_ndy : 1;
   p.nB = BN == 64 ? (p.tb > 1 ? 3 : 6) : (BN == 128 ? 4 : 3);
   int nA = (232448 - fixed - p.nB * p.tb * b_bytes) / p.a_stride;
+  if (nA < 2 && p.tb > 1) {  // tall windows (4 vertical taps): back to one tap per weight slot
+    p.tb = 1;
+    p.nB = 6;
+    nA = (232448 - fixed - p.nB * p.tb * b_bytes) / p.a_stride;
+  }
+  while (nA < 2 && p.nB > 2) {
+    --p.nB;
+    nA = (232448 - fixed - p.nB * p.tb * b_bytes) / p.a_stride;
+  }
   p.nA = nA > 4 ? 4 : nA;
   GSB_REQUIRE(p.nA >= 2, "conv_halo: shared memory budget");
   p.act = act; p.bias = bias; p.stats = stats;

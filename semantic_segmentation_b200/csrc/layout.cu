@@ -195,3 +195,116 @@ extern "C" int gsb_unmerge_upconv(const float* dw_merged, const float* db_merged
   dalpha_kernel<<<1, 1, 0, to_stream(s)>>>(dots, alpha, dalpha);
   return check_launch("unmerge_upconv", 2);
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Batched ("multi-tensor") weight pack / weight-gradient unpack: one launch for every layer of a network instead of
+// one 5-8 us latency-bound launch per layer (34 + 17 launches per U-Net step; visible at 8 images per GPU).
+// ---------------------------------------------------------------------------------------------------------
+namespace gsb {
+constexpr int kMaxLayoutJobs = 64;
+struct LayoutJobs {
+  const void* src[kMaxLayoutJobs];
+  void* dst[kMaxLayoutJobs];
+  int d0[kMaxLayoutJobs], d1[kMaxLayoutJobs], taps[kMaxLayoutJobs];
+  int blk0[kMaxLayoutJobs + 1];
+  uint8_t rows_from_d0[kMaxLayoutJobs];
+  int count, dst_dtype, accumulate;
+};
+constexpr int kLayoutPerBlock = 256 * 8;
+
+__device__ __forceinline__ int find_job(const int* blk0, int count, int b) {
+  int lo = 0, hi = count - 1;
+  while (lo < hi) {
+    int mid = (lo + hi + 1) >> 1;
+    if (blk0[mid] <= b) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+
+__global__ void __launch_bounds__(256) pack_weight_multi_kernel(const __grid_constant__ LayoutJobs J) {
+  const int j = find_job(J.blk0, J.count, blockIdx.x);
+  const int d0 = J.d0[j], d1 = J.d1[j], taps = J.taps[j], rfd = J.rows_from_d0[j];
+  const int rows = rfd ? d0 : d1, cols = rfd ? d1 : d0;
+  const int64_t total = (int64_t)taps * rows * cols;
+  const float* src = reinterpret_cast<const float*>(J.src[j]);
+  const int64_t base = (int64_t)(blockIdx.x - J.blk0[j]) * kLayoutPerBlock;
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+    const int64_t i = base + u * 256 + threadIdx.x;
+    if (i < total) {
+      int c = (int)(i % cols);
+      int64_t r2 = i / cols;
+      int r = (int)(r2 % rows);
+      int tap = (int)(r2 / rows);
+      int i0 = rfd ? r : c, i1 = rfd ? c : r;
+      st_elem(J.dst[j], i, J.dst_dtype, src[((int64_t)i0 * d1 + i1) * taps + tap]);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const __grid_constant__ LayoutJobs J) {
+  const int j = find_job(J.blk0, J.count, blockIdx.x);
+  const int d0 = J.d0[j], d1 = J.d1[j], taps = J.taps[j], rfd = J.rows_from_d0[j];
+  const int rows = rfd ? d0 : d1, cols = rfd ? d1 : d0;
+  const int64_t total = (int64_t)taps * d0 * d1;
+  const float* src = reinterpret_cast<const float*>(J.src[j]);
+  float* dst = reinterpret_cast<float*>(J.dst[j]);
+  const int64_t base = (int64_t)(blockIdx.x - J.blk0[j]) * kLayoutPerBlock;
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+    const int64_t i = base + u * 256 + threadIdx.x;
+    if (i < total) {
+      int tap = (int)(i % taps);
+      int64_t r2 = i / taps;
+      int i1 = (int)(r2 % d1);
+      int i0 = (int)(r2 / d1);
+      int r = rfd ? i0 : i1, c = rfd ? i1 : i0;
+      float v = src[((int64_t)tap * rows + r) * cols + c];
+      dst[i] = J.accumulate ? dst[i] + v : v;
+    }
+  }
+}
+
+static int run_layout_multi(bool pack, int n, const void* const* src, void* const* dst, const int* d0, const int* d1,
+                            const int* taps, const int* rows_from_d0, int dst_dtype, int accumulate, cudaStream_t st) {
+  int launches = 0;
+  for (int begin = 0; begin < n; begin += kMaxLayoutJobs) {
+    LayoutJobs J;
+    memset(&J, 0, sizeof(J));
+    J.count = n - begin < kMaxLayoutJobs ? n - begin : kMaxLayoutJobs;
+    J.dst_dtype = dst_dtype;
+    J.accumulate = accumulate;
+    int blocks = 0;
+    for (int k = 0; k < J.count; ++k) {
+      const int i = begin + k;
+      GSB_REQUIRE(src[i] && dst[i] && d0[i] > 0 && d1[i] > 0 && taps[i] > 0, "layout_multi: bad job %d", i);
+      J.src[k] = src[i]; J.dst[k] = dst[i];
+      J.d0[k] = d0[i]; J.d1[k] = d1[i]; J.taps[k] = taps[i];
+      J.rows_from_d0[k] = (uint8_t)(rows_from_d0[i] != 0);
+      J.blk0[k] = blocks;
+      const int64_t total = (int64_t)d0[i] * d1[i] * taps[i];
+      blocks += (int)((total + kLayoutPerBlock - 1) / kLayoutPerBlock);
+    }
+    J.blk0[J.count] = blocks;
+    if (blocks == 0) continue;
+    if (pack) pack_weight_multi_kernel<<<blocks, 256, 0, st>>>(J);
+    else unpack_wgrad_multi_kernel<<<blocks, 256, 0, st>>>(J);
+    ++launches;
+  }
+  return check_launch(pack ? "pack_weight_multi" : "unpack_wgrad_multi", launches > 0 ? launches : 1);
+}
+}  // namespace gsb
+
+extern "C" int gsb_pack_weight_multi(int n, const void* const* src, void* const* dst, const int* d0, const int* d1,
+                                     const int* taps, const int* rows_from_d0, int dst_dtype, gsb_stream s) {
+  if (n <= 0) return 0;
+  GSB_REQUIRE(src && dst && d0 && d1 && taps && rows_from_d0, "pack_weight_multi: null argument");
+  return gsb::run_layout_multi(true, n, src, dst, d0, d1, taps, rows_from_d0, dst_dtype, 0, gsb::to_stream(s));
+}
+
+extern "C" int gsb_unpack_wgrad_multi(int n, const void* const* src, void* const* dst, const int* d0, const int* d1,
+                                      const int* taps, const int* rows_from_d0, int accumulate, gsb_stream s) {
+  if (n <= 0) return 0;
+  GSB_REQUIRE(src && dst && d0 && d1 && taps && rows_from_d0, "unpack_wgrad_multi: null argument");
+  return gsb::run_layout_multi(false, n, src, dst, d0, d1, taps, rows_from_d0, GSB_F32, accumulate, gsb::to_stream(s));
+}

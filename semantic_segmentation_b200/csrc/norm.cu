@@ -11,7 +11,11 @@
 namespace gsb {
 
 constexpr int kThreads = 256;
-constexpr int kUnroll = 2;  // pixels in flight per thread (memory-level parallelism)
+constexpr int kUnroll = 2;     // pixels in flight per thread (memory-level parallelism)
+#ifndef GSB_BN_BWD_UNROLL
+#define GSB_BN_BWD_UNROLL 1
+#endif
+constexpr int kUnrollBwd = GSB_BN_BWD_UNROLL;  // backward kernels read two tensors: fewer registers, more resident warps
 
 struct PixView {  // pixel-linear view
   void* ptr;
@@ -68,6 +72,7 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
     PixView x, PixView dA1, PixView dA2, int64_t P, int C, const float* __restrict__ scale,
     const float* __restrict__ shift, const float* __restrict__ mean, const float* __restrict__ invstd, int act1,
     int act2, uint64_t drop_seed, const uint8_t* __restrict__ drop_mask, float* __restrict__ partial) {
+  constexpr int KU = MODE == 1 ? kUnrollBwd : kUnroll;
   extern __shared__ float red[];  // [lanes][2][C]
   const int G = C >> 3;
   const int lanes = kThreads / G;
@@ -87,10 +92,10 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
   const bool two = FAST ? false : (dA2.ptr != nullptr);
   if (FAST) { act1 = GSB_ACT_RELU; act2 = GSB_ACT_NONE; }
   const int64_t step = (int64_t)gridDim.x * lanes;
-  for (int64_t p0 = (int64_t)blockIdx.x * lanes + lane; p0 < P; p0 += step * kUnroll) {
-    float v[kUnroll][8], a[kUnroll][8], b[kUnroll][8];
+  for (int64_t p0 = (int64_t)blockIdx.x * lanes + lane; p0 < P; p0 += step * KU) {
+    float v[KU][8], a[KU][8], b[KU][8];
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u)
+    for (int u = 0; u < KU; ++u)
       if (p0 + u * step < P) {
         load8<T>(x, p0 + u * step, c0, v[u]);
         if (MODE == 1) {
@@ -99,7 +104,7 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
         }
       }
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
+    for (int u = 0; u < KU; ++u) {
       const int64_t p = p0 + u * step;
       if (p >= P) break;
       if (MODE == 0) {
@@ -268,16 +273,16 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
       m1[i] = A;
       m0[i] = -sc[i] * m0[i] - A * mu[i];
     }
-    for (int64_t p0 = (int64_t)blockIdx.x * lanes + lane; p0 < P; p0 += step * kUnroll) {
-      float v[kUnroll][8], a[kUnroll][8];
+    for (int64_t p0 = (int64_t)blockIdx.x * lanes + lane; p0 < P; p0 += step * kUnrollBwd) {
+      float v[kUnrollBwd][8], a[kUnrollBwd][8];
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u)
+      for (int u = 0; u < kUnrollBwd; ++u)
         if (p0 + u * step < P) {
           load8<T>(x, p0 + u * step, c0, v[u]);
           load8<T>(dA1, p0 + u * step, c0, a[u]);
         }
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
+      for (int u = 0; u < kUnrollBwd; ++u) {
         const int64_t p = p0 + u * step;
         if (p >= P) break;
         float o[8];
@@ -292,17 +297,17 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
     }
     return;
   }
-  for (int64_t p0 = (int64_t)blockIdx.x * lanes + lane; p0 < P; p0 += step * kUnroll) {
-    float v[kUnroll][8], a[kUnroll][8], b[kUnroll][8];
+  for (int64_t p0 = (int64_t)blockIdx.x * lanes + lane; p0 < P; p0 += step * kUnrollBwd) {
+    float v[kUnrollBwd][8], a[kUnrollBwd][8], b[kUnrollBwd][8];
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u)
+    for (int u = 0; u < kUnrollBwd; ++u)
       if (p0 + u * step < P) {
         load8<T>(x, p0 + u * step, c0, v[u]);
         load8<T>(dA1, p0 + u * step, c0, a[u]);
         if (two) load8<T>(dA2, p0 + u * step, c0, b[u]);
       }
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
+    for (int u = 0; u < kUnrollBwd; ++u) {
       const int64_t p = p0 + u * step;
       if (p >= P) break;
       float o[8];

@@ -72,3 +72,133 @@ extern "C" int gsb_adam_step(float* p, const float* g, float* exp_avg, float* ex
                                                        weight_decay, (float)(1.0 / sqrt(bc2)), grad_scale);
   return check_launch("adam_step");
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Multi-tensor variants: every parameter tensor of a network in ONE launch (block -> (tensor, chunk) table in the
+// kernel parameters) instead of one 5 us launch per tensor (56 per U-Net step).
+// ---------------------------------------------------------------------------------------------------------
+namespace gsb {
+constexpr int kMaxOptJobs = 48;
+constexpr int kOptPerBlock = 256 * 8;
+struct OptJobs {
+  float* p[kMaxOptJobs];
+  const float* g[kMaxOptJobs];
+  float* s1[kMaxOptJobs];
+  float* s2[kMaxOptJobs];
+  int64_t n[kMaxOptJobs];
+  int blk0[kMaxOptJobs + 1];
+  int count;
+};
+__device__ __forceinline__ int opt_find_job(const int* blk0, int count, int b) {
+  int lo = 0, hi = count - 1;
+  while (lo < hi) {
+    int mid = (lo + hi + 1) >> 1;
+    if (blk0[mid] <= b) lo = mid; else hi = mid - 1;
+  }
+  return lo;
+}
+
+__global__ void __launch_bounds__(256) rmsprop_multi_kernel(const __grid_constant__ OptJobs J, float lr, float alpha, float eps,
+                                                           float wd, float momentum, float gscale) {
+  const int j = opt_find_job(J.blk0, J.count, blockIdx.x);
+  float* __restrict__ p = J.p[j];
+  const float* __restrict__ g = J.g[j];
+  float* __restrict__ sq = J.s1[j];
+  float* __restrict__ buf = J.s2[j];
+  const int64_t n = J.n[j], base = (int64_t)(blockIdx.x - J.blk0[j]) * kOptPerBlock;
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+    const int64_t i = base + u * 256 + threadIdx.x;
+    if (i < n) {
+      float w = p[i];
+      float gr = g[i] * gscale;
+      if (wd != 0.f) gr = fmaf(wd, w, gr);
+      float s = alpha * sq[i] + (1.f - alpha) * gr * gr;
+      sq[i] = s;
+      float avg = sqrtf(s) + eps;
+      if (momentum > 0.f) {
+        float b = momentum * buf[i] + gr / avg;
+        buf[i] = b;
+        p[i] = w - lr * b;
+      } else {
+        p[i] = w - lr * gr / avg;
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) adam_multi_kernel(const __grid_constant__ OptJobs J, float step_size, float beta1,
+                                                        float beta2, float eps, float wd, float inv_sqrt_bc2, float gscale) {
+  const int j = opt_find_job(J.blk0, J.count, blockIdx.x);
+  float* __restrict__ p = J.p[j];
+  const float* __restrict__ g = J.g[j];
+  float* __restrict__ m = J.s1[j];
+  float* __restrict__ v = J.s2[j];
+  const int64_t n = J.n[j], base = (int64_t)(blockIdx.x - J.blk0[j]) * kOptPerBlock;
+#pragma unroll
+  for (int u = 0; u < 8; ++u) {
+    const int64_t i = base + u * 256 + threadIdx.x;
+    if (i < n) {
+      float w = p[i];
+      float gr = g[i] * gscale;
+      if (wd != 0.f) gr = fmaf(wd, w, gr);
+      float mi = beta1 * m[i] + (1.f - beta1) * gr;
+      float vi = beta2 * v[i] + (1.f - beta2) * gr * gr;
+      m[i] = mi;
+      v[i] = vi;
+      float denom = sqrtf(vi) * inv_sqrt_bc2 + eps;
+      p[i] = w - step_size * (mi / denom);
+    }
+  }
+}
+
+template <typename F>
+static int run_opt_multi(int n, float* const* p, const float* const* g, float* const* s1, float* const* s2, const int64_t* numel,
+                         bool need_s2, const char* what, F launch) {
+  int launches = 0;
+  for (int begin = 0; begin < n; begin += kMaxOptJobs) {
+    OptJobs J;
+    memset(&J, 0, sizeof(J));
+    J.count = n - begin < kMaxOptJobs ? n - begin : kMaxOptJobs;
+    int blocks = 0;
+    for (int k = 0; k < J.count; ++k) {
+      const int i = begin + k;
+      GSB_REQUIRE(p[i] && g[i] && s1[i] && (!need_s2 || s2[i]) && numel[i] >= 0, "%s: bad tensor %d", what, i);
+      J.p[k] = p[i]; J.g[k] = g[i]; J.s1[k] = s1[i]; J.s2[k] = s2 ? s2[i] : nullptr;
+      J.n[k] = numel[i];
+      J.blk0[k] = blocks;
+      blocks += (int)((numel[i] + kOptPerBlock - 1) / kOptPerBlock);
+    }
+    J.blk0[J.count] = blocks;
+    if (blocks == 0) continue;
+    launch(J, blocks);
+    ++launches;
+  }
+  return check_launch(what, launches > 0 ? launches : 1);
+}
+}  // namespace gsb
+
+extern "C" int gsb_rmsprop_step_multi(int n, float* const* p, const float* const* g, float* const* square_avg,
+                                      float* const* mom_buf, const int64_t* numel, float lr, float alpha, float eps,
+                                      float weight_decay, float momentum, float grad_scale, gsb_stream s) {
+  if (n <= 0) return 0;
+  GSB_REQUIRE(p && g && square_avg && numel && (momentum == 0.f || mom_buf), "rmsprop_step_multi: null argument");
+  cudaStream_t st = gsb::to_stream(s);
+  return gsb::run_opt_multi(n, p, g, square_avg, mom_buf, numel, momentum != 0.f, "rmsprop_step_multi",
+                            [&](const gsb::OptJobs& J, int blocks) {
+                              gsb::rmsprop_multi_kernel<<<blocks, 256, 0, st>>>(J, lr, alpha, eps, weight_decay, momentum, grad_scale);
+                            });
+}
+
+extern "C" int gsb_adam_step_multi(int n, float* const* p, const float* const* g, float* const* exp_avg, float* const* exp_avg_sq,
+                                   const int64_t* numel, float lr, float beta1, float beta2, float eps, float weight_decay,
+                                   int64_t step, float grad_scale, gsb_stream s) {
+  if (n <= 0) return 0;
+  GSB_REQUIRE(p && g && exp_avg && exp_avg_sq && numel && step >= 1, "adam_step_multi: bad argument");
+  double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
+  cudaStream_t st = gsb::to_stream(s);
+  const float step_size = (float)(lr / bc1), isb = (float)(1.0 / sqrt(bc2));
+  return gsb::run_opt_multi(n, p, g, exp_avg, exp_avg_sq, numel, true, "adam_step_multi", [&](const gsb::OptJobs& J, int blocks) {
+    gsb::adam_multi_kernel<<<blocks, 256, 0, st>>>(J, step_size, beta1, beta2, eps, weight_decay, isb, grad_scale);
+  });
+}

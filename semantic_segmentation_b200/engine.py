@@ -117,6 +117,62 @@ def _nhwc_empty(n: int, h: int, w: int, c: int, device, dtype=None, zero: bool =
     return f((n, h, w, c), device=device, dtype=dtype or act_dtype())
 
 
+class WeightPacks:
+    """Packs the conv weights of a whole network (forward layout and, for training, the transposed backward layout)
+    in ONE launch instead of two per layer."""
+
+    def __init__(self):
+        self.jobs, self.map = [], {}
+
+    def add(self, key: str, spec: "ConvSpec", weight: torch.Tensor, need_bwd: bool) -> None:
+        w = weight.detach().contiguous()
+        taps = spec.k * spec.k
+        conv = spec.kind == "conv"
+        # forward layout [taps, cout, cin]; backward layout [taps, cin, cout]
+        wp = torch.empty((taps, spec.cout, spec.cin), device=w.device, dtype=act_dtype())
+        self.jobs.append((w, conv, wp))
+        wpb = None
+        if need_bwd:
+            wpb = torch.empty((taps, spec.cin, spec.cout), device=w.device, dtype=act_dtype())
+            self.jobs.append((w, not conv, wpb))
+        self.map[key] = (wp, wpb)
+
+    def run(self) -> None:
+        ops.pack_weight_multi(self.jobs, act_dtype())
+        self.jobs = []
+
+    def get(self, key: str):
+        return self.map.get(key, (None, None))
+
+
+class BackwardBatch:
+    """Shared zero-initialised weight-gradient workspace (one fill) + deferred, batched un-packing (one launch)."""
+
+    def __init__(self, device, sizes: Dict[str, int]):
+        total = sum(sizes.values())
+        self.flat = torch.zeros(max(total, 1), device=device, dtype=torch.float32)
+        self.offsets, off = {}, 0
+        for k, n in sizes.items():
+            self.offsets[k] = (off, n)
+            off += n
+        self.jobs = []
+
+    def dwp(self, key: str, shape) -> Optional[torch.Tensor]:
+        if key not in self.offsets:
+            return None
+        off, n = self.offsets[key]
+        return self.flat[off:off + n].view(shape)
+
+    def defer_unpack(self, dwp: torch.Tensor, weight_shape, rows_from_d0: bool) -> torch.Tensor:
+        out = torch.empty(weight_shape, device=dwp.device, dtype=torch.float32)
+        self.jobs.append((dwp, rows_from_d0, out))
+        return out
+
+    def flush(self) -> None:
+        ops.unpack_wgrad_multi(self.jobs)
+        self.jobs = []
+
+
 def _is_stem(s: "ConvSpec", x_view: GsbView, x_keep) -> bool:
     return (s.kind == "conv" and s.cin <= 4 and s.cin * s.k * s.k <= 64 and s.cout % 8 == 0 and s.cout <= 256
             and 256 % (s.cout // 8) == 0 and isinstance(x_keep, torch.Tensor) and x_keep.dim() == 4
@@ -137,7 +193,7 @@ class ConvBNAct:
     # x_view: GsbView of the input (NHWC act buffer or the NCHW fp32 network input)
     def forward(self, x_view: GsbView, x_keep, n: int, h: int, w: int, device, weight, bias, bn, training: bool,
                 out1: Optional[torch.Tensor] = None, out2: Optional[torch.Tensor] = None, save: bool = True,
-                drop_seed: int = 0, drop_mask: Optional[torch.Tensor] = None):
+                drop_seed: int = 0, drop_mask: Optional[torch.Tensor] = None, packed=None):
         s = self.spec
         oh, ow = s.out_hw(h, w)
         y = _nhwc_empty(n, oh, ow, s.cout, device)
@@ -146,7 +202,7 @@ class ConvBNAct:
             stats, rows = ops.stem_conv_fwd(x_keep, weight.detach().contiguous(), bias, y, s.k, s.stride, s.pad,
                                             want_stats=self.has_bn and training and _CONFIG["fused_stats"])
         else:
-            wp = s.pack_fwd(weight)
+            wp = packed[0] if packed is not None and packed[0] is not None else s.pack_fwd(weight)
             want_stats = (self.has_bn and training and _CONFIG["fused_stats"]
                           and not (s.kind == "convT" and s.stride > 1))
             stats, rows = ops.conv_gather(x_view, wp, bias, view_nhwc(y), s.fwd_mode, s.k, s.stride, s.pad,
@@ -178,10 +234,12 @@ class ConvBNAct:
             sv.drop_mask = drop_mask if use_drop else None
             sv.extra["train_bn"] = self.has_bn and training
             sv.extra["stem"] = stem
+            sv.extra["wpb"] = packed[1] if packed is not None else None
         return out1, sv
 
     def backward(self, sv: Saved, dA1: torch.Tensor, dA2: Optional[torch.Tensor], need_dx: bool, need_dw: bool,
-                 need_bn: bool, need_db: bool, dx_out: Optional[torch.Tensor] = None, dx_view: Optional[GsbView] = None):
+                 need_bn: bool, need_db: bool, dx_out: Optional[torch.Tensor] = None, dx_view: Optional[GsbView] = None,
+                 batch: Optional["BackwardBatch"] = None, key: Optional[str] = None):
         """Returns (dx, dweight, dbias, dgamma, dbeta).  dx is written to dx_out / dx_view when given."""
         s = self.spec
         y = sv.y
@@ -212,15 +270,22 @@ class ConvBNAct:
         if need_dw and sv.extra.get("stem"):
             dweight = ops.stem_conv_wgrad(sv.x_keep, dY, s.k, s.stride, s.pad)
         elif need_dw:
-            dwp = torch.zeros((s.k * s.k, s.cout, s.cin), device=device, dtype=torch.float32)
+            dwp = batch.dwp(key, (s.k * s.k, s.cout, s.cin)) if batch is not None and key is not None else None
+            if dwp is None:
+                dwp = torch.zeros((s.k * s.k, s.cout, s.cin), device=device, dtype=torch.float32)
             ops.conv_wgrad_into(sv.x_view, dyv, dwp, s.fwd_mode, s.k, s.stride, s.pad, use_tc=_CONFIG["use_tc"])
-            dweight = ops.unpack_wgrad(dwp, s.weight_shape(), s.kind == "conv")
+            if batch is not None:
+                dweight = batch.defer_unpack(dwp, s.weight_shape(), s.kind == "conv")
+            else:
+                dweight = ops.unpack_wgrad(dwp, s.weight_shape(), s.kind == "conv")
         if need_db:
             dbias = torch.zeros(s.cout, device=device, dtype=torch.float32)
             ops.bias_grad(dyv, dbias)
         dx = None
         if need_dx:
-            wpb = s.pack_bwd(sv.weight)
+            wpb = sv.extra.get("wpb")
+            if wpb is None:
+                wpb = s.pack_bwd(sv.weight)
             if dx_view is None:
                 if dx_out is None:
                     xv = sv.x_view

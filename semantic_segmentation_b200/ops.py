@@ -68,6 +68,43 @@ def unpack_wgrad(dwp: torch.Tensor, shape: Tuple[int, int, int, int], rows_from_
     return out
 
 
+def _ptr_array(ts):
+    return (C.c_void_p * len(ts))(*[t.data_ptr() for t in ts])
+
+
+def _int_array(vs):
+    return (C.c_int * len(vs))(*[int(v) for v in vs])
+
+
+def pack_weight_multi(jobs, dtype: torch.dtype) -> None:
+    """jobs: [(w fp32 [d0,d1,kh,kw], rows_from_d0, out [kh*kw, rows, cols] in dtype)] -- one launch for all of them."""
+    if not jobs:
+        return
+    ws = [j[0] for j in jobs]
+    for w, _, out in jobs:
+        assert w.dtype == torch.float32 and w.is_contiguous() and out.dtype == dtype and out.is_contiguous()
+        L.require_cuda(w)
+    check(load().gsb_pack_weight_multi(len(jobs), _ptr_array(ws), _ptr_array([j[2] for j in jobs]),
+                                       _int_array([w.shape[0] for w in ws]), _int_array([w.shape[1] for w in ws]),
+                                       _int_array([w.shape[2] * w.shape[3] for w in ws]),
+                                       _int_array([int(j[1]) for j in jobs]), L.dtype_code(dtype), _s(ws[0])),
+          "pack_weight_multi")
+
+
+def unpack_wgrad_multi(jobs) -> None:
+    """jobs: [(dwp fp32 [kh*kw, rows, cols], rows_from_d0, out fp32 [d0,d1,kh,kw])] -- one launch."""
+    if not jobs:
+        return
+    outs = [j[2] for j in jobs]
+    for dwp, _, out in jobs:
+        assert dwp.dtype == torch.float32 and out.dtype == torch.float32 and dwp.is_contiguous() and out.is_contiguous()
+        L.require_cuda(out)
+    check(load().gsb_unpack_wgrad_multi(len(jobs), _ptr_array([j[0] for j in jobs]), _ptr_array(outs),
+                                        _int_array([t.shape[0] for t in outs]), _int_array([t.shape[1] for t in outs]),
+                                        _int_array([t.shape[2] * t.shape[3] for t in outs]),
+                                        _int_array([int(j[1]) for j in jobs]), 0, _s(outs[0])), "unpack_wgrad_multi")
+
+
 def merge_upconv(w4, w6, w8, b4, b6, b8, alpha_row: torch.Tensor):
     cin, cout = w8.shape[0], w8.shape[1]
     wm = torch.empty_like(w8)
@@ -337,6 +374,23 @@ def act_bwd(out: torch.Tensor, dout: torch.Tensor, act: int) -> torch.Tensor:
 def rmsprop_step(p, g, square_avg, mom_buf, lr, alpha, eps, weight_decay, momentum, grad_scale=1.0) -> None:
     check(load().gsb_rmsprop_step(ptr(p), ptr(g), ptr(square_avg), ptr(mom_buf), p.numel(), lr, alpha, eps,
                                   weight_decay, momentum, grad_scale, _s(p)), "rmsprop_step")
+
+
+def rmsprop_step_multi(ps, gs, sqs, bufs, lr, alpha, eps, weight_decay, momentum, grad_scale=1.0) -> None:
+    if not ps:
+        return
+    n = (C.c_int64 * len(ps))(*[p.numel() for p in ps])
+    check(load().gsb_rmsprop_step_multi(len(ps), _ptr_array(ps), _ptr_array(gs), _ptr_array(sqs),
+                                        _ptr_array(bufs) if momentum > 0 else None, n, lr, alpha, eps, weight_decay, momentum,
+                                        grad_scale, _s(ps[0])), "rmsprop_step_multi")
+
+
+def adam_step_multi(ps, gs, ms, vs, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0) -> None:
+    if not ps:
+        return
+    n = (C.c_int64 * len(ps))(*[p.numel() for p in ps])
+    check(load().gsb_adam_step_multi(len(ps), _ptr_array(ps), _ptr_array(gs), _ptr_array(ms), _ptr_array(vs), n, lr, beta1,
+                                     beta2, eps, weight_decay, int(step), grad_scale, _s(ps[0])), "adam_step_multi")
 
 
 def adam_step(p, g, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0) -> None:

@@ -35,15 +35,20 @@ class RMSprop(_Base):
 
     @torch.no_grad()
     def step(self) -> None:
+        ps, gs, sqs, bufs = [], [], [], []
         for p in self.params:
             if p.grad is None:
                 continue
             st = self.state.get(p)
             if st is None:
                 st = self.state[p] = (torch.zeros_like(p), torch.zeros_like(p) if self.momentum > 0 else None)
-            g = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
-            ops.rmsprop_step(p.data, g, st[0], st[1], self.lr, self.alpha, self.eps, self.weight_decay, self.momentum,
-                             self.grad_scale)
+            ps.append(p.data)
+            gs.append(p.grad if p.grad.is_contiguous() else p.grad.contiguous())
+            sqs.append(st[0])
+            bufs.append(st[1])
+        # one launch over every parameter tensor (multi-tensor kernel)
+        ops.rmsprop_step_multi(ps, gs, sqs, bufs, self.lr, self.alpha, self.eps, self.weight_decay, self.momentum,
+                               self.grad_scale)
 
 
 class Adam(_Base):
@@ -55,12 +60,16 @@ class Adam(_Base):
     @torch.no_grad()
     def step(self) -> None:
         self.t += 1
+        ps, gs, ms, vs = [], [], [], []
         for p in self.params:
             if p.grad is None:
                 continue
             st = self.state.get(p)
             if st is None:
                 st = self.state[p] = (torch.zeros_like(p), torch.zeros_like(p))
-            g = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
-            ops.adam_step(p.data, g, st[0], st[1], self.lr, self.betas[0], self.betas[1], self.eps, self.weight_decay,
-                          self.t, self.grad_scale)
+            ps.append(p.data)
+            gs.append(p.grad if p.grad.is_contiguous() else p.grad.contiguous())
+            ms.append(st[0])
+            vs.append(st[1])
+        ops.adam_step_multi(ps, gs, ms, vs, self.lr, self.betas[0], self.betas[1], self.eps, self.weight_decay, self.t,
+                            self.grad_scale)

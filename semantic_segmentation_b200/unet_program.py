@@ -15,7 +15,7 @@ import torch
 
 from . import ops
 from ._lib import ACT_NONE, ACT_RELU, view_nchw, view_nhwc
-from .engine import ConvBNAct, ConvSpec, EdgeConv, Saved, _nhwc_empty, act_dtype
+from .engine import BackwardBatch, ConvBNAct, ConvSpec, EdgeConv, Saved, WeightPacks, _nhwc_empty, act_dtype
 
 
 def unet_param_names(n_channels: int, n_classes: int, bilinear: bool) -> List[str]:
@@ -52,25 +52,32 @@ class DoubleConvOps:
         return (P[p + ".weight"], P[p + ".bias"], B[p + ".running_mean"], B[p + ".running_var"],
                 B[p + ".num_batches_tracked"])
 
-    def forward(self, x_view, x_keep, n, h, w, device, P, B, training, save, out=None):
+    def conv_layers(self):
         p = self.prefix + ".double_conv"
+        return [(p + ".0.weight", self.c0.spec), (p + ".3.weight", self.c1.spec)]
+
+    def forward(self, x_view, x_keep, n, h, w, device, P, B, training, save, out=None, packs=None):
+        p = self.prefix + ".double_conv"
+        pk0 = packs.get(p + ".0.weight") if packs is not None else None
+        pk1 = packs.get(p + ".3.weight") if packs is not None else None
         a0, s0 = self.c0.forward(x_view, x_keep, n, h, w, device, P[p + ".0.weight"], None, self._bn(P, B, 1),
-                                 training, save=save)
+                                 training, save=save, packed=pk0)
         a1, s1 = self.c1.forward(view_nhwc(a0), a0, n, h, w, device, P[p + ".3.weight"], None, self._bn(P, B, 4),
-                                 training, out1=out, save=save)
+                                 training, out1=out, save=save, packed=pk1)
         return a1, (s0, s1)
 
     def backward(self, saved, dA, G: Dict[str, torch.Tensor], need: Dict[str, bool], need_dx: bool,
-                 dx_out=None, dx_view=None):
+                 dx_out=None, dx_view=None, batch=None):
         s0, s1 = saved
         p = self.prefix + ".double_conv"
         nw1, nb1 = need.get(p + ".3.weight", False), need.get(p + ".4.weight", False) or need.get(p + ".4.bias", False)
-        d0, dw, _, dg, db = self.c1.backward(s1, dA, None, True, nw1, nb1, False)
+        d0, dw, _, dg, db = self.c1.backward(s1, dA, None, True, nw1, nb1, False, batch=batch, key=p + ".3.weight")
         _put(G, p + ".3.weight", dw)
         _put(G, p + ".4.weight", dg)
         _put(G, p + ".4.bias", db)
         nw0, nb0 = need.get(p + ".0.weight", False), need.get(p + ".1.weight", False) or need.get(p + ".1.bias", False)
-        dx, dw, _, dg, db = self.c0.backward(s0, d0, None, need_dx, nw0, nb0, False, dx_out=dx_out, dx_view=dx_view)
+        dx, dw, _, dg, db = self.c0.backward(s0, d0, None, need_dx, nw0, nb0, False, dx_out=dx_out, dx_view=dx_view,
+                                             batch=batch, key=p + ".0.weight")
         _put(G, p + ".0.weight", dw)
         _put(G, p + ".1.weight", dg)
         _put(G, p + ".1.bias", db)
@@ -128,8 +135,16 @@ class UNetProgram:
             hh, ww = sizes[k]
             need_zero = (2 * sizes[k + 1][0] != hh) or (2 * sizes[k + 1][1] != ww)
             cats.append(_nhwc_empty(n, hh, ww, ck + up_c, dev, zero=need_zero and not self.bilinear))
+        # every tensor-core conv weight packed (forward + backward layouts) in one launch
+        packs = WeightPacks()
+        stem_key = "inc.double_conv.0.weight" if self.n_channels <= 4 else None
+        for blk in [self.inc] + self.downs + self.ups:
+            for key, spec in blk.conv_layers():
+                if key != stem_key:
+                    packs.add(key, spec, P[key], need_bwd=save)
+        packs.run()
         # encoder
-        x1, sv = self.inc.forward(view_nchw(x), x, n, h, w, dev, P, B, training, save, out=cats[0][..., :64])
+        x1, sv = self.inc.forward(view_nchw(x), x, n, h, w, dev, P, B, training, save, out=cats[0][..., :64], packs=packs)
         tape["inc"] = sv
         skips = [x1]
         cur = x1
@@ -137,7 +152,8 @@ class UNetProgram:
             pooled = ops.maxpool2_fwd(cur)
             hh, ww = sizes[i + 1]
             out = cats[i + 1][..., :self.chans[i + 1]] if i < 3 else None
-            cur, sv = self.downs[i].forward(view_nhwc(pooled), pooled, n, hh, ww, dev, P, B, training, save, out=out)
+            cur, sv = self.downs[i].forward(view_nhwc(pooled), pooled, n, hh, ww, dev, P, B, training, save, out=out,
+                                            packs=packs)
             tape[f"down{i + 1}"] = sv
             skips.append(cur)
         tape["skips"] = skips if save else None
@@ -164,7 +180,7 @@ class UNetProgram:
                     ops.copy_view(view_nhwc(o1), view_nhwc(window), torch.cuda.current_stream(dev).cuda_stream)
                 tape[name] = sv
             tape[f"up{i + 1}.pad"] = (pad_t, pad_l)
-            cur, sv = self.ups[i].forward(view_nhwc(cat), cat, n, hh, ww, dev, P, B, training, save)
+            cur, sv = self.ups[i].forward(view_nhwc(cat), cat, n, hh, ww, dev, P, B, training, save, packs=packs)
             tape[f"up{i + 1}"] = sv
         logits, sv = self.outc.forward(cur, P["outc.conv.weight"], P["outc.conv.bias"], save)
         tape["outc"] = sv
@@ -178,6 +194,13 @@ class UNetProgram:
         skips = tape["skips"]
         n = dlogits.shape[0]
         dev = dlogits.device
+        sizes_w = {}
+        stem_key = "inc.double_conv.0.weight" if self.n_channels <= 4 else None
+        for blk in [self.inc] + self.downs + self.ups:
+            for key, spec in blk.conv_layers():
+                if key != stem_key and need.get(key, False):
+                    sizes_w[key] = spec.k * spec.k * spec.cout * spec.cin
+        batch = BackwardBatch(dev, sizes_w)
         dcur, dw, db = self.outc.backward(tape["outc"], dlogits, True, need.get("outc.conv.weight", False),
                                           need.get("outc.conv.bias", False))
         _put(G, "outc.conv.weight", dw)
@@ -189,7 +212,7 @@ class UNetProgram:
             hh, ww = sizes[lvl]
             c_cat = tape[f"up{i + 1}"][0].x_view.c
             dcat = _nhwc_empty(n, hh, ww, c_cat, dev)
-            self.ups[i].backward(tape[f"up{i + 1}"], dcur, G, need, True, dx_out=dcat)
+            self.ups[i].backward(tape[f"up{i + 1}"], dcur, G, need, True, dx_out=dcat, batch=batch)
             dskip[lvl] = dcat[..., :c_skip]
             dupper = dcat[..., c_skip:]
             pad_t, pad_l = tape[f"up{i + 1}.pad"]
@@ -213,7 +236,7 @@ class UNetProgram:
             dcur = dprev
         # encoder: dcur = d x5
         for i in range(3, -1, -1):
-            dpooled = self.downs[i].backward(tape[f"down{i + 1}"], dcur, G, need, True)
+            dpooled = self.downs[i].backward(tape[f"down{i + 1}"], dcur, G, need, True, batch=batch)
             # route through the 2x2 max-pool into the skip gradient already holding the concat part
             ops.maxpool2_bwd(skips[i], dpooled, dskip[i], accumulate=True)
             dcur = dskip[i]
@@ -222,5 +245,6 @@ class UNetProgram:
         if need_dx:
             dx = torch.empty_like(tape["x"])
             dxv = view_nchw(dx)
-        self.inc.backward(tape["inc"], dcur, G, need, need_dx, dx_view=dxv, dx_out=dx)
+        self.inc.backward(tape["inc"], dcur, G, need, need_dx, dx_view=dxv, dx_out=dx, batch=batch)
+        batch.flush()
         return dx, G

@@ -12,7 +12,7 @@ fi
 timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench_$TAG.log 2>&1; echo "bench rc=$?"; tail -2 gpurun_out/bench_$TAG.log
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref_$TAG.log 2>&1; echo "ref rc=$?"; tail -1 gpurun_out/bench_ref_$TAG.log
 if [ -z "$SKIP_NCU" ]; then
-CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline"
+CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-graph"
 timeout 600 $CMD > gpurun_out/plain_$TAG.log 2>&1 &&
 timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv \
     --log-file gpurun_out/launches_$TAG.csv $CMD > gpurun_out/ncu_list_$TAG.log 2>&1
