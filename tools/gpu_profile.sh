@@ -17,7 +17,7 @@ timeout 600 $CMD > gpurun_out/plain_$TAG.log 2>&1 &&
 timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv \
     --log-file gpurun_out/launches_$TAG.csv $CMD > gpurun_out/ncu_list_$TAG.log 2>&1
 echo "ncu list rc=$?"
-for K in ${NCU_KERNELS:-conv_tc_fprop conv_tc_wgrad}; do
+for K in ${NCU_KERNELS:-conv_tc_halo_kernel}; do
 timeout 600 $CMD > gpurun_out/plain2_$TAG.log 2>&1 &&
 timeout 1500 ncu --set full --clock-control none --import-source on --profile-from-start off \
     -k regex:"$K" -s ${NCU_SKIP:-0} -c ${NCU_COUNT:-4} -f -o gpurun_out/prof_${TAG}_$K $CMD > gpurun_out/ncu_full_${TAG}_$K.log 2>&1
