@@ -217,6 +217,125 @@ __global__ void __launch_bounds__(256) upsample2_bwd_kernel(const T* __restrict_
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Row-blocked bilinear kernels: one block per output (fwd) / input (bwd) row.  The horizontal lerp table is built
+// once per block in shared memory, the vertical lerp once per row, the item -> (x, channel group) split is a
+// 32-bit division: ~2x fewer instructions per 16-byte item than the flat kernels above, which are issue-bound
+// (profiles/r01j: 0.66 + 0.92 ms per step against ~0.4 ms of HBM time).  Same arithmetic, same summation order.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kMaxUpW = 2048;
+
+template <typename T>
+__global__ void __launch_bounds__(256) upsample2_fwd_rows_kernel(const T* __restrict__ x, int64_t xld, int N, int h, int w, int C,
+                                                                T* __restrict__ out, int64_t old, int OH, int OW, int pad_top,
+                                                                int pad_left) {
+  __shared__ int s_i0[kMaxUpW], s_i1[kMaxUpW];
+  __shared__ float s_l1[kMaxUpW];
+  for (int u = threadIdx.x; u < 2 * w; u += blockDim.x) {
+    Lerp l = lerp_for(u, w, 2 * w);
+    s_i0[u] = l.i0; s_i1[u] = l.i1; s_l1[u] = l.l1;
+  }
+  __syncthreads();
+  const unsigned G = (unsigned)C >> 3, items = (unsigned)OW * G;
+  for (int row = blockIdx.x; row < N * OH; row += gridDim.x) {
+    const int n = row / OH, oy = row - n * OH;
+    const int uy = oy - pad_top;
+    const bool rowvalid = uy >= 0 && uy < 2 * h;
+    Lerp ly = lerp_for(rowvalid ? uy : 0, h, 2 * h);
+    const T* r0 = x + ((int64_t)n * h + ly.i0) * w * xld;
+    const T* r1 = x + ((int64_t)n * h + ly.i1) * w * xld;
+    T* orow = out + (int64_t)row * OW * old;
+    for (unsigned it = threadIdx.x; it < items; it += blockDim.x) {
+      const unsigned ox = it / G, g = it - ox * G;
+      const int ux = (int)ox - pad_left;
+      float o[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      if (rowvalid && ux >= 0 && ux < 2 * w) {
+        const int i0 = s_i0[ux], i1 = s_i1[ux];
+        const float lx1 = s_l1[ux], lx0 = 1.f - lx1;
+        float v00[8], v01[8], v10[8], v11[8];
+        Vec8<T>::load(r0 + (int64_t)i0 * xld + g * 8, v00);
+        Vec8<T>::load(r0 + (int64_t)i1 * xld + g * 8, v01);
+        Vec8<T>::load(r1 + (int64_t)i0 * xld + g * 8, v10);
+        Vec8<T>::load(r1 + (int64_t)i1 * xld + g * 8, v11);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          o[k] = ly.l0 * (lx0 * v00[k] + lx1 * v01[k]) + ly.l1 * (lx0 * v10[k] + lx1 * v11[k]);
+      }
+      Vec8<T>::store(orow + (int64_t)ox * old + g * 8, o);
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) upsample2_bwd_rows_kernel(const T* __restrict__ dout, int64_t dld, int N, int OH, int OW,
+                                                                int C, T* __restrict__ dx, int64_t xld, int h, int w,
+                                                                int pad_top, int pad_left) {
+  __shared__ int s_i0[kMaxUpW], s_i1[kMaxUpW];
+  __shared__ float s_l1[kMaxUpW];
+  __shared__ int s_oy[8];
+  __shared__ float s_wy[8];
+  for (int u = threadIdx.x; u < 2 * w; u += blockDim.x) {
+    Lerp l = lerp_for(u, w, 2 * w);
+    s_i0[u] = l.i0; s_i1[u] = l.i1; s_l1[u] = l.l1;
+  }
+  const unsigned G = (unsigned)C >> 3, items = (unsigned)w * G;
+  for (int row = blockIdx.x; row < N * h; row += gridDim.x) {
+    const int n = row / h, iy = row - n * h;
+    __syncthreads();  // table ready / previous row's candidates consumed
+    if (threadIdx.x < 6) {  // contributing output rows uy in [2iy-2, 2iy+3], ascending (same order as the flat kernel)
+      const int uy = 2 * iy - 2 + (int)threadIdx.x;
+      float wy = 0.f;
+      int oy = -1;
+      if (uy >= 0 && uy < 2 * h) {
+        Lerp ly = lerp_for(uy, h, 2 * h);
+        wy = (ly.i0 == iy ? ly.l0 : 0.f) + (ly.i1 == iy ? ly.l1 : 0.f);
+        oy = uy + pad_top;
+        if (oy < 0 || oy >= OH) wy = 0.f;
+      }
+      s_oy[threadIdx.x] = oy;
+      s_wy[threadIdx.x] = wy;
+    }
+    __syncthreads();
+    for (unsigned it = threadIdx.x; it < items; it += blockDim.x) {
+      const unsigned ix = it / G, g = it - ix * G;
+      int cx[6];
+      float cw[6];
+#pragma unroll
+      for (int c = 0; c < 6; ++c) {
+        const int ux = 2 * (int)ix - 2 + c;
+        float wx = 0.f;
+        int ox = 0;
+        if (ux >= 0 && ux < 2 * w) {
+          const float l1 = s_l1[ux];
+          wx = (s_i0[ux] == (int)ix ? 1.f - l1 : 0.f) + (s_i1[ux] == (int)ix ? l1 : 0.f);
+          ox = ux + pad_left;
+          if (ox < 0 || ox >= OW) { wx = 0.f; ox = 0; }
+        }
+        cx[c] = ox;
+        cw[c] = wx;
+      }
+      float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+      for (int r = 0; r < 6; ++r) {
+        const float wy = s_wy[r];
+        if (wy == 0.f) continue;
+        const T* rowp = dout + ((int64_t)n * OH + s_oy[r]) * OW * dld + g * 8;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+          if (cw[c] != 0.f) {
+            float v[8];
+            Vec8<T>::load(rowp + (int64_t)cx[c] * dld, v);
+            const float wgt = wy * cw[c];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] = fmaf(wgt, v[k], acc[k]);
+          }
+        }
+      }
+      Vec8<T>::store(dx + ((int64_t)row * w + ix) * xld + g * 8, acc);
+    }
+  }
+}
+
 static int ew_grid(int64_t total) {
   int64_t b = (total + 255) / 256;
   int64_t cap = (int64_t)num_sms() * 16;
@@ -271,6 +390,14 @@ extern "C" int gsb_upsample2_fwd(const gsb_view* x, const gsb_view* out, int pad
   GSB_REQUIRE(out->n == x->n && out->c == x->c && out->dtype == x->dtype, "upsample2_fwd: mismatch");
   int64_t total = num_pixels(out) * (x->c / 8);
   if (total == 0) return 0;
+  if (2 * x->w <= kMaxUpW && (int64_t)out->n * out->h < ((int64_t)1 << 30)) {
+    const int rows = out->n * out->h;
+    const int grid = rows < num_sms() * 16 ? rows : num_sms() * 16;
+    DISPATCH_T(x->dtype, upsample2_fwd_rows_kernel<T><<<grid, 256, 0, to_stream(s)>>>(
+                             (const T*)x->ptr, x->sw, x->n, x->h, x->w, x->c, (T*)out->ptr, out->sw, out->h, out->w, pad_top,
+                             pad_left));
+    return check_launch("upsample2_fwd");
+  }
   DISPATCH_T(x->dtype, upsample2_fwd_kernel<T><<<ew_grid(total), 256, 0, to_stream(s)>>>(
                            (const T*)x->ptr, x->sw, x->n, x->h, x->w, x->c, (T*)out->ptr, out->sw, out->h, out->w, pad_top,
                            pad_left));
@@ -282,6 +409,14 @@ extern "C" int gsb_upsample2_bwd(const gsb_view* dout, const gsb_view* dx, int p
   GSB_REQUIRE(dout->n == dx->n && dout->c == dx->c && dout->dtype == dx->dtype, "upsample2_bwd: mismatch");
   int64_t total = num_pixels(dx) * (dx->c / 8);
   if (total == 0) return 0;
+  if (2 * dx->w <= kMaxUpW && (int64_t)dx->n * dx->h < ((int64_t)1 << 30)) {
+    const int rows = dx->n * dx->h;
+    const int grid = rows < num_sms() * 16 ? rows : num_sms() * 16;
+    DISPATCH_T(dx->dtype, upsample2_bwd_rows_kernel<T><<<grid, 256, 0, to_stream(s)>>>(
+                              (const T*)dout->ptr, dout->sw, dout->n, dout->h, dout->w, dout->c, (T*)dx->ptr, dx->sw, dx->h,
+                              dx->w, pad_top, pad_left));
+    return check_launch("upsample2_bwd");
+  }
   DISPATCH_T(dx->dtype, upsample2_bwd_kernel<T><<<ew_grid(total), 256, 0, to_stream(s)>>>(
                             (const T*)dout->ptr, dout->sw, dout->n, dout->h, dout->w, dout->c, (T*)dx->ptr, dx->sw, dx->h,
                             dx->w, pad_top, pad_left));
