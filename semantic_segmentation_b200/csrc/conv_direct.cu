@@ -271,8 +271,16 @@ __global__ void bias_grad_kernel(DView d, float* __restrict__ db) {
   }
 }
 
+int thin_gather_try(const gsb_view* in, const void* wp, int wdtype, const float* bias, const gsb_view* out,
+                    const gsb_conv_geom* g, int act, int accumulate, cudaStream_t st);
+int thin_wgrad_try(const gsb_view* in, const gsb_view* dout, float* dwp, const gsb_conv_geom* g, cudaStream_t st);
+
 int conv_gather_direct(const gsb_view* in, const void* wp, int wdtype, const float* bias, const gsb_view* out,
                        const gsb_conv_geom* g, int act, int accumulate, cudaStream_t st) {
+  {  // layers with 1..4 channels on one side: dedicated bandwidth kernels (thin_conv.cu)
+    int r = thin_gather_try(in, wp, wdtype, bias, out, g, act, accumulate, st);
+    if (r != 0) return r < 0 ? -1 : 0;
+  }
   DView vi = dv(in), vo = dv(out);
   int sub = (g->mode == GSB_MODE_CONVT && g->stride > 1) ? g->stride : 1;
   for (int py = 0; py < sub; ++py)
@@ -294,6 +302,10 @@ int conv_gather_direct(const gsb_view* in, const void* wp, int wdtype, const flo
 }
 
 int conv_wgrad_direct(const gsb_view* in, const gsb_view* dout, float* dwp, const gsb_conv_geom* g, cudaStream_t st) {
+  {
+    int r = thin_wgrad_try(in, dout, dwp, g, st);
+    if (r != 0) return r < 0 ? -1 : 0;
+  }
   DView vi = dv(in), vd = dv(dout);
   const bool conv = g->mode == GSB_MODE_CONV;
   int64_t P = conv ? num_pixels(dout) : num_pixels(in);

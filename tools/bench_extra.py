@@ -1,0 +1,116 @@
+#!/usr/bin/env python
+"""Secondary workloads of BASELINE.json (not the headline bench.py line):
+
+  config 3  Pix2Pix unet_256 generator + 70x70 PatchGAN training step (GANLoss + 100*L1), `optimize_parameters`
+            of models_pix2pix/pix2pix_model.py:132-143 restated with our modules: G fwd, D step on (fake.detach, real),
+            G step with D frozen; Adam(betas=(0.5, 0.999)) on both.
+  config 5  U-Net inference sweep (unet/evaluate.py path): eval forward + fused argmax / Dice counts at
+            (N, H) = (64,256), (16,512), (4,1024) and batch-1 latency.
+
+One JSON line per measurement; CUDA-event timing after warm-up.  Usage: python tools/bench_extra.py [--batch 8]
+"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+
+def timed(fn, steps, warm=3):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.profiler.start()   # ncu --profile-from-start off sees exactly the timed steps
+    s.record()
+    for _ in range(steps):
+        fn()
+    e.record()
+    torch.cuda.synchronize()
+    torch.cuda.profiler.stop()
+    return s.elapsed_time(e) * 1e-3 / steps
+
+
+def pix2pix(batch, steps):
+    import semantic_segmentation_b200 as S
+    from oracle import genseg_oracle as O
+    from semantic_segmentation_b200.models_pix2pix import networks
+    from semantic_segmentation_b200.optim import Adam
+    S.set_precision("bf16")
+    dev = "cuda"
+    G = networks.define_G(1, 1, 64, "unet_256", "batch", True, "normal", 0.02, [])
+    D = networks.define_D(2, 64, "basic", 3, "batch", "normal", 0.02, [])
+    G.load_state_dict(O.seeded_state(O.generator_state_spec(1, 1, 64), 11, conv_std=0.02), strict=True)
+    D.load_state_dict(O.seeded_state(O.discriminator_state_spec(2, 64), 12, conv_std=0.02), strict=True)
+    G, D = G.to(dev).train(), D.to(dev).train()
+    networks.upconv_arch = (1e-3 * torch.randn(8, 3, generator=torch.Generator().manual_seed(5))).to(dev).requires_grad_(True)
+    crit = networks.GANLoss("vanilla").to(dev)
+    optG = Adam(list(G.parameters()), lr=2e-5, betas=(0.5, 0.999))
+    optD = Adam(list(D.parameters()), lr=2e-5, betas=(0.5, 0.999))
+    g = torch.Generator().manual_seed(14)
+    mask = torch.randint(0, 2, (batch, 1, 256, 256), generator=g).float().to(dev)
+    image = torch.rand(batch, 1, 256, 256, generator=g).to(dev)
+
+    def step():
+        fake = G(mask)
+        for p in D.parameters():
+            p.requires_grad_(True)
+        optD.zero_grad()
+        loss_D = 0.5 * (crit(D(torch.cat([mask, fake], 1).detach()), False) + crit(D(torch.cat([mask, image], 1)), True))
+        loss_D.backward()
+        optD.step()
+        for p in D.parameters():
+            p.requires_grad_(False)
+        optG.zero_grad()
+        loss_G = crit(D(torch.cat([mask, fake], 1)), True) + networks.l1_loss(fake, image) * 100.0
+        loss_G.backward()
+        optG.step()
+        return loss_G
+
+    t = timed(step, steps)
+    # algorithmic FLOPs per image: merged-kernel form ~157 GF, as the reference executes it ~234 GF
+    print(json.dumps({"workload": "pix2pix optimize_parameters (unet_256 G + basic D, GANLoss + 100*L1, Adam)", "batch": batch,
+                      "ms_per_step": t * 1e3, "images_per_s": batch / t, "tflops_merged_form": 157e9 * batch / t / 1e12,
+                      "dtype": "bf16", "data": "synthetic"}), flush=True)
+
+
+def evaluate_sweep(steps):
+    import semantic_segmentation_b200 as S
+    from oracle import genseg_oracle as O
+    from semantic_segmentation_b200.unet import UNet
+    from semantic_segmentation_b200.unet.evaluate import dice_from_counts, predict_counts
+    S.set_precision("bf16")
+    dev = "cuda"
+    net = UNet(1, 2, True)
+    net.load_state_dict(O.seeded_state(O.unet_state_spec(1, 2, True), 1234))
+    net = net.to(dev).eval()
+    for n, hw in [(64, 256), (16, 512), (4, 1024), (1, 256), (1, 512), (1, 1024)]:
+        g = torch.Generator().manual_seed(3)
+        x = torch.rand(n, 1, hw, hw, generator=g).to(dev)
+        y = torch.randint(0, 2, (n, hw, hw), generator=g).to(dev)
+
+        def step():
+            with torch.no_grad():
+                counts, _ = predict_counts(net, x, y)
+                return dice_from_counts(counts)
+
+        t = timed(step, steps)
+        print(json.dumps({"workload": "U-Net(1,2,bilinear) eval forward + fused argmax/Dice counts", "batch": n, "hw": hw,
+                          "ms_per_batch": t * 1e3, "images_per_s": n / t, "mpixel_per_s": n * hw * hw / t / 1e6,
+                          "fwd_tflops": 79.818e9 * (hw / 256.0) ** 2 * n / t / 1e12, "dtype": "bf16"}), flush=True)
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--batch", type=int, default=8)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--only", default="")
+    a = ap.parse_args()
+    if a.only in ("", "pix2pix"):
+        pix2pix(a.batch, a.steps)
+    if a.only in ("", "eval"):
+        evaluate_sweep(a.steps)
