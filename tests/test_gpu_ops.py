@@ -341,3 +341,76 @@ def test_head_conv(dtype, c):
     dx, dw, db = ops.head_conv_bwd(xd, wt.to(DEV), dy.to(DEV), True, True, True)
     assert rel(from_nhwc(dx), xr.grad) < (1e-5 if dtype == torch.float32 else 4e-3)
     assert rel(dw, wr.grad) < 2e-5 and rel(db, br.grad) < 1e-5
+
+
+def test_multi_tensor_optimizers_match_torch():
+    """One-launch multi-tensor RMSprop / Adam (the path optim.RMSprop / optim.Adam take) against torch.optim on CPU,
+    over tensors whose sizes straddle the 2048-element block granularity."""
+    from semantic_segmentation_b200.optim import Adam, RMSprop
+    g = torch.Generator().manual_seed(31)
+    shapes = [(3,), (2048,), (2049,), (64, 33, 3, 3), (1,), (5000,)]
+    p0 = [torch.randn(s, generator=g) for s in shapes]
+    grads = [[torch.randn(s, generator=g) for s in shapes] for _ in range(3)]
+    for kind in ("rmsprop", "adam"):
+        ref = [p.clone().requires_grad_(True) for p in p0]
+        dev = [p.clone().to(DEV).requires_grad_(True) for p in p0]
+        if kind == "rmsprop":
+            ro = torch.optim.RMSprop(ref, lr=1e-3, weight_decay=1e-8, momentum=0.9)
+            do = RMSprop(dev, lr=1e-3, weight_decay=1e-8, momentum=0.9)
+        else:
+            ro = torch.optim.Adam(ref, lr=2e-4, betas=(0.5, 0.999))
+            do = Adam(dev, lr=2e-4, betas=(0.5, 0.999))
+        for gs in grads:
+            for r, d, gr in zip(ref, dev, gs):
+                r.grad = gr.clone()
+                d.grad = gr.to(DEV)
+            ro.step()
+            do.step()
+        for r, d in zip(ref, dev):
+            assert rel(d, r) < 1e-6, kind
+
+
+def test_batched_pack_and_unpack_match_single():
+    g = torch.Generator().manual_seed(32)
+    ws = [torch.randn(s, generator=g).to(DEV) for s in [(64, 128, 3, 3), (8, 16, 4, 4), (128, 64, 2, 2), (1, 7, 8, 8)]]
+    for dtype in (torch.bfloat16, torch.float32):
+        jobs, singles = [], []
+        for i, w in enumerate(ws):
+            rfd = i % 2 == 0
+            d0, d1, kh, kw = w.shape
+            rows, cols = (d0, d1) if rfd else (d1, d0)
+            out = torch.empty((kh * kw, rows, cols), device=DEV, dtype=dtype)
+            jobs.append((w, rfd, out))
+            singles.append(ops.pack_weight(w, rfd, dtype))
+        ops.pack_weight_multi(jobs, dtype)
+        for (_, _, out), s in zip(jobs, singles):
+            assert torch.equal(out, s)
+    ujobs, usingles = [], []
+    for i, w in enumerate(ws):
+        rfd = i % 2 == 0
+        d0, d1, kh, kw = w.shape
+        rows, cols = (d0, d1) if rfd else (d1, d0)
+        dwp = torch.randn((kh * kw, rows, cols), generator=g).to(DEV)
+        out = torch.empty(tuple(w.shape), device=DEV, dtype=torch.float32)
+        ujobs.append((dwp, rfd, out))
+        usingles.append(ops.unpack_wgrad(dwp, tuple(w.shape), rfd))
+    ops.unpack_wgrad_multi(ujobs)
+    for (_, _, out), s in zip(ujobs, usingles):
+        assert torch.equal(out, s)
+
+
+THIN = [  # kind, k, stride, pad, cin, cout, n, h, w : 1..4 channels on one side (thin_conv.cu)
+    ("convT", 8, 2, 3, 128, 1, 2, 12, 10),
+    ("conv", 4, 1, 1, 512, 1, 2, 9, 9),
+    ("conv", 4, 2, 1, 2, 64, 2, 16, 12),
+    ("convT", 8, 2, 3, 64, 3, 1, 6, 6),
+]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("geom", THIN, ids=[f"{g[0]}k{g[1]}s{g[2]}_{g[4]}to{g[5]}" for g in THIN])
+def test_thin_convolutions(geom, dtype):
+    """Layers with 1..4 channels on one side run through thin_gather / thin_scatter / thin_wgrad (use_tc=0 path)."""
+    res = conv_case(*geom, dtype=dtype, use_tc=0)
+    tol = 1e-5 if dtype == torch.float32 else 6e-3
+    assert res["fwd"] < tol and res["dgrad"] < tol and res["wgrad"] < (2e-5 if dtype == torch.float32 else 1e-4), res

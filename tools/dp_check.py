@@ -19,7 +19,8 @@ dev = torch.device("cuda", local)
 for prec in ("fp32", "bf16"):
     S.set_precision(prec)
     st = O.seeded_state(O.unet_state_spec(1, 2, True), 1)
-    x, y = O.seeded_inputs(2, 8, 1, 64, 64, 2)
+    GB = int(os.environ.get("DP_GB", "8"))
+    x, y = O.seeded_inputs(2, GB, 1, 64, 64, 2)
     def run(xs, ys):
         net = UNet(1, 2, True); net.load_state_dict(st); net = net.to(dev).train()
         loss = seg_loss(net(xs.to(dev)), ys.to(dev)); loss.backward()
@@ -27,12 +28,13 @@ for prec in ("fp32", "bf16"):
     parallel.shutdown()
     ref_loss, ref_g, _ = run(x, y)                         # single-rank, full global batch
     world = parallel.init_data_parallel(sync_bn=True)
-    lo, hi = parallel.shard_batch(8)
+    lo, hi = parallel.shard_batch(GB)
     loss, g, net = run(x[lo:hi], y[lo:hi])
     parallel.allreduce_gradients(net.parameters())
     g = {k: p.grad for k, p in net.named_parameters()}
-    worst = max(rel(g[k], ref_g[k]) for k in g)           # loss is a global mean -> summed shard grads == full grads
-    rs = {k: rel(net.state_dict()[k], v) for k, v in {}.items()}
+    errs = sorted(((rel(g[k], ref_g[k]), k) for k in g), reverse=True)   # global-mean loss -> summed shard grads == full grads
+    worst = errs[0][0]
     if parallel.rank() == 0:
         print("world %d %s: loss %.7f ref %.7f  worst grad rel %.3e" % (world, prec, loss.item(), ref_loss.item(), worst), flush=True)
+        print("   worst keys: " + ", ".join("%s %.1e" % (k, e) for e, k in errs[:5]) + " | median %.1e" % errs[len(errs) // 2][0], flush=True)
 dist.barrier()
