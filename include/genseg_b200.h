@@ -208,6 +208,21 @@ int gsb_adam_step_multi(int n, float* const* p, const float* const* g, float* co
                         const int64_t* numel, float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
                         float grad_scale, gsb_stream s);
 
+/* ---- NVLink peer-memory all-reduce of small fp64 vectors (the sync-BN statistic exchanges and the CE / Dice
+ * sums; replaces the nn.DataParallel wrap of models_pix2pix/networks.py:117-121 for the batch-sharded path).
+ * Every rank (one process per GPU, same node) creates a region, publishes its CUDA IPC handle, opens its peers'
+ * handles, and then calls gsb_peer_allreduce_f64 in the same order on every rank: one kernel per call stores the
+ * vector into all regions over NVLink, exchanges sequence flags and sums in rank order (bit-identical on all ranks).
+ * n <= gsb_peer_max_elems(), world <= 8.  Graph-capturable (the sequence counter lives in device memory). */
+int64_t gsb_peer_region_bytes(void);
+int gsb_peer_max_elems(void);
+int gsb_peer_handle_bytes(void);
+int gsb_peer_create(void** region, void* handle_out);
+int gsb_peer_open(const void* handle, void** peer_region);
+int gsb_peer_close(void* peer_region);
+int gsb_peer_destroy(void* region);
+int gsb_peer_allreduce_f64(double* buf, int n, void* const* regions, int rank, int world, gsb_stream s);
+
 #ifdef __cplusplus
 }
 #endif

@@ -79,6 +79,14 @@ SIGNATURES = {
     "gsb_adam_step": (_i, [_p, _p, _p, _p, _i64, _f, _f, _f, _f, _f, _i64, _f, _p]),
     "gsb_rmsprop_step_multi": (_i, [_i, _p, _p, _p, _p, _p, _f, _f, _f, _f, _f, _f, _p]),
     "gsb_adam_step_multi": (_i, [_i, _p, _p, _p, _p, _p, _f, _f, _f, _f, _f, _i64, _f, _p]),
+    "gsb_peer_region_bytes": (_i64, []),
+    "gsb_peer_max_elems": (_i, []),
+    "gsb_peer_handle_bytes": (_i, []),
+    "gsb_peer_create": (_i, [_p, _p]),
+    "gsb_peer_open": (_i, [_p, _p]),
+    "gsb_peer_close": (_i, [_p]),
+    "gsb_peer_destroy": (_i, [_p]),
+    "gsb_peer_allreduce_f64": (_i, [_p, _i, _p, _i, _i, _p]),
 }
 
 _lib: Optional[C.CDLL] = None

@@ -21,6 +21,7 @@
 // (models_pix2pix/networks.py:582,647,655; architecture_pix2pix/operations.py:14-39).
 #include <stdlib.h>
 
+#include <cstdio>
 #include "tc_common.cuh"
 
 namespace gsb {
@@ -33,7 +34,8 @@ struct HaloPlan {
   uint8_t wtap[kHaloMaxGroups][kHaloMaxDy];
 };
 struct HaloParams {
-  int tiles_x, tiles_y;  // 16x16 tiles per image
+  int tiles_x, tiles_y;  // (8*mt)x16 tiles per image
+  int mt, tw;            // M-tiles (8x16 pixels each) per CTA tile: 2 (16-wide tile) or 1 (8-wide); tw = 8*mt
   int W, H, N;           // extents of the tiled (output) space
   int cin, cout, n_tiles, num_tiles;
   int nA, nB, a_bytes;   // ring depths and activation box bytes (pw x boxh x 128 B)
@@ -154,7 +156,7 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
         const int nt = tile % p.n_tiles, st = (tile / p.n_tiles) * CL + rank;
         const bool ghost = st >= spatial;  // odd tail: out-of-range image index -> zero-filled loads, no stores
         const int n = ghost ? p.N : st / per_img, r = ghost ? 0 : st % per_img;
-        const int x0 = (r % p.tiles_x) * 16, y0 = (r / p.tiles_x) * 16;
+        const int x0 = (r % p.tiles_x) * p.tw, y0 = (r / p.tiles_x) * 16;
         for (int kb = 0; kb < kblocks; ++kb) {
           for (int g = 0; g < plan.ngroups; ++g) {
             if (!p.full || g == 0) {
@@ -219,9 +221,11 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
                 const uint64_t adesc = adesc0 + (uint64_t)(t * (row_bytes >> 4)), bdesc = bdesc0 + (uint64_t)(t * (B_BYTES >> 4));
 #pragma unroll
                 for (int m = 0; m < 2; ++m) {
+                  if (m < p.mt) {
 #pragma unroll
-                  for (int k = 0; k < 4; ++k)
-                    umma_bf16(d0 + m * BN, adesc + (uint64_t)(64 * m + 2 * k), bdesc + (uint64_t)(2 * k), idesc, accum | (uint32_t)(t | k));
+                    for (int k = 0; k < 4; ++k)
+                      umma_bf16(d0 + m * BN, adesc + (uint64_t)(64 * m + 2 * k), bdesc + (uint64_t)(2 * k), idesc, accum | (uint32_t)(t | k));
+                  }
                 }
               }
               if (CL > 1) umma_commit_mc(&emptyB[sb], kMask); else umma_commit(&emptyB[sb]);
@@ -263,12 +267,13 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
       const int nt = tile % p.n_tiles, st = (tile / p.n_tiles) * CL + rank;
       const bool ghost = st >= spatial;
       const int n = ghost ? p.N : st / per_img, r = ghost ? 0 : st % per_img;
-      const int x0 = (r % p.tiles_x) * 16, y0 = (r / p.tiles_x) * 16;
-      const bool plain = simple && !ghost && (x0 + 16 <= p.W) && (y0 + 16 <= p.H);  // no bias / act / masking
+      const int x0 = (r % p.tiles_x) * p.tw, y0 = (r / p.tiles_x) * 16;
+      const bool plain = simple && !ghost && (x0 + p.tw <= p.W) && (y0 + 16 <= p.H);  // no bias / act / masking
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
 #pragma unroll 1
-      for (int mh = 0; mh < 2 * (BN / OUT_COLS); ++mh) {
+      const int n_mh = p.mt * (BN / OUT_COLS);
+      for (int mh = 0; mh < n_mh; ++mh) {
         const int m = mh / (BN / OUT_COLS), h = mh % (BN / OUT_COLS);  // M-tile, 128-column half
         const bool valid = !ghost && (x0 + m * 8 + (row & 7) < p.W) && (y0 + (row >> 3) < p.H);
         if (et == 0) tma_store_wait_read();  // the previous store has finished reading s_out
@@ -318,7 +323,7 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
             }
           }
         }
-        if (mh == 2 * (BN / OUT_COLS) - 1) {
+        if (mh == n_mh - 1) {
           tc_fence_before();
           mbar_arrive(&tempty[acc]);  // accumulators drained: the MMA warp may reuse this TMEM buffer
         }
@@ -631,27 +636,57 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
   int full = fullhalo_enabled() && uniform && nmaps == 1 && plan.ngroups > 1 ? 1 : 0;
   for (int g = 0; full && g < plan.ngroups; ++g)
     if (plan.dy0[g] != plan.dy0[0] || plan.dx[g] != plan.dx[0] + g) full = 0;
-  const int pw = full ? 16 + plan.ngroups - 1 : 16;
-  if (pw > 24) full = 0;
+  if (16 + plan.ngroups - 1 > 24) full = 0;
+  // Tile shape (BN output channels x mt M-tiles of 8x16 pixels): minimise  tiles-per-CTA x time-per-tile.  Per-SM rates
+  // are the measured ones (profiles/README.md: 1500 / 1100 / 870 TFLOP/s over 148 SMs at BN = 256 / 128 / 64); narrow
+  // tiles (mt = 1) re-read the weight tile twice as often.  Large launches keep the widest tile; launches with fewer
+  // tiles than SMs (deep layers at 8 images per GPU) trade per-tile efficiency for occupancy.
+  int BN = 64, mt = 2;
+  {
+    const double k_flop = 2.0 * 128.0 * (double)cin * (double)taps.ntaps;
+    double best = 1e30;
+    const int sms = num_sms();
+    for (int cand = 0; cand < 6; ++cand) {
+      const int bn = cand / 2 == 0 ? 256 : (cand / 2 == 1 ? 128 : 64), m = cand % 2 == 0 ? 2 : 1;
+      if (cout % bn != 0) continue;
+      if (bn == 256 && !(cin >= 128 && bn256_enabled())) continue;
+      if (m == 1 && !env_flag("GSB_TC_NARROW", true)) continue;
+      const double rate = (bn == 256 ? 10.1e6 : (bn == 128 ? 7.4e6 : 5.9e6)) * (m == 1 ? 0.9 : 1.0);  // FLOP per us per SM
+      const long long sp = (long long)(((int)outv.W + 8 * m - 1) / (8 * m)) * (((int)outv.H + 15) / 16) * (long long)outv.N;
+      const long long tiles = ((sp + 1) / 2) * 2 * (cout / bn);
+      const long long per_cta = (tiles + sms - 1) / sms;
+      const double t = (double)per_cta * (k_flop * m * bn / rate + 1.5) + 4.0;
+      if (t < best * 0.97) { best = t; BN = bn; mt = m; }
+    }
+    // GSB_TC_TILE="<BN>,<mt>" pins the shape (tests sweep every variant; ignored when it does not divide Cout)
+    const char* e = getenv("GSB_TC_TILE");
+    int fb = 0, fm = 0;
+    if (e != nullptr && sscanf(e, "%d,%d", &fb, &fm) == 2 && (fb == 64 || fb == 128 || fb == 256) && (fm == 1 || fm == 2) &&
+        cout % fb == 0) {
+      BN = fb;
+      mt = fm;
+    }
+  }
+  const int tw = 8 * mt;
+  const int pw = full ? tw + plan.ngroups - 1 : tw;
   TcMaps maps;
   memset(&maps, 0, sizeof(maps));
   for (int i = 0; i < nmaps; ++i)
-    if (make_act_map(&maps.in[i], shifted[i], full ? pw : 16, boxh, 1)) return -1;
+    if (make_act_map(&maps.in[i], shifted[i], pw, boxh, 1)) return -1;
   for (int i = nmaps; i < 4; ++i) maps.in[i] = maps.in[0];
   if (make_act_map(&maps.out, outv, 8, 16, 1)) return -1;
-  const int spatial = (((int)outv.W + 15) / 16) * (((int)outv.H + 15) / 16) * (int)outv.N;
+  const int spatial = (((int)outv.W + tw - 1) / tw) * (((int)outv.H + 15) / 16) * (int)outv.N;
   const int CL = (cluster_enabled() && spatial >= 2) ? 2 : 1;
-  // 256-column tiles (single-buffered accumulators) pay off once the K loop dwarfs the un-overlapped epilogue
-  const int BN = (cout % 256 == 0 && cin >= 128 && bn256_enabled()) ? 256 : ((cout % 128 == 0) ? 128 : 64);
   if (make_w_map(&maps.w, wp, (int64_t)taps_total * cout, cin, BN / CL)) return -1;
   HaloParams p;
-  p.tiles_x = ((int)outv.W + 15) / 16;
+  p.mt = mt; p.tw = tw;
+  p.tiles_x = ((int)outv.W + tw - 1) / tw;
   p.tiles_y = ((int)outv.H + 15) / 16;
   p.W = (int)outv.W; p.H = (int)outv.H; p.N = (int)outv.N;
   p.cin = cin; p.cout = cout;
   p.n_tiles = cout / BN;
   p.num_tiles = ((spatial + CL - 1) / CL) * p.n_tiles;  // cluster tiles
-  p.pw = full ? pw : 16;
+  p.pw = pw;
   p.full = full;
   p.a_bytes = p.pw * boxh * 128;
   p.a_stride = (p.a_bytes + 1023) & ~1023;

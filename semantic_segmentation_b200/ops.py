@@ -393,6 +393,41 @@ def adam_step_multi(ps, gs, ms, vs, lr, beta1, beta2, eps, weight_decay, step, g
                                      beta2, eps, weight_decay, int(step), grad_scale, _s(ps[0])), "adam_step_multi")
 
 
+# --- NVLink peer-memory all-reduce (csrc/peer.cu) ------------------------------------------------------
+def peer_create():
+    """-> (region pointer, IPC handle bytes) for this rank's region on the current device."""
+    lib = load()
+    region = C.c_void_p()
+    handle = C.create_string_buffer(lib.gsb_peer_handle_bytes())
+    check(lib.gsb_peer_create(C.byref(region), handle), "peer_create")
+    return int(region.value), bytes(handle.raw)
+
+
+def peer_open(handle: bytes) -> int:
+    out = C.c_void_p()
+    check(load().gsb_peer_open(C.create_string_buffer(handle, len(handle)), C.byref(out)), "peer_open")
+    return int(out.value)
+
+
+def peer_close(region: int) -> None:
+    check(load().gsb_peer_close(C.c_void_p(region)), "peer_close")
+
+
+def peer_destroy(region: int) -> None:
+    check(load().gsb_peer_destroy(C.c_void_p(region)), "peer_destroy")
+
+
+def peer_max_elems() -> int:
+    return int(load().gsb_peer_max_elems())
+
+
+def peer_allreduce_f64(buf: torch.Tensor, regions, rank: int, world: int) -> None:
+    """In-place sum of a contiguous fp64 device vector over the ranks whose regions are given in rank order."""
+    assert buf.dtype == torch.float64 and buf.is_contiguous() and buf.is_cuda
+    arr = (C.c_void_p * world)(*[C.c_void_p(r) for r in regions])
+    check(load().gsb_peer_allreduce_f64(ptr(buf), buf.numel(), arr, rank, world, _s(buf)), "peer_allreduce_f64")
+
+
 def adam_step(p, g, exp_avg, exp_avg_sq, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0) -> None:
     check(load().gsb_adam_step(ptr(p), ptr(g), ptr(exp_avg), ptr(exp_avg_sq), p.numel(), lr, beta1, beta2, eps,
                                weight_decay, int(step), grad_scale, _s(p)), "adam_step")

@@ -1,7 +1,9 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 600 python tools/b1_check.py > gpurun_out/b1_check.log 2>&1; echo "b1 rc=$?"; grep "n=" gpurun_out/b1_check.log
-for GB in 2 8; do
-DP_GB=$GB timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 2951$GB tools/dp_check.py > gpurun_out/dp_check_gb$GB.log 2>&1; echo "dp_check rc=$?"; grep "world\|worst" gpurun_out/dp_check_gb$GB.log
+timeout 180 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29531 tools/peer_check.py > gpurun_out/peer_check.log 2>&1; echo "peer_check rc=$?"; grep "peer_check\|Error\|error" gpurun_out/peer_check.log | head -5
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29532 tools/dp_check.py > gpurun_out/dp_check_2.log 2>&1; echo "dp_check rc=$?"; grep "world\|worst" gpurun_out/dp_check_2.log
+for CFG in "1:" "0:" "1:--no-sync-bn"; do
+PEER=${CFG%%:*}; FLAGS=${CFG#*:}
+GSB_PEER_ALLREDUCE=$PEER timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29544 bench.py --gpus 2 --steps 20 --warmup 3 --per-gpu-batch 8 $FLAGS > gpurun_out/bench_2x8.log 2>&1; echo "bench peer=$PEER $FLAGS rc=$?"
+grep '^{"metric"' gpurun_out/bench_2x8.log | cut -c1-60,95-200
 done
-timeout 900 python -m pytest tests/test_gpu_ops.py -x -q -m gpu -k "multi or batched or thin or optim" > gpurun_out/newtests.log 2>&1; echo "tests rc=$?"; tail -5 gpurun_out/newtests.log
