@@ -208,6 +208,21 @@ int gsb_adam_step_multi(int n, float* const* p, const float* const* g, float* co
                         const int64_t* numel, float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
                         float grad_scale, gsb_stream s);
 
+/* ---- Device-side image chain of the GenSeg end-to-end step (running_files/train_end2end_jsrt.py:186-200).
+ * gsb_minmax_f32      : ordered keys of (min, max) over the whole batch tensor (:197), keys = 2 x uint32 on the device.
+ * gsb_quantize_hist   : q = uint8(clamp(((x-min)/(max-min))*255 + 0.5, 0, 255)) (:197,:199) + 256-bin histogram per plane
+ *                       (x: [planes, plane] fp32; keys NULL = x already normalised).
+ * gsb_equalize_lut    : torchvision.transforms.functional.equalize per plane (:200) followed by a 256-entry LUT
+ *                       (adjust_gamma(.., 0.5), supplied by the host) -> out_f = value / 255.0f and / or out_u8.
+ * gsb_mask_affine     : inverse-mapped bilinear warp (zero outside) of n fp32 masks [n,h,w] by per-image 2x3 matrices
+ *                       (output -> input pixel coordinates) + (> threshold) binarisation (:187-195; replaces the CPU imgaug
+ *                       round trip).  threshold < 0 writes the interpolated value. */
+int gsb_minmax_f32(const float* x, int64_t n, uint32_t* keys, gsb_stream s);
+int gsb_quantize_hist(const float* x, const uint32_t* keys, uint8_t* q, uint32_t* hist, int planes, int plane, gsb_stream s);
+int gsb_equalize_lut(const uint8_t* q, const uint32_t* hist, uint32_t* ws_hist, const uint8_t* post, float* out_f,
+                     uint8_t* out_u8, int planes, int plane, int do_equalize, gsb_stream s);
+int gsb_mask_affine(const float* in, const float* mats, float* out, int n, int h, int w, float threshold, gsb_stream s);
+
 /* ---- NVLink peer-memory all-reduce of small fp64 vectors (the sync-BN statistic exchanges and the CE / Dice
  * sums; replaces the nn.DataParallel wrap of models_pix2pix/networks.py:117-121 for the batch-sharded path).
  * Every rank (one process per GPU, same node) creates a region, publishes its CUDA IPC handle, opens its peers'

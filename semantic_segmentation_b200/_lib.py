@@ -79,6 +79,10 @@ SIGNATURES = {
     "gsb_adam_step": (_i, [_p, _p, _p, _p, _i64, _f, _f, _f, _f, _f, _i64, _f, _p]),
     "gsb_rmsprop_step_multi": (_i, [_i, _p, _p, _p, _p, _p, _f, _f, _f, _f, _f, _f, _p]),
     "gsb_adam_step_multi": (_i, [_i, _p, _p, _p, _p, _p, _f, _f, _f, _f, _f, _i64, _f, _p]),
+    "gsb_minmax_f32": (_i, [_p, _i64, _p, _p]),
+    "gsb_quantize_hist": (_i, [_p, _p, _p, _p, _i, _i, _p]),
+    "gsb_equalize_lut": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _p]),
+    "gsb_mask_affine": (_i, [_p, _p, _p, _i, _i, _i, _f, _p]),
     "gsb_peer_region_bytes": (_i64, []),
     "gsb_peer_max_elems": (_i, []),
     "gsb_peer_handle_bytes": (_i, []),

@@ -393,6 +393,34 @@ def adam_step_multi(ps, gs, ms, vs, lr, beta1, beta2, eps, weight_decay, step, g
                                      beta2, eps, weight_decay, int(step), grad_scale, _s(ps[0])), "adam_step_multi")
 
 
+# --- device-side image chain of the end-to-end step (csrc/augment.cu) -----------------------------------
+def minmax_f32(x: torch.Tensor) -> torch.Tensor:
+    """Ordered keys of (min, max) over a contiguous fp32 CUDA tensor -> int32[2] on the device (opaque; feed to quantize_hist)."""
+    keys = torch.empty(2, device=x.device, dtype=torch.int32)
+    check(load().gsb_minmax_f32(ptr(x), x.numel(), ptr(keys), _s(x)), "minmax_f32")
+    return keys
+
+
+def quantize_hist(x: torch.Tensor, keys: Optional[torch.Tensor], planes: int, plane: int):
+    q = torch.empty(x.shape, device=x.device, dtype=torch.uint8)
+    hist = torch.empty((planes, 256), device=x.device, dtype=torch.int32)
+    check(load().gsb_quantize_hist(ptr(x), ptr(keys), ptr(q), ptr(hist), planes, plane, _s(x)), "quantize_hist")
+    return q, hist
+
+
+def equalize_lut(q: torch.Tensor, hist: Optional[torch.Tensor], post: Optional[torch.Tensor], out: torch.Tensor,
+                 planes: int, plane: int, do_equalize: bool) -> None:
+    ws = None if hist is not None else torch.empty((planes, 256), device=q.device, dtype=torch.int32)
+    out_f = out if out.dtype == torch.float32 else None
+    out_u8 = out if out.dtype == torch.uint8 else None
+    check(load().gsb_equalize_lut(ptr(q), ptr(hist), ptr(ws), ptr(post), ptr(out_f), ptr(out_u8), planes, plane,
+                                  1 if do_equalize else 0, _s(q)), "equalize_lut")
+
+
+def mask_affine(masks: torch.Tensor, mats: torch.Tensor, out: torch.Tensor, n: int, h: int, w: int, threshold: float) -> None:
+    check(load().gsb_mask_affine(ptr(masks), ptr(mats), ptr(out), n, h, w, float(threshold), _s(masks)), "mask_affine")
+
+
 # --- NVLink peer-memory all-reduce (csrc/peer.cu) ------------------------------------------------------
 def peer_create():
     """-> (region pointer, IPC handle bytes) for this rank's region on the current device."""

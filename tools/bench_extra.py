@@ -104,6 +104,30 @@ def evaluate_sweep(steps):
                           "fwd_tflops": 79.818e9 * (hw / 256.0) ** 2 * n / t / 1e12, "dtype": "bf16"}), flush=True)
 
 
+def augment_chain(steps):
+    """the image chain of the end-to-end step (train_end2end_jsrt.py:186-200) at its size (8 x 1 x 256 x 256)
+    and at a bandwidth-relevant size (64 x 1 x 1024 x 1024), device-resident, against the CPU restatement."""
+    import time
+    from oracle import augment_oracle as AO
+    from semantic_segmentation_b200.util import augment as A
+    for n, hw in [(8, 256), (64, 1024)]:
+        g = torch.Generator().manual_seed(1)
+        x = torch.tanh(torch.randn(n, 1, hw, hw, generator=g))
+        xd = x.cuda()
+        t = timed(lambda: A.synth_image_postprocess(xd), steps)
+        # algorithmic bytes: fp32 read twice (min/max, quantise) + u8 write + u8 read + fp32 write = 14 B / pixel
+        cpu = None
+        if n == 8:
+            t0 = time.perf_counter(); AO.synth_image_postprocess(x); cpu = time.perf_counter() - t0
+        print(json.dumps({"workload": "synth image chain (batch min-max, uint8, equalize, gamma 0.5)", "batch": n, "hw": hw,
+                          "us_per_batch": t * 1e6, "mpixel_per_s": n * hw * hw / t / 1e6, "gbytes_per_s": 14.0 * n * hw * hw / t / 1e9,
+                          "cpu_oracle_us": cpu * 1e6 if cpu else None}), flush=True)
+    m = (torch.rand(8, 1, 256, 256) > 0.7).float().cuda()
+    mats = A.draw_affine(8, 256, 256, torch.Generator().manual_seed(2)).cuda()
+    t = timed(lambda: A.augment_masks(m, mats), steps)
+    print(json.dumps({"workload": "mask affine warp + threshold", "batch": 8, "hw": 256, "us_per_batch": t * 1e6}), flush=True)
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--batch", type=int, default=8)
@@ -114,3 +138,5 @@ if __name__ == "__main__":
         pix2pix(a.batch, a.steps)
     if a.only in ("", "eval"):
         evaluate_sweep(a.steps)
+    if a.only in ("", "augment"):
+        augment_chain(a.steps)
