@@ -208,7 +208,7 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        parallel.init_data_parallel(sync_bn=not args.no_sync_bn)
+        parallel.init_data_parallel(sync_bn=not args.no_sync_bn, overlap_grad_allreduce=not args.no_overlap)
     rank = parallel.rank()
     lib = _lib.load()
     S.set_precision("bf16")
@@ -317,6 +317,7 @@ def run_ours(args):
             "config": {"workload": "U-Net(n_channels=1,n_classes=2,bilinear) 256x256 train step: fwd + CE+Dice + bwd + RMSprop",
                        "global_batch": per * world, "per_gpu_batch": per, "parallelism": "dp%d" % world,
                        "sync_bn": bool(world > 1 and not args.no_sync_bn), "cuda_graph": graph is not None,
+                       "grad_allreduce": ("overlapped_in_backward" if not args.no_overlap else "after_backward") if world > 1 else None,
                        "l2": "per-step working set (activations+gradients, >1 GB per GPU) exceeds the 126 MB L2; no flush needed"},
             "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": int(x_host.numel() * 4 + y_host.numel() * 8) * world,
                     "d2h_bytes_per_step": 4 * world},
@@ -344,6 +345,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--per-gpu-batch", type=int, default=0, help="override 64/N (weak scaling experiments)")
     ap.add_argument("--no-sync-bn", action="store_true")
+    ap.add_argument("--no-overlap", action="store_true", help="gradient all-reduce after backward instead of inside it")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying a CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

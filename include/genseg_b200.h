@@ -45,6 +45,9 @@ typedef void* gsb_stream; /* cudaStream_t */
 
 int gsb_version(void);
 const char* gsb_last_error(void);
+/* Set aside n SMs (0..64) for a collective running concurrently on another stream: persistent kernels launched afterwards
+ * size their grids for the remaining SMs.  Returns the previous value.  Host-side state, read at launch time. */
+int gsb_set_sm_reserve(int n);
 /* 1 if the running device is sm_100 and the tcgen05 kernels can launch. */
 int gsb_tc_available(void);
 /* Number of kernels this library has launched in the calling process (bench evidence). */
@@ -149,6 +152,20 @@ int gsb_bn_bwd_apply(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2
 /* dbeta[c] (+)= sums[c], dgamma[c] (+)= sums[c + C]: parameter gradients from the LOCAL backward sums (under
  * sync-BN the sums are all-reduced afterwards; the gradient all-reduce then adds the other ranks' parts). */
 int gsb_bn_param_grad(const double* sums, int c, float* dgamma, float* dbeta, int accumulate, gsb_stream s);
+/* Fused statistic stages (one launch each; with world > 1 the cross-rank sum runs inside the kernel over the peer
+ * regions of gsb_peer_create / gsb_peer_open -- pass regions = NULL, rank = 0, world = 1 on a single GPU):
+ * gsb_bn_stats_finalize = gsb_bn_reduce_partials + all-reduce + gsb_bn_finalize (count = global element count);
+ * gsb_bn_bwd_partial    = stage 1 of gsb_bn_bwd_reduce (rows of per-block sums into workspace, *rows = row count);
+ * gsb_bn_bwd_stats      = gsb_bn_reduce_partials + gsb_bn_param_grad (local sums) + all-reduce -> sums[2c]. */
+int gsb_bn_stats_finalize(const float* partial, int rows, int c, double count, void* const* regions, int rank, int world,
+                          const float* gamma, const float* beta, float* running_mean, float* running_var,
+                          int64_t* num_batches_tracked, float momentum, float eps, float* scale, float* shift, float* mean,
+                          float* invstd, gsb_stream s);
+int gsb_bn_bwd_partial(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale, const float* shift,
+                       const float* mean, const float* invstd, int act1, int act2, uint64_t drop_seed,
+                       const uint8_t* drop_mask, void* workspace, size_t workspace_bytes, int* rows, gsb_stream s);
+int gsb_bn_bwd_stats(const float* partial, int rows, int c, void* const* regions, int rank, int world, float* dgamma,
+                     float* dbeta, int accumulate, double* sums, gsb_stream s);
 
 /* ---- pooling / resampling -- unet_parts.py:34,50,57-67 -------------------------------- */
 int gsb_maxpool2_fwd(const gsb_view* x, const gsb_view* y, gsb_stream s);

@@ -36,6 +36,7 @@ _p, _i, _i64, _f, _d, _u64, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c
 SIGNATURES = {
     "gsb_version": (_i, []),
     "gsb_last_error": (C.c_char_p, []),
+    "gsb_set_sm_reserve": (_i, [_i]),
     "gsb_tc_available": (_i, []),
     "gsb_launch_count": (C.c_ulonglong, []),
     "gsb_copy_view": (_i, [_VP, _VP, _p]),
@@ -62,6 +63,9 @@ SIGNATURES = {
     "gsb_bn_bwd_reduce": (_i, [_VP, _VP, _VP, _p, _p, _p, _p, _i, _i, _u64, _p, _p, _p, _sz, _p]),
     "gsb_bn_bwd_apply": (_i, [_VP, _VP, _VP, _p, _p, _p, _p, _i, _i, _u64, _p, _p, _d, _VP, _p, _p, _p]),
     "gsb_bn_param_grad": (_i, [_p, _i, _p, _p, _i, _p]),
+    "gsb_bn_stats_finalize": (_i, [_p, _i, _i, _d, _p, _i, _i, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p, _p]),
+    "gsb_bn_bwd_partial": (_i, [_VP, _VP, _VP, _p, _p, _p, _p, _i, _i, _u64, _p, _p, _sz, _p, _p]),
+    "gsb_bn_bwd_stats": (_i, [_p, _i, _i, _p, _i, _i, _p, _p, _i, _p, _p]),
     "gsb_maxpool2_fwd": (_i, [_VP, _VP, _p]),
     "gsb_maxpool2_bwd": (_i, [_VP, _VP, _VP, _i, _p]),
     "gsb_upsample2_fwd": (_i, [_VP, _VP, _i, _i, _p]),

@@ -40,6 +40,15 @@ int num_sms() {
   return sms;
 }
 
+// SMs the persistent kernels size their grids for: all of them, minus the ones set aside for a collective that runs
+// concurrently on another stream (gsb_set_sm_reserve; see parallel.py -- the gradient all-reduce overlapped with the
+// encoder backward).  A persistent grid that does not fit beside the collective's CTAs would run its tail as a second wave.
+static int g_sm_reserve = 0;
+int num_sms_avail() {
+  const int n = num_sms() - g_sm_reserve;
+  return n < 8 ? 8 : n;
+}
+
 }  // namespace gsb
 
 extern "C" unsigned long long gsb_launch_count(void) { return gsb::launch_count(); }
@@ -50,4 +59,10 @@ extern "C" int gsb_tc_available(void) {
   if (cudaGetDevice(&dev) != cudaSuccess) return 0;
   if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return 0;
   return major == 10 ? 1 : 0;
+}
+
+extern "C" int gsb_set_sm_reserve(int n) {
+  const int prev = gsb::g_sm_reserve;
+  gsb::g_sm_reserve = n < 0 ? 0 : (n > 64 ? 64 : n);
+  return prev;
 }

@@ -22,7 +22,8 @@ int check_launch(const char* what, int n = 1);  // n = kernels launched by this 
   } while (0)
 
 static inline cudaStream_t to_stream(gsb_stream s) { return reinterpret_cast<cudaStream_t>(s); }
-int num_sms();
+int num_sms();        // SMs of the device
+int num_sms_avail();  // SMs the persistent tensor-core kernels size their grids for (total minus gsb_set_sm_reserve)
 
 // A view is "pixel-linear" when pixel p = (n*h + y)*w + x lives at ptr + p*sw (+ c).
 static inline bool pixel_linear(const gsb_view* v) {

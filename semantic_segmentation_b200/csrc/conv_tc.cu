@@ -456,7 +456,7 @@ static int fprop_launch(const SubView& outv, const SubView* shifted, int nmaps, 
   p.num_tiles = p.tiles_x * p.tiles_y * p.tiles_z * p.n_tiles;
   p.act = act; p.bias = bias; p.stats = stats;
   if (stats_rows) *stats_rows = p.tiles_x * p.tiles_y * p.tiles_z;
-  int grid = p.num_tiles < num_sms() ? p.num_tiles : num_sms();
+  int grid = p.num_tiles < num_sms_avail() ? p.num_tiles : num_sms_avail();
   if (BN == 128) return launch_tc(conv_tc_fprop_kernel<128>, grid, 1, FpropCfg<128>::SMEM, maps, taps, p, st);
   return launch_tc(conv_tc_fprop_kernel<64>, grid, 1, FpropCfg<64>::SMEM, maps, taps, p, st);
 }
@@ -574,7 +574,7 @@ int conv_wgrad_tc(const gsb_view* in, const gsb_view* dout, float* dwp, const gs
   p.dwp = dwp;
   const int m_tiles = (p.a_blocks + 1) / 2;
   const int64_t base = (int64_t)m_tiles * p.n_tiles;
-  int64_t want = ((int64_t)num_sms() * 2 + base - 1) / base;  // ~2 waves
+  int64_t want = ((int64_t)num_sms_avail() * 2 + base - 1) / base;  // ~2 waves
   int64_t max_split = (p.boxes + 15) / 16;                    // >= 16 k-steps per CTA
   if (max_split < 1) max_split = 1;
   int64_t split = want < 1 ? 1 : (want > max_split ? max_split : want);

@@ -645,7 +645,7 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
   {
     const double k_flop = 2.0 * 128.0 * (double)cin * (double)taps.ntaps;
     double best = 1e30;
-    const int sms = num_sms();
+    const int sms = num_sms_avail();
     for (int cand = 0; cand < 6; ++cand) {
       const int bn = cand / 2 == 0 ? 256 : (cand / 2 == 1 ? 128 : 64), m = cand % 2 == 0 ? 2 : 1;
       if (cout % bn != 0) continue;
@@ -709,7 +709,7 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
   GSB_REQUIRE(p.nA >= 2, "conv_halo: shared memory budget");
   p.act = act; p.bias = bias; p.stats = stats;
   const int smem = fixed + p.nA * p.a_stride + p.nB * p.tb * b_bytes;
-  const int max_clusters = num_sms() / CL;
+  const int max_clusters = num_sms_avail() / CL;
   const int grid = (p.num_tiles < max_clusters ? p.num_tiles : max_clusters) * CL;
   if (stats_rows) *stats_rows = grid;  // one row of running sums per CTA
   void (*kern)(TcMaps, HaloPlan, HaloParams) = nullptr;
@@ -773,7 +773,7 @@ int conv_halo_wgrad(const SubView& tiled, const SubView* shifted, int nmaps, con
   const int m_tiles = (p.a_blocks + 1) / 2;
   const int base = m_tiles * p.n_tiles;
   // split-K over the pixel boxes: fill whole waves of SMs, keep >= 2 boxes per CTA
-  const int sms = num_sms();
+  const int sms = num_sms_avail();
   int max_split = p.boxes / 2 > 0 ? p.boxes / 2 : 1;
   int best = 1;
   double best_eff = 0.0;

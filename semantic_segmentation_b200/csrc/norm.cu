@@ -7,6 +7,7 @@
 // Algorithmic bytes: reduce = 1 read; act = 1 read + 1 (or 2) writes; bwd_reduce = 2 (3) reads;
 // bwd_apply = 2 (3) reads + 1 write -- at the storage dtype.
 #include "common.cuh"
+#include "peer.cuh"
 
 namespace gsb {
 
@@ -337,6 +338,111 @@ __global__ void bn_param_grad_kernel(const double* __restrict__ sums, int C, flo
   if (dgamma) dgamma[c] = (accumulate ? dgamma[c] : 0.f) + (float)sums[C + c];
 }
 
+// Statistic rows -> per-channel totals -> (cross-rank exchange) -> consumer, in ONE launch (was reduce_partials +
+// all-reduce + bn_finalize forward, reduce_partials + bn_param_grad + all-reduce backward: 5 launches per BatchNorm layer
+// and direction on the critical path of the step).  Block b owns channels [16b, 16b+16): 32 columns (16 x sum, 16 x
+// second sum) x 32 row lanes, fp64, fixed order.  world > 1: the 32 totals are exchanged through the peer regions
+// (csrc/peer.cu protocol, element index = column); every block reads the call's sequence number, the last block to
+// finish bumps the counter.
+//   MODE 0 (forward):  totals = [sum x, sum x^2] -> scale / shift / mean / invstd, running statistics, num_batches_tracked
+//   MODE 1 (backward): totals = [sum dy, sum dy*xhat] -> dbeta / dgamma from the LOCAL totals (the gradient all-reduce
+//                      adds the other ranks), global totals -> sums_out for bn_bwd_apply
+struct BnFusedFwd {
+  double count;
+  const float* gamma;
+  const float* beta;
+  float* running_mean;
+  float* running_var;
+  int64_t* nbt;
+  float momentum, eps;
+  float* scale;
+  float* shift;
+  float* mean;
+  float* invstd;
+};
+struct BnFusedBwd {
+  float* dgamma;
+  float* dbeta;
+  int accumulate;
+  double* sums;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(1024) bn_stats_fused_kernel(const float* __restrict__ partial, int rows, int C, PeerRegions regs,
+                                                             int rank, int world, BnFusedFwd f, BnFusedBwd b) {
+  __shared__ double red[32][33];
+  __shared__ double tot[32];
+  const int c = threadIdx.x & 31, l = threadIdx.x >> 5;
+  const int ch = blockIdx.x * 16 + (c & 15);
+  const int col = (c < 16 ? 0 : C) + ch;
+  const bool ok = ch < C;
+  const int n = 2 * C;
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+  if (ok) {
+    int r = l;
+    for (; r + 96 < rows; r += 128) {
+      const float v0 = partial[(int64_t)r * n + col], v1 = partial[(int64_t)(r + 32) * n + col];
+      const float v2 = partial[(int64_t)(r + 64) * n + col], v3 = partial[(int64_t)(r + 96) * n + col];
+      a0 += (double)v0; a1 += (double)v1; a2 += (double)v2; a3 += (double)v3;
+    }
+    for (; r < rows; r += 32) a0 += (double)partial[(int64_t)r * n + col];
+  }
+  red[l][c] = (a0 + a1) + (a2 + a3);
+  __syncthreads();
+  PeerHeader* hdr = world > 1 ? reinterpret_cast<PeerHeader*>(regs.r[rank]) : nullptr;
+  unsigned long long seq = 0;
+  if (l == 0) {
+    double t = 0.0;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) t += red[i][c];
+    if (MODE == 1 && ok) {
+      float* dst = c < 16 ? b.dbeta : b.dgamma;
+      if (dst != nullptr) dst[ch] = (b.accumulate ? dst[ch] : 0.f) + (float)t;
+    }
+    if (world > 1) {
+      seq = *reinterpret_cast<volatile unsigned long long*>(&hdr->counter) + 1ull;
+      if (ok && !peer_exchange_sum(t, col, regs, rank, world, (uint32_t)seq, (int)(seq % kPeerSlots))) {
+        hdr->error = seq;
+        __threadfence_system();
+        __trap();
+      }
+    }
+    tot[c] = t;
+    if (MODE == 1 && ok && b.sums != nullptr) b.sums[col] = t;
+  }
+  __syncthreads();
+  if (MODE == 0) {
+    if (threadIdx.x < 16 && blockIdx.x * 16 + threadIdx.x < C) {
+      const int cc = blockIdx.x * 16 + threadIdx.x;
+      const float g = f.gamma ? f.gamma[cc] : 1.f, be = f.beta ? f.beta[cc] : 0.f;
+      const double mu = tot[threadIdx.x] / f.count;
+      double var = tot[16 + threadIdx.x] / f.count - mu * mu;
+      if (var < 0.0) var = 0.0;
+      const float m = (float)mu;
+      const float is = (float)(1.0 / sqrt(var + (double)f.eps));
+      if (f.running_mean) f.running_mean[cc] = (1.f - f.momentum) * f.running_mean[cc] + f.momentum * m;
+      if (f.running_var) {
+        const double unbiased = f.count > 1.0 ? var * f.count / (f.count - 1.0) : var;
+        f.running_var[cc] = (1.f - f.momentum) * f.running_var[cc] + f.momentum * (float)unbiased;
+      }
+      const float sc = g * is;
+      f.scale[cc] = sc;
+      f.shift[cc] = be - m * sc;
+      if (f.mean) f.mean[cc] = m;
+      if (f.invstd) f.invstd[cc] = is;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && f.nbt != nullptr) *f.nbt += 1;
+  }
+  if (world > 1 && threadIdx.x == 0) {  // lane 0 of warp 0 holds seq; all of this block's packets have been consumed
+    __threadfence();
+    const unsigned int prev = atomicAdd(&hdr->done, 1u);
+    if (prev == gridDim.x - 1) {
+      hdr->done = 0;
+      hdr->counter = seq;
+    }
+  }
+}
+
 static int grid_for(int64_t P, int lanes) {
   int64_t want = (P + lanes - 1) / lanes;
   int64_t cap = (int64_t)num_sms() * 8;
@@ -433,10 +539,11 @@ static int check_bwd_views(const gsb_view* x, const gsb_view* dA1, const gsb_vie
   return 0;
 }
 
-extern "C" int gsb_bn_bwd_reduce(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
+// Stage 1 of the backward statistics: per-block rows of [sum dy, sum dy*xhat] into `workspace`; returns the row count.
+static int bn_bwd_partial_launch(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
                                  const float* shift, const float* mean, const float* invstd, int act1, int act2,
-                                 uint64_t drop_seed, const uint8_t* drop_mask, double* sums, void* workspace,
-                                 size_t workspace_bytes, gsb_stream s) {
+                                 uint64_t drop_seed, const uint8_t* drop_mask, void* workspace, size_t workspace_bytes,
+                                 int* rows_out, gsb_stream s) {
   if (check_bwd_views(x, dA1, dA2)) return -1;
   const int C = x->c, lanes = kThreads / (C / 8);
   const int64_t P = num_pixels(x);
@@ -458,9 +565,73 @@ extern "C" int gsb_bn_bwd_reduce(const gsb_view* x, const gsb_view* dA1, const g
     bn_reduce_kernel<float, 1, false><<<grid, kThreads, smem, to_stream(s)>>>(pv(x), pv(dA1), d2, P, C, scale, shift, mean,
                                                                              invstd, act1, act2, drop_seed, drop_mask, partial);
   }
-  int n = 2 * C;
-  reduce_partials_kernel<<<(n + 31) / 32, 1024, 0, to_stream(s)>>>(partial, grid, n, sums);
+  *rows_out = grid;
+  return 0;
+}
+
+extern "C" int gsb_bn_bwd_reduce(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
+                                 const float* shift, const float* mean, const float* invstd, int act1, int act2,
+                                 uint64_t drop_seed, const uint8_t* drop_mask, double* sums, void* workspace,
+                                 size_t workspace_bytes, gsb_stream s) {
+  int grid = 0;
+  if (bn_bwd_partial_launch(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, drop_seed, drop_mask, workspace,
+                            workspace_bytes, &grid, s))
+    return -1;
+  int n = 2 * x->c;
+  reduce_partials_kernel<<<(n + 31) / 32, 1024, 0, to_stream(s)>>>(reinterpret_cast<float*>(workspace), grid, n, sums);
   return check_launch("bn_bwd_reduce", 2);
+}
+
+extern "C" int gsb_bn_bwd_partial(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
+                                  const float* shift, const float* mean, const float* invstd, int act1, int act2,
+                                  uint64_t drop_seed, const uint8_t* drop_mask, void* workspace, size_t workspace_bytes,
+                                  int* rows, gsb_stream s) {
+  GSB_REQUIRE(rows != nullptr, "bn_bwd_partial: rows is null");
+  if (bn_bwd_partial_launch(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, drop_seed, drop_mask, workspace,
+                            workspace_bytes, rows, s))
+    return -1;
+  return check_launch("bn_bwd_partial");
+}
+
+static int fill_regions(PeerRegions& regs, void* const* regions, int rank, int world, int c, const char* who) {
+  memset(&regs, 0, sizeof(regs));
+  GSB_REQUIRE(world >= 1 && world <= kPeerMaxWorld && rank >= 0 && rank < world, "%s: world %d rank %d", who, world, rank);
+  if (world > 1) {
+    GSB_REQUIRE(regions != nullptr, "%s: peer regions required for world > 1", who);
+    GSB_REQUIRE(2 * c <= kPeerMaxN, "%s: %d channels exceed the peer slot size", who, c);
+    for (int i = 0; i < world; ++i) {
+      GSB_REQUIRE(regions[i] != nullptr, "%s: region %d is null", who, i);
+      regs.r[i] = regions[i];
+    }
+  }
+  return 0;
+}
+
+// Forward: statistic rows [rows, 2c] (conv epilogue / stem / bn_reduce stage 1) -> scale, shift, mean, invstd and the
+// running-statistics update, with the cross-rank sum of [sum x, sum x^2] fused in when world > 1 (`count` = GLOBAL count).
+extern "C" int gsb_bn_stats_finalize(const float* partial, int rows, int c, double count, void* const* regions, int rank,
+                                     int world, const float* gamma, const float* beta, float* running_mean, float* running_var,
+                                     int64_t* num_batches_tracked, float momentum, float eps, float* scale, float* shift,
+                                     float* mean, float* invstd, gsb_stream s) {
+  GSB_REQUIRE(partial && scale && shift && rows > 0 && c > 0, "bn_stats_finalize: bad arguments");
+  PeerRegions regs;
+  if (fill_regions(regs, regions, rank, world, c, "bn_stats_finalize")) return -1;
+  BnFusedFwd f{count, gamma, beta, running_mean, running_var, num_batches_tracked, momentum, eps, scale, shift, mean, invstd};
+  BnFusedBwd b{nullptr, nullptr, 0, nullptr};
+  bn_stats_fused_kernel<0><<<(c + 15) / 16, 1024, 0, to_stream(s)>>>(partial, rows, c, regs, rank, world, f, b);
+  return check_launch("bn_stats_finalize");
+}
+
+// Backward: rows of [sum dy, sum dy*xhat] -> dbeta / dgamma from the local totals, global totals -> sums[2c] (fp64).
+extern "C" int gsb_bn_bwd_stats(const float* partial, int rows, int c, void* const* regions, int rank, int world, float* dgamma,
+                                float* dbeta, int accumulate, double* sums, gsb_stream s) {
+  GSB_REQUIRE(partial && sums && rows > 0 && c > 0, "bn_bwd_stats: bad arguments");
+  PeerRegions regs;
+  if (fill_regions(regs, regions, rank, world, c, "bn_bwd_stats")) return -1;
+  BnFusedFwd f{};
+  BnFusedBwd b{dgamma, dbeta, accumulate, sums};
+  bn_stats_fused_kernel<1><<<(c + 15) / 16, 1024, 0, to_stream(s)>>>(partial, rows, c, regs, rank, world, f, b);
+  return check_launch("bn_bwd_stats");
 }
 
 extern "C" int gsb_bn_bwd_apply(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,

@@ -17,32 +17,9 @@
 // are sent only after call seq has been read), so kSlots = 4 leaves margin and a stale tag never equals seq.  A rank
 // that waits longer than ~2 s (a peer died) raises the region's error word and traps instead of hanging the GPU.
 #include "common.cuh"
+#include "peer.cuh"
 
 namespace gsb {
-
-constexpr int kPeerMaxWorld = 8;
-constexpr int kPeerSlots = 4;
-constexpr int kPeerMaxN = 4096;  // doubles per call
-constexpr size_t kPeerHeaderBytes = 1024;
-constexpr size_t kPeerRegionBytes = kPeerHeaderBytes + (size_t)kPeerSlots * kPeerMaxWorld * kPeerMaxN * 16;
-
-struct PeerHeader {
-  unsigned long long counter;  // calls issued by the owner
-  unsigned long long error;    // != 0: a wait timed out
-};
-
-struct PeerRegions {
-  void* r[kPeerMaxWorld];
-};
-
-__device__ __forceinline__ void st_packet(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
-__device__ __forceinline__ uint4 ld_packet(const void* p) {
-  uint4 v;
-  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
-  return v;
-}
 
 constexpr int kPeerThreads = 1024;
 constexpr int kPeerPerThread = kPeerMaxN / kPeerThreads;

@@ -46,11 +46,27 @@ def act_dtype() -> torch.dtype:
 
 
 # --- cross-rank reductions (sync-BN / global Dice); installed by parallel.py ----------------------
-_REDUCER = {"fn": None, "world": 1, "sync_bn": False}
+_REDUCER = {"fn": None, "world": 1, "sync_bn": False, "peer": None, "grad_fn": None, "sm_reserve": 0}
 
 
-def install_reducer(fn, world: int, sync_bn: bool) -> None:
-    _REDUCER.update(fn=fn, world=int(world), sync_bn=bool(sync_bn))
+def install_reducer(fn, world: int, sync_bn: bool, peer=None, grad_fn=None, sm_reserve: int = 0) -> None:
+    """peer = {"regions", "rank", "world"}: NVLink peer regions (parallel.py) -- the BatchNorm statistic kernels then do
+    their cross-rank sums themselves instead of calling ``fn`` between launches.
+    grad_fn(tensor) -> handle with .wait(): asynchronous in-place gradient all-reduce; when set, the U-Net program
+    all-reduces its gradients inside backward (first bucket overlapped with the encoder backward)."""
+    _REDUCER.update(fn=fn, world=int(world), sync_bn=bool(sync_bn), peer=peer, grad_fn=grad_fn, sm_reserve=int(sm_reserve))
+
+
+def _fused_stats_mode():
+    """(usable, peer, world): the fused statistic kernels cover one GPU and sync-BN over peer memory; sync-BN through a
+    plain reducer (gloo / NCCL fallback) keeps the separate reduce -> all-reduce -> finalize launches."""
+    if not _CONFIG.get("fused_bn_stats", True):
+        return False, None, 1
+    if _REDUCER["sync_bn"] and _REDUCER["fn"] is not None and _REDUCER["world"] > 1:
+        if _REDUCER["peer"] is None:
+            return False, None, 1
+        return True, _REDUCER["peer"], _REDUCER["world"]
+    return True, None, 1
 
 
 def _sync_stats(sums: torch.Tensor, count: float) -> Tuple[torch.Tensor, float]:
@@ -146,31 +162,86 @@ class WeightPacks:
 
 
 class BackwardBatch:
-    """Shared zero-initialised weight-gradient workspace (one fill) + deferred, batched un-packing (one launch)."""
+    """Shared zero-initialised weight-gradient workspace (one fill) + deferred, batched un-packing (one launch per
+    flush) into ONE flat gradient buffer laid out in backward order, so that a prefix of it can be handed to the
+    gradient all-reduce while the rest of the backward pass is still running."""
 
     def __init__(self, device, sizes: Dict[str, int]):
         total = sum(sizes.values())
         self.flat = torch.zeros(max(total, 1), device=device, dtype=torch.float32)
-        self.offsets, off = {}, 0
-        for k, n in sizes.items():
-            self.offsets[k] = (off, n)
-            off += n
+        self.gflat = torch.empty(max(total, 1), device=device, dtype=torch.float32)
+        self.sizes = dict(sizes)
+        self.offsets: Dict[str, Tuple[int, int]] = {}
+        self.cursor = 0          # bump allocator: offsets follow the order of first use (= backward order)
+        self.flushed = 0
         self.jobs = []
+        self.pending = []        # (work handle, tensor) of all-reduces in flight
 
     def dwp(self, key: str, shape) -> Optional[torch.Tensor]:
-        if key not in self.offsets:
+        if key not in self.sizes:
             return None
+        if key not in self.offsets:
+            self.offsets[key] = (self.cursor, self.sizes[key])
+            self.cursor += self.sizes[key]
         off, n = self.offsets[key]
         return self.flat[off:off + n].view(shape)
 
     def defer_unpack(self, dwp: torch.Tensor, weight_shape, rows_from_d0: bool) -> torch.Tensor:
-        out = torch.empty(weight_shape, device=dwp.device, dtype=torch.float32)
+        off = dwp.storage_offset() - self.flat.storage_offset()
+        n = dwp.numel()
+        if 0 <= off and off + n <= self.gflat.numel() and dwp.untyped_storage().data_ptr() == self.flat.untyped_storage().data_ptr():
+            out = self.gflat[off:off + n].view(weight_shape)
+        else:
+            out = torch.empty(weight_shape, device=dwp.device, dtype=torch.float32)
         self.jobs.append((dwp, rows_from_d0, out))
         return out
 
-    def flush(self) -> None:
-        ops.unpack_wgrad_multi(self.jobs)
-        self.jobs = []
+    def flush(self) -> Tuple[int, int]:
+        """Un-pack what has been deferred so far; returns the [start, end) range of the flat gradient buffer that became
+        final with this flush."""
+        if self.jobs:
+            ops.unpack_wgrad_multi(self.jobs)
+            self.jobs = []
+        rng = (self.flushed, self.cursor)
+        self.flushed = self.cursor
+        return rng
+
+    # --- gradient all-reduce inside the backward pass (data parallelism) -------------------------------
+    def reduce_async(self) -> None:
+        """Flush and start the all-reduce of the gradients finished so far on the collective's own stream."""
+        start, end = self.flush()
+        gfn = _REDUCER.get("grad_fn")
+        if gfn is None or end <= start:
+            return
+        t = self.gflat[start:end]
+        self.pending.append((gfn(t), t))
+        reserve = int(_REDUCER.get("sm_reserve", 0))
+        if reserve > 0:          # persistent kernels launched from now on leave room for the collective's CTAs
+            ops.set_sm_reserve(reserve)
+
+    def reduce_finish(self, small: List[torch.Tensor]) -> bool:
+        """Flush the rest, all-reduce it together with the small gradients (BatchNorm, biases, stem / head weights) and
+        wait for everything in flight.  Returns True when the gradients have been summed over the ranks."""
+        gfn = _REDUCER.get("grad_fn")
+        start, end = self.flush()
+        if gfn is None:
+            return False
+        if end > start:
+            t = self.gflat[start:end]
+            self.pending.append((gfn(t), t))
+        small = [g for g in small if g is not None]
+        flat_small = None
+        if small:
+            flat_small = torch.cat([g.reshape(-1) for g in small])
+            self.pending.append((gfn(flat_small), flat_small))
+        for work, _t in self.pending:
+            work.wait()
+        self.pending = []
+        if int(_REDUCER.get("sm_reserve", 0)) > 0:
+            ops.set_sm_reserve(0)
+        if flat_small is not None:
+            torch._foreach_copy_(small, [c.view_as(g) for c, g in zip(flat_small.split([g.numel() for g in small]), small)])
+        return True
 
 
 def _is_stem(s: "ConvSpec", x_view: GsbView, x_keep) -> bool:
@@ -212,7 +283,12 @@ class ConvBNAct:
         scale = shift = mean = invstd = None
         if self.has_bn:
             gamma, beta, rm, rv, nbt = bn
-            if training:
+            fused_ok, peer, pworld = _fused_stats_mode()
+            if training and stats is not None and fused_ok:
+                count = count * pworld
+                scale, shift, mean, invstd = ops.bn_stats_finalize(stats, rows, s.cout, count, gamma, beta, rm, rv, nbt,
+                                                                   BN_MOMENTUM, BN_EPS, peer)
+            elif training:
                 sums = ops.bn_reduce_partials(stats, rows, s.cout) if stats is not None else ops.bn_reduce(y)
                 sums, count = _sync_stats(sums, count)
                 scale, shift, mean, invstd = ops.bn_finalize(sums, count, gamma, beta, rm, rv, nbt, BN_MOMENTUM, BN_EPS,
@@ -251,7 +327,12 @@ class ConvBNAct:
         act2 = self.act2 if self.act2 is not None else ACT_NONE
         sums = None
         mean = invstd = None
-        if train_bn:
+        fused_ok, peer, _pw = _fused_stats_mode()
+        if train_bn and fused_ok:
+            sums, dgamma, dbeta = ops.bn_bwd_stats(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2,
+                                                   sv.drop_seed, sv.drop_mask, need_bn, peer)
+            mean, invstd = sv.mean, sv.invstd
+        elif train_bn:
             sums = ops.bn_bwd_reduce(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2,
                                      sv.drop_seed, sv.drop_mask)
             if need_bn:   # parameter gradients from the LOCAL sums (the gradient all-reduce adds the other ranks)

@@ -34,6 +34,7 @@ class ProgramFunction(torch.autograd.Function):
         ctx.tape = tape if need_any else None
         ctx.names = names
         ctx.n_in = n_in
+        ctx.param_refs = params if need_any else None
         return out
 
     @staticmethod
@@ -48,6 +49,11 @@ class ProgramFunction(torch.autograd.Function):
         dxs = (dx,) if n_in == 1 else tuple(dx)
         dxs = tuple(d if nx else None for d, nx in zip(dxs, need_x))
         grads = [G.get(k) if need[k] else None for k in ctx.names]
+        if G.get("__reduced__") and ctx.param_refs is not None:
+            # data parallelism: the program summed these gradients over the ranks inside backward (parallel.py)
+            for p_, g_ in zip(ctx.param_refs, grads):
+                if g_ is not None:
+                    p_._gsb_grad_reduced = True
         return (None, None, None, None, None, *dxs, *grads)
 
 

@@ -260,6 +260,56 @@ def bn_bwd_apply(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, sums, coun
                                   float(count), _ref(view_nhwc(dx)), ptr(dgamma), ptr(dbeta), _s(x)), "bn_bwd_apply")
 
 
+def set_sm_reserve(n: int) -> int:
+    """SMs set aside for a concurrently running collective (persistent kernels size their grids for the rest)."""
+    return int(load().gsb_set_sm_reserve(int(n)))
+
+
+def _peer_args(peer):
+    """peer = None (single GPU) or {"regions": [...], "rank": r, "world": n} from parallel.py."""
+    if peer is None:
+        return None, 0, 1
+    world = int(peer["world"])
+    arr = (C.c_void_p * world)(*[C.c_void_p(r) for r in peer["regions"]])
+    return arr, int(peer["rank"]), world
+
+
+def bn_stats_finalize(partial: torch.Tensor, rows: int, c: int, count: float, gamma, beta, running_mean, running_var, nbt,
+                      momentum: float, eps: float, peer=None):
+    """Statistic rows -> (cross-rank sum over the peer regions) -> scale, shift, mean, invstd + running statistics:
+    one launch.  ``count`` is the GLOBAL element count per channel."""
+    dev = partial.device
+    scale = torch.empty(c, device=dev, dtype=torch.float32)
+    shift = torch.empty(c, device=dev, dtype=torch.float32)
+    mean = torch.empty(c, device=dev, dtype=torch.float32)
+    invstd = torch.empty(c, device=dev, dtype=torch.float32)
+    arr, rank, world = _peer_args(peer)
+    check(load().gsb_bn_stats_finalize(ptr(partial), int(rows), c, float(count), arr, rank, world, ptr(gamma), ptr(beta),
+                                       ptr(running_mean), ptr(running_var), ptr(nbt), float(momentum), float(eps), ptr(scale),
+                                       ptr(shift), ptr(mean), ptr(invstd), _s(partial)), "bn_stats_finalize")
+    return scale, shift, mean, invstd
+
+
+def bn_bwd_stats(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, drop_seed=0, drop_mask=None, want_param_grads=True,
+                 peer=None):
+    """[sum dy, sum dy*xhat] in two launches: per-block rows, then totals + dgamma / dbeta (local) + cross-rank sum.
+    -> (global sums fp64 [2c], dgamma, dbeta)."""
+    v = view_nhwc(x)
+    ws = _bn_ws(v, x.device)
+    rows = C.c_int(0)
+    v2 = view_nhwc(dA2) if dA2 is not None else None
+    check(load().gsb_bn_bwd_partial(_ref(v), _ref(view_nhwc(dA1)), _ref(v2), ptr(scale), ptr(shift), ptr(mean), ptr(invstd),
+                                    act1, act2, int(drop_seed), ptr(drop_mask), ptr(ws), ws.numel() * 4, C.byref(rows),
+                                    _s(x)), "bn_bwd_partial")
+    sums = torch.empty(2 * v.c, device=x.device, dtype=torch.float64)
+    dgamma = torch.empty(v.c, device=x.device, dtype=torch.float32) if want_param_grads else None
+    dbeta = torch.empty(v.c, device=x.device, dtype=torch.float32) if want_param_grads else None
+    arr, rank, world = _peer_args(peer)
+    check(load().gsb_bn_bwd_stats(ptr(ws), rows.value, v.c, arr, rank, world, ptr(dgamma), ptr(dbeta), 0, ptr(sums), _s(x)),
+          "bn_bwd_stats")
+    return sums, dgamma, dbeta
+
+
 def bn_param_grad(sums: torch.Tensor, c: int):
     dgamma = torch.empty(c, device=sums.device, dtype=torch.float32)
     dbeta = torch.empty(c, device=sums.device, dtype=torch.float32)

@@ -50,9 +50,19 @@ def _setup_peer_memory(group) -> None:
     _GROUP["peer"] = {"regions": regions, "max": ops.peer_max_elems(), "own": region, "world": world}
 
 
-def init_data_parallel(sync_bn: bool = True, group=None, backend: Optional[str] = None) -> int:
+def _allreduce_async(t: torch.Tensor):
+    return dist.all_reduce(t, op=dist.ReduceOp.SUM, group=_GROUP["pg"], async_op=True)
+
+
+def init_data_parallel(sync_bn: bool = True, group=None, backend: Optional[str] = None,
+                       overlap_grad_allreduce: bool = False) -> int:
     """Initialise (if needed) torch.distributed from the torchrun env and install the cross-rank reducers.
-    Returns the world size."""
+    Returns the world size.
+
+    overlap_grad_allreduce: the U-Net program all-reduces its gradients INSIDE backward -- the decoder + bottleneck
+    bucket (72 % of the bytes) as soon as it is final, on the collective's stream, under the encoder backward; the
+    rest at the end -- and marks the parameters so that ``allreduce_gradients`` skips them.  Use it with
+    ``loss.backward()`` training loops (``torch.autograd.grad`` callers keep it off)."""
     if not dist.is_initialized():
         if "RANK" not in os.environ:
             engine.install_reducer(None, 1, False)
@@ -68,7 +78,14 @@ def init_data_parallel(sync_bn: bool = True, group=None, backend: Optional[str] 
     _GROUP["rank"] = dist.get_rank(group)
     if backend != "gloo" and torch.cuda.is_available():
         _setup_peer_memory(group)
-    engine.install_reducer(_allreduce_sum if _GROUP["world"] > 1 else None, _GROUP["world"], sync_bn)
+    peer = _GROUP["peer"]
+    peer_arg = None
+    if peer is not None and peer["world"] == _GROUP["world"] and _GROUP["world"] > 1:
+        peer_arg = {"regions": peer["regions"], "rank": _GROUP["rank"], "world": _GROUP["world"]}
+    multi = _GROUP["world"] > 1
+    engine.install_reducer(_allreduce_sum if multi else None, _GROUP["world"], sync_bn, peer_arg,
+                           grad_fn=_allreduce_async if (multi and overlap_grad_allreduce) else None,
+                           sm_reserve=int(os.environ.get("GSB_OVERLAP_SM_RESERVE", "16")) if multi and overlap_grad_allreduce else 0)
     return _GROUP["world"]
 
 
@@ -99,7 +116,13 @@ def allreduce_gradients(params: Iterable[torch.Tensor]) -> None:
     """Sum gradients over ranks (averaging is folded into the optimiser's grad_scale = 1/world)."""
     if _GROUP["world"] <= 1:
         return
-    grads = [p.grad for p in params if p.grad is not None]
+    grads = []
+    for p in params:
+        if getattr(p, "_gsb_grad_reduced", False):   # already summed inside backward (overlap_grad_allreduce)
+            p._gsb_grad_reduced = False
+            continue
+        if p.grad is not None:
+            grads.append(p.grad)
     if not grads:
         return
     # one flat bucket per dtype: a single NCCL all-reduce instead of one latency-bound launch per parameter

@@ -240,11 +240,18 @@ class UNetProgram:
             # route through the 2x2 max-pool into the skip gradient already holding the concat part
             ops.maxpool2_bwd(skips[i], dpooled, dskip[i], accumulate=True)
             dcur = dskip[i]
+            if i == 3:
+                # decoder + bottleneck weight gradients (72 % of the parameters) are final: start their all-reduce now,
+                # it runs on the collective's stream under the remaining (most expensive) part of the backward pass
+                batch.reduce_async()
         dx = None
         dxv = None
         if need_dx:
             dx = torch.empty_like(tape["x"])
             dxv = view_nchw(dx)
         self.inc.backward(tape["inc"], dcur, G, need, need_dx, dx_view=dxv, dx_out=dx, batch=batch)
-        batch.flush()
+        gbase = batch.gflat.untyped_storage().data_ptr()
+        small = [g for g in G.values() if g is not None and g.untyped_storage().data_ptr() != gbase]
+        if batch.reduce_finish(small):
+            G["__reduced__"] = True     # functions.ProgramFunction marks the parameters; parallel.allreduce_gradients skips them
         return dx, G

@@ -9,8 +9,8 @@ Mirrors running_files/train_end2end_jsrt.py:186-200 without the host round trip:
 ``synth_image_postprocess`` is bit-exact against torch / torchvision on the CPU (batch min-max normalise, uint8
 quantise, per-image histogram equalisation, gamma 0.5, / 255).  The mask warp restates the imgaug chain as ONE composed
 affine map per image (flip, crop-and-pad as a scale + shift, scale, translate, rotate, shear; order drawn per image)
-sampled bilinearly with zero fill; imgaug itself is not available offline, so that part is pinned by oracle/augment_oracle.py
-only ("parity unpinned" against imgaug's own resampling).
+sampled bilinearly with zero fill; imgaug itself is not available offline, so that part is pinned only by the CPU
+restatement used in tests/test_augment.py ("parity unpinned" against imgaug's own resampling).
 """
 from __future__ import annotations
 

@@ -27,7 +27,7 @@ for prec in ("fp32", "bf16"):
         return loss.detach(), {k: p.grad.clone() for k, p in net.named_parameters()}, net
     parallel.shutdown()
     ref_loss, ref_g, _ = run(x, y)                         # single-rank, full global batch
-    world = parallel.init_data_parallel(sync_bn=True)
+    world = parallel.init_data_parallel(sync_bn=True, overlap_grad_allreduce=os.environ.get("DP_OVERLAP", "0") == "1")
     lo, hi = parallel.shard_batch(GB)
     loss, g, net = run(x[lo:hi], y[lo:hi])
     parallel.allreduce_gradients(net.parameters())
