@@ -300,7 +300,7 @@ constexpr int kHeadMaxC = 8;
 // CT = compile-time bound on the class count (2 or 8): weights of the lane's 8 channels live in registers when
 // K == 64 (OutConv of the U-Net), pixel arithmetic is 32-bit.
 template <typename T, int CT>
-__global__ void __launch_bounds__(256) head_fwd_kernel(const T* __restrict__ x, int64_t xld, unsigned P, unsigned HW, int K, int C,
+__global__ void __launch_bounds__(256, 4) head_fwd_kernel(const T* __restrict__ x, int64_t xld, unsigned P, unsigned HW, int K, int C,
                                                       const float* __restrict__ w /*[C][K]*/, const float* __restrict__ bias,
                                                       float* __restrict__ out /*[N][C][HW]*/) {
   extern __shared__ float sw[];  // [C][K]
@@ -314,49 +314,62 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(const T* __restrict__ x, 
 #pragma unroll
     for (int j = 0; j < 8; ++j) wr[c][j] = c < C ? sw[c * K + sub * 8 + j] : 0.f;
   const unsigned stride_p = (gridDim.x * blockDim.x) >> 3;
-  // warp-uniform trip count (the shuffles below need all 32 lanes): iterate on the warp's first pixel
-  for (unsigned pw = (blockIdx.x * blockDim.x + (threadIdx.x & ~31u)) >> 3; pw < P; pw += stride_p) {
-    const unsigned p = pw + ((threadIdx.x & 31) >> 3);
-    const bool valid = p < P;
-    float acc[CT];
+  // warp-uniform trip count (the shuffles below need all 32 lanes): iterate on the warp's first pixel.  Two pixels
+  // (pw, pw + stride_p) are in flight per thread: with one the kernel sat at 2.7 TB/s waiting on its single 16-byte load
+  // (ncu profiles/r01n: issue 57 %, long-scoreboard stalls).
+  for (unsigned pw = (blockIdx.x * blockDim.x + (threadIdx.x & ~31u)) >> 3; pw < P; pw += 2 * stride_p) {
+    unsigned pp[2];
+    bool valid[2];
+    float v[2][8], acc[2][CT];
 #pragma unroll
-    for (int c = 0; c < CT; ++c) acc[c] = 0.f;
-    if (valid) {
-      float v[8];
-      Vec8<T>::load(x + (int64_t)p * xld + sub * 8, v);
+    for (int u = 0; u < 2; ++u) {
+      pp[u] = pw + u * stride_p + ((threadIdx.x & 31) >> 3);
+      valid[u] = pp[u] < P;
+      if (valid[u]) Vec8<T>::load(x + (int64_t)pp[u] * xld + sub * 8, v[u]);
+    }
 #pragma unroll
-      for (int c = 0; c < CT; ++c)
+    for (int u = 0; u < 2; ++u) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[c] = fmaf(v[j], wr[c][j], acc[c]);
-      for (int ch = 1; ch < chunks; ++ch) {
-        const int k0 = ch * 64 + sub * 8;
-        Vec8<T>::load(x + (int64_t)p * xld + k0, v);
+      for (int c = 0; c < CT; ++c) acc[u][c] = 0.f;
+      if (valid[u]) {
 #pragma unroll
         for (int c = 0; c < CT; ++c)
-          if (c < C) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[c] = fmaf(v[j], sw[c * K + k0 + j], acc[c]);
-          }
+          for (int j = 0; j < 8; ++j) acc[u][c] = fmaf(v[u][j], wr[c][j], acc[u][c]);
+        for (int ch = 1; ch < chunks; ++ch) {
+          const int k0 = ch * 64 + sub * 8;
+          float t[8];
+          Vec8<T>::load(x + (int64_t)pp[u] * xld + k0, t);
+#pragma unroll
+          for (int c = 0; c < CT; ++c)
+            if (c < C) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) acc[u][c] = fmaf(t[j], sw[c * K + k0 + j], acc[u][c]);
+            }
+        }
       }
     }
 #pragma unroll
-    for (int c = 0; c < CT; ++c) {
-      acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 1);
-      acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 2);
-      acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 4);
-    }
-    if (valid && sub == 0) {
-      const unsigned n = p / HW, r = p - n * HW;
+    for (int u = 0; u < 2; ++u) {
 #pragma unroll
-      for (int c = 0; c < CT; ++c)
-        if (c < C) out[((int64_t)n * C + c) * HW + r] = acc[c] + (bias ? bias[c] : 0.f);
+      for (int c = 0; c < CT; ++c) {
+        acc[u][c] += __shfl_xor_sync(0xffffffffu, acc[u][c], 1);
+        acc[u][c] += __shfl_xor_sync(0xffffffffu, acc[u][c], 2);
+        acc[u][c] += __shfl_xor_sync(0xffffffffu, acc[u][c], 4);
+      }
+      if (valid[u] && sub == 0) {
+        const unsigned n = pp[u] / HW, r = pp[u] - n * HW;
+#pragma unroll
+        for (int c = 0; c < CT; ++c)
+          if (c < C) out[((int64_t)n * C + c) * HW + r] = acc[u][c] + (bias ? bias[c] : 0.f);
+      }
     }
   }
 }
 
 // head backward: dx[p][k] = sum_c d[p][c] w[c][k];  dw[c][k] += sum_p d[p][c] x[p][k];  db[c] += sum_p d[p][c]
 template <typename T, int CT>
-__global__ void __launch_bounds__(256) head_bwd_kernel(const T* __restrict__ x, int64_t xld, unsigned P, unsigned HW, int K, int C,
+__global__ void __launch_bounds__(256, 4) head_bwd_kernel(const T* __restrict__ x, int64_t xld, unsigned P, unsigned HW, int K, int C,
                                                       const float* __restrict__ w, const float* __restrict__ dout,
                                                       T* __restrict__ dx, int64_t dxld, float* __restrict__ dw,
                                                       float* __restrict__ db) {
@@ -383,25 +396,38 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(const T* __restrict__ x, 
       wr[c][j] = c < C ? sw[c * K + g * 8 + j] : 0.f;
     }
   }
-  for (unsigned p = blockIdx.x * lanes + lane; p < P; p += gridDim.x * lanes) {
-    const unsigned n = p / HW, r = p - n * HW;
-    float d[CT];
+  // two pixels in flight per thread (one left the kernel latency-bound at 3.3 TB/s, ncu profiles/r01n)
+  const unsigned pstep = gridDim.x * lanes;
+  for (unsigned p0 = blockIdx.x * lanes + lane; p0 < P; p0 += 2 * pstep) {
+    float d[2][CT], v[2][8];
+    bool valid[2];
 #pragma unroll
-    for (int c = 0; c < CT; ++c) d[c] = c < C ? __ldg(dout + ((int64_t)n * C + c) * HW + r) : 0.f;
-    float v[8], o[8];
-    if (dw != nullptr) Vec8<T>::load(x + (int64_t)p * xld + g * 8, v);
+    for (int u = 0; u < 2; ++u) {
+      const unsigned p = p0 + u * pstep;
+      valid[u] = p < P;
+      const unsigned n = valid[u] ? p / HW : 0, r = valid[u] ? p - n * HW : 0;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) o[j] = 0.f;
+      for (int c = 0; c < CT; ++c) d[u][c] = (valid[u] && c < C) ? __ldg(dout + ((int64_t)n * C + c) * HW + r) : 0.f;
 #pragma unroll
-    for (int c = 0; c < CT; ++c) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        o[j] = fmaf(d[c], wr[c][j], o[j]);
-        if (dw != nullptr) aw[c][j] = fmaf(d[c], v[j], aw[c][j]);
-      }
-      ab[c] += d[c];
+      for (int j = 0; j < 8; ++j) v[u][j] = 0.f;
+      if (valid[u] && dw != nullptr) Vec8<T>::load(x + (int64_t)p * xld + g * 8, v[u]);
     }
-    if (dx != nullptr) Vec8<T>::store(dx + (int64_t)p * dxld + g * 8, o);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = 0.f;
+#pragma unroll
+      for (int c = 0; c < CT; ++c) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          o[j] = fmaf(d[u][c], wr[c][j], o[j]);
+          if (dw != nullptr) aw[c][j] = fmaf(d[u][c], v[u][j], aw[c][j]);
+        }
+        ab[c] += d[u][c];
+      }
+      if (valid[u] && dx != nullptr) Vec8<T>::store(dx + (int64_t)(p0 + u * pstep) * dxld + g * 8, o);
+    }
   }
   if (dw != nullptr) {
 #pragma unroll

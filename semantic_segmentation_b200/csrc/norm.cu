@@ -6,6 +6,7 @@
 // bf16) of a pixel and a fixed channel group, so per-channel parameters live in registers.
 // Algorithmic bytes: reduce = 1 read; act = 1 read + 1 (or 2) writes; bwd_reduce = 2 (3) reads;
 // bwd_apply = 2 (3) reads + 1 write -- at the storage dtype.
+#include <stdlib.h>
 #include "common.cuh"
 #include "peer.cuh"
 
@@ -133,6 +134,78 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
   for (int i = 0; i < 8; ++i) {
     red[(lane * 2 + 0) * C + c0 + i] = s0[i];
     red[(lane * 2 + 1) * C + c0 + i] = s1[i];
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < 2 * C; j += kThreads) {
+    float acc = 0.f;
+    for (int l = 0; l < lanes; ++l) acc += red[l * 2 * C + j];
+    partial[(int64_t)blockIdx.x * 2 * C + j] = acc;
+  }
+}
+
+// Backward statistics of the U-Net layer shape (bf16, ReLU, one gradient stream, no dropout): sum dy, sum dy*xhat with
+// dy = dA * [scale*y + shift > 0].  The generic kernel held 76 registers (3 blocks / SM) with ONE 16-byte load pair in
+// flight per thread and sat at 69 % of HBM bandwidth stalled on the long scoreboard (ncu profiles/r01n).  Here the
+// loads stay packed (uint4) until they are consumed, KU pixel rows are in flight per thread, and the normalisation is
+// applied after the loop:  sum dy*xhat = invstd * (sum dy*y - mean * sum dy)  (mean / invstd leave the loop; the
+// per-thread sums cover ~100 pixels of bf16 data, so the subtraction costs nothing measurable in accuracy).
+template <int KU>
+__global__ void __launch_bounds__(kThreads, 4) bn_bwd_reduce_relu_bf16_kernel(
+    const __nv_bfloat16* __restrict__ x, int64_t xld, const __nv_bfloat16* __restrict__ dA, int64_t dld, int64_t P, int C,
+    const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
+    const float* __restrict__ invstd, float* __restrict__ partial) {
+  extern __shared__ float red[];  // [lanes][2][C]
+  const int G = C >> 3;
+  const int lanes = kThreads / G;
+  const int g = threadIdx.x % G, lane = threadIdx.x / G;
+  const int c0 = g * 8;
+  float s0[8], s1[8], sc[8], sh[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s0[i] = s1[i] = 0.f;
+  load_param8(scale, c0, sc, 1.f);
+  load_param8(shift, c0, sh, 0.f);
+  const int64_t step = (int64_t)gridDim.x * lanes;
+  const __nv_bfloat16* xp = x + c0;
+  const __nv_bfloat16* dp = dA + c0;
+  for (int64_t p0 = (int64_t)blockIdx.x * lanes + lane; p0 < P; p0 += step * KU) {
+    uint4 rv[KU], ra[KU];
+#pragma unroll
+    for (int u = 0; u < KU; ++u) {
+      const int64_t p = p0 + u * step;
+      if (p < P) {
+        rv[u] = *reinterpret_cast<const uint4*>(xp + p * xld);
+        ra[u] = *reinterpret_cast<const uint4*>(dp + p * dld);
+      } else {
+        rv[u] = make_uint4(0, 0, 0, 0);
+        ra[u] = make_uint4(0, 0, 0, 0);  // dA = 0 contributes nothing
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < KU; ++u) {
+      const uint32_t* wv = reinterpret_cast<const uint32_t*>(&rv[u]);
+      const uint32_t* wa = reinterpret_cast<const uint32_t*>(&ra[u]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float v0 = __uint_as_float(wv[i] << 16), v1 = __uint_as_float(wv[i] & 0xffff0000u);
+        const float a0 = __uint_as_float(wa[i] << 16), a1 = __uint_as_float(wa[i] & 0xffff0000u);
+        const float d0 = fmaf(v0, sc[2 * i], sh[2 * i]) > 0.f ? a0 : 0.f;
+        const float d1 = fmaf(v1, sc[2 * i + 1], sh[2 * i + 1]) > 0.f ? a1 : 0.f;
+        s0[2 * i] += d0;
+        s0[2 * i + 1] += d1;
+        s1[2 * i] = fmaf(d0, v0, s1[2 * i]);
+        s1[2 * i + 1] = fmaf(d1, v1, s1[2 * i + 1]);
+      }
+    }
+  }
+  {
+    float mu[8], is[8];
+    load_param8(mean, c0, mu, 0.f);
+    load_param8(invstd, c0, is, 1.f);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      red[(lane * 2 + 0) * C + c0 + i] = s0[i];
+      red[(lane * 2 + 1) * C + c0 + i] = is[i] * fmaf(-mu[i], s0[i], s1[i]);
+    }
   }
   __syncthreads();
   for (int j = threadIdx.x; j < 2 * C; j += kThreads) {
@@ -443,6 +516,15 @@ __global__ void __launch_bounds__(1024) bn_stats_fused_kernel(const float* __res
   }
 }
 
+static bool relu_stats_fast_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("GSB_BN_BWD_FAST2");
+    v = (e != nullptr && e[0] == '0') ? 0 : 1;
+  }
+  return v != 0;
+}
+
 static int grid_for(int64_t P, int lanes) {
   int64_t want = (P + lanes - 1) / lanes;
   int64_t cap = (int64_t)num_sms() * 8;
@@ -555,7 +637,10 @@ static int bn_bwd_partial_launch(const gsb_view* x, const gsb_view* dA1, const g
   const bool fast = act1 == GSB_ACT_RELU && d2.ptr == nullptr && drop_seed == 0 && drop_mask == nullptr && scale && shift &&
                     mean && invstd;
   if (x->dtype == GSB_BF16) {
-    if (fast)
+    if (fast && relu_stats_fast_enabled())
+      bn_bwd_reduce_relu_bf16_kernel<2><<<grid, kThreads, smem, to_stream(s)>>>(
+          (const __nv_bfloat16*)x->ptr, x->sw, (const __nv_bfloat16*)dA1->ptr, dA1->sw, P, C, scale, shift, mean, invstd, partial);
+    else if (fast)
       bn_reduce_kernel<__nv_bfloat16, 1, true><<<grid, kThreads, smem, to_stream(s)>>>(
           pv(x), pv(dA1), d2, P, C, scale, shift, mean, invstd, act1, act2, drop_seed, drop_mask, partial);
     else
