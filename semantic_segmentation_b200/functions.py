@@ -30,6 +30,11 @@ class ProgramFunction(torch.autograd.Function):
         need_any = any(ctx.needs_input_grad)
         xin = xs[0].detach() if n_in == 1 else tuple(x.detach() for x in xs)
         out, tape = program.forward(xin, P, buffers, training, need_any, extra)
+        # The tape may hold the output tensor itself (e.g. the generator's tanh output, needed by its backward).  The
+        # object returned from here gets grad_fn = this node, so returning the SAME object would close a reference
+        # cycle node -> tape -> output -> node and keep the whole tape (1.7 GiB for the generator at batch 8) alive until
+        # the cyclic garbage collector runs.  Return an alias instead.
+        out = tuple(o.detach() for o in out) if isinstance(out, (tuple, list)) else out.detach()
         ctx.program = program
         ctx.tape = tape if need_any else None
         ctx.names = names

@@ -22,6 +22,19 @@ def _s(t: torch.Tensor) -> int:
     return stream_ptr(t.device)
 
 
+_ARRAY_TYPES = {}
+
+
+def _atype(ctype, n: int):
+    """ctypes array types are created on demand and only weakly cached: keep them, or every call leaves a few cyclic
+    type objects behind for the garbage collector."""
+    key = (ctype, n)
+    t = _ARRAY_TYPES.get(key)
+    if t is None:
+        t = _ARRAY_TYPES[key] = ctype * n
+    return t
+
+
 def _ref(v: Optional[GsbView]):
     return C.byref(v) if v is not None else None
 
@@ -69,11 +82,11 @@ def unpack_wgrad(dwp: torch.Tensor, shape: Tuple[int, int, int, int], rows_from_
 
 
 def _ptr_array(ts):
-    return (C.c_void_p * len(ts))(*[t.data_ptr() for t in ts])
+    return _atype(C.c_void_p, len(ts))(*[t.data_ptr() for t in ts])
 
 
 def _int_array(vs):
-    return (C.c_int * len(vs))(*[int(v) for v in vs])
+    return _atype(C.c_int, len(vs))(*[int(v) for v in vs])
 
 
 def pack_weight_multi(jobs, dtype: torch.dtype) -> None:
@@ -270,7 +283,7 @@ def _peer_args(peer):
     if peer is None:
         return None, 0, 1
     world = int(peer["world"])
-    arr = (C.c_void_p * world)(*[C.c_void_p(r) for r in peer["regions"]])
+    arr = _atype(C.c_void_p, world)(*[C.c_void_p(r) for r in peer["regions"]])
     return arr, int(peer["rank"]), world
 
 
@@ -429,7 +442,7 @@ def rmsprop_step(p, g, square_avg, mom_buf, lr, alpha, eps, weight_decay, moment
 def rmsprop_step_multi(ps, gs, sqs, bufs, lr, alpha, eps, weight_decay, momentum, grad_scale=1.0) -> None:
     if not ps:
         return
-    n = (C.c_int64 * len(ps))(*[p.numel() for p in ps])
+    n = _atype(C.c_int64, len(ps))(*[p.numel() for p in ps])
     check(load().gsb_rmsprop_step_multi(len(ps), _ptr_array(ps), _ptr_array(gs), _ptr_array(sqs),
                                         _ptr_array(bufs) if momentum > 0 else None, n, lr, alpha, eps, weight_decay, momentum,
                                         grad_scale, _s(ps[0])), "rmsprop_step_multi")
@@ -438,7 +451,7 @@ def rmsprop_step_multi(ps, gs, sqs, bufs, lr, alpha, eps, weight_decay, momentum
 def adam_step_multi(ps, gs, ms, vs, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0) -> None:
     if not ps:
         return
-    n = (C.c_int64 * len(ps))(*[p.numel() for p in ps])
+    n = _atype(C.c_int64, len(ps))(*[p.numel() for p in ps])
     check(load().gsb_adam_step_multi(len(ps), _ptr_array(ps), _ptr_array(gs), _ptr_array(ms), _ptr_array(vs), n, lr, beta1,
                                      beta2, eps, weight_decay, int(step), grad_scale, _s(ps[0])), "adam_step_multi")
 
@@ -502,7 +515,7 @@ def peer_max_elems() -> int:
 def peer_allreduce_f64(buf: torch.Tensor, regions, rank: int, world: int) -> None:
     """In-place sum of a contiguous fp64 device vector over the ranks whose regions are given in rank order."""
     assert buf.dtype == torch.float64 and buf.is_contiguous() and buf.is_cuda
-    arr = (C.c_void_p * world)(*[C.c_void_p(r) for r in regions])
+    arr = _atype(C.c_void_p, world)(*[C.c_void_p(r) for r in regions])
     check(load().gsb_peer_allreduce_f64(ptr(buf), buf.numel(), arr, rank, world, _s(buf)), "peer_allreduce_f64")
 
 
