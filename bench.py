@@ -296,12 +296,47 @@ def run_ours(args):
     launches = launches_per_step * args.steps if graph is not None else int(lib.gsb_launch_count() - l0)
     clocks = sampler.stop() if rank == 0 else None
 
-    def e2e_step():
-        static_x.copy_(x_host, non_blocking=True)      # pinned host -> device, every step
-        static_y.copy_(y_host, non_blocking=True)
-        return float(run_step().item())                # device -> host read of the step's loss
+    # End to end: every step's inputs come from pinned host memory and its loss is read back to the host.  The copy of
+    # step i+1 is enqueued on a copy stream into the other staging buffer BEFORE the host blocks on the loss of step i
+    # (what a prefetching input pipeline does), so it runs under step i's kernels; the first copy is exposed.  Exactly
+    # `steps` host->device copies and `steps` device->host reads happen inside the timed region.
+    copy_stream = torch.cuda.Stream(device=dev)
+    stage = [(torch.empty_like(static_x), torch.empty_like(static_y)) for _ in range(2)]
+    h2d_done = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
+    state = {"i": 0, "total": 0}
 
-    e2e_step()
+    def enqueue_h2d(slot):
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[slot])          # the staging buffer has been read by its previous user
+            stage[slot][0].copy_(x_host, non_blocking=True)
+            stage[slot][1].copy_(y_host, non_blocking=True)
+            h2d_done[slot].record(copy_stream)
+
+    def e2e_reset(total):
+        state["i"], state["total"] = 0, total
+        cur = torch.cuda.current_stream(dev)
+        for ev in consumed:
+            ev.record(cur)
+
+    def e2e_step():
+        i, cur = state["i"], torch.cuda.current_stream(dev)
+        slot = i & 1
+        if i == 0:
+            enqueue_h2d(slot)                                # nothing to hide the first copy behind
+        cur.wait_event(h2d_done[slot])
+        static_x.copy_(stage[slot][0], non_blocking=True)    # staging -> the graph's static inputs (device copy)
+        static_y.copy_(stage[slot][1], non_blocking=True)
+        consumed[slot].record(cur)
+        loss = run_step()
+        if i + 1 < state["total"]:
+            enqueue_h2d(slot ^ 1)                            # next step's inputs, under this step's kernels
+        state["i"] = i + 1
+        return float(loss.item())                            # device -> host read of the step's loss
+
+    e2e_reset(2)
+    e2e_step(); e2e_step()
+    e2e_reset(args.steps)
     t_e2e = timed(e2e_step, args.steps)
     images = per * world * args.steps
     value, e2e = images / t_dev, images / t_e2e
@@ -316,7 +351,7 @@ def run_ours(args):
             "data": "synthetic",
             "config": {"workload": "U-Net(n_channels=1,n_classes=2,bilinear) 256x256 train step: fwd + CE+Dice + bwd + RMSprop",
                        "global_batch": per * world, "per_gpu_batch": per, "parallelism": "dp%d" % world,
-                       "sync_bn": bool(world > 1 and not args.no_sync_bn), "cuda_graph": graph is not None,
+                       "sync_bn": bool(world > 1 and not args.no_sync_bn), "cuda_graph": graph is not None, "e2e_inputs": "pinned host -> device every step, double-buffered prefetch on a copy stream",
                        "grad_allreduce": ("overlapped_in_backward" if not args.no_overlap else "after_backward") if world > 1 else None,
                        "l2": "per-step working set (activations+gradients, >1 GB per GPU) exceeds the 126 MB L2; no flush needed"},
             "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": int(x_host.numel() * 4 + y_host.numel() * 8) * world,

@@ -131,7 +131,11 @@ __device__ __forceinline__ float stored_value(float v) { return v; }
 template <>
 __device__ __forceinline__ float stored_value<__nv_bfloat16>(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
 
-template <typename T, int PX, int K, int S>
+// NOACT: no activation follows inside this kernel (the U-Net stem feeds BatchNorm) -> the per-element activation switch
+// folds away.  Accumulation and statistics use the packed fp32x2 pipe (FFMA2 / FADD2, sm_100): the kernel is
+// instruction-bound (ncu profiles/r01n: 57 % issue at 25 % occupancy, ALU pipe above the FMA pipe), and the packed
+// forms halve its arithmetic instruction count.
+template <typename T, int PX, int K, int S, bool NOACT>
 __global__ void __launch_bounds__(256, 2) stem_fwd_fast_kernel(const float* __restrict__ x, int N, int Cin, int H, int W,
                                                            const float* __restrict__ w, const float* __restrict__ bias,
                                                            T* __restrict__ y, int64_t yld, int OH, int OW, int Cout, int pad,
@@ -150,22 +154,24 @@ __global__ void __launch_bounds__(256, 2) stem_fwd_fast_kernel(const float* __re
   const unsigned G = (unsigned)Cout >> 3, XQ = (unsigned)(OW + PX - 1) / PX;
   const unsigned total = (unsigned)N * (unsigned)OH * XQ * G;
   const unsigned g = threadIdx.x % G;  // fixed per thread: the grid stride is a multiple of G
-  float s0[8], s1[8], b8[8];
+  float2 s0[4], s1[4], b2[4];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    s0[j] = s1[j] = 0.f;
-    b8[j] = bias ? bias[g * 8 + j] : 0.f;
+  for (int j = 0; j < 4; ++j) {
+    s0[j] = s1[j] = make_float2(0.f, 0.f);
+    b2[j] = bias ? make_float2(bias[g * 8 + 2 * j], bias[g * 8 + 2 * j + 1]) : make_float2(0.f, 0.f);
   }
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const unsigned q = i / G;
     const unsigned xq = q % XQ, row = q / XQ;
     const int oy = (int)(row % (unsigned)OH), n = (int)(row / (unsigned)OH);
     const int ox0 = (int)xq * PX;
-    float acc[PX][8];
+    float2 acc[PX][4];
 #pragma unroll
     for (int px = 0; px < PX; ++px)
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[px][j] = b8[j];
+      for (int j = 0; j < 4; ++j) acc[px][j] = b2[j];
+    const int ixb = ox0 * S - pad;
+    const bool x_inside = ixb >= 0 && ixb + SPAN <= W;
     for (int ci = 0; ci < Cin; ++ci) {
 #pragma unroll
       for (int ky = 0; ky < K; ++ky) {
@@ -173,24 +179,30 @@ __global__ void __launch_bounds__(256, 2) stem_fwd_fast_kernel(const float* __re
         if (iy < 0 || iy >= H) continue;
         const float* xr = x + (((int64_t)n * Cin + ci) * H + iy) * W;
         float xv[SPAN];
-        const int ixb = ox0 * S - pad;
+        if (x_inside) {
 #pragma unroll
-        for (int e = 0; e < SPAN; ++e) {
-          const int ix = ixb + e;
-          xv[e] = (ix >= 0 && ix < W) ? __ldg(xr + ix) : 0.f;
+          for (int e = 0; e < SPAN; ++e) xv[e] = __ldg(xr + ixb + e);
+        } else {
+#pragma unroll
+          for (int e = 0; e < SPAN; ++e) {
+            const int ix = ixb + e;
+            xv[e] = (ix >= 0 && ix < W) ? __ldg(xr + ix) : 0.f;
+          }
         }
         const float* wr = sw + ((ci * K + ky) * K) * Cout + g * 8;
 #pragma unroll
         for (int kx = 0; kx < K; ++kx) {
           const float4 w0 = *reinterpret_cast<const float4*>(wr + kx * Cout);
           const float4 w1 = *reinterpret_cast<const float4*>(wr + kx * Cout + 4);
+          const float2 wa = make_float2(w0.x, w0.y), wb = make_float2(w0.z, w0.w);
+          const float2 wc = make_float2(w1.x, w1.y), wd = make_float2(w1.z, w1.w);
 #pragma unroll
           for (int px = 0; px < PX; ++px) {
-            const float v = xv[px * S + kx];
-            acc[px][0] = fmaf(v, w0.x, acc[px][0]); acc[px][1] = fmaf(v, w0.y, acc[px][1]);
-            acc[px][2] = fmaf(v, w0.z, acc[px][2]); acc[px][3] = fmaf(v, w0.w, acc[px][3]);
-            acc[px][4] = fmaf(v, w1.x, acc[px][4]); acc[px][5] = fmaf(v, w1.y, acc[px][5]);
-            acc[px][6] = fmaf(v, w1.z, acc[px][6]); acc[px][7] = fmaf(v, w1.w, acc[px][7]);
+            const float2 v = make_float2(xv[px * S + kx], xv[px * S + kx]);
+            acc[px][0] = __ffma2_rn(v, wa, acc[px][0]);
+            acc[px][1] = __ffma2_rn(v, wb, acc[px][1]);
+            acc[px][2] = __ffma2_rn(v, wc, acc[px][2]);
+            acc[px][3] = __ffma2_rn(v, wd, acc[px][3]);
           }
         }
       }
@@ -199,15 +211,19 @@ __global__ void __launch_bounds__(256, 2) stem_fwd_fast_kernel(const float* __re
 #pragma unroll
     for (int px = 0; px < PX; ++px) {
       if (ox0 + px < OW) {
+        float o[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[px][j] = act_fwd(acc[px][j], act);
-        Vec8<T>::store(y + (pbase + px) * yld + g * 8, acc[px]);
+        for (int j = 0; j < 4; ++j) {
+          o[2 * j] = NOACT ? acc[px][j].x : act_fwd(acc[px][j].x, act);
+          o[2 * j + 1] = NOACT ? acc[px][j].y : act_fwd(acc[px][j].y, act);
+        }
+        Vec8<T>::store(y + (pbase + px) * yld + g * 8, o);
         if (stats != nullptr) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float r = stored_value<T>(acc[px][j]);
-            s0[j] += r;
-            s1[j] = fmaf(r, r, s1[j]);
+          for (int j = 0; j < 4; ++j) {
+            const float2 r = make_float2(stored_value<T>(o[2 * j]), stored_value<T>(o[2 * j + 1]));
+            s0[j] = __fadd2_rn(s0[j], r);
+            s1[j] = __ffma2_rn(r, r, s1[j]);
           }
         }
       }
@@ -215,9 +231,11 @@ __global__ void __launch_bounds__(256, 2) stem_fwd_fast_kernel(const float* __re
   }
   if (stats != nullptr) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      atomicAdd(&red[g * 8 + j], s0[j]);
-      atomicAdd(&red[Cout + g * 8 + j], s1[j]);
+    for (int j = 0; j < 4; ++j) {
+      atomicAdd(&red[g * 8 + 2 * j], s0[j].x);
+      atomicAdd(&red[g * 8 + 2 * j + 1], s0[j].y);
+      atomicAdd(&red[Cout + g * 8 + 2 * j], s1[j].x);
+      atomicAdd(&red[Cout + g * 8 + 2 * j + 1], s1[j].y);
     }
     __syncthreads();
     for (int i = threadIdx.x; i < 2 * Cout; i += blockDim.x) stats[(int64_t)blockIdx.x * 2 * Cout + i] = red[i];
@@ -237,53 +255,65 @@ __global__ void __launch_bounds__(256, 2) stem_wgrad_fast_kernel(const float* __
   const unsigned g = threadIdx.x % G, lane = threadIdx.x / G;
   for (int i = threadIdx.x; i < (int)G * K * K * 8; i += blockDim.x) sacc[i] = 0.f;
   __syncthreads();
-  float acc[K * K][8];
+  float2 acc[K * K][4];  // packed fp32x2 accumulators (FFMA2): half the arithmetic instructions of the scalar form
 #pragma unroll
   for (int t = 0; t < K * K; ++t)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[t][j] = 0.f;
+    for (int j = 0; j < 4; ++j) acc[t][j] = make_float2(0.f, 0.f);
   const unsigned items = (unsigned)N * (unsigned)OH * XQ;
   for (unsigned q = blockIdx.x * lanes + lane; q < items; q += gridDim.x * lanes) {
     const unsigned xq = q % XQ, row = q / XQ;
     const int oy = (int)(row % (unsigned)OH), n = (int)(row / (unsigned)OH);
     const int ox0 = (int)xq * PX;
     const int64_t pbase = ((int64_t)n * OH + oy) * OW + ox0;
-    float d[PX][8];
+    float2 d[PX][4];
 #pragma unroll
     for (int px = 0; px < PX; ++px) {
+      float t8[8];
       if (ox0 + px < OW) {
-        Vec8<T>::load(dy + (pbase + px) * dld + g * 8, d[px]);
+        Vec8<T>::load(dy + (pbase + px) * dld + g * 8, t8);
       } else {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) d[px][j] = 0.f;
+        for (int j = 0; j < 8; ++j) t8[j] = 0.f;
       }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) d[px][j] = make_float2(t8[2 * j], t8[2 * j + 1]);
     }
+    const int ixb = ox0 * S - pad;
+    const bool x_inside = ixb >= 0 && ixb + SPAN <= W;
 #pragma unroll
     for (int ky = 0; ky < K; ++ky) {
       const int iy = oy * S - pad + ky;
       if (iy < 0 || iy >= H) continue;
       const float* xr = x + (((int64_t)n * Cin + ci) * H + iy) * W;
       float xv[SPAN];
-      const int ixb = ox0 * S - pad;
+      if (x_inside) {
 #pragma unroll
-      for (int e = 0; e < SPAN; ++e) {
-        const int ix = ixb + e;
-        xv[e] = (ix >= 0 && ix < W) ? __ldg(xr + ix) : 0.f;
+        for (int e = 0; e < SPAN; ++e) xv[e] = __ldg(xr + ixb + e);
+      } else {
+#pragma unroll
+        for (int e = 0; e < SPAN; ++e) {
+          const int ix = ixb + e;
+          xv[e] = (ix >= 0 && ix < W) ? __ldg(xr + ix) : 0.f;
+        }
       }
 #pragma unroll
       for (int kx = 0; kx < K; ++kx)
 #pragma unroll
         for (int px = 0; px < PX; ++px) {
-          const float v = xv[px * S + kx];
+          const float2 v = make_float2(xv[px * S + kx], xv[px * S + kx]);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[ky * K + kx][j] = fmaf(v, d[px][j], acc[ky * K + kx][j]);
+          for (int j = 0; j < 4; ++j) acc[ky * K + kx][j] = __ffma2_rn(v, d[px][j], acc[ky * K + kx][j]);
         }
     }
   }
 #pragma unroll
   for (int t = 0; t < K * K; ++t)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) atomicAdd(&sacc[(g * K * K + t) * 8 + j], acc[t][j]);
+    for (int j = 0; j < 4; ++j) {
+      atomicAdd(&sacc[(g * K * K + t) * 8 + 2 * j], acc[t][j].x);
+      atomicAdd(&sacc[(g * K * K + t) * 8 + 2 * j + 1], acc[t][j].y);
+    }
   __syncthreads();
   const int taps = Cin * K * K;
   for (int i = threadIdx.x; i < (int)G * K * K * 8; i += blockDim.x) {
@@ -490,11 +520,14 @@ extern "C" int gsb_stem_conv_fwd(const float* x, int n, int cin, int h, int w, c
     const int64_t items = (int64_t)y->n * y->h * ((y->w + PX - 1) / PX) * (cout / 8);
     int grid = grid_cap((items + 255) / 256, 8);
     size_t smem = ((size_t)cin * k * k * cout + 2 * cout) * sizeof(float);
-    if (k3) {
-      EDGE_DISPATCH_T(y->dtype, stem_fwd_fast_kernel<T, PX, 3, 1><<<grid, 256, smem, to_stream(s)>>>(
+    if (k3 && act == GSB_ACT_NONE) {
+      EDGE_DISPATCH_T(y->dtype, stem_fwd_fast_kernel<T, PX, 3, 1, true><<<grid, 256, smem, to_stream(s)>>>(
+                                    x, n, cin, h, w, weight, bias, (T*)y->ptr, y->sw, y->h, y->w, cout, pad, act, stats_partial));
+    } else if (k3) {
+      EDGE_DISPATCH_T(y->dtype, stem_fwd_fast_kernel<T, PX, 3, 1, false><<<grid, 256, smem, to_stream(s)>>>(
                                     x, n, cin, h, w, weight, bias, (T*)y->ptr, y->sw, y->h, y->w, cout, pad, act, stats_partial));
     } else {
-      EDGE_DISPATCH_T(y->dtype, stem_fwd_fast_kernel<T, PX, 4, 2><<<grid, 256, smem, to_stream(s)>>>(
+      EDGE_DISPATCH_T(y->dtype, stem_fwd_fast_kernel<T, PX, 4, 2, false><<<grid, 256, smem, to_stream(s)>>>(
                                     x, n, cin, h, w, weight, bias, (T*)y->ptr, y->sw, y->h, y->w, cout, pad, act, stats_partial));
     }
     if (stats_partial && stats_rows) *stats_rows = grid;

@@ -257,9 +257,19 @@ __global__ void __launch_bounds__(256) upsample2_fwd_rows_kernel(const T* __rest
         Vec8<T>::load(r0 + (int64_t)i1 * xld + g * 8, v01);
         Vec8<T>::load(r1 + (int64_t)i0 * xld + g * 8, v10);
         Vec8<T>::load(r1 + (int64_t)i1 * xld + g * 8, v11);
+        // packed fp32x2 arithmetic (FMUL2 / FFMA2): the kernel is issue-bound (ncu profiles/r01n: 77 % issue active)
+        const float2 a0 = make_float2(lx0, lx0), a1 = make_float2(lx1, lx1);
+        const float2 b0 = make_float2(ly.l0, ly.l0), b1 = make_float2(ly.l1, ly.l1);
 #pragma unroll
-        for (int k = 0; k < 8; ++k)
-          o[k] = ly.l0 * (lx0 * v00[k] + lx1 * v01[k]) + ly.l1 * (lx0 * v10[k] + lx1 * v11[k]);
+        for (int k = 0; k < 4; ++k) {
+          const float2 top = __ffma2_rn(a1, make_float2(v01[2 * k], v01[2 * k + 1]),
+                                        __fmul2_rn(a0, make_float2(v00[2 * k], v00[2 * k + 1])));
+          const float2 bot = __ffma2_rn(a1, make_float2(v11[2 * k], v11[2 * k + 1]),
+                                        __fmul2_rn(a0, make_float2(v10[2 * k], v10[2 * k + 1])));
+          const float2 r = __ffma2_rn(b1, bot, __fmul2_rn(b0, top));
+          o[2 * k] = r.x;
+          o[2 * k + 1] = r.y;
+        }
       }
       Vec8<T>::store(orow + (int64_t)ox * old + g * 8, o);
     }
@@ -314,7 +324,9 @@ __global__ void __launch_bounds__(256) upsample2_bwd_rows_kernel(const T* __rest
         cx[c] = ox;
         cw[c] = wx;
       }
-      float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      float2 acc2[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) acc2[k] = make_float2(0.f, 0.f);
 #pragma unroll
       for (int r = 0; r < 6; ++r) {
         const float wy = s_wy[r];
@@ -326,10 +338,17 @@ __global__ void __launch_bounds__(256) upsample2_bwd_rows_kernel(const T* __rest
             float v[8];
             Vec8<T>::load(rowp + (int64_t)cx[c] * dld, v);
             const float wgt = wy * cw[c];
+            const float2 w2 = make_float2(wgt, wgt);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) acc[k] = fmaf(wgt, v[k], acc[k]);
+            for (int k = 0; k < 4; ++k) acc2[k] = __ffma2_rn(w2, make_float2(v[2 * k], v[2 * k + 1]), acc2[k]);
           }
         }
+      }
+      float acc[8];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        acc[2 * k] = acc2[k].x;
+        acc[2 * k + 1] = acc2[k].y;
       }
       Vec8<T>::store(dx + ((int64_t)row * w + ix) * xld + g * 8, acc);
     }
