@@ -106,6 +106,27 @@ with torch.no_grad():
 parallel.broadcast_parameters(m)
 assert float(m.weight.sum()) == 0.0
 parallel.shutdown()
+# --- gradient all-reduce inside backward (bucketed, first bucket asynchronous) -- host logic over gloo
+world = parallel.init_data_parallel(sync_bn=True, backend="gloo", overlap_grad_allreduce=True)
+assert engine._REDUCER["grad_fn"] is not None and engine._REDUCER["sm_reserve"] == 16
+bb = engine.BackwardBatch(torch.device("cpu"), {"late": 6, "early": 4})
+assert bb.dwp("early", (2, 2)).shape == (2, 2) and bb.offsets["early"] == (0, 4)      # offsets follow the order of use
+bb.gflat[:4] = float(r + 1)
+bb.reduce_async()                                      # bucket 1 = [0, 4): in flight, SM reserve raised
+assert bb.flushed == 4 and len(bb.pending) == 1
+bb.dwp("late", (6,)); bb.gflat[4:10] = 10.0 * (r + 1)
+small = [torch.full((3,), float(r)), None, torch.full((2, 2), 2.0 * r)]
+assert bb.reduce_finish(small) is True and not bb.pending
+assert bb.gflat[:4].tolist() == [3.0] * 4 and bb.gflat[4:10].tolist() == [30.0] * 6
+assert small[0].tolist() == [1.0] * 3 and small[2].flatten().tolist() == [2.0] * 4
+from semantic_segmentation_b200 import ops
+assert ops.set_sm_reserve(0) == 0                      # reduce_finish restored the full SM count
+p1 = torch.nn.Parameter(torch.zeros(2)); p1.grad = torch.full((2,), float(r + 1)); p1._gsb_grad_reduced = True
+p2 = torch.nn.Parameter(torch.zeros(2)); p2.grad = torch.full((2,), float(r + 1))
+parallel.allreduce_gradients([p1, p2])                 # p1 was summed inside backward: skipped, flag cleared
+assert p1.grad.tolist() == [r + 1.0] * 2 and p2.grad.tolist() == [3.0, 3.0] and p1._gsb_grad_reduced is False
+parallel.shutdown()
+assert engine._REDUCER["grad_fn"] is None
 print("rank", r, "ok")
 '''
 
