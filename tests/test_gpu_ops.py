@@ -418,6 +418,25 @@ def test_batched_pack_and_unpack_match_single():
         assert torch.equal(out, s)
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(5, 70, 3, 3), (64, 1, 4, 4), (33, 129, 8, 8), (512, 256, 1, 1), (16, 32, 2, 2), (130, 17, 4, 4)])
+def test_pack_unpack_against_torch_permute(shape):
+    """Tiled transposes (csrc/layout.cu) against torch.permute: ragged tiles in every dimension, 1..64 taps,
+    both row conventions, bf16 and fp32 packs, accumulate mode of the un-pack."""
+    g = torch.Generator().manual_seed(sum(shape))
+    d0, d1, kh, kw = shape
+    w = torch.randn(shape, generator=g).to(DEV)
+    for rfd in (True, False):
+        ref = w.reshape(d0, d1, kh * kw).permute(2, 0, 1) if rfd else w.reshape(d0, d1, kh * kw).permute(2, 1, 0)
+        for dt in (torch.float32, torch.bfloat16):
+            assert torch.equal(ops.pack_weight(w, rfd, dt), ref.contiguous().to(dt))
+        back = ops.unpack_wgrad(ref.contiguous(), shape, rfd)
+        assert torch.equal(back, w)
+        acc = torch.ones(shape, device=DEV)
+        ops.unpack_wgrad(ref.contiguous(), shape, rfd, out=acc)
+        assert torch.equal(acc, w + 1.0)
+
+
 THIN = [  # kind, k, stride, pad, cin, cout, n, h, w : 1..4 channels on one side (thin_conv.cu)
     ("convT", 8, 2, 3, 128, 1, 2, 12, 10),
     ("conv", 4, 1, 1, 512, 1, 2, 9, 9),
