@@ -40,6 +40,8 @@ struct TcParams {
   int act;
   const float* bias;
   float* stats;                   // [m_tiles][2][cout] or null
+  int ks_split;                   // > 1: split-K -- a tile's K steps are spread over ks_split CTAs, fp32 atomics into ws
+  float* ws;                      // [N*H*W of the tiled space][cout] fp32, zeroed (split-K only)
 };
 
 template <int BN>
@@ -98,21 +100,22 @@ conv_tc_fprop_kernel(const __grid_constant__ TcMaps maps, const __grid_constant_
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-        const int nt = tile % p.n_tiles, mt = tile / p.n_tiles;
+        const int part = tile % p.ks_split, tl = tile / p.ks_split;
+        const int ks0 = (int)((long long)part * ksteps / p.ks_split), ks1 = (int)((long long)(part + 1) * ksteps / p.ks_split);
+        const int nt = tl % p.n_tiles, mt = tl / p.n_tiles;
         const int tx = mt % p.tiles_x, r = mt / p.tiles_x;
         const int x0 = tx * p.tw, y0 = (r % p.tiles_y) * p.th, n0 = (r / p.tiles_y) * p.tn;
-        for (int t = 0; t < taps.ntaps; ++t) {
+        for (int ks = ks0; ks < ks1; ++ks) {
+          const int t = ks / kblocks, kb = ks - t * kblocks;
           const void* amap = &maps.in[taps.map[t]];
           const int xx = x0 + taps.dx[t], yy = y0 + taps.dy[t];
           const int wrow = (int)taps.wtap[t] * p.cout + nt * BN;
-          for (int kb = 0; kb < kblocks; ++kb) {
-            mbar_wait(&empty[stage], phase ^ 1u);
-            mbar_expect_tx(&full[stage], Cfg::STAGE);
-            uint8_t* sa = smem + stage * Cfg::STAGE;
-            tma_load_4d(amap, &full[stage], sa, kb * 64, xx, yy, n0);
-            tma_load_2d(&maps.w, &full[stage], sa + Cfg::A_BYTES, kb * 64, wrow);
-            if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1u; }
-          }
+          mbar_wait(&empty[stage], phase ^ 1u);
+          mbar_expect_tx(&full[stage], Cfg::STAGE);
+          uint8_t* sa = smem + stage * Cfg::STAGE;
+          tma_load_4d(amap, &full[stage], sa, kb * 64, xx, yy, n0);
+          tma_load_2d(&maps.w, &full[stage], sa + Cfg::A_BYTES, kb * 64, wrow);
+          if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1u; }
         }
       }
     }
@@ -125,7 +128,9 @@ conv_tc_fprop_kernel(const __grid_constant__ TcMaps maps, const __grid_constant_
         mbar_wait(&tempty[acc], acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
-        for (int ks = 0; ks < ksteps; ++ks) {
+        const int part = tile % p.ks_split;
+        const int nks = (int)((long long)(part + 1) * ksteps / p.ks_split) - (int)((long long)part * ksteps / p.ks_split);
+        for (int ks = 0; ks < nks; ++ks) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE);
@@ -147,13 +152,33 @@ conv_tc_fprop_kernel(const __grid_constant__ TcMaps maps, const __grid_constant_
     const int et = threadIdx.x - 64;   // 0..127
     uint32_t acc = 0, acc_phase = 0;
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x) {
-      const int nt = tile % p.n_tiles, mt = tile / p.n_tiles;
+      const int tl = tile / p.ks_split;
+      const int nt = tl % p.n_tiles, mt = tl / p.n_tiles;
       const int tx = mt % p.tiles_x, r = mt / p.tiles_x;
       const int x0 = tx * p.tw, y0 = (r % p.tiles_y) * p.th, n0 = (r / p.tiles_y) * p.tn;
       const int px = row % p.tw, py = (row / p.tw) % p.th, pn = row / (p.tw * p.th);
       const bool valid = (x0 + px < p.W) && (y0 + py < p.H) && (n0 + pn < p.N);
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
+      if (p.ks_split > 1) {
+        // split-K: this CTA holds a partial sum over its K range -> fp32 atomics into the workspace; bias, activation,
+        // rounding and the store to the output view happen in splitk_finalize_kernel
+        float* wrow = p.ws + (((int64_t)(n0 + pn) * p.H + (y0 + py)) * p.W + (x0 + px)) * p.cout + nt * BN;
+#pragma unroll 1
+        for (int ch = 0; ch < BN / 32; ++ch) {
+          uint32_t v[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + ch * 32, v);
+          if (valid) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) atomicAdd(wrow + ch * 32 + i, __uint_as_float(v[i]));
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&tempty[acc]);
+        acc ^= 1u;
+        if (acc == 0) acc_phase ^= 1u;
+        continue;
+      }
       if (et == 0) tma_store_wait_read();  // previous tile's store has finished reading s_out
       named_bar_sync(1, 128);
 #pragma unroll 1
@@ -230,6 +255,42 @@ conv_tc_fprop_kernel(const __grid_constant__ TcMaps maps, const __grid_constant_
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
   }
+}
+
+// Split-K epilogue: ws[pixel][cout] fp32 -> (+bias) -> activation -> bf16 -> output view (8 channels per thread).
+__global__ void __launch_bounds__(256) splitk_finalize_kernel(const float* __restrict__ ws, int64_t pixels, int W, int H, int cout,
+                                                             const float* __restrict__ bias, int act, __nv_bfloat16* __restrict__ out,
+                                                             int64_t sw, int64_t sh, int64_t sn) {
+  const int G = cout >> 3;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < pixels * G; i += (int64_t)gridDim.x * blockDim.x) {
+    const int g = (int)(i % G);
+    const int64_t pix = i / G;
+    const int x = (int)(pix % W), y = (int)((pix / W) % H);
+    const int64_t n = pix / ((int64_t)W * H);
+    const float4 a = *reinterpret_cast<const float4*>(ws + pix * cout + g * 8);
+    const float4 b = *reinterpret_cast<const float4*>(ws + pix * cout + g * 8 + 4);
+    float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = act_fwd(v[j] + (bias ? __ldg(bias + g * 8 + j) : 0.f), act);
+    Vec8<__nv_bfloat16>::store(out + n * sn + y * sh + x * sw + g * 8, v);
+  }
+}
+
+// Library-owned scratch of the split-K path (allocated once per process on first use outside stream capture).
+constexpr size_t kSplitKScratchBytes = (size_t)8 << 20;
+static float* splitk_scratch(cudaStream_t st) {
+  static float* buf = nullptr;
+  if (buf == nullptr) {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return nullptr;
+    void* p = nullptr;
+    if (cudaMalloc(&p, kSplitKScratchBytes) != cudaSuccess) {
+      cudaGetLastError();
+      return nullptr;
+    }
+    buf = static_cast<float*>(p);
+  }
+  return buf;
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -455,10 +516,41 @@ static int fprop_launch(const SubView& outv, const SubView* shifted, int nmaps, 
   p.n_tiles = cout / BN;
   p.num_tiles = p.tiles_x * p.tiles_y * p.tiles_z * p.n_tiles;
   p.act = act; p.bias = bias; p.stats = stats;
+  p.ks_split = 1; p.ws = nullptr;
   if (stats_rows) *stats_rows = p.tiles_x * p.tiles_y * p.tiles_z;
-  int grid = p.num_tiles < num_sms_avail() ? p.num_tiles : num_sms_avail();
-  if (BN == 128) return launch_tc(conv_tc_fprop_kernel<128>, grid, 1, FpropCfg<128>::SMEM, maps, taps, p, st);
-  return launch_tc(conv_tc_fprop_kernel<64>, grid, 1, FpropCfg<64>::SMEM, maps, taps, p, st);
+  // Deep generator / discriminator levels: a handful of tiles would stream the whole weight tensor through 4..32 SMs
+  // (2.3 ms per Pix2Pix step, ncu profiles/r01o).  Split the K loop over enough CTAs to fill the GPU instead.
+  const int ksteps = taps.ntaps * (cin / 64);
+  const int64_t pixels = outv.N * outv.H * outv.W;
+  const int sms = num_sms_avail();
+  static const bool splitk_on = []() { const char* e = getenv("GSB_TC_SPLITK"); return !(e && e[0] == '0'); }();
+  if (splitk_on && p.num_tiles * 2 <= sms && ksteps >= 8 && (size_t)pixels * cout * sizeof(float) <= kSplitKScratchBytes &&
+      cout % 8 == 0) {
+    float* ws = splitk_scratch(st);
+    if (ws != nullptr) {
+      int split = sms / p.num_tiles;
+      if (split > ksteps / 4) split = ksteps / 4;
+      if (split > 1) {
+        p.ks_split = split;
+        p.ws = ws;
+        p.num_tiles *= split;
+        p.stats = nullptr;
+        if (stats_rows) *stats_rows = 0;   // no fused statistics on this path: the caller reduces the stored output
+        cudaError_t e = cudaMemsetAsync(ws, 0, (size_t)pixels * cout * sizeof(float), st);
+        GSB_REQUIRE(e == cudaSuccess, "conv_tc split-K memset failed: %s", cudaGetErrorString(e));
+      }
+    }
+  }
+  int grid = p.num_tiles < sms ? p.num_tiles : sms;
+  int rc = BN == 128 ? launch_tc(conv_tc_fprop_kernel<128>, grid, 1, FpropCfg<128>::SMEM, maps, taps, p, st)
+                     : launch_tc(conv_tc_fprop_kernel<64>, grid, 1, FpropCfg<64>::SMEM, maps, taps, p, st);
+  if (rc != 0 || p.ks_split == 1) return rc;
+  int64_t items = pixels * (cout / 8);
+  int fgrid = (int)((items + 255) / 256);
+  if (fgrid > num_sms() * 8) fgrid = num_sms() * 8;
+  splitk_finalize_kernel<<<fgrid, 256, 0, st>>>(p.ws, pixels, (int)outv.W, (int)outv.H, cout, bias, act,
+                                                (__nv_bfloat16*)const_cast<void*>(outv.ptr), outv.sw, outv.sh, outv.sn);
+  return check_launch("conv_tc split-K finalize");
 }
 
 static int floor_div(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
