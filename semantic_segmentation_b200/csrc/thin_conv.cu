@@ -181,7 +181,11 @@ __global__ void __launch_bounds__(256) thin_scatter_kernel(TView in, const void*
 // (blockIdx.y = pass) accumulate in registers; block reduction in shared memory, one atomic per output and block.
 // Relation (forward layer): CONV  q = (p + pad - k) / stride ;  CONVT  q = p * stride - pad + k.
 // ---------------------------------------------------------------------------------------------------------
-template <typename T, int TP>
+// KWT > 0: kernel width known at compile time (4 or 8: the PatchGAN head and the merged 8x8 up-convolution) -- the tap ->
+// (ky, kx) split of the unrolled tap loop is then constant and the per-tap index arithmetic collapses to two adds.
+// Accumulation in packed fp32x2 (FFMA2): the kernel is bound by the FMA pipe (128 ci x 64 taps per pixel, 516 us per launch
+// for the generator's output layer, ncu profiles/r01o).
+template <typename T, int TP, int KWT>
 __global__ void __launch_bounds__(256) thin_wgrad_kernel(TView in, TView dout, float* __restrict__ dwp, int mode, int KH, int KW,
                                                         int stride, int pad, int co) {
   extern __shared__ float sacc[];  // [TP][Cin]
@@ -191,24 +195,30 @@ __global__ void __launch_bounds__(256) thin_wgrad_kernel(TView in, TView dout, f
   __syncthreads();
   const unsigned G = (unsigned)Cin >> 3, lanes = blockDim.x / G;
   const unsigned g = threadIdx.x % G, lane = threadIdx.x / G;
-  float acc[TP][8];
+  float2 acc[TP][4];
 #pragma unroll
   for (int t = 0; t < TP; ++t)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[t][j] = 0.f;
+    for (int j = 0; j < 4; ++j) acc[t][j] = make_float2(0.f, 0.f);
   const unsigned P = (unsigned)in.N * in.H * in.W;
   const T* ip = reinterpret_cast<const T*>(in.ptr);
+  const int ky0 = KWT > 0 ? tap0 / KWT : 0;   // TP is a multiple of KWT: a pass covers whole kernel rows
   for (unsigned p = blockIdx.x * lanes + lane; p < P; p += gridDim.x * lanes) {
     const int ix = (int)(p % (unsigned)in.W);
     const unsigned r = p / (unsigned)in.W;
     const int iy = (int)(r % (unsigned)in.H), n = (int)(r / (unsigned)in.H);
     float v[8];
     Vec8<T>::load(ip + (int64_t)n * in.sn + (int64_t)iy * in.sh + (int64_t)ix * in.sw + g * 8, v);
+    float2 v2[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v2[j] = make_float2(v[2 * j], v[2 * j + 1]);
+    const int64_t dbase = (int64_t)n * dout.sn + (int64_t)co * dout.sc;
 #pragma unroll
     for (int t = 0; t < TP; ++t) {
       const int tap = tap0 + t;
       if (tap < taps) {
-        const int ky = tap / KW, kx = tap - ky * KW;
+        const int ky = KWT > 0 ? ky0 + t / KWT : tap / KW;
+        const int kx = KWT > 0 ? t % KWT : tap - ky * KW;
         int qy, qx;
         bool ok;
         if (mode == GSB_MODE_CONV) {
@@ -220,10 +230,10 @@ __global__ void __launch_bounds__(256) thin_wgrad_kernel(TView in, TView dout, f
           ok = qy >= 0 && qx >= 0 && qy < dout.H && qx < dout.W;
         }
         if (ok) {
-          const float d = ld_elem(dout.ptr, (int64_t)n * dout.sn + (int64_t)qy * dout.sh + (int64_t)qx * dout.sw + (int64_t)co * dout.sc,
-                                  dout.dtype);
+          const float d = ld_elem(dout.ptr, dbase + (int64_t)qy * dout.sh + (int64_t)qx * dout.sw, dout.dtype);
+          const float2 d2 = make_float2(d, d);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[t][j] = fmaf(d, v[j], acc[t][j]);
+          for (int j = 0; j < 4; ++j) acc[t][j] = __ffma2_rn(d2, v2[j], acc[t][j]);
         }
       }
     }
@@ -231,7 +241,10 @@ __global__ void __launch_bounds__(256) thin_wgrad_kernel(TView in, TView dout, f
 #pragma unroll
   for (int t = 0; t < TP; ++t)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) atomicAdd(&sacc[t * Cin + g * 8 + j], acc[t][j]);
+    for (int j = 0; j < 4; ++j) {
+      atomicAdd(&sacc[t * Cin + g * 8 + 2 * j], acc[t][j].x);
+      atomicAdd(&sacc[t * Cin + g * 8 + 2 * j + 1], acc[t][j].y);
+    }
   __syncthreads();
   for (int i = threadIdx.x; i < TP * Cin; i += blockDim.x) {
     const int t = i / Cin, ci = i - t * Cin;
@@ -312,18 +325,24 @@ int thin_wgrad_try(const gsb_view* in, const gsb_view* dout, float* dwp, const g
   if (!(dout->c <= 4 && wide_ok(in)) || in->c > 1024 || 256 % (in->c / 8) != 0) return 0;
   const int64_t P = num_pixels(in);
   if (P <= 0 || P >= ((int64_t)1 << 31)) return 0;
-  constexpr int TP = 16;
-  const int taps = g->kh * g->kw, passes = (taps + TP - 1) / TP;
+  // taps per pass: 8 (one row of the merged 8x8 up-convolution: 64 accumulators, two blocks per SM) or 16
+  const int TPr = (g->kw == 8 && in->dtype == GSB_BF16) ? 8 : 16;
+  const int taps = g->kh * g->kw, passes = (taps + TPr - 1) / TPr;
   const int G = in->c / 8, lanes = 256 / G;
   const int grid = grid_sm((P + lanes - 1) / lanes, 4);
-  const size_t smem = (size_t)TP * in->c * sizeof(float);
+  const size_t smem = (size_t)TPr * in->c * sizeof(float);
   TView vi = tv(in), vd = tv(dout);
   for (int co = 0; co < dout->c; ++co) {
-    if (in->dtype == GSB_BF16)
-      thin_wgrad_kernel<__nv_bfloat16, TP><<<dim3(grid, passes), 256, smem, st>>>(vi, vd, dwp, g->mode, g->kh, g->kw, g->stride,
-                                                                                  g->pad, co);
-    else
-      thin_wgrad_kernel<float, TP><<<dim3(grid, passes), 256, smem, st>>>(vi, vd, dwp, g->mode, g->kh, g->kw, g->stride, g->pad, co);
+#define GSB_THIN_WG(TT, TPV, KWT)                                                                                          \
+  thin_wgrad_kernel<TT, TPV, KWT><<<dim3(grid, passes), 256, smem, st>>>(vi, vd, dwp, g->mode, g->kh, g->kw, g->stride, g->pad, co)
+    if (in->dtype == GSB_BF16) {
+      if (g->kw == 8) GSB_THIN_WG(__nv_bfloat16, 8, 8);
+      else if (g->kw == 4) GSB_THIN_WG(__nv_bfloat16, 16, 4);
+      else GSB_THIN_WG(__nv_bfloat16, 16, 0);
+    } else {
+      GSB_THIN_WG(float, 16, 0);
+    }
+#undef GSB_THIN_WG
   }
   return check_launch("thin_wgrad", dout->c) ? -1 : 1;
 }
