@@ -76,14 +76,24 @@ __global__ void merge_upconv_kernel(const float* __restrict__ w4, const float* _
                                     int64_t pairs, int cout, float* __restrict__ wm, float* bm) {
   float w[3];
   softmax3(alpha, w);
-  const int64_t total = pairs * 64;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    int kx = (int)(i & 7), ky = (int)((i >> 3) & 7);
-    int64_t pr = i >> 6;
-    float v = w[2] * w8[i];
-    if (ky >= 1 && ky < 7 && kx >= 1 && kx < 7) v += w[1] * w6[pr * 36 + (ky - 1) * 6 + (kx - 1)];
-    if (ky >= 2 && ky < 6 && kx >= 2 && kx < 6) v += w[0] * w4[pr * 16 + (ky - 2) * 4 + (kx - 2)];
-    wm[i] = v;
+  const int64_t rows_total = pairs * 8;   // one thread = one kernel row (8 taps) of one (ci, co) pair
+  for (int64_t rix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; rix < rows_total; rix += (int64_t)gridDim.x * blockDim.x) {
+    const int ky = (int)(rix & 7);
+    const int64_t pr = rix >> 3, i = rix * 8;
+    const float4 wa = *reinterpret_cast<const float4*>(w8 + i), wb = *reinterpret_cast<const float4*>(w8 + i + 4);
+    float v[8] = {w[2] * wa.x, w[2] * wa.y, w[2] * wa.z, w[2] * wa.w, w[2] * wb.x, w[2] * wb.y, w[2] * wb.z, w[2] * wb.w};
+    if (ky >= 1 && ky < 7) {
+      const int64_t j = pr * 36 + (ky - 1) * 6;
+      const float2 u0 = *reinterpret_cast<const float2*>(w6 + j), u1 = *reinterpret_cast<const float2*>(w6 + j + 2),
+                   u2 = *reinterpret_cast<const float2*>(w6 + j + 4);
+      v[1] += w[1] * u0.x; v[2] += w[1] * u0.y; v[3] += w[1] * u1.x; v[4] += w[1] * u1.y; v[5] += w[1] * u2.x; v[6] += w[1] * u2.y;
+    }
+    if (ky >= 2 && ky < 6) {
+      const float4 u = *reinterpret_cast<const float4*>(w4 + pr * 16 + (ky - 2) * 4);
+      v[2] += w[0] * u.x; v[3] += w[0] * u.y; v[4] += w[0] * u.z; v[5] += w[0] * u.w;
+    }
+    *reinterpret_cast<float4*>(wm + i) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(wm + i + 4) = make_float4(v[4], v[5], v[6], v[7]);
   }
   if (bm != nullptr && blockIdx.x == 0)
     for (int c = threadIdx.x; c < cout; c += blockDim.x) bm[c] = w[0] * b4[c] + w[1] * b6[c] + w[2] * b8[c];
@@ -97,23 +107,35 @@ __global__ void unmerge_upconv_kernel(const float* __restrict__ dwm, const float
                                       float* db4, float* db6, float* db8, double* dots) {
   float w[3];
   softmax3(alpha, w);
-  const int64_t total = pairs * 64;
+  // one thread = one kernel row (8 taps) of one (ci, co) pair: 2 x 16-byte loads per stream instead of one element per
+  // iteration (the element-wise form sat at ~1.5 TB/s with a single load in flight per thread)
+  const int64_t rows_total = pairs * 8;
   float d0 = 0.f, d1 = 0.f, d2 = 0.f;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    int kx = (int)(i & 7), ky = (int)((i >> 3) & 7);
-    int64_t pr = i >> 6;
-    float g = dwm[i];
-    dw8[i] = w[2] * g;
-    d2 = fmaf(g, w8[i], d2);
-    if (ky >= 1 && ky < 7 && kx >= 1 && kx < 7) {
-      int64_t j = pr * 36 + (ky - 1) * 6 + (kx - 1);
-      dw6[j] = w[1] * g;
-      d1 = fmaf(g, w6[j], d1);
+  for (int64_t rix = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; rix < rows_total; rix += (int64_t)gridDim.x * blockDim.x) {
+    const int ky = (int)(rix & 7);
+    const int64_t pr = rix >> 3, i = rix * 8;
+    const float4 ga = *reinterpret_cast<const float4*>(dwm + i), gb = *reinterpret_cast<const float4*>(dwm + i + 4);
+    const float4 wa = *reinterpret_cast<const float4*>(w8 + i), wb = *reinterpret_cast<const float4*>(w8 + i + 4);
+    const float g[8] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w};
+    *reinterpret_cast<float4*>(dw8 + i) = make_float4(w[2] * ga.x, w[2] * ga.y, w[2] * ga.z, w[2] * ga.w);
+    *reinterpret_cast<float4*>(dw8 + i + 4) = make_float4(w[2] * gb.x, w[2] * gb.y, w[2] * gb.z, w[2] * gb.w);
+    d2 = fmaf(ga.x, wa.x, d2); d2 = fmaf(ga.y, wa.y, d2); d2 = fmaf(ga.z, wa.z, d2); d2 = fmaf(ga.w, wa.w, d2);
+    d2 = fmaf(gb.x, wb.x, d2); d2 = fmaf(gb.y, wb.y, d2); d2 = fmaf(gb.z, wb.z, d2); d2 = fmaf(gb.w, wb.w, d2);
+    if (ky >= 1 && ky < 7) {
+      const int64_t j = pr * 36 + (ky - 1) * 6;        // 6 taps kx = 1..6, 8-byte aligned
+      const float2 u0 = *reinterpret_cast<const float2*>(w6 + j), u1 = *reinterpret_cast<const float2*>(w6 + j + 2),
+                   u2 = *reinterpret_cast<const float2*>(w6 + j + 4);
+      *reinterpret_cast<float2*>(dw6 + j) = make_float2(w[1] * g[1], w[1] * g[2]);
+      *reinterpret_cast<float2*>(dw6 + j + 2) = make_float2(w[1] * g[3], w[1] * g[4]);
+      *reinterpret_cast<float2*>(dw6 + j + 4) = make_float2(w[1] * g[5], w[1] * g[6]);
+      d1 = fmaf(g[1], u0.x, d1); d1 = fmaf(g[2], u0.y, d1); d1 = fmaf(g[3], u1.x, d1);
+      d1 = fmaf(g[4], u1.y, d1); d1 = fmaf(g[5], u2.x, d1); d1 = fmaf(g[6], u2.y, d1);
     }
-    if (ky >= 2 && ky < 6 && kx >= 2 && kx < 6) {
-      int64_t j = pr * 16 + (ky - 2) * 4 + (kx - 2);
-      dw4[j] = w[0] * g;
-      d0 = fmaf(g, w4[j], d0);
+    if (ky >= 2 && ky < 6) {
+      const int64_t j = pr * 16 + (ky - 2) * 4;        // 4 taps kx = 2..5, 16-byte aligned
+      const float4 u = *reinterpret_cast<const float4*>(w4 + j);
+      *reinterpret_cast<float4*>(dw4 + j) = make_float4(w[0] * g[2], w[0] * g[3], w[0] * g[4], w[0] * g[5]);
+      d0 = fmaf(g[2], u.x, d0); d0 = fmaf(g[3], u.y, d0); d0 = fmaf(g[4], u.z, d0); d0 = fmaf(g[5], u.w, d0);
     }
   }
   if (dbm != nullptr && blockIdx.x == 0) {
@@ -181,7 +203,7 @@ extern "C" int gsb_merge_upconv(const float* w4, const float* w6, const float* w
   GSB_REQUIRE(w4 && w6 && w8 && alpha && w_merged, "merge_upconv: null pointer");
   GSB_REQUIRE(b_merged == nullptr || (b4 && b6 && b8), "merge_upconv: biases missing");
   int64_t pairs = (int64_t)cin * cout;
-  merge_upconv_kernel<<<ew_grid(pairs * 64), 256, 0, to_stream(s)>>>(w4, w6, w8, b4, b6, b8, alpha, pairs, cout, w_merged,
+  merge_upconv_kernel<<<ew_grid(pairs * 8), 256, 0, to_stream(s)>>>(w4, w6, w8, b4, b6, b8, alpha, pairs, cout, w_merged,
                                                                     b_merged);
   return check_launch("merge_upconv");
 }
@@ -196,7 +218,7 @@ extern "C" int gsb_unmerge_upconv(const float* dw_merged, const float* db_merged
   double* dots = reinterpret_cast<double*>(workspace);
   cudaMemsetAsync(dots, 0, 3 * sizeof(double), to_stream(s));
   int64_t pairs = (int64_t)cin * cout;
-  unmerge_upconv_kernel<<<ew_grid(pairs * 64), 256, 0, to_stream(s)>>>(dw_merged, db_merged, w4, w6, w8, b4, b6, b8, alpha,
+  unmerge_upconv_kernel<<<ew_grid(pairs * 8), 256, 0, to_stream(s)>>>(dw_merged, db_merged, w4, w6, w8, b4, b6, b8, alpha,
                                                                       pairs, cout, dw4, dw6, dw8, db4, db6, db8, dots);
   dalpha_kernel<<<1, 1, 0, to_stream(s)>>>(dots, alpha, dalpha);
   return check_launch("unmerge_upconv", 2);
