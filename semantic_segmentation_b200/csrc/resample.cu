@@ -3,6 +3,7 @@
 // 'bilinear', align_corners=True) -> F.pad -> torch.cat).  128-bit NHWC accesses; the upsample
 // writes straight into the upper channel half of the concat buffer, so no cat copy exists.
 // Algorithmic bytes: pool fwd = 1 read + 1/4 write; upsample fwd = 1/4 read + 1 write.
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace gsb {
@@ -355,6 +356,109 @@ __global__ void __launch_bounds__(256) upsample2_bwd_rows_kernel(const T* __rest
   }
 }
 
+// Backward, window form: for an input column ix the contributing output columns are a run of at most five, so the
+// block prologue stores (first column, five weights) per ix and the row loop issues five UNCONDITIONAL, independent
+// 16-byte loads per contributing output row.  The kernel above hides its loads behind per-thread weight tests (ncu
+// profiles/r01n: issue 48 %, long-scoreboard bound, 1.5 TB/s).  Same products, same ascending summation order.
+// Why five: the sources that touch ix lie in the open interval ((ix-1)/s, (ix+1)/s) with s = (w-1)/(2w-1), of length
+// 4 + 2/(w-1) <= 5 for w >= 3 (and there are only 2w <= 4 columns for w <= 2).  A wider run traps (fails loudly).
+constexpr int kUpWin = 5;
+template <typename T>
+__global__ void __launch_bounds__(256) upsample2_bwd_win_kernel(const T* __restrict__ dout, int64_t dld, int N, int OH, int OW, int C,
+                                                               T* __restrict__ dx, int64_t xld, int h, int w, int pad_top,
+                                                               int pad_left) {
+  __shared__ int s_c0[kMaxUpW / 2];
+  __shared__ float s_cw[kMaxUpW / 2][kUpWin];
+  __shared__ int s_oy[8];
+  __shared__ float s_wy[8];
+  __shared__ int s_bad;
+  if (threadIdx.x == 0) s_bad = 0;
+  __syncthreads();
+  for (int ix = threadIdx.x; ix < w; ix += blockDim.x) {
+    int lo = 1 << 30, hi = -1;
+    for (int c = 0; c < 6; ++c) {  // candidates ux in [2ix-2, 2ix+3]
+      const int ux = 2 * ix - 2 + c;
+      if (ux < 0 || ux >= 2 * w) continue;
+      const Lerp l = lerp_for(ux, w, 2 * w);
+      const float wx = (l.i0 == ix ? l.l0 : 0.f) + (l.i1 == ix ? l.l1 : 0.f);
+      const int ox = ux + pad_left;
+      if (wx != 0.f && ox >= 0 && ox < OW) {
+        lo = min(lo, ox);
+        hi = max(hi, ox);
+      }
+    }
+    int ws = hi < 0 ? 0 : lo;
+    if (ws > OW - kUpWin) ws = OW - kUpWin;
+    if (ws < 0) ws = 0;
+    if (hi >= 0 && (lo < ws || hi > ws + kUpWin - 1)) s_bad = 1;
+    s_c0[ix] = ws;
+    for (int k = 0; k < kUpWin; ++k) {
+      const int ox = ws + k, ux = ox - pad_left;
+      float wx = 0.f;
+      if (ox < OW && ux >= 0 && ux < 2 * w) {
+        const Lerp l = lerp_for(ux, w, 2 * w);
+        wx = (l.i0 == ix ? l.l0 : 0.f) + (l.i1 == ix ? l.l1 : 0.f);
+      }
+      s_cw[ix][k] = wx;
+    }
+  }
+  __syncthreads();
+  if (s_bad) __trap();
+  const unsigned G = (unsigned)C >> 3, items = (unsigned)w * G;
+  const int lastcol = OW - 1;
+  for (int row = blockIdx.x; row < N * h; row += gridDim.x) {
+    const int n = row / h, iy = row - n * h;
+    __syncthreads();
+    if (threadIdx.x < 6) {
+      const int uy = 2 * iy - 2 + (int)threadIdx.x;
+      float wy = 0.f;
+      int oy = 0;
+      if (uy >= 0 && uy < 2 * h) {
+        const Lerp ly = lerp_for(uy, h, 2 * h);
+        wy = (ly.i0 == iy ? ly.l0 : 0.f) + (ly.i1 == iy ? ly.l1 : 0.f);
+        oy = uy + pad_top;
+        if (oy < 0 || oy >= OH) { wy = 0.f; oy = 0; }
+      }
+      s_oy[threadIdx.x] = oy;
+      s_wy[threadIdx.x] = wy;
+    }
+    __syncthreads();
+    for (unsigned it = threadIdx.x; it < items; it += blockDim.x) {
+      const unsigned ix = it / G, g = it - ix * G;
+      const int c0 = s_c0[ix];
+      float cw[kUpWin];
+#pragma unroll
+      for (int k = 0; k < kUpWin; ++k) cw[k] = s_cw[ix][k];
+      float2 acc2[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) acc2[k] = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int r = 0; r < 6; ++r) {
+        const float wy = s_wy[r];
+        if (wy == 0.f) continue;  // block-uniform
+        const T* rowp = dout + ((int64_t)n * OH + s_oy[r]) * OW * dld + g * 8;
+        float v[kUpWin][8];
+#pragma unroll
+        for (int k = 0; k < kUpWin; ++k) Vec8<T>::load(rowp + (int64_t)min(c0 + k, lastcol) * dld, v[k]);
+#pragma unroll
+        for (int k = 0; k < kUpWin; ++k) {
+          const float wgt = wy * cw[k];
+          const float2 w2 = make_float2(wgt, wgt);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc2[j] = __ffma2_rn(w2, make_float2(v[k][2 * j], v[k][2 * j + 1]), acc2[j]);
+        }
+      }
+      float acc[8];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        acc[2 * k] = acc2[k].x;
+        acc[2 * k + 1] = acc2[k].y;
+      }
+      Vec8<T>::store(dx + ((int64_t)row * w + ix) * xld + g * 8, acc);
+    }
+  }
+}
+
 static int ew_grid(int64_t total) {
   int64_t b = (total + 255) / 256;
   int64_t cap = (int64_t)num_sms() * 16;
@@ -431,9 +535,16 @@ extern "C" int gsb_upsample2_bwd(const gsb_view* dout, const gsb_view* dx, int p
   if (2 * dx->w <= kMaxUpW && (int64_t)dx->n * dx->h < ((int64_t)1 << 30)) {
     const int rows = dx->n * dx->h;
     const int grid = rows < num_sms() * 16 ? rows : num_sms() * 16;
-    DISPATCH_T(dx->dtype, upsample2_bwd_rows_kernel<T><<<grid, 256, 0, to_stream(s)>>>(
-                              (const T*)dout->ptr, dout->sw, dout->n, dout->h, dout->w, dout->c, (T*)dx->ptr, dx->sw, dx->h,
-                              dx->w, pad_top, pad_left));
+    static const bool win = []() { const char* e = getenv("GSB_UP_BWD_WIN"); return !(e && e[0] == '0'); }();
+    if (win) {
+      DISPATCH_T(dx->dtype, upsample2_bwd_win_kernel<T><<<grid, 256, 0, to_stream(s)>>>(
+                                (const T*)dout->ptr, dout->sw, dout->n, dout->h, dout->w, dout->c, (T*)dx->ptr, dx->sw, dx->h,
+                                dx->w, pad_top, pad_left));
+    } else {
+      DISPATCH_T(dx->dtype, upsample2_bwd_rows_kernel<T><<<grid, 256, 0, to_stream(s)>>>(
+                                (const T*)dout->ptr, dout->sw, dout->n, dout->h, dout->w, dout->c, (T*)dx->ptr, dx->sw, dx->h,
+                                dx->w, pad_top, pad_left));
+    }
     return check_launch("upsample2_bwd");
   }
   DISPATCH_T(dx->dtype, upsample2_bwd_kernel<T><<<ew_grid(total), 256, 0, to_stream(s)>>>(
