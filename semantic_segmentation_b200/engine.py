@@ -258,8 +258,13 @@ class ConvBNAct:
     (networks.py:582-607) and the discriminator blocks (networks.py:640-657).
     """
 
-    def __init__(self, spec: ConvSpec, has_bn: bool, act1: int, act2: Optional[int] = None, dropout: bool = False):
+    def __init__(self, spec: ConvSpec, has_bn: bool, act1: int, act2: Optional[int] = None, dropout: bool = False,
+                 instance_norm: bool = False):
+        """instance_norm: the normalisation is nn.InstanceNorm2d(affine=False, track_running_stats=False)
+        (networks.py:34-35, --norm instance): statistics per image and channel in training AND evaluation, no
+        parameters, no buffers.  Runs the BatchNorm kernels once per image (flag-reachable path)."""
         self.spec, self.has_bn, self.act1, self.act2, self.dropout = spec, has_bn, act1, act2, dropout
+        self.instance = bool(instance_norm) and has_bn
 
     # x_view: GsbView of the input (NHWC act buffer or the NCHW fp32 network input)
     def forward(self, x_view: GsbView, x_keep, n: int, h: int, w: int, device, weight, bias, bn, training: bool,
@@ -271,16 +276,39 @@ class ConvBNAct:
         stem = _is_stem(s, x_view, x_keep)
         if stem:   # fp32 NCHW network input with 1..4 channels: bandwidth kernel, torch-layout fp32 weights
             stats, rows = ops.stem_conv_fwd(x_keep, weight.detach().contiguous(), bias, y, s.k, s.stride, s.pad,
-                                            want_stats=self.has_bn and training and _CONFIG["fused_stats"])
+                                            want_stats=self.has_bn and training and _CONFIG["fused_stats"] and not self.instance)
         else:
             wp = packed[0] if packed is not None and packed[0] is not None else s.pack_fwd(weight)
-            want_stats = (self.has_bn and training and _CONFIG["fused_stats"]
+            want_stats = (self.has_bn and training and _CONFIG["fused_stats"] and not self.instance
                           and not (s.kind == "convT" and s.stride > 1))
             stats, rows = ops.conv_gather(x_view, wp, bias, view_nhwc(y), s.fwd_mode, s.k, s.stride, s.pad,
                                           use_tc=_CONFIG["use_tc"], want_stats=want_stats)
         sv = Saved()
         count = float(n * oh * ow)
         scale = shift = mean = invstd = None
+        if self.has_bn and self.instance:
+            if out1 is None:
+                out1 = _nhwc_empty(n, oh, ow, s.cout, device)
+            use_drop = self.dropout and training
+            per = []
+            count = float(oh * ow)        # statistics per image
+            for i in range(n):
+                yi = y[i:i + 1]
+                sums_i = ops.bn_reduce(yi)
+                st_i = ops.bn_finalize(sums_i, count, None, None, None, None, None, BN_MOMENTUM, BN_EPS, s.cout, device)
+                seed_i = (drop_seed + 104729 * (i + 1)) if (use_drop and drop_seed) else 0
+                mask_i = drop_mask[i:i + 1] if (use_drop and drop_mask is not None) else None
+                ops.bn_act(yi, st_i[0], st_i[1], self.act1, out1[i:i + 1], self.act2 if self.act2 is not None else ACT_NONE,
+                           out2[i:i + 1] if self.act2 is not None else None, seed_i, mask_i)
+                per.append((st_i, seed_i, mask_i))
+            if save:
+                sv.x_view, sv.x_keep, sv.y = x_view, x_keep, y
+                sv.count, sv.weight = count, weight
+                sv.extra["instance"] = per
+                sv.extra["train_bn"] = False
+                sv.extra["stem"] = stem
+                sv.extra["wpb"] = packed[1] if packed is not None else None
+            return out1, sv
         if self.has_bn:
             gamma, beta, rm, rv, nbt = bn
             fused_ok, peer, pworld = _fused_stats_mode()
@@ -328,7 +356,15 @@ class ConvBNAct:
         sums = None
         mean = invstd = None
         fused_ok, peer, _pw = _fused_stats_mode()
-        if train_bn and fused_ok:
+        inst = sv.extra.get("instance")
+        if inst is not None:
+            for i, (st_i, seed_i, mask_i) in enumerate(inst):
+                sc, sh, mu, istd = st_i
+                a1, a2 = dA1[i:i + 1], (dA2[i:i + 1] if dA2 is not None else None)
+                sums_i, _, _ = ops.bn_bwd_stats(y[i:i + 1], a1, a2, sc, sh, mu, istd, self.act1, act2, seed_i, mask_i, False, None)
+                ops.bn_bwd_apply(y[i:i + 1], a1, a2, sc, sh, mu, istd, self.act1, act2, sums_i, sv.count, dY[i:i + 1], None, None,
+                                 seed_i, mask_i)
+        elif train_bn and fused_ok:
             sums, dgamma, dbeta = ops.bn_bwd_stats(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2,
                                                    sv.drop_seed, sv.drop_mask, need_bn, peer)
             mean, invstd = sv.mean, sv.invstd
@@ -344,8 +380,9 @@ class ConvBNAct:
             es = ops.bn_bwd_reduce(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2,
                                    sv.drop_seed, sv.drop_mask)
             dgamma, dbeta = ops.bn_param_grad(es, s.cout)
-        ops.bn_bwd_apply(y, dA1, dA2, sv.scale, sv.shift, mean, invstd, self.act1, act2, sums, sv.count, dY,
-                         None, None, sv.drop_seed, sv.drop_mask)
+        if inst is None:
+            ops.bn_bwd_apply(y, dA1, dA2, sv.scale, sv.shift, mean, invstd, self.act1, act2, sums, sv.count, dY,
+                             None, None, sv.drop_seed, sv.drop_mask)
         dyv = view_nhwc(dY)
         dweight = dbias = None
         if need_dw and sv.extra.get("stem"):

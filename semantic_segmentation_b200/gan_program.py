@@ -29,8 +29,11 @@ def _block_prefix(level: int) -> str:
 
 
 class GeneratorProgram:
-    def __init__(self, input_nc: int, output_nc: int, ngf: int = 64, use_dropout: bool = False):
+    def __init__(self, input_nc: int, output_nc: int, ngf: int = 64, use_dropout: bool = False, instance_norm: bool = False):
+        """instance_norm: --norm instance (networks.py:34-35): InstanceNorm2d without parameters, and every convolution
+        carries a bias (use_bias, networks.py:568-571)."""
         self.input_nc, self.output_nc, self.ngf, self.use_dropout = input_nc, output_nc, ngf, use_dropout
+        self.inst = inst = bool(instance_norm)
         c = [None, ngf, ngf * 2, ngf * 4, ngf * 8, ngf * 8, ngf * 8, ngf * 8, ngf * 8]  # channels of e_1..e_8
         self.c = c
         self.down: List[Optional[ConvBNAct]] = [None]
@@ -40,24 +43,29 @@ class GeneratorProgram:
             if L == 8:
                 self.down.append(ConvBNAct(spec, False, ACT_RELU))
             else:
-                self.down.append(ConvBNAct(spec, L != 1, ACT_LRELU, ACT_RELU))
+                self.down.append(ConvBNAct(spec, L != 1, ACT_LRELU, ACT_RELU, instance_norm=inst))
         self.up: List[Optional[ConvBNAct]] = [None] * 8
         for L in range(7, 0, -1):
             cin = c[8] if L == 7 else 2 * c[L + 1]
             self.up[L] = ConvBNAct(ConvSpec("convT", cin, c[L], 8, 2, 3), True, ACT_RELU,
-                                   dropout=use_dropout and L in (4, 5, 6))
+                                   dropout=use_dropout and L in (4, 5, 6), instance_norm=inst)
         self.outer = EdgeConv(ConvSpec("convT", 2 * c[1], output_nc, 8, 2, 3), ACT_TANH)
-        names: List[str] = ["model.model.0.weight"]
+        names: List[str] = ["model.model.0.weight"] + (["model.model.0.bias"] if inst else [])
         for L in range(2, 9):
             q = _block_prefix(L)
             names.append(q + ".model.1.weight")
-            if L != 8:
+            if inst:
+                names.append(q + ".model.1.bias")
+            elif L != 8:
                 names += [q + ".model.2.weight", q + ".model.2.bias"]
         for L in range(7, 0, -1):
             q = _block_prefix(L + 1)
             ui, bi = (3, 4) if L == 7 else (5, 6)
             names += [f"{q}.model.{ui}._ops._ops.{i}.op.weight" for i in range(3)]
-            names += [f"{q}.model.{bi}.weight", f"{q}.model.{bi}.bias"]
+            if inst:
+                names += [f"{q}.model.{ui}._ops._ops.{i}.op.bias" for i in range(3)]
+            else:
+                names += [f"{q}.model.{bi}.weight", f"{q}.model.{bi}.bias"]
         names += [f"model.model.3._ops._ops.{i}.op.weight" for i in range(3)]
         names += [f"model.model.3._ops._ops.{i}.op.bias" for i in range(3)]
         names.append(ARCH_KEY)
@@ -73,6 +81,16 @@ class GeneratorProgram:
         q = _block_prefix(L + 1)
         ui, bi = (3, 4) if L == 7 else (5, 6)
         return [f"{q}.model.{ui}._ops._ops.{i}.op.weight" for i in range(3)], f"{q}.model.{bi}"
+
+    def _up_bias_names(self, L: int):
+        q = _block_prefix(L + 1)
+        ui = 3 if L == 7 else 5
+        return [f"{q}.model.{ui}._ops._ops.{i}.op.bias" for i in range(3)]
+
+    def _down_bias(self, P, L: int):
+        if not self.inst:
+            return None
+        return P["model.model.0.bias" if L == 1 else _block_prefix(L) + ".model.1.bias"]
 
     def forward(self, x: torch.Tensor, P, B, training: bool, save: bool, extra=None):
         x = x.contiguous()
@@ -98,22 +116,27 @@ class GeneratorProgram:
         for L in range(1, 9):
             q = _block_prefix(L)
             wname = "model.model.0.weight" if L == 1 else q + ".model.1.weight"
-            bn = self._bn(P, B, q + ".model.2") if 1 < L < 8 else None
+            bn = self._bn(P, B, q + ".model.2") if (1 < L < 8 and not self.inst) else None
             out2 = cats[L][..., :c[L]] if L < 8 else None
-            s, sv = self.down[L].forward(cur_view, cur_keep, n, ch, cw, dev, P[wname], None, bn, training, out2=out2,
-                                         save=save)
+            s, sv = self.down[L].forward(cur_view, cur_keep, n, ch, cw, dev, P[wname], self._down_bias(P, L), bn, training,
+                                         out2=out2, save=save)
             tape[f"down{L}"] = sv
             cur_view, cur_keep, (ch, cw) = view_nhwc(s), s, sizes[L]
         # ---- decoder
         cur = cur_keep                                   # u = relu(e_8)
         for L in range(7, 0, -1):
             wn, bnp = self._up_names(L)
-            wm, _ = ops.merge_upconv(P[wn[0]], P[wn[1]], P[wn[2]], None, None, None, arch[7 - L])
+            if self.inst:
+                bnm = self._up_bias_names(L)
+                wm, bm_up = ops.merge_upconv(P[wn[0]], P[wn[1]], P[wn[2]], P[bnm[0]], P[bnm[1]], P[bnm[2]], arch[7 - L])
+            else:
+                wm, bm_up = ops.merge_upconv(P[wn[0]], P[wn[1]], P[wn[2]], None, None, None, arch[7 - L])[0], None
             hh, ww = cur.shape[1], cur.shape[2]
             drop = self.up[L].dropout and training
             mask = masks[L - 4] if (drop and masks is not None) else None
             seed = (base_seed + 7919 * L) if (drop and masks is None) else 0
-            _, sv = self.up[L].forward(view_nhwc(cur), cur, n, hh, ww, dev, wm, None, self._bn(P, B, bnp), training,
+            _, sv = self.up[L].forward(view_nhwc(cur), cur, n, hh, ww, dev, wm, bm_up,
+                                       None if self.inst else self._bn(P, B, bnp), training,
                                        out1=cats[L][..., c[L]:], save=save, drop_seed=seed, drop_mask=mask)
             tape[f"up{L}"] = sv
             cur = cats[L]
@@ -154,30 +177,38 @@ class GeneratorProgram:
         dskips: List[Optional[torch.Tensor]] = [None] * 9
         for L in range(1, 8):
             wn, bnp = self._up_names(L)
-            nw = need_arch or any(need.get(k, False) for k in wn)
-            nb = need.get(bnp + ".weight", False) or need.get(bnp + ".bias", False)
+            ubn = self._up_bias_names(L) if self.inst else None
+            nw = need_arch or any(need.get(k, False) for k in wn + (ubn or []))
+            nb = (not self.inst) and (need.get(bnp + ".weight", False) or need.get(bnp + ".bias", False))
             dskips[L] = dcat[..., :c[L]]
-            dnext, dwm, _, dg, db = self.up[L].backward(tape[f"up{L}"], dcat[..., c[L]:], None, True, nw, nb, False)
+            dnext, dwm, dbm_up, dg, db = self.up[L].backward(tape[f"up{L}"], dcat[..., c[L]:], None, True, nw, nb,
+                                                             self.inst and nw)
             if nw:
-                unmerge(dwm, None, wn, None, 7 - L)
-            _put(G, bnp + ".weight", dg)
-            _put(G, bnp + ".bias", db)
+                unmerge(dwm, dbm_up if self.inst else None, wn, ubn, 7 - L)
+            if not self.inst:
+                _put(G, bnp + ".weight", dg)
+                _put(G, bnp + ".bias", db)
             dcat = dnext            # gradient of cat_{L+1} (or of u for L == 7)
         ds = dcat
         dx = None
         for L in range(8, 0, -1):
             q = _block_prefix(L)
             wname = "model.model.0.weight" if L == 1 else q + ".model.1.weight"
-            nb = (need.get(q + ".model.2.weight", False) or need.get(q + ".model.2.bias", False)) if 1 < L < 8 else False
+            nb = ((need.get(q + ".model.2.weight", False) or need.get(q + ".model.2.bias", False))
+                  if (1 < L < 8 and not self.inst) else False)
+            bname = ("model.model.0.bias" if L == 1 else q + ".model.1.bias") if self.inst else None
             want_dx = True if L > 1 else need_dx
             dxo = dxv = None
             if L == 1 and need_dx:
                 dxo = torch.empty_like(tape["x"])
                 dxv = view_nchw(dxo)
-            ds, dw, _, dg, db = self.down[L].backward(tape[f"down{L}"], ds, dskips[L] if L < 8 else None, want_dx,
-                                                      need.get(wname, False), nb, False, dx_out=dxo, dx_view=dxv)
+            ds, dw, dbias, dg, db = self.down[L].backward(tape[f"down{L}"], ds, dskips[L] if L < 8 else None, want_dx,
+                                                          need.get(wname, False), nb, bool(bname and need.get(bname, False)),
+                                                          dx_out=dxo, dx_view=dxv)
             _put(G, wname, dw)
-            if 1 < L < 8:
+            if bname:
+                _put(G, bname, dbias)
+            if 1 < L < 8 and not self.inst:
                 _put(G, q + ".model.2.weight", dg)
                 _put(G, q + ".model.2.bias", db)
             if L == 1:
@@ -190,18 +221,22 @@ class GeneratorProgram:
 class DiscriminatorProgram:
     """NLayerDiscriminator(input_nc, ndf, n_layers=3, BatchNorm2d)."""
 
-    def __init__(self, input_nc: int, ndf: int = 64, n_layers: int = 3):
+    def __init__(self, input_nc: int, ndf: int = 64, n_layers: int = 3, instance_norm: bool = False):
         if n_layers != 3:
             raise NotImplementedError("genseg_b200: only the 'basic' 3-layer PatchGAN is on the B200 path")
         self.input_nc = input_nc
+        self.inst = inst = bool(instance_norm)
         self.l0 = ConvBNAct(ConvSpec("conv", input_nc, ndf, 4, 2, 1), False, ACT_LRELU)
-        self.mid = [(2, ConvBNAct(ConvSpec("conv", ndf, ndf * 2, 4, 2, 1), True, ACT_LRELU)),
-                    (5, ConvBNAct(ConvSpec("conv", ndf * 2, ndf * 4, 4, 2, 1), True, ACT_LRELU)),
-                    (8, ConvBNAct(ConvSpec("conv", ndf * 4, ndf * 8, 4, 1, 1), True, ACT_LRELU))]
+        self.mid = [(2, ConvBNAct(ConvSpec("conv", ndf, ndf * 2, 4, 2, 1), True, ACT_LRELU, instance_norm=inst)),
+                    (5, ConvBNAct(ConvSpec("conv", ndf * 2, ndf * 4, 4, 2, 1), True, ACT_LRELU, instance_norm=inst)),
+                    (8, ConvBNAct(ConvSpec("conv", ndf * 4, ndf * 8, 4, 1, 1), True, ACT_LRELU, instance_norm=inst))]
         self.last = EdgeConv(ConvSpec("conv", ndf * 8, 1, 4, 1, 1), ACT_NONE)
         names = ["model.0.weight", "model.0.bias"]
         for idx, _ in self.mid:
-            names += [f"model.{idx}.weight", f"model.{idx + 1}.weight", f"model.{idx + 1}.bias"]
+            if inst:    # InstanceNorm2d(affine=False): no norm parameters, the convolution has a bias
+                names += [f"model.{idx}.weight", f"model.{idx}.bias"]
+            else:
+                names += [f"model.{idx}.weight", f"model.{idx + 1}.weight", f"model.{idx + 1}.bias"]
         names += ["model.11.weight", "model.11.bias"]
         self.param_names = names
 
@@ -219,10 +254,10 @@ class DiscriminatorProgram:
         tape["l0"] = sv
         for idx, layer in self.mid:
             p = f"model.{idx + 1}"
-            bn = (P[p + ".weight"], P[p + ".bias"], B[p + ".running_mean"], B[p + ".running_var"],
-                  B[p + ".num_batches_tracked"])
-            a, sv = layer.forward(view_nhwc(a), a, n, a.shape[1], a.shape[2], dev, P[f"model.{idx}.weight"], None, bn,
-                                  training, save=save)
+            bn = None if self.inst else (P[p + ".weight"], P[p + ".bias"], B[p + ".running_mean"], B[p + ".running_var"],
+                                         B[p + ".num_batches_tracked"])
+            a, sv = layer.forward(view_nhwc(a), a, n, a.shape[1], a.shape[2], dev, P[f"model.{idx}.weight"],
+                                  P[f"model.{idx}.bias"] if self.inst else None, bn, training, save=save)
             tape[f"l{idx}"] = sv
         out, sv = self.last.forward(a, P["model.11.weight"], P["model.11.bias"], save)
         tape["last"] = sv
@@ -236,12 +271,15 @@ class DiscriminatorProgram:
         _put(G, "model.11.bias", db)
         for idx, layer in reversed(self.mid):
             p = f"model.{idx + 1}"
-            nb = need.get(p + ".weight", False) or need.get(p + ".bias", False)
-            d, dw, _, dg, dbb = layer.backward(tape[f"l{idx}"], d, None, True, need.get(f"model.{idx}.weight", False), nb,
-                                               False)
+            nb = (not self.inst) and (need.get(p + ".weight", False) or need.get(p + ".bias", False))
+            d, dw, dcb, dg, dbb = layer.backward(tape[f"l{idx}"], d, None, True, need.get(f"model.{idx}.weight", False), nb,
+                                                 self.inst and need.get(f"model.{idx}.bias", False))
             _put(G, f"model.{idx}.weight", dw)
-            _put(G, p + ".weight", dg)
-            _put(G, p + ".bias", dbb)
+            if self.inst:
+                _put(G, f"model.{idx}.bias", dcb)
+            else:
+                _put(G, p + ".weight", dg)
+                _put(G, p + ".bias", dbb)
         dx = dxv = None
         if need_dx:
             dx = torch.empty_like(tape["x"])

@@ -249,9 +249,6 @@ class UnetSkipConnectionBlock(nn.Module):
             use_bias = norm_layer.func == nn.InstanceNorm2d
         else:
             use_bias = norm_layer == nn.InstanceNorm2d
-        if use_bias:
-            raise NotImplementedError("genseg_b200: InstanceNorm generators are not on the B200 path yet "
-                                      "(pix2pix_model.py:34 forces norm='batch')")
         if input_nc is None:
             input_nc = outer_nc
         downconv = nn.Conv2d(input_nc, inner_nc, kernel_size=4, stride=2, padding=1, bias=use_bias)
@@ -295,7 +292,8 @@ class UnetGenerator(nn.Module):
         self.model = UnetSkipConnectionBlock(output_nc, ngf, input_nc=input_nc, layer_index=self.layer_index,
                                              submodule=unet_block, outermost=True, norm_layer=norm_layer)
         self.layer_index += 1
-        self._program = GeneratorProgram(input_nc, output_nc, ngf, use_dropout)
+        inst = (norm_layer.func if type(norm_layer) == functools.partial else norm_layer) == nn.InstanceNorm2d
+        self._program = GeneratorProgram(input_nc, output_nc, ngf, use_dropout, instance_norm=inst)
         self._dropout_masks = None      # test hook: list of three uint8 NHWC keep-masks (depth 4, 5, 6)
 
     def forward(self, input):
@@ -322,8 +320,6 @@ class NLayerDiscriminator(nn.Module):
             use_bias = norm_layer.func == nn.InstanceNorm2d
         else:
             use_bias = norm_layer == nn.InstanceNorm2d
-        if use_bias:
-            raise NotImplementedError("genseg_b200: InstanceNorm discriminators are not on the B200 path yet")
         kw, padw = 4, 1
         sequence = [nn.Conv2d(input_nc, ndf, kernel_size=kw, stride=2, padding=padw), nn.LeakyReLU(0.2, True)]
         nf_mult = 1
@@ -336,7 +332,7 @@ class NLayerDiscriminator(nn.Module):
                      norm_layer(ndf * nf_mult), nn.LeakyReLU(0.2, True)]
         sequence += [nn.Conv2d(ndf * nf_mult, 1, kernel_size=kw, stride=1, padding=padw)]
         self.model = nn.Sequential(*sequence)
-        self._program = DiscriminatorProgram(input_nc, ndf, n_layers)
+        self._program = DiscriminatorProgram(input_nc, ndf, n_layers, instance_norm=use_bias)
 
     def forward(self, input):
         from ..functions import run_program

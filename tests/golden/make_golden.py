@@ -212,7 +212,53 @@ def pix2pix_case(name, use_dropout, g_train, batch=2):
           out["fake_mean"], out["fake_std"])
 
 
+def pix2pix_instance_case(name="pix2pix_instance", batch=2):
+    """--norm instance (networks.py:34-35): InstanceNorm2d generator + discriminator, one D step and one G step.
+    Weights: oracle.seeded_state over the reference modules' own state_dict layout (biases on every convolution)."""
+    from collections import OrderedDict
+    G = networks.define_G(1, 1, 64, "unet_256", "instance", False, "normal", 0.02, [])
+    D = networks.define_D(2, 64, "basic", 3, "instance", "normal", 0.02, [])
+    G.load_state_dict(O.seeded_state(OrderedDict((k, tuple(v.shape)) for k, v in G.state_dict().items()), 21, conv_std=0.02))
+    D.load_state_dict(O.seeded_state(OrderedDict((k, tuple(v.shape)) for k, v in D.state_dict().items()), 22, conv_std=0.02))
+    arch = 0.5 * torch.randn(8, 3, generator=torch.Generator().manual_seed(23))
+    networks.upconv_arch.data.copy_(arch)
+    networks.upconv_arch.grad = None
+    g = torch.Generator().manual_seed(24)
+    mask = torch.randint(0, 2, (batch, 1, 256, 256), generator=g).float()
+    image = torch.rand(batch, 1, 256, 256, generator=g)
+    G.train(); D.train()
+    crit = networks.GANLoss("lsgan")           # the other flag-reachable loss (networks.py:237-238)
+    fake = G(mask)
+    pred_fake_d = D(torch.cat([mask, fake], 1).detach())
+    pred_real = D(torch.cat([mask, image], 1))
+    loss_D = 0.5 * (crit(pred_fake_d, False) + crit(pred_real, True))
+    loss_D.backward()
+    gD = grads_of(D)
+    for p in D.parameters():
+        p.grad = None
+        p.requires_grad_(False)
+    pred_fake = D(torch.cat([mask, fake], 1))
+    g_gan = crit(pred_fake, True)
+    g_l1 = torch.nn.L1Loss()(fake, image) * 100.0
+    (g_gan + g_l1).backward()
+    gG = grads_of(G)
+    out = dict(arch=arch.numpy(), fake_sample=fake.detach().flatten()[::13].numpy(), pred_fake=pred_fake.detach().numpy(),
+               pred_real=pred_real.detach().numpy(), loss_D=loss_D.item(), G_GAN=g_gan.item(), G_L1=g_l1.item(),
+               gradG_norms=np.array([gG[k].norm().item() for k in gG], np.float64), gradG_keys=np.array(list(gG.keys())),
+               gradD_norms=np.array([gD[k].norm().item() for k in gD], np.float64), gradD_keys=np.array(list(gD.keys())),
+               grad_arch=networks.upconv_arch.grad.numpy().copy())
+    out["gradG:model.model.0.weight"] = gG["model.model.0.weight"].numpy()
+    out["gradG:outer_w4"] = gG["model.model.3._ops._ops.0.op.weight"].numpy()
+    out["gradD:model.0.weight"] = gD["model.0.weight"].numpy()
+    out["gradD:model.11.weight"] = gD["model.11.weight"].numpy()
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+    print(name, "loss_D", loss_D.item(), "G_GAN", g_gan.item(), "G_L1", g_l1.item())
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "instance":
+        pix2pix_instance_case()
+        sys.exit(0)
     unet_case("unet_c2_bilinear_32", 1, 2, True, 2, 32, 32, wseed=1, xseed=2)
     unet_case("unet_c1_convT_32", 1, 1, False, 2, 32, 32, wseed=3, xseed=4)
     unet_case("unet_c2_bilinear_odd", 1, 2, True, 2, 36, 44, wseed=5, xseed=6)

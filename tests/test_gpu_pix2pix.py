@@ -136,3 +136,73 @@ def test_gan_and_l1_losses_match_oracle():
     out = networks.l1_loss(ad, b.to(DEV))
     out.backward()
     assert abs(out.item() - ref.item()) < 1e-6 and rel(ad.grad, ac.grad) < 1e-6
+
+
+def _run_instance(precision, golden_dir):
+    from collections import OrderedDict
+    gold = np.load(os.path.join(golden_dir, "pix2pix_instance.npz"))
+    S.set_precision(precision)
+    old_arch = networks.upconv_arch
+    try:
+        G = networks.define_G(1, 1, 64, "unet_256", "instance", False, "normal", 0.02, [])
+        D = networks.define_D(2, 64, "basic", 3, "instance", "normal", 0.02, [])
+        G.load_state_dict(O.seeded_state(OrderedDict((k, tuple(v.shape)) for k, v in G.state_dict().items()), 21, conv_std=0.02))
+        D.load_state_dict(O.seeded_state(OrderedDict((k, tuple(v.shape)) for k, v in D.state_dict().items()), 22, conv_std=0.02))
+        assert not any("running" in k for k in G.state_dict()) and "model.2.bias" in D.state_dict()
+        G, D = G.to(DEV).train(), D.to(DEV).train()
+        networks.upconv_arch = torch.from_numpy(gold["arch"]).to(DEV).requires_grad_(True)
+        g = torch.Generator().manual_seed(24)
+        mask = torch.randint(0, 2, (2, 1, 256, 256), generator=g).float().to(DEV)
+        image = torch.rand(2, 1, 256, 256, generator=g).to(DEV)
+        crit = networks.GANLoss("lsgan").to(DEV)
+        fake = G(mask)
+        pred_fake_d = D(torch.cat([mask, fake], 1).detach())
+        pred_real = D(torch.cat([mask, image], 1))
+        loss_D = 0.5 * (crit(pred_fake_d, False) + crit(pred_real, True))
+        loss_D.backward()
+        gD = {k: p.grad.clone() for k, p in D.named_parameters()}
+        for p in D.parameters():
+            p.grad = None
+            p.requires_grad_(False)
+        pred_fake = D(torch.cat([mask, fake], 1))
+        g_gan = crit(pred_fake, True)
+        g_l1 = networks.l1_loss(fake, image) * 100.0
+        (g_gan + g_l1).backward()
+        torch.cuda.synchronize()
+        gG = {k: p.grad for k, p in G.named_parameters()}
+        out = dict(fake=rel(fake.flatten()[::13], gold["fake_sample"]), pred_fake=rel(pred_fake, gold["pred_fake"]),
+                   pred_real=rel(pred_real, gold["pred_real"]), loss_D=abs(loss_D.item() - float(gold["loss_D"])),
+                   G_GAN=abs(g_gan.item() - float(gold["G_GAN"])), G_L1=abs(g_l1.item() - float(gold["G_L1"])))
+        # a convolution bias in front of InstanceNorm is cancelled by the mean subtraction: its gradient is pure rounding
+        # noise in the reference too -> compare the norms of weight gradients only
+        keysG = [str(k) for k in gold["gradG_keys"]]
+        sel = [i for i, k in enumerate(keysG) if k.endswith(".weight")]
+        nG = np.array([gG[keysG[i]].norm().item() for i in sel])
+        out["gradG_norms_median"] = float(np.median(np.abs(nG - gold["gradG_norms"][sel]) / (gold["gradG_norms"][sel] + 1e-12)))
+        out["grad_arch"] = rel(networks.upconv_arch.grad, gold["grad_arch"])
+        out["gG0"] = rel(gG["model.model.0.weight"], gold["gradG:model.model.0.weight"])
+        out["gG_outer_w4"] = rel(gG["model.model.3._ops._ops.0.op.weight"], gold["gradG:outer_w4"])
+        out["gD0"] = rel(gD["model.0.weight"], gold["gradD:model.0.weight"])
+        out["gD11"] = rel(gD["model.11.weight"], gold["gradD:model.11.weight"])
+        return out
+    finally:
+        networks.upconv_arch = old_arch
+        S.set_precision("bf16")
+
+
+def test_pix2pix_instance_norm_lsgan_fp32_matches_reference(golden_dir):
+    """--norm instance --gan_mode lsgan: InstanceNorm2d generator / discriminator with biased convolutions,
+    MSE GAN loss; fixture generated by the reference modules (tests/golden/make_golden.py instance)."""
+    out = _run_instance("fp32", golden_dir)
+    print("instance fp32", out)
+    assert out["fake"] < 2e-4 and out["pred_fake"] < 2e-4 and out["pred_real"] < 1e-4, out
+    assert out["loss_D"] < 1e-4 and out["G_GAN"] < 1e-4 and out["G_L1"] < 2e-3, out
+    assert out["gD0"] < 5e-2 and out["gD11"] < 5e-2 and out["gG_outer_w4"] < 5e-2 and out["gG0"] < 5e-2, out
+    assert out["gradG_norms_median"] < 1e-2 and out["grad_arch"] < 5e-2, out
+
+
+def test_pix2pix_instance_norm_bf16_runs_close(golden_dir):
+    out = _run_instance("bf16", golden_dir)
+    print("instance bf16", out)
+    assert out["fake"] < 1e-1 and out["pred_real"] < 5e-2, out
+    assert out["loss_D"] < 2e-2 and out["G_GAN"] < 2e-2 and out["G_L1"] < 0.5, out
