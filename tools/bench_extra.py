@@ -104,6 +104,85 @@ def evaluate_sweep(steps):
                           "fwd_tflops": 79.818e9 * (hw / 256.0) ** 2 * n / t / 1e12, "dtype": "bf16"}), flush=True)
 
 
+def genseg_iteration(batch, steps):
+    """BASELINE config 3/4 -- one iteration of the GenSeg end-to-end loop of running_files/train_end2end_jsrt.py:141-236 with
+    our modules: Generator.training_step (:141-155) + Adam, Discriminator.training_step (:158-173) + Adam,
+    Unet.training_step (:177-232: real batch, device-side mask augmentation -> G -> image chain -> generated batch,
+    unet_loss = loss + loss_lambda * fake_loss) + RMSprop.  UNet(1, 1, bilinear=False), GANLoss('vanilla'), lambda_L1 100,
+    loss_lambda 1.0 (scripts/train_end2end_jsrt.sh).  NOT included: the Arch problem's hyper-gradient -- it is computed by
+    the external betty-ml engine (DARTS finite differences), absent offline and unpinned by the reference; its
+    training_step (one U-Net forward + loss on a validation batch) is timed as forward + backward to the input."""
+    import semantic_segmentation_b200 as S
+    from oracle import genseg_oracle as O
+    from semantic_segmentation_b200.models_pix2pix import networks
+    from semantic_segmentation_b200.optim import Adam, RMSprop
+    from semantic_segmentation_b200.unet import UNet
+    from semantic_segmentation_b200.util import augment
+    from semantic_segmentation_b200.util.dice_score import seg_loss
+    S.set_precision("bf16")
+    dev = "cuda"
+    G = networks.define_G(1, 1, 64, "unet_256", "batch", True, "normal", 0.02, [])
+    D = networks.define_D(2, 64, "basic", 3, "batch", "normal", 0.02, [])
+    G.load_state_dict(O.seeded_state(O.generator_state_spec(1, 1, 64), 11, conv_std=0.02), strict=True)
+    D.load_state_dict(O.seeded_state(O.discriminator_state_spec(2, 64), 12, conv_std=0.02), strict=True)
+    net = UNet(1, 1, False)
+    net.load_state_dict(O.seeded_state(O.unet_state_spec(1, 1, False), 1234))
+    G, D, net = G.to(dev).train(), D.to(dev).train(), net.to(dev).train()
+    networks.upconv_arch = (1e-3 * torch.randn(8, 3, generator=torch.Generator().manual_seed(5))).to(dev).requires_grad_(True)
+    crit = networks.GANLoss("vanilla").to(dev)
+    optG = Adam(list(G.parameters()), lr=2e-5, betas=(0.5, 0.999))
+    optD = Adam(list(D.parameters()), lr=2e-5, betas=(0.5, 0.999))
+    optU = RMSprop(list(net.parameters()), lr=1e-5, weight_decay=1e-8, momentum=0.9)
+    g = torch.Generator().manual_seed(14)
+    yy, xx = torch.meshgrid(torch.arange(256), torch.arange(256), indexing="ij")
+    lungs = ((((xx - 85) / 50.0) ** 2 + ((yy - 128) / 80.0) ** 2 < 1) | (((xx - 171) / 45.0) ** 2 + ((yy - 130) / 85.0) ** 2 < 1))
+    mask = lungs.float()[None, None].repeat(batch, 1, 1, 1).to(dev)               # JSRT-shaped lung masks
+    image = torch.rand(batch, 1, 256, 256, generator=g).to(dev)
+    val_image, val_mask = torch.rand(batch, 1, 256, 256, generator=g).to(dev), mask.clone()
+    mats = [augment.draw_affine(batch, 256, 256, torch.Generator().manual_seed(100 + i)).to(dev) for i in range(8)]
+    state = {"i": 0}
+
+    def set_d_grad(flag):
+        for p in D.parameters():
+            p.requires_grad_(flag)
+
+    def step():
+        # --- Generator problem
+        set_d_grad(False)
+        optG.zero_grad()
+        fake = G(mask)
+        loss_G = crit(D(torch.cat([mask, fake], 1)), True) + networks.l1_loss(fake, image) * 100.0
+        loss_G.backward()
+        optG.step()
+        # --- Discriminator problem
+        set_d_grad(True)
+        optD.zero_grad()
+        with torch.no_grad():
+            fake = G(mask)
+        loss_D = 0.5 * (crit(D(torch.cat([mask, fake], 1)), False) + crit(D(torch.cat([mask, image], 1)), True))
+        loss_D.backward()
+        optD.step()
+        # --- Unet problem: real batch + generated batch
+        optU.zero_grad()
+        loss = seg_loss(net(image), mask.long())
+        fake_mask = augment.augment_masks(mask, mats[state["i"] % len(mats)])
+        state["i"] += 1
+        with torch.no_grad():
+            fake_image = augment.synth_image_postprocess(G(fake_mask))
+        fake_loss = seg_loss(net(fake_image), fake_mask.long())
+        (loss + 1.0 * fake_loss).backward()
+        optU.step()
+        # --- Arch problem's training_step on the validation batch (loss + gradient; hyper-gradient not included)
+        vi = val_image.clone().requires_grad_(True)
+        seg_loss(net(vi), val_mask.long()).backward()
+        return loss_G
+
+    t = timed(step, steps)
+    print(json.dumps({"workload": "GenSeg end-to-end iteration (G step + D step + U-Net step on real + generated batch + Arch "
+                                  "training_step; Betty hyper-gradient not included)", "batch": batch, "ms_per_iteration": t * 1e3,
+                      "real_images_per_s": batch / t, "dtype": "bf16", "data": "synthetic lung-shaped masks"}), flush=True)
+
+
 def augment_chain(steps):
     """the image chain of the end-to-end step (train_end2end_jsrt.py:186-200) at its size (8 x 1 x 256 x 256)
     and at a bandwidth-relevant size (64 x 1 x 1024 x 1024), device-resident, against the CPU restatement."""
@@ -140,3 +219,5 @@ if __name__ == "__main__":
         evaluate_sweep(a.steps)
     if a.only in ("", "augment"):
         augment_chain(a.steps)
+    if a.only in ("", "e2e"):
+        genseg_iteration(a.batch, a.steps)
