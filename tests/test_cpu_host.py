@@ -139,3 +139,37 @@ def test_data_parallel_host_logic_gloo_world2(tmp_path):
                        capture_output=True, text=True, timeout=240)
     assert r.returncode == 0, r.stdout + r.stderr
     assert r.stdout.count("ok") == 2
+
+
+def test_fused_optimisers_are_torch_optimizers():
+    """what the reference hangs on its optimisers -- ReduceLROnPlateau (train_end2end_jsrt.py:73), state_dict
+    round trips with torch.optim (checkpoints, Betty roll_back) -- works on the fused classes; step() has no CPU path."""
+    from semantic_segmentation_b200.optim import Adam, RMSprop
+    p = torch.nn.Parameter(torch.ones(4))
+    p.grad = torch.ones(4)
+    o = RMSprop([p], lr=1e-2, weight_decay=1e-8, momentum=0.9)
+    assert isinstance(o, torch.optim.Optimizer) and o.param_groups[0]["momentum"] == 0.9
+    sched = torch.optim.lr_scheduler.ReduceLROnPlateau(o, "max", patience=0)
+    sched.step(1.0)
+    sched.step(0.5)
+    assert abs(o.param_groups[0]["lr"] - 1e-3) < 1e-12
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        o.step()
+    assert len(o.state) == 0                                  # nothing was touched before the refusal
+    q = torch.nn.Parameter(torch.ones(4))
+    q.grad = torch.full((4,), 0.5)
+    ref = torch.optim.Adam([q], lr=2e-5, betas=(0.5, 0.999))
+    ref.step()
+    ref.step()
+    a = Adam([p], lr=1.0)
+    a.load_state_dict(ref.state_dict())                       # an optimiser checkpoint of the reference loads
+    assert int(a.state[p]["step"]) == 2 and a.param_groups[0]["betas"] == (0.5, 0.999) and a.param_groups[0]["lr"] == 2e-5
+    assert torch.equal(a.state[p]["exp_avg"], ref.state[q]["exp_avg"]) and torch.equal(a.state[p]["exp_avg_sq"], ref.state[q]["exp_avg_sq"])
+    back = torch.optim.Adam([q], lr=1.0)
+    back.load_state_dict(a.state_dict())                      # and the other way round
+    back.step()
+    assert int(back.state[q]["step"]) == 3
+    o.zero_grad()
+    assert p.grad is None
+    with pytest.raises(NotImplementedError):
+        RMSprop([p], centered=True)

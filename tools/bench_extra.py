@@ -183,6 +183,103 @@ def genseg_iteration(batch, steps):
                       "real_images_per_s": batch / t, "dtype": "bf16", "data": "synthetic lung-shaped masks"}), flush=True)
 
 
+def genseg_betty(batch, steps, intended=False):
+    """BASELINE config 4 through the Betty-compatible driver (semantic_segmentation_b200/betty): the four
+    problems and the dependency graph of train_end2end_jsrt.py:141-342 (``l2u = {netG: [arch]}`` after Python's
+    repeated-key rule, ``u2l = {arch: [netG]}``, inner Config(type='darts', unroll_steps=1), roll_back=True); one
+    ``Engine.train_step`` = one iteration.  With the script's graph the Arch loss does not reach the generator, so the
+    DARTS term vanishes and only its bookkeeping (roll-back snapshot of G + Adam state, G's re-done step) is paid.
+    ``intended=True`` times the graph the method describes instead: Arch owns ``upconv_arch`` and its validation loss
+    runs through the generator, so every iteration carries the two finite-difference generator passes."""
+    import semantic_segmentation_b200 as S
+    from oracle import genseg_oracle as O
+    from semantic_segmentation_b200.betty import Config, Engine, EngineConfig, ImplicitProblem
+    from semantic_segmentation_b200.models_pix2pix import networks
+    from semantic_segmentation_b200.optim import Adam, RMSprop
+    from semantic_segmentation_b200.unet import UNet
+    from semantic_segmentation_b200.util import augment
+    from semantic_segmentation_b200.util.dice_score import seg_loss
+    S.set_precision("bf16")
+    dev = torch.device("cuda")
+    G = networks.define_G(1, 1, 64, "unet_256", "batch", True, "normal", 0.02, [])
+    D = networks.define_D(2, 64, "basic", 3, "batch", "normal", 0.02, [])
+    G.load_state_dict(O.seeded_state(O.generator_state_spec(1, 1, 64), 11, conv_std=0.02), strict=True)
+    D.load_state_dict(O.seeded_state(O.discriminator_state_spec(2, 64), 12, conv_std=0.02), strict=True)
+    net = UNet(1, 1, False)
+    net.load_state_dict(O.seeded_state(O.unet_state_spec(1, 1, False), 1234))
+    G, D, net = G.to(dev).train(), D.to(dev).train(), net.to(dev).train()
+
+    class ArchVars(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.upconv_arch = torch.nn.Parameter((1e-3 * torch.randn(8, 3, generator=torch.Generator().manual_seed(5))).to(dev))
+
+    arch_vars = ArchVars()
+    networks.upconv_arch = arch_vars.upconv_arch
+    crit = networks.GANLoss("vanilla").to(dev)
+    g = torch.Generator().manual_seed(14)
+    yy, xx = torch.meshgrid(torch.arange(256), torch.arange(256), indexing="ij")
+    lungs = ((((xx - 85) / 50.0) ** 2 + ((yy - 128) / 80.0) ** 2 < 1) | (((xx - 171) / 45.0) ** 2 + ((yy - 130) / 85.0) ** 2 < 1))
+    mask = lungs.float()[None, None].repeat(batch, 1, 1, 1)
+    # batches live in pinned host memory; the driver moves them to the device every step (Problem.get_batch)
+    loader = [{"image": torch.rand(batch, 1, 256, 256, generator=g).pin_memory(), "mask": mask.clone().pin_memory(),
+               "image_pix2pix": torch.rand(batch, 1, 256, 256, generator=g).pin_memory(), "mask_pix2pix": mask.clone().pin_memory()}
+              for _ in range(4)]
+    val_loader = [{"image": torch.rand(batch, 1, 256, 256, generator=g).pin_memory(), "mask": mask.clone().pin_memory()}]
+    mats = [augment.draw_affine(batch, 256, 256, torch.Generator().manual_seed(100 + i)).to(dev) for i in range(8)]
+    state = {"i": 0}
+
+    class Generator(ImplicitProblem):
+        def training_step(self, batch):
+            fake = self.module(batch["mask_pix2pix"])
+            return crit(self.netD(torch.cat((batch["mask_pix2pix"], fake), 1)), True) + networks.l1_loss(fake, batch["image_pix2pix"]) * 100.0
+
+    class Discriminator(ImplicitProblem):
+        def training_step(self, batch):
+            with torch.no_grad():
+                fake = self.netG(batch["mask_pix2pix"])
+            return 0.5 * (crit(self.module(torch.cat((batch["mask_pix2pix"], fake), 1)), False)
+                          + crit(self.module(torch.cat((batch["mask_pix2pix"], batch["image_pix2pix"]), 1)), True))
+
+    class Unet(ImplicitProblem):
+        def training_step(self, batch):
+            loss = seg_loss(self.module(batch["image"]), batch["mask"].long())
+            fake_mask = augment.augment_masks(batch["mask"], mats[state["i"] % len(mats)])
+            state["i"] += 1
+            with torch.no_grad():
+                fake_image = augment.synth_image_postprocess(self.netG(fake_mask))
+            return loss + 1.0 * seg_loss(self.module(fake_image), fake_mask.long())
+
+    class Arch(ImplicitProblem):
+        def training_step(self, batch):
+            if intended:     # validation loss of the U-Net on images the generator makes from the validation masks
+                return seg_loss(self.unet(self.netG(batch["mask"])), batch["mask"].long())
+            return seg_loss(self.unet(batch["image"]), batch["mask"].long())
+
+    inner, outer = Config(type="darts", unroll_steps=1), Config(retain_graph=True)
+    netG = Generator(name="netG", module=G, optimizer=Adam(list(G.parameters()), lr=2e-5, betas=(0.5, 0.999)),
+                     train_data_loader=loader, config=inner, device=dev)
+    netD = Discriminator(name="netD", module=D, optimizer=Adam(list(D.parameters()), lr=2e-5, betas=(0.5, 0.999)),
+                         train_data_loader=loader, config=inner, device=dev)
+    unet = Unet(name="unet", module=net, optimizer=RMSprop(list(net.parameters()), lr=1e-5, weight_decay=1e-8, momentum=0.9),
+                train_data_loader=loader, config=inner, device=dev)
+    arch = Arch(name="arch", module=arch_vars if intended else net,
+                optimizer=Adam([arch_vars.upconv_arch], lr=1e-4, betas=(0.5, 0.999), weight_decay=1e-5),
+                train_data_loader=val_loader, config=outer, device=dev)
+    eng = Engine(config=EngineConfig(valid_step=0, train_iters=1, roll_back=True), problems=[netG, netD, unet, arch],
+                 dependencies={"l2u": {netG: [arch]}, "u2l": {arch: [netG]}})
+
+    def step():
+        eng.global_step += 1
+        eng.train_step()
+
+    t = timed(step, steps)
+    print(json.dumps({"workload": "GenSeg end-to-end iteration through the Betty-compatible driver (%s graph; G, D, U-Net, Arch problems, "
+                                  "roll_back, host batches copied every step)" % ("intended: DARTS hyper-gradient through G" if intended else "reference script"),
+                      "batch": batch, "ms_per_iteration": t * 1e3, "real_images_per_s": batch / t, "dtype": "bf16",
+                      "data": "synthetic lung-shaped masks"}), flush=True)
+
+
 def augment_chain(steps):
     """the image chain of the end-to-end step (train_end2end_jsrt.py:186-200) at its size (8 x 1 x 256 x 256)
     and at a bandwidth-relevant size (64 x 1 x 1024 x 1024), device-resident, against the CPU restatement."""
@@ -221,3 +318,6 @@ if __name__ == "__main__":
         augment_chain(a.steps)
     if a.only in ("", "e2e"):
         genseg_iteration(a.batch, a.steps)
+    if a.only in ("", "betty"):
+        genseg_betty(a.batch, a.steps, intended=False)
+        genseg_betty(a.batch, a.steps, intended=True)
