@@ -84,10 +84,11 @@ def unet_state_spec(n_channels: int, n_classes: int, bilinear: bool) -> "Ordered
     return spec
 
 
-def generator_state_spec(input_nc: int, output_nc: int, ngf: int = 64) -> "OrderedDict[str, Tuple[int, ...]]":
-    """Key -> shape of the ``unet_256`` generator built by
-    models_pix2pix/networks.py:514-617 with BatchNorm (use_bias False except the
-    outermost up-cell, :590).  8 levels, ``layer_index`` 0 = innermost."""
+def generator_state_spec(input_nc: int, output_nc: int, ngf: int = 64, num_downs: int = 8
+                         ) -> "OrderedDict[str, Tuple[int, ...]]":
+    """Key -> shape of the ``unet_256`` (num_downs 8) / ``unet_128`` (num_downs 7, networks.py:148-151) generator built
+    by models_pix2pix/networks.py:514-617 with BatchNorm (use_bias False except the
+    outermost up-cell, :590).  ``layer_index`` 0 = innermost."""
     spec: "OrderedDict[str, Tuple[int, ...]]" = OrderedDict()
 
     def bn(prefix: str, c: int) -> None:
@@ -98,8 +99,7 @@ def generator_state_spec(input_nc: int, output_nc: int, ngf: int = 64) -> "Order
         spec[prefix + ".num_batches_tracked"] = ()
 
     # (outer_nc, inner_nc) from the outermost block inwards (networks.py:532-546)
-    levels = [(output_nc, ngf), (ngf, ngf * 2), (ngf * 2, ngf * 4), (ngf * 4, ngf * 8),
-              (ngf * 8, ngf * 8), (ngf * 8, ngf * 8), (ngf * 8, ngf * 8), (ngf * 8, ngf * 8)]
+    levels = [(output_nc, ngf), (ngf, ngf * 2), (ngf * 2, ngf * 4), (ngf * 4, ngf * 8)] + [(ngf * 8, ngf * 8)] * (num_downs - 4)
     prefix = "model.model"
     # outermost: [downconv, submodule, uprelu, upcell, tanh]
     spec[prefix + ".0.weight"] = (ngf, input_nc, 4, 4)
@@ -110,9 +110,9 @@ def generator_state_spec(input_nc: int, output_nc: int, ngf: int = 64) -> "Order
         tail.append((f"{prefix}.3._ops._ops.{i}.op.bias", (output_nc,)))
     tails = [tail]
     p = prefix + ".1"
-    for depth in range(1, 8):
+    for depth in range(1, num_downs):
         outer, inner = levels[depth]
-        innermost = depth == 7
+        innermost = depth == num_downs - 1
         spec[p + ".model.1.weight"] = (inner, outer, 4, 4)
         t: List[Tuple[str, Tuple[int, ...]]] = []
         if innermost:
@@ -138,21 +138,21 @@ def generator_state_spec(input_nc: int, output_nc: int, ngf: int = 64) -> "Order
     return spec
 
 
-def discriminator_state_spec(input_nc: int, ndf: int = 64) -> "OrderedDict[str, Tuple[int, ...]]":
-    """Key -> shape of the 'basic' 3-layer PatchGAN, networks.py:620-665."""
+def discriminator_state_spec(input_nc: int, ndf: int = 64, n_layers: int = 3) -> "OrderedDict[str, Tuple[int, ...]]":
+    """Key -> shape of the PatchGAN, networks.py:620-665 ('basic' = 3 layers; 'n_layers' takes --n_layers_D)."""
     spec: "OrderedDict[str, Tuple[int, ...]]" = OrderedDict()
     spec["model.0.weight"] = (ndf, input_nc, 4, 4)
     spec["model.0.bias"] = (ndf,)
-    chans = [ndf, ndf * 2, ndf * 4, ndf * 8]
+    chans = [ndf * min(2 ** i, 8) for i in range(n_layers + 1)]
     idx = 2
-    for i in range(1, 4):
+    for i in range(1, n_layers + 1):
         spec[f"model.{idx}.weight"] = (chans[i], chans[i - 1], 4, 4)
         for s in ("weight", "bias", "running_mean", "running_var"):
             spec[f"model.{idx + 1}.{s}"] = (chans[i],)
         spec[f"model.{idx + 1}.num_batches_tracked"] = ()
         idx += 3
-    spec["model.11.weight"] = (1, ndf * 8, 4, 4)
-    spec["model.11.bias"] = (1,)
+    spec[f"model.{idx}.weight"] = (1, chans[n_layers], 4, 4)
+    spec[f"model.{idx}.bias"] = (1,)
     return spec
 
 
@@ -395,11 +395,11 @@ def merged_upconv_weight(st: Dict[str, Tensor], prefix: str, alpha_row: Tensor, 
 
 def generator_forward(st: Dict[str, Tensor], x: Tensor, upconv_arch: Tensor, training: bool = True,
                       update_running: bool = False, dropout_masks: Optional[List[Tensor]] = None,
-                      taps: Optional[Dict[str, Tensor]] = None) -> Tensor:
-    """UnetGenerator('unet_256').forward, networks.py:514-617.
+                      taps: Optional[Dict[str, Tensor]] = None, num_downs: int = 8) -> Tensor:
+    """UnetGenerator('unet_256' | 'unet_128').forward, networks.py:514-617 (num_downs 8 | 7).
 
-    Restated iteratively.  Level d = 0 is the outermost block (layer_index 7), d = 7
-    the innermost (layer_index 0).  The in-place LeakyReLU (networks.py:583) makes
+    Restated iteratively.  Level d = 0 is the outermost block (layer_index num_downs-1), d = num_downs-1
+    the innermost (layer_index 0).  The text below is for num_downs = 8; with 7 the dropout blocks are depth 4,5.  The in-place LeakyReLU (networks.py:583) makes
     each skip carry lrelu(x).  Dropout(0.5) follows the up-norm of the
     blocks at depth 4,5,6 (layer_index 3,2,1; networks.py:535-537,606-607);
     ``dropout_masks`` = optional list of three {0,1} keep-masks ordered by depth
@@ -411,43 +411,46 @@ def generator_forward(st: Dict[str, Tensor], x: Tensor, upconv_arch: Tensor, tra
     skips: List[Tensor] = []
     prefixes: List[str] = []
     q = p + ".1"
-    for d in range(1, 8):
+    last = num_downs - 1
+    for d in range(1, num_downs):
         s = F.leaky_relu(e, 0.2)
         skips.append(s)
         prefixes.append(q)
         e = F.conv2d(s, st[q + ".model.1.weight"], None, stride=2, padding=1)
-        if d != 7:
+        if d != last:
             e = _bn(e, st, q + ".model.2", training, update_running)
         if taps is not None:
             taps[f"down{d}"] = e
         q = q + ".model.3"
     # innermost up: relu -> mixed convT -> BN
     h = F.relu(e)
-    for d in range(7, 0, -1):
+    for d in range(last, 0, -1):
         q = prefixes[d - 1]
-        up_idx, bn_idx = (3, 4) if d == 7 else (5, 6)
-        layer_index = 7 - d
+        up_idx, bn_idx = (3, 4) if d == last else (5, 6)
+        layer_index = last - d
         h = mixed_upconv(h, st, f"{q}.model.{up_idx}", upconv_arch[layer_index], bias=False)
         h = _bn(h, st, f"{q}.model.{bn_idx}", training, update_running)
-        if d in (4, 5, 6) and dropout_masks is not None:
+        if 4 <= d < last and dropout_masks is not None:
             h = h * dropout_masks[d - 4] * 2.0
         if taps is not None:
             taps[f"up{d}"] = h
         h = F.relu(torch.cat([skips[d - 1], h], dim=1))  # parent's uprelu over the concat
-    out = mixed_upconv(h, st, p + ".3", upconv_arch[7], bias=True)
+    out = mixed_upconv(h, st, p + ".3", upconv_arch[last], bias=True)
     return torch.tanh(out)
 
 
 def discriminator_forward(st: Dict[str, Tensor], x: Tensor, training: bool = True,
                           update_running: bool = False, taps: Optional[Dict[str, Tensor]] = None) -> Tensor:
-    """NLayerDiscriminator(n_layers=3).forward, networks.py:620-665."""
+    """NLayerDiscriminator.forward, networks.py:620-665 (n_layers read off the state: 3 for 'basic')."""
+    n_layers = sum(1 for k in st if k.endswith(".running_mean"))
     h = F.leaky_relu(F.conv2d(x, st["model.0.weight"], st["model.0.bias"], stride=2, padding=1), 0.2)
-    for idx, stride in ((2, 2), (5, 2), (8, 1)):
+    for idx, stride in [(2 + 3 * i, 2 if i < n_layers - 1 else 1) for i in range(n_layers)]:
         h = F.conv2d(h, st[f"model.{idx}.weight"], None, stride=stride, padding=1)
         if taps is not None:
             taps[f"conv{idx}"] = h
         h = F.leaky_relu(_bn(h, st, f"model.{idx + 1}", training, update_running), 0.2)
-    return F.conv2d(h, st["model.11.weight"], st["model.11.bias"], stride=1, padding=1)
+    idx = 2 + 3 * n_layers
+    return F.conv2d(h, st[f"model.{idx}.weight"], st[f"model.{idx}.bias"], stride=1, padding=1)
 
 
 def gan_loss(pred: Tensor, target_is_real: bool, gan_mode: str = "vanilla") -> Tensor:

@@ -29,38 +29,44 @@ def _block_prefix(level: int) -> str:
 
 
 class GeneratorProgram:
-    def __init__(self, input_nc: int, output_nc: int, ngf: int = 64, use_dropout: bool = False, instance_norm: bool = False):
+    def __init__(self, input_nc: int, output_nc: int, ngf: int = 64, use_dropout: bool = False, instance_norm: bool = False,
+                 num_downs: int = 8):
         """instance_norm: --norm instance (networks.py:34-35): InstanceNorm2d without parameters, and every convolution
-        carries a bias (use_bias, networks.py:568-571)."""
+        carries a bias (use_bias, networks.py:568-571).  num_downs: 8 = unet_256, 7 = unet_128 (networks.py:148-151);
+        level D = num_downs is the innermost block (layer_index 0), dropout sits on the ngf*8 blocks in between."""
+        if not 5 <= num_downs <= 8:
+            raise NotImplementedError("genseg_b200: UnetGenerator with num_downs=%d (upconv_arch has 8 rows; the reference "
+                                      "builds 7 or 8 levels)" % num_downs)
         self.input_nc, self.output_nc, self.ngf, self.use_dropout = input_nc, output_nc, ngf, use_dropout
         self.inst = inst = bool(instance_norm)
-        c = [None, ngf, ngf * 2, ngf * 4, ngf * 8, ngf * 8, ngf * 8, ngf * 8, ngf * 8]  # channels of e_1..e_8
+        self.D = D = int(num_downs)
+        c = [None] + [ngf * min(2 ** (L - 1), 8) for L in range(1, D + 1)]  # channels of e_1..e_D
         self.c = c
         self.down: List[Optional[ConvBNAct]] = [None]
-        for L in range(1, 9):
+        for L in range(1, D + 1):
             cin = input_nc if L == 1 else c[L - 1]
             spec = ConvSpec("conv", cin, c[L], 4, 2, 1)
-            if L == 8:
+            if L == D:
                 self.down.append(ConvBNAct(spec, False, ACT_RELU))
             else:
                 self.down.append(ConvBNAct(spec, L != 1, ACT_LRELU, ACT_RELU, instance_norm=inst))
-        self.up: List[Optional[ConvBNAct]] = [None] * 8
-        for L in range(7, 0, -1):
-            cin = c[8] if L == 7 else 2 * c[L + 1]
+        self.up: List[Optional[ConvBNAct]] = [None] * D
+        for L in range(D - 1, 0, -1):
+            cin = c[D] if L == D - 1 else 2 * c[L + 1]
             self.up[L] = ConvBNAct(ConvSpec("convT", cin, c[L], 8, 2, 3), True, ACT_RELU,
-                                   dropout=use_dropout and L in (4, 5, 6), instance_norm=inst)
+                                   dropout=use_dropout and 4 <= L < D - 1, instance_norm=inst)
         self.outer = EdgeConv(ConvSpec("convT", 2 * c[1], output_nc, 8, 2, 3), ACT_TANH)
         names: List[str] = ["model.model.0.weight"] + (["model.model.0.bias"] if inst else [])
-        for L in range(2, 9):
+        for L in range(2, D + 1):
             q = _block_prefix(L)
             names.append(q + ".model.1.weight")
             if inst:
                 names.append(q + ".model.1.bias")
-            elif L != 8:
+            elif L != D:
                 names += [q + ".model.2.weight", q + ".model.2.bias"]
-        for L in range(7, 0, -1):
+        for L in range(D - 1, 0, -1):
             q = _block_prefix(L + 1)
-            ui, bi = (3, 4) if L == 7 else (5, 6)
+            ui, bi = (3, 4) if L == D - 1 else (5, 6)
             names += [f"{q}.model.{ui}._ops._ops.{i}.op.weight" for i in range(3)]
             if inst:
                 names += [f"{q}.model.{ui}._ops._ops.{i}.op.bias" for i in range(3)]
@@ -79,12 +85,12 @@ class GeneratorProgram:
 
     def _up_names(self, L: int):
         q = _block_prefix(L + 1)
-        ui, bi = (3, 4) if L == 7 else (5, 6)
+        ui, bi = (3, 4) if L == self.D - 1 else (5, 6)
         return [f"{q}.model.{ui}._ops._ops.{i}.op.weight" for i in range(3)], f"{q}.model.{bi}"
 
     def _up_bias_names(self, L: int):
         q = _block_prefix(L + 1)
-        ui = 3 if L == 7 else 5
+        ui = 3 if L == self.D - 1 else 5
         return [f"{q}.model.{ui}._ops._ops.{i}.op.bias" for i in range(3)]
 
     def _down_bias(self, P, L: int):
@@ -97,8 +103,10 @@ class GeneratorProgram:
         if x.dtype != torch.float32:
             x = x.float()
         n, cin, h, w = x.shape
-        if cin != self.input_nc or h % 256 != 0 or w % 256 != 0:
-            raise RuntimeError("UnetGenerator(unet_256): expected input [N,%d,256k,256k], got %s" % (self.input_nc, tuple(x.shape)))
+        D = self.D
+        if cin != self.input_nc or h % (1 << D) != 0 or w % (1 << D) != 0:
+            raise RuntimeError("UnetGenerator(num_downs=%d): expected input [N,%d,%dk,%dk], got %s"
+                               % (D, self.input_nc, 1 << D, 1 << D, tuple(x.shape)))
         dev = x.device
         arch = P[ARCH_KEY]
         if arch.dtype != torch.float32 or tuple(arch.shape) != (8, 3):
@@ -109,28 +117,28 @@ class GeneratorProgram:
         base_seed = int((extra or {}).get("drop_seed", 0)) or (torch.initial_seed() * 1000003 + self._calls) % (1 << 62) + 1
         tape: Dict[str, object] = {"x": x, "arch": arch}
         c = self.c
-        sizes = [(h, w)] + [(h >> L, w >> L) for L in range(1, 9)]      # sizes[L] = spatial of e_L
-        cats = [None] + [_nhwc_empty(n, sizes[L][0], sizes[L][1], 2 * c[L], dev) for L in range(1, 8)]
+        sizes = [(h, w)] + [(h >> L, w >> L) for L in range(1, D + 1)]      # sizes[L] = spatial of e_L
+        cats = [None] + [_nhwc_empty(n, sizes[L][0], sizes[L][1], 2 * c[L], dev) for L in range(1, D)]
         # ---- encoder
         cur_view, cur_keep, ch, cw = view_nchw(x), x, h, w
-        for L in range(1, 9):
+        for L in range(1, D + 1):
             q = _block_prefix(L)
             wname = "model.model.0.weight" if L == 1 else q + ".model.1.weight"
-            bn = self._bn(P, B, q + ".model.2") if (1 < L < 8 and not self.inst) else None
-            out2 = cats[L][..., :c[L]] if L < 8 else None
+            bn = self._bn(P, B, q + ".model.2") if (1 < L < D and not self.inst) else None
+            out2 = cats[L][..., :c[L]] if L < D else None
             s, sv = self.down[L].forward(cur_view, cur_keep, n, ch, cw, dev, P[wname], self._down_bias(P, L), bn, training,
                                          out2=out2, save=save)
             tape[f"down{L}"] = sv
             cur_view, cur_keep, (ch, cw) = view_nhwc(s), s, sizes[L]
         # ---- decoder
-        cur = cur_keep                                   # u = relu(e_8)
-        for L in range(7, 0, -1):
+        cur = cur_keep                                   # u = relu(e_D)
+        for L in range(D - 1, 0, -1):
             wn, bnp = self._up_names(L)
             if self.inst:
                 bnm = self._up_bias_names(L)
-                wm, bm_up = ops.merge_upconv(P[wn[0]], P[wn[1]], P[wn[2]], P[bnm[0]], P[bnm[1]], P[bnm[2]], arch[7 - L])
+                wm, bm_up = ops.merge_upconv(P[wn[0]], P[wn[1]], P[wn[2]], P[bnm[0]], P[bnm[1]], P[bnm[2]], arch[D - 1 - L])
             else:
-                wm, bm_up = ops.merge_upconv(P[wn[0]], P[wn[1]], P[wn[2]], None, None, None, arch[7 - L])[0], None
+                wm, bm_up = ops.merge_upconv(P[wn[0]], P[wn[1]], P[wn[2]], None, None, None, arch[D - 1 - L])[0], None
             hh, ww = cur.shape[1], cur.shape[2]
             drop = self.up[L].dropout and training
             mask = masks[L - 4] if (drop and masks is not None) else None
@@ -142,7 +150,7 @@ class GeneratorProgram:
             cur = cats[L]
         wo = [f"model.model.3._ops._ops.{i}.op.weight" for i in range(3)]
         bo = [f"model.model.3._ops._ops.{i}.op.bias" for i in range(3)]
-        wm, bm = ops.merge_upconv(P[wo[0]], P[wo[1]], P[wo[2]], P[bo[0]], P[bo[1]], P[bo[2]], arch[7])
+        wm, bm = ops.merge_upconv(P[wo[0]], P[wo[1]], P[wo[2]], P[bo[0]], P[bo[1]], P[bo[2]], arch[D - 1])
         out, sv = self.outer.forward(cur, wm, bm, save)
         tape["outer"] = sv
         tape["P"] = P if save else None
@@ -154,7 +162,7 @@ class GeneratorProgram:
         P = tape["P"]
         arch = tape["arch"]
         dev = dout.device
-        c, sizes, n = self.c, tape["sizes"], tape["n"]
+        c, sizes, n, D = self.c, tape["sizes"], tape["n"], self.D
         dalpha = torch.zeros_like(arch)
 
         def unmerge(dwm, dbm, wn, bn_, row):
@@ -173,9 +181,9 @@ class GeneratorProgram:
         need_wo = need_arch or any(need.get(k, False) for k in wo + bo)
         dcat, dwm, dbm = self.outer.backward(tape["outer"], dout, True, need_wo, need_wo)
         if need_wo:
-            unmerge(dwm, dbm, wo, bo, 7)
-        dskips: List[Optional[torch.Tensor]] = [None] * 9
-        for L in range(1, 8):
+            unmerge(dwm, dbm, wo, bo, D - 1)
+        dskips: List[Optional[torch.Tensor]] = [None] * (D + 1)
+        for L in range(1, D):
             wn, bnp = self._up_names(L)
             ubn = self._up_bias_names(L) if self.inst else None
             nw = need_arch or any(need.get(k, False) for k in wn + (ubn or []))
@@ -184,31 +192,31 @@ class GeneratorProgram:
             dnext, dwm, dbm_up, dg, db = self.up[L].backward(tape[f"up{L}"], dcat[..., c[L]:], None, True, nw, nb,
                                                              self.inst and nw)
             if nw:
-                unmerge(dwm, dbm_up if self.inst else None, wn, ubn, 7 - L)
+                unmerge(dwm, dbm_up if self.inst else None, wn, ubn, D - 1 - L)
             if not self.inst:
                 _put(G, bnp + ".weight", dg)
                 _put(G, bnp + ".bias", db)
-            dcat = dnext            # gradient of cat_{L+1} (or of u for L == 7)
+            dcat = dnext            # gradient of cat_{L+1} (or of u for L == D - 1)
         ds = dcat
         dx = None
-        for L in range(8, 0, -1):
+        for L in range(D, 0, -1):
             q = _block_prefix(L)
             wname = "model.model.0.weight" if L == 1 else q + ".model.1.weight"
             nb = ((need.get(q + ".model.2.weight", False) or need.get(q + ".model.2.bias", False))
-                  if (1 < L < 8 and not self.inst) else False)
+                  if (1 < L < D and not self.inst) else False)
             bname = ("model.model.0.bias" if L == 1 else q + ".model.1.bias") if self.inst else None
             want_dx = True if L > 1 else need_dx
             dxo = dxv = None
             if L == 1 and need_dx:
                 dxo = torch.empty_like(tape["x"])
                 dxv = view_nchw(dxo)
-            ds, dw, dbias, dg, db = self.down[L].backward(tape[f"down{L}"], ds, dskips[L] if L < 8 else None, want_dx,
+            ds, dw, dbias, dg, db = self.down[L].backward(tape[f"down{L}"], ds, dskips[L] if L < D else None, want_dx,
                                                           need.get(wname, False), nb, bool(bname and need.get(bname, False)),
                                                           dx_out=dxo, dx_view=dxv)
             _put(G, wname, dw)
             if bname:
                 _put(G, bname, dbias)
-            if 1 < L < 8 and not self.inst:
+            if 1 < L < D and not self.inst:
                 _put(G, q + ".model.2.weight", dg)
                 _put(G, q + ".model.2.bias", db)
             if L == 1:
@@ -219,25 +227,28 @@ class GeneratorProgram:
 
 
 class DiscriminatorProgram:
-    """NLayerDiscriminator(input_nc, ndf, n_layers=3, BatchNorm2d)."""
+    """NLayerDiscriminator(input_nc, ndf, n_layers, norm): 'basic' = 3 layers (70x70 patches), 'n_layers' takes
+    --n_layers_D (networks.py:197-200).  Sequential indices: conv 0, then conv/norm/LeakyReLU triples at 2, 5, ...,
+    2 + 3 (n_layers - 1) (the last with stride 1), and the 1-channel head at 2 + 3 n_layers."""
 
     def __init__(self, input_nc: int, ndf: int = 64, n_layers: int = 3, instance_norm: bool = False):
-        if n_layers != 3:
-            raise NotImplementedError("genseg_b200: only the 'basic' 3-layer PatchGAN is on the B200 path")
+        if n_layers < 1:
+            raise ValueError("NLayerDiscriminator needs n_layers >= 1")
         self.input_nc = input_nc
         self.inst = inst = bool(instance_norm)
+        ch = [ndf * min(2 ** i, 8) for i in range(n_layers + 1)]
         self.l0 = ConvBNAct(ConvSpec("conv", input_nc, ndf, 4, 2, 1), False, ACT_LRELU)
-        self.mid = [(2, ConvBNAct(ConvSpec("conv", ndf, ndf * 2, 4, 2, 1), True, ACT_LRELU, instance_norm=inst)),
-                    (5, ConvBNAct(ConvSpec("conv", ndf * 2, ndf * 4, 4, 2, 1), True, ACT_LRELU, instance_norm=inst)),
-                    (8, ConvBNAct(ConvSpec("conv", ndf * 4, ndf * 8, 4, 1, 1), True, ACT_LRELU, instance_norm=inst))]
-        self.last = EdgeConv(ConvSpec("conv", ndf * 8, 1, 4, 1, 1), ACT_NONE)
+        self.mid = [(2 + 3 * (i - 1), ConvBNAct(ConvSpec("conv", ch[i - 1], ch[i], 4, 2 if i < n_layers else 1, 1), True, ACT_LRELU,
+                                                instance_norm=inst)) for i in range(1, n_layers + 1)]
+        self.head = 2 + 3 * n_layers
+        self.last = EdgeConv(ConvSpec("conv", ch[n_layers], 1, 4, 1, 1), ACT_NONE)
         names = ["model.0.weight", "model.0.bias"]
         for idx, _ in self.mid:
             if inst:    # InstanceNorm2d(affine=False): no norm parameters, the convolution has a bias
                 names += [f"model.{idx}.weight", f"model.{idx}.bias"]
             else:
                 names += [f"model.{idx}.weight", f"model.{idx + 1}.weight", f"model.{idx + 1}.bias"]
-        names += ["model.11.weight", "model.11.bias"]
+        names += [f"model.{self.head}.weight", f"model.{self.head}.bias"]
         self.param_names = names
 
     def forward(self, x: torch.Tensor, P, B, training: bool, save: bool, extra=None):
@@ -259,16 +270,16 @@ class DiscriminatorProgram:
             a, sv = layer.forward(view_nhwc(a), a, n, a.shape[1], a.shape[2], dev, P[f"model.{idx}.weight"],
                                   P[f"model.{idx}.bias"] if self.inst else None, bn, training, save=save)
             tape[f"l{idx}"] = sv
-        out, sv = self.last.forward(a, P["model.11.weight"], P["model.11.bias"], save)
+        out, sv = self.last.forward(a, P[f"model.{self.head}.weight"], P[f"model.{self.head}.bias"], save)
         tape["last"] = sv
         return out, tape
 
     def backward(self, tape, dout, need: Dict[str, bool], need_dx: bool):
         G: Dict[str, torch.Tensor] = {}
-        d, dw, db = self.last.backward(tape["last"], dout, True, need.get("model.11.weight", False),
-                                       need.get("model.11.bias", False))
-        _put(G, "model.11.weight", dw)
-        _put(G, "model.11.bias", db)
+        hw_, hb_ = f"model.{self.head}.weight", f"model.{self.head}.bias"
+        d, dw, db = self.last.backward(tape["last"], dout, True, need.get(hw_, False), need.get(hb_, False))
+        _put(G, hw_, dw)
+        _put(G, hb_, db)
         for idx, layer in reversed(self.mid):
             p = f"model.{idx + 1}"
             nb = (not self.inst) and (need.get(p + ".weight", False) or need.get(p + ".bias", False))

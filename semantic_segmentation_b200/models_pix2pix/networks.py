@@ -80,9 +80,11 @@ def define_G(input_nc, output_nc, ngf, netG, norm='batch', use_dropout=False, in
     norm_layer = get_norm_layer(norm_type=norm)
     if netG == 'unet_256':
         net = UnetGenerator(input_nc, output_nc, 8, ngf, norm_layer=norm_layer, use_dropout=use_dropout)
-    elif netG in ('unet_128', 'resnet_9blocks', 'resnet_6blocks'):
+    elif netG == 'unet_128':
+        net = UnetGenerator(input_nc, output_nc, 7, ngf, norm_layer=norm_layer, use_dropout=use_dropout)
+    elif netG in ('resnet_9blocks', 'resnet_6blocks'):
         raise NotImplementedError('genseg_b200: generator [%s] is outside the B200 hot path (pix2pix_model.py:36 '
-                                  'forces unet_256)' % netG)
+                                  'sets unet_256)' % netG)
     else:
         raise NotImplementedError('Generator model name [%s] is not recognized' % netG)
     return init_net(net, init_type, init_gain, gpu_ids)
@@ -275,8 +277,6 @@ class UnetGenerator(nn.Module):
 
     def __init__(self, input_nc, output_nc, num_downs, ngf=64, norm_layer=nn.BatchNorm2d, use_dropout=False):
         super(UnetGenerator, self).__init__()
-        if num_downs != 8:
-            raise NotImplementedError("genseg_b200: only unet_256 (num_downs=8) is on the B200 path")
         self.layer_index = 0
         unet_block = UnetSkipConnectionBlock(ngf * 8, ngf * 8, input_nc=None, layer_index=self.layer_index, submodule=None,
                                              norm_layer=norm_layer, innermost=True)
@@ -293,7 +293,7 @@ class UnetGenerator(nn.Module):
                                              submodule=unet_block, outermost=True, norm_layer=norm_layer)
         self.layer_index += 1
         inst = (norm_layer.func if type(norm_layer) == functools.partial else norm_layer) == nn.InstanceNorm2d
-        self._program = GeneratorProgram(input_nc, output_nc, ngf, use_dropout, instance_norm=inst)
+        self._program = GeneratorProgram(input_nc, output_nc, ngf, use_dropout, instance_norm=inst, num_downs=num_downs)
         self._dropout_masks = None      # test hook: list of three uint8 NHWC keep-masks (depth 4, 5, 6)
 
     def forward(self, input):

@@ -137,13 +137,16 @@ def dice_kats():
     print("dice kats", {k: v for k, v in out.items() if not hasattr(v, "shape")})
 
 
-def pix2pix_case(name, use_dropout, g_train, batch=2):
-    specG = O.generator_state_spec(1, 1, 64)
-    specD = O.discriminator_state_spec(2, 64)
+def pix2pix_case(name, use_dropout, g_train, batch=2, netG="unet_256", n_layers=3, hw=256):
+    """netG 'unet_128' (networks.py:148-151, 7 levels) and netD 'n_layers' with n_layers != 3 (networks.py:199-200) are the
+    flag-reachable variants of the same modules; their fixtures record netG / n_layers / hw."""
+    num_downs = {"unet_256": 8, "unet_128": 7}[netG]
+    specG = O.generator_state_spec(1, 1, 64, num_downs)
+    specD = O.discriminator_state_spec(2, 64, n_layers)
     stG = O.seeded_state(specG, 11, conv_std=0.02)
     stD = O.seeded_state(specD, 12, conv_std=0.02)
-    G = networks.define_G(1, 1, 64, "unet_256", "batch", use_dropout, "normal", 0.02, [])
-    D = networks.define_D(2, 64, "basic", 3, "batch", "normal", 0.02, [])
+    G = networks.define_G(1, 1, 64, netG, "batch", use_dropout, "normal", 0.02, [])
+    D = networks.define_D(2, 64, "basic" if n_layers == 3 else "n_layers", n_layers, "batch", "normal", 0.02, [])
     assert list(G.state_dict().keys()) == list(specG.keys())
     assert list(D.state_dict().keys()) == list(specD.keys())
     for k in specG:
@@ -156,8 +159,8 @@ def pix2pix_case(name, use_dropout, g_train, batch=2):
     if networks.upconv_arch.grad is not None:
         networks.upconv_arch.grad = None
     g = torch.Generator().manual_seed(14)
-    mask = torch.randint(0, 2, (batch, 1, 256, 256), generator=g).float()
-    image = torch.rand(batch, 1, 256, 256, generator=g)
+    mask = torch.randint(0, 2, (batch, 1, hw, hw), generator=g).float()
+    image = torch.rand(batch, 1, hw, hw, generator=g)
     G.train(g_train)
     D.train()
     masks = []
@@ -195,12 +198,13 @@ def pix2pix_case(name, use_dropout, g_train, batch=2):
         gradD_norms=np.array([gD[k].norm().item() for k in gD], np.float64), gradD_keys=np.array(list(gD.keys())),
         grad_arch=networks.upconv_arch.grad.numpy().copy(),
         mask_sum=mask.sum().item(), image_sum=image.double().sum().item(),
+        num_downs=np.array(num_downs), n_layers=np.array(n_layers), hw=np.array(hw),
     )
     out["gradG:model.model.0.weight"] = gG["model.model.0.weight"].numpy()
     out["gradG:outer_bias8"] = gG["model.model.3._ops._ops.2.op.bias"].numpy()
     out["gradG:outer_w4"] = gG["model.model.3._ops._ops.0.op.weight"].numpy()
     out["gradD:model.0.weight"] = gD["model.0.weight"].numpy()
-    out["gradD:model.11.weight"] = gD["model.11.weight"].numpy()
+    out["gradD:model.11.weight"] = gD["model.%d.weight" % (2 + 3 * n_layers)].numpy()      # the 1-channel head
     if use_dropout and g_train:
         # hooks fire innermost-dropout first: blocks with layer_index 1,2,3 -> depth 6,5,4
         assert len(masks) == 3
@@ -250,7 +254,7 @@ def pix2pix_instance_case(name="pix2pix_instance", batch=2):
     out["gradG:model.model.0.weight"] = gG["model.model.0.weight"].numpy()
     out["gradG:outer_w4"] = gG["model.model.3._ops._ops.0.op.weight"].numpy()
     out["gradD:model.0.weight"] = gD["model.0.weight"].numpy()
-    out["gradD:model.11.weight"] = gD["model.11.weight"].numpy()
+    out["gradD:model.11.weight"] = gD["model.%d.weight" % (2 + 3 * n_layers)].numpy()      # the 1-channel head
     np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
     print(name, "loss_D", loss_D.item(), "G_GAN", g_gan.item(), "G_L1", g_l1.item())
 
@@ -258,6 +262,10 @@ def pix2pix_instance_case(name="pix2pix_instance", batch=2):
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "instance":
         pix2pix_instance_case()
+        sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "variants":
+        pix2pix_case("pix2pix_unet128_nl2", use_dropout=False, g_train=True, netG="unet_128", n_layers=2, hw=128)
+        pix2pix_case("pix2pix_unet128_nl4", use_dropout=False, g_train=True, netG="unet_128", n_layers=4, hw=256)
         sys.exit(0)
     unet_case("unet_c2_bilinear_32", 1, 2, True, 2, 32, 32, wseed=1, xseed=2)
     unet_case("unet_c1_convT_32", 1, 1, False, 2, 32, 32, wseed=3, xseed=4)

@@ -48,6 +48,19 @@ def test_state_dict_layout_matches_reference_spec():
     D = networks.define_D(2, 64, "basic", 3, "batch", "normal", 0.02, [])
     assert list(G.state_dict().keys()) == list(O.generator_state_spec(1, 1, 64).keys())
     assert list(D.state_dict().keys()) == list(O.discriminator_state_spec(2, 64).keys())
+    # flag-reachable variants: --netG unet_128 (networks.py:148-151), --netD n_layers --n_layers_D k (networks.py:199-200)
+    G7 = networks.define_G(1, 3, 64, "unet_128", "batch", True, "normal", 0.02, [])
+    spec7 = O.generator_state_spec(1, 3, 64, 7)
+    assert list(G7.state_dict().keys()) == list(spec7.keys())
+    assert all(tuple(G7.state_dict()[k].shape) == tuple(spec7[k]) for k in spec7)
+    assert set(G7._program.param_names) - {"__upconv_arch__"} == set(dict(G7.named_parameters()).keys())
+    assert [L for L in range(1, 7) if G7._program.up[L].dropout] == [4, 5]
+    for nl in (1, 2, 4, 5):
+        Dn = networks.define_D(4, 64, "n_layers", nl, "batch", "normal", 0.02, [])
+        specn = O.discriminator_state_spec(4, 64, nl)
+        assert list(Dn.state_dict().keys()) == list(specn.keys())
+        assert all(tuple(Dn.state_dict()[k].shape) == tuple(specn[k]) for k in specn)
+        assert set(Dn._program.param_names) == set(dict(Dn.named_parameters()).keys())
     assert networks.arch_parameters()[0] is networks.upconv_arch and tuple(networks.upconv_arch.shape) == (8, 3)
     assert networks.upconv_arch.requires_grad
     # init rule of networks.py:84-101: conv weights N(0, 0.02), BN weight N(1, 0.02)

@@ -35,20 +35,23 @@ def run_pix2pix(name, g_train, drop, precision, golden_dir):
     gold = np.load(os.path.join(golden_dir, name + ".npz"))
     S.set_precision(precision)
     old_arch = networks.upconv_arch
+    num_downs = int(gold["num_downs"]) if "num_downs" in gold else 8        # unet_256 | unet_128
+    n_layers = int(gold["n_layers"]) if "n_layers" in gold else 3            # 'basic' | 'n_layers'
+    hw = int(gold["hw"]) if "hw" in gold else 256
     try:
-        G = networks.define_G(1, 1, 64, "unet_256", "batch", True, "normal", 0.02, [])
-        D = networks.define_D(2, 64, "basic", 3, "batch", "normal", 0.02, [])
-        G.load_state_dict(O.seeded_state(O.generator_state_spec(1, 1, 64), 11, conv_std=0.02), strict=True)
-        D.load_state_dict(O.seeded_state(O.discriminator_state_spec(2, 64), 12, conv_std=0.02), strict=True)
+        G = networks.define_G(1, 1, 64, {8: "unet_256", 7: "unet_128"}[num_downs], "batch", num_downs == 8, "normal", 0.02, [])
+        D = networks.define_D(2, 64, "basic" if n_layers == 3 else "n_layers", n_layers, "batch", "normal", 0.02, [])
+        G.load_state_dict(O.seeded_state(O.generator_state_spec(1, 1, 64, num_downs), 11, conv_std=0.02), strict=True)
+        D.load_state_dict(O.seeded_state(O.discriminator_state_spec(2, 64, n_layers), 12, conv_std=0.02), strict=True)
         G, D = G.to(DEV), D.to(DEV)
         networks.upconv_arch = torch.from_numpy(gold["arch"]).to(DEV).requires_grad_(True)   # like pix2pix_model.py:63
         g = torch.Generator().manual_seed(14)
-        mask = torch.randint(0, 2, (2, 1, 256, 256), generator=g).float().to(DEV)
-        image = torch.rand(2, 1, 256, 256, generator=g).to(DEV)
+        mask = torch.randint(0, 2, (2, 1, hw, hw), generator=g).float().to(DEV)
+        image = torch.rand(2, 1, hw, hw, generator=g).to(DEV)
         G.train(g_train)
         D.train()
         G._dropout_masks = _masks(gold) if drop else None
-        if g_train and not drop:
+        if g_train and not drop and num_downs == 8:
             G._program.use_dropout = False
             for L in (4, 5, 6):
                 G._program.up[L].dropout = False
@@ -82,7 +85,7 @@ def run_pix2pix(name, g_train, drop, precision, golden_dir):
         out["gG_outer_w4"] = rel(gG["model.model.3._ops._ops.0.op.weight"], gold["gradG:outer_w4"])
         out["gG_outer_b8"] = rel(gG["model.model.3._ops._ops.2.op.bias"], gold["gradG:outer_bias8"])
         out["gD0"] = rel(gD["model.0.weight"], gold["gradD:model.0.weight"])
-        out["gD11"] = rel(gD["model.11.weight"], gold["gradD:model.11.weight"])
+        out["gD11"] = rel(gD["model.%d.weight" % (2 + 3 * n_layers)], gold["gradD:model.11.weight"])   # the 1-channel head
         return out
     finally:
         networks.upconv_arch = old_arch
@@ -103,6 +106,30 @@ def test_pix2pix_fp32_matches_reference(name, g_train, drop, golden_dir):
     assert out["gradD_norms"] < 5e-2 and out["gD0"] < 5e-2 and out["gD11"] < 5e-2, out
     assert out["gradG_norms_median"] < 1e-2 and out["gG_outer_w4"] < 5e-2 and out["gG_outer_b8"] < 5e-2, out
     assert out["grad_arch"] < 5e-2, out
+
+
+VARIANTS = ["pix2pix_unet128_nl2", "pix2pix_unet128_nl4"]
+
+
+@pytest.mark.parametrize("name", VARIANTS)
+def test_pix2pix_variants_fp32_match_reference(name, golden_dir):
+    """Flag-reachable variants of the same modules: --netG unet_128 (7 levels, networks.py:148-151) and
+    --netD n_layers with n_layers_D 2 / 4 (networks.py:199-200), at 128^2 and 256^2; same bounds as the unet_256 cases."""
+    out = run_pix2pix(name, True, False, "fp32", golden_dir)
+    print(name, "fp32", out)
+    assert out["fake"] < 2e-4 and out["pred_fake"] < 2e-4 and out["pred_real"] < 1e-4, out
+    assert out["loss_D"] < 1e-4 and out["G_GAN"] < 1e-4 and out["G_L1"] < 2e-3, out
+    assert out["gradD_norms"] < 5e-2 and out["gD0"] < 5e-2 and out["gD11"] < 5e-2, out
+    assert out["gradG_norms_median"] < 1e-2 and out["gG_outer_w4"] < 5e-2 and out["gG_outer_b8"] < 5e-2, out
+    assert out["grad_arch"] < 5e-2, out
+
+
+@pytest.mark.parametrize("name", VARIANTS)
+def test_pix2pix_variants_bf16_run_close(name, golden_dir):
+    out = run_pix2pix(name, True, False, "bf16", golden_dir)
+    print(name, "bf16", out)
+    assert out["fake"] < 1e-1 and out["pred_real"] < 5e-2, out
+    assert out["loss_D"] < 2e-2 and out["G_GAN"] < 2e-2 and out["G_L1"] < 0.5, out
 
 
 @pytest.mark.parametrize("name,g_train,drop", CASES[:2])
@@ -152,8 +179,8 @@ def _run_instance(precision, golden_dir):
         G, D = G.to(DEV).train(), D.to(DEV).train()
         networks.upconv_arch = torch.from_numpy(gold["arch"]).to(DEV).requires_grad_(True)
         g = torch.Generator().manual_seed(24)
-        mask = torch.randint(0, 2, (2, 1, 256, 256), generator=g).float().to(DEV)
-        image = torch.rand(2, 1, 256, 256, generator=g).to(DEV)
+        mask = torch.randint(0, 2, (2, 1, hw, hw), generator=g).float().to(DEV)
+        image = torch.rand(2, 1, hw, hw, generator=g).to(DEV)
         crit = networks.GANLoss("lsgan").to(DEV)
         fake = G(mask)
         pred_fake_d = D(torch.cat([mask, fake], 1).detach())
@@ -183,7 +210,7 @@ def _run_instance(precision, golden_dir):
         out["gG0"] = rel(gG["model.model.0.weight"], gold["gradG:model.model.0.weight"])
         out["gG_outer_w4"] = rel(gG["model.model.3._ops._ops.0.op.weight"], gold["gradG:outer_w4"])
         out["gD0"] = rel(gD["model.0.weight"], gold["gradD:model.0.weight"])
-        out["gD11"] = rel(gD["model.11.weight"], gold["gradD:model.11.weight"])
+        out["gD11"] = rel(gD["model.%d.weight" % (2 + 3 * n_layers)], gold["gradD:model.11.weight"])   # the 1-channel head
         return out
     finally:
         networks.upconv_arch = old_arch

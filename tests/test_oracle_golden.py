@@ -101,15 +101,20 @@ def _unpack_masks(gold):
 
 @pytest.mark.parametrize("name,g_train,drop", [("pix2pix_train_nodrop", True, False),
                                                ("pix2pix_train_drop", True, True),
-                                               ("pix2pix_eval", False, False)])
+                                               ("pix2pix_eval", False, False),
+                                               ("pix2pix_unet128_nl2", True, False),
+                                               ("pix2pix_unet128_nl4", True, False)])
 def test_pix2pix_oracle_matches_reference(name, g_train, drop, golden_dir):
     gold = np.load(os.path.join(golden_dir, name + ".npz"))
-    stG = O.seeded_state(O.generator_state_spec(1, 1, 64), 11, conv_std=0.02)
-    stD = O.seeded_state(O.discriminator_state_spec(2, 64), 12, conv_std=0.02)
+    num_downs = int(gold["num_downs"]) if "num_downs" in gold else 8       # unet_256 | unet_128 (networks.py:148-151)
+    n_layers = int(gold["n_layers"]) if "n_layers" in gold else 3           # 'basic' | 'n_layers' (networks.py:197-200)
+    hw = int(gold["hw"]) if "hw" in gold else 256
+    stG = O.seeded_state(O.generator_state_spec(1, 1, 64, num_downs), 11, conv_std=0.02)
+    stD = O.seeded_state(O.discriminator_state_spec(2, 64, n_layers), 12, conv_std=0.02)
     arch = torch.from_numpy(gold["arch"]).clone().requires_grad_(True)
     g = torch.Generator().manual_seed(14)
-    mask = torch.randint(0, 2, (2, 1, 256, 256), generator=g).float()
-    image = torch.rand(2, 1, 256, 256, generator=g)
+    mask = torch.randint(0, 2, (2, 1, hw, hw), generator=g).float()
+    image = torch.rand(2, 1, hw, hw, generator=g)
     assert mask.sum().item() == float(gold["mask_sum"])
     pG = {k: v.clone().requires_grad_(True) for k, v in stG.items()
           if v.dtype.is_floating_point and "running" not in k}
@@ -119,7 +124,7 @@ def test_pix2pix_oracle_matches_reference(name, g_train, drop, golden_dir):
     wG.update(pG)
     wD.update(pD)
     masks = _unpack_masks(gold) if drop else None
-    fake = O.generator_forward(wG, mask, arch, training=g_train, dropout_masks=masks)
+    fake = O.generator_forward(wG, mask, arch, training=g_train, dropout_masks=masks, num_downs=num_downs)
     assert rel_l2(fake.detach().flatten()[::13], gold["fake_sample"]) < 2e-5
     pred_fake_d = O.discriminator_forward(wD, torch.cat([mask, fake.detach()], 1))
     pred_real = O.discriminator_forward(wD, torch.cat([mask, image], 1))
