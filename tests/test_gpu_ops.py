@@ -387,6 +387,22 @@ def test_multi_tensor_optimizers_match_torch():
             do.step()
         for r, d in zip(ref, dev):
             assert rel(d, r) < 1e-6, kind
+        # torch.optim.Optimizer protocol: the state of the fused optimiser loads into torch.optim's class (and a fresh fused
+        # one), and both continue identically
+        ref2 = [d.detach().cpu().clone().requires_grad_(True) for d in dev]
+        dev2 = [d.detach().clone().requires_grad_(True) for d in dev]
+        ro2 = type(ro)(ref2, **{k: v for k, v in ro.defaults.items() if k in ("lr", "weight_decay", "momentum", "betas")})
+        do2 = type(do)(dev2, lr=9.9)
+        ro2.load_state_dict(do.state_dict())
+        do2.load_state_dict(do.state_dict())
+        for r, d, d2, gr in zip(ref2, dev, dev2, grads[0]):
+            r.grad, d.grad, d2.grad = gr.clone(), gr.to(DEV), gr.to(DEV)
+        ro2.step()
+        do.step()
+        do2.step()
+        for r, d, d2 in zip(ref2, dev, dev2):
+            assert torch.equal(d.detach(), d2.detach()), kind
+            assert rel(d, r) < 1e-6, kind
 
 
 def test_batched_pack_and_unpack_match_single():
