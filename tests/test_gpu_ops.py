@@ -1,4 +1,5 @@
 """GPU parity tests of the individual C-ABI ops against the same torch CPU functionals the oracle uses."""
+import copy
 import math
 
 import numpy as np
@@ -394,7 +395,7 @@ def test_multi_tensor_optimizers_match_torch():
         ro2 = type(ro)(ref2, **{k: v for k, v in ro.defaults.items() if k in ("lr", "weight_decay", "momentum", "betas")})
         do2 = type(do)(dev2, lr=9.9)
         ro2.load_state_dict(do.state_dict())
-        do2.load_state_dict(do.state_dict())
+        do2.load_state_dict(copy.deepcopy(do.state_dict()))     # load_state_dict aliases same-device state tensors
         for r, d, d2, gr in zip(ref2, dev, dev2, grads[0]):
             r.grad, d.grad, d2.grad = gr.clone(), gr.to(DEV), gr.to(DEV)
         ro2.step()
