@@ -26,11 +26,13 @@ __device__ __forceinline__ float key_f32(uint32_t k) {
 }
 
 __global__ void minmax_init_kernel(uint32_t* keys) {
+  GSB_PDL_ENTRY();
   keys[0] = 0xffffffffu;  // min
   keys[1] = 0u;           // max
 }
 
 __global__ void __launch_bounds__(256) minmax_kernel(const float* __restrict__ x, int64_t n, uint32_t* __restrict__ keys) {
+  GSB_PDL_ENTRY();
   uint32_t lo = 0xffffffffu, hi = 0u;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const uint32_t k = f32_key(x[i]);
@@ -61,6 +63,7 @@ __global__ void __launch_bounds__(256) minmax_kernel(const float* __restrict__ x
 // keys == nullptr: x is already in [0, 1] scale-free form and only mul / add / clamp / truncate apply.
 __global__ void __launch_bounds__(256) quant_hist_kernel(const float* __restrict__ x, const uint32_t* __restrict__ keys,
                                                         uint8_t* __restrict__ q, uint32_t* __restrict__ hist, int plane) {
+  GSB_PDL_ENTRY();
   __shared__ uint32_t s_hist[256];
   s_hist[threadIdx.x] = 0;
   __syncthreads();
@@ -84,6 +87,7 @@ __global__ void __launch_bounds__(256) quant_hist_kernel(const float* __restrict
 }
 
 __global__ void __launch_bounds__(256) hist_u8_kernel(const uint8_t* __restrict__ q, uint32_t* __restrict__ hist, int plane) {
+  GSB_PDL_ENTRY();
   __shared__ uint32_t s_hist[256];
   s_hist[threadIdx.x] = 0;
   __syncthreads();
@@ -101,6 +105,7 @@ __global__ void __launch_bounds__(256) hist_u8_kernel(const uint8_t* __restrict_
 __global__ void __launch_bounds__(256) equalize_lut_kernel(const uint8_t* __restrict__ q, const uint32_t* __restrict__ hist,
                                                           const uint8_t* __restrict__ post, float* __restrict__ out_f,
                                                           uint8_t* __restrict__ out_u8, int plane, int do_equalize) {
+  GSB_PDL_ENTRY();
   __shared__ uint32_t s_cum[256];
   __shared__ float s_lut_f[256];
   __shared__ uint8_t s_lut[256];
@@ -142,6 +147,7 @@ __global__ void __launch_bounds__(256) equalize_lut_kernel(const uint8_t* __rest
 // shear in the drawn order and inverts).  thr < 0: the interpolated value itself is written.
 __global__ void __launch_bounds__(256) mask_affine_kernel(const float* __restrict__ in, const float* __restrict__ mats,
                                                          float* __restrict__ out, int h, int w, float thr) {
+  GSB_PDL_ENTRY();
   const int n = blockIdx.y;
   const float* m = mats + n * 6;
   const float m0 = m[0], m1 = m[1], m2 = m[2], m3 = m[3], m4 = m[4], m5 = m[5];
@@ -177,10 +183,10 @@ using namespace gsb;
 extern "C" int gsb_minmax_f32(const float* x, int64_t n, uint32_t* keys, gsb_stream s) {
   GSB_REQUIRE(x && keys && n > 0, "minmax_f32: bad arguments");
   cudaStream_t st = to_stream(s);
-  minmax_init_kernel<<<1, 1, 0, st>>>(keys);
+  gsb::launch(minmax_init_kernel, gsb::LaunchCfg(1, 1, 0, st), keys);
   int64_t b = (n + 256 * 8 - 1) / (256 * 8);
   const int64_t cap = (int64_t)num_sms() * 8;
-  minmax_kernel<<<(int)(b > cap ? cap : b), 256, 0, st>>>(x, n, keys);
+  gsb::launch(minmax_kernel, gsb::LaunchCfg((int)(b > cap ? cap : b), 256, 0, st), x, n, keys);
   return check_launch("minmax_f32", 2);
 }
 
@@ -192,7 +198,7 @@ extern "C" int gsb_quantize_hist(const float* x, const uint32_t* keys, uint8_t* 
   cudaStream_t st = to_stream(s);
   cudaError_t e = cudaMemsetAsync(hist, 0, (size_t)planes * 256 * sizeof(uint32_t), st);
   GSB_REQUIRE(e == cudaSuccess, "quantize_hist: memset failed: %s", cudaGetErrorString(e));
-  quant_hist_kernel<<<dim3(plane_blocks(plane, planes), planes), 256, 0, st>>>(x, keys, q, hist, plane);
+  gsb::launch(quant_hist_kernel, gsb::LaunchCfg(dim3(plane_blocks(plane, planes), planes), 256, 0, st), x, keys, q, hist, plane);
   return check_launch("quantize_hist");
 }
 
@@ -208,10 +214,10 @@ extern "C" int gsb_equalize_lut(const uint8_t* q, const uint32_t* hist, uint32_t
   if (hist == nullptr) {
     cudaError_t e = cudaMemsetAsync(ws_hist, 0, (size_t)planes * 256 * sizeof(uint32_t), st);
     GSB_REQUIRE(e == cudaSuccess, "equalize_lut: memset failed: %s", cudaGetErrorString(e));
-    hist_u8_kernel<<<dim3(blocks, planes), 256, 0, st>>>(q, ws_hist, plane);
+    gsb::launch(hist_u8_kernel, gsb::LaunchCfg(dim3(blocks, planes), 256, 0, st), q, ws_hist, plane);
     hist = ws_hist;
   }
-  equalize_lut_kernel<<<dim3(blocks, planes), 256, 0, st>>>(q, hist, post, out_f, out_u8, plane, do_equalize);
+  gsb::launch(equalize_lut_kernel, gsb::LaunchCfg(dim3(blocks, planes), 256, 0, st), q, hist, post, out_f, out_u8, plane, do_equalize);
   return check_launch("equalize_lut");
 }
 
@@ -219,6 +225,6 @@ extern "C" int gsb_equalize_lut(const uint8_t* q, const uint32_t* hist, uint32_t
 extern "C" int gsb_mask_affine(const float* in, const float* mats, float* out, int n, int h, int w, float threshold,
                                gsb_stream s) {
   GSB_REQUIRE(in && mats && out && n > 0 && h > 0 && w > 0 && n <= 65535, "mask_affine: bad arguments");
-  mask_affine_kernel<<<dim3(plane_blocks(h * w, n), n), 256, 0, to_stream(s)>>>(in, mats, out, h, w, threshold);
+  gsb::launch(mask_affine_kernel, gsb::LaunchCfg(dim3(plane_blocks(h * w, n), n), 256, 0, to_stream(s)), in, mats, out, h, w, threshold);
   return check_launch("mask_affine");
 }

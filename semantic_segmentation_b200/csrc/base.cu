@@ -1,5 +1,6 @@
 // Error plumbing, version and device queries of libgenseg_b200.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -27,6 +28,15 @@ int check_launch(const char* what, int n) {
     return -3;
   }
   return 0;
+}
+
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("GSB_PDL");
+    on = (e && e[0] == '1') ? 1 : 0;   // off by default: measured neutral (profiles/README.md, r01r)
+  }
+  return on == 1;
 }
 
 int num_sms() {

@@ -38,6 +38,7 @@ __global__ void __launch_bounds__(256) conv_gather_kernel(DView in, const void* 
                                                           const float* __restrict__ bias, DView out, int mode, int KH,
                                                           int KW, int stride, int pad, int act, int accumulate,
                                                           int sub, int py, int px) {
+  GSB_PDL_ENTRY();
   static_assert((BM / TM) * (BN / TN) == 256, "tile/thread mismatch");
   constexpr int AR = BM / 16;                    // A rows loaded per thread
   constexpr int BR = (BN + 15) / 16;             // B rows loaded per thread
@@ -156,6 +157,7 @@ __global__ void __launch_bounds__(256) conv_gather_kernel(DView in, const void* 
 template <int BM, int BN, int TM, int TN>
 __global__ void __launch_bounds__(256) conv_wgrad_kernel(DView in, DView dout, float* __restrict__ dwp, int mode, int KH,
                                                          int KW, int stride, int pad, int64_t chunk, int tiles_n) {
+  GSB_PDL_ENTRY();
   static_assert((BM / TM) * (BN / TN) == 256, "tile/thread mismatch");
   __shared__ float As[BK][BM + 4];  // dout  [k][co]
   __shared__ float Bs[BK][BN + 4];  // in    [k][ci]
@@ -250,6 +252,7 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(DView in, DView dout, f
 }
 
 __global__ void bias_grad_kernel(DView d, float* __restrict__ db) {
+  GSB_PDL_ENTRY();
   const int c = blockIdx.x;
   const int64_t P = (int64_t)d.N * d.H * d.W;
   double acc = 0.0;   // bias gradients are cancellation-heavy sums: accumulate in fp64
@@ -290,11 +293,11 @@ int conv_gather_direct(const gsb_view* in, const void* wp, int wdtype, const flo
       if (M <= 0) continue;
       if (out->c <= 8) {
         dim3 grid((unsigned)((M + 127) / 128), (unsigned)((out->c + 7) / 8));
-        conv_gather_kernel<128, 8, 4, 1><<<grid, 256, 0, st>>>(vi, wp, wdtype, bias, vo, g->mode, g->kh, g->kw, g->stride,
+        gsb::launch(conv_gather_kernel<128, 8, 4, 1>, gsb::LaunchCfg(grid, 256, 0, st), vi, wp, wdtype, bias, vo, g->mode, g->kh, g->kw, g->stride,
                                                                g->pad, act, accumulate, sub, py, px);
       } else {
         dim3 grid((unsigned)((M + 63) / 64), (unsigned)((out->c + 63) / 64));
-        conv_gather_kernel<64, 64, 4, 4><<<grid, 256, 0, st>>>(vi, wp, wdtype, bias, vo, g->mode, g->kh, g->kw, g->stride,
+        gsb::launch(conv_gather_kernel<64, 64, 4, 4>, gsb::LaunchCfg(grid, 256, 0, st), vi, wp, wdtype, bias, vo, g->mode, g->kh, g->kw, g->stride,
                                                                g->pad, act, accumulate, sub, py, px);
       }
     }
@@ -320,7 +323,7 @@ int conv_wgrad_direct(const gsb_view* in, const gsb_view* dout, float* dwp, cons
     int64_t chunk = ((P + split - 1) / split + BK - 1) / BK * BK;
     split = (P + chunk - 1) / chunk;
     dim3 grid((unsigned)(tiles_m * tiles_n), (unsigned)taps, (unsigned)split);
-    kernel<<<grid, 256, 0, st>>>(vi, vd, dwp, g->mode, g->kh, g->kw, g->stride, g->pad, chunk, tiles_n);
+    gsb::launch(kernel, gsb::LaunchCfg(grid, 256, 0, st), vi, vd, dwp, g->mode, g->kh, g->kw, g->stride, g->pad, chunk, tiles_n);
   };
   if (dout->c <= 8)
     launch(conv_wgrad_kernel<8, 128, 1, 4>, 8, 128);
@@ -342,6 +345,6 @@ extern "C" int gsb_bias_grad(const gsb_view* dout, float* db, gsb_stream s) {
   if (by < 1) by = 1;
   if (by > 64) by = 64;
   dim3 grid((unsigned)dout->c, (unsigned)by);
-  bias_grad_kernel<<<grid, 256, 0, to_stream(s)>>>(dv(dout), db);
+  gsb::launch(bias_grad_kernel, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), dv(dout), db);
   return check_launch("bias_grad");
 }

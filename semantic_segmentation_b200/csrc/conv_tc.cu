@@ -59,6 +59,7 @@ struct FpropCfg {
 template <int BN>
 __global__ void __launch_bounds__(192, 1)
 conv_tc_fprop_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcTaps taps, const TcParams p) {
+  GSB_PDL_ENTRY();
   using Cfg = FpropCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -261,6 +262,7 @@ conv_tc_fprop_kernel(const __grid_constant__ TcMaps maps, const __grid_constant_
 __global__ void __launch_bounds__(256) splitk_finalize_kernel(const float* __restrict__ ws, int64_t pixels, int W, int H, int cout,
                                                              const float* __restrict__ bias, int act, __nv_bfloat16* __restrict__ out,
                                                              int64_t sw, int64_t sh, int64_t sn) {
+  GSB_PDL_ENTRY();
   const int G = cout >> 3;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < pixels * G; i += (int64_t)gridDim.x * blockDim.x) {
     const int g = (int)(i % G);
@@ -320,6 +322,7 @@ struct WgradCfg {
 template <int BN>
 __global__ void __launch_bounds__(192, 1)
 conv_tc_wgrad_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ TcTaps taps, const WgParams p) {
+  GSB_PDL_ENTRY();
   using Cfg = WgradCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -484,7 +487,7 @@ static int launch_tc(Kern kern, int grid_x, int grid_y, int smem, const TcMaps& 
                      cudaStream_t st) {
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   GSB_REQUIRE(e == cudaSuccess, "cudaFuncSetAttribute(smem=%d) failed: %s", smem, cudaGetErrorString(e));
-  kern<<<dim3(grid_x, grid_y), 192, smem, st>>>(maps, taps, prm);
+  gsb::launch(kern, gsb::LaunchCfg(dim3(grid_x, grid_y), 192, smem, st), maps, taps, prm);
   return check_launch("conv_tc launch");
 }
 
@@ -548,7 +551,7 @@ static int fprop_launch(const SubView& outv, const SubView* shifted, int nmaps, 
   int64_t items = pixels * (cout / 8);
   int fgrid = (int)((items + 255) / 256);
   if (fgrid > num_sms() * 8) fgrid = num_sms() * 8;
-  splitk_finalize_kernel<<<fgrid, 256, 0, st>>>(p.ws, pixels, (int)outv.W, (int)outv.H, cout, bias, act,
+  gsb::launch(splitk_finalize_kernel, gsb::LaunchCfg(fgrid, 256, 0, st), p.ws, pixels, (int)outv.W, (int)outv.H, cout, bias, act,
                                                 (__nv_bfloat16*)const_cast<void*>(outv.ptr), outv.sw, outv.sh, outv.sn);
   return check_launch("conv_tc split-K finalize");
 }

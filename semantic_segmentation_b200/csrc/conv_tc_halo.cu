@@ -93,6 +93,7 @@ __device__ __forceinline__ void cluster_sync_all() {
 template <int BN, int CL>
 __global__ void __launch_bounds__(320, 1)
 conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ HaloPlan plan, const HaloParams p) {
+  GSB_PDL_ENTRY();
   constexpr int B_BYTES = BN * 128;
   constexpr int OUT_COLS = BN > 128 ? 128 : BN;
   constexpr int OUT_BYTES = 128 * OUT_COLS * 2;
@@ -408,6 +409,7 @@ struct WgHaloParams {
 template <int BN>
 __global__ void __launch_bounds__(192, 1)
 conv_tc_wgrad_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ HaloPlan plan, const WgHaloParams p) {
+  GSB_PDL_ENTRY();
   constexpr int B_BYTES = (BN / 64) * 16384;
   constexpr int TMEM_COLS = BN == 128 ? 512 : 256;
   extern __shared__ uint8_t smem_raw[];
@@ -723,13 +725,15 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
   cfg.blockDim = dim3(320);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CL;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // PDL, see common.cuh
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
   e = cudaLaunchKernelEx(&cfg, kern, maps, plan, p);
   GSB_REQUIRE(e == cudaSuccess, "conv_tc_halo launch failed: %s", cudaGetErrorString(e));
   if (check_launch("conv_tc_halo launch")) return -1;
@@ -792,11 +796,11 @@ int conv_halo_wgrad(const SubView& tiled, const SubView* shifted, int nmaps, con
   if (BN == 128) {
     e = cudaFuncSetAttribute(conv_tc_wgrad_halo_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     GSB_REQUIRE(e == cudaSuccess, "cudaFuncSetAttribute(smem=%d) failed: %s", smem, cudaGetErrorString(e));
-    conv_tc_wgrad_halo_kernel<128><<<dim3(base, split), 192, smem, st>>>(maps, plan, p);
+    gsb::launch(conv_tc_wgrad_halo_kernel<128>, gsb::LaunchCfg(dim3(base, split), 192, smem, st), maps, plan, p);
   } else {
     e = cudaFuncSetAttribute(conv_tc_wgrad_halo_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     GSB_REQUIRE(e == cudaSuccess, "cudaFuncSetAttribute(smem=%d) failed: %s", smem, cudaGetErrorString(e));
-    conv_tc_wgrad_halo_kernel<64><<<dim3(base, split), 192, smem, st>>>(maps, plan, p);
+    gsb::launch(conv_tc_wgrad_halo_kernel<64>, gsb::LaunchCfg(dim3(base, split), 192, smem, st), maps, plan, p);
   }
   if (check_launch("conv_tc_wgrad_halo launch")) return -1;
   return 1;

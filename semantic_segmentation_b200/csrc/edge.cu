@@ -21,6 +21,7 @@ __global__ void __launch_bounds__(256) stem_fwd_kernel(const float* __restrict__
                                                       const float* __restrict__ w /*[Cout][Cin][k][k]*/,
                                                       const float* __restrict__ bias, T* __restrict__ y, int64_t yld, int OH,
                                                       int OW, int Cout, int k, int stride, int pad, int act) {
+  GSB_PDL_ENTRY();
   extern __shared__ float sw[];  // [taps][Cout]
   const int taps = Cin * k * k;
   for (int i = threadIdx.x; i < taps * Cout; i += blockDim.x) {
@@ -69,6 +70,7 @@ template <typename T, int TP>
 __global__ void __launch_bounds__(256) stem_wgrad_kernel(const float* __restrict__ x, int N, int Cin, int H, int W,
                                                         const T* __restrict__ dy, int64_t dld, int OH, int OW, int Cout,
                                                         int k, int stride, int pad, int tap0, float* __restrict__ dw) {
+  GSB_PDL_ENTRY();
   extern __shared__ float sacc[];  // [G][TP][8]
   __shared__ int s_ci[TP], s_ky[TP], s_kx[TP];
   const int taps = Cin * k * k;
@@ -140,6 +142,7 @@ __global__ void __launch_bounds__(256, 2) stem_fwd_fast_kernel(const float* __re
                                                            const float* __restrict__ w, const float* __restrict__ bias,
                                                            T* __restrict__ y, int64_t yld, int OH, int OW, int Cout, int pad,
                                                            int act, float* __restrict__ stats) {
+  GSB_PDL_ENTRY();
   extern __shared__ float sw[];  // [taps][Cout] | red[2][Cout]
   const int taps = Cin * K * K;
   float* red = sw + taps * Cout;
@@ -247,6 +250,7 @@ template <typename T, int PX, int K, int S>
 __global__ void __launch_bounds__(256, 2) stem_wgrad_fast_kernel(const float* __restrict__ x, int N, int Cin, int H, int W,
                                                              const T* __restrict__ dy, int64_t dld, int OH, int OW, int Cout,
                                                              int pad, float* __restrict__ dw) {
+  GSB_PDL_ENTRY();
   extern __shared__ float sacc[];  // [G][K*K][8]
   constexpr int SPAN = (PX - 1) * S + K;
   const int ci = blockIdx.y;
@@ -333,6 +337,7 @@ template <typename T, int CT>
 __global__ void __launch_bounds__(256, 4) head_fwd_kernel(const T* __restrict__ x, int64_t xld, unsigned P, unsigned HW, int K, int C,
                                                       const float* __restrict__ w /*[C][K]*/, const float* __restrict__ bias,
                                                       float* __restrict__ out /*[N][C][HW]*/) {
+  GSB_PDL_ENTRY();
   extern __shared__ float sw[];  // [C][K]
   for (int i = threadIdx.x; i < C * K; i += blockDim.x) sw[i] = w[i];
   __syncthreads();
@@ -403,6 +408,7 @@ __global__ void __launch_bounds__(256, 4) head_bwd_kernel(const T* __restrict__ 
                                                       const float* __restrict__ w, const float* __restrict__ dout,
                                                       T* __restrict__ dx, int64_t dxld, float* __restrict__ dw,
                                                       float* __restrict__ db) {
+  GSB_PDL_ENTRY();
   extern __shared__ float sm[];  // sw[C][K] | sdw[C][K] | sdb[C]
   float* sw = sm;
   float* sdw = sm + C * K;
@@ -521,13 +527,13 @@ extern "C" int gsb_stem_conv_fwd(const float* x, int n, int cin, int h, int w, c
     int grid = grid_cap((items + 255) / 256, 8);
     size_t smem = ((size_t)cin * k * k * cout + 2 * cout) * sizeof(float);
     if (k3 && act == GSB_ACT_NONE) {
-      EDGE_DISPATCH_T(y->dtype, stem_fwd_fast_kernel<T, PX, 3, 1, true><<<grid, 256, smem, to_stream(s)>>>(
+      EDGE_DISPATCH_T(y->dtype, gsb::launch(stem_fwd_fast_kernel<T, PX, 3, 1, true>, gsb::LaunchCfg(grid, 256, smem, to_stream(s)), 
                                     x, n, cin, h, w, weight, bias, (T*)y->ptr, y->sw, y->h, y->w, cout, pad, act, stats_partial));
     } else if (k3) {
-      EDGE_DISPATCH_T(y->dtype, stem_fwd_fast_kernel<T, PX, 3, 1, false><<<grid, 256, smem, to_stream(s)>>>(
+      EDGE_DISPATCH_T(y->dtype, gsb::launch(stem_fwd_fast_kernel<T, PX, 3, 1, false>, gsb::LaunchCfg(grid, 256, smem, to_stream(s)), 
                                     x, n, cin, h, w, weight, bias, (T*)y->ptr, y->sw, y->h, y->w, cout, pad, act, stats_partial));
     } else {
-      EDGE_DISPATCH_T(y->dtype, stem_fwd_fast_kernel<T, PX, 4, 2, false><<<grid, 256, smem, to_stream(s)>>>(
+      EDGE_DISPATCH_T(y->dtype, gsb::launch(stem_fwd_fast_kernel<T, PX, 4, 2, false>, gsb::LaunchCfg(grid, 256, smem, to_stream(s)), 
                                     x, n, cin, h, w, weight, bias, (T*)y->ptr, y->sw, y->h, y->w, cout, pad, act, stats_partial));
     }
     if (stats_partial && stats_rows) *stats_rows = grid;
@@ -535,7 +541,7 @@ extern "C" int gsb_stem_conv_fwd(const float* x, int n, int cin, int h, int w, c
   }
   size_t smem = (size_t)cin * k * k * cout * sizeof(float);
   int grid = grid_cap((total + 255) / 256, 16);
-  EDGE_DISPATCH_T(y->dtype, stem_fwd_kernel<T><<<grid, 256, smem, to_stream(s)>>>(x, n, cin, h, w, weight, bias, (T*)y->ptr, y->sw,
+  EDGE_DISPATCH_T(y->dtype, gsb::launch(stem_fwd_kernel<T>, gsb::LaunchCfg(grid, 256, smem, to_stream(s)), x, n, cin, h, w, weight, bias, (T*)y->ptr, y->sw,
                                                                                    y->h, y->w, cout, k, stride, pad, act));
   return check_launch("stem_conv_fwd");
 }
@@ -553,7 +559,7 @@ extern "C" int gsb_stem_conv_wgrad(const float* x, int n, int cin, int h, int w,
     const int64_t items = (int64_t)dy->n * dy->h * ((dy->w + PX - 1) / PX);
     int gx = grid_cap((items + lanes - 1) / lanes, 4);
     size_t smem = (size_t)G * 9 * 8 * sizeof(float);
-    EDGE_DISPATCH_T(dy->dtype, stem_wgrad_fast_kernel<T, PX, 3, 1><<<dim3(gx, cin), 256, smem, to_stream(s)>>>(
+    EDGE_DISPATCH_T(dy->dtype, gsb::launch(stem_wgrad_fast_kernel<T, PX, 3, 1>, gsb::LaunchCfg(dim3(gx, cin), 256, smem, to_stream(s)), 
                                    x, n, cin, h, w, (const T*)dy->ptr, dy->sw, dy->h, dy->w, cout, pad, dweight));
     return check_launch("stem_conv_wgrad");
   }
@@ -561,7 +567,7 @@ extern "C" int gsb_stem_conv_wgrad(const float* x, int n, int cin, int h, int w,
   size_t smem = (size_t)G * TP * 8 * sizeof(float);
   int launches = 0;
   for (int tap0 = 0; tap0 < taps; tap0 += TP, ++launches) {
-    EDGE_DISPATCH_T(dy->dtype, stem_wgrad_kernel<T, TP><<<grid, 256, smem, to_stream(s)>>>(
+    EDGE_DISPATCH_T(dy->dtype, gsb::launch(stem_wgrad_kernel<T, TP>, gsb::LaunchCfg(grid, 256, smem, to_stream(s)), 
                                    x, n, cin, h, w, (const T*)dy->ptr, dy->sw, dy->h, dy->w, cout, k, stride, pad, tap0, dweight));
   }
   return check_launch("stem_conv_wgrad", launches);
@@ -582,10 +588,10 @@ extern "C" int gsb_head_conv_fwd(const gsb_view* x, const float* weight, const f
   size_t smem = (size_t)c * x->c * sizeof(float);
   GSB_REQUIRE(P < ((int64_t)1 << 28), "head_conv_fwd: too many pixels");
   if (c <= 2) {
-    EDGE_DISPATCH_T(x->dtype, head_fwd_kernel<T, 2><<<grid, 256, smem, to_stream(s)>>>((const T*)x->ptr, x->sw, (unsigned)P, (unsigned)HW,
+    EDGE_DISPATCH_T(x->dtype, gsb::launch(head_fwd_kernel<T, 2>, gsb::LaunchCfg(grid, 256, smem, to_stream(s)), (const T*)x->ptr, x->sw, (unsigned)P, (unsigned)HW,
                                                                                         x->c, c, weight, bias, logits));
   } else {
-    EDGE_DISPATCH_T(x->dtype, head_fwd_kernel<T, 8><<<grid, 256, smem, to_stream(s)>>>((const T*)x->ptr, x->sw, (unsigned)P, (unsigned)HW,
+    EDGE_DISPATCH_T(x->dtype, gsb::launch(head_fwd_kernel<T, 8>, gsb::LaunchCfg(grid, 256, smem, to_stream(s)), (const T*)x->ptr, x->sw, (unsigned)P, (unsigned)HW,
                                                                                         x->c, c, weight, bias, logits));
   }
   return check_launch("head_conv_fwd");
@@ -605,11 +611,11 @@ extern "C" int gsb_head_conv_bwd(const gsb_view* x, const float* weight, int c, 
   size_t smem = (size_t)(2 * c * K + c) * sizeof(float);
   GSB_REQUIRE(P < ((int64_t)1 << 31), "head_conv_bwd: too many pixels");
   if (c <= 2) {
-    EDGE_DISPATCH_T(x->dtype, head_bwd_kernel<T, 2><<<grid, 256, smem, to_stream(s)>>>(
+    EDGE_DISPATCH_T(x->dtype, gsb::launch(head_bwd_kernel<T, 2>, gsb::LaunchCfg(grid, 256, smem, to_stream(s)), 
                                   (const T*)x->ptr, x->sw, (unsigned)P, (unsigned)HW, K, c, weight, dlogits,
                                   (dx && dx->ptr) ? (T*)dx->ptr : nullptr, dx ? dx->sw : 0, dweight, dbias));
   } else {
-    EDGE_DISPATCH_T(x->dtype, head_bwd_kernel<T, 8><<<grid, 256, smem, to_stream(s)>>>(
+    EDGE_DISPATCH_T(x->dtype, gsb::launch(head_bwd_kernel<T, 8>, gsb::LaunchCfg(grid, 256, smem, to_stream(s)), 
                                   (const T*)x->ptr, x->sw, (unsigned)P, (unsigned)HW, K, c, weight, dlogits,
                                   (dx && dx->ptr) ? (T*)dx->ptr : nullptr, dx ? dx->sw : 0, dweight, dbias));
   }

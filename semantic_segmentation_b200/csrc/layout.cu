@@ -17,6 +17,7 @@ struct CView {
 static CView cv(const gsb_view* v) { return CView{v->ptr, v->dtype, v->n, v->h, v->w, v->c, v->sn, v->sh, v->sw, v->sc}; }
 
 __global__ void copy_view_kernel(CView src, CView dst, int c_fastest) {
+  GSB_PDL_ENTRY();
   const int64_t total = (int64_t)dst.N * dst.H * dst.W * dst.C;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     int n, y, x, c;
@@ -37,6 +38,7 @@ __global__ void copy_view_kernel(CView src, CView dst, int c_fastest) {
 
 __global__ void pack_weight_kernel(const float* __restrict__ src, int d0, int d1, int taps, int rows_from_d0, void* dst,
                                    int dst_dtype) {
+  GSB_PDL_ENTRY();
   const int rows = rows_from_d0 ? d0 : d1, cols = rows_from_d0 ? d1 : d0;
   const int64_t total = (int64_t)taps * rows * cols;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -51,6 +53,7 @@ __global__ void pack_weight_kernel(const float* __restrict__ src, int d0, int d1
 
 __global__ void unpack_wgrad_kernel(const float* __restrict__ src, int d0, int d1, int taps, int rows_from_d0,
                                     float* __restrict__ dst, int accumulate) {
+  GSB_PDL_ENTRY();
   const int rows = rows_from_d0 ? d0 : d1, cols = rows_from_d0 ? d1 : d0;
   const int64_t total = (int64_t)taps * d0 * d1;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -74,6 +77,7 @@ __device__ __forceinline__ void softmax3(const float* alpha, float (&w)[3]) {
 __global__ void merge_upconv_kernel(const float* __restrict__ w4, const float* __restrict__ w6, const float* __restrict__ w8,
                                     const float* b4, const float* b6, const float* b8, const float* __restrict__ alpha,
                                     int64_t pairs, int cout, float* __restrict__ wm, float* bm) {
+  GSB_PDL_ENTRY();
   float w[3];
   softmax3(alpha, w);
   const int64_t rows_total = pairs * 8;   // one thread = one kernel row (8 taps) of one (ci, co) pair
@@ -105,6 +109,7 @@ __global__ void unmerge_upconv_kernel(const float* __restrict__ dwm, const float
                                       const float* b6, const float* b8, const float* __restrict__ alpha, int64_t pairs,
                                       int cout, float* __restrict__ dw4, float* __restrict__ dw6, float* __restrict__ dw8,
                                       float* db4, float* db6, float* db8, double* dots) {
+  GSB_PDL_ENTRY();
   float w[3];
   softmax3(alpha, w);
   // one thread = one kernel row (8 taps) of one (ci, co) pair: 2 x 16-byte loads per stream instead of one element per
@@ -154,6 +159,7 @@ __global__ void unmerge_upconv_kernel(const float* __restrict__ dwm, const float
 }
 
 __global__ void dalpha_kernel(const double* __restrict__ dots, const float* __restrict__ alpha, float* dalpha) {
+  GSB_PDL_ENTRY();
   float w[3];
   softmax3(alpha, w);
   double mean = w[0] * dots[0] + w[1] * dots[1] + w[2] * dots[2];
@@ -175,7 +181,7 @@ extern "C" int gsb_copy_view(const gsb_view* src, const gsb_view* dst, gsb_strea
   GSB_REQUIRE(src->n == dst->n && src->h == dst->h && src->w == dst->w && src->c == dst->c, "copy_view: shape mismatch");
   int64_t total = (int64_t)dst->n * dst->h * dst->w * dst->c;
   if (total == 0) return 0;
-  copy_view_kernel<<<ew_grid(total), 256, 0, to_stream(s)>>>(cv(src), cv(dst), dst->sc == 1 ? 1 : 0);
+  gsb::launch(copy_view_kernel, gsb::LaunchCfg(ew_grid(total), 256, 0, to_stream(s)), cv(src), cv(dst), dst->sc == 1 ? 1 : 0);
   return check_launch("copy_view");
 }
 
@@ -203,7 +209,7 @@ extern "C" int gsb_merge_upconv(const float* w4, const float* w6, const float* w
   GSB_REQUIRE(w4 && w6 && w8 && alpha && w_merged, "merge_upconv: null pointer");
   GSB_REQUIRE(b_merged == nullptr || (b4 && b6 && b8), "merge_upconv: biases missing");
   int64_t pairs = (int64_t)cin * cout;
-  merge_upconv_kernel<<<ew_grid(pairs * 8), 256, 0, to_stream(s)>>>(w4, w6, w8, b4, b6, b8, alpha, pairs, cout, w_merged,
+  gsb::launch(merge_upconv_kernel, gsb::LaunchCfg(ew_grid(pairs * 8), 256, 0, to_stream(s)), w4, w6, w8, b4, b6, b8, alpha, pairs, cout, w_merged,
                                                                     b_merged);
   return check_launch("merge_upconv");
 }
@@ -218,9 +224,9 @@ extern "C" int gsb_unmerge_upconv(const float* dw_merged, const float* db_merged
   double* dots = reinterpret_cast<double*>(workspace);
   cudaMemsetAsync(dots, 0, 3 * sizeof(double), to_stream(s));
   int64_t pairs = (int64_t)cin * cout;
-  unmerge_upconv_kernel<<<ew_grid(pairs * 8), 256, 0, to_stream(s)>>>(dw_merged, db_merged, w4, w6, w8, b4, b6, b8, alpha,
+  gsb::launch(unmerge_upconv_kernel, gsb::LaunchCfg(ew_grid(pairs * 8), 256, 0, to_stream(s)), dw_merged, db_merged, w4, w6, w8, b4, b6, b8, alpha,
                                                                       pairs, cout, dw4, dw6, dw8, db4, db6, db8, dots);
-  dalpha_kernel<<<1, 1, 0, to_stream(s)>>>(dots, alpha, dalpha);
+  gsb::launch(dalpha_kernel, gsb::LaunchCfg(1, 1, 0, to_stream(s)), dots, alpha, dalpha);
   return check_launch("unmerge_upconv", 2);
 }
 
@@ -331,12 +337,14 @@ __device__ __forceinline__ void layout_tile_dispatch(const LayoutJobs& J, int j,
 }
 
 __global__ void __launch_bounds__(256) pack_weight_multi_kernel(const __grid_constant__ LayoutJobs J) {
+  GSB_PDL_ENTRY();
   __shared__ float sm[kTI0 * kTPitch0];
   const int j = find_job(J.blk0, J.count, blockIdx.x);
   layout_tile_dispatch<true>(J, j, blockIdx.x - J.blk0[j], sm);
 }
 
 __global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const __grid_constant__ LayoutJobs J) {
+  GSB_PDL_ENTRY();
   __shared__ float sm[kTI0 * kTPitch0];
   const int j = find_job(J.blk0, J.count, blockIdx.x);
   layout_tile_dispatch<false>(J, j, blockIdx.x - J.blk0[j], sm);
@@ -363,8 +371,8 @@ static int run_layout_multi(bool pack, int n, const void* const* src, void* cons
     }
     J.blk0[J.count] = blocks;
     if (blocks == 0) continue;
-    if (pack) pack_weight_multi_kernel<<<blocks, 256, 0, st>>>(J);
-    else unpack_wgrad_multi_kernel<<<blocks, 256, 0, st>>>(J);
+    if (pack) gsb::launch(pack_weight_multi_kernel, gsb::LaunchCfg(blocks, 256, 0, st), J);
+    else gsb::launch(unpack_wgrad_multi_kernel, gsb::LaunchCfg(blocks, 256, 0, st), J);
     ++launches;
   }
   return check_launch(pack ? "pack_weight_multi" : "unpack_wgrad_multi", launches > 0 ? launches : 1);

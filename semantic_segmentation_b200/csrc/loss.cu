@@ -29,6 +29,7 @@ __device__ __forceinline__ double block_sum_d(double v, double* sh) {
 __global__ void __launch_bounds__(256) seg_loss_reduce_kernel(const float* __restrict__ logits,
                                                              const int64_t* __restrict__ labels, int64_t P, int64_t HW,
                                                              int C, double* __restrict__ partial) {
+  GSB_PDL_ENTRY();
   __shared__ double sh[8];
   float ce = 0.f, inter = 0.f, sp = 0.f, st = 0.f;
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P; p += (int64_t)gridDim.x * blockDim.x) {
@@ -76,6 +77,7 @@ __global__ void __launch_bounds__(256) seg_loss_reduce_kernel(const float* __res
 }
 
 __global__ void sum_rows4_kernel(const double* __restrict__ partial, int rows, double* __restrict__ sums) {
+  GSB_PDL_ENTRY();
   __shared__ double sh[8];
   for (int j = 0; j < 4; ++j) {
     double a = 0.0;
@@ -100,6 +102,7 @@ __device__ __forceinline__ void dice_terms(const double* sums, double& dice, dou
 }
 
 __global__ void seg_loss_finalize_kernel(const double* __restrict__ sums, double count, float* out) {
+  GSB_PDL_ENTRY();
   double dice, a, b;
   dice_terms(sums, dice, a, b);
   double ce = sums[0] / count;
@@ -112,6 +115,7 @@ __global__ void __launch_bounds__(256) seg_loss_bwd_kernel(const float* __restri
                                                           int64_t P, int64_t HW, int C, const double* __restrict__ sums,
                                                           double count, const float* __restrict__ gscale,
                                                           float* __restrict__ dlogits) {
+  GSB_PDL_ENTRY();
   double dice, ad, bd;
   dice_terms(sums, dice, ad, bd);
   const float gs = gscale ? *gscale : 1.f;
@@ -155,6 +159,7 @@ __global__ void __launch_bounds__(256) seg_loss_bwd_kernel(const float* __restri
 __global__ void __launch_bounds__(256) eval_counts_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels,
                                                          int64_t HW, int C, uint8_t* __restrict__ mask,
                                                          unsigned long long* __restrict__ counts) {
+  GSB_PDL_ENTRY();
   __shared__ unsigned int sc[kMaxC * 3];
   const int K = C > 1 ? C - 1 : 1;
   for (int i = threadIdx.x; i < K * 3; i += blockDim.x) sc[i] = 0;
@@ -200,6 +205,7 @@ __global__ void __launch_bounds__(256) eval_counts_kernel(const float* __restric
 
 __global__ void __launch_bounds__(256) dice_sums_kernel(const float* __restrict__ a, const float* __restrict__ b, int64_t inner,
                                                        double* __restrict__ sums) {
+  GSB_PDL_ENTRY();
   __shared__ double sh[8];
   const int64_t s = blockIdx.y;
   const float* pa = a + s * inner;
@@ -222,6 +228,7 @@ __global__ void __launch_bounds__(256) dice_sums_kernel(const float* __restrict_
 // mode 0 vanilla (BCE with logits), 1 lsgan (MSE), 2 wgangp.  acc (double) += sum of per-element loss.
 __global__ void __launch_bounds__(256) gan_loss_kernel(const float* __restrict__ pred, int64_t n, int mode, float label,
                                                       double* acc, const float* __restrict__ gscale, float* __restrict__ dpred) {
+  GSB_PDL_ENTRY();
   __shared__ double sh[8];
   float l = 0.f;
   const float gs = (gscale ? *gscale : 1.f) / (float)n;
@@ -249,6 +256,7 @@ __global__ void __launch_bounds__(256) gan_loss_kernel(const float* __restrict__
 
 __global__ void __launch_bounds__(256) l1_loss_kernel(const float* __restrict__ a, const float* __restrict__ b, int64_t n,
                                                      double* acc, const float* __restrict__ gscale, float* __restrict__ da) {
+  GSB_PDL_ENTRY();
   __shared__ double sh[8];
   float l = 0.f;
   const float gs = (gscale ? *gscale : 1.f) / (float)n;
@@ -265,6 +273,7 @@ __global__ void __launch_bounds__(256) l1_loss_kernel(const float* __restrict__ 
 
 __global__ void __launch_bounds__(256) act_bwd_kernel(const float* __restrict__ out, const float* __restrict__ dout, int act,
                                                      float* __restrict__ dx, int64_t n) {
+  GSB_PDL_ENTRY();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     float o = out[i], g = dout[i], d;
     switch (act) {
@@ -277,7 +286,8 @@ __global__ void __launch_bounds__(256) act_bwd_kernel(const float* __restrict__ 
   }
 }
 
-__global__ void mean_out_kernel(const double* acc, double n, float* out) { out[0] = (float)(acc[0] / n); }
+__global__ void mean_out_kernel(const double* acc, double n, float* out) {
+  GSB_PDL_ENTRY(); out[0] = (float)(acc[0] / n); }
 
 static int grid1d(int64_t total, int per_sm = 8) {
   int64_t b = (total + 255) / 256;
@@ -302,14 +312,14 @@ extern "C" int gsb_seg_loss_reduce(const float* logits, const int64_t* labels, i
   int grid = grid1d(P);
   GSB_REQUIRE(workspace_bytes >= (size_t)grid * 4 * sizeof(double), "seg_loss_reduce: workspace too small");
   double* partial = reinterpret_cast<double*>(workspace);
-  seg_loss_reduce_kernel<<<grid, 256, 0, to_stream(s)>>>(logits, labels, P, HW, c, partial);
-  sum_rows4_kernel<<<1, 256, 0, to_stream(s)>>>(partial, grid, sums);
+  gsb::launch(seg_loss_reduce_kernel, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), logits, labels, P, HW, c, partial);
+  gsb::launch(sum_rows4_kernel, gsb::LaunchCfg(1, 256, 0, to_stream(s)), partial, grid, sums);
   return check_launch("seg_loss_reduce", 2);
 }
 
 extern "C" int gsb_seg_loss_finalize(const double* sums, double count, float* out, gsb_stream s) {
   GSB_REQUIRE(sums && out && count > 0, "seg_loss_finalize: bad argument");
-  seg_loss_finalize_kernel<<<1, 1, 0, to_stream(s)>>>(sums, count, out);
+  gsb::launch(seg_loss_finalize_kernel, gsb::LaunchCfg(1, 1, 0, to_stream(s)), sums, count, out);
   return check_launch("seg_loss_finalize");
 }
 
@@ -318,7 +328,7 @@ extern "C" int gsb_seg_loss_bwd(const float* logits, const int64_t* labels, int 
   GSB_REQUIRE(logits && labels && sums && dlogits && count > 0, "seg_loss_bwd: bad argument");
   GSB_REQUIRE(c >= 1 && c <= kMaxC, "seg_loss: n_classes %d unsupported (max %d)", c, kMaxC);
   int64_t HW = (int64_t)h * w, P = (int64_t)n * HW;
-  seg_loss_bwd_kernel<<<grid1d(P, 16), 256, 0, to_stream(s)>>>(logits, labels, P, HW, c, sums, count, gscale, dlogits);
+  gsb::launch(seg_loss_bwd_kernel, gsb::LaunchCfg(grid1d(P, 16), 256, 0, to_stream(s)), logits, labels, P, HW, c, sums, count, gscale, dlogits);
   return check_launch("seg_loss_bwd");
 }
 
@@ -332,7 +342,7 @@ extern "C" int gsb_eval_counts(const float* logits, const int64_t* labels, int n
   int gx = (int)((HW + 256 * 8 - 1) / (256 * 8));
   if (gx < 1) gx = 1;
   dim3 grid((unsigned)gx, (unsigned)n);
-  eval_counts_kernel<<<grid, 256, 0, to_stream(s)>>>(logits, labels, HW, c, mask, reinterpret_cast<unsigned long long*>(counts));
+  gsb::launch(eval_counts_kernel, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), logits, labels, HW, c, mask, reinterpret_cast<unsigned long long*>(counts));
   return check_launch("eval_counts");
 }
 
@@ -343,7 +353,7 @@ extern "C" int gsb_dice_sums(const float* a, const float* b, int64_t slices, int
   if (gx < 1) gx = 1;
   if (gx > 1024) gx = 1024;
   dim3 grid((unsigned)gx, (unsigned)slices);
-  dice_sums_kernel<<<grid, 256, 0, to_stream(s)>>>(a, b, inner, sums);
+  gsb::launch(dice_sums_kernel, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), a, b, inner, sums);
   return check_launch("dice_sums");
 }
 
@@ -353,8 +363,8 @@ extern "C" int gsb_gan_loss(const float* pred, int64_t numel, int mode, float la
   GSB_REQUIRE(loss == nullptr || workspace != nullptr, "gan_loss: workspace (8 bytes) required for the forward value");
   double* acc = loss ? reinterpret_cast<double*>(workspace) : nullptr;
   if (acc) cudaMemsetAsync(acc, 0, sizeof(double), to_stream(s));
-  gan_loss_kernel<<<grid1d(numel, 4), 256, 0, to_stream(s)>>>(pred, numel, mode, label, acc, gscale, dpred);
-  if (acc) mean_out_kernel<<<1, 1, 0, to_stream(s)>>>(acc, (double)numel, loss);
+  gsb::launch(gan_loss_kernel, gsb::LaunchCfg(grid1d(numel, 4), 256, 0, to_stream(s)), pred, numel, mode, label, acc, gscale, dpred);
+  if (acc) gsb::launch(mean_out_kernel, gsb::LaunchCfg(1, 1, 0, to_stream(s)), acc, (double)numel, loss);
   return check_launch("gan_loss", acc ? 2 : 1);
 }
 
@@ -364,14 +374,14 @@ extern "C" int gsb_l1_loss(const float* a, const float* b, int64_t numel, float*
   GSB_REQUIRE(loss == nullptr || workspace != nullptr, "l1_loss: workspace (8 bytes) required for the forward value");
   double* acc = loss ? reinterpret_cast<double*>(workspace) : nullptr;
   if (acc) cudaMemsetAsync(acc, 0, sizeof(double), to_stream(s));
-  l1_loss_kernel<<<grid1d(numel, 8), 256, 0, to_stream(s)>>>(a, b, numel, acc, gscale, da);
-  if (acc) mean_out_kernel<<<1, 1, 0, to_stream(s)>>>(acc, (double)numel, loss);
+  gsb::launch(l1_loss_kernel, gsb::LaunchCfg(grid1d(numel, 8), 256, 0, to_stream(s)), a, b, numel, acc, gscale, da);
+  if (acc) gsb::launch(mean_out_kernel, gsb::LaunchCfg(1, 1, 0, to_stream(s)), acc, (double)numel, loss);
   return check_launch("l1_loss", acc ? 2 : 1);
 }
 
 extern "C" int gsb_act_bwd(const float* out, const float* dout, int act, float* dx, int64_t numel, gsb_stream s) {
   GSB_REQUIRE(out && dout && dx, "act_bwd: null pointer");
   if (numel == 0) return 0;
-  act_bwd_kernel<<<grid1d(numel, 8), 256, 0, to_stream(s)>>>(out, dout, act, dx, numel);
+  gsb::launch(act_bwd_kernel, gsb::LaunchCfg(grid1d(numel, 8), 256, 0, to_stream(s)), out, dout, act, dx, numel);
   return check_launch("act_bwd");
 }

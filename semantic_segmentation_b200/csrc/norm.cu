@@ -74,6 +74,7 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
     PixView x, PixView dA1, PixView dA2, int64_t P, int C, const float* __restrict__ scale,
     const float* __restrict__ shift, const float* __restrict__ mean, const float* __restrict__ invstd, int act1,
     int act2, uint64_t drop_seed, const uint8_t* __restrict__ drop_mask, float* __restrict__ partial) {
+  GSB_PDL_ENTRY();
   constexpr int KU = MODE == 1 ? kUnrollBwd : kUnroll;
   extern __shared__ float red[];  // [lanes][2][C]
   const int G = C >> 3;
@@ -154,6 +155,7 @@ __global__ void __launch_bounds__(kThreads, 4) bn_bwd_reduce_relu_bf16_kernel(
     const __nv_bfloat16* __restrict__ x, int64_t xld, const __nv_bfloat16* __restrict__ dA, int64_t dld, int64_t P, int C,
     const float* __restrict__ scale, const float* __restrict__ shift, const float* __restrict__ mean,
     const float* __restrict__ invstd, float* __restrict__ partial) {
+  GSB_PDL_ENTRY();
   extern __shared__ float red[];  // [lanes][2][C]
   const int G = C >> 3;
   const int lanes = kThreads / G;
@@ -219,6 +221,7 @@ __global__ void __launch_bounds__(kThreads, 4) bn_bwd_reduce_relu_bf16_kernel(
 // four independent loads in flight per thread, fp64 accumulation, fixed summation order (deterministic).
 __global__ void __launch_bounds__(1024) reduce_partials_kernel(const float* __restrict__ partial, int rows, int n,
                                                               double* __restrict__ sums) {
+  GSB_PDL_ENTRY();
   __shared__ double red[32][33];
   const int c = threadIdx.x & 31, l = threadIdx.x >> 5;
   const int col = blockIdx.x * 32 + c;
@@ -246,6 +249,7 @@ __global__ void bn_finalize_kernel(const double* __restrict__ sums, double count
                                    const float* __restrict__ beta, float* running_mean, float* running_var,
                                    int64_t* nbt, float momentum, float eps, int C, float* scale, float* shift,
                                    float* mean_out, float* invstd_out) {
+  GSB_PDL_ENTRY();
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c == 0 && nbt != nullptr && sums != nullptr) *nbt += 1;
   if (c >= C) return;
@@ -278,6 +282,7 @@ __global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, 
                                                          const float* __restrict__ shift, int act1, PixView out1,
                                                          int act2, PixView out2, uint64_t drop_seed,
                                                          const uint8_t* __restrict__ drop_mask) {
+  GSB_PDL_ENTRY();
   const int G = C >> 3;
   const int lanes = kThreads / G;
   const int g = threadIdx.x % G, lane = threadIdx.x / G;
@@ -319,6 +324,7 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
     const float* __restrict__ shift, const float* __restrict__ mean, const float* __restrict__ invstd, int act1,
     int act2, uint64_t drop_seed, const uint8_t* __restrict__ drop_mask, const double* __restrict__ sums,
     double inv_count, PixView dx) {
+  GSB_PDL_ENTRY();
   const int G = C >> 3;
   const int lanes = kThreads / G;
   const int g = threadIdx.x % G, lane = threadIdx.x / G;
@@ -405,6 +411,7 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
 }
 
 __global__ void bn_param_grad_kernel(const double* __restrict__ sums, int C, float* dgamma, float* dbeta, int accumulate = 1) {
+  GSB_PDL_ENTRY();
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   if (dbeta) dbeta[c] = (accumulate ? dbeta[c] : 0.f) + (float)sums[c];
@@ -443,6 +450,7 @@ struct BnFusedBwd {
 template <int MODE>
 __global__ void __launch_bounds__(1024) bn_stats_fused_kernel(const float* __restrict__ partial, int rows, int C, PeerRegions regs,
                                                              int rank, int world, BnFusedFwd f, BnFusedBwd b) {
+  GSB_PDL_ENTRY();
   __shared__ double red[32][33];
   __shared__ double tot[32];
   const int c = threadIdx.x & 31, l = threadIdx.x >> 5;
@@ -558,19 +566,19 @@ extern "C" int gsb_bn_reduce(const gsb_view* x, double* sums, void* workspace, s
   float* partial = reinterpret_cast<float*>(workspace);
   PixView nul{nullptr, 0};
   if (x->dtype == GSB_BF16)
-    bn_reduce_kernel<__nv_bfloat16, 0, false><<<grid, kThreads, smem, to_stream(s)>>>(pv(x), nul, nul, P, C, nullptr, nullptr,
+    gsb::launch(bn_reduce_kernel<__nv_bfloat16, 0, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), nul, nul, P, C, nullptr, nullptr,
                                                                                      nullptr, nullptr, 0, 0, 0, nullptr, partial);
   else
-    bn_reduce_kernel<float, 0, false><<<grid, kThreads, smem, to_stream(s)>>>(pv(x), nul, nul, P, C, nullptr, nullptr, nullptr,
+    gsb::launch(bn_reduce_kernel<float, 0, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), nul, nul, P, C, nullptr, nullptr, nullptr,
                                                                              nullptr, 0, 0, 0, nullptr, partial);
   int n = 2 * C;
-  reduce_partials_kernel<<<(n + 31) / 32, 1024, 0, to_stream(s)>>>(partial, grid, n, sums);
+  gsb::launch(reduce_partials_kernel, gsb::LaunchCfg((n + 31) / 32, 1024, 0, to_stream(s)), partial, grid, n, sums);
   return check_launch("bn_reduce", 2);
 }
 
 extern "C" int gsb_bn_reduce_partials(const float* partial, int rows, int c, double* sums, gsb_stream s) {
   int n = 2 * c;
-  reduce_partials_kernel<<<(n + 31) / 32, 1024, 0, to_stream(s)>>>(partial, rows, n, sums);
+  gsb::launch(reduce_partials_kernel, gsb::LaunchCfg((n + 31) / 32, 1024, 0, to_stream(s)), partial, rows, n, sums);
   return check_launch("bn_reduce_partials");
 }
 
@@ -579,7 +587,7 @@ extern "C" int gsb_bn_finalize(const double* sums, double count, const float* ga
                                float eps, int c, float* scale, float* shift, float* mean, float* invstd, gsb_stream s) {
   GSB_REQUIRE(scale && shift, "bn_finalize: scale/shift required");
   GSB_REQUIRE(sums != nullptr || (running_mean && running_var), "bn_finalize: eval mode needs running stats");
-  bn_finalize_kernel<<<(c + 127) / 128, 128, 0, to_stream(s)>>>(sums, count, gamma, beta, running_mean, running_var,
+  gsb::launch(bn_finalize_kernel, gsb::LaunchCfg((c + 127) / 128, 128, 0, to_stream(s)), sums, count, gamma, beta, running_mean, running_var,
                                                                num_batches_tracked, momentum, eps, c, scale, shift,
                                                                mean, invstd);
   return check_launch("bn_finalize");
@@ -599,13 +607,13 @@ extern "C" int gsb_bn_act(const gsb_view* x, const float* scale, const float* sh
   const bool fast = act1 == GSB_ACT_RELU && o2.ptr == nullptr && drop_seed == 0 && drop_mask == nullptr && scale && shift;
   if (x->dtype == GSB_BF16) {
     if (fast)
-      bn_act_kernel<__nv_bfloat16, true><<<grid, kThreads, 0, to_stream(s)>>>(pv(x), P, C, scale, shift, act1, pv(out1), act2, o2,
+      gsb::launch(bn_act_kernel<__nv_bfloat16, true>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), P, C, scale, shift, act1, pv(out1), act2, o2,
                                                                               drop_seed, drop_mask);
     else
-      bn_act_kernel<__nv_bfloat16, false><<<grid, kThreads, 0, to_stream(s)>>>(pv(x), P, C, scale, shift, act1, pv(out1), act2,
+      gsb::launch(bn_act_kernel<__nv_bfloat16, false>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), P, C, scale, shift, act1, pv(out1), act2,
                                                                                o2, drop_seed, drop_mask);
   } else {
-    bn_act_kernel<float, false><<<grid, kThreads, 0, to_stream(s)>>>(pv(x), P, C, scale, shift, act1, pv(out1), act2, o2,
+    gsb::launch(bn_act_kernel<float, false>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), P, C, scale, shift, act1, pv(out1), act2, o2,
                                                                      drop_seed, drop_mask);
   }
   return check_launch("bn_act");
@@ -638,16 +646,16 @@ static int bn_bwd_partial_launch(const gsb_view* x, const gsb_view* dA1, const g
                     mean && invstd;
   if (x->dtype == GSB_BF16) {
     if (fast && relu_stats_fast_enabled())
-      bn_bwd_reduce_relu_bf16_kernel<2><<<grid, kThreads, smem, to_stream(s)>>>(
+      gsb::launch(bn_bwd_reduce_relu_bf16_kernel<2>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), 
           (const __nv_bfloat16*)x->ptr, x->sw, (const __nv_bfloat16*)dA1->ptr, dA1->sw, P, C, scale, shift, mean, invstd, partial);
     else if (fast)
-      bn_reduce_kernel<__nv_bfloat16, 1, true><<<grid, kThreads, smem, to_stream(s)>>>(
+      gsb::launch(bn_reduce_kernel<__nv_bfloat16, 1, true>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), 
           pv(x), pv(dA1), d2, P, C, scale, shift, mean, invstd, act1, act2, drop_seed, drop_mask, partial);
     else
-      bn_reduce_kernel<__nv_bfloat16, 1, false><<<grid, kThreads, smem, to_stream(s)>>>(
+      gsb::launch(bn_reduce_kernel<__nv_bfloat16, 1, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), 
           pv(x), pv(dA1), d2, P, C, scale, shift, mean, invstd, act1, act2, drop_seed, drop_mask, partial);
   } else {
-    bn_reduce_kernel<float, 1, false><<<grid, kThreads, smem, to_stream(s)>>>(pv(x), pv(dA1), d2, P, C, scale, shift, mean,
+    gsb::launch(bn_reduce_kernel<float, 1, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), pv(dA1), d2, P, C, scale, shift, mean,
                                                                              invstd, act1, act2, drop_seed, drop_mask, partial);
   }
   *rows_out = grid;
@@ -663,7 +671,7 @@ extern "C" int gsb_bn_bwd_reduce(const gsb_view* x, const gsb_view* dA1, const g
                             workspace_bytes, &grid, s))
     return -1;
   int n = 2 * x->c;
-  reduce_partials_kernel<<<(n + 31) / 32, 1024, 0, to_stream(s)>>>(reinterpret_cast<float*>(workspace), grid, n, sums);
+  gsb::launch(reduce_partials_kernel, gsb::LaunchCfg((n + 31) / 32, 1024, 0, to_stream(s)), reinterpret_cast<float*>(workspace), grid, n, sums);
   return check_launch("bn_bwd_reduce", 2);
 }
 
@@ -703,7 +711,7 @@ extern "C" int gsb_bn_stats_finalize(const float* partial, int rows, int c, doub
   if (fill_regions(regs, regions, rank, world, c, "bn_stats_finalize")) return -1;
   BnFusedFwd f{count, gamma, beta, running_mean, running_var, num_batches_tracked, momentum, eps, scale, shift, mean, invstd};
   BnFusedBwd b{nullptr, nullptr, 0, nullptr};
-  bn_stats_fused_kernel<0><<<(c + 15) / 16, 1024, 0, to_stream(s)>>>(partial, rows, c, regs, rank, world, f, b);
+  gsb::launch(bn_stats_fused_kernel<0>, gsb::LaunchCfg((c + 15) / 16, 1024, 0, to_stream(s)), partial, rows, c, regs, rank, world, f, b);
   return check_launch("bn_stats_finalize");
 }
 
@@ -715,7 +723,7 @@ extern "C" int gsb_bn_bwd_stats(const float* partial, int rows, int c, void* con
   if (fill_regions(regs, regions, rank, world, c, "bn_bwd_stats")) return -1;
   BnFusedFwd f{};
   BnFusedBwd b{dgamma, dbeta, accumulate, sums};
-  bn_stats_fused_kernel<1><<<(c + 15) / 16, 1024, 0, to_stream(s)>>>(partial, rows, c, regs, rank, world, f, b);
+  gsb::launch(bn_stats_fused_kernel<1>, gsb::LaunchCfg((c + 15) / 16, 1024, 0, to_stream(s)), partial, rows, c, regs, rank, world, f, b);
   return check_launch("bn_bwd_stats");
 }
 
@@ -735,22 +743,22 @@ extern "C" int gsb_bn_bwd_apply(const gsb_view* x, const gsb_view* dA1, const gs
                     mean && invstd;
   if (x->dtype == GSB_BF16) {
     if (fast)
-      bn_bwd_apply_kernel<__nv_bfloat16, true><<<grid, kThreads, 0, to_stream(s)>>>(
+      gsb::launch(bn_bwd_apply_kernel<__nv_bfloat16, true>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), 
           pv(x), pv(dA1), d2, P, C, scale, shift, mean, invstd, act1, act2, drop_seed, drop_mask, sums, inv, pv(dx));
     else
-      bn_bwd_apply_kernel<__nv_bfloat16, false><<<grid, kThreads, 0, to_stream(s)>>>(
+      gsb::launch(bn_bwd_apply_kernel<__nv_bfloat16, false>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), 
           pv(x), pv(dA1), d2, P, C, scale, shift, mean, invstd, act1, act2, drop_seed, drop_mask, sums, inv, pv(dx));
   } else {
-    bn_bwd_apply_kernel<float, false><<<grid, kThreads, 0, to_stream(s)>>>(pv(x), pv(dA1), d2, P, C, scale, shift, mean, invstd,
+    gsb::launch(bn_bwd_apply_kernel<float, false>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), pv(dA1), d2, P, C, scale, shift, mean, invstd,
                                                                            act1, act2, drop_seed, drop_mask, sums, inv, pv(dx));
   }
   if (mean != nullptr && (dgamma || dbeta))
-    bn_param_grad_kernel<<<(C + 127) / 128, 128, 0, to_stream(s)>>>(sums, C, dgamma, dbeta);
+    gsb::launch(bn_param_grad_kernel, gsb::LaunchCfg((C + 127) / 128, 128, 0, to_stream(s)), sums, C, dgamma, dbeta, 1);
   return check_launch("bn_bwd_apply", (mean != nullptr && (dgamma || dbeta)) ? 2 : 1);
 }
 
 extern "C" int gsb_bn_param_grad(const double* sums, int c, float* dgamma, float* dbeta, int accumulate, gsb_stream s) {
   GSB_REQUIRE(sums != nullptr, "bn_param_grad: null sums");
-  bn_param_grad_kernel<<<(c + 127) / 128, 128, 0, to_stream(s)>>>(sums, c, dgamma, dbeta, accumulate);
+  gsb::launch(bn_param_grad_kernel, gsb::LaunchCfg((c + 127) / 128, 128, 0, to_stream(s)), sums, c, dgamma, dbeta, accumulate);
   return check_launch("bn_param_grad");
 }

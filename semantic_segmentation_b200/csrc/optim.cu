@@ -11,6 +11,7 @@ namespace gsb {
 __global__ void __launch_bounds__(256) rmsprop_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                      float* __restrict__ sq, float* __restrict__ buf, int64_t n, float lr,
                                                      float alpha, float eps, float wd, float momentum, float gscale) {
+  GSB_PDL_ENTRY();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     float w = p[i];
     float gr = g[i] * gscale;
@@ -31,6 +32,7 @@ __global__ void __launch_bounds__(256) rmsprop_kernel(float* __restrict__ p, con
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                                   float* __restrict__ v, int64_t n, float step_size, float beta1, float beta2,
                                                   float eps, float wd, float inv_sqrt_bc2, float gscale) {
+  GSB_PDL_ENTRY();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     float w = p[i];
     float gr = g[i] * gscale;
@@ -58,7 +60,7 @@ extern "C" int gsb_rmsprop_step(float* p, const float* g, float* square_avg, flo
                                 float alpha, float eps, float weight_decay, float momentum, float grad_scale, gsb_stream s) {
   GSB_REQUIRE(p && g && square_avg && (momentum == 0.f || mom_buf), "rmsprop_step: null pointer");
   if (numel == 0) return 0;
-  rmsprop_kernel<<<grid1d(numel), 256, 0, to_stream(s)>>>(p, g, square_avg, mom_buf, numel, lr, alpha, eps, weight_decay,
+  gsb::launch(rmsprop_kernel, gsb::LaunchCfg(grid1d(numel), 256, 0, to_stream(s)), p, g, square_avg, mom_buf, numel, lr, alpha, eps, weight_decay,
                                                           momentum, grad_scale);
   return check_launch("rmsprop_step");
 }
@@ -68,7 +70,7 @@ extern "C" int gsb_adam_step(float* p, const float* g, float* exp_avg, float* ex
   GSB_REQUIRE(p && g && exp_avg && exp_avg_sq && step >= 1, "adam_step: bad argument");
   if (numel == 0) return 0;
   double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
-  adam_kernel<<<grid1d(numel), 256, 0, to_stream(s)>>>(p, g, exp_avg, exp_avg_sq, numel, (float)(lr / bc1), beta1, beta2, eps,
+  gsb::launch(adam_kernel, gsb::LaunchCfg(grid1d(numel), 256, 0, to_stream(s)), p, g, exp_avg, exp_avg_sq, numel, (float)(lr / bc1), beta1, beta2, eps,
                                                        weight_decay, (float)(1.0 / sqrt(bc2)), grad_scale);
   return check_launch("adam_step");
 }
@@ -100,6 +102,7 @@ __device__ __forceinline__ int opt_find_job(const int* blk0, int count, int b) {
 
 __global__ void __launch_bounds__(256) rmsprop_multi_kernel(const __grid_constant__ OptJobs J, float lr, float alpha, float eps,
                                                            float wd, float momentum, float gscale) {
+  GSB_PDL_ENTRY();
   const int j = opt_find_job(J.blk0, J.count, blockIdx.x);
   float* __restrict__ p = J.p[j];
   const float* __restrict__ g = J.g[j];
@@ -129,6 +132,7 @@ __global__ void __launch_bounds__(256) rmsprop_multi_kernel(const __grid_constan
 
 __global__ void __launch_bounds__(256) adam_multi_kernel(const __grid_constant__ OptJobs J, float step_size, float beta1,
                                                         float beta2, float eps, float wd, float inv_sqrt_bc2, float gscale) {
+  GSB_PDL_ENTRY();
   const int j = opt_find_job(J.blk0, J.count, blockIdx.x);
   float* __restrict__ p = J.p[j];
   const float* __restrict__ g = J.g[j];
@@ -186,7 +190,7 @@ extern "C" int gsb_rmsprop_step_multi(int n, float* const* p, const float* const
   cudaStream_t st = gsb::to_stream(s);
   return gsb::run_opt_multi(n, p, g, square_avg, mom_buf, numel, momentum != 0.f, "rmsprop_step_multi",
                             [&](const gsb::OptJobs& J, int blocks) {
-                              gsb::rmsprop_multi_kernel<<<blocks, 256, 0, st>>>(J, lr, alpha, eps, weight_decay, momentum, grad_scale);
+                              gsb::launch(gsb::rmsprop_multi_kernel, gsb::LaunchCfg(blocks, 256, 0, st), J, lr, alpha, eps, weight_decay, momentum, grad_scale);
                             });
 }
 
@@ -199,6 +203,6 @@ extern "C" int gsb_adam_step_multi(int n, float* const* p, const float* const* g
   cudaStream_t st = gsb::to_stream(s);
   const float step_size = (float)(lr / bc1), isb = (float)(1.0 / sqrt(bc2));
   return gsb::run_opt_multi(n, p, g, exp_avg, exp_avg_sq, numel, true, "adam_step_multi", [&](const gsb::OptJobs& J, int blocks) {
-    gsb::adam_multi_kernel<<<blocks, 256, 0, st>>>(J, step_size, beta1, beta2, eps, weight_decay, isb, grad_scale);
+    gsb::launch(gsb::adam_multi_kernel, gsb::LaunchCfg(blocks, 256, 0, st), J, step_size, beta1, beta2, eps, weight_decay, isb, grad_scale);
   });
 }

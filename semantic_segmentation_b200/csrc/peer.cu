@@ -26,6 +26,7 @@ constexpr int kPeerPerThread = kPeerMaxN / kPeerThreads;
 
 __global__ void __launch_bounds__(kPeerThreads, 1) peer_allreduce_f64_kernel(double* __restrict__ buf, int n, PeerRegions regs,
                                                                               int rank, int world) {
+  GSB_PDL_ENTRY();
   __shared__ unsigned long long s_seq;
   PeerHeader* mine = reinterpret_cast<PeerHeader*>(regs.r[rank]);
   if (threadIdx.x == 0) s_seq = ++mine->counter;
@@ -136,6 +137,6 @@ extern "C" int gsb_peer_allreduce_f64(double* buf, int n, void* const* regions, 
     GSB_REQUIRE(regions[i] != nullptr, "peer_allreduce: region %d is null", i);
     regs.r[i] = regions[i];
   }
-  peer_allreduce_f64_kernel<<<1, 1024, 0, to_stream(s)>>>(buf, n, regs, rank, world);
+  gsb::launch(peer_allreduce_f64_kernel, gsb::LaunchCfg(1, 1024, 0, to_stream(s)), buf, n, regs, rank, world);
   return check_launch("peer_allreduce_f64");
 }

@@ -39,6 +39,7 @@ __device__ __forceinline__ ItemIdx decode_item(int64_t i, int G, int OW, int OH)
 template <typename T>
 __global__ void __launch_bounds__(256) maxpool2_fwd_kernel(const T* __restrict__ x, int64_t xld, int N, int H, int W, int C,
                                                           T* __restrict__ y, int64_t yld) {
+  GSB_PDL_ENTRY();
   const int G = C >> 3, OH = H >> 1, OW = W >> 1;
   const int64_t total = (int64_t)N * OH * OW * G;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -63,6 +64,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) maxpool2_bwd_kernel(const T* __restrict__ x, int64_t xld, int N, int H, int W, int C,
                                                           const T* __restrict__ dy, int64_t dyld, T* __restrict__ dx,
                                                           int64_t dxld, int accumulate) {
+  GSB_PDL_ENTRY();
   const int G = C >> 3, OH = H >> 1, OW = W >> 1;
   const int WH = (H + 1) >> 1, WW = (W + 1) >> 1;  // windows incl. the ragged last row/col
   const int64_t total = (int64_t)N * WH * WW * G;
@@ -134,6 +136,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) upsample2_fwd_kernel(const T* __restrict__ x, int64_t xld, int N, int h, int w, int C,
                                                            T* __restrict__ out, int64_t old, int OH, int OW, int pad_top,
                                                            int pad_left) {
+  GSB_PDL_ENTRY();
   const int G = C >> 3;
   const int64_t total = (int64_t)N * OH * OW * G;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -163,6 +166,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) upsample2_bwd_kernel(const T* __restrict__ dout, int64_t dld, int N, int OH, int OW,
                                                            int C, T* __restrict__ dx, int64_t xld, int h, int w, int pad_top,
                                                            int pad_left) {
+  GSB_PDL_ENTRY();
   const int G = C >> 3;
   const int64_t total = (int64_t)N * h * w * G;
   const float sy = 2 * h > 1 ? (float)(h - 1) / (float)(2 * h - 1) : 0.f;
@@ -230,6 +234,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) upsample2_fwd_rows_kernel(const T* __restrict__ x, int64_t xld, int N, int h, int w, int C,
                                                                 T* __restrict__ out, int64_t old, int OH, int OW, int pad_top,
                                                                 int pad_left) {
+  GSB_PDL_ENTRY();
   __shared__ int s_i0[kMaxUpW], s_i1[kMaxUpW];
   __shared__ float s_l1[kMaxUpW];
   for (int u = threadIdx.x; u < 2 * w; u += blockDim.x) {
@@ -281,6 +286,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) upsample2_bwd_rows_kernel(const T* __restrict__ dout, int64_t dld, int N, int OH, int OW,
                                                                 int C, T* __restrict__ dx, int64_t xld, int h, int w,
                                                                 int pad_top, int pad_left) {
+  GSB_PDL_ENTRY();
   __shared__ int s_i0[kMaxUpW], s_i1[kMaxUpW];
   __shared__ float s_l1[kMaxUpW];
   __shared__ int s_oy[8];
@@ -367,6 +373,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) upsample2_bwd_win_kernel(const T* __restrict__ dout, int64_t dld, int N, int OH, int OW, int C,
                                                                T* __restrict__ dx, int64_t xld, int h, int w, int pad_top,
                                                                int pad_left) {
+  GSB_PDL_ENTRY();
   __shared__ int s_c0[kMaxUpW / 2];
   __shared__ float s_cw[kMaxUpW / 2][kUpWin];
   __shared__ int s_oy[8];
@@ -489,7 +496,7 @@ extern "C" int gsb_maxpool2_fwd(const gsb_view* x, const gsb_view* y, gsb_stream
               "maxpool2_fwd: shape mismatch");
   int64_t total = num_pixels(y) * (x->c / 8);
   if (total == 0) return 0;
-  DISPATCH_T(x->dtype, maxpool2_fwd_kernel<T><<<ew_grid(total), 256, 0, to_stream(s)>>>(
+  DISPATCH_T(x->dtype, gsb::launch(maxpool2_fwd_kernel<T>, gsb::LaunchCfg(ew_grid(total), 256, 0, to_stream(s)), 
                            (const T*)x->ptr, x->sw, x->n, x->h, x->w, x->c, (T*)y->ptr, y->sw));
   return check_launch("maxpool2_fwd");
 }
@@ -502,7 +509,7 @@ extern "C" int gsb_maxpool2_bwd(const gsb_view* x, const gsb_view* dy, const gsb
               "maxpool2_bwd: dx mismatch");
   int64_t total = (int64_t)x->n * ((x->h + 1) / 2) * ((x->w + 1) / 2) * (x->c / 8);
   if (total == 0) return 0;
-  DISPATCH_T(x->dtype, maxpool2_bwd_kernel<T><<<ew_grid(total), 256, 0, to_stream(s)>>>(
+  DISPATCH_T(x->dtype, gsb::launch(maxpool2_bwd_kernel<T>, gsb::LaunchCfg(ew_grid(total), 256, 0, to_stream(s)), 
                            (const T*)x->ptr, x->sw, x->n, x->h, x->w, x->c, (const T*)dy->ptr, dy->sw, (T*)dx->ptr, dx->sw,
                            accumulate));
   return check_launch("maxpool2_bwd");
@@ -516,12 +523,12 @@ extern "C" int gsb_upsample2_fwd(const gsb_view* x, const gsb_view* out, int pad
   if (2 * x->w <= kMaxUpW && (int64_t)out->n * out->h < ((int64_t)1 << 30)) {
     const int rows = out->n * out->h;
     const int grid = rows < num_sms() * 16 ? rows : num_sms() * 16;
-    DISPATCH_T(x->dtype, upsample2_fwd_rows_kernel<T><<<grid, 256, 0, to_stream(s)>>>(
+    DISPATCH_T(x->dtype, gsb::launch(upsample2_fwd_rows_kernel<T>, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), 
                              (const T*)x->ptr, x->sw, x->n, x->h, x->w, x->c, (T*)out->ptr, out->sw, out->h, out->w, pad_top,
                              pad_left));
     return check_launch("upsample2_fwd");
   }
-  DISPATCH_T(x->dtype, upsample2_fwd_kernel<T><<<ew_grid(total), 256, 0, to_stream(s)>>>(
+  DISPATCH_T(x->dtype, gsb::launch(upsample2_fwd_kernel<T>, gsb::LaunchCfg(ew_grid(total), 256, 0, to_stream(s)), 
                            (const T*)x->ptr, x->sw, x->n, x->h, x->w, x->c, (T*)out->ptr, out->sw, out->h, out->w, pad_top,
                            pad_left));
   return check_launch("upsample2_fwd");
@@ -537,17 +544,17 @@ extern "C" int gsb_upsample2_bwd(const gsb_view* dout, const gsb_view* dx, int p
     const int grid = rows < num_sms() * 16 ? rows : num_sms() * 16;
     static const bool win = []() { const char* e = getenv("GSB_UP_BWD_WIN"); return !(e && e[0] == '0'); }();
     if (win) {
-      DISPATCH_T(dx->dtype, upsample2_bwd_win_kernel<T><<<grid, 256, 0, to_stream(s)>>>(
+      DISPATCH_T(dx->dtype, gsb::launch(upsample2_bwd_win_kernel<T>, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), 
                                 (const T*)dout->ptr, dout->sw, dout->n, dout->h, dout->w, dout->c, (T*)dx->ptr, dx->sw, dx->h,
                                 dx->w, pad_top, pad_left));
     } else {
-      DISPATCH_T(dx->dtype, upsample2_bwd_rows_kernel<T><<<grid, 256, 0, to_stream(s)>>>(
+      DISPATCH_T(dx->dtype, gsb::launch(upsample2_bwd_rows_kernel<T>, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), 
                                 (const T*)dout->ptr, dout->sw, dout->n, dout->h, dout->w, dout->c, (T*)dx->ptr, dx->sw, dx->h,
                                 dx->w, pad_top, pad_left));
     }
     return check_launch("upsample2_bwd");
   }
-  DISPATCH_T(dx->dtype, upsample2_bwd_kernel<T><<<ew_grid(total), 256, 0, to_stream(s)>>>(
+  DISPATCH_T(dx->dtype, gsb::launch(upsample2_bwd_kernel<T>, gsb::LaunchCfg(ew_grid(total), 256, 0, to_stream(s)), 
                             (const T*)dout->ptr, dout->sw, dout->n, dout->h, dout->w, dout->c, (T*)dx->ptr, dx->sw, dx->h,
                             dx->w, pad_top, pad_left));
   return check_launch("upsample2_bwd");

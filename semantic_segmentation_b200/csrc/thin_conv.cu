@@ -52,6 +52,7 @@ template <typename T, int CO>
 __global__ void __launch_bounds__(256) thin_gather_kernel(TView in, const void* __restrict__ wp, int wdtype,
                                                          const float* __restrict__ bias, TView out, int mode, int KH, int KW,
                                                          int stride, int pad, int act, int L) {
+  GSB_PDL_ENTRY();
   extern __shared__ float sw[];  // [taps][CO][Cin]
   const int Cin = in.C, taps = KH * KW;
   for (int i = threadIdx.x; i < taps * CO * Cin; i += blockDim.x) {
@@ -126,6 +127,7 @@ template <typename T, int CI>
 __global__ void __launch_bounds__(256) thin_scatter_kernel(TView in, const void* __restrict__ wp, int wdtype,
                                                           const float* __restrict__ bias, TView out, int mode, int KH, int KW,
                                                           int stride, int pad, int act) {
+  GSB_PDL_ENTRY();
   extern __shared__ float sw[];  // [taps][CI][Cout]
   const int Cout = out.C, taps = KH * KW;
   for (int i = threadIdx.x; i < taps * CI * Cout; i += blockDim.x) {
@@ -188,6 +190,7 @@ __global__ void __launch_bounds__(256) thin_scatter_kernel(TView in, const void*
 template <typename T, int TP, int KWT>
 __global__ void __launch_bounds__(256) thin_wgrad_kernel(TView in, TView dout, float* __restrict__ dwp, int mode, int KH, int KW,
                                                         int stride, int pad, int co) {
+  GSB_PDL_ENTRY();
   extern __shared__ float sacc[];  // [TP][Cin]
   const int Cin = in.C, taps = KH * KW;
   const int tap0 = blockIdx.y * TP;
@@ -285,7 +288,7 @@ int thin_gather_try(const gsb_view* in, const void* wp, int wdtype, const float*
 #define GSB_THIN_G(T, C)                                                                                              \
   do {                                                                                                                \
     cudaFuncSetAttribute(thin_gather_kernel<T, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);           \
-    thin_gather_kernel<T, C><<<grid, 256, smem, st>>>(vi, wp, wdtype, bias, vo, g->mode, g->kh, g->kw, g->stride,     \
+    gsb::launch(thin_gather_kernel<T, C>, gsb::LaunchCfg(grid, 256, smem, st), vi, wp, wdtype, bias, vo, g->mode, g->kh, g->kw, g->stride,     \
                                                       g->pad, act, L);                                                \
   } while (0)
     if (in->dtype == GSB_BF16) {
@@ -307,7 +310,7 @@ int thin_gather_try(const gsb_view* in, const void* wp, int wdtype, const float*
 #define GSB_THIN_S(T, C)                                                                                              \
   do {                                                                                                                \
     cudaFuncSetAttribute(thin_scatter_kernel<T, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);          \
-    thin_scatter_kernel<T, C><<<grid, 256, smem, st>>>(vi, wp, wdtype, bias, vo, g->mode, g->kh, g->kw, g->stride,    \
+    gsb::launch(thin_scatter_kernel<T, C>, gsb::LaunchCfg(grid, 256, smem, st), vi, wp, wdtype, bias, vo, g->mode, g->kh, g->kw, g->stride,    \
                                                        g->pad, act);                                                  \
   } while (0)
     if (out->dtype == GSB_BF16) {
@@ -334,7 +337,7 @@ int thin_wgrad_try(const gsb_view* in, const gsb_view* dout, float* dwp, const g
   TView vi = tv(in), vd = tv(dout);
   for (int co = 0; co < dout->c; ++co) {
 #define GSB_THIN_WG(TT, TPV, KWT)                                                                                          \
-  thin_wgrad_kernel<TT, TPV, KWT><<<dim3(grid, passes), 256, smem, st>>>(vi, vd, dwp, g->mode, g->kh, g->kw, g->stride, g->pad, co)
+  gsb::launch(thin_wgrad_kernel<TT, TPV, KWT>, gsb::LaunchCfg(dim3(grid, passes), 256, smem, st), vi, vd, dwp, g->mode, g->kh, g->kw, g->stride, g->pad, co)
     if (in->dtype == GSB_BF16) {
       if (g->kw == 8) GSB_THIN_WG(__nv_bfloat16, 8, 8);
       else if (g->kw == 4) GSB_THIN_WG(__nv_bfloat16, 16, 4);
