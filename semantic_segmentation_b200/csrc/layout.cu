@@ -307,14 +307,110 @@ __device__ __forceinline__ void layout_tile(const float* __restrict__ tsrc, floa
       }
     }
   };
+  // ---- vector paths (full tiles): 16-byte global accesses on both sides.  The scalar loops above issue one 4-byte load and
+  // one 2-byte store per element plus ~30 index instructions: instruction-issue bound (pack of the U-Net's 17 M weights into
+  // both layouts 143 us against ~25 us of HBM time, profiles/r01r).
+  const bool full = (i0b + kTI0 <= d0) && (i1b + kTI1 <= d1) && (tb + tt <= taps);
+  const float* tptr = PACK ? tsrc : tdst;
+  const void* pptr = PACK ? (const void*)pdst : (const void*)psrc;
+  // a group of 4 consecutive torch-layout floats starting at a multiple of 4 inside the tile is contiguous and 16-byte
+  // aligned when the tile spans all taps (rows of 32 * taps floats) or when the tap chunk itself is a multiple of 4
+  const bool vec_t = full && (tt == taps ? (((int64_t)d1 * taps) % 4 == 0) : (tt % 4 == 0 && taps % 4 == 0)) &&
+                     ((reinterpret_cast<uintptr_t>(tptr) & 15) == 0);
+  const bool vec_p = full && (cols % 8 == 0) && ((reinterpret_cast<uintptr_t>(pptr) & 15) == 0);
+  auto torch_side_vec = [&](bool load) {
+    const int per_row = kTI1 * tt;                       // floats per i0 row of the tile
+    if (TT > 0 && load) {
+      // all global loads of the thread first (up to 8 x 16 bytes in flight), then the shared-memory scatter
+      constexpr int NG = TT > 0 ? (kTI0 * kTI1 * TT / 4 + 255) / 256 : 1;
+      float4 v[NG];
+#pragma unroll
+      for (int u = 0; u < NG; ++u) {
+        const int g = threadIdx.x + u * 256;
+        if (g < nA / 4) {
+          const int e = g * 4, i0l = e / per_row, rem = e - i0l * per_row, i1l = rem / tt, t = rem - i1l * tt;
+          v[u] = __ldg(reinterpret_cast<const float4*>(tsrc + ((int64_t)(i0b + i0l) * d1 + i1b + i1l) * taps + tb + t));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < NG; ++u) {
+        const int g = threadIdx.x + u * 256;
+        if (g < nA / 4) {
+          const int e = g * 4, i0l = e / per_row, rem = e - i0l * per_row;
+          int i1l = rem / tt, t = rem - i1l * tt;
+          float* row = sm + i0l * kTPitch0;
+          const float vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            row[i1l * kTPitch1 + t] = vv[k];
+            if (++t == tt) { t = 0; ++i1l; }
+          }
+        }
+      }
+      return;
+    }
+    for (int g = threadIdx.x; g < nA / 4; g += blockDim.x) {
+      const int e = g * 4;
+      const int i0l = e / per_row, rem = e - i0l * per_row;
+      int i1l = rem / tt, t = rem - i1l * tt;
+      const int64_t off = ((int64_t)(i0b + i0l) * d1 + i1b + i1l) * taps + tb + t;
+      float* row = sm + i0l * kTPitch0;
+      if (load) {
+        const float4 v = *reinterpret_cast<const float4*>(tsrc + off);
+        const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          row[i1l * kTPitch1 + t] = vv[k];
+          if (++t == tt) { t = 0; ++i1l; }
+        }
+      } else {
+        float vv[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          vv[k] = row[i1l * kTPitch1 + t];
+          if (++t == tt) { t = 0; ++i1l; }
+        }
+        float4* d = reinterpret_cast<float4*>(tdst + off);
+        if (accumulate) {
+          const float4 o = *d;
+          vv[0] += o.x; vv[1] += o.y; vv[2] += o.z; vv[3] += o.w;
+        }
+        *d = make_float4(vv[0], vv[1], vv[2], vv[3]);
+      }
+    }
+  };
+  auto packed_side_vec = [&](bool load) {
+    // one item = 8 consecutive columns of one packed row: rfd -> (tap, i0l) rows of 32 i1 (4 items), else (tap, i1l) rows
+    // of 16 i0 (2 items); tt * 64 items per tile either way
+#pragma unroll 4
+    for (int item = threadIdx.x; item < tt * 64; item += blockDim.x) {
+      int t, i0l, i1l, r, c;
+      if (rfd) { const int c8 = item & 3; i0l = (item >> 2) & 15; t = item >> 6; i1l = c8 * 8; r = i0b + i0l; c = i1b + i1l; }
+      else     { const int c8 = item & 1; i1l = (item >> 1) & 31; t = item >> 6; i0l = c8 * 8; r = i1b + i1l; c = i0b + i0l; }
+      const int64_t off = ((int64_t)(tb + t) * rows + r) * cols + c;
+      float* cell = sm + i0l * kTPitch0 + i1l * kTPitch1 + t;
+      const int step = rfd ? kTPitch1 : kTPitch0;          // next column = next i1 (rfd) or next i0
+      if (load) {
+        const float4 a = *reinterpret_cast<const float4*>(psrc + off), b = *reinterpret_cast<const float4*>(psrc + off + 4);
+        cell[0] = a.x; cell[step] = a.y; cell[2 * step] = a.z; cell[3 * step] = a.w;
+        cell[4 * step] = b.x; cell[5 * step] = b.y; cell[6 * step] = b.z; cell[7 * step] = b.w;
+      } else {
+        float v[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = cell[k * step];
+        if (pdtype == GSB_BF16) Vec8<__nv_bfloat16>::store(reinterpret_cast<__nv_bfloat16*>(pdst) + off, v);
+        else Vec8<float>::store(reinterpret_cast<float*>(pdst) + off, v);
+      }
+    }
+  };
   if (PACK) {
-    torch_side(true);
+    if (vec_t) torch_side_vec(true); else torch_side(true);
     __syncthreads();
-    packed_side(false);
+    if (vec_p) packed_side_vec(false); else packed_side(false);
   } else {
-    packed_side(true);
+    if (vec_p) packed_side_vec(true); else packed_side(true);
     __syncthreads();
-    torch_side(false);
+    if (vec_t) torch_side_vec(false); else torch_side(false);
   }
 }
 

@@ -436,7 +436,11 @@ def test_batched_pack_and_unpack_match_single():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("shape", [(5, 70, 3, 3), (64, 1, 4, 4), (33, 129, 8, 8), (512, 256, 1, 1), (16, 32, 2, 2), (130, 17, 4, 4)])
+@pytest.mark.parametrize("shape", [(5, 70, 3, 3), (64, 1, 4, 4), (33, 129, 8, 8), (512, 256, 1, 1), (16, 32, 2, 2), (130, 17, 4, 4),
+                                   # full tiles -> the 16-byte vector paths: all taps per tile (9, 16, 1), tap chunks (64 = 4 x 16),
+                                   # and mixes of full / ragged tiles and of aligned / unaligned row lengths
+                                   (64, 128, 3, 3), (128, 64, 3, 3), (96, 64, 4, 4), (64, 96, 8, 8), (64, 64, 1, 1), (48, 40, 3, 3),
+                                   (64, 36, 3, 3), (36, 64, 3, 3), (32, 33, 4, 4), (64, 64, 5, 5)])
 def test_pack_unpack_against_torch_permute(shape):
     """Tiled transposes (csrc/layout.cu) against torch.permute: ragged tiles in every dimension, 1..64 taps,
     both row conventions, bf16 and fp32 packs, accumulate mode of the un-pack."""
