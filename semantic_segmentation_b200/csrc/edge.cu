@@ -7,6 +7,8 @@
 //     fp32 NCHW logits; backward fuses dX, dW and db in one pass over (x, dlogits).
 // All four are HBM-bound; algorithmic bytes: stem fwd = N*H*W*(4 Cin + Cout*esz); stem wgrad = one read of dY
 // per 16-tap pass + x; head fwd = N*H*W*(K*esz + 4C); head bwd = N*H*W*(2 K*esz + 4C).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace gsb {
@@ -245,23 +247,26 @@ __global__ void __launch_bounds__(256, 2) stem_fwd_fast_kernel(const float* __re
   }
 }
 
-// dw[co][ci][ky][kx] += sum_pix dY[pix][co] * x[pix @ (ky,kx)]; blockIdx.y = ci; all K*K taps of 8 channels in registers
-template <typename T, int PX, int K, int S>
+// dw[co][ci][ky][kx] += sum_pix dY[pix][co] * x[pix @ (ky,kx)]; blockIdx.y = ci; KYN*K taps of 8 channels in registers:
+// KYN = K for the 3x3 stem; the 4x4 stride-2 first convolutions of the Pix2Pix generator / discriminator take KYN = 2
+// kernel rows per CTA (blockIdx.z = which pair), 64 accumulator registers instead of 128
+template <typename T, int PX, int K, int S, int KYN>
 __global__ void __launch_bounds__(256, 2) stem_wgrad_fast_kernel(const float* __restrict__ x, int N, int Cin, int H, int W,
                                                              const T* __restrict__ dy, int64_t dld, int OH, int OW, int Cout,
                                                              int pad, float* __restrict__ dw) {
   GSB_PDL_ENTRY();
-  extern __shared__ float sacc[];  // [G][K*K][8]
+  extern __shared__ float sacc[];  // [G][KYN*K][8]
   constexpr int SPAN = (PX - 1) * S + K;
-  const int ci = blockIdx.y;
+  constexpr int KT = KYN * K;      // taps of this CTA
+  const int ci = blockIdx.y, ky0 = blockIdx.z * KYN;
   const unsigned G = (unsigned)Cout >> 3, XQ = (unsigned)(OW + PX - 1) / PX;
   const unsigned lanes = blockDim.x / G;
   const unsigned g = threadIdx.x % G, lane = threadIdx.x / G;
-  for (int i = threadIdx.x; i < (int)G * K * K * 8; i += blockDim.x) sacc[i] = 0.f;
+  for (int i = threadIdx.x; i < (int)G * KT * 8; i += blockDim.x) sacc[i] = 0.f;
   __syncthreads();
-  float2 acc[K * K][4];  // packed fp32x2 accumulators (FFMA2): half the arithmetic instructions of the scalar form
+  float2 acc[KT][4];  // packed fp32x2 accumulators (FFMA2): half the arithmetic instructions of the scalar form
 #pragma unroll
-  for (int t = 0; t < K * K; ++t)
+  for (int t = 0; t < KT; ++t)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[t][j] = make_float2(0.f, 0.f);
   const unsigned items = (unsigned)N * (unsigned)OH * XQ;
@@ -286,8 +291,8 @@ __global__ void __launch_bounds__(256, 2) stem_wgrad_fast_kernel(const float* __
     const int ixb = ox0 * S - pad;
     const bool x_inside = ixb >= 0 && ixb + SPAN <= W;
 #pragma unroll
-    for (int ky = 0; ky < K; ++ky) {
-      const int iy = oy * S - pad + ky;
+    for (int ky = 0; ky < KYN; ++ky) {
+      const int iy = oy * S - pad + ky0 + ky;
       if (iy < 0 || iy >= H) continue;
       const float* xr = x + (((int64_t)n * Cin + ci) * H + iy) * W;
       float xv[SPAN];
@@ -312,17 +317,17 @@ __global__ void __launch_bounds__(256, 2) stem_wgrad_fast_kernel(const float* __
     }
   }
 #pragma unroll
-  for (int t = 0; t < K * K; ++t)
+  for (int t = 0; t < KT; ++t)
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      atomicAdd(&sacc[(g * K * K + t) * 8 + 2 * j], acc[t][j].x);
-      atomicAdd(&sacc[(g * K * K + t) * 8 + 2 * j + 1], acc[t][j].y);
+      atomicAdd(&sacc[(g * KT + t) * 8 + 2 * j], acc[t][j].x);
+      atomicAdd(&sacc[(g * KT + t) * 8 + 2 * j + 1], acc[t][j].y);
     }
   __syncthreads();
   const int taps = Cin * K * K;
-  for (int i = threadIdx.x; i < (int)G * K * K * 8; i += blockDim.x) {
-    const int j = i % 8, t = (i / 8) % (K * K), gg = i / (8 * K * K);
-    atomicAdd(dw + (int64_t)(gg * 8 + j) * taps + ci * K * K + t, sacc[i]);
+  for (int i = threadIdx.x; i < (int)G * KT * 8; i += blockDim.x) {
+    const int j = i % 8, t = (i / 8) % KT, gg = i / (8 * KT);
+    atomicAdd(dw + (int64_t)(gg * 8 + j) * taps + ci * K * K + ky0 * K + t, sacc[i]);
   }
 }
 
@@ -559,7 +564,18 @@ extern "C" int gsb_stem_conv_wgrad(const float* x, int n, int cin, int h, int w,
     const int64_t items = (int64_t)dy->n * dy->h * ((dy->w + PX - 1) / PX);
     int gx = grid_cap((items + lanes - 1) / lanes, 4);
     size_t smem = (size_t)G * 9 * 8 * sizeof(float);
-    EDGE_DISPATCH_T(dy->dtype, gsb::launch(stem_wgrad_fast_kernel<T, PX, 3, 1>, gsb::LaunchCfg(dim3(gx, cin), 256, smem, to_stream(s)), 
+    EDGE_DISPATCH_T(dy->dtype, gsb::launch(stem_wgrad_fast_kernel<T, PX, 3, 1, 3>, gsb::LaunchCfg(dim3(gx, cin), 256, smem, to_stream(s)), 
+                                   x, n, cin, h, w, (const T*)dy->ptr, dy->sw, dy->h, dy->w, cout, pad, dweight));
+    return check_launch("stem_conv_wgrad");
+  }
+  if (k == 4 && stride == 2 && num_pixels(dy) < (int64_t)1 << 31 && getenv("GSB_STEM_WGRAD_FAST42") == nullptr) {
+    // first convolutions of the Pix2Pix generator (1 -> 64) and discriminator (2 -> 64): one launch instead of
+    // cin * 16 / 9 launches of the generic kernel (0.75 ms per Pix2Pix step, profiles/r01r)
+    constexpr int PX = 2;
+    const int64_t items = (int64_t)dy->n * dy->h * ((dy->w + PX - 1) / PX);
+    int gx = grid_cap((items + lanes - 1) / lanes, 2);
+    size_t smem = (size_t)G * 8 * 8 * sizeof(float);
+    EDGE_DISPATCH_T(dy->dtype, gsb::launch(stem_wgrad_fast_kernel<T, PX, 4, 2, 2>, gsb::LaunchCfg(dim3(gx, cin, 2), 256, smem, to_stream(s)), 
                                    x, n, cin, h, w, (const T*)dy->ptr, dy->sw, dy->h, dy->w, cout, pad, dweight));
     return check_launch("stem_conv_wgrad");
   }
