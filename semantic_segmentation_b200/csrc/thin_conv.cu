@@ -7,6 +7,8 @@
 //   * thin_wgrad  : weight gradient when dout has <= 4 channels
 // All three are bandwidth / FMA-issue kernels with the small operand's weights in shared memory and 128-bit accesses
 // on the wide NHWC tensor; the narrow tensor is addressed through its element strides (NCHW fp32 at the API edge).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace gsb {
@@ -115,6 +117,114 @@ __global__ void __launch_bounds__(256) thin_gather_kernel(TView in, const void* 
           const float z = act_fwd(acc[c] + (bias ? bias[c] : 0.f), act);
           st_elem(out.ptr, (int64_t)n * out.sn + (int64_t)oy * out.sh + (int64_t)ox * out.sw + (int64_t)c * out.sc, out.dtype, z);
         }
+    }
+  }
+}
+
+// Register-blocked form: one lane group computes PXB output pixels of one row that share their tap set (neighbours for a
+// convolution, pixels `stride` apart -- the same sub-pixel phase -- for a transposed convolution), so every weight vector
+// read from shared memory feeds PXB * 8 FMAs instead of 8.  The one-pixel form above issues two LDS.128 per 8 FMAs and is
+// bound by shared-memory bandwidth (generator output cell 128 -> 1, merged 8x8: 170 us per launch against ~10 us of HBM
+// time, profiles/r01r).
+template <typename T, int CO, int PXB>
+__global__ void __launch_bounds__(256) thin_gather_px_kernel(TView in, const void* __restrict__ wp, int wdtype,
+                                                            const float* __restrict__ bias, TView out, int mode, int KH, int KW,
+                                                            int stride, int pad, int act, int L) {
+  GSB_PDL_ENTRY();
+  extern __shared__ float sw[];  // [taps][CO][Cin]
+  const int Cin = in.C, taps = KH * KW;
+  for (int i = threadIdx.x; i < taps * CO * Cin; i += blockDim.x) {
+    const int ci = i % Cin, co = (i / Cin) % CO, t = i / (Cin * CO);
+    sw[i] = co < out.C ? wload(wp, wdtype, ((int64_t)t * out.C + co) * Cin + ci) : 0.f;
+  }
+  __syncthreads();
+  const int slices = Cin >> 3;
+  const int l = threadIdx.x % L;
+  const bool conv = mode == GSB_MODE_CONV;
+  const int spacing = conv ? 1 : stride;   // distance between the output pixels of one item
+  const int xstep = conv ? stride : 1;     // distance between the input pixels they read for one tap
+  const unsigned wq = ((unsigned)out.W + spacing - 1) / spacing, XB = (wq + PXB - 1) / PXB;
+  const unsigned items = (unsigned)out.N * out.H * spacing * XB;
+  const unsigned ipb = blockDim.x / L;
+  const T* ip = reinterpret_cast<const T*>(in.ptr);
+  for (unsigned it0 = blockIdx.x * ipb; it0 < items; it0 += gridDim.x * ipb) {   // uniform trip count (shuffles below)
+    const unsigned it = it0 + threadIdx.x / L;
+    const bool valid = it < items;
+    float acc[PXB][CO];
+#pragma unroll
+    for (int j = 0; j < PXB; ++j)
+#pragma unroll
+      for (int c = 0; c < CO; ++c) acc[j][c] = 0.f;
+    int ox0 = 0, oy = 0, n = 0;
+    if (valid) {
+      const unsigned xb = it % XB;
+      unsigned r = it / XB;
+      const int ph = (int)(r % (unsigned)spacing);
+      r /= (unsigned)spacing;
+      oy = (int)(r % (unsigned)out.H);
+      n = (int)(r / (unsigned)out.H);
+      ox0 = ph + spacing * (int)(xb * PXB);
+      int ky0, kys, kx0, kxs;
+      tap_range(mode, oy, stride, pad, ky0, kys);
+      tap_range(mode, ox0, stride, pad, kx0, kxs);     // depends on ox0 only through its phase: shared by the PXB pixels
+      for (int ky = ky0; ky < KH; ky += kys) {
+        int iy;
+        if (!tap_src(mode, oy, ky, stride, pad, in.H, iy)) continue;
+        const T* srow = ip + (int64_t)n * in.sn + (int64_t)iy * in.sh;
+        for (int kx = kx0; kx < KW; kx += kxs) {
+          // input column of pixel 0 (may lie outside; pixel j reads ixb + j * xstep)
+          const int ixb = conv ? ox0 * stride - pad + kx : (ox0 + pad - kx) / stride;   // exact: kx = (ox0 + pad) mod stride
+          bool ok[PXB];
+          bool any = false;
+#pragma unroll
+          for (int j = 0; j < PXB; ++j) {
+            const int ix = ixb + j * xstep;
+            ok[j] = (ox0 + j * spacing < out.W) && ix >= 0 && ix < in.W;
+            any |= ok[j];
+          }
+          if (!any) continue;
+          const float* wt = sw + (ky * KW + kx) * CO * Cin;
+          for (int sidx = l; sidx < slices; sidx += L) {
+            float4 w0[CO], w1[CO];
+#pragma unroll
+            for (int c = 0; c < CO; ++c) {
+              w0[c] = *reinterpret_cast<const float4*>(wt + c * Cin + sidx * 8);
+              w1[c] = *reinterpret_cast<const float4*>(wt + c * Cin + sidx * 8 + 4);
+            }
+#pragma unroll
+            for (int j = 0; j < PXB; ++j) {
+              if (!ok[j]) continue;
+              float v[8];
+              Vec8<T>::load(srow + (int64_t)(ixb + j * xstep) * in.sw + sidx * 8, v);
+#pragma unroll
+              for (int c = 0; c < CO; ++c) {
+                float a = acc[j][c];
+                a = fmaf(v[0], w0[c].x, a); a = fmaf(v[1], w0[c].y, a); a = fmaf(v[2], w0[c].z, a); a = fmaf(v[3], w0[c].w, a);
+                a = fmaf(v[4], w1[c].x, a); a = fmaf(v[5], w1[c].y, a); a = fmaf(v[6], w1[c].z, a); a = fmaf(v[7], w1[c].w, a);
+                acc[j][c] = a;
+              }
+            }
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < PXB; ++j)
+#pragma unroll
+      for (int c = 0; c < CO; ++c)
+        for (int o = L >> 1; o > 0; o >>= 1) acc[j][c] += __shfl_xor_sync(0xffffffffu, acc[j][c], o);
+    if (valid && l == 0) {
+#pragma unroll
+      for (int j = 0; j < PXB; ++j) {
+        const int ox = ox0 + j * spacing;
+        if (ox >= out.W) continue;
+#pragma unroll
+        for (int c = 0; c < CO; ++c)
+          if (c < out.C) {
+            const float z = act_fwd(acc[j][c] + (bias ? bias[c] : 0.f), act);
+            st_elem(out.ptr, (int64_t)n * out.sn + (int64_t)oy * out.sh + (int64_t)ox * out.sw + (int64_t)c * out.sc, out.dtype, z);
+          }
+      }
     }
   }
 }
@@ -283,8 +393,30 @@ int thin_gather_try(const gsb_view* in, const void* wp, int wdtype, const float*
     int L = pow2_floor(in->c / 8);
     if (L > 16) L = 16;
     const int ppb = 256 / L;
-    const int grid = grid_sm((P + ppb - 1) / ppb, 8);
     TView vi = tv(in), vo = tv(out);
+    static const bool px_on = []() { const char* e = getenv("GSB_THIN_PX"); return !(e && e[0] == '0'); }();
+    if (px_on) {
+      // register-blocked kernel: 4 pixels of one row and phase per lane group
+      constexpr int PXB = 4;
+      const int spacing = g->mode == GSB_MODE_CONV ? 1 : g->stride;
+      const int64_t wq = (out->w + spacing - 1) / spacing, xb = (wq + PXB - 1) / PXB;
+      const int64_t items = (int64_t)out->n * out->h * spacing * xb;
+      const int pgrid = grid_sm((items + ppb - 1) / ppb, 8);
+#define GSB_THIN_GP(T, C)                                                                                             \
+  do {                                                                                                                \
+    cudaFuncSetAttribute(thin_gather_px_kernel<T, C, PXB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   \
+    gsb::launch(thin_gather_px_kernel<T, C, PXB>, gsb::LaunchCfg(pgrid, 256, smem, st), vi, wp, wdtype, bias, vo, g->mode, g->kh, g->kw,  \
+                g->stride, g->pad, act, L);                                                                           \
+  } while (0)
+      if (in->dtype == GSB_BF16) {
+        if (CO == 1) GSB_THIN_GP(__nv_bfloat16, 1); else if (CO == 2) GSB_THIN_GP(__nv_bfloat16, 2); else GSB_THIN_GP(__nv_bfloat16, 4);
+      } else {
+        if (CO == 1) GSB_THIN_GP(float, 1); else if (CO == 2) GSB_THIN_GP(float, 2); else GSB_THIN_GP(float, 4);
+      }
+#undef GSB_THIN_GP
+      return check_launch("thin_gather_px") ? -1 : 1;
+    }
+    const int grid = grid_sm((P + ppb - 1) / ppb, 8);
 #define GSB_THIN_G(T, C)                                                                                              \
   do {                                                                                                                \
     cudaFuncSetAttribute(thin_gather_kernel<T, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);           \

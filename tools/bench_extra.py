@@ -76,6 +76,24 @@ def pix2pix(batch, steps):
     print(json.dumps({"workload": "pix2pix optimize_parameters (unet_256 G + basic D, GANLoss + 100*L1, Adam)", "batch": batch,
                       "ms_per_step": t * 1e3, "images_per_s": batch / t, "tflops_merged_form": 157e9 * batch / t / 1e12,
                       "dtype": "bf16", "data": "synthetic"}), flush=True)
+    if os.environ.get("P2P_GRAPH", "0") == "1":
+        # Diagnostic only: is the eager step (~510 launches through ctypes) host-bound?  Replays one captured step; the
+        # Adam step count and the dropout seed are frozen in the graph, so this is a timing probe, not a training loop.
+        try:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                step()
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                step()
+            tg = timed(graph.replay, steps)
+            print(json.dumps({"workload": "pix2pix step, CUDA-graph replay (diagnostic)", "batch": batch, "ms_per_step": tg * 1e3,
+                              "images_per_s": batch / tg}), flush=True)
+        except Exception as exc:  # noqa: BLE001
+            print(json.dumps({"workload": "pix2pix step, CUDA-graph replay (diagnostic)", "error": repr(exc)[:300]}), flush=True)
 
 
 def evaluate_sweep(steps):
