@@ -124,7 +124,18 @@ def check(rc: int, what: str = "") -> None:
         raise RuntimeError("genseg_b200 %s failed (%d): %s" % (what, rc, msg))
 
 
+_RAW_STREAM = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream_ptr(device=None) -> int:
+    """cudaStream_t of torch's current stream on ``device`` (honours ``torch.cuda.stream(...)`` and graph capture).
+    ``torch.cuda.current_stream()`` builds a Stream object per call (~7 us, 16 % of the host time of an eager Pix2Pix step
+    with its 510 launches); the raw accessor returns the handle directly."""
+    if _RAW_STREAM is not None:
+        idx = device if isinstance(device, int) else getattr(device, "index", None)
+        if idx is None:
+            idx = torch.cuda.current_device()
+        return _RAW_STREAM(idx)
     return torch.cuda.current_stream(device).cuda_stream
 
 

@@ -17,7 +17,7 @@ import torch
 
 from . import ops
 from ._lib import ACT_LRELU, ACT_NONE, ACT_RELU, ACT_TANH, view_nchw, view_nhwc
-from .engine import ConvBNAct, ConvSpec, EdgeConv, Saved, _nhwc_empty, act_dtype
+from .engine import ConvBNAct, ConvSpec, EdgeConv, Saved, WeightPacks, _nhwc_empty, act_dtype
 from .unet_program import _put
 
 ARCH_KEY = "__upconv_arch__"
@@ -119,6 +119,21 @@ class GeneratorProgram:
         c = self.c
         sizes = [(h, w)] + [(h >> L, w >> L) for L in range(1, D + 1)]      # sizes[L] = spatial of e_L
         cats = [None] + [_nhwc_empty(n, sizes[L][0], sizes[L][1], 2 * c[L], dev) for L in range(1, D)]
+        # ---- weights: the eight merges first, then every tensor-core weight (forward and, when a tape is kept, backward
+        # layout) packed by ONE launch instead of one or two per layer (the eager step is host-bound: profiles/README.md 13)
+        packs = WeightPacks()
+        for L in range(2, D + 1):
+            packs.add(f"down{L}", self.down[L].spec, P[_block_prefix(L) + ".model.1.weight"], need_bwd=save)
+        merged = {}
+        for L in range(D - 1, 0, -1):
+            wn, _ = self._up_names(L)
+            if self.inst:
+                bnm = self._up_bias_names(L)
+                merged[L] = ops.merge_upconv(P[wn[0]], P[wn[1]], P[wn[2]], P[bnm[0]], P[bnm[1]], P[bnm[2]], arch[D - 1 - L])
+            else:
+                merged[L] = (ops.merge_upconv(P[wn[0]], P[wn[1]], P[wn[2]], None, None, None, arch[D - 1 - L])[0], None)
+            packs.add(f"up{L}", self.up[L].spec, merged[L][0], need_bwd=save)
+        packs.run()
         # ---- encoder
         cur_view, cur_keep, ch, cw = view_nchw(x), x, h, w
         for L in range(1, D + 1):
@@ -127,25 +142,22 @@ class GeneratorProgram:
             bn = self._bn(P, B, q + ".model.2") if (1 < L < D and not self.inst) else None
             out2 = cats[L][..., :c[L]] if L < D else None
             s, sv = self.down[L].forward(cur_view, cur_keep, n, ch, cw, dev, P[wname], self._down_bias(P, L), bn, training,
-                                         out2=out2, save=save)
+                                         out2=out2, save=save, packed=packs.get(f"down{L}") if L > 1 else None)
             tape[f"down{L}"] = sv
             cur_view, cur_keep, (ch, cw) = view_nhwc(s), s, sizes[L]
         # ---- decoder
         cur = cur_keep                                   # u = relu(e_D)
         for L in range(D - 1, 0, -1):
             wn, bnp = self._up_names(L)
-            if self.inst:
-                bnm = self._up_bias_names(L)
-                wm, bm_up = ops.merge_upconv(P[wn[0]], P[wn[1]], P[wn[2]], P[bnm[0]], P[bnm[1]], P[bnm[2]], arch[D - 1 - L])
-            else:
-                wm, bm_up = ops.merge_upconv(P[wn[0]], P[wn[1]], P[wn[2]], None, None, None, arch[D - 1 - L])[0], None
+            wm, bm_up = merged[L]
             hh, ww = cur.shape[1], cur.shape[2]
             drop = self.up[L].dropout and training
             mask = masks[L - 4] if (drop and masks is not None) else None
             seed = (base_seed + 7919 * L) if (drop and masks is None) else 0
             _, sv = self.up[L].forward(view_nhwc(cur), cur, n, hh, ww, dev, wm, bm_up,
                                        None if self.inst else self._bn(P, B, bnp), training,
-                                       out1=cats[L][..., c[L]:], save=save, drop_seed=seed, drop_mask=mask)
+                                       out1=cats[L][..., c[L]:], save=save, drop_seed=seed, drop_mask=mask,
+                                       packed=packs.get(f"up{L}"))
             tape[f"up{L}"] = sv
             cur = cats[L]
         wo = [f"model.model.3._ops._ops.{i}.op.weight" for i in range(3)]
@@ -263,12 +275,17 @@ class DiscriminatorProgram:
         a, sv = self.l0.forward(view_nchw(x), x, n, h, w, dev, P["model.0.weight"], P["model.0.bias"], None, training,
                                 save=save)
         tape["l0"] = sv
+        packs = WeightPacks()
+        for idx, layer in self.mid:
+            packs.add(f"l{idx}", layer.spec, P[f"model.{idx}.weight"], need_bwd=save)
+        packs.run()
         for idx, layer in self.mid:
             p = f"model.{idx + 1}"
             bn = None if self.inst else (P[p + ".weight"], P[p + ".bias"], B[p + ".running_mean"], B[p + ".running_var"],
                                          B[p + ".num_batches_tracked"])
             a, sv = layer.forward(view_nhwc(a), a, n, a.shape[1], a.shape[2], dev, P[f"model.{idx}.weight"],
-                                  P[f"model.{idx}.bias"] if self.inst else None, bn, training, save=save)
+                                  P[f"model.{idx}.bias"] if self.inst else None, bn, training, save=save,
+                                  packed=packs.get(f"l{idx}"))
             tape[f"l{idx}"] = sv
         out, sv = self.last.forward(a, P[f"model.{self.head}.weight"], P[f"model.{self.head}.bias"], save)
         tape["last"] = sv
