@@ -275,3 +275,65 @@ def test_distributed_gradient_average_gloo_world2(tmp_path):
                        capture_output=True, text=True, timeout=240)
     assert r.returncode == 0, r.stdout + r.stderr
     assert r.stdout.count("ok") == 2
+
+
+def test_gradient_accumulation_warmup_and_scheduler():
+    """gradient_accumulation g: the optimiser steps every g-th training_step on the mean of the g losses; warmup_steps: no
+    upper-level step before the lower level has taken them; a scheduler attached to a problem steps with its optimiser."""
+    torch.manual_seed(0)
+    w = Vec([1.0, -2.0, 0.5])
+    data = [torch.tensor([float(i + 1)] * 3, dtype=torch.float64) for i in range(4)]
+
+    class P(ImplicitProblem):
+        def training_step(self, batch):
+            return 0.5 * ((self.module() - batch) ** 2).sum()
+
+    opt = torch.optim.SGD(w.parameters(), lr=0.5)
+    sched = torch.optim.lr_scheduler.StepLR(opt, step_size=1, gamma=0.5)
+    p = P(name="p", module=w, optimizer=opt, scheduler=sched, train_data_loader=data, config=Config(gradient_accumulation=2))
+    eng = Engine(problems=[p], config=EngineConfig(train_iters=4, valid_step=0))
+    w0 = w.v.detach().clone()
+    eng.run()
+    g1 = 0.5 * ((w0 - data[0]) + (w0 - data[1]))                 # mean of two gradients at the same point
+    w1 = w0 - 0.5 * g1
+    g2 = 0.5 * ((w1 - data[2]) + (w1 - data[3]))
+    w2 = w1 - 0.25 * g2                                           # StepLR halved the rate after the first optimiser step
+    assert torch.allclose(w.v.detach(), w2, atol=1e-12) and p.count == 4
+    assert abs(opt.param_groups[0]["lr"] - 0.125) < 1e-12
+
+    lower, upper, *_ = quadratic_problems(unroll=1)
+    lower.warmup_steps = 3
+    eng = make_engine(lower, upper, train_iters=5, valid_step=0)
+    eng.run()
+    assert lower.count == 5 and upper.count == 2                  # upper steps only after lower steps 4 and 5
+
+
+def test_problem_state_dict_round_trip_and_batch_forms():
+    lower, upper, *_ = quadratic_problems()
+    eng = make_engine(lower, upper, train_iters=3, valid_step=0)
+    eng.run()
+    state = lower.state_dict()
+    assert state["count"] == 3 and "v" in state["module"]
+    fresh_l, fresh_u, *_ = quadratic_problems(seed=9)
+    make_engine(fresh_l, fresh_u, train_iters=1, valid_step=0)
+    fresh_l.load_state_dict(state)
+    assert torch.equal(fresh_l.module.v.detach(), lower.module.v.detach()) and fresh_l.count == 3
+
+    # training_step may return a tensor, a dict with "loss", or a tuple whose first entry is the loss; batches may be
+    # tensors, tuples or dicts (moved to the problem's device)
+    seen = []
+
+    class P(ImplicitProblem):
+        def training_step(self, batch):
+            seen.append(type(batch).__name__)
+            x = batch["x"] if isinstance(batch, dict) else (batch[0] if isinstance(batch, (tuple, list)) else batch)
+            loss = ((self.module() - x) ** 2).sum()
+            return {"loss": loss, "aux": 1} if isinstance(batch, dict) else ((loss, 2) if isinstance(batch, (tuple, list)) else loss)
+
+    m = Vec([0.0])
+    one = torch.ones(1, dtype=torch.float64)
+    p = P(name="p", module=m, optimizer=torch.optim.SGD(m.parameters(), lr=0.25),
+          train_data_loader=[one, (one, 0), {"x": one}], config=Config(), device=torch.device("cpu"))
+    Engine(problems=[p], config=EngineConfig(train_iters=3, valid_step=0)).run()
+    assert seen == ["Tensor", "tuple", "dict"]
+    assert torch.allclose(m.v.detach(), torch.tensor([1.0 - 0.5 ** 3], dtype=torch.float64))
