@@ -287,6 +287,87 @@ __global__ void __launch_bounds__(256) thin_scatter_kernel(TView in, const void*
   }
 }
 
+// Register-blocked thin_scatter (same idea as thin_gather_px_kernel): thread = (PXB output pixels of one row that share
+// their tap set, 8-channel group); a weight vector read from shared memory feeds PXB * 8 FMAs.
+template <typename T, int CI, int PXB>
+__global__ void __launch_bounds__(256) thin_scatter_px_kernel(TView in, const void* __restrict__ wp, int wdtype,
+                                                             const float* __restrict__ bias, TView out, int mode, int KH, int KW,
+                                                             int stride, int pad, int act) {
+  GSB_PDL_ENTRY();
+  extern __shared__ float sw[];  // [taps][CI][Cout]
+  const int Cout = out.C, taps = KH * KW;
+  for (int i = threadIdx.x; i < taps * CI * Cout; i += blockDim.x) {
+    const int c = i % Cout, ci = (i / Cout) % CI, t = i / (Cout * CI);
+    sw[i] = ci < in.C ? wload(wp, wdtype, ((int64_t)t * Cout + c) * in.C + ci) : 0.f;
+  }
+  __syncthreads();
+  const bool conv = mode == GSB_MODE_CONV;
+  const int spacing = conv ? 1 : stride, xstep = conv ? stride : 1;
+  const unsigned G = (unsigned)Cout >> 3;
+  const unsigned wq = ((unsigned)out.W + spacing - 1) / spacing, XB = (wq + PXB - 1) / PXB;
+  const unsigned total = (unsigned)out.N * out.H * spacing * XB * G;
+  T* op = reinterpret_cast<T*>(out.ptr);
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const unsigned it = i / G, g = i - it * G;
+    const unsigned xb = it % XB;
+    unsigned r = it / XB;
+    const int ph = (int)(r % (unsigned)spacing);
+    r /= (unsigned)spacing;
+    const int oy = (int)(r % (unsigned)out.H), n = (int)(r / (unsigned)out.H);
+    const int ox0 = ph + spacing * (int)(xb * PXB);
+    if (ox0 >= out.W) continue;
+    float acc[PXB][8];
+#pragma unroll
+    for (int j = 0; j < PXB; ++j)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[j][e] = bias ? bias[g * 8 + e] : 0.f;
+    int ky0, kys, kx0, kxs;
+    tap_range(mode, oy, stride, pad, ky0, kys);
+    tap_range(mode, ox0, stride, pad, kx0, kxs);
+    for (int ky = ky0; ky < KH; ky += kys) {
+      int iy;
+      if (!tap_src(mode, oy, ky, stride, pad, in.H, iy)) continue;
+      const int64_t rbase = (int64_t)n * in.sn + (int64_t)iy * in.sh;
+      for (int kx = kx0; kx < KW; kx += kxs) {
+        const int ixb = conv ? ox0 * stride - pad + kx : (ox0 + pad - kx) / stride;   // exact for the transposed form
+        const float* wt = sw + (ky * KW + kx) * CI * Cout + g * 8;
+#pragma unroll
+        for (int ci = 0; ci < CI; ++ci) {
+          if (ci < in.C) {
+            float v[PXB];
+            bool any = false;
+#pragma unroll
+            for (int j = 0; j < PXB; ++j) {
+              const int ix = ixb + j * xstep;
+              const bool ok = (ox0 + j * spacing < out.W) && ix >= 0 && ix < in.W;
+              v[j] = ok ? ld_elem(in.ptr, rbase + (int64_t)ix * in.sw + (int64_t)ci * in.sc, in.dtype) : 0.f;
+              any |= ok;
+            }
+            if (!any) continue;
+            const float4 w0 = *reinterpret_cast<const float4*>(wt + ci * Cout);
+            const float4 w1 = *reinterpret_cast<const float4*>(wt + ci * Cout + 4);
+#pragma unroll
+            for (int j = 0; j < PXB; ++j) {
+              acc[j][0] = fmaf(v[j], w0.x, acc[j][0]); acc[j][1] = fmaf(v[j], w0.y, acc[j][1]);
+              acc[j][2] = fmaf(v[j], w0.z, acc[j][2]); acc[j][3] = fmaf(v[j], w0.w, acc[j][3]);
+              acc[j][4] = fmaf(v[j], w1.x, acc[j][4]); acc[j][5] = fmaf(v[j], w1.y, acc[j][5]);
+              acc[j][6] = fmaf(v[j], w1.z, acc[j][6]); acc[j][7] = fmaf(v[j], w1.w, acc[j][7]);
+            }
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < PXB; ++j) {
+      const int ox = ox0 + j * spacing;
+      if (ox >= out.W) continue;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[j][e] = act_fwd(acc[j][e], act);
+      Vec8<T>::store(op + (int64_t)n * out.sn + (int64_t)oy * out.sh + (int64_t)ox * out.sw + g * 8, acc[j]);
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // thin_wgrad: dwp[tap][co][ci] += sum over pixels of dout[q][co] * in[p][ci],  CO = dout.C <= 4 (dwp is [taps][CO][Cin]).
 // Thread = (pixel lane over the WIDE tensor `in`, 8-channel group); TP taps of one kernel row band per pass
@@ -437,8 +518,29 @@ int thin_gather_try(const gsb_view* in, const void* wp, int wdtype, const float*
     if (smem > 96 * 1024) return 0;
     const int64_t total = P * (out->c / 8);
     if (total >= ((int64_t)1 << 31)) return 0;
-    const int grid = grid_sm((total + 255) / 256, 8);
     TView vi = tv(in), vo = tv(out);
+    static const bool spx_on = []() { const char* e = getenv("GSB_THIN_SPX"); return !(e && e[0] == '0'); }();   // on by default (validated r01s)
+    if (spx_on) {
+      constexpr int PXB = 4;
+      const int spacing = g->mode == GSB_MODE_CONV ? 1 : g->stride;
+      const int64_t wq = (out->w + spacing - 1) / spacing, xb = (wq + PXB - 1) / PXB;
+      const int64_t ptotal = (int64_t)out->n * out->h * spacing * xb * (out->c / 8);
+      const int pgrid = grid_sm((ptotal + 255) / 256, 8);
+#define GSB_THIN_SP(T, C)                                                                                             \
+  do {                                                                                                                \
+    cudaFuncSetAttribute(thin_scatter_px_kernel<T, C, PXB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);  \
+    gsb::launch(thin_scatter_px_kernel<T, C, PXB>, gsb::LaunchCfg(pgrid, 256, smem, st), vi, wp, wdtype, bias, vo, g->mode, g->kh, g->kw, \
+                g->stride, g->pad, act);                                                                              \
+  } while (0)
+      if (out->dtype == GSB_BF16) {
+        if (CI == 1) GSB_THIN_SP(__nv_bfloat16, 1); else if (CI == 2) GSB_THIN_SP(__nv_bfloat16, 2); else GSB_THIN_SP(__nv_bfloat16, 4);
+      } else {
+        if (CI == 1) GSB_THIN_SP(float, 1); else if (CI == 2) GSB_THIN_SP(float, 2); else GSB_THIN_SP(float, 4);
+      }
+#undef GSB_THIN_SP
+      return check_launch("thin_scatter_px") ? -1 : 1;
+    }
+    const int grid = grid_sm((total + 255) / 256, 8);
 #define GSB_THIN_S(T, C)                                                                                              \
   do {                                                                                                                \
     cudaFuncSetAttribute(thin_scatter_kernel<T, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);          \
