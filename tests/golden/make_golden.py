@@ -2,7 +2,9 @@
 
 Run in the build container only (needs /root/reference, read-only):
 
-    PYTHONDONTWRITEBYTECODE=1 python tests/golden/make_golden.py
+    PYTHONDONTWRITEBYTECODE=1 python tests/golden/make_golden.py            # U-Net, Dice KATs, unet_256 Pix2Pix cases
+    PYTHONDONTWRITEBYTECODE=1 python tests/golden/make_golden.py instance   # --norm instance --gan_mode lsgan
+    PYTHONDONTWRITEBYTECODE=1 python tests/golden/make_golden.py variants   # --netG unet_128, --netD n_layers (2 / 4)
 
 The reference ships no tests or golden vectors, so parity is pinned on outputs of
 the reference itself, on seeded weights/inputs from oracle.genseg_oracle
