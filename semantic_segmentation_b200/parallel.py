@@ -135,6 +135,17 @@ def allreduce_gradients(params: Iterable[torch.Tensor]) -> None:
         torch._foreach_copy_(gs, [c.view_as(g) for c, g in zip(flat.split([g.numel() for g in gs]), gs)])
 
 
+def mean_over_ranks(total, count: int) -> torch.Tensor:
+    """Evaluation is "replicas only" (SURVEY 8e): every rank scores its own batches and the ranks only exchange two numbers,
+    the sum of the per-batch Dice scores and the number of batches.  Returns sum(total) / sum(count) over the ranks."""
+    t = torch.as_tensor(total, dtype=torch.float64).detach().reshape(())
+    if _GROUP["world"] <= 1:
+        return (t / max(int(count), 1)).float()
+    pair = torch.stack([t.to(torch.float64), torch.tensor(float(count), dtype=torch.float64, device=t.device)])
+    dist.all_reduce(pair, op=dist.ReduceOp.SUM, group=_GROUP["pg"])
+    return (pair[0] / pair[1].clamp_min(1.0)).float()
+
+
 def broadcast_parameters(module: torch.nn.Module, src: int = 0) -> None:
     if _GROUP["world"] <= 1:
         return

@@ -24,13 +24,22 @@ def predict_counts(net, image: torch.Tensor, mask_true: torch.Tensor):
     return ops.eval_counts(logits.float().contiguous(), labels.contiguous())
 
 
-def evaluate(net, dataloader, device, amp):
+def evaluate(net, dataloader, device, amp, sharded=False):
+    """``sharded=True`` (an addition; default = the reference's behaviour): under ``parallel.init_data_parallel`` rank r
+    scores the batches i with i % world == r and the ranks exchange (sum of scores, number of batches) -- every rank
+    returns the same value as one process scoring all batches."""
+    from .. import parallel
+    world, rank = (parallel.world_size(), parallel.rank()) if sharded else (1, 0)
     net.eval()
     num_val_batches = len(dataloader)
     dice_score = 0
+    scored = 0
     # `amp` only selected fp16 autocast for the reference's cuDNN forward (evaluate.py:16); our forward
     # always computes in the engine's precision (bf16 with fp32 accumulation by default).
     for i, batch in enumerate(dataloader):
+        if i % world != rank:
+            continue
+        scored += 1
         image, mask_true = batch['image'], batch['mask']
         image = image.to(device=device, dtype=torch.float32)
         mask_true = mask_true.to(device=device, dtype=torch.long)
@@ -42,4 +51,6 @@ def evaluate(net, dataloader, device, amp):
         counts, _ = predict_counts(net, image, mask_true)
         dice_score += dice_from_counts(counts)
     net.train()
+    if sharded and world > 1:
+        return parallel.mean_over_ranks(dice_score, scored)
     return dice_score / max(num_val_batches, 1)

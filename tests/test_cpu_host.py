@@ -118,6 +118,8 @@ with torch.no_grad():
     m.weight.fill_(float(r))
 parallel.broadcast_parameters(m)
 assert float(m.weight.sum()) == 0.0
+# evaluation is "replicas only": ranks exchange (sum of per-batch Dice, number of batches)
+assert abs(float(parallel.mean_over_ranks(torch.tensor(float(r + 1)), 2 + r)) - 3.0 / 5.0) < 1e-7
 parallel.shutdown()
 # --- gradient all-reduce inside backward (bucketed, first bucket asynchronous) -- host logic over gloo
 world = parallel.init_data_parallel(sync_bn=True, backend="gloo", overlap_grad_allreduce=True)

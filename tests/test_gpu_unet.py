@@ -175,6 +175,8 @@ def test_evaluate_matches_reference(case, golden_dir):
     try:
         with torch.no_grad():
             d = evaluate(net, [dict(image=x, mask=y)], torch.device(DEV), False)
+            d_sharded = evaluate(net, [dict(image=x, mask=y)], torch.device(DEV), False, sharded=True)
+        assert float(d) == float(d_sharded)   # one process: the sharded form scores every batch itself
         assert net.training          # evaluate() leaves the net in train mode like the reference (:42)
         # masks from OUR logits vs oracle counts on OUR logits: bit exact; Dice vs reference's: close
         net.eval()
