@@ -197,7 +197,6 @@ def committed_traffic(per_gpu_batch: int):
 
 def run_ours(args):
     import semantic_segmentation_b200 as S
-    from oracle import genseg_oracle as O
     from semantic_segmentation_b200 import _lib, parallel
     from semantic_segmentation_b200.optim import RMSprop
     from semantic_segmentation_b200.unet import UNet
@@ -215,12 +214,14 @@ def run_ours(args):
     if GLOBAL_BATCH % world != 0:
         raise SystemExit("global batch 64 must be divisible by the number of GPUs")
     per = args.per_gpu_batch or GLOBAL_BATCH // world
+    torch.manual_seed(1234)              # the reference's default initialisation (SURVEY 8c Protocol A), same on every rank
     net = UNet(1, N_CLASSES, True)
-    net.load_state_dict(O.seeded_state(O.unet_state_spec(1, N_CLASSES, True), 1234))
     net = net.to(dev).train()
     params = list(net.parameters())
     opt = RMSprop(params, lr=1e-4, weight_decay=1e-8, momentum=0.9)
-    opt.grad_scale = 1.0 / world
+    # seg_loss is a mean over the GLOBAL batch (CE count and Dice sums are all-reduced), so the SUM of the ranks' gradients
+    # is already the full-batch gradient: no 1/world here (that is for per-rank-mean losses such as GANLoss / L1)
+    opt.grad_scale = 1.0
     xg, yg = synthetic_batch(per * world)
     lo, hi = rank * per, (rank + 1) * per
     x_host, y_host = xg[lo:hi].contiguous().pin_memory(), yg[lo:hi].contiguous().pin_memory()

@@ -113,7 +113,10 @@ def shard_batch(n_global: int, rank_: Optional[int] = None, world: Optional[int]
 
 
 def allreduce_gradients(params: Iterable[torch.Tensor]) -> None:
-    """Sum gradients over ranks (averaging is folded into the optimiser's grad_scale = 1/world)."""
+    """Sum gradients over ranks.  Whether the optimiser must then divide depends on the loss: ``seg_loss`` under
+    init_data_parallel is a mean over the GLOBAL batch (its CE count and Dice sums are all-reduced), so the sum of the
+    ranks' gradients already is the full-batch gradient (``grad_scale = 1``); per-rank-mean losses (GANLoss, l1_loss)
+    need ``optimizer.grad_scale = 1 / world``."""
     if _GROUP["world"] <= 1:
         return
     grads = []
@@ -141,7 +144,10 @@ def mean_over_ranks(total, count: int) -> torch.Tensor:
     t = torch.as_tensor(total, dtype=torch.float64).detach().reshape(())
     if _GROUP["world"] <= 1:
         return (t / max(int(count), 1)).float()
-    pair = torch.stack([t.to(torch.float64), torch.tensor(float(count), dtype=torch.float64, device=t.device)])
+    if dist.get_backend(_GROUP["pg"]) == "nccl" and not t.is_cuda:
+        # a rank that scored no batch holds the Python number 0: the collective still needs a tensor on this rank's GPU
+        t = t.to(torch.device("cuda", torch.cuda.current_device()))
+    pair = torch.stack([t, torch.tensor(float(count), dtype=torch.float64, device=t.device)])
     dist.all_reduce(pair, op=dist.ReduceOp.SUM, group=_GROUP["pg"])
     return (pair[0] / pair[1].clamp_min(1.0)).float()
 

@@ -17,23 +17,31 @@ class _DiceCoeff(torch.autograd.Function):
         b = tgt.contiguous().float()
         sums = ops.dice_sums(a, b, slices, inner)            # [slices, 3] fp64: sum a*b, sum a, sum b
         inter = (2.0 * sums[:, 0]).float()
-        sets = (sums[:, 1] + sums[:, 2]).float()
-        sets = torch.where(sets == 0, inter, sets)
+        raw = (sums[:, 1] + sums[:, 2]).float()
+        empty = raw == 0                                     # util/dice_score.py:14: sets_sum[sets_sum == 0] = inter
+        sets = torch.where(empty, inter, raw)
         dice = (inter + epsilon) / (sets + epsilon)
-        ctx.save_for_backward(b, inter, sets)
-        ctx.meta = (slices, inner, epsilon, inp.shape, inp.dtype, bool((sums[:, 1] + sums[:, 2] == 0).any()))
-        return dice.mean()
+        ctx.save_for_backward(a, b, inter, sets, empty)
+        ctx.meta = (slices, inner, epsilon, inp.shape, inp.dtype, tgt.shape, tgt.dtype)
+        return dice.mean()                                   # no host synchronisation: graph-capturable
 
     @staticmethod
     def backward(ctx, g):
-        b, inter, sets = ctx.saved_tensors
-        slices, inner, eps, shape, dtype, _ = ctx.meta
-        # d dice_s / d a = (2 b (S+eps) - (2I+eps)) / (S+eps)^2   (S, I per slice)
+        a, b, inter, sets, empty = ctx.saved_tensors
+        slices, inner, eps, shape, dtype, tshape, tdtype = ctx.meta
+        # dice_s = (2I+eps)/(S+eps), I = sum a*b, S = sum a + sum b:
+        #   d dice_s / d a = (2 b (S+eps) - (2I+eps)) / (S+eps)^2, and symmetrically for b.
+        # An empty slice (S == 0) has dice_s = (2I+eps)/(2I+eps) == 1 identically: zero gradient, like the reference's graph.
         den = (sets + eps)
-        ca = (2.0 / den) * (g / slices)
-        cb = ((inter + eps) / (den * den)) * (g / slices)
-        d = b.view(slices, inner) * ca[:, None] - cb[:, None]
-        return d.view(shape).to(dtype), None, None, None, None
+        keep = (~empty).to(den.dtype)
+        ca = (2.0 / den) * (g / slices) * keep
+        cb = ((inter + eps) / (den * den)) * (g / slices) * keep
+        da = db = None
+        if ctx.needs_input_grad[0]:
+            da = (b.view(slices, inner) * ca[:, None] - cb[:, None]).view(shape).to(dtype)
+        if ctx.needs_input_grad[1] and tdtype.is_floating_point:
+            db = (a.view(slices, inner) * ca[:, None] - cb[:, None]).view(tshape).to(tdtype)
+        return da, db, None, None, None
 
 
 def dice_coeff(input: Tensor, target: Tensor, reduce_batch_first: bool = False, epsilon: float = 1e-6):

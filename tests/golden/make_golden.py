@@ -256,7 +256,7 @@ def pix2pix_instance_case(name="pix2pix_instance", batch=2):
     out["gradG:model.model.0.weight"] = gG["model.model.0.weight"].numpy()
     out["gradG:outer_w4"] = gG["model.model.3._ops._ops.0.op.weight"].numpy()
     out["gradD:model.0.weight"] = gD["model.0.weight"].numpy()
-    out["gradD:model.11.weight"] = gD["model.%d.weight" % (2 + 3 * n_layers)].numpy()      # the 1-channel head
+    out["gradD:model.11.weight"] = gD["model.11.weight"].numpy()      # the 1-channel head of the 'basic' (n_layers 3) net
     np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
     print(name, "loss_D", loss_D.item(), "G_GAN", g_gan.item(), "G_L1", g_l1.item())
 

@@ -135,6 +135,59 @@ def test_conv_tcgen05_tile_shapes(geom, tile):
         assert res["stats"] < 1e-5, res
 
 
+# Every tensor-core convolution of the bench step (BASELINE config 2: UNet(1,2,bilinear) at 256x256), at the per-GPU batch
+# of 1 rank (64 images) and of 8 ranks (8 images): the shapes whose kernel variants (BN=256 cluster path, 64-column tiles,
+# one-tile-per-CTA launches, split-K weight gradients) the bench actually times.
+PROD_LAYERS = [  # cin, cout, hw
+    (64, 64, 256), (128, 64, 256), (64, 128, 128), (128, 128, 128), (256, 128, 128), (128, 64, 128),
+    (128, 256, 64), (256, 256, 64), (512, 256, 64), (256, 128, 64), (256, 512, 32), (512, 512, 32), (1024, 512, 32),
+    (512, 256, 32), (512, 512, 16),
+]
+
+
+def _rel_dev(a: torch.Tensor, b_cpu: torch.Tensor) -> float:
+    b = b_cpu.to(DEV)
+    num = (a.float() - b).double().square().sum()
+    return float((num / b.double().square().sum().clamp_min(1e-300)).sqrt())
+
+
+@pytest.mark.parametrize("batch", [64, 8])
+@pytest.mark.parametrize("layer", PROD_LAYERS, ids=["%dto%d_%d" % l for l in PROD_LAYERS])
+def test_conv_tcgen05_production_shapes(layer, batch):
+    """fprop / dgrad / wgrad of one 3x3 layer at its production shape against torch's CPU fp32 convolution on the same
+    bf16-representable operands: <= 6e-3 (bf16 rounding of the stored output; north_star per-layer bound 1e-2) for the
+    activations and input gradients, <= 1e-4 for the fp32 weight gradient; the fused BatchNorm statistics of the
+    epilogue <= 1e-5."""
+    cin, cout, hw = layer
+    g = torch.Generator().manual_seed(cin * 7 + cout * 3 + hw + batch)
+    x = torch.randn(batch, cin, hw, hw, generator=g).bfloat16().float()
+    wt = (torch.randn(cout, cin, 3, 3, generator=g) / math.sqrt(cin * 9)).bfloat16().float()
+    dy = torch.randn(batch, cout, hw, hw, generator=g).bfloat16().float()
+    x.requires_grad_(True)
+    wt.requires_grad_(True)
+    y = F.conv2d(x, wt, None, padding=1)
+    y.backward(dy)
+    xd = nhwc(x.detach(), torch.bfloat16)
+    dyd = nhwc(dy, torch.bfloat16)
+    wd = wt.detach().to(DEV)
+    wp, wpb = ops.pack_weight(wd, True, torch.bfloat16), ops.pack_weight(wd, False, torch.bfloat16)
+    yd = torch.empty((batch, hw, hw, cout), device=DEV, dtype=torch.bfloat16)
+    stats, rows = ops.conv_gather(view_nhwc(xd), wp, None, view_nhwc(yd), MODE_CONV, 3, 1, 1, use_tc=1, want_stats=True)
+    dxd = torch.empty_like(xd)
+    ops.conv_gather(view_nhwc(dyd), wpb, None, view_nhwc(dxd), MODE_CONVT, 3, 1, 1, use_tc=1)
+    dwp = torch.zeros((9, cout, cin), device=DEV, dtype=torch.float32)
+    ops.conv_wgrad_into(view_nhwc(xd), view_nhwc(dyd), dwp, MODE_CONV, 3, 1, 1, use_tc=1)
+    dw = ops.unpack_wgrad(dwp, (cout, cin, 3, 3), True)
+    torch.cuda.synchronize()
+    res = dict(fwd=_rel_dev(yd.permute(0, 3, 1, 2), y.detach()), dgrad=_rel_dev(dxd.permute(0, 3, 1, 2), x.grad),
+               wgrad=_rel_dev(dw, wt.grad))
+    sums = ops.bn_reduce_partials(stats, rows, cout)
+    yq = yd.double()
+    res["stats"] = rel(sums, torch.cat([yq.sum((0, 1, 2)), (yq * yq).sum((0, 1, 2))]))
+    print(layer, batch, res)
+    assert res["fwd"] < 6e-3 and res["dgrad"] < 6e-3 and res["wgrad"] < 1e-4 and res["stats"] < 1e-5, res
+
+
 def test_edge_strided_views_direct():
     """NCHW fp32 network edges (Cin=1 input, Cout=2 output with bias+tanh) through the SIMT kernel."""
     g = torch.Generator().manual_seed(3)

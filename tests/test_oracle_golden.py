@@ -158,3 +158,53 @@ def test_merged_upconv_equals_mixed():
     W, b = O.merged_upconv_weight(st, "c", alpha, bias=True)
     out = F.conv_transpose2d(x, W, b, stride=2, padding=3)
     assert (ref - out).abs().max().item() < 1e-12
+
+
+def _protocol_a_state():
+    """SURVEY 8c Protocol A: the reference's default initialisation under torch.manual_seed(1234), drawn through plain
+    torch.nn containers in the reference's construction order (what both UNet classes do)."""
+    from semantic_segmentation_b200.unet import UNet           # parameter containers only: no CUDA needed to construct
+    torch.manual_seed(1234)
+    return {k: v.clone() for k, v in UNet(1, 2, True).state_dict().items()}
+
+
+def test_oracle_on_protocol_a(golden_dir):
+    """BASELINE config 1 (UNet(1,2,bilinear) on 4x1x256x256): the oracle against the reference's own run -- logits mean
+    0.155573, CE 0.724931, the bit-exact counts 108265 / 53905 / 239025, every convolution output and a sample of every
+    parameter gradient."""
+    gold = np.load(os.path.join(golden_dir, "unet_protocol_a.npz"))
+    st = _protocol_a_state()
+    keys = [str(k) for k in gold["state_keys"]]
+    np.testing.assert_allclose([st[k].double().sum().item() for k in keys], gold["state_sums"], rtol=0, atol=1e-9)
+    g = torch.Generator().manual_seed(4321)
+    x = torch.rand(4, 1, 256, 256, generator=g)
+    y = torch.randint(0, 2, (4, 256, 256), generator=g)
+    params = {k: v.clone().requires_grad_(True) for k, v in st.items() if v.dtype.is_floating_point and "running" not in k}
+    work = dict(st)
+    work.update(params)
+    taps = {}
+    logits = O.unet_forward(work, x, True, training=True, taps=taps)
+    loss, ce, dl = O.seg_loss(logits, y)
+    loss.backward()
+    assert rel_l2(logits.detach(), gold["logits"]) < 1e-5
+    assert abs(logits.mean().item() - 0.155573) < 1e-6 and abs(ce.item() - 0.724931) < 1e-6
+    assert abs(dl.item() - 0.500099) < 1e-6
+    c = O.eval_counts(gold["logits"], y.numpy())
+    assert (int(c["psum"].sum()), int(c["inter"].sum()), int(c["psum"].sum() + c["tsum"].sum())) == (108265, 53905, 239025)
+
+    def take(t):
+        f = t.detach().reshape(-1)
+        s = max(1, f.numel() // 2048)
+        return f[::(s | 1 if s > 1 else 1)]
+
+    for k in gold["tap_keys"]:
+        k = str(k)
+        if k == "outc.conv":
+            continue
+        assert rel_l2(take(taps[k]), gold["tap:" + k]) < 1e-5, k
+    # gradients: within 3x of the reference's own fp32-vs-fp64 distance (ReLU-branch flips), floor 1e-5
+    for k in gold["grad_keys"]:
+        k = str(k)
+        e = rel_l2(take(params[k].grad), gold["grad64:" + k])
+        e_ref = rel_l2(gold["grad:" + k], gold["grad64:" + k])
+        assert e <= max(3 * e_ref, 1e-5), (k, e, e_ref)
