@@ -7,6 +7,7 @@
 // Algorithmic bytes: reduce = 1 read; act = 1 read + 1 (or 2) writes; bwd_reduce = 2 (3) reads;
 // bwd_apply = 2 (3) reads + 1 write -- at the storage dtype.
 #include <stdlib.h>
+#include <type_traits>
 #include "common.cuh"
 #include "peer.cuh"
 
@@ -76,14 +77,21 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
     int act2, uint64_t drop_seed, const uint8_t* __restrict__ drop_mask, float* __restrict__ partial) {
   GSB_PDL_ENTRY();
   constexpr int KU = MODE == 1 ? kUnrollBwd : kUnroll;
-  extern __shared__ float red[];  // [lanes][2][C]
+  // fp32 validation mode: fp64 accumulation, and every block writes TWO partial rows (hi, lo = the fp64 sum split into two
+  // floats) which the fp64 second stage adds back together.  sum x^2 - (sum x)^2 / n cancels badly when a channel's mean
+  // dominates its spread (BatchNorm over the 8..32 samples of the generator's deep levels): fp32 partial sums put the
+  // whole network 1e-4 away from the reference there, fp64 ones 1e-6 (torch's CPU kernel is two-pass).
+  constexpr bool WIDE = std::is_same<T, float>::value;
+  using Acc = typename std::conditional<WIDE, double, float>::type;
+  extern __shared__ double red_raw[];
+  Acc* red = reinterpret_cast<Acc*>(red_raw);  // [lanes][2][C]
   const int G = C >> 3;
   const int lanes = kThreads / G;
   const int g = threadIdx.x % G, lane = threadIdx.x / G;
   const int c0 = g * 8;
-  float s0[8], s1[8];
+  Acc s0[8], s1[8];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) s0[i] = s1[i] = 0.f;
+  for (int i = 0; i < 8; ++i) s0[i] = s1[i] = (Acc)0;
   float sc[8], sh[8], mu[8], is[8];
   if (MODE == 1) {
     load_param8(scale, c0, sc, 1.f);
@@ -113,8 +121,8 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
       if (MODE == 0) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          s0[i] += v[u][i];
-          s1[i] = fmaf(v[u][i], v[u][i], s1[i]);
+          s0[i] += (Acc)v[u][i];
+          s1[i] += (Acc)v[u][i] * (Acc)v[u][i];
         }
       } else {
         uint32_t keep = has_drop ? keep_bits(drop_seed, drop_mask, p, C, c0) : 0xFFu;
@@ -125,8 +133,8 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
           float dy = a[u][i] * dm * act_grad(z * dm, act1);
           if (two) dy += b[u][i] * act_grad(z, act2);
           float xh = (v[u][i] - mu[i]) * is[i];
-          s0[i] += dy;
-          s1[i] = fmaf(dy, xh, s1[i]);
+          s0[i] += (Acc)dy;
+          s1[i] += (Acc)dy * (Acc)xh;
         }
       }
     }
@@ -138,9 +146,15 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
   }
   __syncthreads();
   for (int j = threadIdx.x; j < 2 * C; j += kThreads) {
-    float acc = 0.f;
+    Acc acc = (Acc)0;
     for (int l = 0; l < lanes; ++l) acc += red[l * 2 * C + j];
-    partial[(int64_t)blockIdx.x * 2 * C + j] = acc;
+    if (WIDE) {
+      const float hi = (float)acc;
+      partial[((int64_t)blockIdx.x * 2) * 2 * C + j] = hi;
+      partial[((int64_t)blockIdx.x * 2 + 1) * 2 * C + j] = (float)((double)acc - (double)hi);
+    } else {
+      partial[(int64_t)blockIdx.x * 2 * C + j] = (float)acc;
+    }
   }
 }
 
@@ -553,7 +567,7 @@ static PixView pv(const gsb_view* v) { return v ? PixView{v->ptr, v->sw} : PixVi
 using namespace gsb;
 
 extern "C" size_t gsb_bn_workspace_bytes(const gsb_view* x) {
-  return (size_t)num_sms() * 8 * 2 * (size_t)x->c * sizeof(float);
+  return (size_t)num_sms() * 8 * 2 * 2 * (size_t)x->c * sizeof(float);   // fp32 views write two rows (hi, lo) per block
 }
 
 extern "C" int gsb_bn_reduce(const gsb_view* x, double* sums, void* workspace, size_t workspace_bytes, gsb_stream s) {
@@ -561,10 +575,13 @@ extern "C" int gsb_bn_reduce(const gsb_view* x, double* sums, void* workspace, s
   const int C = x->c, lanes = kThreads / (C / 8);
   const int64_t P = num_pixels(x);
   int grid = grid_for(P, lanes);
-  GSB_REQUIRE(workspace_bytes >= (size_t)grid * 2 * C * sizeof(float), "bn_reduce: workspace too small");
-  size_t smem = (size_t)lanes * 2 * C * sizeof(float);
+  const int wide = x->dtype == GSB_BF16 ? 1 : 2;
+  GSB_REQUIRE(workspace_bytes >= (size_t)grid * wide * 2 * C * sizeof(float), "bn_reduce: workspace too small");
+  size_t smem = (size_t)lanes * 2 * C * sizeof(float) * wide;
   float* partial = reinterpret_cast<float*>(workspace);
   PixView nul{nullptr, 0};
+  if (smem > 48 * 1024)
+    cudaFuncSetAttribute(bn_reduce_kernel<float, 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (x->dtype == GSB_BF16)
     gsb::launch(bn_reduce_kernel<__nv_bfloat16, 0, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), nul, nul, P, C, nullptr, nullptr,
                                                                                      nullptr, nullptr, 0, 0, 0, nullptr, partial);
@@ -572,7 +589,7 @@ extern "C" int gsb_bn_reduce(const gsb_view* x, double* sums, void* workspace, s
     gsb::launch(bn_reduce_kernel<float, 0, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), nul, nul, P, C, nullptr, nullptr, nullptr,
                                                                              nullptr, 0, 0, 0, nullptr, partial);
   int n = 2 * C;
-  gsb::launch(reduce_partials_kernel, gsb::LaunchCfg((n + 31) / 32, 1024, 0, to_stream(s)), partial, grid, n, sums);
+  gsb::launch(reduce_partials_kernel, gsb::LaunchCfg((n + 31) / 32, 1024, 0, to_stream(s)), partial, grid * wide, n, sums);
   return check_launch("bn_reduce", 2);
 }
 
@@ -638,8 +655,11 @@ static int bn_bwd_partial_launch(const gsb_view* x, const gsb_view* dA1, const g
   const int C = x->c, lanes = kThreads / (C / 8);
   const int64_t P = num_pixels(x);
   int grid = grid_for(P, lanes);
-  GSB_REQUIRE(workspace_bytes >= (size_t)grid * 2 * C * sizeof(float), "bn_bwd_reduce: workspace too small");
-  size_t smem = (size_t)lanes * 2 * C * sizeof(float);
+  const int wide = x->dtype == GSB_BF16 ? 1 : 2;
+  GSB_REQUIRE(workspace_bytes >= (size_t)grid * wide * 2 * C * sizeof(float), "bn_bwd_reduce: workspace too small");
+  size_t smem = (size_t)lanes * 2 * C * sizeof(float) * wide;
+  if (smem > 48 * 1024)
+    cudaFuncSetAttribute(bn_reduce_kernel<float, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   float* partial = reinterpret_cast<float*>(workspace);
   PixView d2 = (dA2 && dA2->ptr) ? pv(dA2) : PixView{nullptr, 0};
   const bool fast = act1 == GSB_ACT_RELU && d2.ptr == nullptr && drop_seed == 0 && drop_mask == nullptr && scale && shift &&
@@ -658,7 +678,7 @@ static int bn_bwd_partial_launch(const gsb_view* x, const gsb_view* dA1, const g
     gsb::launch(bn_reduce_kernel<float, 1, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), pv(dA1), d2, P, C, scale, shift, mean,
                                                                              invstd, act1, act2, drop_seed, drop_mask, partial);
   }
-  *rows_out = grid;
+  *rows_out = grid * wide;
   return 0;
 }
 
