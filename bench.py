@@ -165,13 +165,14 @@ def _conv_pass_tflops(b, cin, cout, hw):
     wp, wpb = ops.pack_weight(w, True, torch.bfloat16), ops.pack_weight(w, False, torch.bfloat16)
     y = torch.empty(b, hw, hw, cout, device=dev, dtype=torch.bfloat16)
     dx = torch.empty_like(x)
-    dwp = torch.zeros(9, cout, cin, device=dev, dtype=torch.float32)
     xv, yv, dxv = view_nhwc(x), view_nhwc(y), view_nhwc(dx)
+    nsl = ops.conv_wgrad_plan(xv, yv, MODE_CONV, 3, 1, 1, use_tc=1)     # partial-sum slices (no atomics), see DESIGN.md
+    dws = torch.empty(nsl, 9, cout, cin, device=dev, dtype=torch.float32)
     flops = 2.0 * b * hw * hw * 9 * cin * cout
     out = {}
     out["fprop"] = flops / time_kernel(lambda: ops.conv_gather(xv, wp, None, yv, MODE_CONV, 3, 1, 1, use_tc=1, want_stats=True))
     out["dgrad"] = flops / time_kernel(lambda: ops.conv_gather(yv, wpb, None, dxv, MODE_CONVT, 3, 1, 1, use_tc=1))
-    out["wgrad"] = flops / time_kernel(lambda: ops.conv_wgrad_into(xv, yv, dwp, MODE_CONV, 3, 1, 1, use_tc=1))
+    out["wgrad"] = flops / time_kernel(lambda: ops.conv_wgrad_slices(xv, yv, dws, nsl, MODE_CONV, 3, 1, 1, use_tc=1))
     return {k: v / 1e12 for k, v in out.items()}, flops
 
 

@@ -61,15 +61,18 @@ int gsb_copy_view(const gsb_view* src, const gsb_view* dst, gsb_stream s);
  * operations.py:18).  rows_from_d0 != 0 -> rows = d0, cols = d1; else rows = d1, cols = d0. */
 int gsb_pack_weight(const float* src, int d0, int d1, int kh, int kw, int rows_from_d0, void* dst,
                     int dst_dtype, gsb_stream s);
-/* Inverse for gradients: dWp fp32 [tap][rows][cols] -> torch layout fp32 [d0][d1][kh][kw];
- * accumulate != 0 adds into dst. */
-int gsb_unpack_wgrad(const float* src, int d0, int d1, int kh, int kw, int rows_from_d0, float* dst,
+/* Inverse for gradients: dWp fp32 [nslices][tap][rows][cols] (partial-sum slices written by gsb_conv_wgrad, added here in
+ * slice order) -> torch layout fp32 [d0][d1][kh][kw]; accumulate != 0 adds into dst. */
+int gsb_unpack_wgrad(const float* src, int nslices, int d0, int d1, int kh, int kw, int rows_from_d0, float* dst,
                      int accumulate, gsb_stream s);
 /* Batched forms of the two calls above: n (layer) jobs in one launch; taps = kh*kw; host arrays. */
 int gsb_pack_weight_multi(int n, const void* const* src, void* const* dst, const int* d0, const int* d1, const int* taps,
                           const int* rows_from_d0, int dst_dtype, gsb_stream s);
-int gsb_unpack_wgrad_multi(int n, const void* const* src, void* const* dst, const int* d0, const int* d1, const int* taps,
-                           const int* rows_from_d0, int accumulate, gsb_stream s);
+int gsb_unpack_wgrad_multi(int n, const void* const* src, const int* nslices, void* const* dst, const int* d0, const int* d1,
+                           const int* taps, const int* rows_from_d0, int accumulate, gsb_stream s);
+/* dst[i] (+)= sum over s < nslices of ws[s * n + i], slice order, fp64 accumulation: the deterministic second stage of the
+ * split reductions (no atomics anywhere in the library: two runs of a step give the same bits). */
+int gsb_sum_slices(const float* ws, int nslices, int64_t n, float* dst, int accumulate, gsb_stream s);
 /* Mixed transposed-conv cell (networks.py:495-511, operations.py:14-39): softmax(alpha[3])-
  * weighted, zero-padded sum of the IOHW k4/k6/k8 weights -> one IOHW 8x8 fp32 weight, and
  * merged bias (nullable).  SURVEY fact 4. */
@@ -91,33 +94,45 @@ int gsb_unmerge_upconv(const float* dw_merged, const float* db_merged, const flo
  * 1 = tcgen05/TMEM/TMA implicit GEMM (bf16 NHWC, cin%64==0, cout%64==0), 2 = auto.
  * stats_partial (nullable, TC path only): fp32 [m_tiles][2][cout] per-CTA sum / sum-of-squares
  * of the bf16-rounded outputs for BatchNorm; *stats_rows receives m_tiles.
- * accumulate != 0: out += result (SIMT path only). */
+ * accumulate != 0: out += result (SIMT path only).
+ * scratch (nullable, caller-owned, 16-byte aligned): fp32 partial-sum slices for launches whose few tiles would leave most
+ * SMs idle (deep generator levels): the K loop is then split over CTAs, part i stores into slice i, and a second kernel
+ * adds the slices in slice order.  Without scratch the launch is not split.  The buffer may be reused by the next call on
+ * the same stream. */
 int gsb_conv_gather(const gsb_view* in, const void* wp, int wdtype, const float* bias, const gsb_view* out,
                     const gsb_conv_geom* g, int act, int accumulate, int use_tc, float* stats_partial,
-                    int* stats_rows, gsb_stream s);
+                    int* stats_rows, void* scratch, size_t scratch_bytes, gsb_stream s);
 size_t gsb_conv_stats_rows(const gsb_view* out, const gsb_conv_geom* g);
-/* dWp[tap][cout][cin] (fp32, ACCUMULATED into -- caller zeroes) =
- * sum_pixels dout[pix][cout] * in[pix@tap][cin], with the forward op's gather mode. */
-int gsb_conv_wgrad(const gsb_view* in, const gsb_view* dout, float* dwp, const gsb_conv_geom* g, int use_tc,
-                   gsb_stream s);
+/* Weight gradient: sum_pixels dout[pix][cout] * in[pix@tap][cin], with the forward op's gather mode.  The pixel range is
+ * split over CTAs; split i STORES its partial sums into slice i of ws[max_slices][kh*kw][cout][cin] (fp32, every used slice
+ * written completely, nothing to clear); *used_slices receives the count.  The caller adds the slices in slice order
+ * (gsb_unpack_wgrad / _multi / gsb_sum_slices).  gsb_conv_wgrad_plan returns the slice count the launch will use. */
+int gsb_conv_wgrad_plan(const gsb_view* in, const gsb_view* dout, const gsb_conv_geom* g, int use_tc);
+int gsb_conv_wgrad(const gsb_view* in, const gsb_view* dout, float* ws, int max_slices, int* used_slices,
+                   const gsb_conv_geom* g, int use_tc, gsb_stream s);
 /* Network-edge convolutions as bandwidth kernels (one side has 1..4 / 1..8 channels).
  * stem: Conv2d(cin<=4 -> y.c, k x k, stride, pad) from the fp32 NCHW input x[n][cin][h][w] with the torch OIHW fp32
  *       weight (unet_model.py:14 / unet_parts.py:16; networks.py:582 outermost, :640); wgrad writes dweight (OIHW).
  * head: 1x1 Conv2d(x.c -> c<=8) + bias to fp32 NCHW logits (OutConv, unet_parts.py:71-77); backward writes
- *       dx (nullable), dweight[c][x.c] and dbias[c] (nullable; zeroed by the callee). */
+ *       dx (nullable), dweight[c][x.c] and dbias[c] (nullable).
+ * The two weight-gradient calls take a caller-owned workspace for their per-CTA partial rows (stem: y.c*cin*k*k floats per
+ * row, head: c*x.c + 8 floats per row; gsb_edge_rows() rows; fewer rows = fewer CTA columns), added in row order. */
 /* stats_partial (optional): [gsb_stem_stats_rows()][2][y.c] fp32 per-block BatchNorm sum / sum-of-squares of the stored
  * values; *stats_rows receives the rows written (0 when the shape ran through the kernel without fused statistics). */
 int gsb_stem_stats_rows(void);
 int gsb_stem_conv_fwd(const float* x, int n, int cin, int h, int w, const float* weight, const float* bias,
                       const gsb_view* y, int k, int stride, int pad, int act, float* stats_partial, int* stats_rows,
                       gsb_stream s);
+int gsb_edge_rows(void);
 int gsb_stem_conv_wgrad(const float* x, int n, int cin, int h, int w, const gsb_view* dy, int k, int stride, int pad,
-                        float* dweight, gsb_stream s);
+                        float* dweight, void* workspace, size_t workspace_bytes, gsb_stream s);
 int gsb_head_conv_fwd(const gsb_view* x, const float* weight, const float* bias, int c, float* logits, gsb_stream s);
 int gsb_head_conv_bwd(const gsb_view* x, const float* weight, int c, const float* dlogits, const gsb_view* dx,
-                      float* dweight, float* dbias, gsb_stream s);
-/* Per-channel sum over pixels (conv bias gradient), fp32 accumulate into db[c]. */
-int gsb_bias_grad(const gsb_view* dout, float* db, gsb_stream s);
+                      float* dweight, float* dbias, void* workspace, size_t workspace_bytes, gsb_stream s);
+/* Per-channel sum over pixels (conv bias gradient): db[c] is STORED.  workspace (nullable) >= gsb_bias_grad_workspace_bytes
+ * enables the vectorised two-stage form for NHWC views. */
+size_t gsb_bias_grad_workspace_bytes(const gsb_view* dout);
+int gsb_bias_grad(const gsb_view* dout, float* db, void* workspace, size_t workspace_bytes, gsb_stream s);
 
 /* ---- BatchNorm2d (+ activation, dropout) -- unet_parts.py:17-21, networks.py:584-607 -- */
 /* sums[2][c] (fp64) <- sum x, sum x^2 over (n,h,w); workspace >= gsb_bn_workspace_bytes. */
@@ -193,16 +208,19 @@ int gsb_seg_loss_bwd(const float* logits, const int64_t* labels, int n, int c, i
  * (image, class>=1): counts[n][max(c-1,1)][3] int64 = inter, pred, true.  unet/evaluate.py:29-40. */
 int gsb_eval_counts(const float* logits, const int64_t* labels, int n, int c, int h, int w, uint8_t* mask,
                     int64_t* counts, gsb_stream s);
-/* dice_coeff pieces: per-slice sums[slices][3] fp64 = sum a*b, sum a, sum b over `inner` elements. */
-int gsb_dice_sums(const float* a, const float* b, int64_t slices, int64_t inner, double* sums, gsb_stream s);
+/* dice_coeff pieces: per-slice sums[slices][3] fp64 = sum a*b, sum a, sum b over `inner` elements.
+ * workspace: fp64 partial rows [rows][slices][3], rows <= 1024 (one per CTA column), added in row order. */
+int gsb_dice_sums(const float* a, const float* b, int64_t slices, int64_t inner, double* sums, void* workspace,
+                  size_t workspace_bytes, gsb_stream s);
 
 /* ---- GAN / L1 losses -- networks.py:263-281, pix2pix_model.py:73,127 -------------------- */
 /* mode 0 vanilla (BCE-with-logits vs constant label), 1 lsgan (MSE), 2 wgangp (+-mean).
  * loss[0] (fp32) = mean; dpred (nullable) = gscale * dloss/dpred. */
 int gsb_gan_loss(const float* pred, int64_t numel, int mode, float label, float* loss, const float* gscale,
-                 float* dpred, void* workspace /* 8 bytes, needed when loss != NULL */, gsb_stream s);
+                 float* dpred, void* workspace /* one double per CTA, needed when loss != NULL */, size_t workspace_bytes,
+                 gsb_stream s);
 int gsb_l1_loss(const float* a, const float* b, int64_t numel, float* loss, const float* gscale, float* da,
-                void* workspace /* 8 bytes, needed when loss != NULL */, gsb_stream s);
+                void* workspace /* one double per CTA, needed when loss != NULL */, size_t workspace_bytes, gsb_stream s);
 
 /* dx = dout * act'(.) from the activation OUTPUT (contiguous fp32; the Tanh of the generator's
  * outermost block, networks.py:592). */

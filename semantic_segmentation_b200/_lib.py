@@ -41,20 +41,24 @@ SIGNATURES = {
     "gsb_launch_count": (C.c_ulonglong, []),
     "gsb_copy_view": (_i, [_VP, _VP, _p]),
     "gsb_pack_weight": (_i, [_p, _i, _i, _i, _i, _i, _p, _i, _p]),
-    "gsb_unpack_wgrad": (_i, [_p, _i, _i, _i, _i, _i, _p, _i, _p]),
+    "gsb_unpack_wgrad": (_i, [_p, _i, _i, _i, _i, _i, _i, _p, _i, _p]),
+    "gsb_sum_slices": (_i, [_p, _i, _i64, _p, _i, _p]),
     "gsb_pack_weight_multi": (_i, [_i, _p, _p, _p, _p, _p, _p, _i, _p]),
-    "gsb_unpack_wgrad_multi": (_i, [_i, _p, _p, _p, _p, _p, _p, _i, _p]),
+    "gsb_unpack_wgrad_multi": (_i, [_i, _p, _p, _p, _p, _p, _p, _p, _i, _p]),
     "gsb_merge_upconv": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _p, _p, _p]),
     "gsb_unmerge_upconv": (_i, [_p] * 9 + [_i, _i] + [_p] * 7 + [_p, _sz, _p]),
-    "gsb_conv_gather": (_i, [_VP, _p, _i, _p, _VP, _GP, _i, _i, _i, _p, _p, _p]),
+    "gsb_conv_gather": (_i, [_VP, _p, _i, _p, _VP, _GP, _i, _i, _i, _p, _p, _p, _sz, _p]),
     "gsb_conv_stats_rows": (_sz, [_VP, _GP]),
-    "gsb_conv_wgrad": (_i, [_VP, _VP, _p, _GP, _i, _p]),
+    "gsb_conv_wgrad_plan": (_i, [_VP, _VP, _GP, _i]),
+    "gsb_conv_wgrad": (_i, [_VP, _VP, _p, _i, _p, _GP, _i, _p]),
+    "gsb_edge_rows": (_i, []),
     "gsb_stem_stats_rows": (_i, []),
     "gsb_stem_conv_fwd": (_i, [_p, _i, _i, _i, _i, _p, _p, _VP, _i, _i, _i, _i, _p, _p, _p]),
-    "gsb_stem_conv_wgrad": (_i, [_p, _i, _i, _i, _i, _VP, _i, _i, _i, _p, _p]),
+    "gsb_stem_conv_wgrad": (_i, [_p, _i, _i, _i, _i, _VP, _i, _i, _i, _p, _p, _sz, _p]),
     "gsb_head_conv_fwd": (_i, [_VP, _p, _p, _i, _p, _p]),
-    "gsb_head_conv_bwd": (_i, [_VP, _p, _i, _p, _VP, _p, _p, _p]),
-    "gsb_bias_grad": (_i, [_VP, _p, _p]),
+    "gsb_head_conv_bwd": (_i, [_VP, _p, _i, _p, _VP, _p, _p, _p, _sz, _p]),
+    "gsb_bias_grad_workspace_bytes": (_sz, [_VP]),
+    "gsb_bias_grad": (_i, [_VP, _p, _p, _sz, _p]),
     "gsb_bn_workspace_bytes": (_sz, [_VP]),
     "gsb_bn_reduce": (_i, [_VP, _p, _p, _sz, _p]),
     "gsb_bn_reduce_partials": (_i, [_p, _i, _i, _p, _p]),
@@ -75,9 +79,9 @@ SIGNATURES = {
     "gsb_seg_loss_finalize": (_i, [_p, _d, _p, _p]),
     "gsb_seg_loss_bwd": (_i, [_p, _p, _i, _i, _i, _i, _p, _d, _p, _p, _p]),
     "gsb_eval_counts": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p]),
-    "gsb_dice_sums": (_i, [_p, _p, _i64, _i64, _p, _p]),
-    "gsb_gan_loss": (_i, [_p, _i64, _i, _f, _p, _p, _p, _p, _p]),
-    "gsb_l1_loss": (_i, [_p, _p, _i64, _p, _p, _p, _p, _p]),
+    "gsb_dice_sums": (_i, [_p, _p, _i64, _i64, _p, _p, _sz, _p]),
+    "gsb_gan_loss": (_i, [_p, _i64, _i, _f, _p, _p, _p, _p, _sz, _p]),
+    "gsb_l1_loss": (_i, [_p, _p, _i64, _p, _p, _p, _p, _sz, _p]),
     "gsb_act_bwd": (_i, [_p, _p, _i, _p, _i64, _p]),
     "gsb_rmsprop_step": (_i, [_p, _p, _p, _p, _i64, _f, _f, _f, _f, _f, _f, _p]),
     "gsb_adam_step": (_i, [_p, _p, _p, _p, _i64, _f, _f, _f, _f, _f, _i64, _f, _p]),

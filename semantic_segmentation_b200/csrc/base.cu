@@ -39,15 +39,16 @@ bool pdl_enabled() {
   return on == 1;
 }
 
-int num_sms() {
-  static int sms = 0;
-  if (sms == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
-        sms <= 0)
-      sms = 148;
+int num_sms() {  // of the CURRENT device (cached per device ordinal)
+  static int sms[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (sms[dev] == 0) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+    sms[dev] = v;
   }
-  return sms;
+  return sms[dev];
 }
 
 // SMs the persistent kernels size their grids for: all of them, minus the ones set aside for a collective that runs
@@ -59,7 +60,57 @@ int num_sms_avail() {
   return n < 8 ? 8 : n;
 }
 
+// dst[i] (+)= sum_s ws[s][i], s ascending, fp64 accumulation: the deterministic second stage of every split reduction of
+// the library (weight-gradient slices, per-CTA partial rows of the edge kernels); no atomics anywhere.
+__global__ void __launch_bounds__(256) sum_slices_kernel(const float* __restrict__ ws, int nslices, int64_t slice_stride, int64_t n,
+                                                        float* __restrict__ dst, int accumulate, int vec) {
+  GSB_PDL_ENTRY();
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  if (vec) {
+    const int64_t n4 = n >> 2;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll 4
+      for (int s = 0; s < nslices; ++s) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(ws + (int64_t)s * slice_stride) + i);
+        a0 += (double)v.x; a1 += (double)v.y; a2 += (double)v.z; a3 += (double)v.w;
+      }
+      float4* d = reinterpret_cast<float4*>(dst) + i;
+      if (accumulate) {
+        const float4 o = *d;
+        a0 += (double)o.x; a1 += (double)o.y; a2 += (double)o.z; a3 += (double)o.w;
+      }
+      *d = make_float4((float)a0, (float)a1, (float)a2, (float)a3);
+    }
+  } else {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+      double a = 0.0;
+#pragma unroll 4
+      for (int s = 0; s < nslices; ++s) a += (double)__ldg(ws + (int64_t)s * slice_stride + i);
+      if (accumulate) a += (double)dst[i];
+      dst[i] = (float)a;
+    }
+  }
+}
+
+int sum_slices(const float* ws, int nslices, int64_t slice_stride, int64_t n, float* dst, int accumulate, cudaStream_t st) {
+  const int vec = (n % 4 == 0) && (slice_stride % 4 == 0) && ((uintptr_t)ws % 16 == 0) && ((uintptr_t)dst % 16 == 0);
+  const int64_t items = vec ? n / 4 : n;
+  int64_t blocks = (items + 255) / 256;
+  const int64_t cap = (int64_t)num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  launch(sum_slices_kernel, LaunchCfg((unsigned)blocks, 256, 0, st), ws, nslices, slice_stride, n, dst, accumulate, vec);
+  return 0;
+}
+
 }  // namespace gsb
+
+extern "C" int gsb_sum_slices(const float* ws, int nslices, int64_t n, float* dst, int accumulate, gsb_stream s) {
+  GSB_REQUIRE(ws && dst && nslices >= 1 && n >= 1, "sum_slices: bad argument");
+  gsb::sum_slices(ws, nslices, n, n, dst, accumulate, gsb::to_stream(s));
+  return gsb::check_launch("sum_slices");
+}
 
 extern "C" unsigned long long gsb_launch_count(void) { return gsb::launch_count(); }
 extern "C" int gsb_version(void) { return 100; }

@@ -60,7 +60,9 @@ static inline cudaError_t launch(void (*kern)(KArgs...), const LaunchCfg& lc, Ar
     asm volatile("griddepcontrol.launch_dependents;");           \
     asm volatile("griddepcontrol.wait;" ::: "memory");           \
   } while (0)
-int num_sms();        // SMs of the device
+// dst[i] (+)= sum over s < nslices of ws[s * slice_stride + i], i < n, in slice order with fp64 accumulation (base.cu)
+int sum_slices(const float* ws, int nslices, int64_t slice_stride, int64_t n, float* dst, int accumulate, cudaStream_t st);
+int num_sms();        // SMs of the current device
 int num_sms_avail();  // SMs the persistent tensor-core kernels size their grids for (total minus gsb_set_sm_reserve)
 
 // A view is "pixel-linear" when pixel p = (n*h + y)*w + x lives at ptr + p*sw (+ c).

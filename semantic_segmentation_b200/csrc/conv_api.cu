@@ -4,11 +4,13 @@
 namespace gsb {
 int conv_gather_direct(const gsb_view* in, const void* wp, int wdtype, const float* bias, const gsb_view* out,
                        const gsb_conv_geom* g, int act, int accumulate, cudaStream_t st);
-int conv_wgrad_direct(const gsb_view* in, const gsb_view* dout, float* dwp, const gsb_conv_geom* g, cudaStream_t st);
+int conv_wgrad_direct(const gsb_view* in, const gsb_view* dout, float* ws, int max_slices, int* used, const gsb_conv_geom* g,
+                      cudaStream_t st);
 bool conv_tc_supported(const gsb_view* in, const gsb_view* out, const gsb_conv_geom* g);
 int conv_gather_tc(const gsb_view* in, const void* wp, const float* bias, const gsb_view* out, const gsb_conv_geom* g, int act,
-                   float* stats, int* stats_rows, cudaStream_t st);
-int conv_wgrad_tc(const gsb_view* in, const gsb_view* dout, float* dwp, const gsb_conv_geom* g, cudaStream_t st);
+                   float* stats, int* stats_rows, float* scratch, size_t scratch_bytes, cudaStream_t st);
+int conv_wgrad_tc(const gsb_view* in, const gsb_view* dout, float* ws, int max_slices, int* used, const gsb_conv_geom* g,
+                  cudaStream_t st);
 int conv_tc_m_tiles(const gsb_view* out);
 
 static int out_extent(int mode, int in, int k, int stride, int pad) {
@@ -32,7 +34,7 @@ extern "C" size_t gsb_conv_stats_rows(const gsb_view* out, const gsb_conv_geom* 
 
 extern "C" int gsb_conv_gather(const gsb_view* in, const void* wp, int wdtype, const float* bias, const gsb_view* out,
                                const gsb_conv_geom* g, int act, int accumulate, int use_tc, float* stats_partial,
-                               int* stats_rows, gsb_stream s) {
+                               int* stats_rows, void* scratch, size_t scratch_bytes, gsb_stream s) {
   if (check_geom(g)) return -1;
   GSB_REQUIRE(in && out && wp && in->ptr && out->ptr, "conv_gather: null argument");
   GSB_REQUIRE(in->n == out->n, "conv_gather: batch mismatch");
@@ -50,18 +52,37 @@ extern "C" int gsb_conv_gather(const gsb_view* in, const void* wp, int wdtype, c
   if (stats_rows) *stats_rows = 0;
   bool tc_ok = wdtype == GSB_BF16 && !accumulate && gsb_tc_available() && conv_tc_supported(in, out, g);
   if (use_tc == 1) GSB_REQUIRE(tc_ok, "conv_gather: tcgen05 path requested but shape/dtype unsupported");
-  if (use_tc != 0 && tc_ok) return conv_gather_tc(in, wp, bias, out, g, act, stats_partial, stats_rows, gsb::to_stream(s));
+  if (use_tc != 0 && tc_ok)
+    return conv_gather_tc(in, wp, bias, out, g, act, stats_partial, stats_rows, reinterpret_cast<float*>(scratch), scratch_bytes,
+                          gsb::to_stream(s));
   GSB_REQUIRE(stats_partial == nullptr || use_tc != 1, "conv_gather: stats need the tcgen05 path");
   return conv_gather_direct(in, wp, wdtype, bias, out, g, act, accumulate, gsb::to_stream(s));
 }
 
-extern "C" int gsb_conv_wgrad(const gsb_view* in, const gsb_view* dout, float* dwp, const gsb_conv_geom* g, int use_tc,
-                              gsb_stream s) {
+// Weight gradient, deterministic split reduction: the launch writes `*used_slices` complete fp32 slices
+// ws[slice][kh*kw][cout][cin] (one per split of the pixel range) with plain stores; the caller adds them in slice order
+// (gsb_sum_slices, or gsb_unpack_wgrad(_multi) with the slice count).  gsb_conv_wgrad_plan returns the slice count the
+// launch will use for this geometry on the current device, so the caller can size the workspace.
+static int wgrad_dispatch(const gsb_view* in, const gsb_view* dout, float* ws, int max_slices, int* used, const gsb_conv_geom* g,
+                          int use_tc, gsb_stream s) {
   if (check_geom(g)) return -1;
-  GSB_REQUIRE(in && dout && dwp && in->ptr && dout->ptr, "conv_wgrad: null argument");
+  GSB_REQUIRE(in && dout && in->ptr && dout->ptr && used, "conv_wgrad: null argument");
   GSB_REQUIRE(in->n == dout->n, "conv_wgrad: batch mismatch");
+  *used = 0;
   bool tc_ok = gsb_tc_available() && conv_tc_supported(in, dout, g);
   if (use_tc == 1) GSB_REQUIRE(tc_ok, "conv_wgrad: tcgen05 path requested but shape/dtype unsupported");
-  if (use_tc != 0 && tc_ok) return conv_wgrad_tc(in, dout, dwp, g, gsb::to_stream(s));
-  return conv_wgrad_direct(in, dout, dwp, g, gsb::to_stream(s));
+  if (use_tc != 0 && tc_ok) return conv_wgrad_tc(in, dout, ws, max_slices, used, g, gsb::to_stream(s));
+  return conv_wgrad_direct(in, dout, ws, max_slices, used, g, gsb::to_stream(s));
+}
+
+extern "C" int gsb_conv_wgrad_plan(const gsb_view* in, const gsb_view* dout, const gsb_conv_geom* g, int use_tc) {
+  int used = 0;
+  if (wgrad_dispatch(in, dout, nullptr, 0, &used, g, use_tc, nullptr)) return -1;
+  return used;
+}
+
+extern "C" int gsb_conv_wgrad(const gsb_view* in, const gsb_view* dout, float* ws, int max_slices, int* used_slices,
+                              const gsb_conv_geom* g, int use_tc, gsb_stream s) {
+  GSB_REQUIRE(ws != nullptr && max_slices >= 1, "conv_wgrad: workspace required");
+  return wgrad_dispatch(in, dout, ws, max_slices, used_slices, g, use_tc, s);
 }

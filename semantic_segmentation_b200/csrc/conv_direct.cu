@@ -152,11 +152,13 @@ __global__ void __launch_bounds__(256) conv_gather_kernel(DView in, const void* 
   }
 }
 
-// dWp[tap][co][ci] += sum over driver pixels of dout[.][co] * in[.][ci].
+// slice[blockIdx.z][tap][co][ci] = sum over this split's driver pixels of dout[.][co] * in[.][ci]  (plain stores: every
+// slice is written completely, the caller adds the slices in slice order -> deterministic, no atomics).
 // Driver = the lower-resolution side: output pixels for CONV, input pixels for CONVT.
 template <int BM, int BN, int TM, int TN>
-__global__ void __launch_bounds__(256) conv_wgrad_kernel(DView in, DView dout, float* __restrict__ dwp, int mode, int KH,
-                                                         int KW, int stride, int pad, int64_t chunk, int tiles_n) {
+__global__ void __launch_bounds__(256) conv_wgrad_kernel(DView in, DView dout, float* __restrict__ dwp, int64_t slice_elems,
+                                                         int mode, int KH, int KW, int stride, int pad, int64_t chunk,
+                                                         int tiles_n) {
   GSB_PDL_ENTRY();
   static_assert((BM / TM) * (BN / TN) == 256, "tile/thread mismatch");
   __shared__ float As[BK][BM + 4];  // dout  [k][co]
@@ -246,17 +248,19 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(DView in, DView dout, f
     for (int j = 0; j < TN; ++j) {
       int ci = ci0 + tx * TN + j;
       if (ci >= Cin) continue;
-      atomicAdd(dwp + ((int64_t)tap * Cout + co) * Cin + ci, acc[i][j]);
+      dwp[(int64_t)blockIdx.z * slice_elems + ((int64_t)tap * Cout + co) * Cin + ci] = acc[i][j];
     }
   }
 }
 
+// One CTA per channel; fixed summation order (thread-strided fp64 partials, shuffle tree, 8 warp sums in index order):
+// deterministic, and the result is STORED (the earlier form added partial sums of several CTAs with atomics).
 __global__ void bias_grad_kernel(DView d, float* __restrict__ db) {
   GSB_PDL_ENTRY();
   const int c = blockIdx.x;
   const int64_t P = (int64_t)d.N * d.H * d.W;
   double acc = 0.0;   // bias gradients are cancellation-heavy sums: accumulate in fp64
-  for (int64_t p = (int64_t)blockIdx.y * blockDim.x + threadIdx.x; p < P; p += (int64_t)gridDim.y * blockDim.x) {
+  for (int64_t p = threadIdx.x; p < P; p += blockDim.x) {
     int x = (int)(p % d.W);
     int64_t r = p / d.W;
     int y = (int)(r % d.H);
@@ -270,13 +274,44 @@ __global__ void bias_grad_kernel(DView d, float* __restrict__ db) {
   if (threadIdx.x < 32) {
     double v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.0;
     v = warp_sum_d(v);
-    if (threadIdx.x == 0) atomicAdd(db + c, (float)v);
+    if (threadIdx.x == 0) db[c] = (float)v;
+  }
+}
+
+// NHWC views with C % 8 == 0: 16-byte loads, every CTA covers a pixel range and writes TWO partial rows (its fp64 sums
+// split into hi + lo floats); gsb::sum_slices adds the rows in row order.
+template <typename T>
+__global__ void __launch_bounds__(256) bias_grad_vec_kernel(const T* __restrict__ d, int64_t ld, int64_t P, int C,
+                                                           float* __restrict__ partial) {
+  GSB_PDL_ENTRY();
+  __shared__ double red[256][8];
+  const int G = C >> 3, lanes = 256 / G;
+  const int g = threadIdx.x % G, lane = threadIdx.x / G;
+  double acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.0;
+  for (int64_t p = (int64_t)blockIdx.x * lanes + lane; p < P; p += (int64_t)gridDim.x * lanes) {
+    float v[8];
+    Vec8<T>::load(d + p * ld + g * 8, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] += (double)v[j];
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[threadIdx.x][j] = acc[j];
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += 256) {
+    double t = 0.0;
+    for (int l = 0; l < lanes; ++l) t += red[l * G + (c >> 3)][c & 7];
+    const float hi = (float)t;
+    partial[((int64_t)blockIdx.x * 2) * C + c] = hi;
+    partial[((int64_t)blockIdx.x * 2 + 1) * C + c] = (float)(t - (double)hi);
   }
 }
 
 int thin_gather_try(const gsb_view* in, const void* wp, int wdtype, const float* bias, const gsb_view* out,
                     const gsb_conv_geom* g, int act, int accumulate, cudaStream_t st);
-int thin_wgrad_try(const gsb_view* in, const gsb_view* dout, float* dwp, const gsb_conv_geom* g, cudaStream_t st);
+int thin_wgrad_try(const gsb_view* in, const gsb_view* dout, float* ws, int max_slices, int* used, const gsb_conv_geom* g,
+                   cudaStream_t st);
 
 int conv_gather_direct(const gsb_view* in, const void* wp, int wdtype, const float* bias, const gsb_view* out,
                        const gsb_conv_geom* g, int act, int accumulate, cudaStream_t st) {
@@ -304,11 +339,15 @@ int conv_gather_direct(const gsb_view* in, const void* wp, int wdtype, const flo
   return check_launch("conv_gather(direct)", sub * sub);
 }
 
-int conv_wgrad_direct(const gsb_view* in, const gsb_view* dout, float* dwp, const gsb_conv_geom* g, cudaStream_t st) {
+// ws == nullptr: plan only (*used = number of slices the launch would write).
+int conv_wgrad_direct(const gsb_view* in, const gsb_view* dout, float* ws, int max_slices, int* used, const gsb_conv_geom* g,
+                      cudaStream_t st) {
   {
-    int r = thin_wgrad_try(in, dout, dwp, g, st);
+    int r = thin_wgrad_try(in, dout, ws, max_slices, used, g, st);
     if (r != 0) return r < 0 ? -1 : 0;
   }
+  const int64_t slice_elems = (int64_t)g->kh * g->kw * dout->c * in->c;
+  int rc = 0;
   DView vi = dv(in), vd = dv(dout);
   const bool conv = g->mode == GSB_MODE_CONV;
   int64_t P = conv ? num_pixels(dout) : num_pixels(in);
@@ -318,12 +357,17 @@ int conv_wgrad_direct(const gsb_view* in, const gsb_view* dout, float* dwp, cons
     int64_t base = (int64_t)tiles_m * tiles_n * taps;
     int64_t want = ((int64_t)num_sms() * 4 + base - 1) / base;
     int64_t max_split = (P + 255) / 256;
+    if (ws != nullptr && max_split > max_slices) max_split = max_slices;
+    if (max_split > 256) max_split = 256;
     int64_t split = want < 1 ? 1 : (want > max_split ? max_split : want);
-    if (split > 65535) split = 65535;
     int64_t chunk = ((P + split - 1) / split + BK - 1) / BK * BK;
     split = (P + chunk - 1) / chunk;
+    if (split < 1) split = 1;
+    *used = (int)split;
+    if (ws == nullptr) return;
+    if (split > max_slices) { rc = -1; return; }
     dim3 grid((unsigned)(tiles_m * tiles_n), (unsigned)taps, (unsigned)split);
-    gsb::launch(kernel, gsb::LaunchCfg(grid, 256, 0, st), vi, vd, dwp, g->mode, g->kh, g->kw, g->stride, g->pad, chunk, tiles_n);
+    gsb::launch(kernel, gsb::LaunchCfg(grid, 256, 0, st), vi, vd, ws, slice_elems, g->mode, g->kh, g->kw, g->stride, g->pad, chunk, tiles_n);
   };
   if (dout->c <= 8)
     launch(conv_wgrad_kernel<8, 128, 1, 4>, 8, 128);
@@ -331,6 +375,8 @@ int conv_wgrad_direct(const gsb_view* in, const gsb_view* dout, float* dwp, cons
     launch(conv_wgrad_kernel<64, 8, 2, 1>, 64, 8);
   else
     launch(conv_wgrad_kernel<64, 64, 4, 4>, 64, 64);
+  GSB_REQUIRE(rc == 0, "conv_wgrad(direct): %d slices needed, workspace holds %d", *used, max_slices);
+  if (ws == nullptr) return 0;
   return check_launch("conv_wgrad(direct)");
 }
 
@@ -338,13 +384,34 @@ int conv_wgrad_direct(const gsb_view* in, const gsb_view* dout, float* dwp, cons
 
 using namespace gsb;
 
-extern "C" int gsb_bias_grad(const gsb_view* dout, float* db, gsb_stream s) {
+extern "C" size_t gsb_bias_grad_workspace_bytes(const gsb_view* dout) {
+  return (size_t)num_sms() * 4 * 2 * (size_t)(dout ? dout->c : 0) * sizeof(float);
+}
+
+// db[c] = sum over pixels of dout[., c]  (stored, not accumulated; deterministic)
+extern "C" int gsb_bias_grad(const gsb_view* dout, float* db, void* workspace, size_t workspace_bytes, gsb_stream s) {
   GSB_REQUIRE(dout && dout->ptr && db, "bias_grad: null argument");
-  int64_t P = num_pixels(dout);
-  int by = (int)((P + 256 * 64 - 1) / (256 * 64));
-  if (by < 1) by = 1;
-  if (by > 64) by = 64;
-  dim3 grid((unsigned)dout->c, (unsigned)by);
+  const int C = dout->c;
+  const int64_t P = num_pixels(dout);
+  if (vec8_ok(dout) && C >= 8 && 256 % (C / 8) == 0 && C / 8 <= 256 && workspace != nullptr) {
+    const int lanes = 256 / (C / 8);
+    int64_t want = (P + (int64_t)lanes * 8 - 1) / ((int64_t)lanes * 8);
+    int64_t cap = (int64_t)(workspace_bytes / (2 * (size_t)C * sizeof(float)));
+    if (cap > (int64_t)num_sms() * 4) cap = (int64_t)num_sms() * 4;
+    int grid = (int)(want < 1 ? 1 : (want > cap ? cap : want));
+    if (grid >= 1 && cap >= 1) {
+      float* partial = reinterpret_cast<float*>(workspace);
+      if (dout->dtype == GSB_BF16)
+        gsb::launch(bias_grad_vec_kernel<__nv_bfloat16>, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), (const __nv_bfloat16*)dout->ptr,
+                    (int64_t)dout->sw, P, C, partial);
+      else
+        gsb::launch(bias_grad_vec_kernel<float>, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), (const float*)dout->ptr, (int64_t)dout->sw, P, C,
+                    partial);
+      gsb::sum_slices(partial, 2 * grid, C, C, db, 0, to_stream(s));
+      return check_launch("bias_grad", 2);
+    }
+  }
+  dim3 grid((unsigned)C, 1u);
   gsb::launch(bias_grad_kernel, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), dv(dout), db);
   return check_launch("bias_grad");
 }

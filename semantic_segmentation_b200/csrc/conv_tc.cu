@@ -40,8 +40,9 @@ struct TcParams {
   int act;
   const float* bias;
   float* stats;                   // [m_tiles][2][cout] or null
-  int ks_split;                   // > 1: split-K -- a tile's K steps are spread over ks_split CTAs, fp32 atomics into ws
-  float* ws;                      // [N*H*W of the tiled space][cout] fp32, zeroed (split-K only)
+  int ks_split;                   // > 1: split-K -- a tile's K steps are spread over ks_split CTAs, part i stores into slice i
+  float* ws;                      // [ks_split][N*H*W of the tiled space][cout] fp32 partial sums (split-K only)
+  int64_t ws_slice;               // elements per slice
 };
 
 template <int BN>
@@ -162,16 +163,21 @@ conv_tc_fprop_kernel(const __grid_constant__ TcMaps maps, const __grid_constant_
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       if (p.ks_split > 1) {
-        // split-K: this CTA holds a partial sum over its K range -> fp32 atomics into the workspace; bias, activation,
-        // rounding and the store to the output view happen in splitk_finalize_kernel
-        float* wrow = p.ws + (((int64_t)(n0 + pn) * p.H + (y0 + py)) * p.W + (x0 + px)) * p.cout + nt * BN;
+        // split-K: this CTA holds a partial sum over its K range -> plain stores into its own slice of the workspace; the
+        // slices are added in slice order, then bias, activation, rounding and the store to the output view, in
+        // splitk_finalize_kernel (deterministic: no atomics)
+        float* wrow = p.ws + (int64_t)(tile % p.ks_split) * p.ws_slice +
+                      (((int64_t)(n0 + pn) * p.H + (y0 + py)) * p.W + (x0 + px)) * p.cout + nt * BN;
 #pragma unroll 1
         for (int ch = 0; ch < BN / 32; ++ch) {
           uint32_t v[32];
           tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + ch * 32, v);
           if (valid) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) atomicAdd(wrow + ch * 32 + i, __uint_as_float(v[i]));
+            for (int i = 0; i < 8; ++i)
+              *reinterpret_cast<float4*>(wrow + ch * 32 + 4 * i) =
+                  make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]),
+                              __uint_as_float(v[4 * i + 3]));
           }
         }
         tc_fence_before();
@@ -258,8 +264,10 @@ conv_tc_fprop_kernel(const __grid_constant__ TcMaps maps, const __grid_constant_
   }
 }
 
-// Split-K epilogue: ws[pixel][cout] fp32 -> (+bias) -> activation -> bf16 -> output view (8 channels per thread).
-__global__ void __launch_bounds__(256) splitk_finalize_kernel(const float* __restrict__ ws, int64_t pixels, int W, int H, int cout,
+// Split-K epilogue: sum over the slices ws[slice][pixel][cout] (fp32, slice order) -> (+bias) -> activation -> bf16 ->
+// output view (8 channels per thread).
+__global__ void __launch_bounds__(256) splitk_finalize_kernel(const float* __restrict__ ws, int nslices, int64_t slice_elems,
+                                                             int64_t pixels, int W, int H, int cout,
                                                              const float* __restrict__ bias, int act, __nv_bfloat16* __restrict__ out,
                                                              int64_t sw, int64_t sh, int64_t sn) {
   GSB_PDL_ENTRY();
@@ -269,30 +277,17 @@ __global__ void __launch_bounds__(256) splitk_finalize_kernel(const float* __res
     const int64_t pix = i / G;
     const int x = (int)(pix % W), y = (int)((pix / W) % H);
     const int64_t n = pix / ((int64_t)W * H);
-    const float4 a = *reinterpret_cast<const float4*>(ws + pix * cout + g * 8);
-    const float4 b = *reinterpret_cast<const float4*>(ws + pix * cout + g * 8 + 4);
-    float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int s = 0; s < nslices; ++s) {
+      const float* src = ws + (int64_t)s * slice_elems + pix * cout + g * 8;
+      const float4 a = *reinterpret_cast<const float4*>(src), b = *reinterpret_cast<const float4*>(src + 4);
+      v[0] += a.x; v[1] += a.y; v[2] += a.z; v[3] += a.w;
+      v[4] += b.x; v[5] += b.y; v[6] += b.z; v[7] += b.w;
+    }
 #pragma unroll
     for (int j = 0; j < 8; ++j) v[j] = act_fwd(v[j] + (bias ? __ldg(bias + g * 8 + j) : 0.f), act);
     Vec8<__nv_bfloat16>::store(out + n * sn + y * sh + x * sw + g * 8, v);
   }
-}
-
-// Library-owned scratch of the split-K path (allocated once per process on first use outside stream capture).
-constexpr size_t kSplitKScratchBytes = (size_t)8 << 20;
-static float* splitk_scratch(cudaStream_t st) {
-  static float* buf = nullptr;
-  if (buf == nullptr) {
-    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
-    if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return nullptr;
-    void* p = nullptr;
-    if (cudaMalloc(&p, kSplitKScratchBytes) != cudaSuccess) {
-      cudaGetLastError();
-      return nullptr;
-    }
-    buf = static_cast<float*>(p);
-  }
-  return buf;
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -306,7 +301,8 @@ struct WgParams {
   int n_tiles;                    // unshifted-side channel tiles of BN
   int a_is_in;                    // 1: shifted side is the forward input (rows = ci), 0: it is dY (rows = co)
   int cin, cout;
-  float* dwp;
+  float* dwp;                     // slice workspace [split][taps][cout][cin]: split s stores into slice s (no atomics)
+  int64_t slice_elems;
 };
 
 template <int BN>
@@ -405,6 +401,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ TcMaps maps, const __grid_constant_
     const int a_ch = rvalid ? (blk % p.a_cblocks) * 64 + (row & 63) : 0;
     mbar_wait(tfull, 0);
     tc_fence_after();
+    float* __restrict__ slice = p.dwp + (int64_t)blockIdx.y * p.slice_elems;
 #pragma unroll 1
     for (int ch = 0; ch < BN / 32; ++ch) {
       uint32_t v[32];
@@ -415,7 +412,7 @@ conv_tc_wgrad_kernel(const __grid_constant__ TcMaps maps, const __grid_constant_
           const int b_ch = nt * BN + ch * 32 + j;
           const int64_t idx = p.a_is_in ? ((int64_t)tap * p.cout + b_ch) * p.cin + a_ch
                                         : ((int64_t)tap * p.cout + a_ch) * p.cin + b_ch;
-          atomicAdd(p.dwp + idx, __uint_as_float(v[j]));
+          slice[idx] = __uint_as_float(v[j]);
         }
       }
     }
@@ -436,7 +433,7 @@ int conv_halo_m_tiles(int w, int h, int n);
 int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, const TcTaps& taps, const void* wp, int taps_total,
                     int cin, int cout, const float* bias, int act, float* stats, int* stats_rows, cudaStream_t st);
 int conv_halo_wgrad(const SubView& tiled, const SubView* shifted, int nmaps, const TcTaps& taps, int shifted_c, int a_is_in,
-                    int cin, int cout, float* dwp, cudaStream_t st);
+                    int cin, int cout, int taps_total, float* ws, int max_slices, int* used, cudaStream_t st);
 
 static int pow2ceil(int v) {
   int p = 1;
@@ -494,7 +491,8 @@ static int launch_tc(Kern kern, int grid_x, int grid_y, int smem, const TcMaps& 
 
 // One fprop-style launch over a tiled output (sub)view.
 static int fprop_launch(const SubView& outv, const SubView* shifted, int nmaps, const TcTaps& taps, const void* wp, int taps_total,
-                        int cin, int cout, const float* bias, int act, float* stats, int* stats_rows, cudaStream_t st) {
+                        int cin, int cout, const float* bias, int act, float* stats, int* stats_rows, float* scratch,
+                        size_t scratch_bytes, cudaStream_t st) {
   {  // halo-stationary kernel first (16x16 tiles, operand reuse across vertical taps); falls through when not applicable
     int r = conv_halo_fprop(outv, shifted, nmaps, taps, wp, taps_total, cin, cout, bias, act, stats, stats_rows, st);
     if (r != 0) return r < 0 ? -1 : 0;
@@ -519,7 +517,7 @@ static int fprop_launch(const SubView& outv, const SubView* shifted, int nmaps, 
   p.n_tiles = cout / BN;
   p.num_tiles = p.tiles_x * p.tiles_y * p.tiles_z * p.n_tiles;
   p.act = act; p.bias = bias; p.stats = stats;
-  p.ks_split = 1; p.ws = nullptr;
+  p.ks_split = 1; p.ws = nullptr; p.ws_slice = 0;
   if (stats_rows) *stats_rows = p.tiles_x * p.tiles_y * p.tiles_z;
   // Deep generator / discriminator levels: a handful of tiles would stream the whole weight tensor through 4..32 SMs
   // (2.3 ms per Pix2Pix step, ncu profiles/r01o).  Split the K loop over enough CTAs to fill the GPU instead.
@@ -527,21 +525,21 @@ static int fprop_launch(const SubView& outv, const SubView* shifted, int nmaps, 
   const int64_t pixels = outv.N * outv.H * outv.W;
   const int sms = num_sms_avail();
   static const bool splitk_on = []() { const char* e = getenv("GSB_TC_SPLITK"); return !(e && e[0] == '0'); }();
-  if (splitk_on && p.num_tiles * 2 <= sms && ksteps >= 8 && (size_t)pixels * cout * sizeof(float) <= kSplitKScratchBytes &&
-      cout % 8 == 0) {
-    float* ws = splitk_scratch(st);
-    if (ws != nullptr) {
-      int split = sms / p.num_tiles;
-      if (split > ksteps / 4) split = ksteps / 4;
-      if (split > 1) {
-        p.ks_split = split;
-        p.ws = ws;
-        p.num_tiles *= split;
-        p.stats = nullptr;
-        if (stats_rows) *stats_rows = 0;   // no fused statistics on this path: the caller reduces the stored output
-        cudaError_t e = cudaMemsetAsync(ws, 0, (size_t)pixels * cout * sizeof(float), st);
-        GSB_REQUIRE(e == cudaSuccess, "conv_tc split-K memset failed: %s", cudaGetErrorString(e));
-      }
+  const size_t slice_bytes = (size_t)pixels * cout * sizeof(float);
+  if (splitk_on && scratch != nullptr && p.num_tiles * 2 <= sms && ksteps >= 8 && 2 * slice_bytes <= scratch_bytes &&
+      cout % 8 == 0 && ((uintptr_t)scratch % 16) == 0) {
+    // the caller's scratch holds one fp32 partial-sum slice per K part (every valid pixel row of a slice is written by
+    // exactly one CTA, so no clearing and no atomics: the finalize kernel adds the slices in slice order)
+    int split = sms / p.num_tiles;
+    if (split > ksteps / 4) split = ksteps / 4;
+    if ((size_t)split * slice_bytes > scratch_bytes) split = (int)(scratch_bytes / slice_bytes);
+    if (split > 1) {
+      p.ks_split = split;
+      p.ws = scratch;
+      p.ws_slice = pixels * cout;
+      p.num_tiles *= split;
+      p.stats = nullptr;
+      if (stats_rows) *stats_rows = 0;   // no fused statistics on this path: the caller reduces the stored output
     }
   }
   int grid = p.num_tiles < sms ? p.num_tiles : sms;
@@ -551,7 +549,7 @@ static int fprop_launch(const SubView& outv, const SubView* shifted, int nmaps, 
   int64_t items = pixels * (cout / 8);
   int fgrid = (int)((items + 255) / 256);
   if (fgrid > num_sms() * 8) fgrid = num_sms() * 8;
-  gsb::launch(splitk_finalize_kernel, gsb::LaunchCfg(fgrid, 256, 0, st), p.ws, pixels, (int)outv.W, (int)outv.H, cout, bias, act,
+  gsb::launch(splitk_finalize_kernel, gsb::LaunchCfg(fgrid, 256, 0, st), p.ws, p.ks_split, p.ws_slice, pixels, (int)outv.W, (int)outv.H, cout, bias, act,
                                                 (__nv_bfloat16*)const_cast<void*>(outv.ptr), outv.sw, outv.sh, outv.sn);
   return check_launch("conv_tc split-K finalize");
 }
@@ -559,7 +557,7 @@ static int fprop_launch(const SubView& outv, const SubView* shifted, int nmaps, 
 static int floor_div(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
 
 int conv_gather_tc(const gsb_view* in, const void* wp, const float* bias, const gsb_view* out, const gsb_conv_geom* g, int act,
-                   float* stats, int* stats_rows, cudaStream_t st) {
+                   float* stats, int* stats_rows, float* scratch, size_t scratch_bytes, cudaStream_t st) {
   const int s = g->stride, taps_total = g->kh * g->kw;
   GSB_REQUIRE(stats == nullptr || !(g->mode == GSB_MODE_CONVT && s > 1), "conv_tc: fused BN statistics unsupported for strided transposed conv");
   if (g->mode == GSB_MODE_CONV) {
@@ -585,7 +583,7 @@ int conv_gather_tc(const gsb_view* in, const void* wp, const float* bias, const 
       }
     GSB_REQUIRE(taps.ntaps > 0, "conv_tc: no taps");
     SubView ov = subview(out, 1, 0, 0);
-    return fprop_launch(ov, subs, nmaps, taps, wp, taps_total, in->c, out->c, bias, act, stats, stats_rows, st);
+    return fprop_launch(ov, subs, nmaps, taps, wp, taps_total, in->c, out->c, bias, act, stats, stats_rows, scratch, scratch_bytes, st);
   }
   // transposed-conv gather: one launch per output parity
   for (int py = 0; py < s; ++py)
@@ -607,14 +605,18 @@ int conv_gather_tc(const gsb_view* in, const void* wp, const float* bias, const 
       SubView ov = subview(out, s, py, px);
       SubView iv = subview(in, 1, 0, 0);
       if (taps.ntaps == 0) continue;  // (cannot happen for k >= s)
-      if (fprop_launch(ov, &iv, 1, taps, wp, taps_total, in->c, out->c, bias, act, stats, s == 1 ? stats_rows : nullptr, st))
+      if (fprop_launch(ov, &iv, 1, taps, wp, taps_total, in->c, out->c, bias, act, stats, s == 1 ? stats_rows : nullptr, scratch,
+                       scratch_bytes, st))
         return -1;
     }
   return 0;
 }
 
-int conv_wgrad_tc(const gsb_view* in, const gsb_view* dout, float* dwp, const gsb_conv_geom* g, cudaStream_t st) {
+// ws == nullptr: plan only (*used = number of slices the launch would write).
+int conv_wgrad_tc(const gsb_view* in, const gsb_view* dout, float* ws, int max_slices, int* used, const gsb_conv_geom* g,
+                  cudaStream_t st) {
   const int s = g->stride;
+  const int taps_total = g->kh * g->kw;
   const bool conv = g->mode == GSB_MODE_CONV;
   // driver (tiled, unshifted) side: dY for conv, X for transposed conv; shifted side is the other one
   const gsb_view* tiled = conv ? dout : in;
@@ -640,19 +642,22 @@ int conv_wgrad_tc(const gsb_view* in, const gsb_view* dout, float* dwp, const gs
     }
   GSB_REQUIRE(taps.ntaps > 0, "conv_wgrad_tc: no taps");
   if (getenv("GSB_TC_HALO_WGRAD") == nullptr || getenv("GSB_TC_HALO_WGRAD")[0] != '0') {
-    int r = conv_halo_wgrad(subview(tiled, 1, 0, 0), subs, nmaps, taps, shv->c, conv ? 1 : 0, in->c, dout->c, dwp, st);
+    int r = conv_halo_wgrad(subview(tiled, 1, 0, 0), subs, nmaps, taps, shv->c, conv ? 1 : 0, in->c, dout->c, taps_total, ws,
+                            max_slices, used, st);
     if (r != 0) return r < 0 ? -1 : 0;
   }
   TcMaps maps;
   memset(&maps, 0, sizeof(maps));
   int tw, th, tn;
   pick_box(tiled->w, tiled->h, 64, tw, th, tn);
-  for (int i = 0; i < nmaps; ++i)
-    if (make_act_map(&maps.in[i], subs[i], tw, th, tn)) return -1;
-  for (int i = nmaps; i < 4; ++i) maps.in[i] = maps.in[0];
-  SubView tv = subview(tiled, 1, 0, 0);
-  if (make_act_map(&maps.w, tv, tw, th, tn)) return -1;
-  maps.out = maps.w;
+  if (ws != nullptr) {
+    for (int i = 0; i < nmaps; ++i)
+      if (make_act_map(&maps.in[i], subs[i], tw, th, tn)) return -1;
+    for (int i = nmaps; i < 4; ++i) maps.in[i] = maps.in[0];
+    SubView tv = subview(tiled, 1, 0, 0);
+    if (make_act_map(&maps.w, tv, tw, th, tn)) return -1;
+    maps.out = maps.w;
+  }
   const int b_ch = tiled->c;
   const int BN = (b_ch % 128 == 0) ? 128 : 64;
   WgParams p;
@@ -666,16 +671,26 @@ int conv_wgrad_tc(const gsb_view* in, const gsb_view* dout, float* dwp, const gs
   p.n_tiles = b_ch / BN;
   p.a_is_in = conv ? 1 : 0;
   p.cin = in->c; p.cout = dout->c;
-  p.dwp = dwp;
+  p.dwp = ws;
+  p.slice_elems = (int64_t)taps_total * dout->c * in->c;
   const int m_tiles = (p.a_blocks + 1) / 2;
   const int64_t base = (int64_t)m_tiles * p.n_tiles;
   int64_t want = ((int64_t)num_sms_avail() * 2 + base - 1) / base;  // ~2 waves
   int64_t max_split = (p.boxes + 15) / 16;                    // >= 16 k-steps per CTA
   if (max_split < 1) max_split = 1;
+  if (ws != nullptr && max_split > max_slices) max_split = max_slices;
   int64_t split = want < 1 ? 1 : (want > max_split ? max_split : want);
   p.boxes_per_split = (int)((p.boxes + split - 1) / split);
   split = (p.boxes + p.boxes_per_split - 1) / p.boxes_per_split;
   GSB_REQUIRE(split <= 65535, "conv_wgrad_tc: split too large");
+  *used = (int)split;
+  if (ws == nullptr) return 0;
+  GSB_REQUIRE(split <= max_slices, "conv_wgrad_tc: %d slices needed, workspace holds %d", (int)split, max_slices);
+  if (taps.ntaps != taps_total) {
+    // taps whose parity sub-view is empty never hit (inputs narrower than the stride): their entries stay zero
+    cudaError_t e = cudaMemsetAsync(ws, 0, (size_t)split * p.slice_elems * sizeof(float), st);
+    GSB_REQUIRE(e == cudaSuccess, "conv_wgrad_tc: memset failed: %s", cudaGetErrorString(e));
+  }
   if (BN == 128) return launch_tc(conv_tc_wgrad_kernel<128>, (int)base, (int)split, WgradCfg<128>::SMEM, maps, taps, p, st);
   return launch_tc(conv_tc_wgrad_kernel<64>, (int)base, (int)split, WgradCfg<64>::SMEM, maps, taps, p, st);
 }

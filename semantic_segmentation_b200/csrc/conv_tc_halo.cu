@@ -393,7 +393,9 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
 // an N-tile = BN channels of the TILED tensor, and a range of 8x16-pixel boxes (split-K).  The shifted boxes are
 // loaded with a vertical halo (8 x (16+ndy-1) pixels); the ndy vertical taps are K-row shifts of +1024 B and
 // accumulate into ndy separate TMEM accumulators, so one pass over the pixels produces all vertical taps:
-// 3x less operand traffic than one (tap, block) pair per CTA.  Epilogue: fp32 red.global.add into dWp.
+// 3x less operand traffic than one (tap, block) pair per CTA.  Epilogue: split s stores its fp32 partial sums into slice
+// s of the caller's workspace with plain stores (every slice is written completely); the slices are added in slice
+// order by the un-pack kernel, so the result does not depend on the order in which CTAs finish (was: red.global.add).
 // ------------------------------------------------------------------------------------------------------
 struct WgHaloParams {
   int tiles_x, tiles_y;  // 8x16 pixel boxes per image
@@ -403,7 +405,8 @@ struct WgHaloParams {
   int a_is_in;              // 1: shifted side is the forward input (rows = ci), 0: it is dY (rows = co)
   int cin, cout;
   int a_block_bytes, nstages;
-  float* dwp;
+  float* dwp;            // slice workspace [split][taps][cout][cin]
+  int64_t slice_elems;
 };
 
 template <int BN>
@@ -505,6 +508,7 @@ conv_tc_wgrad_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_cons
     const int a_ch = rvalid ? (blk % p.a_cblocks) * 64 + (row & 63) : 0;
     mbar_wait(tfull, 0);
     tc_fence_after();
+    float* __restrict__ slice = p.dwp + (int64_t)blockIdx.y * p.slice_elems;
 #pragma unroll 1
     for (int j = 0; j < p.ndy; ++j) {
       const int tap = (int)plan.wtap[g][j];
@@ -518,7 +522,7 @@ conv_tc_wgrad_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_cons
             const int b_ch = nt * BN + ch * 32 + i;
             const int64_t idx = p.a_is_in ? ((int64_t)tap * p.cout + b_ch) * p.cin + a_ch
                                           : ((int64_t)tap * p.cout + a_ch) * p.cin + b_ch;
-            atomicAdd(p.dwp + idx, __uint_as_float(v[i]));
+            slice[idx] = __uint_as_float(v[i]);
           }
         }
       }
@@ -740,24 +744,29 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
   return 1;
 }
 
-// Weight gradient through the halo kernel.  Returns 1 when launched, 0 when not applicable, -1 on error.
+// Weight gradient through the halo kernel.  Returns 1 when launched (or planned), 0 when not applicable, -1 on error.
+// ws = slice workspace [max_slices][taps_total * cout * cin]; *used = slices written (each completely).  ws == nullptr:
+// plan only (*used = the split the launch would take).
 int conv_halo_wgrad(const SubView& tiled, const SubView* shifted, int nmaps, const TcTaps& taps, int shifted_c, int a_is_in,
-                    int cin, int cout, float* dwp, cudaStream_t st) {
+                    int cin, int cout, int taps_total, float* ws, int max_slices, int* used, cudaStream_t st) {
   if (!halo_enabled() || tiled.W < 8 || tiled.H < 16) return 0;
   HaloPlan plan;
   int max_ndy;
   bool uniform;
   if (!build_halo_plan(taps, plan, max_ndy, uniform) || !uniform) return 0;
+  if (taps.ntaps != taps_total) return 0;   // a skipped tap would leave its slice entries unwritten
   const int BN = (tiled.C % 128 == 0) ? 128 : 64;
   if (max_ndy * BN > (BN == 128 ? 512 : 256)) return 0;
   const int boxh = 16 + max_ndy - 1;
   TcMaps maps;
   memset(&maps, 0, sizeof(maps));
-  for (int i = 0; i < nmaps; ++i)
-    if (make_act_map(&maps.in[i], shifted[i], 8, boxh, 1)) return -1;
-  for (int i = nmaps; i < 4; ++i) maps.in[i] = maps.in[0];
-  if (make_act_map(&maps.w, tiled, 8, 16, 1)) return -1;
-  maps.out = maps.w;
+  if (ws != nullptr) {
+    for (int i = 0; i < nmaps; ++i)
+      if (make_act_map(&maps.in[i], shifted[i], 8, boxh, 1)) return -1;
+    for (int i = nmaps; i < 4; ++i) maps.in[i] = maps.in[0];
+    if (make_act_map(&maps.w, tiled, 8, 16, 1)) return -1;
+    maps.out = maps.w;
+  }
   WgHaloParams p;
   p.tiles_x = ((int)tiled.W + 7) / 8;
   p.tiles_y = ((int)tiled.H + 15) / 16;
@@ -769,7 +778,8 @@ int conv_halo_wgrad(const SubView& tiled, const SubView* shifted, int nmaps, con
   p.a_is_in = a_is_in;
   p.cin = cin; p.cout = cout;
   p.a_block_bytes = 8 * boxh * 128;
-  p.dwp = dwp;
+  p.dwp = ws;
+  p.slice_elems = (int64_t)taps_total * cout * cin;
   const int stage_bytes = 2 * p.a_block_bytes + (BN / 64) * 16384;
   int nst = (232448 - 1024 - 256) / stage_bytes;
   p.nstages = nst > 8 ? 8 : nst;
@@ -779,6 +789,7 @@ int conv_halo_wgrad(const SubView& tiled, const SubView* shifted, int nmaps, con
   // split-K over the pixel boxes: fill whole waves of SMs, keep >= 2 boxes per CTA
   const int sms = num_sms_avail();
   int max_split = p.boxes / 2 > 0 ? p.boxes / 2 : 1;
+  if (ws != nullptr && max_split > max_slices) max_split = max_slices;
   int best = 1;
   double best_eff = 0.0;
   for (int sp = 1; sp <= max_split && sp <= 4 * sms; ++sp) {
@@ -791,6 +802,9 @@ int conv_halo_wgrad(const SubView& tiled, const SubView* shifted, int nmaps, con
   p.boxes_per_split = (p.boxes + best - 1) / best;
   const int split = (p.boxes + p.boxes_per_split - 1) / p.boxes_per_split;
   GSB_REQUIRE(split <= 65535, "conv_halo_wgrad: split too large");
+  *used = split;
+  if (ws == nullptr) return 1;
+  GSB_REQUIRE(split <= max_slices, "conv_halo_wgrad: %d slices needed, workspace holds %d", split, max_slices);
   const int smem = 1024 + 256 + p.nstages * stage_bytes;
   cudaError_t e;
   if (BN == 128) {

@@ -66,7 +66,10 @@ __global__ void __launch_bounds__(256) stem_fwd_kernel(const float* __restrict__
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// stem weight gradient: dw[co][tap] += sum_pix dY[pix][co] * x[pix@tap]; TP taps per pass kept in registers
+// stem weight gradient: dw[co][tap] = sum_pix dY[pix][co] * x[pix@tap]; TP taps per pass kept in registers.
+// Deterministic reduction (all weight-gradient kernels of this file): the pixel lanes of a CTA add their registers into
+// shared memory one lane after the other, the CTA STORES its sums into row blockIdx.x of a partial buffer, and
+// gsb::sum_slices adds the rows in row order.  No atomics: two runs give the same bits.
 // ---------------------------------------------------------------------------------------------------------
 template <typename T, int TP>
 __global__ void __launch_bounds__(256) stem_wgrad_kernel(const float* __restrict__ x, int N, int Cin, int H, int W,
@@ -111,15 +114,20 @@ __global__ void __launch_bounds__(256) stem_wgrad_kernel(const float* __restrict
       }
     }
   }
+  for (int l = 0; l < lanes; ++l) {
+    if (lane == l) {
 #pragma unroll
-  for (int t = 0; t < TP; ++t)
+      for (int t = 0; t < TP; ++t)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) atomicAdd(&sacc[(g * TP + t) * 8 + j], acc[t][j]);
-  __syncthreads();
+        for (int j = 0; j < 8; ++j) sacc[(g * TP + t) * 8 + j] += acc[t][j];
+    }
+    __syncthreads();
+  }
+  float* __restrict__ row = dw + (int64_t)blockIdx.x * Cout * taps;
   for (int i = threadIdx.x; i < G * TP * 8; i += blockDim.x) {
     const int j = i % 8, t = (i / 8) % TP, gg = i / (8 * TP);
     const int tap = tap0 + t;
-    if (tap < taps) atomicAdd(dw + (int64_t)(gg * 8 + j) * taps + tap, sacc[i]);
+    if (tap < taps) row[(int64_t)(gg * 8 + j) * taps + tap] = sacc[i];
   }
 }
 
@@ -235,14 +243,20 @@ __global__ void __launch_bounds__(256, 2) stem_fwd_fast_kernel(const float* __re
     }
   }
   if (stats != nullptr) {
+    // threads sharing a channel group add in a fixed order (deterministic statistics rows)
+    const unsigned lanes = blockDim.x / G, lane = threadIdx.x / G;
+    for (unsigned l = 0; l < lanes; ++l) {
+      if (lane == l) {
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      atomicAdd(&red[g * 8 + 2 * j], s0[j].x);
-      atomicAdd(&red[g * 8 + 2 * j + 1], s0[j].y);
-      atomicAdd(&red[Cout + g * 8 + 2 * j], s1[j].x);
-      atomicAdd(&red[Cout + g * 8 + 2 * j + 1], s1[j].y);
+        for (int j = 0; j < 4; ++j) {
+          red[g * 8 + 2 * j] += s0[j].x;
+          red[g * 8 + 2 * j + 1] += s0[j].y;
+          red[Cout + g * 8 + 2 * j] += s1[j].x;
+          red[Cout + g * 8 + 2 * j + 1] += s1[j].y;
+        }
+      }
+      __syncthreads();
     }
-    __syncthreads();
     for (int i = threadIdx.x; i < 2 * Cout; i += blockDim.x) stats[(int64_t)blockIdx.x * 2 * Cout + i] = red[i];
   }
 }
@@ -316,18 +330,23 @@ __global__ void __launch_bounds__(256, 2) stem_wgrad_fast_kernel(const float* __
         }
     }
   }
+  for (unsigned l = 0; l < lanes; ++l) {
+    if (lane == l) {
 #pragma unroll
-  for (int t = 0; t < KT; ++t)
+      for (int t = 0; t < KT; ++t)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      atomicAdd(&sacc[(g * KT + t) * 8 + 2 * j], acc[t][j].x);
-      atomicAdd(&sacc[(g * KT + t) * 8 + 2 * j + 1], acc[t][j].y);
+        for (int j = 0; j < 4; ++j) {
+          sacc[(g * KT + t) * 8 + 2 * j] += acc[t][j].x;
+          sacc[(g * KT + t) * 8 + 2 * j + 1] += acc[t][j].y;
+        }
     }
-  __syncthreads();
+    __syncthreads();
+  }
   const int taps = Cin * K * K;
+  float* __restrict__ row = dw + (int64_t)blockIdx.x * Cout * taps;   // partial row of this CTA column
   for (int i = threadIdx.x; i < (int)G * KT * 8; i += blockDim.x) {
     const int j = i % 8, t = (i / 8) % KT, gg = i / (8 * KT);
-    atomicAdd(dw + (int64_t)(gg * 8 + j) * taps + ci * K * K + ky0 * K + t, sacc[i]);
+    row[(int64_t)(gg * 8 + j) * taps + ci * K * K + ky0 * K + t] = sacc[i];
   }
 }
 
@@ -470,23 +489,29 @@ __global__ void __launch_bounds__(256, 4) head_bwd_kernel(const T* __restrict__ 
       if (valid[u] && dx != nullptr) Vec8<T>::store(dx + (int64_t)(p0 + u * pstep) * dxld + g * 8, o);
     }
   }
-  if (dw != nullptr) {
+  // deterministic: lanes add in lane order, the CTA stores row blockIdx.x = [dw (C*K) | db (C)] of the partial buffer
+  for (unsigned l = 0; l < lanes; ++l) {
+    if (lane == l) {
+      if (dw != nullptr) {
 #pragma unroll
-    for (int c = 0; c < CT; ++c)
-      if (c < C) {
+        for (int c = 0; c < CT; ++c)
+          if (c < C) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) atomicAdd(&sdw[c * K + g * 8 + j], aw[c][j]);
+            for (int j = 0; j < 8; ++j) sdw[c * K + g * 8 + j] += aw[c][j];
+          }
       }
-  }
-  if (db != nullptr && g == 0) {
+      if (db != nullptr && g == 0) {
 #pragma unroll
-    for (int c = 0; c < CT; ++c)
-      if (c < C) atomicAdd(&sdb[c], ab[c]);
+        for (int c = 0; c < CT; ++c)
+          if (c < C) sdb[c] += ab[c];
+      }
+    }
+    __syncthreads();
   }
-  __syncthreads();
+  const int rowlen = C * K + kHeadMaxC;
   if (dw != nullptr)
-    for (int i = threadIdx.x; i < C * K; i += blockDim.x) atomicAdd(dw + i, sdw[i]);
-  if (db != nullptr && threadIdx.x < C) atomicAdd(db + threadIdx.x, sdb[threadIdx.x]);
+    for (int i = threadIdx.x; i < C * K; i += blockDim.x) dw[(int64_t)blockIdx.x * rowlen + i] = sdw[i];
+  if (db != nullptr && threadIdx.x < C) db[(int64_t)blockIdx.x * rowlen + threadIdx.x] = sdb[threadIdx.x];
 }
 
 static int grid_cap(int64_t want, int per_sm) {
@@ -551,42 +576,56 @@ extern "C" int gsb_stem_conv_fwd(const float* x, int n, int cin, int h, int w, c
   return check_launch("stem_conv_fwd");
 }
 
+// Partial rows of stem_conv_wgrad (row = cout * cin*k*k floats) and head_conv_bwd (row = c * x.c + 8 floats): the workspace
+// should hold gsb_edge_rows() rows; with fewer the launch uses fewer CTA columns.
+extern "C" int gsb_edge_rows(void) { return num_sms() * 4; }
+
 extern "C" int gsb_stem_conv_wgrad(const float* x, int n, int cin, int h, int w, const gsb_view* dy, int k, int stride, int pad,
-                                   float* dweight, gsb_stream s) {
+                                   float* dweight, void* workspace, size_t workspace_bytes, gsb_stream s) {
   if (stem_check(x, dy, cin, k)) return -1;
-  GSB_REQUIRE(dweight && dy->n == n, "stem_conv_wgrad: bad argument");
+  GSB_REQUIRE(dweight && dy->n == n && workspace, "stem_conv_wgrad: bad argument");
   const int cout = dy->c, taps = cin * k * k;
   constexpr int TP = 9;
-  cudaMemsetAsync(dweight, 0, (size_t)cout * taps * sizeof(float), to_stream(s));
   const int G = cout / 8, lanes = 256 / G;
+  const size_t row_bytes = (size_t)cout * taps * sizeof(float);
+  const int64_t max_rows = (int64_t)(workspace_bytes / row_bytes);
+  GSB_REQUIRE(max_rows >= 1, "stem_conv_wgrad: workspace too small");
+  float* partial = reinterpret_cast<float*>(workspace);
+  auto rows_for = [&](int64_t want, int per_sm) {
+    int g = grid_cap(want, per_sm);
+    return (int)(g > max_rows ? max_rows : g);
+  };
   if (k == 3 && stride == 1 && num_pixels(dy) < (int64_t)1 << 31) {
     constexpr int PX = 4;
     const int64_t items = (int64_t)dy->n * dy->h * ((dy->w + PX - 1) / PX);
-    int gx = grid_cap((items + lanes - 1) / lanes, 4);
+    int gx = rows_for((items + lanes - 1) / lanes, 4);
     size_t smem = (size_t)G * 9 * 8 * sizeof(float);
     EDGE_DISPATCH_T(dy->dtype, gsb::launch(stem_wgrad_fast_kernel<T, PX, 3, 1, 3>, gsb::LaunchCfg(dim3(gx, cin), 256, smem, to_stream(s)), 
-                                   x, n, cin, h, w, (const T*)dy->ptr, dy->sw, dy->h, dy->w, cout, pad, dweight));
-    return check_launch("stem_conv_wgrad");
+                                   x, n, cin, h, w, (const T*)dy->ptr, dy->sw, dy->h, dy->w, cout, pad, partial));
+    gsb::sum_slices(partial, gx, (int64_t)cout * taps, (int64_t)cout * taps, dweight, 0, to_stream(s));
+    return check_launch("stem_conv_wgrad", 2);
   }
   if (k == 4 && stride == 2 && num_pixels(dy) < (int64_t)1 << 31 && getenv("GSB_STEM_WGRAD_FAST42") == nullptr) {
     // first convolutions of the Pix2Pix generator (1 -> 64) and discriminator (2 -> 64): one launch instead of
     // cin * 16 / 9 launches of the generic kernel (0.75 ms per Pix2Pix step, profiles/r01r)
     constexpr int PX = 2;
     const int64_t items = (int64_t)dy->n * dy->h * ((dy->w + PX - 1) / PX);
-    int gx = grid_cap((items + lanes - 1) / lanes, 2);
+    int gx = rows_for((items + lanes - 1) / lanes, 2);
     size_t smem = (size_t)G * 8 * 8 * sizeof(float);
     EDGE_DISPATCH_T(dy->dtype, gsb::launch(stem_wgrad_fast_kernel<T, PX, 4, 2, 2>, gsb::LaunchCfg(dim3(gx, cin, 2), 256, smem, to_stream(s)), 
-                                   x, n, cin, h, w, (const T*)dy->ptr, dy->sw, dy->h, dy->w, cout, pad, dweight));
-    return check_launch("stem_conv_wgrad");
+                                   x, n, cin, h, w, (const T*)dy->ptr, dy->sw, dy->h, dy->w, cout, pad, partial));
+    gsb::sum_slices(partial, gx, (int64_t)cout * taps, (int64_t)cout * taps, dweight, 0, to_stream(s));
+    return check_launch("stem_conv_wgrad", 2);
   }
-  int grid = grid_cap((num_pixels(dy) + lanes - 1) / lanes, 4);
+  int grid = rows_for((num_pixels(dy) + lanes - 1) / lanes, 4);
   size_t smem = (size_t)G * TP * 8 * sizeof(float);
   int launches = 0;
   for (int tap0 = 0; tap0 < taps; tap0 += TP, ++launches) {
     EDGE_DISPATCH_T(dy->dtype, gsb::launch(stem_wgrad_kernel<T, TP>, gsb::LaunchCfg(grid, 256, smem, to_stream(s)), 
-                                   x, n, cin, h, w, (const T*)dy->ptr, dy->sw, dy->h, dy->w, cout, k, stride, pad, tap0, dweight));
+                                   x, n, cin, h, w, (const T*)dy->ptr, dy->sw, dy->h, dy->w, cout, k, stride, pad, tap0, partial));
   }
-  return check_launch("stem_conv_wgrad", launches);
+  gsb::sum_slices(partial, grid, (int64_t)cout * taps, (int64_t)cout * taps, dweight, 0, to_stream(s));
+  return check_launch("stem_conv_wgrad", launches + 1);
 }
 
 static int head_check(const gsb_view* x, int c) {
@@ -614,26 +653,37 @@ extern "C" int gsb_head_conv_fwd(const gsb_view* x, const float* weight, const f
 }
 
 extern "C" int gsb_head_conv_bwd(const gsb_view* x, const float* weight, int c, const float* dlogits, const gsb_view* dx,
-                                 float* dweight, float* dbias, gsb_stream s) {
+                                 float* dweight, float* dbias, void* workspace, size_t workspace_bytes, gsb_stream s) {
   if (head_check(x, c)) return -1;
   GSB_REQUIRE(weight && dlogits, "head_conv_bwd: null pointer");
+  GSB_REQUIRE(workspace || (!dweight && !dbias), "head_conv_bwd: workspace required for the parameter gradients");
   if (dx && dx->ptr)
     GSB_REQUIRE(vec8_ok(dx) && dx->c == x->c && num_pixels(dx) == num_pixels(x) && dx->dtype == x->dtype, "head_conv_bwd: dx mismatch");
   const int64_t P = num_pixels(x), HW = (int64_t)x->h * x->w;
   const int K = x->c, G = K / 8, lanes = 256 / G;
-  if (dweight) cudaMemsetAsync(dweight, 0, (size_t)c * K * sizeof(float), to_stream(s));
-  if (dbias) cudaMemsetAsync(dbias, 0, (size_t)c * sizeof(float), to_stream(s));
   int grid = grid_cap((P + lanes - 1) / lanes, 4);
+  const int rowlen = c * K + kHeadMaxC;
+  float* partial = reinterpret_cast<float*>(workspace);
+  if (dweight || dbias) {
+    const int64_t max_rows = (int64_t)(workspace_bytes / ((size_t)rowlen * sizeof(float)));
+    GSB_REQUIRE(max_rows >= 1, "head_conv_bwd: workspace too small");
+    if (grid > max_rows) grid = (int)max_rows;
+  }
+  float* pdw = dweight ? partial : nullptr;
+  float* pdb = dbias ? partial + (size_t)c * K : nullptr;
   size_t smem = (size_t)(2 * c * K + c) * sizeof(float);
   GSB_REQUIRE(P < ((int64_t)1 << 31), "head_conv_bwd: too many pixels");
   if (c <= 2) {
     EDGE_DISPATCH_T(x->dtype, gsb::launch(head_bwd_kernel<T, 2>, gsb::LaunchCfg(grid, 256, smem, to_stream(s)), 
                                   (const T*)x->ptr, x->sw, (unsigned)P, (unsigned)HW, K, c, weight, dlogits,
-                                  (dx && dx->ptr) ? (T*)dx->ptr : nullptr, dx ? dx->sw : 0, dweight, dbias));
+                                  (dx && dx->ptr) ? (T*)dx->ptr : nullptr, dx ? dx->sw : 0, pdw, pdb));
   } else {
     EDGE_DISPATCH_T(x->dtype, gsb::launch(head_bwd_kernel<T, 8>, gsb::LaunchCfg(grid, 256, smem, to_stream(s)), 
                                   (const T*)x->ptr, x->sw, (unsigned)P, (unsigned)HW, K, c, weight, dlogits,
-                                  (dx && dx->ptr) ? (T*)dx->ptr : nullptr, dx ? dx->sw : 0, dweight, dbias));
+                                  (dx && dx->ptr) ? (T*)dx->ptr : nullptr, dx ? dx->sw : 0, pdw, pdb));
   }
-  return check_launch("head_conv_bwd");
+  int launches = 1;
+  if (dweight) { gsb::sum_slices(pdw, grid, rowlen, (int64_t)c * K, dweight, 0, to_stream(s)); ++launches; }
+  if (dbias) { gsb::sum_slices(pdb, grid, rowlen, c, dbias, 0, to_stream(s)); ++launches; }
+  return check_launch("head_conv_bwd", launches);
 }

@@ -5,7 +5,8 @@
 namespace gsb {
 
 static int run_layout_multi(bool pack, int n, const void* const* src, void* const* dst, const int* d0, const int* d1,
-                            const int* taps, const int* rows_from_d0, int dst_dtype, int accumulate, cudaStream_t st);
+                            const int* taps, const int* rows_from_d0, const int* nslices, int dst_dtype, int accumulate,
+                            cudaStream_t st);
 
 
 struct CView {
@@ -103,7 +104,8 @@ __global__ void merge_upconv_kernel(const float* __restrict__ w4, const float* _
     for (int c = threadIdx.x; c < cout; c += blockDim.x) bm[c] = w[0] * b4[c] + w[1] * b6[c] + w[2] * b8[c];
 }
 
-// dots[3] += <crop_i(dWm), W_i> (+ <db, b_i>);  dW_i = w_i * crop_i(dWm)
+// dots[blockIdx.x][3] = this CTA's part of <crop_i(dWm), W_i> (+ <db, b_i>);  dW_i = w_i * crop_i(dWm).
+// The per-CTA rows are added in row order by dalpha_kernel (deterministic, no atomics).
 __global__ void unmerge_upconv_kernel(const float* __restrict__ dwm, const float* dbm, const float* __restrict__ w4,
                                       const float* __restrict__ w6, const float* __restrict__ w8, const float* b4,
                                       const float* b6, const float* b8, const float* __restrict__ alpha, int64_t pairs,
@@ -150,20 +152,50 @@ __global__ void unmerge_upconv_kernel(const float* __restrict__ dwm, const float
       d0 = fmaf(g, b4[c], d0); d1 = fmaf(g, b6[c], d1); d2 = fmaf(g, b8[c], d2);
     }
   }
+  __shared__ double sred[8][3];
   d0 = warp_sum(d0); d1 = warp_sum(d1); d2 = warp_sum(d2);
   if ((threadIdx.x & 31) == 0) {
-    atomicAdd(dots + 0, (double)d0);
-    atomicAdd(dots + 1, (double)d1);
-    atomicAdd(dots + 2, (double)d2);
+    sred[threadIdx.x >> 5][0] = (double)d0;
+    sred[threadIdx.x >> 5][1] = (double)d1;
+    sred[threadIdx.x >> 5][2] = (double)d2;
+  }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    double t = 0.0;
+    for (int w_ = 0; w_ < (int)(blockDim.x >> 5); ++w_) t += sred[w_][threadIdx.x];
+    dots[(int64_t)blockIdx.x * 3 + threadIdx.x] = t;
   }
 }
 
-__global__ void dalpha_kernel(const double* __restrict__ dots, const float* __restrict__ alpha, float* dalpha) {
+__global__ void __launch_bounds__(256) dalpha_kernel(const double* __restrict__ dots, int rows, const float* __restrict__ alpha,
+                                                    float* dalpha) {
   GSB_PDL_ENTRY();
-  float w[3];
-  softmax3(alpha, w);
-  double mean = w[0] * dots[0] + w[1] * dots[1] + w[2] * dots[2];
-  for (int j = 0; j < 3; ++j) dalpha[j] += (float)(w[j] * (dots[j] - mean));
+  __shared__ double sh[8][3];
+  __shared__ double tot[3];
+  double a[3] = {0.0, 0.0, 0.0};
+  for (int r = threadIdx.x; r < rows; r += blockDim.x) {
+    a[0] += dots[(int64_t)r * 3 + 0]; a[1] += dots[(int64_t)r * 3 + 1]; a[2] += dots[(int64_t)r * 3 + 2];
+  }
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    double v = a[j];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5][j] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    double t = 0.0;
+    for (int w_ = 0; w_ < 8; ++w_) t += sh[w_][threadIdx.x];
+    tot[threadIdx.x] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float w[3];
+    softmax3(alpha, w);
+    double mean = w[0] * tot[0] + w[1] * tot[1] + w[2] * tot[2];
+    for (int j = 0; j < 3; ++j) dalpha[j] += (float)(w[j] * (tot[j] - mean));
+  }
 }
 
 static int ew_grid(int64_t total) {
@@ -191,16 +223,16 @@ extern "C" int gsb_pack_weight(const float* src, int d0, int d1, int kh, int kw,
   const void* srcs[1] = {src};
   void* dsts[1] = {dst};
   const int taps = kh * kw;
-  return gsb::run_layout_multi(true, 1, srcs, dsts, &d0, &d1, &taps, &rows_from_d0, dst_dtype, 0, to_stream(s));
+  return gsb::run_layout_multi(true, 1, srcs, dsts, &d0, &d1, &taps, &rows_from_d0, nullptr, dst_dtype, 0, to_stream(s));
 }
 
-extern "C" int gsb_unpack_wgrad(const float* src, int d0, int d1, int kh, int kw, int rows_from_d0, float* dst,
+extern "C" int gsb_unpack_wgrad(const float* src, int nslices, int d0, int d1, int kh, int kw, int rows_from_d0, float* dst,
                                 int accumulate, gsb_stream s) {
-  GSB_REQUIRE(src && dst, "unpack_wgrad: null pointer");
+  GSB_REQUIRE(src && dst && nslices >= 1, "unpack_wgrad: bad argument");
   const void* srcs[1] = {src};
   void* dsts[1] = {dst};
   const int taps = kh * kw;
-  return gsb::run_layout_multi(false, 1, srcs, dsts, &d0, &d1, &taps, &rows_from_d0, GSB_F32, accumulate, to_stream(s));
+  return gsb::run_layout_multi(false, 1, srcs, dsts, &d0, &d1, &taps, &rows_from_d0, &nslices, GSB_F32, accumulate, to_stream(s));
 }
 
 extern "C" int gsb_merge_upconv(const float* w4, const float* w6, const float* w8, const float* b4, const float* b6,
@@ -221,12 +253,13 @@ extern "C" int gsb_unmerge_upconv(const float* dw_merged, const float* db_merged
   GSB_REQUIRE(dw_merged && w4 && w6 && w8 && alpha && dw4 && dw6 && dw8 && dalpha, "unmerge_upconv: null pointer");
   GSB_REQUIRE(workspace && workspace_bytes >= 3 * sizeof(double), "unmerge_upconv: workspace too small");
   GSB_REQUIRE(db_merged == nullptr || (b4 && b6 && b8 && db4 && db6 && db8), "unmerge_upconv: biases missing");
-  double* dots = reinterpret_cast<double*>(workspace);
-  cudaMemsetAsync(dots, 0, 3 * sizeof(double), to_stream(s));
+  double* dots = reinterpret_cast<double*>(workspace);   // one row of 3 partial dot products per CTA
   int64_t pairs = (int64_t)cin * cout;
-  gsb::launch(unmerge_upconv_kernel, gsb::LaunchCfg(ew_grid(pairs * 8), 256, 0, to_stream(s)), dw_merged, db_merged, w4, w6, w8, b4, b6, b8, alpha,
+  int grid = ew_grid(pairs * 8);
+  if ((size_t)grid * 3 * sizeof(double) > workspace_bytes) grid = (int)(workspace_bytes / (3 * sizeof(double)));
+  gsb::launch(unmerge_upconv_kernel, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), dw_merged, db_merged, w4, w6, w8, b4, b6, b8, alpha,
                                                                       pairs, cout, dw4, dw6, dw8, db4, db6, db8, dots);
-  gsb::launch(dalpha_kernel, gsb::LaunchCfg(1, 1, 0, to_stream(s)), dots, alpha, dalpha);
+  gsb::launch(dalpha_kernel, gsb::LaunchCfg(1, 256, 0, to_stream(s)), (const double*)dots, grid, alpha, dalpha);
   return check_launch("unmerge_upconv", 2);
 }
 
@@ -241,6 +274,7 @@ struct LayoutJobs {
   void* dst[kMaxLayoutJobs];
   int d0[kMaxLayoutJobs], d1[kMaxLayoutJobs], taps[kMaxLayoutJobs];
   int blk0[kMaxLayoutJobs + 1];
+  int nslices[kMaxLayoutJobs];   // un-pack: the packed source holds this many partial-sum slices, added in slice order
   uint8_t rows_from_d0[kMaxLayoutJobs];
   int count, dst_dtype, accumulate;
 };
@@ -273,13 +307,14 @@ static int layout_tiles_host(int d0, int d1, int taps) {
 template <bool PACK, int TT>
 __device__ __forceinline__ void layout_tile(const float* __restrict__ tsrc, float* __restrict__ tdst, const float* __restrict__ psrc,
                                             void* __restrict__ pdst, int pdtype, int d0, int d1, int taps, int rfd, int tile,
-                                            int accumulate, float* sm) {
+                                            int accumulate, int nslices, float* sm) {
   const int tt = TT > 0 ? TT : (taps < kTTmax ? taps : kTTmax);
   const int n1 = (d1 + kTI1 - 1) / kTI1, nt = (taps + tt - 1) / tt;
   const int tc = tile % nt, b1 = (tile / nt) % n1, b0 = tile / (nt * n1);
   const int i0b = b0 * kTI0, i1b = b1 * kTI1, tb = tc * tt;
   const int rows = rfd ? d0 : d1, cols = rfd ? d1 : d0;
   const int nA = kTI0 * kTI1 * tt;
+  const int64_t slice_stride = (int64_t)taps * rows * cols;
   auto torch_side = [&](bool load) {
     for (int idx = threadIdx.x; idx < nA; idx += blockDim.x) {
       const int t = idx % tt, i1l = (idx / tt) % kTI1, i0l = idx / (tt * kTI1);
@@ -302,8 +337,11 @@ __device__ __forceinline__ void layout_tile(const float* __restrict__ tsrc, floa
         const int r = rfd ? i0 : i1, c = rfd ? i1 : i0;
         const int64_t off = ((int64_t)tap * rows + r) * cols + c;
         float* cell = sm + i0l * kTPitch0 + i1l * kTPitch1 + t;
-        if (load) *cell = psrc[off];
-        else st_elem(pdst, off, pdtype, *cell);
+        if (load) {
+          float acc = psrc[off];
+          for (int sl = 1; sl < nslices; ++sl) acc += psrc[(int64_t)sl * slice_stride + off];
+          *cell = acc;
+        } else st_elem(pdst, off, pdtype, *cell);
       }
     }
   };
@@ -317,7 +355,7 @@ __device__ __forceinline__ void layout_tile(const float* __restrict__ tsrc, floa
   // aligned when the tile spans all taps (rows of 32 * taps floats) or when the tap chunk itself is a multiple of 4
   const bool vec_t = full && (tt == taps ? (((int64_t)d1 * taps) % 4 == 0) : (tt % 4 == 0 && taps % 4 == 0)) &&
                      ((reinterpret_cast<uintptr_t>(tptr) & 15) == 0);
-  const bool vec_p = full && (cols % 8 == 0) && ((reinterpret_cast<uintptr_t>(pptr) & 15) == 0);
+  const bool vec_p = full && (cols % 8 == 0) && ((reinterpret_cast<uintptr_t>(pptr) & 15) == 0) && (slice_stride % 4 == 0);
   auto torch_side_vec = [&](bool load) {
     const int per_row = kTI1 * tt;                       // floats per i0 row of the tile
     if (TT > 0 && load) {
@@ -391,7 +429,13 @@ __device__ __forceinline__ void layout_tile(const float* __restrict__ tsrc, floa
       float* cell = sm + i0l * kTPitch0 + i1l * kTPitch1 + t;
       const int step = rfd ? kTPitch1 : kTPitch0;          // next column = next i1 (rfd) or next i0
       if (load) {
-        const float4 a = *reinterpret_cast<const float4*>(psrc + off), b = *reinterpret_cast<const float4*>(psrc + off + 4);
+        float4 a = *reinterpret_cast<const float4*>(psrc + off), b = *reinterpret_cast<const float4*>(psrc + off + 4);
+        for (int sl = 1; sl < nslices; ++sl) {
+          const float* q = psrc + (int64_t)sl * slice_stride + off;
+          const float4 a2 = *reinterpret_cast<const float4*>(q), b2 = *reinterpret_cast<const float4*>(q + 4);
+          a.x += a2.x; a.y += a2.y; a.z += a2.z; a.w += a2.w;
+          b.x += b2.x; b.y += b2.y; b.z += b2.z; b.w += b2.w;
+        }
         cell[0] = a.x; cell[step] = a.y; cell[2 * step] = a.z; cell[3 * step] = a.w;
         cell[4 * step] = b.x; cell[5 * step] = b.y; cell[6 * step] = b.z; cell[7 * step] = b.w;
       } else {
@@ -421,7 +465,7 @@ __device__ __forceinline__ void layout_tile_dispatch(const LayoutJobs& J, int j,
   const float* psrc = PACK ? nullptr : reinterpret_cast<const float*>(J.src[j]);
   void* pdst = PACK ? J.dst[j] : nullptr;
   const int taps = J.taps[j], tt = taps < kTTmax ? taps : kTTmax;
-#define GSB_LT(N) layout_tile<PACK, N>(tsrc, tdst, psrc, pdst, J.dst_dtype, J.d0[j], J.d1[j], taps, J.rows_from_d0[j], tile, J.accumulate, sm)
+#define GSB_LT(N) layout_tile<PACK, N>(tsrc, tdst, psrc, pdst, J.dst_dtype, J.d0[j], J.d1[j], taps, J.rows_from_d0[j], tile, J.accumulate, PACK ? 1 : J.nslices[j], sm)
   switch (tt) {
     case 16: GSB_LT(16); break;
     case 9: GSB_LT(9); break;
@@ -447,7 +491,8 @@ __global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const __grid_co
 }
 
 static int run_layout_multi(bool pack, int n, const void* const* src, void* const* dst, const int* d0, const int* d1,
-                            const int* taps, const int* rows_from_d0, int dst_dtype, int accumulate, cudaStream_t st) {
+                            const int* taps, const int* rows_from_d0, const int* nslices, int dst_dtype, int accumulate,
+                            cudaStream_t st) {
   int launches = 0;
   for (int begin = 0; begin < n; begin += kMaxLayoutJobs) {
     LayoutJobs J;
@@ -462,6 +507,7 @@ static int run_layout_multi(bool pack, int n, const void* const* src, void* cons
       J.src[k] = src[i]; J.dst[k] = dst[i];
       J.d0[k] = d0[i]; J.d1[k] = d1[i]; J.taps[k] = taps[i];
       J.rows_from_d0[k] = (uint8_t)(rows_from_d0[i] != 0);
+      J.nslices[k] = (nslices != nullptr && nslices[i] > 1) ? nslices[i] : 1;
       J.blk0[k] = blocks;
       blocks += layout_tiles_host(d0[i], d1[i], taps[i]);
     }
@@ -479,12 +525,12 @@ extern "C" int gsb_pack_weight_multi(int n, const void* const* src, void* const*
                                      const int* taps, const int* rows_from_d0, int dst_dtype, gsb_stream s) {
   if (n <= 0) return 0;
   GSB_REQUIRE(src && dst && d0 && d1 && taps && rows_from_d0, "pack_weight_multi: null argument");
-  return gsb::run_layout_multi(true, n, src, dst, d0, d1, taps, rows_from_d0, dst_dtype, 0, gsb::to_stream(s));
+  return gsb::run_layout_multi(true, n, src, dst, d0, d1, taps, rows_from_d0, nullptr, dst_dtype, 0, gsb::to_stream(s));
 }
 
-extern "C" int gsb_unpack_wgrad_multi(int n, const void* const* src, void* const* dst, const int* d0, const int* d1,
-                                      const int* taps, const int* rows_from_d0, int accumulate, gsb_stream s) {
+extern "C" int gsb_unpack_wgrad_multi(int n, const void* const* src, const int* nslices, void* const* dst, const int* d0,
+                                      const int* d1, const int* taps, const int* rows_from_d0, int accumulate, gsb_stream s) {
   if (n <= 0) return 0;
-  GSB_REQUIRE(src && dst && d0 && d1 && taps && rows_from_d0, "unpack_wgrad_multi: null argument");
-  return gsb::run_layout_multi(false, n, src, dst, d0, d1, taps, rows_from_d0, GSB_F32, accumulate, gsb::to_stream(s));
+  GSB_REQUIRE(src && dst && d0 && d1 && taps && rows_from_d0 && nslices, "unpack_wgrad_multi: null argument");
+  return gsb::run_layout_multi(false, n, src, dst, d0, d1, taps, rows_from_d0, nslices, GSB_F32, accumulate, gsb::to_stream(s));
 }

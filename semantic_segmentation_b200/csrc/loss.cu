@@ -203,8 +203,9 @@ __global__ void __launch_bounds__(256) eval_counts_kernel(const float* __restric
     if (sc[i]) atomicAdd(&counts[(int64_t)n * K * 3 + i], (unsigned long long)sc[i]);
 }
 
+// partial[blockIdx.x][slice][3]: per-CTA sums, added in row order by sum_rows_kernel (deterministic, no atomics)
 __global__ void __launch_bounds__(256) dice_sums_kernel(const float* __restrict__ a, const float* __restrict__ b, int64_t inner,
-                                                       double* __restrict__ sums) {
+                                                       double* __restrict__ partial) {
   GSB_PDL_ENTRY();
   __shared__ double sh[8];
   const int64_t s = blockIdx.y;
@@ -219,13 +220,29 @@ __global__ void __launch_bounds__(256) dice_sums_kernel(const float* __restrict_
   }
   double r0 = block_sum_d((double)ab, sh), r1 = block_sum_d((double)sa, sh), r2 = block_sum_d((double)sb, sh);
   if (threadIdx.x == 0) {
-    atomicAdd(sums + s * 3 + 0, r0);
-    atomicAdd(sums + s * 3 + 1, r1);
-    atomicAdd(sums + s * 3 + 2, r2);
+    double* row = partial + ((int64_t)blockIdx.x * gridDim.y + s) * 3;
+    row[0] = r0; row[1] = r1; row[2] = r2;
   }
 }
 
-// mode 0 vanilla (BCE with logits), 1 lsgan (MSE), 2 wgangp.  acc (double) += sum of per-element loss.
+// sums[j] = (sum over rows of partial[r][j]) / divisor, fixed order (thread-strided, shuffle tree, warp sums in index order);
+// out_f (optional) receives the fp32 value of column 0
+__global__ void __launch_bounds__(256) sum_rows_kernel(const double* __restrict__ partial, int rows, int ncols, double divisor,
+                                                      double* __restrict__ sums, float* __restrict__ out_f) {
+  GSB_PDL_ENTRY();
+  __shared__ double sh[8];
+  for (int j = 0; j < ncols; ++j) {
+    double a = 0.0;
+    for (int r = threadIdx.x; r < rows; r += blockDim.x) a += partial[(int64_t)r * ncols + j];
+    a = block_sum_d(a, sh);
+    if (threadIdx.x == 0) {
+      if (sums) sums[j] = a / divisor;
+      if (out_f && j == 0) out_f[0] = (float)(a / divisor);
+    }
+  }
+}
+
+// mode 0 vanilla (BCE with logits), 1 lsgan (MSE), 2 wgangp.  acc[blockIdx.x] = this CTA's sum of the per-element loss.
 __global__ void __launch_bounds__(256) gan_loss_kernel(const float* __restrict__ pred, int64_t n, int mode, float label,
                                                       double* acc, const float* __restrict__ gscale, float* __restrict__ dpred) {
   GSB_PDL_ENTRY();
@@ -250,7 +267,7 @@ __global__ void __launch_bounds__(256) gan_loss_kernel(const float* __restrict__
   }
   if (acc) {
     double r = block_sum_d((double)l, sh);
-    if (threadIdx.x == 0) atomicAdd(acc, r);
+    if (threadIdx.x == 0) acc[blockIdx.x] = r;
   }
 }
 
@@ -267,7 +284,7 @@ __global__ void __launch_bounds__(256) l1_loss_kernel(const float* __restrict__ 
   }
   if (acc) {
     double r = block_sum_d((double)l, sh);
-    if (threadIdx.x == 0) atomicAdd(acc, r);
+    if (threadIdx.x == 0) acc[blockIdx.x] = r;
   }
 }
 
@@ -285,9 +302,6 @@ __global__ void __launch_bounds__(256) act_bwd_kernel(const float* __restrict__ 
     dx[i] = g * d;
   }
 }
-
-__global__ void mean_out_kernel(const double* acc, double n, float* out) {
-  GSB_PDL_ENTRY(); out[0] = (float)(acc[0] / n); }
 
 static int grid1d(int64_t total, int per_sm = 8) {
   int64_t b = (total + 255) / 256;
@@ -346,36 +360,50 @@ extern "C" int gsb_eval_counts(const float* logits, const int64_t* labels, int n
   return check_launch("eval_counts");
 }
 
-extern "C" int gsb_dice_sums(const float* a, const float* b, int64_t slices, int64_t inner, double* sums, gsb_stream s) {
-  GSB_REQUIRE(a && b && sums && slices > 0 && slices < 65536, "dice_sums: bad argument");
-  cudaMemsetAsync(sums, 0, (size_t)slices * 3 * sizeof(double), to_stream(s));
-  int gx = (int)((inner + 256 * 16 - 1) / (256 * 16));
+// workspace: fp64 partial rows [gx][slices][3]; gx = min(ceil(inner / 4096), 1024, what the workspace holds)
+extern "C" int gsb_dice_sums(const float* a, const float* b, int64_t slices, int64_t inner, double* sums, void* workspace,
+                             size_t workspace_bytes, gsb_stream s) {
+  GSB_REQUIRE(a && b && sums && workspace && slices > 0 && slices < 65536, "dice_sums: bad argument");
+  const size_t row_bytes = (size_t)slices * 3 * sizeof(double);
+  GSB_REQUIRE(workspace_bytes >= row_bytes, "dice_sums: workspace too small");
+  int64_t gx = (inner + 256 * 16 - 1) / (256 * 16);
   if (gx < 1) gx = 1;
   if (gx > 1024) gx = 1024;
+  if ((size_t)gx * row_bytes > workspace_bytes) gx = (int64_t)(workspace_bytes / row_bytes);
+  double* partial = reinterpret_cast<double*>(workspace);
   dim3 grid((unsigned)gx, (unsigned)slices);
-  gsb::launch(dice_sums_kernel, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), a, b, inner, sums);
-  return check_launch("dice_sums");
+  gsb::launch(dice_sums_kernel, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), a, b, inner, partial);
+  gsb::launch(sum_rows_kernel, gsb::LaunchCfg(1, 256, 0, to_stream(s)), (const double*)partial, (int)gx, (int)(slices * 3), 1.0, sums,
+              (float*)nullptr);
+  return check_launch("dice_sums", 2);
 }
 
+// workspace (forward value only): one double per CTA; the launch uses min(grid, workspace_bytes / 8) CTAs
 extern "C" int gsb_gan_loss(const float* pred, int64_t numel, int mode, float label, float* loss, const float* gscale,
-                            float* dpred, void* workspace, gsb_stream s) {
+                            float* dpred, void* workspace, size_t workspace_bytes, gsb_stream s) {
   GSB_REQUIRE(pred && numel > 0 && mode >= 0 && mode <= 2, "gan_loss: bad argument");
-  GSB_REQUIRE(loss == nullptr || workspace != nullptr, "gan_loss: workspace (8 bytes) required for the forward value");
+  GSB_REQUIRE(loss == nullptr || (workspace != nullptr && workspace_bytes >= sizeof(double)),
+              "gan_loss: workspace (>= 8 bytes) required for the forward value");
   double* acc = loss ? reinterpret_cast<double*>(workspace) : nullptr;
-  if (acc) cudaMemsetAsync(acc, 0, sizeof(double), to_stream(s));
-  gsb::launch(gan_loss_kernel, gsb::LaunchCfg(grid1d(numel, 4), 256, 0, to_stream(s)), pred, numel, mode, label, acc, gscale, dpred);
-  if (acc) gsb::launch(mean_out_kernel, gsb::LaunchCfg(1, 1, 0, to_stream(s)), acc, (double)numel, loss);
+  int grid = grid1d(numel, 4);
+  if (acc && (size_t)grid * sizeof(double) > workspace_bytes) grid = (int)(workspace_bytes / sizeof(double));
+  gsb::launch(gan_loss_kernel, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), pred, numel, mode, label, acc, gscale, dpred);
+  if (acc)
+    gsb::launch(sum_rows_kernel, gsb::LaunchCfg(1, 256, 0, to_stream(s)), (const double*)acc, grid, 1, (double)numel, (double*)nullptr, loss);
   return check_launch("gan_loss", acc ? 2 : 1);
 }
 
 extern "C" int gsb_l1_loss(const float* a, const float* b, int64_t numel, float* loss, const float* gscale, float* da,
-                           void* workspace, gsb_stream s) {
+                           void* workspace, size_t workspace_bytes, gsb_stream s) {
   GSB_REQUIRE(a && b && numel > 0, "l1_loss: bad argument");
-  GSB_REQUIRE(loss == nullptr || workspace != nullptr, "l1_loss: workspace (8 bytes) required for the forward value");
+  GSB_REQUIRE(loss == nullptr || (workspace != nullptr && workspace_bytes >= sizeof(double)),
+              "l1_loss: workspace (>= 8 bytes) required for the forward value");
   double* acc = loss ? reinterpret_cast<double*>(workspace) : nullptr;
-  if (acc) cudaMemsetAsync(acc, 0, sizeof(double), to_stream(s));
-  gsb::launch(l1_loss_kernel, gsb::LaunchCfg(grid1d(numel, 8), 256, 0, to_stream(s)), a, b, numel, acc, gscale, da);
-  if (acc) gsb::launch(mean_out_kernel, gsb::LaunchCfg(1, 1, 0, to_stream(s)), acc, (double)numel, loss);
+  int grid = grid1d(numel, 8);
+  if (acc && (size_t)grid * sizeof(double) > workspace_bytes) grid = (int)(workspace_bytes / sizeof(double));
+  gsb::launch(l1_loss_kernel, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), a, b, numel, acc, gscale, da);
+  if (acc)
+    gsb::launch(sum_rows_kernel, gsb::LaunchCfg(1, 256, 0, to_stream(s)), (const double*)acc, grid, 1, (double)numel, (double*)nullptr, loss);
   return check_launch("l1_loss", acc ? 2 : 1);
 }
 

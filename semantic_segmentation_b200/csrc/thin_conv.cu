@@ -379,8 +379,8 @@ __global__ void __launch_bounds__(256) thin_scatter_px_kernel(TView in, const vo
 // Accumulation in packed fp32x2 (FFMA2): the kernel is bound by the FMA pipe (128 ci x 64 taps per pixel, 516 us per launch
 // for the generator's output layer, ncu profiles/r01o).
 template <typename T, int TP, int KWT>
-__global__ void __launch_bounds__(256) thin_wgrad_kernel(TView in, TView dout, float* __restrict__ dwp, int mode, int KH, int KW,
-                                                        int stride, int pad, int co) {
+__global__ void __launch_bounds__(256) thin_wgrad_kernel(TView in, TView dout, float* __restrict__ dwp, int64_t slice_elems,
+                                                        int mode, int KH, int KW, int stride, int pad, int co) {
   GSB_PDL_ENTRY();
   extern __shared__ float sacc[];  // [TP][Cin]
   const int Cin = in.C, taps = KH * KW;
@@ -432,17 +432,24 @@ __global__ void __launch_bounds__(256) thin_wgrad_kernel(TView in, TView dout, f
       }
     }
   }
+  // deterministic reduction: the pixel lanes add their registers into shared memory one lane after the other, and the
+  // CTA STORES its sums into its own slice (blockIdx.x) of the workspace; the caller adds the slices in slice order
+  for (unsigned l = 0; l < lanes; ++l) {
+    if (lane == l) {
 #pragma unroll
-  for (int t = 0; t < TP; ++t)
+      for (int t = 0; t < TP; ++t)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      atomicAdd(&sacc[t * Cin + g * 8 + 2 * j], acc[t][j].x);
-      atomicAdd(&sacc[t * Cin + g * 8 + 2 * j + 1], acc[t][j].y);
+        for (int j = 0; j < 4; ++j) {
+          sacc[t * Cin + g * 8 + 2 * j] += acc[t][j].x;
+          sacc[t * Cin + g * 8 + 2 * j + 1] += acc[t][j].y;
+        }
     }
-  __syncthreads();
+    __syncthreads();
+  }
+  float* __restrict__ slice = dwp + (int64_t)blockIdx.x * slice_elems;
   for (int i = threadIdx.x; i < TP * Cin; i += blockDim.x) {
     const int t = i / Cin, ci = i - t * Cin;
-    if (tap0 + t < taps) atomicAdd(dwp + ((int64_t)(tap0 + t) * dout.C + co) * Cin + ci, sacc[i]);
+    if (tap0 + t < taps) slice[((int64_t)(tap0 + t) * dout.C + co) * Cin + ci] = sacc[i];
   }
 }
 
@@ -558,7 +565,9 @@ int thin_gather_try(const gsb_view* in, const void* wp, int wdtype, const float*
   return 0;
 }
 
-int thin_wgrad_try(const gsb_view* in, const gsb_view* dout, float* dwp, const gsb_conv_geom* g, cudaStream_t st) {
+// ws == nullptr: plan only.  *used = slices written (one per CTA column, each completely).
+int thin_wgrad_try(const gsb_view* in, const gsb_view* dout, float* dwp, int max_slices, int* used, const gsb_conv_geom* g,
+                   cudaStream_t st) {
   if (!(dout->c <= 4 && wide_ok(in)) || in->c > 1024 || 256 % (in->c / 8) != 0) return 0;
   const int64_t P = num_pixels(in);
   if (P <= 0 || P >= ((int64_t)1 << 31)) return 0;
@@ -566,12 +575,17 @@ int thin_wgrad_try(const gsb_view* in, const gsb_view* dout, float* dwp, const g
   const int TPr = (g->kw == 8 && in->dtype == GSB_BF16) ? 8 : 16;
   const int taps = g->kh * g->kw, passes = (taps + TPr - 1) / TPr;
   const int G = in->c / 8, lanes = 256 / G;
-  const int grid = grid_sm((P + lanes - 1) / lanes, 4);
+  int grid = grid_sm((P + lanes * 16 - 1) / (lanes * 16), 2);
+  if (dwp != nullptr && grid > max_slices) grid = max_slices;
+  *used = grid;
+  if (dwp == nullptr) return 1;
+  GSB_REQUIRE(grid >= 1, "thin_wgrad: no workspace slices");
+  const int64_t slice_elems = (int64_t)taps * dout->c * in->c;
   const size_t smem = (size_t)TPr * in->c * sizeof(float);
   TView vi = tv(in), vd = tv(dout);
   for (int co = 0; co < dout->c; ++co) {
 #define GSB_THIN_WG(TT, TPV, KWT)                                                                                          \
-  gsb::launch(thin_wgrad_kernel<TT, TPV, KWT>, gsb::LaunchCfg(dim3(grid, passes), 256, smem, st), vi, vd, dwp, g->mode, g->kh, g->kw, g->stride, g->pad, co)
+  gsb::launch(thin_wgrad_kernel<TT, TPV, KWT>, gsb::LaunchCfg(dim3(grid, passes), 256, smem, st), vi, vd, dwp, slice_elems, g->mode, g->kh, g->kw, g->stride, g->pad, co)
     if (in->dtype == GSB_BF16) {
       if (g->kw == 8) GSB_THIN_WG(__nv_bfloat16, 8, 8);
       else if (g->kw == 4) GSB_THIN_WG(__nv_bfloat16, 16, 4);

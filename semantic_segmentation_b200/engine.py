@@ -162,13 +162,13 @@ class WeightPacks:
 
 
 class BackwardBatch:
-    """Shared zero-initialised weight-gradient workspace (one fill) + deferred, batched un-packing (one launch per
-    flush) into ONE flat gradient buffer laid out in backward order, so that a prefix of it can be handed to the
-    gradient all-reduce while the rest of the backward pass is still running."""
+    """Weight gradients of one backward pass: every layer's tensor-core weight gradient arrives as partial-sum slices
+    (``ops.conv_wgrad_slices``: plain stores, no atomics), is un-packed -- slices added in slice order -- by ONE batched
+    launch per flush into ONE flat gradient buffer laid out in backward order, so that a prefix of that buffer can be
+    handed to the gradient all-reduce while the rest of the backward pass is still running."""
 
     def __init__(self, device, sizes: Dict[str, int]):
         total = sum(sizes.values())
-        self.flat = torch.zeros(max(total, 1), device=device, dtype=torch.float32)
         self.gflat = torch.empty(max(total, 1), device=device, dtype=torch.float32)
         self.sizes = dict(sizes)
         self.offsets: Dict[str, Tuple[int, int]] = {}
@@ -177,23 +177,19 @@ class BackwardBatch:
         self.jobs = []
         self.pending = []        # (work handle, tensor) of all-reduces in flight
 
-    def dwp(self, key: str, shape) -> Optional[torch.Tensor]:
+    def reserve(self, key: str) -> Optional[Tuple[int, int]]:
+        """[offset, offset + n) of the flat gradient buffer for this layer (assigned at first use)."""
         if key not in self.sizes:
             return None
         if key not in self.offsets:
             self.offsets[key] = (self.cursor, self.sizes[key])
             self.cursor += self.sizes[key]
-        off, n = self.offsets[key]
-        return self.flat[off:off + n].view(shape)
+        return self.offsets[key]
 
-    def defer_unpack(self, dwp: torch.Tensor, weight_shape, rows_from_d0: bool) -> torch.Tensor:
-        off = dwp.storage_offset() - self.flat.storage_offset()
-        n = dwp.numel()
-        if 0 <= off and off + n <= self.gflat.numel() and dwp.untyped_storage().data_ptr() == self.flat.untyped_storage().data_ptr():
-            out = self.gflat[off:off + n].view(weight_shape)
-        else:
-            out = torch.empty(weight_shape, device=dwp.device, dtype=torch.float32)
-        self.jobs.append((dwp, rows_from_d0, out))
+    def defer_unpack(self, key: str, ws: torch.Tensor, nslices: int, weight_shape, rows_from_d0: bool) -> torch.Tensor:
+        off, n = self.reserve(key)
+        out = self.gflat[off:off + n].view(weight_shape)
+        self.jobs.append((ws, rows_from_d0, out, int(nslices)))
         return out
 
     def flush(self) -> Tuple[int, int]:
@@ -242,6 +238,19 @@ class BackwardBatch:
         if flat_small is not None:
             torch._foreach_copy_(small, [c.view_as(g) for c, g in zip(flat_small.split([g.numel() for g in small]), small)])
         return True
+
+
+def conv_weight_grad(spec: "ConvSpec", x_view: GsbView, dy_view: GsbView, device, use_tc: int,
+                     batch: Optional["BackwardBatch"] = None, key: Optional[str] = None) -> torch.Tensor:
+    """Weight gradient of one convolution in torch layout.  The kernel writes partial-sum slices (one per split of the pixel
+    range); they are added in slice order while un-packing -- immediately, or by the batch's next flush."""
+    shape = (spec.k * spec.k, spec.cout, spec.cin)
+    n = ops.conv_wgrad_plan(x_view, dy_view, spec.fwd_mode, spec.k, spec.stride, spec.pad, use_tc=use_tc)
+    ws = torch.empty((n,) + shape, device=device, dtype=torch.float32)
+    used = ops.conv_wgrad_slices(x_view, dy_view, ws, n, spec.fwd_mode, spec.k, spec.stride, spec.pad, use_tc=use_tc)
+    if batch is not None and key is not None and key in batch.sizes:
+        return batch.defer_unpack(key, ws, used, spec.weight_shape(), spec.kind == "conv")
+    return ops.unpack_wgrad(ws, spec.weight_shape(), spec.kind == "conv", nslices=used)
 
 
 def _is_stem(s: "ConvSpec", x_view: GsbView, x_keep) -> bool:
@@ -388,16 +397,9 @@ class ConvBNAct:
         if need_dw and sv.extra.get("stem"):
             dweight = ops.stem_conv_wgrad(sv.x_keep, dY, s.k, s.stride, s.pad)
         elif need_dw:
-            dwp = batch.dwp(key, (s.k * s.k, s.cout, s.cin)) if batch is not None and key is not None else None
-            if dwp is None:
-                dwp = torch.zeros((s.k * s.k, s.cout, s.cin), device=device, dtype=torch.float32)
-            ops.conv_wgrad_into(sv.x_view, dyv, dwp, s.fwd_mode, s.k, s.stride, s.pad, use_tc=_CONFIG["use_tc"])
-            if batch is not None:
-                dweight = batch.defer_unpack(dwp, s.weight_shape(), s.kind == "conv")
-            else:
-                dweight = ops.unpack_wgrad(dwp, s.weight_shape(), s.kind == "conv")
+            dweight = conv_weight_grad(s, sv.x_view, dyv, device, _CONFIG["use_tc"], batch, key)
         if need_db:
-            dbias = torch.zeros(s.cout, device=device, dtype=torch.float32)
+            dbias = torch.empty(s.cout, device=device, dtype=torch.float32)
             ops.bias_grad(dyv, dbias)
         dx = None
         if need_dx:
@@ -461,11 +463,9 @@ class EdgeConv:
         if sv.extra.get("head") and dx_out is None:
             return ops.head_conv_bwd(sv.x_keep, sv.weight.detach().contiguous(), dout, need_dx, need_dw, need_db)
         if need_dw:
-            dwp = torch.zeros((s.k * s.k, s.cout, s.cin), device=device, dtype=torch.float32)
-            ops.conv_wgrad_into(sv.x_view, dv, dwp, s.fwd_mode, s.k, s.stride, s.pad, use_tc=0)
-            dweight = ops.unpack_wgrad(dwp, s.weight_shape(), s.kind == "conv")
+            dweight = conv_weight_grad(s, sv.x_view, dv, device, 0)
         if need_db:
-            dbias = torch.zeros(s.cout, device=device, dtype=torch.float32)
+            dbias = torch.empty(s.cout, device=device, dtype=torch.float32)
             ops.bias_grad(dv, dbias)
         if need_dx:
             xv = sv.x_view

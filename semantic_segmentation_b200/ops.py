@@ -39,6 +39,27 @@ def _ref(v: Optional[GsbView]):
     return C.byref(v) if v is not None else None
 
 
+# Per-(device, stream) scratch for kernels whose partial results are consumed INSIDE the same C call (per-CTA partial rows of
+# the deterministic two-stage reductions, split-K slices of the small-tile convolution).  Calls on one stream are ordered,
+# so the buffer is reused; a buffer that had to grow is kept alive (a captured CUDA graph may still hold its address).
+_SCRATCH = {}
+_SCRATCH_RETIRED = []
+
+
+def _scratch(device, nbytes: int) -> torch.Tensor:
+    idx = device.index if isinstance(device, torch.device) else int(device)
+    if idx is None:
+        idx = torch.cuda.current_device()
+    key = (idx, stream_ptr(idx))
+    buf = _SCRATCH.get(key)
+    if buf is None or buf.numel() < nbytes:
+        if buf is not None:
+            _SCRATCH_RETIRED.append(buf)
+        buf = torch.empty(max(int(nbytes), 1 << 20), device=torch.device("cuda", idx), dtype=torch.uint8)
+        _SCRATCH[key] = buf
+    return buf
+
+
 # ---- layout ---------------------------------------------------------------------------------
 
 def nchw_to_nhwc(x: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
@@ -71,14 +92,19 @@ def pack_weight(w: torch.Tensor, rows_from_d0: bool, dtype: torch.dtype) -> torc
 
 
 def unpack_wgrad(dwp: torch.Tensor, shape: Tuple[int, int, int, int], rows_from_d0: bool,
-                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                 out: Optional[torch.Tensor] = None, nslices: int = 1) -> torch.Tensor:
+    """dwp: fp32 [nslices, kh*kw, rows, cols] partial-sum slices (or one slice), added in slice order while un-packing."""
     d0, d1, kh, kw = shape
     acc = out is not None
     if out is None:
         out = torch.empty(shape, device=dwp.device, dtype=torch.float32)
-    check(load().gsb_unpack_wgrad(ptr(dwp), d0, d1, kh, kw, int(rows_from_d0), ptr(out), int(acc), _s(dwp)),
+    check(load().gsb_unpack_wgrad(ptr(dwp), int(nslices), d0, d1, kh, kw, int(rows_from_d0), ptr(out), int(acc), _s(dwp)),
           "unpack_wgrad")
     return out
+
+
+def sum_slices(ws: torch.Tensor, nslices: int, n: int, dst: torch.Tensor, accumulate: bool = False) -> None:
+    check(load().gsb_sum_slices(ptr(ws), int(nslices), int(n), ptr(dst), int(accumulate), _s(ws)), "sum_slices")
 
 
 def _ptr_array(ts):
@@ -105,14 +131,16 @@ def pack_weight_multi(jobs, dtype: torch.dtype) -> None:
 
 
 def unpack_wgrad_multi(jobs) -> None:
-    """jobs: [(dwp fp32 [kh*kw, rows, cols], rows_from_d0, out fp32 [d0,d1,kh,kw])] -- one launch."""
+    """jobs: [(dwp fp32 [nslices, kh*kw, rows, cols], rows_from_d0, out fp32 [d0,d1,kh,kw], nslices)] -- one launch; the
+    partial-sum slices of every job are added in slice order while un-packing."""
     if not jobs:
         return
     outs = [j[2] for j in jobs]
-    for dwp, _, out in jobs:
+    for dwp, _, out, _ns in jobs:
         assert dwp.dtype == torch.float32 and out.dtype == torch.float32 and dwp.is_contiguous() and out.is_contiguous()
         L.require_cuda(out)
-    check(load().gsb_unpack_wgrad_multi(len(jobs), _ptr_array([j[0] for j in jobs]), _ptr_array(outs),
+    check(load().gsb_unpack_wgrad_multi(len(jobs), _ptr_array([j[0] for j in jobs]), _int_array([j[3] for j in jobs]),
+                                        _ptr_array(outs),
                                         _int_array([t.shape[0] for t in outs]), _int_array([t.shape[1] for t in outs]),
                                         _int_array([t.shape[2] * t.shape[3] for t in outs]),
                                         _int_array([int(j[1]) for j in jobs]), 0, _s(outs[0])), "unpack_wgrad_multi")
@@ -133,10 +161,10 @@ def unmerge_upconv(dwm, dbm, w4, w6, w8, b4, b6, b8, alpha_row, dalpha_row):
     db4 = db6 = db8 = None
     if dbm is not None:
         db4, db6, db8 = torch.empty_like(b4), torch.empty_like(b6), torch.empty_like(b8)
-    ws = torch.empty(4, device=w8.device, dtype=torch.float64)
+    ws = _scratch(w8.device, 4096 * 3 * 8)      # one row of 3 fp64 partial dot products per CTA
     check(load().gsb_unmerge_upconv(ptr(dwm), ptr(dbm), ptr(w4), ptr(w6), ptr(w8), ptr(b4), ptr(b6), ptr(b8),
                                     ptr(alpha_row), cin, cout, ptr(dw4), ptr(dw6), ptr(dw8), ptr(db4), ptr(db6),
-                                    ptr(db8), ptr(dalpha_row), ptr(ws), ws.numel() * 8, _s(w8)), "unmerge_upconv")
+                                    ptr(db8), ptr(dalpha_row), ptr(ws), 4096 * 3 * 8, _s(w8)), "unmerge_upconv")
     return dw4, dw6, dw8, db4, db6, db8
 
 
@@ -153,18 +181,47 @@ def conv_gather(inp: GsbView, wp: torch.Tensor, bias: Optional[torch.Tensor], ou
     if want_stats and use_tc != 0 and wp.dtype == torch.bfloat16:
         nrows = lib.gsb_conv_stats_rows(_ref(out), C.byref(g))
         stats = torch.empty((nrows, 2, out.c), device=wp.device, dtype=torch.float32)
+    scratch, sbytes = None, 0
+    if use_tc != 0 and wp.dtype == torch.bfloat16 and out.n * out.h * out.w <= 9472 and stream is None:
+        # launches with a handful of tiles split their K loop over CTAs into fp32 slices of this buffer (<= 9.7 MB needed)
+        scratch, sbytes = _scratch(wp.device, _SPLITK_BYTES), _SPLITK_BYTES
     check(lib.gsb_conv_gather(_ref(inp), ptr(wp), L.dtype_code(wp.dtype), ptr(bias), _ref(out), C.byref(g), act,
-                              int(accumulate), use_tc, ptr(stats), C.byref(rows),
+                              int(accumulate), use_tc, ptr(stats), C.byref(rows), ptr(scratch), sbytes,
                               stream if stream is not None else _s(wp)), "conv_gather")
     if stats is not None and rows.value > 0:
         return stats, rows.value
     return None, 0
 
 
+_SPLITK_BYTES = 16 << 20
+
+
+def conv_wgrad_plan(inp: GsbView, dout: GsbView, mode: int, k: int, stride: int, pad: int, use_tc: int = 2) -> int:
+    """Number of partial-sum slices gsb_conv_wgrad will write for this geometry (host-side, no launch)."""
+    g = GsbConvGeom(mode, k, k, stride, pad)
+    n = load().gsb_conv_wgrad_plan(_ref(inp), _ref(dout), C.byref(g), use_tc)
+    if n < 1:
+        check(-1, "conv_wgrad_plan")
+    return int(n)
+
+
+def conv_wgrad_slices(inp: GsbView, dout: GsbView, ws: torch.Tensor, max_slices: int, mode: int, k: int, stride: int,
+                      pad: int, use_tc: int = 2) -> int:
+    """Weight gradient as partial-sum slices ws[slice][k*k][cout][cin] (plain stores, no atomics); returns the slices used."""
+    g = GsbConvGeom(mode, k, k, stride, pad)
+    used = C.c_int(0)
+    check(load().gsb_conv_wgrad(_ref(inp), _ref(dout), ptr(ws), int(max_slices), C.byref(used), C.byref(g), use_tc, _s(ws)),
+          "conv_wgrad")
+    return int(used.value)
+
+
 def conv_wgrad_into(inp: GsbView, dout: GsbView, dwp: torch.Tensor, mode: int, k: int, stride: int, pad: int,
                     use_tc: int = 2) -> None:
-    g = GsbConvGeom(mode, k, k, stride, pad)
-    check(load().gsb_conv_wgrad(_ref(inp), _ref(dout), ptr(dwp), C.byref(g), use_tc, _s(dwp)), "conv_wgrad")
+    """dwp[k*k][cout][cin] (fp32) += weight gradient: slices into a temporary workspace, added to dwp in slice order."""
+    n = conv_wgrad_plan(inp, dout, mode, k, stride, pad, use_tc)
+    ws = torch.empty((n,) + tuple(dwp.shape), device=dwp.device, dtype=torch.float32)
+    used = conv_wgrad_slices(inp, dout, ws, n, mode, k, stride, pad, use_tc)
+    sum_slices(ws, used, dwp.numel(), dwp, accumulate=True)
 
 
 def stem_conv_fwd(x: torch.Tensor, weight: torch.Tensor, bias, y: torch.Tensor, k: int, stride: int, pad: int,
@@ -186,7 +243,9 @@ def stem_conv_fwd(x: torch.Tensor, weight: torch.Tensor, bias, y: torch.Tensor, 
 def stem_conv_wgrad(x: torch.Tensor, dy: torch.Tensor, k: int, stride: int, pad: int) -> torch.Tensor:
     n, cin, h, w = x.shape
     dw = torch.empty((dy.shape[3], cin, k, k), device=x.device, dtype=torch.float32)
-    check(load().gsb_stem_conv_wgrad(ptr(x), n, cin, h, w, _ref(view_nhwc(dy)), k, stride, pad, ptr(dw), _s(x)),
+    nbytes = load().gsb_edge_rows() * dw.numel() * 4          # one partial row per CTA column, added in row order
+    ws = _scratch(x.device, nbytes)
+    check(load().gsb_stem_conv_wgrad(ptr(x), n, cin, h, w, _ref(view_nhwc(dy)), k, stride, pad, ptr(dw), ptr(ws), nbytes, _s(x)),
           "stem_conv_wgrad")
     return dw
 
@@ -205,13 +264,20 @@ def head_conv_bwd(x: torch.Tensor, weight: torch.Tensor, dlogits: torch.Tensor, 
     dx = torch.empty_like(x) if need_dx else None
     dw = torch.empty_like(weight) if need_dw else None
     db = torch.empty(c, device=x.device, dtype=torch.float32) if need_db else None
+    ws, nbytes = None, 0
+    if need_dw or need_db:
+        nbytes = load().gsb_edge_rows() * (c * x.shape[3] + 8) * 4
+        ws = _scratch(x.device, nbytes)
     check(load().gsb_head_conv_bwd(_ref(view_nhwc(x)), ptr(weight), c, ptr(dlogits), _ref(view_nhwc(dx)) if need_dx else None,
-                                   ptr(dw), ptr(db), _s(x)), "head_conv_bwd")
+                                   ptr(dw), ptr(db), ptr(ws), nbytes, _s(x)), "head_conv_bwd")
     return dx, dw, db
 
 
 def bias_grad(dout: GsbView, db: torch.Tensor) -> None:
-    check(load().gsb_bias_grad(_ref(dout), ptr(db), _s(db)), "bias_grad")
+    """db[c] = sum over pixels of dout[., c] (stored)."""
+    nbytes = load().gsb_bias_grad_workspace_bytes(_ref(dout))
+    ws = _scratch(db.device, nbytes)
+    check(load().gsb_bias_grad(_ref(dout), ptr(db), ptr(ws), nbytes, _s(db)), "bias_grad")
 
 
 # ---- batch norm -----------------------------------------------------------------------------
@@ -393,35 +459,41 @@ def eval_counts(logits: torch.Tensor, labels: torch.Tensor, want_mask: bool = Tr
 
 def dice_sums(a: torch.Tensor, b: torch.Tensor, slices: int, inner: int) -> torch.Tensor:
     sums = torch.empty((slices, 3), device=a.device, dtype=torch.float64)
-    check(load().gsb_dice_sums(ptr(a), ptr(b), slices, inner, ptr(sums), _s(a)), "dice_sums")
+    rows = max(1, min(1024, (inner + 4095) // 4096, (8 << 20) // (slices * 24)))
+    nbytes = rows * slices * 24
+    ws = _scratch(a.device, nbytes)
+    check(load().gsb_dice_sums(ptr(a), ptr(b), slices, inner, ptr(sums), ptr(ws), nbytes, _s(a)), "dice_sums")
     return sums
+
+
+_LOSS_WS_BYTES = 2048 * 8      # one fp64 partial per CTA (grids are capped at 148 * 8 CTAs)
 
 
 def gan_loss_fwd(pred: torch.Tensor, mode: int, label: float) -> torch.Tensor:
     loss = torch.empty((), device=pred.device, dtype=torch.float32)
-    ws = torch.empty(1, device=pred.device, dtype=torch.float64)
-    check(load().gsb_gan_loss(ptr(pred), pred.numel(), mode, float(label), ptr(loss), None, None, ptr(ws), _s(pred)),
-          "gan_loss")
+    ws = _scratch(pred.device, _LOSS_WS_BYTES)
+    check(load().gsb_gan_loss(ptr(pred), pred.numel(), mode, float(label), ptr(loss), None, None, ptr(ws), _LOSS_WS_BYTES,
+                              _s(pred)), "gan_loss")
     return loss
 
 
 def gan_loss_bwd(pred: torch.Tensor, mode: int, label: float, gscale: torch.Tensor) -> torch.Tensor:
     d = torch.empty_like(pred)
-    check(load().gsb_gan_loss(ptr(pred), pred.numel(), mode, float(label), None, ptr(gscale), ptr(d), None, _s(pred)),
+    check(load().gsb_gan_loss(ptr(pred), pred.numel(), mode, float(label), None, ptr(gscale), ptr(d), None, 0, _s(pred)),
           "gan_loss")
     return d
 
 
 def l1_loss_fwd(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
     loss = torch.empty((), device=a.device, dtype=torch.float32)
-    ws = torch.empty(1, device=a.device, dtype=torch.float64)
-    check(load().gsb_l1_loss(ptr(a), ptr(b), a.numel(), ptr(loss), None, None, ptr(ws), _s(a)), "l1_loss")
+    ws = _scratch(a.device, _LOSS_WS_BYTES)
+    check(load().gsb_l1_loss(ptr(a), ptr(b), a.numel(), ptr(loss), None, None, ptr(ws), _LOSS_WS_BYTES, _s(a)), "l1_loss")
     return loss
 
 
 def l1_loss_bwd(a: torch.Tensor, b: torch.Tensor, gscale: torch.Tensor) -> torch.Tensor:
     d = torch.empty_like(a)
-    check(load().gsb_l1_loss(ptr(a), ptr(b), a.numel(), None, ptr(gscale), ptr(d), None, _s(a)), "l1_loss")
+    check(load().gsb_l1_loss(ptr(a), ptr(b), a.numel(), None, ptr(gscale), ptr(d), None, 0, _s(a)), "l1_loss")
     return d
 
 

@@ -125,11 +125,12 @@ parallel.shutdown()
 world = parallel.init_data_parallel(sync_bn=True, backend="gloo", overlap_grad_allreduce=True)
 assert engine._REDUCER["grad_fn"] is not None and engine._REDUCER["sm_reserve"] == 16
 bb = engine.BackwardBatch(torch.device("cpu"), {"late": 6, "early": 4})
-assert bb.dwp("early", (2, 2)).shape == (2, 2) and bb.offsets["early"] == (0, 4)      # offsets follow the order of use
+assert bb.reserve("early") == (0, 4) and bb.offsets["early"] == (0, 4)                 # offsets follow the order of use
+assert bb.reserve("unknown") is None
 bb.gflat[:4] = float(r + 1)
 bb.reduce_async()                                      # bucket 1 = [0, 4): in flight, SM reserve raised
 assert bb.flushed == 4 and len(bb.pending) == 1
-bb.dwp("late", (6,)); bb.gflat[4:10] = 10.0 * (r + 1)
+bb.reserve("late"); bb.gflat[4:10] = 10.0 * (r + 1)
 small = [torch.full((3,), float(r)), None, torch.full((2, 2), 2.0 * r)]
 assert bb.reduce_finish(small) is True and not bb.pending
 assert bb.gflat[:4].tolist() == [3.0] * 4 and bb.gflat[4:10].tolist() == [30.0] * 6

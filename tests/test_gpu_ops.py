@@ -479,12 +479,20 @@ def test_batched_pack_and_unpack_match_single():
         rfd = i % 2 == 0
         d0, d1, kh, kw = w.shape
         rows, cols = (d0, d1) if rfd else (d1, d0)
-        dwp = torch.randn((kh * kw, rows, cols), generator=g).to(DEV)
+        nsl = 1 + i                                # partial-sum slices, added in slice order while un-packing
+        dwp = torch.randn((nsl, kh * kw, rows, cols), generator=g).to(DEV)
         out = torch.empty(tuple(w.shape), device=DEV, dtype=torch.float32)
-        ujobs.append((dwp, rfd, out))
-        usingles.append(ops.unpack_wgrad(dwp, tuple(w.shape), rfd))
+        ujobs.append((dwp, rfd, out, nsl))
+        usingles.append(ops.unpack_wgrad(dwp, tuple(w.shape), rfd, nslices=nsl))
+        total = dwp[0].clone()
+        for sl in range(1, nsl):
+            total = total + dwp[sl]                # the same order, fp32
+        assert torch.equal(usingles[-1], ops.unpack_wgrad(total, tuple(w.shape), rfd))
+        acc = torch.zeros_like(total).reshape(-1)
+        ops.sum_slices(dwp, nsl, total.numel(), acc)
+        assert rel(acc, dwp.double().sum(0).reshape(-1)) < 1e-6
     ops.unpack_wgrad_multi(ujobs)
-    for (_, _, out), s in zip(ujobs, usingles):
+    for (_, _, out, _n), s in zip(ujobs, usingles):
         assert torch.equal(out, s)
 
 
@@ -509,6 +517,40 @@ def test_pack_unpack_against_torch_permute(shape):
         acc = torch.ones(shape, device=DEV)
         ops.unpack_wgrad(ref.contiguous(), shape, rfd, out=acc)
         assert torch.equal(acc, w + 1.0)
+
+
+DET_GEOMS = [("conv", 3, 1, 1, 128, 128, 8, 32, 32, 1), ("conv", 3, 1, 1, 64, 64, 2, 64, 64, 1), ("conv", 4, 2, 1, 64, 128, 5, 4, 4, 1),
+             ("convT", 8, 2, 3, 128, 64, 2, 4, 4, 1), ("conv", 3, 1, 1, 64, 128, 3, 9, 11, 0), ("convT", 8, 2, 3, 128, 1, 2, 12, 10, 0),
+             ("conv", 4, 2, 1, 2, 64, 2, 16, 12, 0)]
+
+
+@pytest.mark.parametrize("geom", DET_GEOMS, ids=[f"{g[0]}k{g[1]}s{g[2]}_{g[4]}to{g[5]}_{g[7]}x{g[8]}_tc{g[9]}" for g in DET_GEOMS])
+def test_conv_kernels_are_deterministic(geom):
+    """No atomics in the split reductions: the weight gradient (tcgen05 halo / small-tile kernels, SIMT, thin), the
+    split-K forward of launches with few tiles and the bias gradient give the same BITS on every run."""
+    kind, k, stride, pad, cin, cout, n, h, w, use_tc = geom
+    dtype = torch.bfloat16 if use_tc else torch.float32
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(n, h, w, cin, generator=g).to(DEV, dtype)
+    wshape = (cout, cin, k, k) if kind == "conv" else (cin, cout, k, k)
+    wt = (torch.randn(wshape, generator=g) / math.sqrt(cin * k * k)).to(DEV)
+    fwd_mode = MODE_CONV if kind == "conv" else MODE_CONVT
+    oh = (h + 2 * pad - k) // stride + 1 if kind == "conv" else (h - 1) * stride - 2 * pad + k
+    ow = (w + 2 * pad - k) // stride + 1 if kind == "conv" else (w - 1) * stride - 2 * pad + k
+    dy = torch.randn(n, oh, ow, cout, generator=g).to(DEV, dtype)
+    wp = ops.pack_weight(wt, kind == "conv", dtype)
+    runs = []
+    for _ in range(3):
+        y = torch.empty((n, oh, ow, cout), device=DEV, dtype=dtype)
+        ops.conv_gather(view_nhwc(x), wp, None, view_nhwc(y), fwd_mode, k, stride, pad, use_tc=use_tc)
+        dwp = torch.zeros((k * k, cout, cin), device=DEV, dtype=torch.float32)
+        ops.conv_wgrad_into(view_nhwc(x), view_nhwc(dy), dwp, fwd_mode, k, stride, pad, use_tc=use_tc)
+        db = torch.empty(cout, device=DEV, dtype=torch.float32)
+        ops.bias_grad(view_nhwc(dy), db)
+        runs.append((y.clone(), dwp.clone(), db.clone()))
+    for r in runs[1:]:
+        assert torch.equal(r[0], runs[0][0]) and torch.equal(r[1], runs[0][1]) and torch.equal(r[2], runs[0][2])
+    assert rel(runs[0][2], dy.double().sum((0, 1, 2))) < (1e-6 if dtype == torch.float32 else 1e-5)
 
 
 THIN = [  # kind, k, stride, pad, cin, cout, n, h, w : 1..4 channels on one side (thin_conv.cu)

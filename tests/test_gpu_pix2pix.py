@@ -233,3 +233,49 @@ def test_pix2pix_instance_norm_bf16_runs_close(golden_dir):
     print("instance bf16", out)
     assert out["fake"] < 1e-1 and out["pred_real"] < 5e-2, out
     assert out["loss_D"] < 2e-2 and out["G_GAN"] < 2e-2 and out["G_L1"] < 0.5, out
+
+
+def test_pix2pix_step_is_bit_reproducible(golden_dir):
+    """Two runs of the bf16 D step + G step (merged up-cells, thin 128 -> 1 output layer, 512 -> 1 head, split-K deep
+    levels, dalpha dot products, GAN / L1 reductions): every loss and every gradient bit-identical (no atomics)."""
+    a = run_pix2pix_raw("pix2pix_train_nodrop", golden_dir)
+    b = run_pix2pix_raw("pix2pix_train_nodrop", golden_dir)
+    assert a["losses"] == b["losses"]
+    for k in a["gG"]:
+        assert torch.equal(a["gG"][k], b["gG"][k]), k
+    for k in a["gD"]:
+        assert torch.equal(a["gD"][k], b["gD"][k]), k
+    assert torch.equal(a["ga"], b["ga"])
+
+
+def run_pix2pix_raw(name, golden_dir):
+    gold = np.load(os.path.join(golden_dir, name + ".npz"))
+    S.set_precision("bf16")
+    old_arch = networks.upconv_arch
+    try:
+        G = networks.define_G(1, 1, 64, "unet_256", "batch", False, "normal", 0.02, [])
+        D = networks.define_D(2, 64, "basic", 3, "batch", "normal", 0.02, [])
+        G.load_state_dict(O.seeded_state(O.generator_state_spec(1, 1, 64, 8), 11, conv_std=0.02), strict=True)
+        D.load_state_dict(O.seeded_state(O.discriminator_state_spec(2, 64, 3), 12, conv_std=0.02), strict=True)
+        G, D = G.to(DEV).train(), D.to(DEV).train()
+        networks.upconv_arch = torch.from_numpy(gold["arch"]).to(DEV).requires_grad_(True)
+        g = torch.Generator().manual_seed(14)
+        mask = torch.randint(0, 2, (2, 1, 256, 256), generator=g).float().to(DEV)
+        image = torch.rand(2, 1, 256, 256, generator=g).to(DEV)
+        crit = networks.GANLoss("vanilla").to(DEV)
+        fake = G(mask)
+        loss_D = 0.5 * (crit(D(torch.cat([mask, fake], 1).detach()), False) + crit(D(torch.cat([mask, image], 1)), True))
+        loss_D.backward()
+        gD = {k: p.grad.clone() for k, p in D.named_parameters()}
+        for p in D.parameters():
+            p.grad = None
+            p.requires_grad_(False)
+        g_gan = crit(D(torch.cat([mask, fake], 1)), True)
+        g_l1 = networks.l1_loss(fake, image) * 100.0
+        (g_gan + g_l1).backward()
+        torch.cuda.synchronize()
+        return dict(losses=(loss_D.item(), g_gan.item(), g_l1.item()), gD=gD, gG={k: p.grad.clone() for k, p in G.named_parameters()},
+                    ga=networks.upconv_arch.grad.clone())
+    finally:
+        networks.upconv_arch = old_arch
+        S.set_precision("bf16")
