@@ -56,6 +56,8 @@ unsigned long long gsb_launch_count(void);
 /* ---- layout / packing -------------------------------------------------------------- */
 /* dst <- cast(src) element-wise over (n,h,w,c) with arbitrary strides (NCHW<->NHWC, dtype). */
 int gsb_copy_view(const gsb_view* src, const gsb_view* dst, gsb_stream s);
+/* Flat fp32 <-> bf16 cast (16-byte aligned buffers): the gradient buckets of the data-parallel all-reduce travel as bf16. */
+int gsb_cast_flat(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n, gsb_stream s);
 /* Pack a torch weight into the GEMM operand layout Wp[tap][rows][cols] (cols contiguous).
  * src is fp32 [d0][d1][kh][kw] (Conv2d: OIHW, unet_parts.py:16; ConvTranspose2d: IOHW,
  * operations.py:18).  rows_from_d0 != 0 -> rows = d0, cols = d1; else rows = d1, cols = d0. */
@@ -145,23 +147,29 @@ int gsb_bn_reduce_partials(const float* partial, int rows, int c, double* sums, 
  * except sums/scale/shift).  Eval: pass sums = NULL -> scale/shift from running stats. */
 int gsb_bn_finalize(const double* sums, double count, const float* gamma, const float* beta,
                     float* running_mean, float* running_var, int64_t* num_batches_tracked, float momentum,
-                    float eps, int c, float* scale, float* shift, float* mean, float* invstd, gsb_stream s);
-/* out1 = act1(drop(x*scale+shift)); out2 (nullable) = act2(x*scale+shift).
- * scale/shift nullable (identity).  Dropout(0.5) on the out1 path: explicit keep-mask drop_mask
+                    float eps, int c, float* scale, float* shift, float* mean, float* invstd, int centered,
+                    gsb_stream s);
+/* z = (x - center)*scale + shift;  out1 = act1(drop(z)); out2 (nullable) = act2(z).
+ * scale/shift/center nullable (identity / 0).  Two forms of the normalisation: folded (centered = 0 at finalize:
+ * shift = beta - mean*scale, center = NULL; the bf16 production mode) and centered (centered = 1: shift = beta,
+ * center = mean; the fp32 validation mode evaluates (x - mean)*scale + beta like torch, the folded form loses
+ * |mean|/std digits to cancellation).  Dropout(0.5) on the out1 path: explicit keep-mask drop_mask
  * (uint8 dense NHWC, nullable) or, if drop_seed != 0, a stateless Philox4x32-10 mask keyed by
- * (drop_seed, logical element index) that backward recomputes. */
-int gsb_bn_act(const gsb_view* x, const float* scale, const float* shift, int act1, const gsb_view* out1,
-               int act2, const gsb_view* out2, uint64_t drop_seed, const uint8_t* drop_mask, gsb_stream s);
-/* Backward.  dy = act1'(z)*drop*dA1 + act2'(z)*dA2 (dA2 nullable), z = x*scale+shift.
+ * (drop_seed, drop_offset + local element index) that backward recomputes; drop_offset = first global sample of this
+ * rank * h*w*c makes the masks of a batch sharded over N ranks those of the one-rank run. */
+int gsb_bn_act(const gsb_view* x, const float* scale, const float* shift, const float* center, int act1,
+               const gsb_view* out1, int act2, const gsb_view* out2, uint64_t drop_seed, int64_t drop_offset,
+               const uint8_t* drop_mask, gsb_stream s);
+/* Backward.  dy = act1'(z)*drop*dA1 + act2'(z)*dA2 (dA2 nullable), z as above.
  * reduce: sums[2][c] fp64 <- sum dy, sum dy*xhat.   apply (has_bn): dx = scale*(dy - s0/cnt - xhat*s1/cnt);
  * (no bn: pass mean = NULL -> dx = dy).  dgamma/dbeta accumulate (nullable). */
 int gsb_bn_bwd_reduce(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
-                      const float* shift, const float* mean, const float* invstd, int act1, int act2,
-                      uint64_t drop_seed, const uint8_t* drop_mask, double* sums, void* workspace,
+                      const float* shift, const float* center, const float* mean, const float* invstd, int act1, int act2,
+                      uint64_t drop_seed, int64_t drop_offset, const uint8_t* drop_mask, double* sums, void* workspace,
                       size_t workspace_bytes, gsb_stream s);
 int gsb_bn_bwd_apply(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
-                     const float* shift, const float* mean, const float* invstd, int act1, int act2,
-                     uint64_t drop_seed, const uint8_t* drop_mask, const double* sums, double count,
+                     const float* shift, const float* center, const float* mean, const float* invstd, int act1, int act2,
+                     uint64_t drop_seed, int64_t drop_offset, const uint8_t* drop_mask, const double* sums, double count,
                      const gsb_view* dx, float* dgamma, float* dbeta, gsb_stream s);
 
 /* dbeta[c] (+)= sums[c], dgamma[c] (+)= sums[c + C]: parameter gradients from the LOCAL backward sums (under
@@ -175,10 +183,11 @@ int gsb_bn_param_grad(const double* sums, int c, float* dgamma, float* dbeta, in
 int gsb_bn_stats_finalize(const float* partial, int rows, int c, double count, void* const* regions, int rank, int world,
                           const float* gamma, const float* beta, float* running_mean, float* running_var,
                           int64_t* num_batches_tracked, float momentum, float eps, float* scale, float* shift, float* mean,
-                          float* invstd, gsb_stream s);
+                          float* invstd, int centered, gsb_stream s);
 int gsb_bn_bwd_partial(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale, const float* shift,
-                       const float* mean, const float* invstd, int act1, int act2, uint64_t drop_seed,
-                       const uint8_t* drop_mask, void* workspace, size_t workspace_bytes, int* rows, gsb_stream s);
+                       const float* center, const float* mean, const float* invstd, int act1, int act2, uint64_t drop_seed,
+                       int64_t drop_offset, const uint8_t* drop_mask, void* workspace, size_t workspace_bytes, int* rows,
+                       gsb_stream s);
 int gsb_bn_bwd_stats(const float* partial, int rows, int c, void* const* regions, int rank, int world, float* dgamma,
                      float* dbeta, int accumulate, double* sums, gsb_stream s);
 
@@ -263,7 +272,10 @@ int gsb_mask_affine(const float* in, const float* mats, float* out, int n, int h
  * Every rank (one process per GPU, same node) creates a region, publishes its CUDA IPC handle, opens its peers'
  * handles, and then calls gsb_peer_allreduce_f64 in the same order on every rank: one kernel per call stores the
  * vector into all regions over NVLink, exchanges sequence flags and sums in rank order (bit-identical on all ranks).
- * n <= gsb_peer_max_elems(), world <= 8.  Graph-capturable (the sequence counter lives in device memory). */
+ * n <= gsb_peer_max_elems(), world <= 8.  Graph-capturable (the sequence counter lives in device memory).
+ * Every rank must issue the same sequence of exchanges.  A wait longer than GSB_PEER_TIMEOUT_S seconds (default 1800,
+ * 0 = no limit) does NOT trap: the kernel records the call's sequence number in its region's error word, keeps its local
+ * values and returns; gsb_peer_error(own region, &seq) reads that word (0 = healthy; synchronises the device). */
 int64_t gsb_peer_region_bytes(void);
 int gsb_peer_max_elems(void);
 int gsb_peer_handle_bytes(void);
@@ -271,6 +283,7 @@ int gsb_peer_create(void** region, void* handle_out);
 int gsb_peer_open(const void* handle, void** peer_region);
 int gsb_peer_close(void* peer_region);
 int gsb_peer_destroy(void* region);
+int gsb_peer_error(void* region, unsigned long long* seq_out);
 int gsb_peer_allreduce_f64(double* buf, int n, void* const* regions, int rank, int world, gsb_stream s);
 
 #ifdef __cplusplus

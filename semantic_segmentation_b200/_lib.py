@@ -40,6 +40,7 @@ SIGNATURES = {
     "gsb_tc_available": (_i, []),
     "gsb_launch_count": (C.c_ulonglong, []),
     "gsb_copy_view": (_i, [_VP, _VP, _p]),
+    "gsb_cast_flat": (_i, [_p, _i, _p, _i, _i64, _p]),
     "gsb_pack_weight": (_i, [_p, _i, _i, _i, _i, _i, _p, _i, _p]),
     "gsb_unpack_wgrad": (_i, [_p, _i, _i, _i, _i, _i, _i, _p, _i, _p]),
     "gsb_sum_slices": (_i, [_p, _i, _i64, _p, _i, _p]),
@@ -62,13 +63,13 @@ SIGNATURES = {
     "gsb_bn_workspace_bytes": (_sz, [_VP]),
     "gsb_bn_reduce": (_i, [_VP, _p, _p, _sz, _p]),
     "gsb_bn_reduce_partials": (_i, [_p, _i, _i, _p, _p]),
-    "gsb_bn_finalize": (_i, [_p, _d, _p, _p, _p, _p, _p, _f, _f, _i, _p, _p, _p, _p, _p]),
-    "gsb_bn_act": (_i, [_VP, _p, _p, _i, _VP, _i, _VP, _u64, _p, _p]),
-    "gsb_bn_bwd_reduce": (_i, [_VP, _VP, _VP, _p, _p, _p, _p, _i, _i, _u64, _p, _p, _p, _sz, _p]),
-    "gsb_bn_bwd_apply": (_i, [_VP, _VP, _VP, _p, _p, _p, _p, _i, _i, _u64, _p, _p, _d, _VP, _p, _p, _p]),
+    "gsb_bn_finalize": (_i, [_p, _d, _p, _p, _p, _p, _p, _f, _f, _i, _p, _p, _p, _p, _i, _p]),
+    "gsb_bn_act": (_i, [_VP, _p, _p, _p, _i, _VP, _i, _VP, _u64, _i64, _p, _p]),
+    "gsb_bn_bwd_reduce": (_i, [_VP, _VP, _VP, _p, _p, _p, _p, _p, _i, _i, _u64, _i64, _p, _p, _p, _sz, _p]),
+    "gsb_bn_bwd_apply": (_i, [_VP, _VP, _VP, _p, _p, _p, _p, _p, _i, _i, _u64, _i64, _p, _p, _d, _VP, _p, _p, _p]),
     "gsb_bn_param_grad": (_i, [_p, _i, _p, _p, _i, _p]),
-    "gsb_bn_stats_finalize": (_i, [_p, _i, _i, _d, _p, _i, _i, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p, _p]),
-    "gsb_bn_bwd_partial": (_i, [_VP, _VP, _VP, _p, _p, _p, _p, _i, _i, _u64, _p, _p, _sz, _p, _p]),
+    "gsb_bn_stats_finalize": (_i, [_p, _i, _i, _d, _p, _i, _i, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p, _i, _p]),
+    "gsb_bn_bwd_partial": (_i, [_VP, _VP, _VP, _p, _p, _p, _p, _p, _i, _i, _u64, _i64, _p, _p, _sz, _p, _p]),
     "gsb_bn_bwd_stats": (_i, [_p, _i, _i, _p, _i, _i, _p, _p, _i, _p, _p]),
     "gsb_maxpool2_fwd": (_i, [_VP, _VP, _p]),
     "gsb_maxpool2_bwd": (_i, [_VP, _VP, _VP, _i, _p]),
@@ -98,6 +99,7 @@ SIGNATURES = {
     "gsb_peer_open": (_i, [_p, _p]),
     "gsb_peer_close": (_i, [_p]),
     "gsb_peer_destroy": (_i, [_p]),
+    "gsb_peer_error": (_i, [_p, _p]),
     "gsb_peer_allreduce_f64": (_i, [_p, _i, _p, _i, _i, _p]),
 }
 

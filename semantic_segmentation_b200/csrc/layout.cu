@@ -208,6 +208,42 @@ static int ew_grid(int64_t total) {
 
 using namespace gsb;
 
+// fp32 <-> bf16 casts of flat buffers (gradient buckets of the data-parallel all-reduce travel as bf16), 8 elements per thread
+__global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n) {
+  GSB_PDL_ENTRY();
+  const int64_t n8 = n >> 3, stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    float v[8];
+    Vec8<float>::load(src + i * 8, v);
+    Vec8<__nv_bfloat16>::store(dst + i * 8, v);
+  }
+  for (int64_t i = n8 * 8 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) dst[i] = __float2bfloat16_rn(src[i]);
+}
+__global__ void __launch_bounds__(256) cast_bf16_f32_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, int64_t n) {
+  GSB_PDL_ENTRY();
+  const int64_t n8 = n >> 3, stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    float v[8];
+    Vec8<__nv_bfloat16>::load(src + i * 8, v);
+    Vec8<float>::store(dst + i * 8, v);
+  }
+  for (int64_t i = n8 * 8 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) dst[i] = __bfloat162float(src[i]);
+}
+
+extern "C" int gsb_cast_flat(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n, gsb_stream s) {
+  GSB_REQUIRE(src && dst && n >= 0, "cast_flat: bad argument");
+  GSB_REQUIRE(((uintptr_t)src % 16 == 0) && ((uintptr_t)dst % 16 == 0), "cast_flat: buffers must be 16-byte aligned");
+  if (n == 0) return 0;
+  const int grid = ew_grid((n + 7) / 8);
+  if (src_dtype == GSB_F32 && dst_dtype == GSB_BF16)
+    gsb::launch(cast_f32_bf16_kernel, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), (const float*)src, (__nv_bfloat16*)dst, n);
+  else if (src_dtype == GSB_BF16 && dst_dtype == GSB_F32)
+    gsb::launch(cast_bf16_f32_kernel, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), (const __nv_bfloat16*)src, (float*)dst, n);
+  else
+    GSB_REQUIRE(false, "cast_flat: unsupported dtype pair %d -> %d", src_dtype, dst_dtype);
+  return check_launch("cast_flat");
+}
+
 extern "C" int gsb_copy_view(const gsb_view* src, const gsb_view* dst, gsb_stream s) {
   GSB_REQUIRE(src && dst && src->ptr && dst->ptr, "copy_view: null view");
   GSB_REQUIRE(src->n == dst->n && src->h == dst->h && src->w == dst->w && src->c == dst->c, "copy_view: shape mismatch");

@@ -47,7 +47,9 @@ __device__ __forceinline__ void load_param8(const float* p, int c0, float (&f)[8
 }
 
 // keep bits for the 8 channels of (pixel p, channel group c0); logical index = p*C + c0
-__device__ __forceinline__ uint32_t keep_bits(uint64_t seed, const uint8_t* mask, int64_t p, int C, int c0) {
+// (explicit masks are indexed locally; Philox masks by the GLOBAL element index = local index + drop_offset, so that a
+// batch sharded over N ranks draws the masks of the one-rank run: drop_offset = first global sample * H * W * C)
+__device__ __forceinline__ uint32_t keep_bits(uint64_t seed, int64_t drop_offset, const uint8_t* mask, int64_t p, int C, int c0) {
   if (mask != nullptr) {
     const uint8_t* m = mask + p * C + c0;
     uint2 r = *reinterpret_cast<const uint2*>(m);
@@ -59,7 +61,7 @@ __device__ __forceinline__ uint32_t keep_bits(uint64_t seed, const uint8_t* mask
     }
     return bits;
   }
-  if (seed != 0) return dropout_keep8(seed, (uint64_t)p * (uint64_t)C + (uint64_t)c0);
+  if (seed != 0) return dropout_keep8(seed, (uint64_t)drop_offset + (uint64_t)p * (uint64_t)C + (uint64_t)c0);
   return 0xFFu;
 }
 
@@ -73,8 +75,9 @@ __device__ __forceinline__ uint32_t keep_bits(uint64_t seed, const uint8_t* mask
 template <typename T, int MODE, bool FAST>
 __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
     PixView x, PixView dA1, PixView dA2, int64_t P, int C, const float* __restrict__ scale,
-    const float* __restrict__ shift, const float* __restrict__ mean, const float* __restrict__ invstd, int act1,
-    int act2, uint64_t drop_seed, const uint8_t* __restrict__ drop_mask, float* __restrict__ partial) {
+    const float* __restrict__ shift, const float* __restrict__ center, const float* __restrict__ mean,
+    const float* __restrict__ invstd, int act1,
+    int act2, uint64_t drop_seed, int64_t drop_offset, const uint8_t* __restrict__ drop_mask, float* __restrict__ partial) {
   GSB_PDL_ENTRY();
   constexpr int KU = MODE == 1 ? kUnrollBwd : kUnroll;
   // fp32 validation mode: fp64 accumulation, and every block writes TWO partial rows (hi, lo = the fp64 sum split into two
@@ -92,10 +95,11 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
   Acc s0[8], s1[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) s0[i] = s1[i] = (Acc)0;
-  float sc[8], sh[8], mu[8], is[8];
+  float sc[8], sh[8], mu[8], is[8], ce[8];
   if (MODE == 1) {
     load_param8(scale, c0, sc, 1.f);
     load_param8(shift, c0, sh, 0.f);
+    load_param8(FAST ? nullptr : center, c0, ce, 0.f);
     load_param8(mean, c0, mu, 0.f);
     load_param8(invstd, c0, is, 1.f);
   }
@@ -125,10 +129,10 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
           s1[i] += (Acc)v[u][i] * (Acc)v[u][i];
         }
       } else {
-        uint32_t keep = has_drop ? keep_bits(drop_seed, drop_mask, p, C, c0) : 0xFFu;
+        uint32_t keep = has_drop ? keep_bits(drop_seed, drop_offset, drop_mask, p, C, c0) : 0xFFu;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          float z = fmaf(v[u][i], sc[i], sh[i]);
+          float z = FAST ? fmaf(v[u][i], sc[i], sh[i]) : fmaf(v[u][i] - ce[i], sc[i], sh[i]);
           float dm = has_drop ? (((keep >> i) & 1u) ? 2.f : 0.f) : 1.f;
           float dy = a[u][i] * dm * act_grad(z * dm, act1);
           if (two) dy += b[u][i] * act_grad(z, act2);
@@ -262,7 +266,7 @@ __global__ void __launch_bounds__(1024) reduce_partials_kernel(const float* __re
 __global__ void bn_finalize_kernel(const double* __restrict__ sums, double count, const float* __restrict__ gamma,
                                    const float* __restrict__ beta, float* running_mean, float* running_var,
                                    int64_t* nbt, float momentum, float eps, int C, float* scale, float* shift,
-                                   float* mean_out, float* invstd_out) {
+                                   float* mean_out, float* invstd_out, int centered) {
   GSB_PDL_ENTRY();
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c == 0 && nbt != nullptr && sums != nullptr) *nbt += 1;
@@ -286,24 +290,29 @@ __global__ void bn_finalize_kernel(const double* __restrict__ sums, double count
   }
   float sc = g * is;
   scale[c] = sc;
-  shift[c] = b - m * sc;
+  // centered (fp32 validation mode): the consumers evaluate (x - mean) * scale + beta like torch does; the folded form
+  // x * scale + (beta - mean * scale) loses |mean| / std digits to cancellation (channels of the generator's deep levels
+  // are normalised over 8..32 samples), which put the fp32 mode 1e-4 away from the reference and flipped ReLU branches
+  shift[c] = centered ? b : b - m * sc;
   if (mean_out) mean_out[c] = m;
   if (invstd_out) invstd_out[c] = is;
 }
 
 template <typename T, bool FAST>
 __global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, int C, const float* __restrict__ scale,
-                                                         const float* __restrict__ shift, int act1, PixView out1,
-                                                         int act2, PixView out2, uint64_t drop_seed,
+                                                         const float* __restrict__ shift, const float* __restrict__ center,
+                                                         int act1, PixView out1,
+                                                         int act2, PixView out2, uint64_t drop_seed, int64_t drop_offset,
                                                          const uint8_t* __restrict__ drop_mask) {
   GSB_PDL_ENTRY();
   const int G = C >> 3;
   const int lanes = kThreads / G;
   const int g = threadIdx.x % G, lane = threadIdx.x / G;
   const int c0 = g * 8;
-  float sc[8], sh[8];
+  float sc[8], sh[8], ce[8];
   load_param8(scale, c0, sc, 1.f);
   load_param8(shift, c0, sh, 0.f);
+  load_param8(FAST ? nullptr : center, c0, ce, 0.f);   // z = (x - center) * scale + shift
   const bool has_drop = FAST ? false : ((drop_seed != 0) || (drop_mask != nullptr));
   const bool has_out2 = FAST ? false : (out2.ptr != nullptr);
   if (FAST) { act1 = GSB_ACT_RELU; act2 = GSB_ACT_NONE; }
@@ -318,10 +327,10 @@ __global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, 
       const int64_t p = p0 + u * step;
       if (p >= P) break;
       float o1[8], o2[8];
-      uint32_t keep = has_drop ? keep_bits(drop_seed, drop_mask, p, C, c0) : 0xFFu;
+      uint32_t keep = has_drop ? keep_bits(drop_seed, drop_offset, drop_mask, p, C, c0) : 0xFFu;
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        float z = fmaf(v[u][i], sc[i], sh[i]);
+        float z = FAST ? fmaf(v[u][i], sc[i], sh[i]) : fmaf(v[u][i] - ce[i], sc[i], sh[i]);
         float dm = has_drop ? (((keep >> i) & 1u) ? 2.f : 0.f) : 1.f;
         o1[i] = act_fwd(z * dm, act1);
         if (has_out2) o2[i] = act_fwd(z, act2);
@@ -335,17 +344,19 @@ __global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, 
 template <typename T, bool FAST>
 __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
     PixView x, PixView dA1, PixView dA2, int64_t P, int C, const float* __restrict__ scale,
-    const float* __restrict__ shift, const float* __restrict__ mean, const float* __restrict__ invstd, int act1,
-    int act2, uint64_t drop_seed, const uint8_t* __restrict__ drop_mask, const double* __restrict__ sums,
+    const float* __restrict__ shift, const float* __restrict__ center, const float* __restrict__ mean,
+    const float* __restrict__ invstd, int act1,
+    int act2, uint64_t drop_seed, int64_t drop_offset, const uint8_t* __restrict__ drop_mask, const double* __restrict__ sums,
     double inv_count, PixView dx) {
   GSB_PDL_ENTRY();
   const int G = C >> 3;
   const int lanes = kThreads / G;
   const int g = threadIdx.x % G, lane = threadIdx.x / G;
   const int c0 = g * 8;
-  float sc[8], sh[8], mu[8], is[8], m0[8], m1[8];
+  float sc[8], sh[8], mu[8], is[8], m0[8], m1[8], ce[8];
   load_param8(scale, c0, sc, 1.f);
   load_param8(shift, c0, sh, 0.f);
+  load_param8(FAST ? nullptr : center, c0, ce, 0.f);
   const bool has_bn = FAST ? true : (mean != nullptr);
   load_param8(mean, c0, mu, 0.f);
   load_param8(invstd, c0, is, 1.f);
@@ -405,10 +416,10 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
       const int64_t p = p0 + u * step;
       if (p >= P) break;
       float o[8];
-      uint32_t keep = has_drop ? keep_bits(drop_seed, drop_mask, p, C, c0) : 0xFFu;
+      uint32_t keep = has_drop ? keep_bits(drop_seed, drop_offset, drop_mask, p, C, c0) : 0xFFu;
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        float z = fmaf(v[u][i], sc[i], sh[i]);
+        float z = fmaf(v[u][i] - ce[i], sc[i], sh[i]);
         float dm = has_drop ? (((keep >> i) & 1u) ? 2.f : 0.f) : 1.f;
         float dy = a[u][i] * dm * act_grad(z * dm, act1);
         if (two) dy += b[u][i] * act_grad(z, act2);
@@ -453,6 +464,7 @@ struct BnFusedFwd {
   float* shift;
   float* mean;
   float* invstd;
+  int centered;   // shift = beta, consumers evaluate (x - mean) * scale + beta (fp32 validation mode)
 };
 struct BnFusedBwd {
   float* dgamma;
@@ -463,7 +475,8 @@ struct BnFusedBwd {
 
 template <int MODE>
 __global__ void __launch_bounds__(1024) bn_stats_fused_kernel(const float* __restrict__ partial, int rows, int C, PeerRegions regs,
-                                                             int rank, int world, BnFusedFwd f, BnFusedBwd b) {
+                                                             int rank, int world, BnFusedFwd f, BnFusedBwd b,
+                                                             long long timeout_ns) {
   GSB_PDL_ENTRY();
   __shared__ double red[32][33];
   __shared__ double tot[32];
@@ -496,11 +509,8 @@ __global__ void __launch_bounds__(1024) bn_stats_fused_kernel(const float* __res
     }
     if (world > 1) {
       seq = *reinterpret_cast<volatile unsigned long long*>(&hdr->counter) + 1ull;
-      if (ok && !peer_exchange_sum(t, col, regs, rank, world, (uint32_t)seq, (int)(seq % kPeerSlots))) {
-        hdr->error = seq;
-        __threadfence_system();
-        __trap();
-      }
+      if (ok && !peer_exchange_sum(t, col, regs, rank, world, (uint32_t)seq, (int)(seq % kPeerSlots), timeout_ns))
+        hdr->error = seq;   // watchdog expired: local statistics are used, the host raises after gsb_peer_error()
     }
     tot[c] = t;
     if (MODE == 1 && ok && b.sums != nullptr) b.sums[col] = t;
@@ -522,7 +532,7 @@ __global__ void __launch_bounds__(1024) bn_stats_fused_kernel(const float* __res
       }
       const float sc = g * is;
       f.scale[cc] = sc;
-      f.shift[cc] = be - m * sc;
+      f.shift[cc] = f.centered ? be : be - m * sc;
       if (f.mean) f.mean[cc] = m;
       if (f.invstd) f.invstd[cc] = is;
     }
@@ -583,11 +593,11 @@ extern "C" int gsb_bn_reduce(const gsb_view* x, double* sums, void* workspace, s
   if (smem > 48 * 1024)
     cudaFuncSetAttribute(bn_reduce_kernel<float, 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (x->dtype == GSB_BF16)
-    gsb::launch(bn_reduce_kernel<__nv_bfloat16, 0, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), nul, nul, P, C, nullptr, nullptr,
-                                                                                     nullptr, nullptr, 0, 0, 0, nullptr, partial);
+    gsb::launch(bn_reduce_kernel<__nv_bfloat16, 0, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), nul, nul, P, C, nullptr, nullptr, nullptr,
+                                                                                     nullptr, nullptr, 0, 0, 0, 0, nullptr, partial);
   else
-    gsb::launch(bn_reduce_kernel<float, 0, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), nul, nul, P, C, nullptr, nullptr, nullptr,
-                                                                             nullptr, 0, 0, 0, nullptr, partial);
+    gsb::launch(bn_reduce_kernel<float, 0, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), nul, nul, P, C, nullptr, nullptr, nullptr, nullptr,
+                                                                             nullptr, 0, 0, 0, 0, nullptr, partial);
   int n = 2 * C;
   gsb::launch(reduce_partials_kernel, gsb::LaunchCfg((n + 31) / 32, 1024, 0, to_stream(s)), partial, grid * wide, n, sums);
   return check_launch("bn_reduce", 2);
@@ -601,17 +611,20 @@ extern "C" int gsb_bn_reduce_partials(const float* partial, int rows, int c, dou
 
 extern "C" int gsb_bn_finalize(const double* sums, double count, const float* gamma, const float* beta,
                                float* running_mean, float* running_var, int64_t* num_batches_tracked, float momentum,
-                               float eps, int c, float* scale, float* shift, float* mean, float* invstd, gsb_stream s) {
+                               float eps, int c, float* scale, float* shift, float* mean, float* invstd, int centered,
+                               gsb_stream s) {
   GSB_REQUIRE(scale && shift, "bn_finalize: scale/shift required");
+  GSB_REQUIRE(!centered || mean != nullptr, "bn_finalize: the centered form needs the mean output");
   GSB_REQUIRE(sums != nullptr || (running_mean && running_var), "bn_finalize: eval mode needs running stats");
   gsb::launch(bn_finalize_kernel, gsb::LaunchCfg((c + 127) / 128, 128, 0, to_stream(s)), sums, count, gamma, beta, running_mean, running_var,
                                                                num_batches_tracked, momentum, eps, c, scale, shift,
-                                                               mean, invstd);
+                                                               mean, invstd, centered);
   return check_launch("bn_finalize");
 }
 
-extern "C" int gsb_bn_act(const gsb_view* x, const float* scale, const float* shift, int act1, const gsb_view* out1,
-                          int act2, const gsb_view* out2, uint64_t drop_seed, const uint8_t* drop_mask, gsb_stream s) {
+extern "C" int gsb_bn_act(const gsb_view* x, const float* scale, const float* shift, const float* center, int act1,
+                          const gsb_view* out1,
+                          int act2, const gsb_view* out2, uint64_t drop_seed, int64_t drop_offset, const uint8_t* drop_mask, gsb_stream s) {
   if (check_vec_view(x, "bn_act.x") || check_vec_view(out1, "bn_act.out1")) return -1;
   if (out2 && out2->ptr && check_vec_view(out2, "bn_act.out2")) return -1;
   GSB_REQUIRE(out1->dtype == x->dtype && out1->c == x->c && num_pixels(out1) == num_pixels(x), "bn_act: out1 mismatch");
@@ -621,17 +634,18 @@ extern "C" int gsb_bn_act(const gsb_view* x, const float* scale, const float* sh
   const int64_t P = num_pixels(x);
   int grid = grid_for(P, lanes * 4);
   PixView o2 = (out2 && out2->ptr) ? pv(out2) : PixView{nullptr, 0};
-  const bool fast = act1 == GSB_ACT_RELU && o2.ptr == nullptr && drop_seed == 0 && drop_mask == nullptr && scale && shift;
+  const bool fast = act1 == GSB_ACT_RELU && o2.ptr == nullptr && drop_seed == 0 && drop_mask == nullptr && scale && shift &&
+                    center == nullptr;
   if (x->dtype == GSB_BF16) {
     if (fast)
-      gsb::launch(bn_act_kernel<__nv_bfloat16, true>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), P, C, scale, shift, act1, pv(out1), act2, o2,
-                                                                              drop_seed, drop_mask);
+      gsb::launch(bn_act_kernel<__nv_bfloat16, true>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), P, C, scale, shift, center, act1, pv(out1), act2, o2,
+                                                                              drop_seed, drop_offset, drop_mask);
     else
-      gsb::launch(bn_act_kernel<__nv_bfloat16, false>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), P, C, scale, shift, act1, pv(out1), act2,
-                                                                               o2, drop_seed, drop_mask);
+      gsb::launch(bn_act_kernel<__nv_bfloat16, false>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), P, C, scale, shift, center, act1, pv(out1), act2,
+                                                                               o2, drop_seed, drop_offset, drop_mask);
   } else {
-    gsb::launch(bn_act_kernel<float, false>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), P, C, scale, shift, act1, pv(out1), act2, o2,
-                                                                     drop_seed, drop_mask);
+    gsb::launch(bn_act_kernel<float, false>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), P, C, scale, shift, center, act1, pv(out1), act2, o2,
+                                                                     drop_seed, drop_offset, drop_mask);
   }
   return check_launch("bn_act");
 }
@@ -648,8 +662,8 @@ static int check_bwd_views(const gsb_view* x, const gsb_view* dA1, const gsb_vie
 
 // Stage 1 of the backward statistics: per-block rows of [sum dy, sum dy*xhat] into `workspace`; returns the row count.
 static int bn_bwd_partial_launch(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
-                                 const float* shift, const float* mean, const float* invstd, int act1, int act2,
-                                 uint64_t drop_seed, const uint8_t* drop_mask, void* workspace, size_t workspace_bytes,
+                                 const float* shift, const float* center, const float* mean, const float* invstd, int act1, int act2,
+                                 uint64_t drop_seed, int64_t drop_offset, const uint8_t* drop_mask, void* workspace, size_t workspace_bytes,
                                  int* rows_out, gsb_stream s) {
   if (check_bwd_views(x, dA1, dA2)) return -1;
   const int C = x->c, lanes = kThreads / (C / 8);
@@ -663,31 +677,31 @@ static int bn_bwd_partial_launch(const gsb_view* x, const gsb_view* dA1, const g
   float* partial = reinterpret_cast<float*>(workspace);
   PixView d2 = (dA2 && dA2->ptr) ? pv(dA2) : PixView{nullptr, 0};
   const bool fast = act1 == GSB_ACT_RELU && d2.ptr == nullptr && drop_seed == 0 && drop_mask == nullptr && scale && shift &&
-                    mean && invstd;
+                    mean && invstd && center == nullptr;
   if (x->dtype == GSB_BF16) {
     if (fast && relu_stats_fast_enabled())
       gsb::launch(bn_bwd_reduce_relu_bf16_kernel<2>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), 
           (const __nv_bfloat16*)x->ptr, x->sw, (const __nv_bfloat16*)dA1->ptr, dA1->sw, P, C, scale, shift, mean, invstd, partial);
     else if (fast)
       gsb::launch(bn_reduce_kernel<__nv_bfloat16, 1, true>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), 
-          pv(x), pv(dA1), d2, P, C, scale, shift, mean, invstd, act1, act2, drop_seed, drop_mask, partial);
+          pv(x), pv(dA1), d2, P, C, scale, shift, center, mean, invstd, act1, act2, drop_seed, drop_offset, drop_mask, partial);
     else
       gsb::launch(bn_reduce_kernel<__nv_bfloat16, 1, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), 
-          pv(x), pv(dA1), d2, P, C, scale, shift, mean, invstd, act1, act2, drop_seed, drop_mask, partial);
+          pv(x), pv(dA1), d2, P, C, scale, shift, center, mean, invstd, act1, act2, drop_seed, drop_offset, drop_mask, partial);
   } else {
-    gsb::launch(bn_reduce_kernel<float, 1, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), pv(dA1), d2, P, C, scale, shift, mean,
-                                                                             invstd, act1, act2, drop_seed, drop_mask, partial);
+    gsb::launch(bn_reduce_kernel<float, 1, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), pv(dA1), d2, P, C, scale, shift, center, mean,
+                                                                             invstd, act1, act2, drop_seed, drop_offset, drop_mask, partial);
   }
   *rows_out = grid * wide;
   return 0;
 }
 
 extern "C" int gsb_bn_bwd_reduce(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
-                                 const float* shift, const float* mean, const float* invstd, int act1, int act2,
-                                 uint64_t drop_seed, const uint8_t* drop_mask, double* sums, void* workspace,
+                                 const float* shift, const float* center, const float* mean, const float* invstd, int act1, int act2,
+                                 uint64_t drop_seed, int64_t drop_offset, const uint8_t* drop_mask, double* sums, void* workspace,
                                  size_t workspace_bytes, gsb_stream s) {
   int grid = 0;
-  if (bn_bwd_partial_launch(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, drop_seed, drop_mask, workspace,
+  if (bn_bwd_partial_launch(x, dA1, dA2, scale, shift, center, mean, invstd, act1, act2, drop_seed, drop_offset, drop_mask, workspace,
                             workspace_bytes, &grid, s))
     return -1;
   int n = 2 * x->c;
@@ -696,11 +710,11 @@ extern "C" int gsb_bn_bwd_reduce(const gsb_view* x, const gsb_view* dA1, const g
 }
 
 extern "C" int gsb_bn_bwd_partial(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
-                                  const float* shift, const float* mean, const float* invstd, int act1, int act2,
-                                  uint64_t drop_seed, const uint8_t* drop_mask, void* workspace, size_t workspace_bytes,
+                                  const float* shift, const float* center, const float* mean, const float* invstd, int act1, int act2,
+                                  uint64_t drop_seed, int64_t drop_offset, const uint8_t* drop_mask, void* workspace, size_t workspace_bytes,
                                   int* rows, gsb_stream s) {
   GSB_REQUIRE(rows != nullptr, "bn_bwd_partial: rows is null");
-  if (bn_bwd_partial_launch(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, drop_seed, drop_mask, workspace,
+  if (bn_bwd_partial_launch(x, dA1, dA2, scale, shift, center, mean, invstd, act1, act2, drop_seed, drop_offset, drop_mask, workspace,
                             workspace_bytes, rows, s))
     return -1;
   return check_launch("bn_bwd_partial");
@@ -725,13 +739,15 @@ static int fill_regions(PeerRegions& regs, void* const* regions, int rank, int w
 extern "C" int gsb_bn_stats_finalize(const float* partial, int rows, int c, double count, void* const* regions, int rank,
                                      int world, const float* gamma, const float* beta, float* running_mean, float* running_var,
                                      int64_t* num_batches_tracked, float momentum, float eps, float* scale, float* shift,
-                                     float* mean, float* invstd, gsb_stream s) {
+                                     float* mean, float* invstd, int centered, gsb_stream s) {
   GSB_REQUIRE(partial && scale && shift && rows > 0 && c > 0, "bn_stats_finalize: bad arguments");
+  GSB_REQUIRE(!centered || mean != nullptr, "bn_stats_finalize: the centered form needs the mean output");
   PeerRegions regs;
   if (fill_regions(regs, regions, rank, world, c, "bn_stats_finalize")) return -1;
-  BnFusedFwd f{count, gamma, beta, running_mean, running_var, num_batches_tracked, momentum, eps, scale, shift, mean, invstd};
+  BnFusedFwd f{count, gamma, beta, running_mean, running_var, num_batches_tracked, momentum, eps, scale, shift, mean, invstd, centered};
   BnFusedBwd b{nullptr, nullptr, 0, nullptr};
-  gsb::launch(bn_stats_fused_kernel<0>, gsb::LaunchCfg((c + 15) / 16, 1024, 0, to_stream(s)), partial, rows, c, regs, rank, world, f, b);
+  gsb::launch(bn_stats_fused_kernel<0>, gsb::LaunchCfg((c + 15) / 16, 1024, 0, to_stream(s)), partial, rows, c, regs, rank, world, f, b,
+              peer_timeout_ns());
   return check_launch("bn_stats_finalize");
 }
 
@@ -743,13 +759,14 @@ extern "C" int gsb_bn_bwd_stats(const float* partial, int rows, int c, void* con
   if (fill_regions(regs, regions, rank, world, c, "bn_bwd_stats")) return -1;
   BnFusedFwd f{};
   BnFusedBwd b{dgamma, dbeta, accumulate, sums};
-  gsb::launch(bn_stats_fused_kernel<1>, gsb::LaunchCfg((c + 15) / 16, 1024, 0, to_stream(s)), partial, rows, c, regs, rank, world, f, b);
+  gsb::launch(bn_stats_fused_kernel<1>, gsb::LaunchCfg((c + 15) / 16, 1024, 0, to_stream(s)), partial, rows, c, regs, rank, world, f, b,
+              peer_timeout_ns());
   return check_launch("bn_bwd_stats");
 }
 
 extern "C" int gsb_bn_bwd_apply(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
-                                const float* shift, const float* mean, const float* invstd, int act1, int act2,
-                                uint64_t drop_seed, const uint8_t* drop_mask, const double* sums, double count,
+                                const float* shift, const float* center, const float* mean, const float* invstd, int act1, int act2,
+                                uint64_t drop_seed, int64_t drop_offset, const uint8_t* drop_mask, const double* sums, double count,
                                 const gsb_view* dx, float* dgamma, float* dbeta, gsb_stream s) {
   if (check_bwd_views(x, dA1, dA2) || check_vec_view(dx, "bn_bwd.dx")) return -1;
   GSB_REQUIRE(dx->dtype == x->dtype && dx->c == x->c && num_pixels(dx) == num_pixels(x), "bn_bwd_apply: dx mismatch");
@@ -760,17 +777,17 @@ extern "C" int gsb_bn_bwd_apply(const gsb_view* x, const gsb_view* dA1, const gs
   PixView d2 = (dA2 && dA2->ptr) ? pv(dA2) : PixView{nullptr, 0};
   double inv = count > 0 ? 1.0 / count : 0.0;
   const bool fast = act1 == GSB_ACT_RELU && d2.ptr == nullptr && drop_seed == 0 && drop_mask == nullptr && scale && shift &&
-                    mean && invstd;
+                    mean && invstd && center == nullptr;
   if (x->dtype == GSB_BF16) {
     if (fast)
       gsb::launch(bn_bwd_apply_kernel<__nv_bfloat16, true>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), 
-          pv(x), pv(dA1), d2, P, C, scale, shift, mean, invstd, act1, act2, drop_seed, drop_mask, sums, inv, pv(dx));
+          pv(x), pv(dA1), d2, P, C, scale, shift, center, mean, invstd, act1, act2, drop_seed, drop_offset, drop_mask, sums, inv, pv(dx));
     else
       gsb::launch(bn_bwd_apply_kernel<__nv_bfloat16, false>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), 
-          pv(x), pv(dA1), d2, P, C, scale, shift, mean, invstd, act1, act2, drop_seed, drop_mask, sums, inv, pv(dx));
+          pv(x), pv(dA1), d2, P, C, scale, shift, center, mean, invstd, act1, act2, drop_seed, drop_offset, drop_mask, sums, inv, pv(dx));
   } else {
-    gsb::launch(bn_bwd_apply_kernel<float, false>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), pv(dA1), d2, P, C, scale, shift, mean, invstd,
-                                                                           act1, act2, drop_seed, drop_mask, sums, inv, pv(dx));
+    gsb::launch(bn_bwd_apply_kernel<float, false>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), pv(dA1), d2, P, C, scale, shift, center, mean, invstd,
+                                                                           act1, act2, drop_seed, drop_offset, drop_mask, sums, inv, pv(dx));
   }
   if (mean != nullptr && (dgamma || dbeta))
     gsb::launch(bn_param_grad_kernel, gsb::LaunchCfg((C + 127) / 128, 128, 0, to_stream(s)), sums, C, dgamma, dbeta, 1);

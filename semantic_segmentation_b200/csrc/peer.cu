@@ -15,17 +15,32 @@
 // One NVLink one-way latency per call instead of store + system fence + flag + acquire.  A slot is reused after
 // kSlots calls; a peer can be at most one call ahead (call seq + 2 needs this rank's packets of call seq + 1, which
 // are sent only after call seq has been read), so kSlots = 4 leaves margin and a stale tag never equals seq.  A rank
-// that waits longer than ~2 s (a peer died) raises the region's error word and traps instead of hanging the GPU.
+// that waits longer than GSB_PEER_TIMEOUT_S (default 30 minutes; 0 = no limit) records the call in its region's error word,
+// keeps its local values and returns -- no trap; the host polls gsb_peer_error().  Every rank must issue the same sequence
+// of exchanges (train-mode BatchNorm layers, seg_loss calls): a rank that skips one leaves the others waiting.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "peer.cuh"
 
 namespace gsb {
 
+long long peer_timeout_ns() {
+  static long long ns = -1;
+  if (ns < 0) {
+    const char* e = getenv("GSB_PEER_TIMEOUT_S");
+    double sec = e != nullptr && e[0] != 0 ? atof(e) : 1800.0;
+    if (sec < 0) sec = 0;
+    ns = (long long)(sec * 1e9);
+  }
+  return ns;
+}
+
 constexpr int kPeerThreads = 1024;
 constexpr int kPeerPerThread = kPeerMaxN / kPeerThreads;
 
 __global__ void __launch_bounds__(kPeerThreads, 1) peer_allreduce_f64_kernel(double* __restrict__ buf, int n, PeerRegions regs,
-                                                                              int rank, int world) {
+                                                                              int rank, int world, long long timeout_ns) {
   GSB_PDL_ENTRY();
   __shared__ unsigned long long s_seq;
   PeerHeader* mine = reinterpret_cast<PeerHeader*>(regs.r[rank]);
@@ -48,26 +63,28 @@ __global__ void __launch_bounds__(kPeerThreads, 1) peer_allreduce_f64_kernel(dou
   }
   // 3. poll the packets of my elements, sum in rank order
   const char* base = reinterpret_cast<const char*>(mine) + kPeerHeaderBytes + (size_t)slot * kPeerMaxWorld * kPeerMaxN * 16;
-  const long long t0 = clock64();
+  const unsigned long long t0 = global_ns();
 #pragma unroll
   for (int j = 0; j < kPeerPerThread; ++j) {
     const int i = threadIdx.x + j * kPeerThreads;
     if (i < n) {
       double a = 0.0;
-      for (int q = 0; q < world; ++q) {
+      bool ok = true;
+      for (int q = 0; q < world && ok; ++q) {
         const char* src = base + ((size_t)q * kPeerMaxN + i) * 16;
         uint4 v = ld_packet(src);
+        unsigned int spins = 0;
         while (v.y != tag || v.w != tag) {
-          if (clock64() - t0 > 4000000000ll) {  // ~2 s: a peer is gone
-            mine->error = s_seq;
-            __threadfence_system();
-            __trap();
+          if (timeout_ns > 0 && (++spins & 1023u) == 0 && global_ns() - t0 > (unsigned long long)timeout_ns) {
+            ok = false;   // watchdog: record the call, keep the local value, return normally (host: gsb_peer_error)
+            break;
           }
           v = ld_packet(src);
         }
         a += __longlong_as_double((long long)(((unsigned long long)v.z << 32) | (unsigned long long)v.x));
       }
-      buf[i] = a;
+      if (ok) buf[i] = a;
+      else mine->error = s_seq;
     }
   }
 }
@@ -117,6 +134,17 @@ extern "C" int gsb_peer_close(void* peer_region) {
   return 0;
 }
 
+// Error word of this rank's OWN region: 0, or the sequence number of an exchange that gave up waiting (synchronises the
+// device: call it at a step / epoch boundary, not per layer).
+extern "C" int gsb_peer_error(void* region, unsigned long long* seq_out) {
+  GSB_REQUIRE(region && seq_out, "peer_error: null pointer");
+  PeerHeader h;
+  cudaError_t e = cudaMemcpy(&h, region, sizeof(h), cudaMemcpyDeviceToHost);
+  GSB_REQUIRE(e == cudaSuccess, "peer_error: %s", cudaGetErrorString(e));
+  *seq_out = h.error;
+  return 0;
+}
+
 extern "C" int gsb_peer_destroy(void* region) {
   if (region == nullptr) return 0;
   cudaError_t e = cudaFree(region);
@@ -137,6 +165,6 @@ extern "C" int gsb_peer_allreduce_f64(double* buf, int n, void* const* regions, 
     GSB_REQUIRE(regions[i] != nullptr, "peer_allreduce: region %d is null", i);
     regs.r[i] = regions[i];
   }
-  gsb::launch(peer_allreduce_f64_kernel, gsb::LaunchCfg(1, 1024, 0, to_stream(s)), buf, n, regs, rank, world);
+  gsb::launch(peer_allreduce_f64_kernel, gsb::LaunchCfg(1, 1024, 0, to_stream(s)), buf, n, regs, rank, world, peer_timeout_ns());
   return check_launch("peer_allreduce_f64");
 }

@@ -46,15 +46,27 @@ def act_dtype() -> torch.dtype:
 
 
 # --- cross-rank reductions (sync-BN / global Dice); installed by parallel.py ----------------------
-_REDUCER = {"fn": None, "world": 1, "sync_bn": False, "peer": None, "grad_fn": None, "sm_reserve": 0}
+_REDUCER = {"fn": None, "world": 1, "rank": 0, "sync_bn": False, "peer": None, "grad_fn": None, "sm_reserve": 0}
 
 
-def install_reducer(fn, world: int, sync_bn: bool, peer=None, grad_fn=None, sm_reserve: int = 0) -> None:
+def first_global_sample(n_local: int) -> int:
+    """Index of this rank's first sample in the global batch (equal shards, rank-major: parallel.shard_batch)."""
+    return int(_REDUCER.get("rank", 0)) * int(n_local) if int(_REDUCER.get("world", 1)) > 1 else 0
+
+
+def centered_bn() -> bool:
+    """fp32 validation mode: BatchNorm is applied as (x - mean) * scale + beta like torch; the bf16 production mode keeps the
+    folded x * scale + shift (its inputs carry 2^-9 relative rounding anyway)."""
+    return _CONFIG["dtype"] == torch.float32
+
+
+def install_reducer(fn, world: int, sync_bn: bool, peer=None, grad_fn=None, sm_reserve: int = 0, rank: int = 0) -> None:
     """peer = {"regions", "rank", "world"}: NVLink peer regions (parallel.py) -- the BatchNorm statistic kernels then do
     their cross-rank sums themselves instead of calling ``fn`` between launches.
     grad_fn(tensor) -> handle with .wait(): asynchronous in-place gradient all-reduce; when set, the U-Net program
     all-reduces its gradients inside backward (first bucket overlapped with the encoder backward)."""
-    _REDUCER.update(fn=fn, world=int(world), sync_bn=bool(sync_bn), peer=peer, grad_fn=grad_fn, sm_reserve=int(sm_reserve))
+    _REDUCER.update(fn=fn, world=int(world), sync_bn=bool(sync_bn), peer=peer, grad_fn=grad_fn, sm_reserve=int(sm_reserve),
+                    rank=int(rank))
 
 
 def _fused_stats_mode():
@@ -124,7 +136,9 @@ class Saved:
     count: float = 0.0
     weight: Optional[torch.Tensor] = None     # fp32 weight in torch layout as used in forward
     drop_seed: int = 0
+    drop_offset: int = 0                      # global element index of the tensor's first element (Philox dropout)
     drop_mask: Optional[torch.Tensor] = None
+    center: Optional[torch.Tensor] = None     # = mean in the centered (fp32) form, else None
     extra: Dict[str, object] = field(default_factory=dict)
 
 
@@ -295,6 +309,9 @@ class ConvBNAct:
         sv = Saved()
         count = float(n * oh * ow)
         scale = shift = mean = invstd = None
+        centered = centered_bn()
+        first = first_global_sample(n)
+        drop_offset = first * oh * ow * s.cout
         if self.has_bn and self.instance:
             if out1 is None:
                 out1 = _nhwc_empty(n, oh, ow, s.cout, device)
@@ -304,11 +321,13 @@ class ConvBNAct:
             for i in range(n):
                 yi = y[i:i + 1]
                 sums_i = ops.bn_reduce(yi)
-                st_i = ops.bn_finalize(sums_i, count, None, None, None, None, None, BN_MOMENTUM, BN_EPS, s.cout, device)
-                seed_i = (drop_seed + 104729 * (i + 1)) if (use_drop and drop_seed) else 0
+                st_i = ops.bn_finalize(sums_i, count, None, None, None, None, None, BN_MOMENTUM, BN_EPS, s.cout, device,
+                                       centered=centered)
+                seed_i = (drop_seed + 104729 * (first + i + 1)) if (use_drop and drop_seed) else 0
                 mask_i = drop_mask[i:i + 1] if (use_drop and drop_mask is not None) else None
                 ops.bn_act(yi, st_i[0], st_i[1], self.act1, out1[i:i + 1], self.act2 if self.act2 is not None else ACT_NONE,
-                           out2[i:i + 1] if self.act2 is not None else None, seed_i, mask_i)
+                           out2[i:i + 1] if self.act2 is not None else None, seed_i, mask_i,
+                           center=st_i[2] if centered else None)
                 per.append((st_i, seed_i, mask_i))
             if save:
                 sv.x_view, sv.x_keep, sv.y = x_view, x_keep, y
@@ -324,25 +343,28 @@ class ConvBNAct:
             if training and stats is not None and fused_ok:
                 count = count * pworld
                 scale, shift, mean, invstd = ops.bn_stats_finalize(stats, rows, s.cout, count, gamma, beta, rm, rv, nbt,
-                                                                   BN_MOMENTUM, BN_EPS, peer)
+                                                                   BN_MOMENTUM, BN_EPS, peer, centered=centered)
             elif training:
                 sums = ops.bn_reduce_partials(stats, rows, s.cout) if stats is not None else ops.bn_reduce(y)
                 sums, count = _sync_stats(sums, count)
                 scale, shift, mean, invstd = ops.bn_finalize(sums, count, gamma, beta, rm, rv, nbt, BN_MOMENTUM, BN_EPS,
-                                                             s.cout, device)
+                                                             s.cout, device, centered=centered)
             else:
                 scale, shift, mean, invstd = ops.bn_finalize(None, count, gamma, beta, rm, rv, None, BN_MOMENTUM,
-                                                             BN_EPS, s.cout, device)
+                                                             BN_EPS, s.cout, device, centered=centered)
         if out1 is None:
             out1 = _nhwc_empty(n, oh, ow, s.cout, device)
         use_drop = self.dropout and training
+        center = mean if (centered and self.has_bn) else None
         ops.bn_act(y, scale, shift, self.act1, out1, self.act2 if self.act2 is not None else ACT_NONE,
                    out2 if self.act2 is not None else None, drop_seed if use_drop else 0,
-                   drop_mask if use_drop else None)
+                   drop_mask if use_drop else None, center=center, drop_offset=drop_offset if use_drop else 0)
         if save:
             sv.x_view, sv.x_keep, sv.y = x_view, x_keep, y
             sv.scale, sv.shift, sv.mean, sv.invstd, sv.count = scale, shift, mean, invstd, count
             sv.weight = weight
+            sv.center = center
+            sv.drop_offset = drop_offset if use_drop else 0
             sv.drop_seed = drop_seed if use_drop else 0
             sv.drop_mask = drop_mask if use_drop else None
             sv.extra["train_bn"] = self.has_bn and training
@@ -370,16 +392,19 @@ class ConvBNAct:
             for i, (st_i, seed_i, mask_i) in enumerate(inst):
                 sc, sh, mu, istd = st_i
                 a1, a2 = dA1[i:i + 1], (dA2[i:i + 1] if dA2 is not None else None)
-                sums_i, _, _ = ops.bn_bwd_stats(y[i:i + 1], a1, a2, sc, sh, mu, istd, self.act1, act2, seed_i, mask_i, False, None)
+                ce_i = mu if centered_bn() else None
+                sums_i, _, _ = ops.bn_bwd_stats(y[i:i + 1], a1, a2, sc, sh, mu, istd, self.act1, act2, seed_i, mask_i, False, None,
+                                                center=ce_i)
                 ops.bn_bwd_apply(y[i:i + 1], a1, a2, sc, sh, mu, istd, self.act1, act2, sums_i, sv.count, dY[i:i + 1], None, None,
-                                 seed_i, mask_i)
+                                 seed_i, mask_i, center=ce_i)
         elif train_bn and fused_ok:
             sums, dgamma, dbeta = ops.bn_bwd_stats(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2,
-                                                   sv.drop_seed, sv.drop_mask, need_bn, peer)
+                                                   sv.drop_seed, sv.drop_mask, need_bn, peer, center=sv.center,
+                                                   drop_offset=sv.drop_offset)
             mean, invstd = sv.mean, sv.invstd
         elif train_bn:
             sums = ops.bn_bwd_reduce(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2,
-                                     sv.drop_seed, sv.drop_mask)
+                                     sv.drop_seed, sv.drop_mask, center=sv.center, drop_offset=sv.drop_offset)
             if need_bn:   # parameter gradients from the LOCAL sums (the gradient all-reduce adds the other ranks)
                 dgamma, dbeta = ops.bn_param_grad(sums, s.cout)
             sums, _ = _sync_stats(sums, 0.0)
@@ -387,11 +412,11 @@ class ConvBNAct:
         elif self.has_bn and need_bn:
             # eval-mode BatchNorm (running statistics are constants): dgamma = sum dy*xhat_running, dbeta = sum dy
             es = ops.bn_bwd_reduce(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2,
-                                   sv.drop_seed, sv.drop_mask)
+                                   sv.drop_seed, sv.drop_mask, center=sv.center, drop_offset=sv.drop_offset)
             dgamma, dbeta = ops.bn_param_grad(es, s.cout)
         if inst is None:
             ops.bn_bwd_apply(y, dA1, dA2, sv.scale, sv.shift, mean, invstd, self.act1, act2, sums, sv.count, dY,
-                             None, None, sv.drop_seed, sv.drop_mask)
+                             None, None, sv.drop_seed, sv.drop_mask, center=sv.center, drop_offset=sv.drop_offset)
         dyv = view_nhwc(dY)
         dweight = dbias = None
         if need_dw and sv.extra.get("stem"):

@@ -114,6 +114,8 @@ class GeneratorProgram:
         arch = arch.contiguous()
         self._calls += 1
         masks = (extra or {}).get("drop_masks")
+        # one seed per forward call, the same on every rank (same torch seed, same call count); the masks are indexed by the
+        # GLOBAL element index (engine.first_global_sample), so a batch sharded over N ranks draws the one-rank masks
         base_seed = int((extra or {}).get("drop_seed", 0)) or (torch.initial_seed() * 1000003 + self._calls) % (1 << 62) + 1
         tape: Dict[str, object] = {"x": x, "arch": arch}
         c = self.c

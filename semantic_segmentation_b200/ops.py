@@ -80,6 +80,13 @@ def copy_view(src: GsbView, dst: GsbView, stream: int) -> None:
     check(load().gsb_copy_view(_ref(src), _ref(dst), stream), "copy_view")
 
 
+def cast_flat(src: torch.Tensor, dst: torch.Tensor) -> None:
+    """dst <- cast(src) for contiguous fp32 / bf16 buffers of equal length (gradient buckets)."""
+    assert src.is_contiguous() and dst.is_contiguous() and src.numel() == dst.numel()
+    check(load().gsb_cast_flat(ptr(src), L.dtype_code(src.dtype), ptr(dst), L.dtype_code(dst.dtype), src.numel(), _s(src)),
+          "cast_flat")
+
+
 def pack_weight(w: torch.Tensor, rows_from_d0: bool, dtype: torch.dtype) -> torch.Tensor:
     """fp32 [d0,d1,kh,kw] -> [kh*kw, rows, cols] in `dtype` (cols contiguous)."""
     assert w.dtype == torch.float32 and w.is_contiguous()
@@ -302,40 +309,46 @@ def bn_reduce_partials(partial: torch.Tensor, rows: int, c: int) -> torch.Tensor
 
 
 def bn_finalize(sums: Optional[torch.Tensor], count: float, gamma, beta, running_mean, running_var, nbt,
-                momentum: float, eps: float, c: int, device, want_saved: bool = True):
+                momentum: float, eps: float, c: int, device, want_saved: bool = True, centered: bool = False):
+    """centered: shift = beta and the consumers get center = mean, i.e. (x - mean) * scale + beta (fp32 validation mode);
+    otherwise the folded form x * scale + (beta - mean * scale)."""
     scale = torch.empty(c, device=device, dtype=torch.float32)
     shift = torch.empty(c, device=device, dtype=torch.float32)
     mean = torch.empty(c, device=device, dtype=torch.float32) if want_saved else None
     invstd = torch.empty(c, device=device, dtype=torch.float32) if want_saved else None
     check(load().gsb_bn_finalize(ptr(sums), float(count), ptr(gamma), ptr(beta), ptr(running_mean), ptr(running_var),
                                  ptr(nbt), float(momentum), float(eps), c, ptr(scale), ptr(shift), ptr(mean),
-                                 ptr(invstd), stream_ptr(device)), "bn_finalize")
+                                 ptr(invstd), int(centered), stream_ptr(device)), "bn_finalize")
     return scale, shift, mean, invstd
 
 
 def bn_act(x: torch.Tensor, scale, shift, act1: int, out1: torch.Tensor, act2: int = ACT_NONE,
-           out2: Optional[torch.Tensor] = None, drop_seed: int = 0, drop_mask: Optional[torch.Tensor] = None) -> None:
+           out2: Optional[torch.Tensor] = None, drop_seed: int = 0, drop_mask: Optional[torch.Tensor] = None,
+           center: Optional[torch.Tensor] = None, drop_offset: int = 0) -> None:
+    """z = (x - center) * scale + shift (center None = 0); drop_offset: global element index of this tensor's first element
+    (Philox dropout masks of a sharded batch equal those of the one-rank run)."""
     v2 = view_nhwc(out2) if out2 is not None else None
-    check(load().gsb_bn_act(_ref(view_nhwc(x)), ptr(scale), ptr(shift), act1, _ref(view_nhwc(out1)), act2, _ref(v2),
-                            int(drop_seed), ptr(drop_mask), _s(x)), "bn_act")
+    check(load().gsb_bn_act(_ref(view_nhwc(x)), ptr(scale), ptr(shift), ptr(center), act1, _ref(view_nhwc(out1)), act2, _ref(v2),
+                            int(drop_seed), int(drop_offset), ptr(drop_mask), _s(x)), "bn_act")
 
 
-def bn_bwd_reduce(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, drop_seed=0, drop_mask=None) -> torch.Tensor:
+def bn_bwd_reduce(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, drop_seed=0, drop_mask=None, center=None,
+                  drop_offset=0) -> torch.Tensor:
     v = view_nhwc(x)
     ws = _bn_ws(v, x.device)
     sums = torch.empty(2 * v.c, device=x.device, dtype=torch.float64)
     v2 = view_nhwc(dA2) if dA2 is not None else None
-    check(load().gsb_bn_bwd_reduce(_ref(v), _ref(view_nhwc(dA1)), _ref(v2), ptr(scale), ptr(shift), ptr(mean),
-                                   ptr(invstd), act1, act2, int(drop_seed), ptr(drop_mask), ptr(sums), ptr(ws),
-                                   ws.numel() * 4, _s(x)), "bn_bwd_reduce")
+    check(load().gsb_bn_bwd_reduce(_ref(v), _ref(view_nhwc(dA1)), _ref(v2), ptr(scale), ptr(shift), ptr(center), ptr(mean),
+                                   ptr(invstd), act1, act2, int(drop_seed), int(drop_offset), ptr(drop_mask), ptr(sums),
+                                   ptr(ws), ws.numel() * 4, _s(x)), "bn_bwd_reduce")
     return sums
 
 
 def bn_bwd_apply(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, sums, count, dx, dgamma=None, dbeta=None,
-                 drop_seed=0, drop_mask=None) -> None:
+                 drop_seed=0, drop_mask=None, center=None, drop_offset=0) -> None:
     v2 = view_nhwc(dA2) if dA2 is not None else None
-    check(load().gsb_bn_bwd_apply(_ref(view_nhwc(x)), _ref(view_nhwc(dA1)), _ref(v2), ptr(scale), ptr(shift),
-                                  ptr(mean), ptr(invstd), act1, act2, int(drop_seed), ptr(drop_mask), ptr(sums),
+    check(load().gsb_bn_bwd_apply(_ref(view_nhwc(x)), _ref(view_nhwc(dA1)), _ref(v2), ptr(scale), ptr(shift), ptr(center),
+                                  ptr(mean), ptr(invstd), act1, act2, int(drop_seed), int(drop_offset), ptr(drop_mask), ptr(sums),
                                   float(count), _ref(view_nhwc(dx)), ptr(dgamma), ptr(dbeta), _s(x)), "bn_bwd_apply")
 
 
@@ -354,7 +367,7 @@ def _peer_args(peer):
 
 
 def bn_stats_finalize(partial: torch.Tensor, rows: int, c: int, count: float, gamma, beta, running_mean, running_var, nbt,
-                      momentum: float, eps: float, peer=None):
+                      momentum: float, eps: float, peer=None, centered: bool = False):
     """Statistic rows -> (cross-rank sum over the peer regions) -> scale, shift, mean, invstd + running statistics:
     one launch.  ``count`` is the GLOBAL element count per channel."""
     dev = partial.device
@@ -365,21 +378,21 @@ def bn_stats_finalize(partial: torch.Tensor, rows: int, c: int, count: float, ga
     arr, rank, world = _peer_args(peer)
     check(load().gsb_bn_stats_finalize(ptr(partial), int(rows), c, float(count), arr, rank, world, ptr(gamma), ptr(beta),
                                        ptr(running_mean), ptr(running_var), ptr(nbt), float(momentum), float(eps), ptr(scale),
-                                       ptr(shift), ptr(mean), ptr(invstd), _s(partial)), "bn_stats_finalize")
+                                       ptr(shift), ptr(mean), ptr(invstd), int(centered), _s(partial)), "bn_stats_finalize")
     return scale, shift, mean, invstd
 
 
 def bn_bwd_stats(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, drop_seed=0, drop_mask=None, want_param_grads=True,
-                 peer=None):
+                 peer=None, center=None, drop_offset=0):
     """[sum dy, sum dy*xhat] in two launches: per-block rows, then totals + dgamma / dbeta (local) + cross-rank sum.
     -> (global sums fp64 [2c], dgamma, dbeta)."""
     v = view_nhwc(x)
     ws = _bn_ws(v, x.device)
     rows = C.c_int(0)
     v2 = view_nhwc(dA2) if dA2 is not None else None
-    check(load().gsb_bn_bwd_partial(_ref(v), _ref(view_nhwc(dA1)), _ref(v2), ptr(scale), ptr(shift), ptr(mean), ptr(invstd),
-                                    act1, act2, int(drop_seed), ptr(drop_mask), ptr(ws), ws.numel() * 4, C.byref(rows),
-                                    _s(x)), "bn_bwd_partial")
+    check(load().gsb_bn_bwd_partial(_ref(v), _ref(view_nhwc(dA1)), _ref(v2), ptr(scale), ptr(shift), ptr(center), ptr(mean),
+                                    ptr(invstd), act1, act2, int(drop_seed), int(drop_offset), ptr(drop_mask), ptr(ws),
+                                    ws.numel() * 4, C.byref(rows), _s(x)), "bn_bwd_partial")
     sums = torch.empty(2 * v.c, device=x.device, dtype=torch.float64)
     dgamma = torch.empty(v.c, device=x.device, dtype=torch.float32) if want_param_grads else None
     dbeta = torch.empty(v.c, device=x.device, dtype=torch.float32) if want_param_grads else None
@@ -578,6 +591,13 @@ def peer_close(region: int) -> None:
 
 def peer_destroy(region: int) -> None:
     check(load().gsb_peer_destroy(C.c_void_p(region)), "peer_destroy")
+
+
+def peer_error(region: int) -> int:
+    """0, or the sequence number of an exchange of this rank that gave up waiting for a peer (synchronises the device)."""
+    seq = C.c_ulonglong(0)
+    check(load().gsb_peer_error(C.c_void_p(region), C.byref(seq)), "peer_error")
+    return int(seq.value)
 
 
 def peer_max_elems() -> int:

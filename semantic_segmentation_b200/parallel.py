@@ -50,19 +50,46 @@ def _setup_peer_memory(group) -> None:
     _GROUP["peer"] = {"regions": regions, "max": ops.peer_max_elems(), "own": region, "world": world}
 
 
+class _Bf16Bucket:
+    """An fp32 gradient bucket whose all-reduce travels as bf16 (half the NVLink bytes): cast -> asynchronous NCCL
+    all-reduce of the bf16 copy -> ``wait()`` casts the sum back over the fp32 bucket.  The fp32 tensor stays the
+    parameter's ``.grad`` storage."""
+
+    def __init__(self, t: torch.Tensor):
+        from . import ops
+        self.t = t
+        self.buf = torch.empty(t.numel(), device=t.device, dtype=torch.bfloat16)
+        ops.cast_flat(t, self.buf)
+        self.work = dist.all_reduce(self.buf, op=dist.ReduceOp.SUM, group=_GROUP["pg"], async_op=True)
+
+    def wait(self) -> None:
+        from . import ops
+        self.work.wait()
+        ops.cast_flat(self.buf, self.t)
+
+
 def _allreduce_async(t: torch.Tensor):
+    """Asynchronous in-place sum of a flat fp32 gradient bucket over the ranks -> handle with .wait().
+    GSB_GRAD_COMM_DTYPE=bf16 (set by init_data_parallel(grad_comm_dtype=...)) sends the bucket as bf16."""
+    if (_GROUP.get("grad_dtype") == torch.bfloat16 and t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()
+            and t.data_ptr() % 16 == 0 and t.numel() >= 4096):
+        return _Bf16Bucket(t)
     return dist.all_reduce(t, op=dist.ReduceOp.SUM, group=_GROUP["pg"], async_op=True)
 
 
 def init_data_parallel(sync_bn: bool = True, group=None, backend: Optional[str] = None,
-                       overlap_grad_allreduce: bool = False) -> int:
+                       overlap_grad_allreduce: bool = False, grad_comm_dtype: Optional[str] = None) -> int:
     """Initialise (if needed) torch.distributed from the torchrun env and install the cross-rank reducers.
     Returns the world size.
 
     overlap_grad_allreduce: the U-Net program all-reduces its gradients INSIDE backward -- the decoder + bottleneck
     bucket (72 % of the bytes) as soon as it is final, on the collective's stream, under the encoder backward; the
     rest at the end -- and marks the parameters so that ``allreduce_gradients`` skips them.  Use it with
-    ``loss.backward()`` training loops (``torch.autograd.grad`` callers keep it off)."""
+    ``loss.backward()`` training loops (``torch.autograd.grad`` callers keep it off).
+
+    grad_comm_dtype: 'fp32' (default; an N-rank run then equals the 1-rank run up to fp32 summation order) or 'bf16'
+    (gradient buckets are cast to bf16 for the all-reduce: half the bytes, 2^-9 relative rounding per addend); the
+    environment variable GSB_GRAD_COMM_DTYPE overrides."""
     if not dist.is_initialized():
         if "RANK" not in os.environ:
             engine.install_reducer(None, 1, False)
@@ -73,6 +100,10 @@ def init_data_parallel(sync_bn: bool = True, group=None, backend: Optional[str] 
         if backend == "nccl":
             torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
         dist.init_process_group(backend=backend)
+    gd = os.environ.get("GSB_GRAD_COMM_DTYPE", grad_comm_dtype or "fp32").lower()
+    if gd not in ("fp32", "bf16"):
+        raise ValueError("grad_comm_dtype must be 'fp32' or 'bf16'")
+    _GROUP["grad_dtype"] = torch.bfloat16 if gd == "bf16" else torch.float32
     _GROUP["pg"] = group
     _GROUP["world"] = dist.get_world_size(group)
     _GROUP["rank"] = dist.get_rank(group)
@@ -85,11 +116,32 @@ def init_data_parallel(sync_bn: bool = True, group=None, backend: Optional[str] 
     multi = _GROUP["world"] > 1
     engine.install_reducer(_allreduce_sum if multi else None, _GROUP["world"], sync_bn, peer_arg,
                            grad_fn=_allreduce_async if (multi and overlap_grad_allreduce) else None,
-                           sm_reserve=int(os.environ.get("GSB_OVERLAP_SM_RESERVE", "16")) if multi and overlap_grad_allreduce else 0)
+                           sm_reserve=int(os.environ.get("GSB_OVERLAP_SM_RESERVE", "16")) if multi and overlap_grad_allreduce else 0,
+                           rank=_GROUP["rank"])
     return _GROUP["world"]
 
 
+def check_peer_health() -> None:
+    """Raise if one of this rank's peer-memory exchanges (sync-BN statistics, CE / Dice sums) gave up waiting for a peer
+    (GSB_PEER_TIMEOUT_S, default 30 minutes).  The kernels never trap: they record the call, continue with the local value
+    and return, so the CUDA context stays usable and the failure surfaces here as an ordinary exception.  Synchronises the
+    device: call it at step / epoch boundaries (``evaluate`` and ``shutdown`` do).  Every rank must issue the same sequence
+    of train-mode BatchNorm layers and ``seg_loss`` calls; a rank that skips one (a validation loss only rank 0 computes)
+    leaves the others waiting."""
+    peer = _GROUP["peer"]
+    if peer is None:
+        return
+    from . import ops
+    seq = ops.peer_error(peer["own"])
+    if seq:
+        raise RuntimeError("genseg_b200: peer-memory exchange #%d on rank %d timed out waiting for a peer "
+                           "(GSB_PEER_TIMEOUT_S); the ranks did not issue the same sequence of sync-BN / seg_loss calls, "
+                           "or a peer died" % (seq, _GROUP["rank"]))
+
+
 def shutdown() -> None:
+    if _GROUP["peer"] is not None and _GROUP["world"] > 1:
+        check_peer_health()
     engine.install_reducer(None, 1, False)
     _GROUP.update(pg=None, world=1, rank=0)   # peer regions stay mapped: a later init_data_parallel reuses them
 
@@ -128,14 +180,22 @@ def allreduce_gradients(params: Iterable[torch.Tensor]) -> None:
             grads.append(p.grad)
     if not grads:
         return
-    # one flat bucket per dtype: a single NCCL all-reduce instead of one latency-bound launch per parameter
-    by_dtype = {}
+    # Large contiguous gradients (the generator's 64 MB up-cell kernels) are reduced IN PLACE, back to back and
+    # asynchronously: no concatenated copy of a 1 GB gradient set.  The small ones (BatchNorm, biases, thin layers) share
+    # one flat bucket per dtype: a single all-reduce instead of one latency-bound launch per parameter.
+    big, small = [], {}
     for g in grads:
-        by_dtype.setdefault(g.dtype, []).append(g)
-    for gs in by_dtype.values():
+        if g.is_contiguous() and g.numel() >= (1 << 20):
+            big.append(g)
+        else:
+            small.setdefault(g.dtype, []).append(g)
+    handles = [_allreduce_async(g.view(-1)) for g in big]
+    for gs in small.values():
         flat = torch.cat([g.reshape(-1) for g in gs])
         dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=_GROUP["pg"])
         torch._foreach_copy_(gs, [c.view_as(g) for c, g in zip(flat.split([g.numel() for g in gs]), gs)])
+    for h in handles:
+        h.wait()
 
 
 def mean_over_ranks(total, count: int) -> torch.Tensor:

@@ -240,9 +240,10 @@ class UNetProgram:
             # route through the 2x2 max-pool into the skip gradient already holding the concat part
             ops.maxpool2_bwd(skips[i], dpooled, dskip[i], accumulate=True)
             dcur = dskip[i]
-            if i == 3:
-                # decoder + bottleneck weight gradients (72 % of the parameters) are final: start their all-reduce now,
-                # it runs on the collective's stream under the remaining (most expensive) part of the backward pass
+            if i >= 2:
+                # i == 3: decoder + bottleneck weight gradients (72 % of the parameters) are final: start their all-reduce
+                # now, it runs on the collective's stream under the remaining (most expensive) part of the backward pass;
+                # i == 2: down3 (20 %) follows, so that only 7 % of the bytes are left for the exposed tail bucket
                 batch.reduce_async()
         dx = None
         dxv = None
