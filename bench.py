@@ -4,6 +4,7 @@
 
     python bench.py --gpus N --steps K --warmup W            # our arm (one JSON line on rank 0)
     python bench.py --impl reference --steps K --warmup W    # the CPU oracle port on the host cores
+    python bench.py --workload pix2pix|genseg|eval ...       # BASELINE configs 3 / 4 / 5 (same JSON contract, own metric)
 
 See the module docstrings of semantic_segmentation_b200 and DESIGN.md for what is timed.
 """
@@ -196,6 +197,100 @@ def committed_traffic(per_gpu_batch: int):
         return None
 
 
+def run_secondary(args):
+    """BASELINE configs 3 (pix2pix), 4 (genseg), 5 (eval) through the same contract: W warm-up steps, K timed steps between
+    barriers, CUDA events, max over ranks, clocks sampled during the timed region, end-to-end leg with the host -> device
+    copy of every step's inputs and a device -> host read of its result.  Weak scaling: 8 images per GPU."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import bench_workloads as BW
+    from semantic_segmentation_b200 import _lib, parallel
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        parallel.init_data_parallel(sync_bn=not args.no_sync_bn, overlap_grad_allreduce=not args.no_overlap,
+                                    grad_comm_dtype=args.grad_comm_dtype)
+    rank = parallel.rank()
+    lib = _lib.load()
+    per = args.per_gpu_batch or 8
+    lines = []
+    cases = [(64, 256), (16, 512), (4, 1024)] if args.workload == "eval" else [None]
+    for case in cases:
+        if args.workload == "pix2pix":
+            wl = BW.pix2pix(dev, per, rank, world)
+        elif args.workload == "genseg":
+            wl = BW.genseg(dev, per, rank, world)
+        else:
+            wl = BW.evaluate(dev, case[0], case[1])
+        host = wl["host_batch"]
+        static = tuple(t.to(dev) for t in host)
+
+        def barrier():
+            if world > 1:
+                torch.distributed.barrier()
+            torch.cuda.synchronize()
+
+        def timed(fn, steps):
+            barrier()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            for _ in range(steps):
+                fn()
+            e.record()
+            barrier()
+            t = torch.tensor([s.elapsed_time(e) * 1e-3], device=dev, dtype=torch.float64)
+            if world > 1:
+                torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+            return float(t.item())
+
+        for _ in range(max(args.warmup, 3)):
+            wl["step"](static)
+        sampler = ClockSampler(local_rank)
+        if rank == 0:
+            sampler.start()
+        l0 = lib.gsb_launch_count()
+        torch.cuda.profiler.start()
+        t_dev = timed(lambda: wl["step"](static), args.steps)
+        torch.cuda.profiler.stop()
+        launches = int(lib.gsb_launch_count() - l0)
+        clocks = sampler.stop() if rank == 0 else None
+
+        def e2e_step():
+            for d, h in zip(static, host):
+                d.copy_(h, non_blocking=True)             # this step's inputs from pinned host memory
+            return float(wl["step"](static).item())       # and its result back to the host
+
+        e2e_step()
+        t_e2e = timed(e2e_step, args.steps)
+        units = wl["units"] * world * args.steps
+        if rank != 0:
+            continue
+        burst, sustained, hbm, src = peaks()
+        line = {"metric": wl["metric"], "value": units / t_dev, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                "config": {"workload": wl["workload"], "global_batch": wl["units"] * world, "per_gpu_batch": wl["units"],
+                           "parallelism": "dp%d" % world if args.workload != "eval" else "replicas x%d" % world,
+                           "sync_bn": bool(world > 1 and not args.no_sync_bn and args.workload != "eval"),
+                           "grad_comm_dtype": args.grad_comm_dtype if world > 1 and args.workload != "eval" else None,
+                           "cuda_graph": False, "l2": "per-step working set exceeds the 126 MB L2; no flush needed"},
+                "e2e": {"value": units / t_e2e, "unit": "images/s",
+                        "h2d_bytes_per_step": int(sum(t.numel() * t.element_size() for t in host)) * world, "d2h_bytes_per_step": 4 * world},
+                "gpu_launches": launches, "clocks": clocks}
+        if wl.get("flops_per_unit"):
+            tf = wl["flops_per_unit"] * wl["units"] * args.steps / t_dev / 1e12
+            line["roofline"] = {"bound": "tensor" if args.workload == "eval" else "hbm+tensor (weight streaming at the deep levels)",
+                                "achieved": tf, "peak": sustained, "unit": "TFLOP/s", "frac": tf / sustained, "traffic": None,
+                                "peak_source": src + " (sustained: whole step)", "flops_note": wl["flops_note"],
+                                "weight_bytes_note": wl.get("weight_bytes_note")}
+        lines.append(line)
+        del wl, static
+        torch.cuda.empty_cache()
+    for line in lines:
+        print(json.dumps(line), flush=True)
+
+
 def run_ours(args):
     import semantic_segmentation_b200 as S
     from semantic_segmentation_b200 import _lib, parallel
@@ -208,7 +303,8 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        parallel.init_data_parallel(sync_bn=not args.no_sync_bn, overlap_grad_allreduce=not args.no_overlap)
+        parallel.init_data_parallel(sync_bn=not args.no_sync_bn, overlap_grad_allreduce=not args.no_overlap,
+                                    grad_comm_dtype=args.grad_comm_dtype)
     rank = parallel.rank()
     lib = _lib.load()
     S.set_precision("bf16")
@@ -355,6 +451,7 @@ def run_ours(args):
                        "global_batch": per * world, "per_gpu_batch": per, "parallelism": "dp%d" % world,
                        "sync_bn": bool(world > 1 and not args.no_sync_bn), "cuda_graph": graph is not None, "e2e_inputs": "pinned host -> device every step, double-buffered prefetch on a copy stream",
                        "grad_allreduce": ("overlapped_in_backward" if not args.no_overlap else "after_backward") if world > 1 else None,
+                       "grad_comm_dtype": args.grad_comm_dtype if world > 1 else None,
                        "l2": "per-step working set (activations+gradients, >1 GB per GPU) exceeds the 126 MB L2; no flush needed"},
             "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": int(x_host.numel() * 4 + y_host.numel() * 8) * world,
                     "d2h_bytes_per_step": 4 * world},
@@ -367,6 +464,16 @@ def run_ours(args):
                                                   "up4.conv0 fprop<64>": small["fprop"], "up4.conv0 dgrad<128>": small["dgrad"],
                                                   "up4.conv0 wgrad<64>": small["wgrad"]},
                          "whole_step_tflops_per_gpu": step_tf, "whole_step_frac_of_sustained": step_tf / sustained}}
+    if not args.no_hbm_roofline:
+        # the non-convolution kernels against the measured copy bandwidth (target >= 0.70), each timed alone
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import bench_hbm
+        del static_x, static_y
+        torch.cuda.empty_cache()
+        rh = bench_hbm.hbm_rooflines(per, hbm)
+        line["roofline_hbm"] = {"peak": hbm, "unit": "GB/s", "peak_source": src, "per_gpu_batch": per,
+                                "kernels": {k: {"gbs": round(v["gbs"], 1), "frac": round(v["frac"], 3), "us": round(v["us"], 1),
+                                                "bytes": v["bytes"], "shape": v["shape"]} for k, v in rh.items()}}
     if world == 1 and not args.no_cpu_baseline:
         t, threads = cpu_oracle_step_time(4, 3, 1)
         line["cpu_baseline"] = {"value": 4 / t, "unit": "images/s", "cores": threads, "kind": "port",
@@ -385,12 +492,20 @@ def main():
     ap.add_argument("--no-overlap", action="store_true", help="gradient all-reduce after backward instead of inside it")
     ap.add_argument("--no-graph", action="store_true", help="launch every kernel eagerly instead of replaying a CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-hbm-roofline", action="store_true", help="skip the per-kernel HBM roofline block")
+    ap.add_argument("--workload", default="unet", choices=["unet", "pix2pix", "genseg", "eval"],
+                    help="unet = the headline (BASELINE config 2); pix2pix / genseg / eval = configs 3 / 4 / 5")
+    ap.add_argument("--grad-comm-dtype", default="bf16", choices=["fp32", "bf16"],
+                    help="dtype of the gradient buckets on the wire (N > 1); fp32 makes N ranks equal 1 rank to fp32 rounding")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
         return
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the B200 path has no CPU fallback (use --impl reference)")
+    if args.workload != "unet":
+        run_secondary(args)
+        return
     run_ours(args)
 
 

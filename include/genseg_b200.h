@@ -139,7 +139,9 @@ int gsb_bias_grad(const gsb_view* dout, float* db, void* workspace, size_t works
 /* ---- BatchNorm2d (+ activation, dropout) -- unet_parts.py:17-21, networks.py:584-607 -- */
 /* sums[2][c] (fp64) <- sum x, sum x^2 over (n,h,w); workspace >= gsb_bn_workspace_bytes. */
 size_t gsb_bn_workspace_bytes(const gsb_view* x);
-int gsb_bn_reduce(const gsb_view* x, double* sums, void* workspace, size_t workspace_bytes, gsb_stream s);
+/* per_image != 0 (here and in gsb_bn_act / gsb_bn_bwd_partial / gsb_bn_bwd_apply): InstanceNorm2d (networks.py:34-35) --
+ * statistics per (image, channel) in the SAME launches: sums are [2][n*c], per-channel arrays [n][c], count = h*w. */
+int gsb_bn_reduce(const gsb_view* x, int per_image, double* sums, void* workspace, size_t workspace_bytes, gsb_stream s);
 /* Reduce TC-conv per-CTA partials [rows][2][c] fp32 -> sums[2][c] fp64. */
 int gsb_bn_reduce_partials(const float* partial, int rows, int c, double* sums, gsb_stream s);
 /* Training finalize: mean/biased var from sums & count -> scale = g*invstd, shift = b - mean*scale,
@@ -159,7 +161,7 @@ int gsb_bn_finalize(const double* sums, double count, const float* gamma, const 
  * rank * h*w*c makes the masks of a batch sharded over N ranks those of the one-rank run. */
 int gsb_bn_act(const gsb_view* x, const float* scale, const float* shift, const float* center, int act1,
                const gsb_view* out1, int act2, const gsb_view* out2, uint64_t drop_seed, int64_t drop_offset,
-               const uint8_t* drop_mask, gsb_stream s);
+               const uint8_t* drop_mask, int per_image, gsb_stream s);
 /* Backward.  dy = act1'(z)*drop*dA1 + act2'(z)*dA2 (dA2 nullable), z as above.
  * reduce: sums[2][c] fp64 <- sum dy, sum dy*xhat.   apply (has_bn): dx = scale*(dy - s0/cnt - xhat*s1/cnt);
  * (no bn: pass mean = NULL -> dx = dy).  dgamma/dbeta accumulate (nullable). */
@@ -170,7 +172,7 @@ int gsb_bn_bwd_reduce(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA
 int gsb_bn_bwd_apply(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
                      const float* shift, const float* center, const float* mean, const float* invstd, int act1, int act2,
                      uint64_t drop_seed, int64_t drop_offset, const uint8_t* drop_mask, const double* sums, double count,
-                     const gsb_view* dx, float* dgamma, float* dbeta, gsb_stream s);
+                     const gsb_view* dx, float* dgamma, float* dbeta, int per_image, gsb_stream s);
 
 /* dbeta[c] (+)= sums[c], dgamma[c] (+)= sums[c + C]: parameter gradients from the LOCAL backward sums (under
  * sync-BN the sums are all-reduced afterwards; the gradient all-reduce then adds the other ranks' parts). */
@@ -187,7 +189,7 @@ int gsb_bn_stats_finalize(const float* partial, int rows, int c, double count, v
 int gsb_bn_bwd_partial(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale, const float* shift,
                        const float* center, const float* mean, const float* invstd, int act1, int act2, uint64_t drop_seed,
                        int64_t drop_offset, const uint8_t* drop_mask, void* workspace, size_t workspace_bytes, int* rows,
-                       gsb_stream s);
+                       int per_image, gsb_stream s);
 int gsb_bn_bwd_stats(const float* partial, int rows, int c, void* const* regions, int rank, int world, float* dgamma,
                      float* dbeta, int accumulate, double* sums, gsb_stream s);
 

@@ -93,7 +93,34 @@ __global__ void __launch_bounds__(256) sum_slices_kernel(const float* __restrict
   }
 }
 
+// Many slices, few columns (per-CTA partial rows of the edge kernels: 592 rows of 576 floats): one thread per column would
+// walk hundreds of dependent loads (130 us for 1.4 MB).  Here a block owns 8 columns x 32 slice lanes: lane l adds slices
+// l, l + 32, ... (fp64), the 32 lane sums are added in lane order.  Fixed mapping -> deterministic.
+__global__ void __launch_bounds__(256) sum_slices_wide_kernel(const float* __restrict__ ws, int nslices, int64_t slice_stride,
+                                                             int64_t n, float* __restrict__ dst, int accumulate) {
+  GSB_PDL_ENTRY();
+  __shared__ double red[32][9];
+  const int c = threadIdx.x & 7, l = threadIdx.x >> 3;
+  const int64_t col = (int64_t)blockIdx.x * 8 + c;
+  double a = 0.0;
+  if (col < n)
+    for (int s = l; s < nslices; s += 32) a += (double)__ldg(ws + (int64_t)s * slice_stride + col);
+  red[l][c] = a;
+  __syncthreads();
+  if (l == 0 && col < n) {
+    double t = 0.0;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) t += red[i][c];
+    if (accumulate) t += (double)dst[col];
+    dst[col] = (float)t;
+  }
+}
+
 int sum_slices(const float* ws, int nslices, int64_t slice_stride, int64_t n, float* dst, int accumulate, cudaStream_t st) {
+  if (nslices >= 16 && n <= ((int64_t)1 << 22)) {
+    launch(sum_slices_wide_kernel, LaunchCfg((unsigned)((n + 7) / 8), 256, 0, st), ws, nslices, slice_stride, n, dst, accumulate);
+    return 0;
+  }
   const int vec = (n % 4 == 0) && (slice_stride % 4 == 0) && ((uintptr_t)ws % 16 == 0) && ((uintptr_t)dst % 16 == 0);
   const int64_t items = vec ? n / 4 : n;
   int64_t blocks = (items + 255) / 256;

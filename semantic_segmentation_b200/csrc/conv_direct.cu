@@ -173,11 +173,14 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(DView in, DView dout, f
   const int64_t P = (int64_t)DN * DH * DW;
   const int64_t p_begin = (int64_t)blockIdx.z * chunk;
   const int64_t p_end = p_begin + chunk < P ? p_begin + chunk : P;
-  float acc[TM][TN];
+  // Two-level accumulation: fp32 FMAs inside a BK-pixel block, fp64 across blocks.  A weight gradient behind BatchNorm is a
+  // sum of thousands of products that nearly cancel (sum_p dY[p] = 0 per channel), so a plain fp32 running sum left the
+  // fp32 validation mode 1e-3 away from the fp64 reference where torch's blocked CPU kernel is at 1e-5.
+  double acc[TM][TN];
 #pragma unroll
   for (int a = 0; a < TM; ++a)
 #pragma unroll
-    for (int b = 0; b < TN; ++b) acc[a][b] = 0.f;
+    for (int b = 0; b < TN; ++b) acc[a][b] = 0.0;
 
   __shared__ int64_t s_in[BK], s_out[BK];
   for (int64_t pb = p_begin; pb < p_end; pb += BK) {
@@ -226,6 +229,11 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(DView in, DView dout, f
       Bs[k][c] = v;
     }
     __syncthreads();
+    float part[TM][TN];
+#pragma unroll
+    for (int i = 0; i < TM; ++i)
+#pragma unroll
+      for (int j = 0; j < TN; ++j) part[i][j] = 0.f;
 #pragma unroll
     for (int k = 0; k < BK; ++k) {
       float a[TM], b[TN];
@@ -236,8 +244,12 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(DView in, DView dout, f
 #pragma unroll
       for (int i = 0; i < TM; ++i)
 #pragma unroll
-        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        for (int j = 0; j < TN; ++j) part[i][j] = fmaf(a[i], b[j], part[i][j]);
     }
+#pragma unroll
+    for (int i = 0; i < TM; ++i)
+#pragma unroll
+      for (int j = 0; j < TN; ++j) acc[i][j] += (double)part[i][j];
     __syncthreads();
   }
 #pragma unroll
@@ -248,7 +260,7 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(DView in, DView dout, f
     for (int j = 0; j < TN; ++j) {
       int ci = ci0 + tx * TN + j;
       if (ci >= Cin) continue;
-      dwp[(int64_t)blockIdx.z * slice_elems + ((int64_t)tap * Cout + co) * Cin + ci] = acc[i][j];
+      dwp[(int64_t)blockIdx.z * slice_elems + ((int64_t)tap * Cout + co) * Cin + ci] = (float)acc[i][j];
     }
   }
 }

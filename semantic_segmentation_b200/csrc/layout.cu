@@ -374,9 +374,9 @@ __device__ __forceinline__ void layout_tile(const float* __restrict__ tsrc, floa
         const int64_t off = ((int64_t)tap * rows + r) * cols + c;
         float* cell = sm + i0l * kTPitch0 + i1l * kTPitch1 + t;
         if (load) {
-          float acc = psrc[off];
-          for (int sl = 1; sl < nslices; ++sl) acc += psrc[(int64_t)sl * slice_stride + off];
-          *cell = acc;
+          double acc = (double)psrc[off];   // slice order, fp64: partial sums of a weight gradient nearly cancel
+          for (int sl = 1; sl < nslices; ++sl) acc += (double)psrc[(int64_t)sl * slice_stride + off];
+          *cell = (float)acc;
         } else st_elem(pdst, off, pdtype, *cell);
       }
     }
@@ -466,11 +466,17 @@ __device__ __forceinline__ void layout_tile(const float* __restrict__ tsrc, floa
       const int step = rfd ? kTPitch1 : kTPitch0;          // next column = next i1 (rfd) or next i0
       if (load) {
         float4 a = *reinterpret_cast<const float4*>(psrc + off), b = *reinterpret_cast<const float4*>(psrc + off + 4);
-        for (int sl = 1; sl < nslices; ++sl) {
-          const float* q = psrc + (int64_t)sl * slice_stride + off;
-          const float4 a2 = *reinterpret_cast<const float4*>(q), b2 = *reinterpret_cast<const float4*>(q + 4);
-          a.x += a2.x; a.y += a2.y; a.z += a2.z; a.w += a2.w;
-          b.x += b2.x; b.y += b2.y; b.z += b2.z; b.w += b2.w;
+        if (nslices > 1) {   // slice order, fp64 accumulation
+          double d[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll 2
+          for (int sl = 1; sl < nslices; ++sl) {
+            const float* q = psrc + (int64_t)sl * slice_stride + off;
+            const float4 a2 = __ldg(reinterpret_cast<const float4*>(q)), b2 = __ldg(reinterpret_cast<const float4*>(q + 4));
+            d[0] += a2.x; d[1] += a2.y; d[2] += a2.z; d[3] += a2.w;
+            d[4] += b2.x; d[5] += b2.y; d[6] += b2.z; d[7] += b2.w;
+          }
+          a = make_float4((float)d[0], (float)d[1], (float)d[2], (float)d[3]);
+          b = make_float4((float)d[4], (float)d[5], (float)d[6], (float)d[7]);
         }
         cell[0] = a.x; cell[step] = a.y; cell[2 * step] = a.z; cell[3 * step] = a.w;
         cell[4 * step] = b.x; cell[5 * step] = b.y; cell[6 * step] = b.z; cell[7 * step] = b.w;
@@ -526,10 +532,69 @@ __global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const __grid_co
   layout_tile_dispatch<false>(J, j, blockIdx.x - J.blk0[j], sm);
 }
 
+// Jobs of an un-pack launch whose source holds many partial-sum slices (small layers split 24..74 ways over the pixels):
+// the tile loader below would walk them one after the other per element (8 CTAs x 74 dependent 16-byte loads: 120 us).
+// One launch first folds the slices of all such jobs into their slice 0, in place: a block owns `cols` columns x L slice
+// lanes (L = power of two >= nslices, <= 32); lane l adds slices l, l + L, ... in fp64, the lane sums are added in lane order.
+struct SliceJobs {
+  float* ws[kMaxLayoutJobs];
+  int64_t n[kMaxLayoutJobs];
+  int nslices[kMaxLayoutJobs], lanes[kMaxLayoutJobs];
+  int blk0[kMaxLayoutJobs + 1];
+  int count;
+};
+__global__ void __launch_bounds__(256) fold_slices_multi_kernel(const __grid_constant__ SliceJobs J) {
+  GSB_PDL_ENTRY();
+  __shared__ double red[256];
+  const int j = find_job(J.blk0, J.count, blockIdx.x);
+  const int L = J.lanes[j], cols = 256 / L;
+  const int c = threadIdx.x % cols, l = threadIdx.x / cols;
+  const int64_t n = J.n[j], col = (int64_t)(blockIdx.x - J.blk0[j]) * cols + c;
+  float* ws = J.ws[j];
+  double a = 0.0;
+  if (col < n)
+    for (int s = l; s < J.nslices[j]; s += L) a += (double)ws[(int64_t)s * n + col];
+  red[l * cols + c] = a;
+  __syncthreads();
+  if (l == 0 && col < n) {
+    double t = 0.0;
+    for (int i = 0; i < L; ++i) t += red[i * cols + c];
+    ws[col] = (float)t;
+  }
+}
+
 static int run_layout_multi(bool pack, int n, const void* const* src, void* const* dst, const int* d0, const int* d1,
                             const int* taps, const int* rows_from_d0, const int* nslices, int dst_dtype, int accumulate,
                             cudaStream_t st) {
   int launches = 0;
+  bool folded[kMaxLayoutJobs * 4];
+  for (int i = 0; i < n && i < kMaxLayoutJobs * 4; ++i) folded[i] = false;
+  if (!pack && nslices != nullptr) {
+    for (int begin = 0; begin < n; begin += kMaxLayoutJobs) {
+      SliceJobs S;
+      memset(&S, 0, sizeof(S));
+      int blocks = 0;
+      const int end = n - begin < kMaxLayoutJobs ? n : begin + kMaxLayoutJobs;
+      for (int i = begin; i < end; ++i) {
+        if (nslices[i] <= 4 || i >= kMaxLayoutJobs * 4) continue;
+        int L = 1;
+        while (L < nslices[i] && L < 32) L <<= 1;
+        const int k = S.count++;
+        S.ws[k] = reinterpret_cast<float*>(const_cast<void*>(src[i]));
+        S.n[k] = (int64_t)taps[i] * d0[i] * d1[i];
+        S.nslices[k] = nslices[i];
+        S.lanes[k] = L;
+        S.blk0[k] = blocks;
+        blocks += (int)((S.n[k] + (256 / L) - 1) / (256 / L));
+        folded[i] = true;
+      }
+      S.blk0[S.count] = blocks;
+      if (S.count > 0 && blocks > 0) {
+        gsb::launch(fold_slices_multi_kernel, gsb::LaunchCfg(blocks, 256, 0, st), S);
+        ++launches;
+      }
+    }
+  }
   for (int begin = 0; begin < n; begin += kMaxLayoutJobs) {
     LayoutJobs J;
     memset(&J, 0, sizeof(J));
@@ -543,7 +608,7 @@ static int run_layout_multi(bool pack, int n, const void* const* src, void* cons
       J.src[k] = src[i]; J.dst[k] = dst[i];
       J.d0[k] = d0[i]; J.d1[k] = d1[i]; J.taps[k] = taps[i];
       J.rows_from_d0[k] = (uint8_t)(rows_from_d0[i] != 0);
-      J.nslices[k] = (nslices != nullptr && nslices[i] > 1) ? nslices[i] : 1;
+      J.nslices[k] = (nslices != nullptr && nslices[i] > 1 && !(i < kMaxLayoutJobs * 4 && folded[i])) ? nslices[i] : 1;
       J.blk0[k] = blocks;
       blocks += layout_tiles_host(d0[i], d1[i], taps[i]);
     }

@@ -92,16 +92,20 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
   const int lanes = kThreads / G;
   const int g = threadIdx.x % G, lane = threadIdx.x / G;
   const int c0 = g * 8;
+  // per-image statistics (InstanceNorm, gridDim.y = images): P = pixels of ONE image, this block row works on image
+  // blockIdx.y, the per-channel parameter arrays are [images][C] and a partial row is [2][images * C]
+  const int img = blockIdx.y, NC = gridDim.y * C, poff = img * C;
+  const int64_t pbase = (int64_t)img * P;
   Acc s0[8], s1[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) s0[i] = s1[i] = (Acc)0;
   float sc[8], sh[8], mu[8], is[8], ce[8];
   if (MODE == 1) {
-    load_param8(scale, c0, sc, 1.f);
-    load_param8(shift, c0, sh, 0.f);
-    load_param8(FAST ? nullptr : center, c0, ce, 0.f);
-    load_param8(mean, c0, mu, 0.f);
-    load_param8(invstd, c0, is, 1.f);
+    load_param8(scale ? scale + poff : nullptr, c0, sc, 1.f);
+    load_param8(shift ? shift + poff : nullptr, c0, sh, 0.f);
+    load_param8((FAST || !center) ? nullptr : center + poff, c0, ce, 0.f);
+    load_param8(mean ? mean + poff : nullptr, c0, mu, 0.f);
+    load_param8(invstd ? invstd + poff : nullptr, c0, is, 1.f);
   }
   const bool has_drop = FAST ? false : ((drop_seed != 0) || (drop_mask != nullptr));
   const bool two = FAST ? false : (dA2.ptr != nullptr);
@@ -112,10 +116,10 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
 #pragma unroll
     for (int u = 0; u < KU; ++u)
       if (p0 + u * step < P) {
-        load8<T>(x, p0 + u * step, c0, v[u]);
+        load8<T>(x, pbase + p0 + u * step, c0, v[u]);
         if (MODE == 1) {
-          load8<T>(dA1, p0 + u * step, c0, a[u]);
-          if (two) load8<T>(dA2, p0 + u * step, c0, b[u]);
+          load8<T>(dA1, pbase + p0 + u * step, c0, a[u]);
+          if (two) load8<T>(dA2, pbase + p0 + u * step, c0, b[u]);
         }
       }
 #pragma unroll
@@ -129,7 +133,7 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
           s1[i] += (Acc)v[u][i] * (Acc)v[u][i];
         }
       } else {
-        uint32_t keep = has_drop ? keep_bits(drop_seed, drop_offset, drop_mask, p, C, c0) : 0xFFu;
+        uint32_t keep = has_drop ? keep_bits(drop_seed, drop_offset, drop_mask, pbase + p, C, c0) : 0xFFu;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           float z = FAST ? fmaf(v[u][i], sc[i], sh[i]) : fmaf(v[u][i] - ce[i], sc[i], sh[i]);
@@ -152,12 +156,13 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
   for (int j = threadIdx.x; j < 2 * C; j += kThreads) {
     Acc acc = (Acc)0;
     for (int l = 0; l < lanes; ++l) acc += red[l * 2 * C + j];
+    const int col = j < C ? poff + j : NC + poff + (j - C);
     if (WIDE) {
       const float hi = (float)acc;
-      partial[((int64_t)blockIdx.x * 2) * 2 * C + j] = hi;
-      partial[((int64_t)blockIdx.x * 2 + 1) * 2 * C + j] = (float)((double)acc - (double)hi);
+      partial[((int64_t)blockIdx.x * 2) * 2 * NC + col] = hi;
+      partial[((int64_t)blockIdx.x * 2 + 1) * 2 * NC + col] = (float)((double)acc - (double)hi);
     } else {
-      partial[(int64_t)blockIdx.x * 2 * C + j] = (float)acc;
+      partial[(int64_t)blockIdx.x * 2 * NC + col] = (float)acc;
     }
   }
 }
@@ -309,10 +314,12 @@ __global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, 
   const int lanes = kThreads / G;
   const int g = threadIdx.x % G, lane = threadIdx.x / G;
   const int c0 = g * 8;
+  const int poff = blockIdx.y * C;                   // per-image parameters (InstanceNorm): gridDim.y = images, P per image
+  const int64_t pbase = (int64_t)blockIdx.y * P;
   float sc[8], sh[8], ce[8];
-  load_param8(scale, c0, sc, 1.f);
-  load_param8(shift, c0, sh, 0.f);
-  load_param8(FAST ? nullptr : center, c0, ce, 0.f);   // z = (x - center) * scale + shift
+  load_param8(scale ? scale + poff : nullptr, c0, sc, 1.f);
+  load_param8(shift ? shift + poff : nullptr, c0, sh, 0.f);
+  load_param8((FAST || !center) ? nullptr : center + poff, c0, ce, 0.f);   // z = (x - center) * scale + shift
   const bool has_drop = FAST ? false : ((drop_seed != 0) || (drop_mask != nullptr));
   const bool has_out2 = FAST ? false : (out2.ptr != nullptr);
   if (FAST) { act1 = GSB_ACT_RELU; act2 = GSB_ACT_NONE; }
@@ -321,13 +328,13 @@ __global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, 
     float v[kUnroll][8];
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u)
-      if (p0 + u * step < P) load8<T>(x, p0 + u * step, c0, v[u]);
+      if (p0 + u * step < P) load8<T>(x, pbase + p0 + u * step, c0, v[u]);
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u) {
       const int64_t p = p0 + u * step;
       if (p >= P) break;
       float o1[8], o2[8];
-      uint32_t keep = has_drop ? keep_bits(drop_seed, drop_offset, drop_mask, p, C, c0) : 0xFFu;
+      uint32_t keep = has_drop ? keep_bits(drop_seed, drop_offset, drop_mask, pbase + p, C, c0) : 0xFFu;
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         float z = FAST ? fmaf(v[u][i], sc[i], sh[i]) : fmaf(v[u][i] - ce[i], sc[i], sh[i]);
@@ -335,8 +342,8 @@ __global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, 
         o1[i] = act_fwd(z * dm, act1);
         if (has_out2) o2[i] = act_fwd(z, act2);
       }
-      store8<T>(out1, p, c0, o1);
-      if (has_out2) store8<T>(out2, p, c0, o2);
+      store8<T>(out1, pbase + p, c0, o1);
+      if (has_out2) store8<T>(out2, pbase + p, c0, o2);
     }
   }
 }
@@ -353,17 +360,19 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
   const int lanes = kThreads / G;
   const int g = threadIdx.x % G, lane = threadIdx.x / G;
   const int c0 = g * 8;
+  const int NC = gridDim.y * C, poff = blockIdx.y * C;   // per-image parameters / sums (InstanceNorm), P per image
+  const int64_t pbase = (int64_t)blockIdx.y * P;
   float sc[8], sh[8], mu[8], is[8], m0[8], m1[8], ce[8];
-  load_param8(scale, c0, sc, 1.f);
-  load_param8(shift, c0, sh, 0.f);
-  load_param8(FAST ? nullptr : center, c0, ce, 0.f);
+  load_param8(scale ? scale + poff : nullptr, c0, sc, 1.f);
+  load_param8(shift ? shift + poff : nullptr, c0, sh, 0.f);
+  load_param8((FAST || !center) ? nullptr : center + poff, c0, ce, 0.f);
   const bool has_bn = FAST ? true : (mean != nullptr);
-  load_param8(mean, c0, mu, 0.f);
-  load_param8(invstd, c0, is, 1.f);
+  load_param8(mean ? mean + poff : nullptr, c0, mu, 0.f);
+  load_param8(invstd ? invstd + poff : nullptr, c0, is, 1.f);
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    m0[i] = has_bn ? (float)(sums[c0 + i] * inv_count) : 0.f;
-    m1[i] = has_bn ? (float)(sums[C + c0 + i] * inv_count) : 0.f;
+    m0[i] = has_bn ? (float)(sums[poff + c0 + i] * inv_count) : 0.f;
+    m1[i] = has_bn ? (float)(sums[NC + poff + c0 + i] * inv_count) : 0.f;
   }
   const bool has_drop = FAST ? false : ((drop_seed != 0) || (drop_mask != nullptr));
   const bool two = FAST ? false : (dA2.ptr != nullptr);
@@ -407,16 +416,16 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
 #pragma unroll
     for (int u = 0; u < kUnrollBwd; ++u)
       if (p0 + u * step < P) {
-        load8<T>(x, p0 + u * step, c0, v[u]);
-        load8<T>(dA1, p0 + u * step, c0, a[u]);
-        if (two) load8<T>(dA2, p0 + u * step, c0, b[u]);
+        load8<T>(x, pbase + p0 + u * step, c0, v[u]);
+        load8<T>(dA1, pbase + p0 + u * step, c0, a[u]);
+        if (two) load8<T>(dA2, pbase + p0 + u * step, c0, b[u]);
       }
 #pragma unroll
     for (int u = 0; u < kUnrollBwd; ++u) {
       const int64_t p = p0 + u * step;
       if (p >= P) break;
       float o[8];
-      uint32_t keep = has_drop ? keep_bits(drop_seed, drop_offset, drop_mask, p, C, c0) : 0xFFu;
+      uint32_t keep = has_drop ? keep_bits(drop_seed, drop_offset, drop_mask, pbase + p, C, c0) : 0xFFu;
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         float z = fmaf(v[u][i] - ce[i], sc[i], sh[i]);
@@ -430,7 +439,7 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
           o[i] = dy * sc[i];
         }
       }
-      store8<T>(dx, p, c0, o);
+      store8<T>(dx, pbase + p, c0, o);
     }
   }
 }
@@ -580,25 +589,35 @@ extern "C" size_t gsb_bn_workspace_bytes(const gsb_view* x) {
   return (size_t)num_sms() * 8 * 2 * 2 * (size_t)x->c * sizeof(float);   // fp32 views write two rows (hi, lo) per block
 }
 
-extern "C" int gsb_bn_reduce(const gsb_view* x, double* sums, void* workspace, size_t workspace_bytes, gsb_stream s) {
+// per_image != 0: statistics per (image, channel) -- InstanceNorm -- in the same launches: sums[2][n * c], blocks (x, image)
+static int per_image_grid(int64_t P_img, int lanes, int n) {
+  int g = grid_for(P_img, lanes);
+  const int cap = (num_sms() * 8) / (n > 0 ? n : 1);     // so that rows x 2 x n x c still fits gsb_bn_workspace_bytes
+  if (g > cap) g = cap;
+  return g < 1 ? 1 : g;
+}
+
+extern "C" int gsb_bn_reduce(const gsb_view* x, int per_image, double* sums, void* workspace, size_t workspace_bytes,
+                             gsb_stream s) {
   if (check_vec_view(x, "bn_reduce.x")) return -1;
   const int C = x->c, lanes = kThreads / (C / 8);
-  const int64_t P = num_pixels(x);
-  int grid = grid_for(P, lanes);
+  const int nimg = per_image ? x->n : 1;
+  const int64_t P = num_pixels(x) / nimg;
+  int grid = per_image ? per_image_grid(P, lanes, nimg) : grid_for(P, lanes);
   const int wide = x->dtype == GSB_BF16 ? 1 : 2;
-  GSB_REQUIRE(workspace_bytes >= (size_t)grid * wide * 2 * C * sizeof(float), "bn_reduce: workspace too small");
+  GSB_REQUIRE(workspace_bytes >= (size_t)grid * wide * 2 * C * nimg * sizeof(float), "bn_reduce: workspace too small");
   size_t smem = (size_t)lanes * 2 * C * sizeof(float) * wide;
   float* partial = reinterpret_cast<float*>(workspace);
   PixView nul{nullptr, 0};
   if (smem > 48 * 1024)
     cudaFuncSetAttribute(bn_reduce_kernel<float, 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (x->dtype == GSB_BF16)
-    gsb::launch(bn_reduce_kernel<__nv_bfloat16, 0, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), nul, nul, P, C, nullptr, nullptr, nullptr,
+    gsb::launch(bn_reduce_kernel<__nv_bfloat16, 0, false>, gsb::LaunchCfg(dim3(grid, nimg), kThreads, smem, to_stream(s)), pv(x), nul, nul, P, C, nullptr, nullptr, nullptr,
                                                                                      nullptr, nullptr, 0, 0, 0, 0, nullptr, partial);
   else
-    gsb::launch(bn_reduce_kernel<float, 0, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), nul, nul, P, C, nullptr, nullptr, nullptr, nullptr,
+    gsb::launch(bn_reduce_kernel<float, 0, false>, gsb::LaunchCfg(dim3(grid, nimg), kThreads, smem, to_stream(s)), pv(x), nul, nul, P, C, nullptr, nullptr, nullptr, nullptr,
                                                                              nullptr, 0, 0, 0, 0, nullptr, partial);
-  int n = 2 * C;
+  int n = 2 * C * nimg;
   gsb::launch(reduce_partials_kernel, gsb::LaunchCfg((n + 31) / 32, 1024, 0, to_stream(s)), partial, grid * wide, n, sums);
   return check_launch("bn_reduce", 2);
 }
@@ -624,18 +643,20 @@ extern "C" int gsb_bn_finalize(const double* sums, double count, const float* ga
 
 extern "C" int gsb_bn_act(const gsb_view* x, const float* scale, const float* shift, const float* center, int act1,
                           const gsb_view* out1,
-                          int act2, const gsb_view* out2, uint64_t drop_seed, int64_t drop_offset, const uint8_t* drop_mask, gsb_stream s) {
+                          int act2, const gsb_view* out2, uint64_t drop_seed, int64_t drop_offset, const uint8_t* drop_mask,
+                          int per_image, gsb_stream s) {
   if (check_vec_view(x, "bn_act.x") || check_vec_view(out1, "bn_act.out1")) return -1;
   if (out2 && out2->ptr && check_vec_view(out2, "bn_act.out2")) return -1;
   GSB_REQUIRE(out1->dtype == x->dtype && out1->c == x->c && num_pixels(out1) == num_pixels(x), "bn_act: out1 mismatch");
   if (out2 && out2->ptr)
     GSB_REQUIRE(out2->dtype == x->dtype && out2->c == x->c && num_pixels(out2) == num_pixels(x), "bn_act: out2 mismatch");
   const int C = x->c, lanes = kThreads / (C / 8);
-  const int64_t P = num_pixels(x);
-  int grid = grid_for(P, lanes * 4);
+  const int nimg = per_image ? x->n : 1;     // per_image: scale / shift / center are [n][c] (InstanceNorm)
+  const int64_t P = num_pixels(x) / nimg;
+  dim3 grid(grid_for(P, lanes * 4), nimg);
   PixView o2 = (out2 && out2->ptr) ? pv(out2) : PixView{nullptr, 0};
   const bool fast = act1 == GSB_ACT_RELU && o2.ptr == nullptr && drop_seed == 0 && drop_mask == nullptr && scale && shift &&
-                    center == nullptr;
+                    center == nullptr && !per_image;
   if (x->dtype == GSB_BF16) {
     if (fast)
       gsb::launch(bn_act_kernel<__nv_bfloat16, true>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), P, C, scale, shift, center, act1, pv(out1), act2, o2,
@@ -664,20 +685,22 @@ static int check_bwd_views(const gsb_view* x, const gsb_view* dA1, const gsb_vie
 static int bn_bwd_partial_launch(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
                                  const float* shift, const float* center, const float* mean, const float* invstd, int act1, int act2,
                                  uint64_t drop_seed, int64_t drop_offset, const uint8_t* drop_mask, void* workspace, size_t workspace_bytes,
-                                 int* rows_out, gsb_stream s) {
+                                 int* rows_out, int per_image, gsb_stream s) {
   if (check_bwd_views(x, dA1, dA2)) return -1;
   const int C = x->c, lanes = kThreads / (C / 8);
-  const int64_t P = num_pixels(x);
-  int grid = grid_for(P, lanes);
+  const int nimg = per_image ? x->n : 1;
+  const int64_t P = num_pixels(x) / nimg;
+  const int gx = per_image ? per_image_grid(P, lanes, nimg) : grid_for(P, lanes);
+  dim3 grid(gx, nimg);
   const int wide = x->dtype == GSB_BF16 ? 1 : 2;
-  GSB_REQUIRE(workspace_bytes >= (size_t)grid * wide * 2 * C * sizeof(float), "bn_bwd_reduce: workspace too small");
+  GSB_REQUIRE(workspace_bytes >= (size_t)gx * wide * 2 * C * nimg * sizeof(float), "bn_bwd_reduce: workspace too small");
   size_t smem = (size_t)lanes * 2 * C * sizeof(float) * wide;
   if (smem > 48 * 1024)
     cudaFuncSetAttribute(bn_reduce_kernel<float, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   float* partial = reinterpret_cast<float*>(workspace);
   PixView d2 = (dA2 && dA2->ptr) ? pv(dA2) : PixView{nullptr, 0};
   const bool fast = act1 == GSB_ACT_RELU && d2.ptr == nullptr && drop_seed == 0 && drop_mask == nullptr && scale && shift &&
-                    mean && invstd && center == nullptr;
+                    mean && invstd && center == nullptr && !per_image;
   if (x->dtype == GSB_BF16) {
     if (fast && relu_stats_fast_enabled())
       gsb::launch(bn_bwd_reduce_relu_bf16_kernel<2>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), 
@@ -692,7 +715,7 @@ static int bn_bwd_partial_launch(const gsb_view* x, const gsb_view* dA1, const g
     gsb::launch(bn_reduce_kernel<float, 1, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), pv(dA1), d2, P, C, scale, shift, center, mean,
                                                                              invstd, act1, act2, drop_seed, drop_offset, drop_mask, partial);
   }
-  *rows_out = grid * wide;
+  *rows_out = gx * wide;
   return 0;
 }
 
@@ -702,7 +725,7 @@ extern "C" int gsb_bn_bwd_reduce(const gsb_view* x, const gsb_view* dA1, const g
                                  size_t workspace_bytes, gsb_stream s) {
   int grid = 0;
   if (bn_bwd_partial_launch(x, dA1, dA2, scale, shift, center, mean, invstd, act1, act2, drop_seed, drop_offset, drop_mask, workspace,
-                            workspace_bytes, &grid, s))
+                            workspace_bytes, &grid, 0, s))
     return -1;
   int n = 2 * x->c;
   gsb::launch(reduce_partials_kernel, gsb::LaunchCfg((n + 31) / 32, 1024, 0, to_stream(s)), reinterpret_cast<float*>(workspace), grid, n, sums);
@@ -712,10 +735,10 @@ extern "C" int gsb_bn_bwd_reduce(const gsb_view* x, const gsb_view* dA1, const g
 extern "C" int gsb_bn_bwd_partial(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
                                   const float* shift, const float* center, const float* mean, const float* invstd, int act1, int act2,
                                   uint64_t drop_seed, int64_t drop_offset, const uint8_t* drop_mask, void* workspace, size_t workspace_bytes,
-                                  int* rows, gsb_stream s) {
+                                  int* rows, int per_image, gsb_stream s) {
   GSB_REQUIRE(rows != nullptr, "bn_bwd_partial: rows is null");
   if (bn_bwd_partial_launch(x, dA1, dA2, scale, shift, center, mean, invstd, act1, act2, drop_seed, drop_offset, drop_mask, workspace,
-                            workspace_bytes, rows, s))
+                            workspace_bytes, rows, per_image, s))
     return -1;
   return check_launch("bn_bwd_partial");
 }
@@ -767,17 +790,19 @@ extern "C" int gsb_bn_bwd_stats(const float* partial, int rows, int c, void* con
 extern "C" int gsb_bn_bwd_apply(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2, const float* scale,
                                 const float* shift, const float* center, const float* mean, const float* invstd, int act1, int act2,
                                 uint64_t drop_seed, int64_t drop_offset, const uint8_t* drop_mask, const double* sums, double count,
-                                const gsb_view* dx, float* dgamma, float* dbeta, gsb_stream s) {
+                                const gsb_view* dx, float* dgamma, float* dbeta, int per_image, gsb_stream s) {
   if (check_bwd_views(x, dA1, dA2) || check_vec_view(dx, "bn_bwd.dx")) return -1;
   GSB_REQUIRE(dx->dtype == x->dtype && dx->c == x->c && num_pixels(dx) == num_pixels(x), "bn_bwd_apply: dx mismatch");
   GSB_REQUIRE(mean == nullptr || sums != nullptr, "bn_bwd_apply: sums required with BN");
   const int C = x->c, lanes = kThreads / (C / 8);
-  const int64_t P = num_pixels(x);
-  int grid = grid_for(P, lanes * 4);
+  const int nimg = per_image ? x->n : 1;     // per_image: parameters [n][c], sums [2][n * c], count = pixels per image
+  const int64_t P = num_pixels(x) / nimg;
+  dim3 grid(grid_for(P, lanes * 4), nimg);
   PixView d2 = (dA2 && dA2->ptr) ? pv(dA2) : PixView{nullptr, 0};
   double inv = count > 0 ? 1.0 / count : 0.0;
   const bool fast = act1 == GSB_ACT_RELU && d2.ptr == nullptr && drop_seed == 0 && drop_mask == nullptr && scale && shift &&
-                    mean && invstd && center == nullptr;
+                    mean && invstd && center == nullptr && !per_image;
+  GSB_REQUIRE(!per_image || (dgamma == nullptr && dbeta == nullptr), "bn_bwd_apply: per-image statistics have no affine parameters");
   if (x->dtype == GSB_BF16) {
     if (fast)
       gsb::launch(bn_bwd_apply_kernel<__nv_bfloat16, true>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), 

@@ -254,6 +254,47 @@ class BackwardBatch:
         return True
 
 
+class AsyncGradReducer:
+    """Gradient all-reduce inside a program's backward pass (data parallelism): ``start(t)`` launches the asynchronous
+    in-place sum of a finished contiguous gradient on the collective's stream (``parallel._allreduce_async``: NCCL, bf16
+    on the wire when configured) while the backward pass goes on; ``finish(small)`` sends the small gradients as one flat
+    bucket and waits for everything.  Inactive (``active`` False) without ``overlap_grad_allreduce``."""
+
+    def __init__(self):
+        self.gfn = _REDUCER.get("grad_fn") if int(_REDUCER.get("world", 1)) > 1 else None
+        self.pending = []
+        self.reserved = False
+
+    @property
+    def active(self) -> bool:
+        return self.gfn is not None
+
+    def start(self, t: torch.Tensor) -> None:
+        self.pending.append(self.gfn(t.view(-1)))
+        reserve = int(_REDUCER.get("sm_reserve", 0))
+        if reserve > 0 and not self.reserved:     # persistent tensor-core kernels leave room for the collective's CTAs
+            ops.set_sm_reserve(reserve)
+            self.reserved = True
+
+    def wait_all(self) -> None:
+        for w in self.pending:
+            w.wait()
+        self.pending = []
+
+    def finish(self, small: List[torch.Tensor]) -> None:
+        small = [g for g in small if g is not None]
+        flat = None
+        if small:
+            flat = torch.cat([g.reshape(-1) for g in small])
+            self.pending.append(self.gfn(flat))
+        self.wait_all()
+        if self.reserved:
+            ops.set_sm_reserve(0)
+            self.reserved = False
+        if flat is not None:
+            torch._foreach_copy_(small, [c.view_as(g) for c, g in zip(flat.split([g.numel() for g in small]), small)])
+
+
 def conv_weight_grad(spec: "ConvSpec", x_view: GsbView, dy_view: GsbView, device, use_tc: int,
                      batch: Optional["BackwardBatch"] = None, key: Optional[str] = None) -> torch.Tensor:
     """Weight gradient of one convolution in torch layout.  The kernel writes partial-sum slices (one per split of the pixel
@@ -285,7 +326,7 @@ class ConvBNAct:
                  instance_norm: bool = False):
         """instance_norm: the normalisation is nn.InstanceNorm2d(affine=False, track_running_stats=False)
         (networks.py:34-35, --norm instance): statistics per image and channel in training AND evaluation, no
-        parameters, no buffers.  Runs the BatchNorm kernels once per image (flag-reachable path)."""
+        parameters, no buffers.  Same kernels as BatchNorm with a grid dimension over the images."""
         self.spec, self.has_bn, self.act1, self.act2, self.dropout = spec, has_bn, act1, act2, dropout
         self.instance = bool(instance_norm) and has_bn
 
@@ -313,26 +354,27 @@ class ConvBNAct:
         first = first_global_sample(n)
         drop_offset = first * oh * ow * s.cout
         if self.has_bn and self.instance:
+            # InstanceNorm2d(affine=False): statistics per (image, channel) -- the BatchNorm kernels with a second grid
+            # dimension over the images, so a layer costs the same launches at any batch size
             if out1 is None:
                 out1 = _nhwc_empty(n, oh, ow, s.cout, device)
             use_drop = self.dropout and training
-            per = []
-            count = float(oh * ow)        # statistics per image
-            for i in range(n):
-                yi = y[i:i + 1]
-                sums_i = ops.bn_reduce(yi)
-                st_i = ops.bn_finalize(sums_i, count, None, None, None, None, None, BN_MOMENTUM, BN_EPS, s.cout, device,
-                                       centered=centered)
-                seed_i = (drop_seed + 104729 * (first + i + 1)) if (use_drop and drop_seed) else 0
-                mask_i = drop_mask[i:i + 1] if (use_drop and drop_mask is not None) else None
-                ops.bn_act(yi, st_i[0], st_i[1], self.act1, out1[i:i + 1], self.act2 if self.act2 is not None else ACT_NONE,
-                           out2[i:i + 1] if self.act2 is not None else None, seed_i, mask_i,
-                           center=st_i[2] if centered else None)
-                per.append((st_i, seed_i, mask_i))
+            count = float(oh * ow)
+            sums = ops.bn_reduce(y, per_image=True)
+            scale, shift, mean, invstd = ops.bn_finalize(sums, count, None, None, None, None, None, BN_MOMENTUM, BN_EPS,
+                                                         n * s.cout, device, centered=centered)
+            center = mean if centered else None
+            ops.bn_act(y, scale, shift, self.act1, out1, self.act2 if self.act2 is not None else ACT_NONE,
+                       out2 if self.act2 is not None else None, drop_seed if use_drop else 0, drop_mask if use_drop else None,
+                       center=center, drop_offset=drop_offset if use_drop else 0, per_image=True)
             if save:
                 sv.x_view, sv.x_keep, sv.y = x_view, x_keep, y
-                sv.count, sv.weight = count, weight
-                sv.extra["instance"] = per
+                sv.scale, sv.shift, sv.mean, sv.invstd, sv.count = scale, shift, mean, invstd, count
+                sv.weight, sv.center = weight, center
+                sv.drop_seed = drop_seed if use_drop else 0
+                sv.drop_offset = drop_offset if use_drop else 0
+                sv.drop_mask = drop_mask if use_drop else None
+                sv.extra["instance"] = True
                 sv.extra["train_bn"] = False
                 sv.extra["stem"] = stem
                 sv.extra["wpb"] = packed[1] if packed is not None else None
@@ -389,14 +431,10 @@ class ConvBNAct:
         fused_ok, peer, _pw = _fused_stats_mode()
         inst = sv.extra.get("instance")
         if inst is not None:
-            for i, (st_i, seed_i, mask_i) in enumerate(inst):
-                sc, sh, mu, istd = st_i
-                a1, a2 = dA1[i:i + 1], (dA2[i:i + 1] if dA2 is not None else None)
-                ce_i = mu if centered_bn() else None
-                sums_i, _, _ = ops.bn_bwd_stats(y[i:i + 1], a1, a2, sc, sh, mu, istd, self.act1, act2, seed_i, mask_i, False, None,
-                                                center=ce_i)
-                ops.bn_bwd_apply(y[i:i + 1], a1, a2, sc, sh, mu, istd, self.act1, act2, sums_i, sv.count, dY[i:i + 1], None, None,
-                                 seed_i, mask_i, center=ce_i)
+            sums, _, _ = ops.bn_bwd_stats(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2, sv.drop_seed,
+                                          sv.drop_mask, False, None, center=sv.center, drop_offset=sv.drop_offset, per_image=True)
+            ops.bn_bwd_apply(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2, sums, sv.count, dY, None, None,
+                             sv.drop_seed, sv.drop_mask, center=sv.center, drop_offset=sv.drop_offset, per_image=True)
         elif train_bn and fused_ok:
             sums, dgamma, dbeta = ops.bn_bwd_stats(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2,
                                                    sv.drop_seed, sv.drop_mask, need_bn, peer, center=sv.center,

@@ -17,7 +17,7 @@ import torch
 
 from . import ops
 from ._lib import ACT_LRELU, ACT_NONE, ACT_RELU, ACT_TANH, view_nchw, view_nhwc
-from .engine import ConvBNAct, ConvSpec, EdgeConv, Saved, WeightPacks, _nhwc_empty, act_dtype
+from .engine import AsyncGradReducer, ConvBNAct, ConvSpec, EdgeConv, Saved, WeightPacks, _nhwc_empty, act_dtype
 from .unet_program import _put
 
 ARCH_KEY = "__upconv_arch__"
@@ -178,6 +178,22 @@ class GeneratorProgram:
         dev = dout.device
         c, sizes, n, D = self.c, tape["sizes"], tape["n"], self.D
         dalpha = torch.zeros_like(arch)
+        # Data parallelism (parallel.init_data_parallel(overlap_grad_allreduce=True)): the MERGED 8x8 up-cell gradients are
+        # all-reduced -- 64 instead of 4*4 + 6*6 + 8*8 = 116 values per (ci, co) pair, asynchronously, under the rest of the
+        # backward pass -- and un-merged afterwards: the un-merge (crops, softmax weights, the dot products of d alpha) is
+        # linear in dWm, so dW4 / dW6 / dW8 / d alpha come out summed over the ranks.  The down-convolution gradients
+        # follow as they are produced; BatchNorm / bias gradients go in one small bucket at the end.
+        red = AsyncGradReducer()
+        deferred = []
+
+        def unmerge_or_defer(dwm, dbm, wn, bn_, row):
+            if not red.active:
+                unmerge(dwm, dbm, wn, bn_, row)
+                return
+            red.start(dwm)
+            if dbm is not None:
+                red.start(dbm)
+            deferred.append((dwm, dbm, wn, bn_, row))
 
         def unmerge(dwm, dbm, wn, bn_, row):
             ws = [P[k] for k in wn]
@@ -195,7 +211,7 @@ class GeneratorProgram:
         need_wo = need_arch or any(need.get(k, False) for k in wo + bo)
         dcat, dwm, dbm = self.outer.backward(tape["outer"], dout, True, need_wo, need_wo)
         if need_wo:
-            unmerge(dwm, dbm, wo, bo, D - 1)
+            unmerge_or_defer(dwm, dbm, wo, bo, D - 1)
         dskips: List[Optional[torch.Tensor]] = [None] * (D + 1)
         for L in range(1, D):
             wn, bnp = self._up_names(L)
@@ -206,13 +222,14 @@ class GeneratorProgram:
             dnext, dwm, dbm_up, dg, db = self.up[L].backward(tape[f"up{L}"], dcat[..., c[L]:], None, True, nw, nb,
                                                              self.inst and nw)
             if nw:
-                unmerge(dwm, dbm_up if self.inst else None, wn, ubn, D - 1 - L)
+                unmerge_or_defer(dwm, dbm_up if self.inst else None, wn, ubn, D - 1 - L)
             if not self.inst:
                 _put(G, bnp + ".weight", dg)
                 _put(G, bnp + ".bias", db)
             dcat = dnext            # gradient of cat_{L+1} (or of u for L == D - 1)
         ds = dcat
         dx = None
+        big_done = set()
         for L in range(D, 0, -1):
             q = _block_prefix(L)
             wname = "model.model.0.weight" if L == 1 else q + ".model.1.weight"
@@ -228,6 +245,9 @@ class GeneratorProgram:
                                                           need.get(wname, False), nb, bool(bname and need.get(bname, False)),
                                                           dx_out=dxo, dx_view=dxv)
             _put(G, wname, dw)
+            if red.active and dw is not None and dw.is_contiguous() and dw.numel() >= (1 << 16):
+                red.start(dw)
+                big_done.add(wname)
             if bname:
                 _put(G, bname, dbias)
             if 1 < L < D and not self.inst:
@@ -235,6 +255,11 @@ class GeneratorProgram:
                 _put(G, q + ".model.2.bias", db)
             if L == 1:
                 dx = ds
+        if red.active:
+            red.finish([g for k, g in G.items() if k not in big_done])     # BatchNorm / bias / first-layer gradients
+            for dwm, dbm, wn, bn_, row in deferred:                          # summed merged gradients -> dW4/6/8, d alpha
+                unmerge(dwm, dbm, wn, bn_, row)
+            G["__reduced__"] = True
         if need_arch:
             G[ARCH_KEY] = dalpha
         return dx, G

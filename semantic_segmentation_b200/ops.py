@@ -294,11 +294,12 @@ def _bn_ws(v: GsbView, device) -> torch.Tensor:
     return torch.empty(nbytes // 4, device=device, dtype=torch.float32)
 
 
-def bn_reduce(x: torch.Tensor) -> torch.Tensor:
+def bn_reduce(x: torch.Tensor, per_image: bool = False) -> torch.Tensor:
+    """[sum x, sum x^2] per channel (fp64 [2c]); per_image: per (image, channel), fp64 [2 * n * c] (InstanceNorm)."""
     v = view_nhwc(x)
     ws = _bn_ws(v, x.device)
-    sums = torch.empty(2 * v.c, device=x.device, dtype=torch.float64)
-    check(load().gsb_bn_reduce(_ref(v), ptr(sums), ptr(ws), ws.numel() * 4, _s(x)), "bn_reduce")
+    sums = torch.empty(2 * v.c * (v.n if per_image else 1), device=x.device, dtype=torch.float64)
+    check(load().gsb_bn_reduce(_ref(v), int(per_image), ptr(sums), ptr(ws), ws.numel() * 4, _s(x)), "bn_reduce")
     return sums
 
 
@@ -324,12 +325,12 @@ def bn_finalize(sums: Optional[torch.Tensor], count: float, gamma, beta, running
 
 def bn_act(x: torch.Tensor, scale, shift, act1: int, out1: torch.Tensor, act2: int = ACT_NONE,
            out2: Optional[torch.Tensor] = None, drop_seed: int = 0, drop_mask: Optional[torch.Tensor] = None,
-           center: Optional[torch.Tensor] = None, drop_offset: int = 0) -> None:
+           center: Optional[torch.Tensor] = None, drop_offset: int = 0, per_image: bool = False) -> None:
     """z = (x - center) * scale + shift (center None = 0); drop_offset: global element index of this tensor's first element
     (Philox dropout masks of a sharded batch equal those of the one-rank run)."""
     v2 = view_nhwc(out2) if out2 is not None else None
     check(load().gsb_bn_act(_ref(view_nhwc(x)), ptr(scale), ptr(shift), ptr(center), act1, _ref(view_nhwc(out1)), act2, _ref(v2),
-                            int(drop_seed), int(drop_offset), ptr(drop_mask), _s(x)), "bn_act")
+                            int(drop_seed), int(drop_offset), ptr(drop_mask), int(per_image), _s(x)), "bn_act")
 
 
 def bn_bwd_reduce(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, drop_seed=0, drop_mask=None, center=None,
@@ -345,11 +346,11 @@ def bn_bwd_reduce(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, drop_seed
 
 
 def bn_bwd_apply(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, sums, count, dx, dgamma=None, dbeta=None,
-                 drop_seed=0, drop_mask=None, center=None, drop_offset=0) -> None:
+                 drop_seed=0, drop_mask=None, center=None, drop_offset=0, per_image=False) -> None:
     v2 = view_nhwc(dA2) if dA2 is not None else None
     check(load().gsb_bn_bwd_apply(_ref(view_nhwc(x)), _ref(view_nhwc(dA1)), _ref(v2), ptr(scale), ptr(shift), ptr(center),
                                   ptr(mean), ptr(invstd), act1, act2, int(drop_seed), int(drop_offset), ptr(drop_mask), ptr(sums),
-                                  float(count), _ref(view_nhwc(dx)), ptr(dgamma), ptr(dbeta), _s(x)), "bn_bwd_apply")
+                                  float(count), _ref(view_nhwc(dx)), ptr(dgamma), ptr(dbeta), int(per_image), _s(x)), "bn_bwd_apply")
 
 
 def set_sm_reserve(n: int) -> int:
@@ -383,7 +384,7 @@ def bn_stats_finalize(partial: torch.Tensor, rows: int, c: int, count: float, ga
 
 
 def bn_bwd_stats(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, drop_seed=0, drop_mask=None, want_param_grads=True,
-                 peer=None, center=None, drop_offset=0):
+                 peer=None, center=None, drop_offset=0, per_image=False):
     """[sum dy, sum dy*xhat] in two launches: per-block rows, then totals + dgamma / dbeta (local) + cross-rank sum.
     -> (global sums fp64 [2c], dgamma, dbeta)."""
     v = view_nhwc(x)
@@ -392,12 +393,13 @@ def bn_bwd_stats(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, drop_seed=
     v2 = view_nhwc(dA2) if dA2 is not None else None
     check(load().gsb_bn_bwd_partial(_ref(v), _ref(view_nhwc(dA1)), _ref(v2), ptr(scale), ptr(shift), ptr(center), ptr(mean),
                                     ptr(invstd), act1, act2, int(drop_seed), int(drop_offset), ptr(drop_mask), ptr(ws),
-                                    ws.numel() * 4, C.byref(rows), _s(x)), "bn_bwd_partial")
-    sums = torch.empty(2 * v.c, device=x.device, dtype=torch.float64)
-    dgamma = torch.empty(v.c, device=x.device, dtype=torch.float32) if want_param_grads else None
-    dbeta = torch.empty(v.c, device=x.device, dtype=torch.float32) if want_param_grads else None
+                                    ws.numel() * 4, C.byref(rows), int(per_image), _s(x)), "bn_bwd_partial")
+    cc = v.c * (v.n if per_image else 1)          # per_image: one "channel" per (image, channel)
+    sums = torch.empty(2 * cc, device=x.device, dtype=torch.float64)
+    dgamma = torch.empty(cc, device=x.device, dtype=torch.float32) if want_param_grads else None
+    dbeta = torch.empty(cc, device=x.device, dtype=torch.float32) if want_param_grads else None
     arr, rank, world = _peer_args(peer)
-    check(load().gsb_bn_bwd_stats(ptr(ws), rows.value, v.c, arr, rank, world, ptr(dgamma), ptr(dbeta), 0, ptr(sums), _s(x)),
+    check(load().gsb_bn_bwd_stats(ptr(ws), rows.value, cc, arr, rank, world, ptr(dgamma), ptr(dbeta), 0, ptr(sums), _s(x)),
           "bn_bwd_stats")
     return sums, dgamma, dbeta
 

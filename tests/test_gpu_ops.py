@@ -484,10 +484,8 @@ def test_batched_pack_and_unpack_match_single():
         out = torch.empty(tuple(w.shape), device=DEV, dtype=torch.float32)
         ujobs.append((dwp, rfd, out, nsl))
         usingles.append(ops.unpack_wgrad(dwp, tuple(w.shape), rfd, nslices=nsl))
-        total = dwp[0].clone()
-        for sl in range(1, nsl):
-            total = total + dwp[sl]                # the same order, fp32
-        assert torch.equal(usingles[-1], ops.unpack_wgrad(total, tuple(w.shape), rfd))
+        total = dwp.double().sum(0).float()        # slices are added in slice order with fp64 accumulation
+        assert rel(usingles[-1], ops.unpack_wgrad(total, tuple(w.shape), rfd)) < 1e-7
         acc = torch.zeros_like(total).reshape(-1)
         ops.sum_slices(dwp, nsl, total.numel(), acc)
         assert rel(acc, dwp.double().sum(0).reshape(-1)) < 1e-6
@@ -568,3 +566,43 @@ def test_thin_convolutions(geom, dtype):
     res = conv_case(*geom, dtype=dtype, use_tc=0)
     tol = 1e-5 if dtype == torch.float32 else 6e-3
     assert res["fwd"] < tol and res["dgrad"] < tol and res["wgrad"] < (2e-5 if dtype == torch.float32 else 1e-4), res
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_instance_norm_batched_kernels(dtype):
+    """InstanceNorm2d(affine=False) (networks.py:34-35) at batch 8 through the per-image mode of the BatchNorm kernels:
+    statistics, normalise + LeakyReLU / ReLU outputs and the backward pass against torch, in ONE launch per stage whatever
+    the batch size."""
+    from semantic_segmentation_b200._lib import load
+    g = torch.Generator().manual_seed(41)
+    n, c, h, w = 8, 64, 12, 10
+    x = (torch.randn(n, c, h, w, generator=g) * 1.3 + 0.4 * torch.randn(n, c, 1, 1, generator=g))
+    if dtype == torch.bfloat16:
+        x = x.bfloat16().float()
+    xr = x.clone().requires_grad_(True)
+    z = F.instance_norm(xr, eps=1e-5)
+    a1, a2 = F.leaky_relu(z, 0.2), F.relu(z)
+    d1, d2 = torch.randn(a1.shape, generator=g), torch.randn(a1.shape, generator=g)
+    if dtype == torch.bfloat16:
+        d1, d2 = d1.bfloat16().float(), d2.bfloat16().float()
+    (a1 * d1 + a2 * d2).sum().backward()
+    xd = nhwc(x, dtype)
+    centered = dtype == torch.float32
+    l0 = load().gsb_launch_count()
+    sums = ops.bn_reduce(xd, per_image=True)
+    scale, shift, mean, invstd = ops.bn_finalize(sums, h * w, None, None, None, None, None, 0.1, 1e-5, n * c, torch.device(DEV),
+                                                 centered=centered)
+    o1, o2 = torch.empty_like(xd), torch.empty_like(xd)
+    ce = mean if centered else None
+    ops.bn_act(xd, scale, shift, ACT_LRELU, o1, ACT_RELU, o2, center=ce, per_image=True)
+    d1d, d2d = nhwc(d1, dtype), nhwc(d2, dtype)
+    bs, _, _ = ops.bn_bwd_stats(xd, d1d, d2d, scale, shift, mean, invstd, ACT_LRELU, ACT_RELU, 0, None, False, None, center=ce,
+                                per_image=True)
+    dx = torch.empty_like(xd)
+    ops.bn_bwd_apply(xd, d1d, d2d, scale, shift, mean, invstd, ACT_LRELU, ACT_RELU, bs, h * w, dx, center=ce, per_image=True)
+    launches = load().gsb_launch_count() - l0
+    assert launches == 7          # reduce (2) + finalize + act + bwd partial + bwd stats + bwd apply: independent of the batch size
+    tol = 2e-5 if dtype == torch.float32 else 8e-3
+    assert rel(from_nhwc(o1), a1) < tol and rel(from_nhwc(o2), a2) < tol
+    assert rel(mean.view(n, c), x.mean((2, 3))) < 1e-5
+    assert rel(from_nhwc(dx), xr.grad) < (5e-5 if dtype == torch.float32 else 1e-2)

@@ -112,15 +112,20 @@ def _torchrun(script, nproc, port, env=None):
 def test_two_ranks_peer_allreduce_and_parity():
     r = _torchrun("peer_check.py", 2, 29561)
     assert r.returncode == 0 and "bitwise equal across ranks" in r.stdout, r.stdout + r.stderr
-    # Bit-level equality of the 2-rank and 1-rank forward needs order-independent kernels: the split-K path of the small-tile
-    # tcgen05 kernel (fp32 red.global.add; taken by the 4x4 .. 8x8 levels of this 64x64 fixture) sums in arrival order, so
-    # it is switched off for the strict check and on for the tolerance check (ordinary bf16 rounding noise, <= 1e-3).
-    for port, env, tol in ((29562, {"DP_OVERLAP": "1", "GSB_TC_SPLITK": "0"}, 2e-6), (29563, {"DP_OVERLAP": "1"}, 1e-3)):
-        r = _torchrun("dp_check.py", 2, port, env)
-        print(env, [l for l in r.stdout.splitlines() if l.startswith("world 2")])
-        assert r.returncode == 0, r.stdout + r.stderr
-        lines = [l for l in r.stdout.splitlines() if l.startswith("world 2")]
-        assert len(lines) == 2
-        for l in lines:                                            # loss of the 2-rank run == 1-rank run
-            loss, ref = float(l.split("loss")[1].split()[0]), float(l.split("ref")[1].split()[0])
-            assert abs(loss - ref) < (2e-6 if "fp32" in l else tol), l
+    # Every kernel is order-independent (no atomics), so a run is bit-reproducible; the 2-rank and the 1-rank run still group
+    # their fp32 partial sums differently (tile counts and split factors follow the per-rank batch), which is ordinary
+    # rounding noise: <= 2e-6 on the fp32 loss, <= 1e-3 on the bf16 loss.  After ONE RMSprop step (grad_scale = 1: seg_loss is a
+    # global-batch mean) the 2-rank parameters equal the 1-rank parameters: a step moves a weight by lr * 10 = 1e-3, a wrong
+    # 1 / world would show as ~5e-4; rounding-level gradient differences move the update by < 2e-5 (fp32 mode).
+    r = _torchrun("dp_check.py", 2, 29562, {"DP_OVERLAP": "1"})
+    print([l for l in r.stdout.splitlines() if l.startswith("world 2") or l.startswith("dropout")])
+    assert r.returncode == 0, r.stdout + r.stderr
+    lines = [l for l in r.stdout.splitlines() if l.startswith("world 2")]
+    assert len(lines) == 2
+    for l in lines:                                            # loss of the 2-rank run == 1-rank run
+        loss, ref = float(l.split("loss")[1].split()[0]), float(l.split("ref")[1].split()[0])
+        assert abs(loss - ref) < (2e-6 if "fp32" in l else 1e-3), l
+        step = float(l.split("RMSprop step")[1].split()[0])
+        assert step < (2e-5 if "fp32" in l else 3e-4), l
+    drop = [l for l in r.stdout.splitlines() if l.startswith("dropout invariance")]
+    assert len(drop) == 1 and all(float(v) < 1e-4 for v in drop[0].split(":")[-1].split(",")), drop

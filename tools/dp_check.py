@@ -34,7 +34,46 @@ for prec in ("fp32", "bf16"):
     g = {k: p.grad for k, p in net.named_parameters()}
     errs = sorted(((rel(g[k], ref_g[k]), k) for k in g), reverse=True)   # global-mean loss -> summed shard grads == full grads
     worst = errs[0][0]
-    if parallel.rank() == 0:
-        print("world %d %s: loss %.7f ref %.7f  worst grad rel %.3e" % (world, prec, loss.item(), ref_loss.item(), worst), flush=True)
+    # one optimiser step: seg_loss is a GLOBAL-batch mean, so the summed shard gradients are the full-batch gradient and the
+    # optimiser must not divide by the world size (grad_scale = 1): N-rank parameters after the step == 1-rank parameters
+    from semantic_segmentation_b200.optim import RMSprop
+    parallel.shutdown()
+    ref_net = UNet(1, 2, True); ref_net.load_state_dict(st); ref_net = ref_net.to(dev).train()
+    for k, p in ref_net.named_parameters():
+        p.grad = ref_g[k].clone()
+    RMSprop(ref_net.parameters(), lr=1e-4, weight_decay=1e-8, momentum=0.9).step()
+    opt = RMSprop(net.parameters(), lr=1e-4, weight_decay=1e-8, momentum=0.9)
+    opt.grad_scale = 1.0
+    opt.step()
+    ref_p = dict(ref_net.named_parameters())
+    step_err = max(float((p.detach() - ref_p[k].detach()).abs().max()) for k, p in net.named_parameters())
+    if int(os.environ.get("RANK", "0")) == 0:
+        print("world %d %s: loss %.7f ref %.7f  worst grad rel %.3e  max |param - 1-rank param| after one RMSprop step %.3e (lr 1e-4)"
+              % (world, prec, loss.item(), ref_loss.item(), worst, step_err), flush=True)
         print("   worst keys: " + ", ".join("%s %.1e" % (k, e) for e, k in errs[:5]) + " | median %.1e" % errs[len(errs) // 2][0], flush=True)
+# rank-count-invariant dropout: the generator's Philox masks are indexed by the GLOBAL element, so a sharded batch draws the
+# masks of the one-rank run (sync-BN on): the 2-rank outputs equal the matching rows of the 1-rank output
+from semantic_segmentation_b200.models_pix2pix import networks
+S.set_precision("fp32")
+parallel.shutdown()
+torch.manual_seed(77)
+G = networks.define_G(1, 1, 64, "unet_256", "batch", True, "normal", 0.02, []).to(dev).train()
+networks.upconv_arch = (1e-3 * torch.randn(8, 3, generator=torch.Generator().manual_seed(5))).to(dev).requires_grad_(True)
+m = torch.randint(0, 2, (4, 1, 256, 256), generator=torch.Generator().manual_seed(6)).float()
+sd = {k: v.clone() for k, v in G.state_dict().items()}
+torch.manual_seed(99); G._program._calls = 0
+with torch.no_grad():
+    full = G(m.to(dev))
+world = parallel.init_data_parallel(sync_bn=True)
+G.load_state_dict(sd)
+lo, hi = parallel.shard_batch(4)
+torch.manual_seed(99); G._program._calls = 0
+with torch.no_grad():
+    part = G(m[lo:hi].to(dev))
+e = rel(part, full[lo:hi])
+allv = [None] * world
+dist.all_gather_object(allv, e)
+if int(os.environ.get("RANK", "0")) == 0:
+    print("dropout invariance world %d: rel-L2 of the sharded generator output against the one-rank rows: %s" % (world, ", ".join("%.2e" % v for v in allv)), flush=True)
+S.set_precision("bf16")
 dist.barrier()
