@@ -69,11 +69,14 @@ __global__ void __launch_bounds__(256) conv_gather_kernel(DView in, const void* 
       aoy[i] = aox[i] = 0;
     }
   }
-  float acc[TM][TN];
+  // two-level accumulation (this is the kernel of the fp32 validation mode): fp32 FMAs inside a BK-channel block, fp64
+  // across blocks and taps, so a K = 8192 reduction is as accurate as torch's blocked CPU kernel (a plain fp32 running sum
+  // was 3x further from the fp64 reference and flipped 3x more ReLU branches in whole-network gradient comparisons)
+  double acc[TM][TN];
 #pragma unroll
   for (int a = 0; a < TM; ++a)
 #pragma unroll
-    for (int b = 0; b < TN; ++b) acc[a][b] = 0.f;
+    for (int b = 0; b < TN; ++b) acc[a][b] = 0.0;
 
   // transposed conv with sub == stride: only taps with k == (o + pad) mod stride contribute
   int ky0 = 0, kx0 = 0, kstep = 1;
@@ -114,6 +117,11 @@ __global__ void __launch_bounds__(256) conv_gather_kernel(DView in, const void* 
           }
         }
         __syncthreads();
+        float part[TM][TN];
+#pragma unroll
+        for (int i = 0; i < TM; ++i)
+#pragma unroll
+          for (int j = 0; j < TN; ++j) part[i][j] = 0.f;
 #pragma unroll
         for (int k = 0; k < BK; ++k) {
           float a[TM], b[TN];
@@ -124,8 +132,12 @@ __global__ void __launch_bounds__(256) conv_gather_kernel(DView in, const void* 
 #pragma unroll
           for (int i = 0; i < TM; ++i)
 #pragma unroll
-            for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+            for (int j = 0; j < TN; ++j) part[i][j] = fmaf(a[i], b[j], part[i][j]);
         }
+#pragma unroll
+        for (int i = 0; i < TM; ++i)
+#pragma unroll
+          for (int j = 0; j < TN; ++j) acc[i][j] += (double)part[i][j];
         __syncthreads();
       }
     }
@@ -143,7 +155,7 @@ __global__ void __launch_bounds__(256) conv_gather_kernel(DView in, const void* 
     for (int j = 0; j < TN; ++j) {
       int co = n0 + tx * TN + j;
       if (co >= Cout) continue;
-      float v = acc[i][j];
+      float v = (float)acc[i][j];
       if (bias != nullptr) v += bias[co];
       int64_t o = obase + (int64_t)co * out.sc;
       if (accumulate) v += ld_elem(out.ptr, o, out.dtype);

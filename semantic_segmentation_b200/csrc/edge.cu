@@ -514,6 +514,13 @@ __global__ void __launch_bounds__(256, 4) head_bwd_kernel(const T* __restrict__ 
   if (db != nullptr && threadIdx.x < C) db[(int64_t)blockIdx.x * rowlen + threadIdx.x] = sdb[threadIdx.x];
 }
 
+// tensor-core stem (stem_tc.cu)
+bool stem_tc_applicable(int cin, int cout, int k, int stride, int dtype, int64_t pixels);
+int stem_tc_fwd(const float* x, int h, int w, const float* weight, const gsb_view* y, int k, int stride, int pad, float* stats,
+                int max_rows, int* rows, cudaStream_t st);
+int stem_tc_wgrad(const float* x, int h, int w, const gsb_view* dy, int k, int stride, int pad, float* partial, int max_rows,
+                  int* rows, cudaStream_t st);
+
 static int grid_cap(int64_t want, int per_sm) {
   int64_t cap = (int64_t)num_sms() * per_sm;
   return (int)(want < 1 ? 1 : (want > cap ? cap : want));
@@ -550,6 +557,13 @@ extern "C" int gsb_stem_conv_fwd(const float* x, int n, int cin, int h, int w, c
   const int cout = y->c;
   int64_t total = num_pixels(y) * (cout / 8);
   if (stats_rows) *stats_rows = 0;
+  if (bias == nullptr && act == GSB_ACT_NONE && stem_tc_applicable(cin, cout, k, stride, y->dtype, num_pixels(y))) {
+    // im2col tile in shared memory + tcgen05.mma (hi / lo bf16 split of the fp32 input and weights): bound by the output stream
+    int rows = 0;
+    if (stem_tc_fwd(x, h, w, weight, y, k, stride, pad, stats_partial, gsb_stem_stats_rows(), &rows, to_stream(s))) return -1;
+    if (stats_partial && stats_rows) *stats_rows = rows;
+    return check_launch("stem_conv_fwd(tc)");
+  }
   const bool k3 = (k == 3 && stride == 1), k4 = (k == 4 && stride == 2);
   if ((k3 || k4) && total < (int64_t)1 << 31) {
     constexpr int PX = 4;
@@ -595,6 +609,13 @@ extern "C" int gsb_stem_conv_wgrad(const float* x, int n, int cin, int h, int w,
     int g = grid_cap(want, per_sm);
     return (int)(g > max_rows ? max_rows : g);
   };
+  if (dy->sw == cout && ((uintptr_t)dy->ptr % 128) == 0 && stem_tc_applicable(cin, cout, k, stride, dy->dtype, num_pixels(dy))) {
+    int rows = 0;
+    if (stem_tc_wgrad(x, h, w, dy, k, stride, pad, partial, (int)(max_rows > (1 << 20) ? (1 << 20) : max_rows), &rows, to_stream(s)))
+      return -1;
+    gsb::sum_slices(partial, rows, (int64_t)cout * taps, (int64_t)cout * taps, dweight, 0, to_stream(s));
+    return check_launch("stem_conv_wgrad(tc)", 2);
+  }
   if (k == 3 && stride == 1 && num_pixels(dy) < (int64_t)1 << 31) {
     constexpr int PX = 4;
     const int64_t items = (int64_t)dy->n * dy->h * ((dy->w + PX - 1) / PX);

@@ -536,6 +536,7 @@ __global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const __grid_co
 // the tile loader below would walk them one after the other per element (8 CTAs x 74 dependent 16-byte loads: 120 us).
 // One launch first folds the slices of all such jobs into their slice 0, in place: a block owns `cols` columns x L slice
 // lanes (L = power of two >= nslices, <= 32); lane l adds slices l, l + L, ... in fp64, the lane sums are added in lane order.
+constexpr int kFoldReps = 32;
 struct SliceJobs {
   float* ws[kMaxLayoutJobs];
   int64_t n[kMaxLayoutJobs];
@@ -547,19 +548,24 @@ __global__ void __launch_bounds__(256) fold_slices_multi_kernel(const __grid_con
   GSB_PDL_ENTRY();
   __shared__ double red[256];
   const int j = find_job(J.blk0, J.count, blockIdx.x);
-  const int L = J.lanes[j], cols = 256 / L;
+  const int L = J.lanes[j], cols = 256 / L, ns = J.nslices[j];
   const int c = threadIdx.x % cols, l = threadIdx.x / cols;
-  const int64_t n = J.n[j], col = (int64_t)(blockIdx.x - J.blk0[j]) * cols + c;
+  const int64_t n = J.n[j];
   float* ws = J.ws[j];
-  double a = 0.0;
-  if (col < n)
-    for (int s = l; s < J.nslices[j]; s += L) a += (double)ws[(int64_t)s * n + col];
-  red[l * cols + c] = a;
-  __syncthreads();
-  if (l == 0 && col < n) {
-    double t = 0.0;
-    for (int i = 0; i < L; ++i) t += red[i * cols + c];
-    ws[col] = (float)t;
+  // kFoldReps column chunks per block: a block per chunk drowned in block-scheduling overhead (150 k blocks, 1.1 ms)
+  for (int rep = 0; rep < kFoldReps; ++rep) {
+    const int64_t col = ((int64_t)(blockIdx.x - J.blk0[j]) * kFoldReps + rep) * cols + c;
+    double a = 0.0;
+    if (col < n)
+      for (int s = l; s < ns; s += L) a += (double)ws[(int64_t)s * n + col];
+    red[l * cols + c] = a;
+    __syncthreads();
+    if (l == 0 && col < n) {
+      double t = 0.0;
+      for (int i = 0; i < L; ++i) t += red[i * cols + c];
+      ws[col] = (float)t;
+    }
+    __syncthreads();
   }
 }
 
@@ -576,7 +582,7 @@ static int run_layout_multi(bool pack, int n, const void* const* src, void* cons
       int blocks = 0;
       const int end = n - begin < kMaxLayoutJobs ? n : begin + kMaxLayoutJobs;
       for (int i = begin; i < end; ++i) {
-        if (nslices[i] <= 4 || i >= kMaxLayoutJobs * 4) continue;
+        if (nslices[i] <= 8 || i >= kMaxLayoutJobs * 4) continue;
         int L = 1;
         while (L < nslices[i] && L < 32) L <<= 1;
         const int k = S.count++;
@@ -585,7 +591,7 @@ static int run_layout_multi(bool pack, int n, const void* const* src, void* cons
         S.nslices[k] = nslices[i];
         S.lanes[k] = L;
         S.blk0[k] = blocks;
-        blocks += (int)((S.n[k] + (256 / L) - 1) / (256 / L));
+        blocks += (int)((S.n[k] + (int64_t)(256 / L) * kFoldReps - 1) / ((int64_t)(256 / L) * kFoldReps));
         folded[i] = true;
       }
       S.blk0[S.count] = blocks;

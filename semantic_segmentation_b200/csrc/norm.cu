@@ -34,6 +34,12 @@ __device__ __forceinline__ void store8(const PixView& v, int64_t p, int c0, cons
   Vec8<T>::store(reinterpret_cast<T*>(v.ptr) + p * v.ld + c0, f);
 }
 
+// per-image mode: move a pixel-linear view to image `img` (P pixels per image), once, outside the pixel loops
+template <typename T>
+__device__ __forceinline__ void advance_view(PixView& v, int64_t pixels) {
+  if (v.ptr != nullptr) v.ptr = reinterpret_cast<T*>(v.ptr) + pixels * v.ld;
+}
+
 __device__ __forceinline__ void load_param8(const float* p, int c0, float (&f)[8], float dflt) {
   if (p == nullptr) {
 #pragma unroll
@@ -96,6 +102,11 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
   // blockIdx.y, the per-channel parameter arrays are [images][C] and a partial row is [2][images * C]
   const int img = blockIdx.y, NC = gridDim.y * C, poff = img * C;
   const int64_t pbase = (int64_t)img * P;
+  if (img != 0) {
+    advance_view<T>(x, pbase);
+    advance_view<T>(dA1, pbase);
+    advance_view<T>(dA2, pbase);
+  }
   Acc s0[8], s1[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) s0[i] = s1[i] = (Acc)0;
@@ -116,10 +127,10 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
 #pragma unroll
     for (int u = 0; u < KU; ++u)
       if (p0 + u * step < P) {
-        load8<T>(x, pbase + p0 + u * step, c0, v[u]);
+        load8<T>(x, p0 + u * step, c0, v[u]);
         if (MODE == 1) {
-          load8<T>(dA1, pbase + p0 + u * step, c0, a[u]);
-          if (two) load8<T>(dA2, pbase + p0 + u * step, c0, b[u]);
+          load8<T>(dA1, p0 + u * step, c0, a[u]);
+          if (two) load8<T>(dA2, p0 + u * step, c0, b[u]);
         }
       }
 #pragma unroll
@@ -316,6 +327,11 @@ __global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, 
   const int c0 = g * 8;
   const int poff = blockIdx.y * C;                   // per-image parameters (InstanceNorm): gridDim.y = images, P per image
   const int64_t pbase = (int64_t)blockIdx.y * P;
+  if (blockIdx.y != 0) {
+    advance_view<T>(x, pbase);
+    advance_view<T>(out1, pbase);
+    advance_view<T>(out2, pbase);
+  }
   float sc[8], sh[8], ce[8];
   load_param8(scale ? scale + poff : nullptr, c0, sc, 1.f);
   load_param8(shift ? shift + poff : nullptr, c0, sh, 0.f);
@@ -328,7 +344,7 @@ __global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, 
     float v[kUnroll][8];
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u)
-      if (p0 + u * step < P) load8<T>(x, pbase + p0 + u * step, c0, v[u]);
+      if (p0 + u * step < P) load8<T>(x, p0 + u * step, c0, v[u]);
 #pragma unroll
     for (int u = 0; u < kUnroll; ++u) {
       const int64_t p = p0 + u * step;
@@ -342,8 +358,8 @@ __global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, 
         o1[i] = act_fwd(z * dm, act1);
         if (has_out2) o2[i] = act_fwd(z, act2);
       }
-      store8<T>(out1, pbase + p, c0, o1);
-      if (has_out2) store8<T>(out2, pbase + p, c0, o2);
+      store8<T>(out1, p, c0, o1);
+      if (has_out2) store8<T>(out2, p, c0, o2);
     }
   }
 }
@@ -362,6 +378,12 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
   const int c0 = g * 8;
   const int NC = gridDim.y * C, poff = blockIdx.y * C;   // per-image parameters / sums (InstanceNorm), P per image
   const int64_t pbase = (int64_t)blockIdx.y * P;
+  if (blockIdx.y != 0) {
+    advance_view<T>(x, pbase);
+    advance_view<T>(dA1, pbase);
+    advance_view<T>(dA2, pbase);
+    advance_view<T>(dx, pbase);
+  }
   float sc[8], sh[8], mu[8], is[8], m0[8], m1[8], ce[8];
   load_param8(scale ? scale + poff : nullptr, c0, sc, 1.f);
   load_param8(shift ? shift + poff : nullptr, c0, sh, 0.f);
@@ -416,9 +438,9 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
 #pragma unroll
     for (int u = 0; u < kUnrollBwd; ++u)
       if (p0 + u * step < P) {
-        load8<T>(x, pbase + p0 + u * step, c0, v[u]);
-        load8<T>(dA1, pbase + p0 + u * step, c0, a[u]);
-        if (two) load8<T>(dA2, pbase + p0 + u * step, c0, b[u]);
+        load8<T>(x, p0 + u * step, c0, v[u]);
+        load8<T>(dA1, p0 + u * step, c0, a[u]);
+        if (two) load8<T>(dA2, p0 + u * step, c0, b[u]);
       }
 #pragma unroll
     for (int u = 0; u < kUnrollBwd; ++u) {
@@ -439,7 +461,7 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
           o[i] = dy * sc[i];
         }
       }
-      store8<T>(dx, pbase + p, c0, o);
+      store8<T>(dx, p, c0, o);
     }
   }
 }

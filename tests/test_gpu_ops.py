@@ -606,3 +606,37 @@ def test_instance_norm_batched_kernels(dtype):
     assert rel(from_nhwc(o1), a1) < tol and rel(from_nhwc(o2), a2) < tol
     assert rel(mean.view(n, c), x.mean((2, 3))) < 1e-5
     assert rel(from_nhwc(dx), xr.grad) < (5e-5 if dtype == torch.float32 else 1e-2)
+
+
+@pytest.mark.parametrize("cfg", [(3, 1, 1, 5, 40, 56), (4, 2, 1, 3, 64, 32), (3, 1, 1, 2, 256, 256)])
+def test_stem_conv_tensor_core(cfg):
+    """Network-input convolutions on the tensor cores (stem_tc.cu: im2col tile in shared memory, hi / lo bf16 split of the
+    fp32 input and weights, tcgen05.mma, fp32 accumulation in TMEM): forward against torch's fp32 convolution to bf16
+    output rounding, the fused BatchNorm statistics of the stored values exactly, the weight gradient to 2e-5; a pixel
+    count that is not a multiple of the 128-pixel tile; bit-reproducible."""
+    k, s, p, n, h, w = cfg
+    g = torch.Generator().manual_seed(13)
+    x = torch.rand(n, 1, h, w, generator=g)
+    wt = torch.randn(64, 1, k, k, generator=g) * 0.3
+    wr = wt.clone().requires_grad_(True)
+    y = F.conv2d(x, wr, None, stride=s, padding=p)
+    dy = torch.randn(y.shape, generator=g).bfloat16().float()
+    y.backward(dy)
+    oh, ow = y.shape[2], y.shape[3]
+    xd, wd = x.to(DEV), wt.to(DEV)
+    outs = []
+    for _ in range(2):
+        yd = torch.empty((n, oh, ow, 64), device=DEV, dtype=torch.bfloat16)
+        stats, rows = ops.stem_conv_fwd(xd, wd, None, yd, k, s, p, want_stats=True)
+        dw = ops.stem_conv_wgrad(xd, nhwc(dy, torch.bfloat16), k, s, p)
+        sums = ops.bn_reduce_partials(stats, rows, 64)
+        outs.append((yd.clone(), sums.clone(), dw.clone()))
+    yd, sums, dw = outs[0]
+    assert all(torch.equal(a, b) for a, b in zip(outs[0], outs[1]))
+    assert rel(from_nhwc(yd), y) < 3e-3
+    # against the exactly rounded fp32 result: the split keeps 16 mantissa bits of every product -> at most a few ulps of bf16
+    exact = y.detach().bfloat16().float()
+    assert float((from_nhwc(yd) - exact).abs().max()) <= 2.0 ** -7 * float(y.detach().abs().max())
+    yq = yd.double()
+    assert rel(sums, torch.cat([yq.sum((0, 1, 2)), (yq * yq).sum((0, 1, 2))])) < 1e-5
+    assert rel(dw, wr.grad) < 2e-5
