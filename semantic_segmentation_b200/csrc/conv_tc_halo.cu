@@ -58,6 +58,50 @@ __device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t mask) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
                ::"r"(smem_u32(bar)), "h"(mask) : "memory");
 }
+// ---- CTA-pair forms (tcgen05 cta_group::2): the two CTAs of a cluster issue ONE M = 256 MMA per step.  CTA r supplies rows
+// [128 r, 128 r + 128) of A from its own shared memory and N/2 columns of B, so every CTA reads only half of each weight tile
+// from shared memory (the N = 64 / 128 tiles of the one-CTA form are bound by shared-memory operand bandwidth: 192 / 128 bytes
+// per clock for 128 available).  The MMA is issued by the leader (cluster rank 0); TMA loads of both CTAs signal the LEADER's
+// barriers (peer bit of the shared::cluster address cleared), commits are multicast to both CTAs.
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
+__device__ __forceinline__ void mbar_expect_tx_cluster(uint32_t bar_addr, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cluster.b64 _, [%0], %1;" ::"r"(bar_addr), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar_addr) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d_pair(const void* map, uint32_t bar_addr, void* dst, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(bar_addr), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(const void* map, uint32_t bar_addr, void* dst, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(bar_addr), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair_mc(uint64_t* bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* holder, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(holder)), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+
 __device__ __forceinline__ void sts_128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
@@ -90,11 +134,14 @@ __device__ __forceinline__ void cluster_sync_all() {
 // BN = output channels per tile (64 / 128 double-buffered accumulators, 256 single-buffered);
 // CL = cluster size: the CL CTAs of a cluster own CL different 16x16 tiles with the SAME weight tile, each
 // loads 1/CL of every weight slot and multicasts it to all of them (L2 weight reads / CL).
-template <int BN, int CL>
+// PAIR (needs CL == 2): the cta_group::2 form described above; B_SLOT = bytes of one weight tap in THIS CTA's shared memory.
+template <int BN, int CL, bool PAIR = false>
 __global__ void __launch_bounds__(320, 1)
 conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__ HaloPlan plan, const HaloParams p) {
   GSB_PDL_ENTRY();
+  static_assert(!PAIR || CL == 2, "the CTA-pair MMA needs a cluster of two");
   constexpr int B_BYTES = BN * 128;
+  constexpr int B_SLOT = PAIR ? B_BYTES / 2 : B_BYTES;
   constexpr int OUT_COLS = BN > 128 ? 128 : BN;
   constexpr int OUT_BYTES = 128 * OUT_COLS * 2;
   constexpr int RED_BYTES = 8 * 2 * OUT_COLS * 4;
@@ -105,7 +152,7 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem;
   uint8_t* sB = sA + p.nA * p.a_stride;
-  uint8_t* s_out = sB + p.nB * p.tb * B_BYTES;
+  uint8_t* s_out = sB + p.nB * p.tb * B_SLOT;
   float* s_red = reinterpret_cast<float*>(s_out + OUT_BYTES);
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_out + OUT_BYTES + RED_BYTES);
   float* s_acc = reinterpret_cast<float*>(bars + 32);  // [2][cout] running BN sums of this CTA (only when p.stats)
@@ -120,16 +167,16 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     for (int i = 0; i < 4; ++i) {
-      mbar_init(&fullA[i], 1);
+      mbar_init(&fullA[i], PAIR ? 2 : 1);   // PAIR: the leader's barrier collects the loads of both CTAs
       mbar_init(&emptyA[i], 1);
     }
     for (int i = 0; i < 8; ++i) {
-      mbar_init(&fullB[i], 1);
-      mbar_init(&emptyB[i], CL);  // every CTA of the cluster reads the slot its peers multicast into
+      mbar_init(&fullB[i], PAIR ? 2 : 1);
+      mbar_init(&emptyB[i], PAIR ? 1 : CL);  // one-CTA form: every CTA of the cluster reads the slot its peers multicast into
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tfull[i], 1);
-      mbar_init(&tempty[i], 256);
+      mbar_init(&tempty[i], PAIR ? 512 : 256);   // PAIR: the epilogue threads of both CTAs release the leader's MMA warp
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     prefetch_tmap(&maps.w);
@@ -137,7 +184,9 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
     prefetch_tmap(&maps.in[0]);
   }
   __syncthreads();
-  if (warp == 1) tmem_alloc(tmem_holder, TMEM_COLS);
+  if (warp == 1) {
+    if (PAIR) tmem_alloc_pair(tmem_holder, TMEM_COLS); else tmem_alloc(tmem_holder, TMEM_COLS);
+  }
   tc_fence_before();
   if (CL > 1) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
@@ -162,19 +211,29 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
           for (int g = 0; g < plan.ngroups; ++g) {
             if (!p.full || g == 0) {
               mbar_wait(&emptyA[sa], pa ^ 1u);
-              mbar_expect_tx(&fullA[sa], (uint32_t)p.a_bytes);
-              tma_load_4d(&maps.in[plan.map[g]], &fullA[sa], sA + sa * p.a_stride, kb * 64, x0 + plan.dx[g], y0 + plan.dy0[g], n);
+              if (PAIR) {
+                const uint32_t fb = smem_u32(&fullA[sa]) & kPeerBitMask;   // the leader's barrier
+                mbar_expect_tx_cluster(fb, (uint32_t)p.a_bytes);
+                tma_load_4d_pair(&maps.in[plan.map[g]], fb, sA + sa * p.a_stride, kb * 64, x0 + plan.dx[g], y0 + plan.dy0[g], n);
+              } else {
+                mbar_expect_tx(&fullA[sa], (uint32_t)p.a_bytes);
+                tma_load_4d(&maps.in[plan.map[g]], &fullA[sa], sA + sa * p.a_stride, kb * 64, x0 + plan.dx[g], y0 + plan.dy0[g], n);
+              }
               if (++sa == p.nA) { sa = 0; pa ^= 1u; }
             }
             const int nd = plan.ndy[g];
             for (int j0 = 0; j0 < nd; j0 += p.tb) {
               const int nt_ = nd - j0 < p.tb ? nd - j0 : p.tb;
               mbar_wait(&emptyB[sb], pb ^ 1u);
-              mbar_expect_tx(&fullB[sb], (uint32_t)(nt_ * B_BYTES));
+              const uint32_t fbB = smem_u32(&fullB[sb]) & kPeerBitMask;
+              if (PAIR) mbar_expect_tx_cluster(fbB, (uint32_t)(nt_ * B_SLOT));
+              else mbar_expect_tx(&fullB[sb], (uint32_t)(nt_ * B_BYTES));
               for (int t = 0; t < nt_; ++t) {
                 const int wrow = (int)plan.wtap[g][j0 + t] * p.cout + nt * BN;
-                uint8_t* dst = sB + (sb * p.tb + t) * B_BYTES;
-                if (CL > 1)
+                uint8_t* dst = sB + (sb * p.tb + t) * B_SLOT;
+                if (PAIR)      // this CTA keeps ITS half of the weight rows only: the pair MMA reads both halves in place
+                  tma_load_2d_pair(&maps.w, fbB, dst, kb * 64, wrow + rank * (BN / 2));
+                else if (CL > 1)
                   tma_load_2d_mc(&maps.w, &fullB[sb], dst + rank * (B_BYTES / CL), kb * 64, wrow + rank * (BN / CL), kMask);
                 else
                   tma_load_2d(&maps.w, &fullB[sb], dst, kb * 64, wrow);
@@ -185,12 +244,14 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
         }
       }
     }
+  } else if (warp == 1 && PAIR && rank != 0) {
+    // the peer's MMA warp has nothing to issue: the leader's instructions drive both tensor cores
   } else if (warp == 1) {
     // ---------------- MMA issuer ----------------
     // The WHOLE warp runs the loop (warp-uniform control flow and operands, so descriptors and barrier addresses stay
     // in uniform registers); one elected lane issues.  With `if (lane == 0)` around the loop every tcgen05.mma cost
     // ~20 dependent per-thread instructions (~120 cycles, ncu profiles/r01e) against 32-128 cycles of tensor time.
-    constexpr uint32_t idesc = umma_idesc(128, BN, 0, 0);
+    constexpr uint32_t idesc = umma_idesc(PAIR ? 256 : 128, BN, 0, 0);
     int sa = 0, sb = 0;
     uint32_t pa = 0, pb = 0, acc = 0, acc_phase = 0;
     const uint32_t row_bytes = (uint32_t)p.pw * 128u;
@@ -215,34 +276,44 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
             const int nt_ = nd - j0 < p.tb ? nd - j0 : p.tb;
             mbar_wait(&fullB[sb], pb);
             tc_fence_after();
-            const uint64_t bdesc0 = desc_hi_b | (uint64_t)(((sB_u + sb * p.tb * B_BYTES) & 0x3FFFFu) >> 4);
+            const uint64_t bdesc0 = desc_hi_b | (uint64_t)(((sB_u + sb * p.tb * B_SLOT) & 0x3FFFFu) >> 4);
             const uint64_t adesc0 = desc_hi_a | (uint64_t)(((a_base + j0 * row_bytes) & 0x3FFFFu) >> 4);
             if (elect_one()) {
               for (int t = 0; t < nt_; ++t) {
-                const uint64_t adesc = adesc0 + (uint64_t)(t * (row_bytes >> 4)), bdesc = bdesc0 + (uint64_t)(t * (B_BYTES >> 4));
+                const uint64_t adesc = adesc0 + (uint64_t)(t * (row_bytes >> 4)), bdesc = bdesc0 + (uint64_t)(t * (B_SLOT >> 4));
 #pragma unroll
                 for (int m = 0; m < 2; ++m) {
                   if (m < p.mt) {
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                      umma_bf16(d0 + m * BN, adesc + (uint64_t)(64 * m + 2 * k), bdesc + (uint64_t)(2 * k), idesc, accum | (uint32_t)(t | k));
+                    for (int k = 0; k < 4; ++k) {
+                      if (PAIR)
+                        umma_bf16_pair(d0 + m * BN, adesc + (uint64_t)(64 * m + 2 * k), bdesc + (uint64_t)(2 * k), idesc, accum | (uint32_t)(t | k));
+                      else
+                        umma_bf16(d0 + m * BN, adesc + (uint64_t)(64 * m + 2 * k), bdesc + (uint64_t)(2 * k), idesc, accum | (uint32_t)(t | k));
+                    }
                   }
                 }
               }
-              if (CL > 1) umma_commit_mc(&emptyB[sb], kMask); else umma_commit(&emptyB[sb]);
+              if (PAIR) umma_commit_pair_mc(&emptyB[sb], kMask);
+              else if (CL > 1) umma_commit_mc(&emptyB[sb], kMask);
+              else umma_commit(&emptyB[sb]);
             }
             __syncwarp();
             accum = 1;
             if (++sb == p.nB) { sb = 0; pb ^= 1u; }
           }
           if (!p.full || g == plan.ngroups - 1) {
-            if (elect_one()) umma_commit(&emptyA[sa]);
+            if (elect_one()) {
+              if (PAIR) umma_commit_pair_mc(&emptyA[sa], kMask); else umma_commit(&emptyA[sa]);
+            }
             __syncwarp();
             if (++sa == p.nA) { sa = 0; pa ^= 1u; }
           }
         }
       }
-      if (elect_one()) umma_commit(&tfull[acc]);
+      if (elect_one()) {
+        if (PAIR) umma_commit_pair_mc(&tfull[acc], kMask); else umma_commit(&tfull[acc]);
+      }
       __syncwarp();
       if (++acc == NBUF) { acc = 0; acc_phase ^= 1u; }
     }
@@ -326,7 +397,8 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
         }
         if (mh == n_mh - 1) {
           tc_fence_before();
-          mbar_arrive(&tempty[acc]);  // accumulators drained: the MMA warp may reuse this TMEM buffer
+          // accumulators drained: the MMA warp (PAIR: the leader's) may reuse this TMEM buffer
+          if (PAIR) mbar_arrive_cluster(smem_u32(&tempty[acc]) & kPeerBitMask); else mbar_arrive(&tempty[acc]);
         }
         fence_proxy_async();
         named_bar_sync(1, 256);
@@ -381,7 +453,7 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
   if (CL > 1) cluster_sync_all(); else __syncthreads();  // no CTA may exit while a peer still multicasts into it
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    if (PAIR) tmem_dealloc_pair(tmem_base, TMEM_COLS); else tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
@@ -617,6 +689,12 @@ static bool fullhalo_enabled() {
   if (v < 0) v = env_flag("GSB_TC_FULLHALO", true) ? 1 : 0;
   return v != 0;
 }
+// GSB_TC_PAIR: 0 = one-CTA MMAs everywhere, 1 = cta_group::2 (CTA pair) for the 64- and 128-column tiles (default),
+// 2 = also for the 256-column tiles
+static int pair_mode() {   // read on every call (tests and A/B runs switch it inside one process)
+  const char* e = getenv("GSB_TC_PAIR");
+  return (e != nullptr && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1;
+}
 static bool bn256_enabled() {
   static int v = -1;
   if (v < 0) v = env_flag("GSB_TC_BN256", true) ? 1 : 0;
@@ -683,6 +761,7 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
   if (make_act_map(&maps.out, outv, 8, 16, 1)) return -1;
   const int spatial = (((int)outv.W + tw - 1) / tw) * (((int)outv.H + 15) / 16) * (int)outv.N;
   const int CL = (cluster_enabled() && spatial >= 2) ? 2 : 1;
+  const bool pair = CL == 2 && (pair_mode() == 2 || (pair_mode() == 1 && BN <= 128));
   if (make_w_map(&maps.w, wp, (int64_t)taps_total * cout, cin, BN / CL)) return -1;
   HaloParams p;
   p.mt = mt; p.tw = tw;
@@ -696,7 +775,7 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
   p.full = full;
   p.a_bytes = p.pw * boxh * 128;
   p.a_stride = (p.a_bytes + 1023) & ~1023;
-  const int b_bytes = BN * 128;
+  const int b_bytes = pair ? BN * 64 : BN * 128;   // CTA pair: every CTA holds half of the weight rows
   const int out_cols = BN > 128 ? 128 : BN;
   const int fixed = 1024 + 128 * out_cols * 2 + 8 * 2 * out_cols * 4 + 256 + (stats ? 2 * cout * 4 : 0);
   p.tb = (BN == 64 && uniform) ? max_ndy : 1;
@@ -719,7 +798,8 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
   const int grid = (p.num_tiles < max_clusters ? p.num_tiles : max_clusters) * CL;
   if (stats_rows) *stats_rows = grid;  // one row of running sums per CTA
   void (*kern)(TcMaps, HaloPlan, HaloParams) = nullptr;
-  if (CL == 2) kern = BN == 256 ? conv_tc_halo_kernel<256, 2> : (BN == 128 ? conv_tc_halo_kernel<128, 2> : conv_tc_halo_kernel<64, 2>);
+  if (pair) kern = BN == 256 ? conv_tc_halo_kernel<256, 2, true> : (BN == 128 ? conv_tc_halo_kernel<128, 2, true> : conv_tc_halo_kernel<64, 2, true>);
+  else if (CL == 2) kern = BN == 256 ? conv_tc_halo_kernel<256, 2> : (BN == 128 ? conv_tc_halo_kernel<128, 2> : conv_tc_halo_kernel<64, 2>);
   else kern = BN == 256 ? conv_tc_halo_kernel<256, 1> : (BN == 128 ? conv_tc_halo_kernel<128, 1> : conv_tc_halo_kernel<64, 1>);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   GSB_REQUIRE(e == cudaSuccess, "cudaFuncSetAttribute(smem=%d) failed: %s", smem, cudaGetErrorString(e));

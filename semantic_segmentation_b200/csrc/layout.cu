@@ -534,36 +534,45 @@ __global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const __grid_co
 
 // Jobs of an un-pack launch whose source holds many partial-sum slices (small layers split 24..74 ways over the pixels):
 // the tile loader below would walk them one after the other per element (8 CTAs x 74 dependent 16-byte loads: 120 us).
-// One launch first folds the slices of all such jobs into their slice 0, in place: a block owns `cols` columns x L slice
-// lanes (L = power of two >= nslices, <= 32); lane l adds slices l, l + L, ... in fp64, the lane sums are added in lane order.
-constexpr int kFoldReps = 32;
+// One launch first folds the slices of all such jobs into their slice 0, in place (the source workspace is scratch).
+constexpr int kFoldReps = 8;          // 128-column chunks per block
 struct SliceJobs {
   float* ws[kMaxLayoutJobs];
   int64_t n[kMaxLayoutJobs];
-  int nslices[kMaxLayoutJobs], lanes[kMaxLayoutJobs];
+  int nslices[kMaxLayoutJobs];
   int blk0[kMaxLayoutJobs + 1];
   int count;
 };
+// Block = 8 warps; a chunk = 128 columns (one float4 per lane: 512 contiguous bytes per slice row and warp); warp w adds
+// slices w, w + 8, ... in fp64 (independent 16-byte loads in flight), the 8 warp sums are added in warp order.  Fixed
+// mapping -> deterministic.  n is a multiple of 4 and the workspace 16-byte aligned (checked by the caller).
 __global__ void __launch_bounds__(256) fold_slices_multi_kernel(const __grid_constant__ SliceJobs J) {
   GSB_PDL_ENTRY();
-  __shared__ double red[256];
+  __shared__ double red[8][128];
   const int j = find_job(J.blk0, J.count, blockIdx.x);
-  const int L = J.lanes[j], cols = 256 / L, ns = J.nslices[j];
-  const int c = threadIdx.x % cols, l = threadIdx.x / cols;
+  const int ns = J.nslices[j];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t n = J.n[j];
   float* ws = J.ws[j];
-  // kFoldReps column chunks per block: a block per chunk drowned in block-scheduling overhead (150 k blocks, 1.1 ms)
   for (int rep = 0; rep < kFoldReps; ++rep) {
-    const int64_t col = ((int64_t)(blockIdx.x - J.blk0[j]) * kFoldReps + rep) * cols + c;
-    double a = 0.0;
-    if (col < n)
-      for (int s = l; s < ns; s += L) a += (double)ws[(int64_t)s * n + col];
-    red[l * cols + c] = a;
+    const int64_t col0 = ((int64_t)(blockIdx.x - J.blk0[j]) * kFoldReps + rep) * 128;
+    if (col0 >= n) break;                                  // uniform over the block
+    const int64_t col = col0 + lane * 4;
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    if (col < n) {
+#pragma unroll 4
+      for (int s = w; s < ns; s += 8) {
+        const float4 v = *reinterpret_cast<const float4*>(ws + (int64_t)s * n + col);
+        a0 += (double)v.x; a1 += (double)v.y; a2 += (double)v.z; a3 += (double)v.w;
+      }
+    }
+    red[w][lane * 4 + 0] = a0; red[w][lane * 4 + 1] = a1; red[w][lane * 4 + 2] = a2; red[w][lane * 4 + 3] = a3;
     __syncthreads();
-    if (l == 0 && col < n) {
+    if (threadIdx.x < 128 && col0 + threadIdx.x < n) {
       double t = 0.0;
-      for (int i = 0; i < L; ++i) t += red[i * cols + c];
-      ws[col] = (float)t;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) t += red[i][threadIdx.x];
+      ws[col0 + threadIdx.x] = (float)t;
     }
     __syncthreads();
   }
@@ -582,16 +591,14 @@ static int run_layout_multi(bool pack, int n, const void* const* src, void* cons
       int blocks = 0;
       const int end = n - begin < kMaxLayoutJobs ? n : begin + kMaxLayoutJobs;
       for (int i = begin; i < end; ++i) {
-        if (nslices[i] <= 8 || i >= kMaxLayoutJobs * 4) continue;
-        int L = 1;
-        while (L < nslices[i] && L < 32) L <<= 1;
+        const int64_t ne = (int64_t)taps[i] * d0[i] * d1[i];
+        if (nslices[i] <= 4 || i >= kMaxLayoutJobs * 4 || (ne & 3) != 0 || ((uintptr_t)src[i] & 15) != 0) continue;
         const int k = S.count++;
         S.ws[k] = reinterpret_cast<float*>(const_cast<void*>(src[i]));
-        S.n[k] = (int64_t)taps[i] * d0[i] * d1[i];
+        S.n[k] = ne;
         S.nslices[k] = nslices[i];
-        S.lanes[k] = L;
         S.blk0[k] = blocks;
-        blocks += (int)((S.n[k] + (int64_t)(256 / L) * kFoldReps - 1) / ((int64_t)(256 / L) * kFoldReps));
+        blocks += (int)((ne + 128 * kFoldReps - 1) / (128 * kFoldReps));
         folded[i] = true;
       }
       S.blk0[S.count] = blocks;

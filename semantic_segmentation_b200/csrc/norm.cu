@@ -78,7 +78,7 @@ __device__ __forceinline__ uint32_t keep_bits(uint64_t seed, int64_t drop_offset
 // FAST = the U-Net layer shape (act1 = ReLU, no second branch, no dropout): the activation switches, the dropout
 // mask and the second gradient stream fold away at compile time (3-4x fewer instructions per 16-byte item; the
 // generic kernels are issue-bound, ncu profiles/r01b).
-template <typename T, int MODE, bool FAST>
+template <typename T, int MODE, bool FAST, bool PERIMG = false>
 __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
     PixView x, PixView dA1, PixView dA2, int64_t P, int C, const float* __restrict__ scale,
     const float* __restrict__ shift, const float* __restrict__ center, const float* __restrict__ mean,
@@ -100,9 +100,11 @@ __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(
   const int c0 = g * 8;
   // per-image statistics (InstanceNorm, gridDim.y = images): P = pixels of ONE image, this block row works on image
   // blockIdx.y, the per-channel parameter arrays are [images][C] and a partial row is [2][images * C]
-  const int img = blockIdx.y, NC = gridDim.y * C, poff = img * C;
+  // (PERIMG is a template parameter: the whole-batch kernels must not pay for the indexing -- an earlier run-time form cost
+  // the bf16 bn_act kernel 20 % of its bandwidth through a different load schedule)
+  const int img = PERIMG ? (int)blockIdx.y : 0, NC = PERIMG ? (int)gridDim.y * C : C, poff = img * C;
   const int64_t pbase = (int64_t)img * P;
-  if (img != 0) {
+  if (PERIMG && img != 0) {
     advance_view<T>(x, pbase);
     advance_view<T>(dA1, pbase);
     advance_view<T>(dA2, pbase);
@@ -314,7 +316,7 @@ __global__ void bn_finalize_kernel(const double* __restrict__ sums, double count
   if (invstd_out) invstd_out[c] = is;
 }
 
-template <typename T, bool FAST>
+template <typename T, bool FAST, bool PERIMG = false>
 __global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, int C, const float* __restrict__ scale,
                                                          const float* __restrict__ shift, const float* __restrict__ center,
                                                          int act1, PixView out1,
@@ -325,9 +327,9 @@ __global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, 
   const int lanes = kThreads / G;
   const int g = threadIdx.x % G, lane = threadIdx.x / G;
   const int c0 = g * 8;
-  const int poff = blockIdx.y * C;                   // per-image parameters (InstanceNorm): gridDim.y = images, P per image
-  const int64_t pbase = (int64_t)blockIdx.y * P;
-  if (blockIdx.y != 0) {
+  const int poff = PERIMG ? (int)blockIdx.y * C : 0;   // per-image parameters (InstanceNorm): gridDim.y = images, P per image
+  const int64_t pbase = PERIMG ? (int64_t)blockIdx.y * P : 0;
+  if (PERIMG && blockIdx.y != 0) {
     advance_view<T>(x, pbase);
     advance_view<T>(out1, pbase);
     advance_view<T>(out2, pbase);
@@ -364,7 +366,7 @@ __global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, 
   }
 }
 
-template <typename T, bool FAST>
+template <typename T, bool FAST, bool PERIMG = false>
 __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
     PixView x, PixView dA1, PixView dA2, int64_t P, int C, const float* __restrict__ scale,
     const float* __restrict__ shift, const float* __restrict__ center, const float* __restrict__ mean,
@@ -376,9 +378,9 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
   const int lanes = kThreads / G;
   const int g = threadIdx.x % G, lane = threadIdx.x / G;
   const int c0 = g * 8;
-  const int NC = gridDim.y * C, poff = blockIdx.y * C;   // per-image parameters / sums (InstanceNorm), P per image
-  const int64_t pbase = (int64_t)blockIdx.y * P;
-  if (blockIdx.y != 0) {
+  const int NC = PERIMG ? (int)gridDim.y * C : C, poff = PERIMG ? (int)blockIdx.y * C : 0;   // per-image parameters / sums
+  const int64_t pbase = PERIMG ? (int64_t)blockIdx.y * P : 0;
+  if (PERIMG && blockIdx.y != 0) {
     advance_view<T>(x, pbase);
     advance_view<T>(dA1, pbase);
     advance_view<T>(dA2, pbase);
@@ -631,14 +633,18 @@ extern "C" int gsb_bn_reduce(const gsb_view* x, int per_image, double* sums, voi
   size_t smem = (size_t)lanes * 2 * C * sizeof(float) * wide;
   float* partial = reinterpret_cast<float*>(workspace);
   PixView nul{nullptr, 0};
-  if (smem > 48 * 1024)
-    cudaFuncSetAttribute(bn_reduce_kernel<float, 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (x->dtype == GSB_BF16)
-    gsb::launch(bn_reduce_kernel<__nv_bfloat16, 0, false>, gsb::LaunchCfg(dim3(grid, nimg), kThreads, smem, to_stream(s)), pv(x), nul, nul, P, C, nullptr, nullptr, nullptr,
-                                                                                     nullptr, nullptr, 0, 0, 0, 0, nullptr, partial);
-  else
-    gsb::launch(bn_reduce_kernel<float, 0, false>, gsb::LaunchCfg(dim3(grid, nimg), kThreads, smem, to_stream(s)), pv(x), nul, nul, P, C, nullptr, nullptr, nullptr, nullptr,
-                                                                             nullptr, 0, 0, 0, 0, nullptr, partial);
+#define GSB_BN_REDUCE0(TT, PI)                                                                                              \
+  do {                                                                                                                      \
+    if (smem > 48 * 1024) cudaFuncSetAttribute(bn_reduce_kernel<TT, 0, false, PI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    gsb::launch(bn_reduce_kernel<TT, 0, false, PI>, gsb::LaunchCfg(dim3(grid, nimg), kThreads, smem, to_stream(s)), pv(x), nul, nul, P, C, \
+                nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0, 0, 0, nullptr, partial);                                  \
+  } while (0)
+  if (x->dtype == GSB_BF16) {
+    if (per_image) GSB_BN_REDUCE0(__nv_bfloat16, true); else GSB_BN_REDUCE0(__nv_bfloat16, false);
+  } else {
+    if (per_image) GSB_BN_REDUCE0(float, true); else GSB_BN_REDUCE0(float, false);
+  }
+#undef GSB_BN_REDUCE0
   int n = 2 * C * nimg;
   gsb::launch(reduce_partials_kernel, gsb::LaunchCfg((n + 31) / 32, 1024, 0, to_stream(s)), partial, grid * wide, n, sums);
   return check_launch("bn_reduce", 2);
@@ -683,9 +689,15 @@ extern "C" int gsb_bn_act(const gsb_view* x, const float* scale, const float* sh
     if (fast)
       gsb::launch(bn_act_kernel<__nv_bfloat16, true>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), P, C, scale, shift, center, act1, pv(out1), act2, o2,
                                                                               drop_seed, drop_offset, drop_mask);
+    else if (per_image)
+      gsb::launch(bn_act_kernel<__nv_bfloat16, false, true>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), P, C, scale, shift, center, act1,
+                  pv(out1), act2, o2, drop_seed, drop_offset, drop_mask);
     else
       gsb::launch(bn_act_kernel<__nv_bfloat16, false>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), P, C, scale, shift, center, act1, pv(out1), act2,
                                                                                o2, drop_seed, drop_offset, drop_mask);
+  } else if (per_image) {
+    gsb::launch(bn_act_kernel<float, false, true>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), P, C, scale, shift, center, act1, pv(out1),
+                act2, o2, drop_seed, drop_offset, drop_mask);
   } else {
     gsb::launch(bn_act_kernel<float, false>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), P, C, scale, shift, center, act1, pv(out1), act2, o2,
                                                                      drop_seed, drop_offset, drop_mask);
@@ -717,8 +729,10 @@ static int bn_bwd_partial_launch(const gsb_view* x, const gsb_view* dA1, const g
   const int wide = x->dtype == GSB_BF16 ? 1 : 2;
   GSB_REQUIRE(workspace_bytes >= (size_t)gx * wide * 2 * C * nimg * sizeof(float), "bn_bwd_reduce: workspace too small");
   size_t smem = (size_t)lanes * 2 * C * sizeof(float) * wide;
-  if (smem > 48 * 1024)
+  if (smem > 48 * 1024) {
     cudaFuncSetAttribute(bn_reduce_kernel<float, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(bn_reduce_kernel<float, 1, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  }
   float* partial = reinterpret_cast<float*>(workspace);
   PixView d2 = (dA2 && dA2->ptr) ? pv(dA2) : PixView{nullptr, 0};
   const bool fast = act1 == GSB_ACT_RELU && d2.ptr == nullptr && drop_seed == 0 && drop_mask == nullptr && scale && shift &&
@@ -730,9 +744,15 @@ static int bn_bwd_partial_launch(const gsb_view* x, const gsb_view* dA1, const g
     else if (fast)
       gsb::launch(bn_reduce_kernel<__nv_bfloat16, 1, true>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), 
           pv(x), pv(dA1), d2, P, C, scale, shift, center, mean, invstd, act1, act2, drop_seed, drop_offset, drop_mask, partial);
+    else if (per_image)
+      gsb::launch(bn_reduce_kernel<__nv_bfloat16, 1, false, true>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), 
+          pv(x), pv(dA1), d2, P, C, scale, shift, center, mean, invstd, act1, act2, drop_seed, drop_offset, drop_mask, partial);
     else
       gsb::launch(bn_reduce_kernel<__nv_bfloat16, 1, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), 
           pv(x), pv(dA1), d2, P, C, scale, shift, center, mean, invstd, act1, act2, drop_seed, drop_offset, drop_mask, partial);
+  } else if (per_image) {
+    gsb::launch(bn_reduce_kernel<float, 1, false, true>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), pv(dA1), d2, P, C, scale, shift, center, mean,
+                invstd, act1, act2, drop_seed, drop_offset, drop_mask, partial);
   } else {
     gsb::launch(bn_reduce_kernel<float, 1, false>, gsb::LaunchCfg(grid, kThreads, smem, to_stream(s)), pv(x), pv(dA1), d2, P, C, scale, shift, center, mean,
                                                                              invstd, act1, act2, drop_seed, drop_offset, drop_mask, partial);
@@ -829,9 +849,15 @@ extern "C" int gsb_bn_bwd_apply(const gsb_view* x, const gsb_view* dA1, const gs
     if (fast)
       gsb::launch(bn_bwd_apply_kernel<__nv_bfloat16, true>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), 
           pv(x), pv(dA1), d2, P, C, scale, shift, center, mean, invstd, act1, act2, drop_seed, drop_offset, drop_mask, sums, inv, pv(dx));
+    else if (per_image)
+      gsb::launch(bn_bwd_apply_kernel<__nv_bfloat16, false, true>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), 
+          pv(x), pv(dA1), d2, P, C, scale, shift, center, mean, invstd, act1, act2, drop_seed, drop_offset, drop_mask, sums, inv, pv(dx));
     else
       gsb::launch(bn_bwd_apply_kernel<__nv_bfloat16, false>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), 
           pv(x), pv(dA1), d2, P, C, scale, shift, center, mean, invstd, act1, act2, drop_seed, drop_offset, drop_mask, sums, inv, pv(dx));
+  } else if (per_image) {
+    gsb::launch(bn_bwd_apply_kernel<float, false, true>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), pv(dA1), d2, P, C, scale, shift, center, mean,
+                invstd, act1, act2, drop_seed, drop_offset, drop_mask, sums, inv, pv(dx));
   } else {
     gsb::launch(bn_bwd_apply_kernel<float, false>, gsb::LaunchCfg(grid, kThreads, 0, to_stream(s)), pv(x), pv(dA1), d2, P, C, scale, shift, center, mean, invstd,
                                                                            act1, act2, drop_seed, drop_offset, drop_mask, sums, inv, pv(dx));

@@ -136,11 +136,13 @@ __global__ void __launch_bounds__(128) stem_tc_fwd_kernel(const float* __restric
   uint32_t phase = 0;
   const int cp = tid & 31, rg = tid >> 5;     // statistics: channel pair (2 cp, 2 cp + 1), rows [32 rg, 32 rg + 32)
   float2 s0 = make_float2(0.f, 0.f), s1 = make_float2(0.f, 0.f);
+  // software pipeline: the input values of the NEXT tile are gathered (global loads in flight) while the tensor core, the
+  // epilogue and the statistics pass work on the current one -- the serial chain gather -> MMA -> store per tile was the limit
+  float v[T];
+  int64_t p = (int64_t)blockIdx.x * 128 + tid;
+  bool valid = p < P;
+  if ((int)blockIdx.x < num_tiles) gather_taps<T, K, S>(x, H, W, OH, OW, pad, p, valid, v);
   for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-    const int64_t p = (int64_t)tile * 128 + tid;
-    const bool valid = p < P;
-    float v[T];
-    gather_taps<T, K, S>(x, H, W, OH, OW, pad, p, valid, v);
     write_split_row<T, 3, NCH>(sA, tid, v);
     fence_proxy_async();            // generic-proxy writes -> visible to the tensor core's async-proxy reads
     tc_fence_before();
@@ -151,6 +153,9 @@ __global__ void __launch_bounds__(128) stem_tc_fwd_kernel(const float* __restric
       for (int ks = 0; ks < KS; ++ks) umma_bf16(tmem_base, adesc + 2 * ks, bdesc + 2 * ks, idesc, ks > 0 ? 1u : 0u);
       umma_commit(bar);
     }
+    const int64_t p_next = (int64_t)(tile + gridDim.x) * 128 + tid;
+    const bool valid_next = p_next < P;
+    if (tile + (int)gridDim.x < num_tiles) gather_taps<T, K, S>(x, H, W, OH, OW, pad, p_next, valid_next, v);
     mbar_wait(bar, phase);
     phase ^= 1u;
     tc_fence_after();
@@ -193,6 +198,8 @@ __global__ void __launch_bounds__(128) stem_tc_fwd_kernel(const float* __restric
     }
     tc_fence_before();
     __syncthreads();                // accumulator and staging tile are free for the next tile
+    p = p_next;
+    valid = valid_next;
   }
   if (stats != nullptr) {
     red[(rg * 2 + 0) * 64 + 2 * cp] = s0.x;

@@ -119,17 +119,21 @@ def test_conv_tcgen05_bf16(geom):
 TILE_GEOMS = [("conv", 3, 1, 1, 128, 256, 3, 40, 24), ("conv", 4, 2, 1, 64, 128, 2, 32, 64), ("convT", 4, 2, 1, 128, 256, 1, 16, 24)]
 
 
+@pytest.mark.parametrize("pair", ["0", "2"])
 @pytest.mark.parametrize("tile", ["256,2", "256,1", "128,2", "128,1", "64,2", "64,1"])
 @pytest.mark.parametrize("geom", TILE_GEOMS, ids=[f"{g[0]}k{g[1]}s{g[2]}_{g[4]}to{g[5]}_{g[7]}x{g[8]}" for g in TILE_GEOMS])
-def test_conv_tcgen05_tile_shapes(geom, tile):
+def test_conv_tcgen05_tile_shapes(geom, tile, pair):
     """Every (BN output channels, mt M-tiles) shape of the halo kernel on the same problem (the cost model would
-    pick only one of them): 16- and 8-pixel-wide tiles, partial tiles in x and y, odd tile counts (ghost cluster tile)."""
+    pick only one of them): 16- and 8-pixel-wide tiles, partial tiles in x and y, odd tile counts (ghost cluster tile);
+    each with one-CTA MMAs (GSB_TC_PAIR=0) and with the CTA-pair form (tcgen05 cta_group::2, M = 256) for every width."""
     import os
     os.environ["GSB_TC_TILE"] = tile
+    os.environ["GSB_TC_PAIR"] = pair
     try:
         res = conv_case(*geom, dtype=torch.bfloat16, use_tc=1, seed=3)
     finally:
         del os.environ["GSB_TC_TILE"]
+        del os.environ["GSB_TC_PAIR"]
     assert res["fwd"] < 6e-3 and res["dgrad"] < 6e-3 and res["wgrad"] < 1e-4, res
     if "stats" in res:
         assert res["stats"] < 1e-5, res
