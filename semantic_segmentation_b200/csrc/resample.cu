@@ -119,7 +119,7 @@ struct Lerp {
 // guard_index_and_lambda), all in fp32.
 __device__ __forceinline__ Lerp lerp_for(int o, int in, int out) {
   float scale = out > 1 ? (float)(in - 1) / (float)(out - 1) : 0.f;
-  float real = scale * (float)o;
+  float real = __fmul_rn(scale, (float)o);  // rounded product as ATen's CPU path (no contraction into the subtraction below)
   int i0 = (int)real;
   if (i0 > in - 1) i0 = in - 1;
   float l1 = real - (float)i0;
@@ -466,6 +466,226 @@ __global__ void __launch_bounds__(256) upsample2_bwd_win_kernel(const T* __restr
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Block form of the align_corners x2 lerp (un-padded case OH = 2h, OW = 2w, the one every even-sized level takes).
+// With scale = (in-1)/(2in-1) < 1/2 the source of output u = 2b+1 lies in [b, b+1/2) and that of u = 2b+2 in
+// (b+1/2, b+1): both outputs of block b = (u+1)/2 - 1 interpolate between the SAME two inputs b and b+1 (clamped to
+// the tensor at b = -1 and b = in-1, where only one of the two outputs exists).  So a 2x2 output block reads one 2x2
+// input block: 4 loads for 4 outputs (the row kernels above issue 4 loads per output and sit at ~0.4 of the HBM
+// roofline, issue / L1 bound), and the transpose is separable with a 4-tap window: input i receives from outputs
+// 2i-1 .. 2i+2.  The weight on the upper tap is clamp(scale*u - b, 0, 1), which equals lerp_for's l1 whenever
+// (int)(scale*u) == b; when fp32 rounding puts scale*u an ulp across an integer (only possible at u = 2in-1) the
+// result differs from lerp_for's by <= ulp * |x[b+1] - x[b]|.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float up_blk_w1(int u, int in) {
+  const float scale = (float)(in - 1) / (float)(2 * in - 1);
+  const int b = ((u + 1) >> 1) - 1;
+  return fminf(fmaxf(__fmul_rn(scale, (float)u) - (float)b, 0.f), 1.f);  // rounded product, as lerp_for / ATen
+}
+// weight with which output u feeds input i (the transpose of the above); 0 outside the tensor
+__device__ __forceinline__ float up_blk_wgt(int u, int i, int in) {
+  if (u < 0 || u >= 2 * in) return 0.f;
+  const int b = ((u + 1) >> 1) - 1;
+  const float w1 = up_blk_w1(u, in), w0 = 1.f - w1;
+  const int ia = max(b, 0), ib = min(b + 1, in - 1);
+  return (ia == i ? w0 : 0.f) + (ib == i ? w1 : 0.f);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) upsample2_fwd_blk_kernel(const T* __restrict__ x, int64_t xld, int N, int h, int w, int C,
+                                                               T* __restrict__ out, int64_t old) {
+  GSB_PDL_ENTRY();
+  // one flat grid-stride loop over (image, row block, column block, channel group): no per-row tail (a row of the
+  // production shape has 129 * 8 = 1032 items, 4.03 per thread of a row-owning block)
+  __shared__ float s_wx[kMaxUpW];
+  for (int v = threadIdx.x; v < 2 * w; v += blockDim.x) s_wx[v] = up_blk_w1(v, w);
+  __syncthreads();
+  const unsigned G = (unsigned)C >> 3, per_row = (unsigned)(w + 1) * G;
+  const unsigned H1 = (unsigned)h + 1;
+  const int OW = 2 * w;
+  const uint64_t total = (uint64_t)N * H1 * per_row;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
+    unsigned rb, it;
+    if ((i >> 32) == 0) {
+      rb = (unsigned)i / per_row;
+      it = (unsigned)i - rb * per_row;
+    } else {
+      rb = (unsigned)(i / per_row);
+      it = (unsigned)(i - (uint64_t)rb * per_row);
+    }
+    const unsigned n = rb / H1;
+    const int bi = (int)(rb - n * H1) - 1;
+    const int u0 = 2 * bi + 1, u1 = u0 + 1;
+    const bool hasr0 = bi >= 0, hasr1 = bi < h - 1;
+    const float wy0 = hasr0 ? up_blk_w1(u0, h) : 0.f, wy1 = hasr1 ? up_blk_w1(u1, h) : 0.f;
+    const T* r0 = x + ((int64_t)n * h + max(bi, 0)) * w * xld;
+    const T* r1 = x + ((int64_t)n * h + min(bi + 1, h - 1)) * w * xld;
+    T* o0 = out + ((int64_t)n * 2 * h + u0) * OW * old;
+    T* o1 = o0 + (int64_t)OW * old;
+    const float2 y00 = make_float2(1.f - wy0, 1.f - wy0), y01 = make_float2(wy0, wy0);
+    const float2 y10 = make_float2(1.f - wy1, 1.f - wy1), y11 = make_float2(wy1, wy1);
+    const unsigned bjp = it / G, g = it - bjp * G;
+    const int bj = (int)bjp - 1;
+    const int ca = max(bj, 0), cb = min(bj + 1, w - 1);
+    const int v0 = 2 * bj + 1, v1 = v0 + 1;
+    const bool hasc0 = bj >= 0, hasc1 = bj < w - 1;
+    float v00[8], v01[8], v10[8], v11[8];
+    Vec8<T>::load(r0 + (int64_t)ca * xld + g * 8, v00);
+    Vec8<T>::load(r0 + (int64_t)cb * xld + g * 8, v01);
+    Vec8<T>::load(r1 + (int64_t)ca * xld + g * 8, v10);
+    Vec8<T>::load(r1 + (int64_t)cb * xld + g * 8, v11);
+    const float wx0 = s_wx[hasc0 ? v0 : 0], wx1 = s_wx[hasc1 ? v1 : 0];
+    const float2 a00 = make_float2(1.f - wx0, 1.f - wx0), a01 = make_float2(wx0, wx0);
+    const float2 a10 = make_float2(1.f - wx1, 1.f - wx1), a11 = make_float2(wx1, wx1);
+    float o00[8], o01[8], o10[8], o11[8];  // [row][col]
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 p00 = make_float2(v00[2 * k], v00[2 * k + 1]), p01 = make_float2(v01[2 * k], v01[2 * k + 1]);
+      const float2 p10 = make_float2(v10[2 * k], v10[2 * k + 1]), p11 = make_float2(v11[2 * k], v11[2 * k + 1]);
+      // same association as the row kernel: ly0 * (lx0 * v00 + lx1 * v01) + ly1 * (lx0 * v10 + lx1 * v11)
+      const float2 top0 = __ffma2_rn(a01, p01, __fmul2_rn(a00, p00)), bot0 = __ffma2_rn(a01, p11, __fmul2_rn(a00, p10));
+      const float2 top1 = __ffma2_rn(a11, p01, __fmul2_rn(a10, p00)), bot1 = __ffma2_rn(a11, p11, __fmul2_rn(a10, p10));
+      const float2 q00 = __ffma2_rn(y01, bot0, __fmul2_rn(y00, top0)), q01 = __ffma2_rn(y01, bot1, __fmul2_rn(y00, top1));
+      const float2 q10 = __ffma2_rn(y11, bot0, __fmul2_rn(y10, top0)), q11 = __ffma2_rn(y11, bot1, __fmul2_rn(y10, top1));
+      o00[2 * k] = q00.x; o00[2 * k + 1] = q00.y;
+      o01[2 * k] = q01.x; o01[2 * k + 1] = q01.y;
+      o10[2 * k] = q10.x; o10[2 * k + 1] = q10.y;
+      o11[2 * k] = q11.x; o11[2 * k + 1] = q11.y;
+    }
+    if (hasr0) {
+      if (hasc0) Vec8<T>::store(o0 + (int64_t)v0 * old + g * 8, o00);
+      if (hasc1) Vec8<T>::store(o0 + (int64_t)v1 * old + g * 8, o01);
+    }
+    if (hasr1) {
+      if (hasc0) Vec8<T>::store(o1 + (int64_t)v0 * old + g * 8, o10);
+      if (hasc1) Vec8<T>::store(o1 + (int64_t)v1 * old + g * 8, o11);
+    }
+  }
+}
+// Backward, separable: a block owns one input row and a run of JC input columns.  Phase 1 folds the (<= 4) contributing
+// output rows into one fp32 row tile in shared memory (4 coalesced 16-byte loads per output column and channel group),
+// phase 2 folds the 4 contributing columns of that tile per input column: 8 global loads per dx vector where the window
+// kernel issues 20.  Tile layout [column][half][group][4 floats] so that both phases move 16-byte words conflict-free.
+template <typename T> struct RawVec8;
+template <> struct RawVec8<__nv_bfloat16> {
+  using type = uint4;
+  static __device__ __forceinline__ uint4 load(const __nv_bfloat16* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+  static __device__ __forceinline__ void unpack(const uint4& r, float (&v)[8]) {
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[2 * i] = __uint_as_float(w[i] << 16);
+      v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
+};
+template <> struct RawVec8<float> {
+  struct type { float4 a, b; };
+  static __device__ __forceinline__ type load(const float* p) {
+    type t;
+    t.a = __ldg(reinterpret_cast<const float4*>(p));
+    t.b = __ldg(reinterpret_cast<const float4*>(p + 4));
+    return t;
+  }
+  static __device__ __forceinline__ void unpack(const type& r, float (&v)[8]) {
+    v[0] = r.a.x; v[1] = r.a.y; v[2] = r.a.z; v[3] = r.a.w;
+    v[4] = r.b.x; v[5] = r.b.y; v[6] = r.b.z; v[7] = r.b.w;
+  }
+};
+constexpr int kSepMaxJC = 512;
+template <typename T>
+__global__ void __launch_bounds__(256) upsample2_bwd_sep_kernel(const T* __restrict__ dout, int64_t dld, int N, int C,
+                                                               T* __restrict__ dx, int64_t xld, int h, int w, int JC) {
+  GSB_PDL_ENTRY();
+  extern __shared__ __align__(16) float s_t[];
+  __shared__ float s_cw[kSepMaxJC][4];
+  const int j0 = blockIdx.y * JC, jn = min(JC, w - j0);
+  const int vbase = 2 * j0 - 1, ncol = 2 * jn + 2, OW = 2 * w;
+  for (int i = threadIdx.x; i < jn * 4; i += blockDim.x) {
+    const int ix = i >> 2, k = i & 3;
+    s_cw[ix][k] = up_blk_wgt(2 * (j0 + ix) - 1 + k, j0 + ix, w);
+  }
+  const unsigned G = (unsigned)C >> 3, items1 = (unsigned)ncol * G, items2 = (unsigned)jn * G;
+  const int halfC = C >> 1;
+  for (int row = blockIdx.x; row < N * h; row += gridDim.x) {
+    const int n = row / h, iy = row - n * h;
+    float wy[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) wy[r] = up_blk_wgt(2 * iy - 1 + r, iy, h);
+    const T* base = dout + ((int64_t)n * 2 * h + (2 * iy - 1)) * OW * dld;
+    const int64_t rstride = (int64_t)OW * dld;
+    __syncthreads();  // the previous row's phase 2 (and the weight table) is done
+    // batches of U items per thread: the 4U row loads of a batch are independent and issued together (one memory round
+    // trip per batch; one item at a time left the block latency-bound: 5 dependent round trips per row at 1040 items)
+    constexpr int U = sizeof(T) == 2 ? 5 : 2;
+    using Raw = typename RawVec8<T>::type;
+    for (unsigned b0 = 0; b0 < items1; b0 += 256 * U) {
+      Raw raw[U][4];
+      bool ok[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const unsigned it = b0 + u * 256 + threadIdx.x;
+        const unsigned c = it / G, g = it - c * G;
+        const int v = vbase + (int)c;
+        ok[u] = it < items1 && v >= 0 && v < OW;
+        const T* p = base + (int64_t)(ok[u] ? v : 0) * dld + g * 8;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          // rows outside the tensor (block-uniform test) weigh 0: they are read from the nearest row inside it
+          const int rr = min(max(r, iy == 0 ? 1 : 0), iy == h - 1 ? 2 : 3);
+          if (ok[u]) raw[u][r] = RawVec8<T>::load(p + rr * rstride);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const unsigned it = b0 + u * 256 + threadIdx.x;
+        if (it >= items1) continue;
+        const unsigned c = it / G, g = it - c * G;
+        float2 acc[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) acc[k] = make_float2(0.f, 0.f);
+        if (ok[u]) {
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            float t[8];
+            RawVec8<T>::unpack(raw[u][r], t);
+            const float2 w2 = make_float2(wy[r], wy[r]);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) acc[k] = __ffma2_rn(w2, make_float2(t[2 * k], t[2 * k + 1]), acc[k]);
+          }
+        }
+        float* d = s_t + (size_t)c * C + g * 4;
+        *reinterpret_cast<float4*>(d) = make_float4(acc[0].x, acc[0].y, acc[1].x, acc[1].y);
+        *reinterpret_cast<float4*>(d + halfC) = make_float4(acc[2].x, acc[2].y, acc[3].x, acc[3].y);
+      }
+    }
+    __syncthreads();
+    for (unsigned it = threadIdx.x; it < items2; it += blockDim.x) {
+      const unsigned ix = it / G, g = it - ix * G;
+      float2 acc[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) acc[k] = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float* sp = s_t + (size_t)(2 * ix + k) * C + g * 4;
+        const float4 lo = *reinterpret_cast<const float4*>(sp), hi = *reinterpret_cast<const float4*>(sp + halfC);
+        const float cw = s_cw[ix][k];
+        const float2 w2 = make_float2(cw, cw);
+        acc[0] = __ffma2_rn(w2, make_float2(lo.x, lo.y), acc[0]);
+        acc[1] = __ffma2_rn(w2, make_float2(lo.z, lo.w), acc[1]);
+        acc[2] = __ffma2_rn(w2, make_float2(hi.x, hi.y), acc[2]);
+        acc[3] = __ffma2_rn(w2, make_float2(hi.z, hi.w), acc[3]);
+      }
+      float o[8];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        o[2 * k] = acc[k].x;
+        o[2 * k + 1] = acc[k].y;
+      }
+      Vec8<T>::store(dx + ((int64_t)row * w + j0 + ix) * xld + g * 8, o);
+    }
+  }
+}
 static int ew_grid(int64_t total) {
   int64_t b = (total + 255) / 256;
   int64_t cap = (int64_t)num_sms() * 16;
@@ -520,6 +740,14 @@ extern "C" int gsb_upsample2_fwd(const gsb_view* x, const gsb_view* out, int pad
   GSB_REQUIRE(out->n == x->n && out->c == x->c && out->dtype == x->dtype, "upsample2_fwd: mismatch");
   int64_t total = num_pixels(out) * (x->c / 8);
   if (total == 0) return 0;
+  static const bool blk = []() { const char* e = getenv("GSB_UP_BLK"); return !(e && e[0] == '0'); }();
+  if (blk && pad_top == 0 && pad_left == 0 && out->h == 2 * x->h && out->w == 2 * x->w && 2 * x->w <= kMaxUpW &&
+      (int64_t)x->n * (x->h + 1) < ((int64_t)1 << 30)) {
+    const int grid = ew_grid((int64_t)x->n * (x->h + 1) * (x->w + 1) * (x->c / 8));
+    DISPATCH_T(x->dtype, gsb::launch(upsample2_fwd_blk_kernel<T>, gsb::LaunchCfg(grid, 256, 0, to_stream(s)),
+                             (const T*)x->ptr, x->sw, x->n, x->h, x->w, x->c, (T*)out->ptr, out->sw));
+    return check_launch("upsample2_fwd");
+  }
   if (2 * x->w <= kMaxUpW && (int64_t)out->n * out->h < ((int64_t)1 << 30)) {
     const int rows = out->n * out->h;
     const int grid = rows < num_sms() * 16 ? rows : num_sms() * 16;
@@ -539,6 +767,23 @@ extern "C" int gsb_upsample2_bwd(const gsb_view* dout, const gsb_view* dx, int p
   GSB_REQUIRE(dout->n == dx->n && dout->c == dx->c && dout->dtype == dx->dtype, "upsample2_bwd: mismatch");
   int64_t total = num_pixels(dx) * (dx->c / 8);
   if (total == 0) return 0;
+  static const bool blk = []() { const char* e = getenv("GSB_UP_BLK"); return !(e && e[0] == '0'); }();
+  if (blk && pad_top == 0 && pad_left == 0 && dout->h == 2 * dx->h && dout->w == 2 * dx->w && dx->c <= 1024 &&
+      (int64_t)dx->n * dx->h < ((int64_t)1 << 30)) {
+    int jc = 4096 / dx->c;
+    if (jc < 1) jc = 1;
+    if (jc > dx->w) jc = dx->w;
+    if (jc > kSepMaxJC) jc = kSepMaxJC;
+    const int chunks = (dx->w + jc - 1) / jc;
+    const int rows = dx->n * dx->h;
+    int gx = num_sms() * 16 / chunks;
+    if (gx < 1) gx = 1;
+    if (gx > rows) gx = rows;
+    const size_t smem = (size_t)(2 * jc + 2) * dx->c * sizeof(float);
+    DISPATCH_T(dx->dtype, gsb::launch(upsample2_bwd_sep_kernel<T>, gsb::LaunchCfg(dim3(gx, chunks), 256, smem, to_stream(s)),
+                              (const T*)dout->ptr, dout->sw, dout->n, dout->c, (T*)dx->ptr, dx->sw, dx->h, dx->w, jc));
+    return check_launch("upsample2_bwd");
+  }
   if (2 * dx->w <= kMaxUpW && (int64_t)dx->n * dx->h < ((int64_t)1 << 30)) {
     const int rows = dx->n * dx->h;
     const int grid = rows < num_sms() * 16 ? rows : num_sms() * 16;

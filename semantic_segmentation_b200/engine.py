@@ -175,13 +175,62 @@ class WeightPacks:
         return self.map.get(key, (None, None))
 
 
+_SIDE_STREAMS: Dict[int, "torch.cuda.Stream"] = {}
+
+
+def wgrad_stream_enabled() -> bool:
+    """Weight-gradient kernels on a second stream (``GSB_WGRAD_STREAM=1``): see BackwardBatch.side."""
+    import os
+    return os.environ.get("GSB_WGRAD_STREAM", "0") != "0"
+
+
+def _side_stream(device) -> "torch.cuda.Stream":
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    st = _SIDE_STREAMS.get(idx)
+    if st is None:
+        st = _SIDE_STREAMS[idx] = torch.cuda.Stream(device=idx)
+    return st
+
+
+class _OnSide:
+    """with batch.on_side(keep): the body's launches go to the batch's side stream, ordered after everything the main
+    stream has been given so far; ``keep`` (the tensors the body reads) stays referenced until the next join, so the
+    caching allocator cannot hand their memory to a later main-stream allocation while the side stream still reads it."""
+
+    def __init__(self, batch: "BackwardBatch", keep):
+        self.batch, self.keep, self.ctx = batch, keep, None
+
+    def __enter__(self):
+        b = self.batch
+        b.keep.append(self.keep)
+        ev = torch.cuda.Event()
+        ev.record()
+        b.side.wait_event(ev)
+        self.ctx = torch.cuda.stream(b.side)
+        self.ctx.__enter__()
+        b.forked = True
+        return b.side
+
+    def __exit__(self, *exc):
+        return self.ctx.__exit__(*exc)
+
+
 class BackwardBatch:
     """Weight gradients of one backward pass: every layer's tensor-core weight gradient arrives as partial-sum slices
     (``ops.conv_wgrad_slices``: plain stores, no atomics), is un-packed -- slices added in slice order -- by ONE batched
     launch per flush into ONE flat gradient buffer laid out in backward order, so that a prefix of that buffer can be
-    handed to the gradient all-reduce while the rest of the backward pass is still running."""
+    handed to the gradient all-reduce while the rest of the backward pass is still running.
+
+    ``side`` (``GSB_WGRAD_STREAM=1``, experimental): the weight-gradient kernels of a layer depend on dY only and nothing
+    on the backward chain depends on them before the un-pack; they can be launched on a second stream (fork after the
+    data gradient of the layer, join in ``flush``), so that the tensor-bound weight gradient of layer L runs under the
+    HBM-bound BatchNorm / pooling / upsampling backward kernels of layer L-1 (fork / join are events: graph capture
+    records them as dependencies)."""
 
     def __init__(self, device, sizes: Dict[str, int]):
+        self.side = _side_stream(device) if (wgrad_stream_enabled() and device.type == "cuda") else None
+        self.keep: List[object] = []
+        self.forked = False
         total = sum(sizes.values())
         self.gflat = torch.empty(max(total, 1), device=device, dtype=torch.float32)
         self.sizes = dict(sizes)
@@ -206,9 +255,22 @@ class BackwardBatch:
         self.jobs.append((ws, rows_from_d0, out, int(nslices)))
         return out
 
+    def on_side(self, keep) -> _OnSide:
+        return _OnSide(self, keep)
+
+    def join(self) -> None:
+        """The current stream waits for the side stream's work; the kept inputs may be released after that."""
+        if self.forked:
+            ev = torch.cuda.Event()
+            ev.record(self.side)
+            torch.cuda.current_stream().wait_event(ev)
+            self.forked = False
+        self.keep = []
+
     def flush(self) -> Tuple[int, int]:
         """Un-pack what has been deferred so far; returns the [start, end) range of the flat gradient buffer that became
         final with this flush."""
+        self.join()
         if self.jobs:
             ops.unpack_wgrad_multi(self.jobs)
             self.jobs = []
@@ -457,8 +519,11 @@ class ConvBNAct:
                              None, None, sv.drop_seed, sv.drop_mask, center=sv.center, drop_offset=sv.drop_offset)
         dyv = view_nhwc(dY)
         dweight = dbias = None
+        side_wgrad = False
         if need_dw and sv.extra.get("stem"):
             dweight = ops.stem_conv_wgrad(sv.x_keep, dY, s.k, s.stride, s.pad)
+        elif need_dw and batch is not None and batch.side is not None and key is not None and key in batch.sizes:
+            side_wgrad = True                   # launched AFTER the data gradient, on the side stream (below)
         elif need_dw:
             dweight = conv_weight_grad(s, sv.x_view, dyv, device, _CONFIG["use_tc"], batch, key)
         if need_db:
@@ -476,6 +541,11 @@ class ConvBNAct:
                 dx_view = view_nhwc(dx_out)
             ops.conv_gather(dyv, wpb, None, dx_view, s.bwd_mode, s.k, s.stride, s.pad, use_tc=_CONFIG["use_tc"])
             dx = dx_out
+        if side_wgrad:
+            # fork AFTER the data gradient: queued behind it, the weight gradient starts when the data gradient's CTAs
+            # drain and runs under the HBM-bound BatchNorm / pooling / upsampling backward kernels of the next layer
+            with batch.on_side((dY, sv)):
+                dweight = conv_weight_grad(s, sv.x_view, dyv, device, _CONFIG["use_tc"], batch, key)
         return dx, dweight, dbias, dgamma, dbeta
 
 

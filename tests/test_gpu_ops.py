@@ -325,6 +325,35 @@ def test_upsample_into_concat_slice(hw, out_hw):
     assert rel(from_nhwc(dxd), xr.grad) < 1e-5
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(2, 64, 128, 128), (3, 512, 16, 16), (2, 8, 7, 300), (1, 64, 1, 1), (2, 128, 2, 3)])
+def test_upsample_block_kernels(shape, dtype):
+    """The 2x2-block forward and the separable backward (un-padded x2 case) against torch, at the production shapes
+    (unet_parts.py:50: Upsample(scale_factor=2, 'bilinear', align_corners=True)) and at ragged / degenerate ones."""
+    g = torch.Generator().manual_seed(21)
+    n, c, h, w = shape
+    x = torch.randn(n, c, h, w, generator=g)
+    if dtype == torch.bfloat16:
+        x = x.bfloat16().float()
+    xr = x.clone().requires_grad_(True)
+    up = F.interpolate(xr, scale_factor=2, mode="bilinear", align_corners=True)
+    dref = torch.randn(up.shape, generator=g)
+    if dtype == torch.bfloat16:
+        dref = dref.bfloat16().float()
+    up.backward(dref)
+    xd = nhwc(x, dtype)
+    out = torch.full((n, 2 * h, 2 * w, c), 5.0, device=DEV, dtype=dtype)
+    ops.upsample2_fwd(xd, out, 0, 0)
+    tol = 1e-6 if dtype == torch.float32 else 3e-3
+    assert rel(from_nhwc(out).float(), up.detach()) < tol
+    dxd = torch.full_like(xd, 9.0)
+    ops.upsample2_bwd(nhwc(dref, dtype), dxd, 0, 0)
+    assert rel(from_nhwc(dxd).float(), xr.grad) < (2e-6 if dtype == torch.float32 else 3e-3)
+    # element-wise: no output of the block form is more than a rounding away from torch's
+    err = (from_nhwc(out).float() - up.detach()).abs().max().item()
+    assert err <= (1e-5 if dtype == torch.float32 else 2.0 ** -8 * up.abs().max().item())
+
+
 def test_merge_unmerge_upconv():
     from oracle import genseg_oracle as O
     g = torch.Generator().manual_seed(5)
