@@ -223,6 +223,16 @@ int gsb_eval_counts(const float* logits, const int64_t* labels, int n, int c, in
  * workspace: fp64 partial rows [rows][slices][3], rows <= 1024 (one per CTA column), added in row order. */
 int gsb_dice_sums(const float* a, const float* b, int64_t slices, int64_t inner, double* sums, void* workspace,
                   size_t workspace_bytes, gsb_stream s);
+/* gsb_dice_sums without a caller workspace and without any allocation (no cudaMalloc / cudaFree / allocating library
+ * call, so it may be called where allocation is forbidden).  It has NO counterpart in the reference.
+ * The partial rows live in a 96 KiB file-scope `static __device__` array that every
+ * GPU loading the library holds until exit (its device address is resolved once per device with cudaGetSymbolAddress).
+ * Limit: slices <= gsb_dice_sums_noalloc_max_slices() (= 64); more is rejected with an error (use gsb_dice_sums).
+ * Same result as gsb_dice_sums given the same number of partial rows (rows = min(ceil(inner/4096), 1024,
+ * 12288 / (3*slices))).  Every call shares the array and it keeps the previous call's contents (nothing needs
+ * clearing: each launch stores every row it later reads); calls that OVERLAP on the GPU (different streams) race. */
+int gsb_dice_sums_noalloc(const float* a, const float* b, int64_t slices, int64_t inner, double* sums, gsb_stream s);
+size_t gsb_dice_sums_noalloc_max_slices(void);
 
 /* ---- GAN / L1 losses -- networks.py:263-281, pix2pix_model.py:73,127 -------------------- */
 /* mode 0 vanilla (BCE-with-logits vs constant label), 1 lsgan (MSE), 2 wgangp (+-mean).

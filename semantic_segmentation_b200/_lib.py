@@ -81,6 +81,8 @@ SIGNATURES = {
     "gsb_seg_loss_bwd": (_i, [_p, _p, _i, _i, _i, _i, _p, _d, _p, _p, _p]),
     "gsb_eval_counts": (_i, [_p, _p, _i, _i, _i, _i, _p, _p, _p]),
     "gsb_dice_sums": (_i, [_p, _p, _i64, _i64, _p, _p, _sz, _p]),
+    "gsb_dice_sums_noalloc": (_i, [_p, _p, _i64, _i64, _p, _p]),
+    "gsb_dice_sums_noalloc_max_slices": (_sz, []),
     "gsb_gan_loss": (_i, [_p, _i64, _i, _f, _p, _p, _p, _p, _sz, _p]),
     "gsb_l1_loss": (_i, [_p, _p, _i64, _p, _p, _p, _p, _sz, _p]),
     "gsb_act_bwd": (_i, [_p, _p, _i, _p, _i64, _p]),

@@ -6,6 +6,7 @@
 // logits + int64 labels produces the four sums; a second pass writes dlogits.  Eval
 // (unet/evaluate.py:29-40) is an argmax / sigmoid>0.5 pass with exact integer counts.
 // All HBM-bound: algorithmic bytes = logits (4c B/pixel) + labels (8 B/pixel) [+ dlogits].
+#include <mutex>
 #include "common.cuh"
 
 namespace gsb {
@@ -376,6 +377,62 @@ extern "C" int gsb_dice_sums(const float* a, const float* b, int64_t slices, int
   gsb::launch(sum_rows_kernel, gsb::LaunchCfg(1, 256, 0, to_stream(s)), (const double*)partial, (int)gx, (int)(slices * 3), 1.0, sums,
               (float*)nullptr);
   return check_launch("dice_sums", 2);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// gsb_dice_sums_noalloc: gsb_dice_sums for callers that cannot allocate (no counterpart in the reference).
+// The fp64 partial rows live in a file-scope device array of 96 KiB that every GPU
+// loading the library holds until exit.  In HOST code `g_dice_noalloc_scratch` is only a stand-in for the symbol, not
+// a device address: the address is looked up once per device with cudaGetSymbolAddress (that device current) and it
+// is that pointer the kernels receive.  All calls share the array: calls that overlap on the GPU (two streams) race.
+// Nothing has to start at zero: every row the summation reads is stored by the launch in front of it.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kDiceNoAllocDoubles = 12288;      // 96 KiB
+constexpr int kDiceNoAllocMaxSlices = 64;       // -> at least 64 partial rows
+static __device__ __align__(256) double g_dice_noalloc_scratch[kDiceNoAllocDoubles];
+
+static double* dice_noalloc_scratch_ptr() {   // null + gsb_last_error on failure
+  constexpr int kMaxDev = 64;
+  static double* ptrs[kMaxDev] = {};
+  static std::mutex mu;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDev) {
+    gsb::set_error("dice_sums_noalloc: cudaGetDevice failed or device index %d out of range (%s)", dev, cudaGetErrorString(e));
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    double* p = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_dice_noalloc_scratch);   // the current device's copy
+    if (e != cudaSuccess || p == nullptr) {
+      gsb::set_error("dice_sums_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return nullptr;
+    }
+    ptrs[dev] = p;
+  }
+  return ptrs[dev];
+}
+
+extern "C" size_t gsb_dice_sums_noalloc_max_slices(void) { return (size_t)kDiceNoAllocMaxSlices; }
+
+extern "C" int gsb_dice_sums_noalloc(const float* a, const float* b, int64_t slices, int64_t inner, double* sums, gsb_stream s) {
+  GSB_REQUIRE(a && b && sums && inner > 0, "dice_sums_noalloc: bad argument");
+  GSB_REQUIRE(slices > 0 && slices <= kDiceNoAllocMaxSlices,
+              "dice_sums_noalloc: %lld slices exceed the built-in scratch (max %d slices, %d KiB); use gsb_dice_sums with a "
+              "caller workspace", (long long)slices, kDiceNoAllocMaxSlices, (int)(kDiceNoAllocDoubles * sizeof(double) / 1024));
+  double* partial = dice_noalloc_scratch_ptr();
+  if (partial == nullptr) return -1;
+  int64_t gx = (inner + 256 * 16 - 1) / (256 * 16);   // same row count rule as gsb_dice_sums
+  if (gx < 1) gx = 1;
+  if (gx > 1024) gx = 1024;
+  const int64_t cap = kDiceNoAllocDoubles / (slices * 3);
+  if (gx > cap) gx = cap;
+  dim3 grid((unsigned)gx, (unsigned)slices);
+  gsb::launch(dice_sums_kernel, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), a, b, inner, partial);
+  gsb::launch(sum_rows_kernel, gsb::LaunchCfg(1, 256, 0, to_stream(s)), (const double*)partial, (int)gx, (int)(slices * 3), 1.0, sums,
+              (float*)nullptr);
+  return check_launch("dice_sums_noalloc", 2);
 }
 
 // workspace (forward value only): one double per CTA; the launch uses min(grid, workspace_bytes / 8) CTAs
