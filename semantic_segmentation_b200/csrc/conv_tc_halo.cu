@@ -868,6 +868,7 @@ int conv_halo_wgrad(const SubView& tiled, const SubView* shifted, int nmaps, con
   const int base = m_tiles * p.n_tiles;
   // split-K over the pixel boxes: fill whole waves of SMs, keep >= 2 boxes per CTA
   const int sms = num_sms_avail();
+  static const bool one_wave = env_flag("GSB_WGRAD_ONE_WAVE", true);
   int max_split = p.boxes / 2 > 0 ? p.boxes / 2 : 1;
   if (ws != nullptr && max_split > max_slices) max_split = max_slices;
   int best = 1;
@@ -877,7 +878,9 @@ int conv_halo_wgrad(const SubView& tiled, const SubView* shifted, int nmaps, con
     const long long waves = (ctas + sms - 1) / sms;
     const double eff = (double)ctas / (double)(waves * sms);
     if (eff > best_eff + 1e-9) { best_eff = eff; best = sp; }
-    if (eff >= 0.95 && ctas >= sms) { best = sp; break; }
+    // the FIRST split that fills a wave: one wave of CTAs with twice the pixel range costs the same MMA time as two
+    // waves, writes half the partial-sum slices (3 * 128 * BN fp32 per CTA) and halves what the fold kernel reads
+    if (eff >= 0.95 && (one_wave || ctas >= sms)) { best = sp; break; }
   }
   p.boxes_per_split = (p.boxes + best - 1) / best;
   const int split = (p.boxes + p.boxes_per_split - 1) / p.boxes_per_split;

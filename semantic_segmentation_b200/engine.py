@@ -179,9 +179,9 @@ _SIDE_STREAMS: Dict[int, "torch.cuda.Stream"] = {}
 
 
 def wgrad_stream_enabled() -> bool:
-    """Weight-gradient kernels on a second stream (``GSB_WGRAD_STREAM=1``): see BackwardBatch.side."""
+    """Weight-gradient kernels on a second stream (default on; ``GSB_WGRAD_STREAM=0`` switches it off): see BackwardBatch.side."""
     import os
-    return os.environ.get("GSB_WGRAD_STREAM", "0") != "0"
+    return os.environ.get("GSB_WGRAD_STREAM", "1") != "0"
 
 
 def _side_stream(device) -> "torch.cuda.Stream":
@@ -221,8 +221,8 @@ class BackwardBatch:
     launch per flush into ONE flat gradient buffer laid out in backward order, so that a prefix of that buffer can be
     handed to the gradient all-reduce while the rest of the backward pass is still running.
 
-    ``side`` (``GSB_WGRAD_STREAM=1``, experimental): the weight-gradient kernels of a layer depend on dY only and nothing
-    on the backward chain depends on them before the un-pack; they can be launched on a second stream (fork after the
+    ``side``: the weight-gradient kernels of a layer depend on dY only and nothing on the backward chain depends on them
+    before the un-pack; they are launched on a second stream (fork after the
     data gradient of the layer, join in ``flush``), so that the tensor-bound weight gradient of layer L runs under the
     HBM-bound BatchNorm / pooling / upsampling backward kernels of layer L-1 (fork / join are events: graph capture
     records them as dependencies)."""
