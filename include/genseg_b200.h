@@ -162,6 +162,10 @@ int gsb_bn_finalize(const double* sums, double count, const float* gamma, const 
 int gsb_bn_act(const gsb_view* x, const float* scale, const float* shift, const float* center, int act1,
                const gsb_view* out1, int act2, const gsb_view* out2, uint64_t drop_seed, int64_t drop_offset,
                const uint8_t* drop_mask, int per_image, gsb_stream s);
+/* relu(x * scale + shift) written to out1 AND its MaxPool2d(2) written to pooled, one pass (unet_parts.py:21 -> :34, the
+ * DoubleConv -> Down seam); bit-identical to gsb_bn_act(ReLU) followed by gsb_maxpool2_fwd.  Even h and w. */
+int gsb_bn_act_pool(const gsb_view* x, const float* scale, const float* shift, const gsb_view* out1, const gsb_view* pooled,
+                    gsb_stream s);
 /* Backward.  dy = act1'(z)*drop*dA1 + act2'(z)*dA2 (dA2 nullable), z as above.
  * reduce: sums[2][c] fp64 <- sum dy, sum dy*xhat.   apply (has_bn): dx = scale*(dy - s0/cnt - xhat*s1/cnt);
  * (no bn: pass mean = NULL -> dx = dy).  dgamma/dbeta accumulate (nullable). */

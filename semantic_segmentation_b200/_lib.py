@@ -65,6 +65,7 @@ SIGNATURES = {
     "gsb_bn_reduce_partials": (_i, [_p, _i, _i, _p, _p]),
     "gsb_bn_finalize": (_i, [_p, _d, _p, _p, _p, _p, _p, _f, _f, _i, _p, _p, _p, _p, _i, _p]),
     "gsb_bn_act": (_i, [_VP, _p, _p, _p, _i, _VP, _i, _VP, _u64, _i64, _p, _i, _p]),
+    "gsb_bn_act_pool": (_i, [_VP, _p, _p, _VP, _VP, _p]),
     "gsb_bn_bwd_reduce": (_i, [_VP, _VP, _VP, _p, _p, _p, _p, _p, _i, _i, _u64, _i64, _p, _p, _p, _sz, _p]),
     "gsb_bn_bwd_apply": (_i, [_VP, _VP, _VP, _p, _p, _p, _p, _p, _i, _i, _u64, _i64, _p, _p, _d, _VP, _p, _p, _i, _p]),
     "gsb_bn_param_grad": (_i, [_p, _i, _p, _p, _i, _p]),

@@ -535,7 +535,7 @@ __global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const __grid_co
 // Jobs of an un-pack launch whose source holds many partial-sum slices (small layers split 24..74 ways over the pixels):
 // the tile loader below would walk them one after the other per element (8 CTAs x 74 dependent 16-byte loads: 120 us).
 // One launch first folds the slices of all such jobs into their slice 0, in place (the source workspace is scratch).
-constexpr int kFoldReps = 8;          // 128-column chunks per block
+constexpr int kFoldCols = 1024;        // columns per block: one float4 per thread
 struct SliceJobs {
   float* ws[kMaxLayoutJobs];
   int64_t n[kMaxLayoutJobs];
@@ -543,39 +543,32 @@ struct SliceJobs {
   int blk0[kMaxLayoutJobs + 1];
   int count;
 };
-// Block = 8 warps; a chunk = 128 columns (one float4 per lane: 512 contiguous bytes per slice row and warp); warp w adds
-// slices w, w + 8, ... in fp64 (independent 16-byte loads in flight), the 8 warp sums are added in warp order.  Fixed
-// mapping -> deterministic.  n is a multiple of 4 and the workspace 16-byte aligned (checked by the caller).
+// One float4 column group per thread; the slices are added IN SLICE ORDER in fp64, eight independent 16-byte loads in
+// flight per thread, no shared memory and no barrier (the form with 8 warps over the slices and a shared-memory reduction
+// per 128 columns was barrier / latency bound: ncu profiles/r02k, 12-16 long-scoreboard + 6-9 barrier stall cycles per
+// issue at 1.6-3.5 TB/s).  Fixed mapping and order -> deterministic.  n is a multiple of 4 and the workspace 16-byte
+// aligned (checked by the caller).
 __global__ void __launch_bounds__(256) fold_slices_multi_kernel(const __grid_constant__ SliceJobs J) {
   GSB_PDL_ENTRY();
-  __shared__ double red[8][128];
   const int j = find_job(J.blk0, J.count, blockIdx.x);
   const int ns = J.nslices[j];
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t n = J.n[j];
   float* ws = J.ws[j];
-  for (int rep = 0; rep < kFoldReps; ++rep) {
-    const int64_t col0 = ((int64_t)(blockIdx.x - J.blk0[j]) * kFoldReps + rep) * 128;
-    if (col0 >= n) break;                                  // uniform over the block
-    const int64_t col = col0 + lane * 4;
-    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-    if (col < n) {
-#pragma unroll 4
-      for (int s = w; s < ns; s += 8) {
-        const float4 v = *reinterpret_cast<const float4*>(ws + (int64_t)s * n + col);
-        a0 += (double)v.x; a1 += (double)v.y; a2 += (double)v.z; a3 += (double)v.w;
-      }
-    }
-    red[w][lane * 4 + 0] = a0; red[w][lane * 4 + 1] = a1; red[w][lane * 4 + 2] = a2; red[w][lane * 4 + 3] = a3;
-    __syncthreads();
-    if (threadIdx.x < 128 && col0 + threadIdx.x < n) {
-      double t = 0.0;
+  const int64_t col = ((int64_t)(blockIdx.x - J.blk0[j]) * 256 + threadIdx.x) * 4;
+  if (col >= n) return;
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+  const float* src = ws + col;
+  for (int s0 = 0; s0 < ns; s0 += 8) {
+    float4 v[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) t += red[i][threadIdx.x];
-      ws[col0 + threadIdx.x] = (float)t;
+    for (int i = 0; i < 8; ++i)
+      v[i] = s0 + i < ns ? __ldg(reinterpret_cast<const float4*>(src + (int64_t)(s0 + i) * n)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      a0 += (double)v[i].x; a1 += (double)v[i].y; a2 += (double)v[i].z; a3 += (double)v[i].w;
     }
-    __syncthreads();
   }
+  *reinterpret_cast<float4*>(ws + col) = make_float4((float)a0, (float)a1, (float)a2, (float)a3);
 }
 
 static int run_layout_multi(bool pack, int n, const void* const* src, void* const* dst, const int* d0, const int* d1,
@@ -598,7 +591,7 @@ static int run_layout_multi(bool pack, int n, const void* const* src, void* cons
         S.n[k] = ne;
         S.nslices[k] = nslices[i];
         S.blk0[k] = blocks;
-        blocks += (int)((ne + 128 * kFoldReps - 1) / (128 * kFoldReps));
+        blocks += (int)((ne + kFoldCols - 1) / kFoldCols);
         folded[i] = true;
       }
       S.blk0[S.count] = blocks;

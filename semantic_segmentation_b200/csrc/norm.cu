@@ -366,6 +366,64 @@ __global__ void __launch_bounds__(kThreads) bn_act_kernel(PixView x, int64_t P, 
   }
 }
 
+// BatchNorm apply + ReLU + MaxPool2d(2) in one pass (the encoder's `DoubleConv -> Down` seam, unet_parts.py:21,34): a thread
+// owns one 2x2 window of 8 channels, writes the four activations (the skip tensor, possibly a channel slice of a concat
+// buffer) and their maximum (the pooled tensor), so the pooling pass does not read the activation back (1 read + 1/4
+// write of the tensor saved).  Same arithmetic as bn_act_kernel<T, true> followed by maxpool2_fwd_kernel: rounding to
+// the storage type is monotonic, so round(max) == max(round) and the pooled values are bit-identical.  H, W even.
+template <typename T>
+__global__ void __launch_bounds__(kThreads) bn_act_pool_kernel(PixView x, int N, int H, int W, int C, const float* __restrict__ scale,
+                                                              const float* __restrict__ shift, PixView out1, PixView pooled) {
+  GSB_PDL_ENTRY();
+  const unsigned G = (unsigned)C >> 3, OW = (unsigned)W >> 1, OH = (unsigned)H >> 1;
+  const uint64_t total = (uint64_t)N * OH * OW * G;
+  const bool fixed_g = (kThreads % G) == 0;   // the grid stride is a multiple of G: a thread keeps its channel group
+  float sc[8], sh[8];
+  if (fixed_g) {
+    load_param8(scale, (int)(threadIdx.x % G) * 8, sc, 1.f);
+    load_param8(shift, (int)(threadIdx.x % G) * 8, sh, 0.f);
+  }
+  for (uint64_t i = (uint64_t)blockIdx.x * kThreads + threadIdx.x; i < total; i += (uint64_t)gridDim.x * kThreads) {
+    unsigned g, ox, oy, n;
+    if ((i >> 32) == 0) {
+      const unsigned u = (unsigned)i, q = u / G;
+      g = u - q * G;
+      const unsigned row = q / OW;
+      ox = q - row * OW;
+      n = row / OH;
+      oy = row - n * OH;
+    } else {
+      const uint64_t q = i / G;
+      g = (unsigned)(i - q * G);
+      const uint64_t row = q / OW;
+      ox = (unsigned)(q - row * OW);
+      n = (unsigned)(row / OH);
+      oy = (unsigned)(row - (uint64_t)n * OH);
+    }
+    const int c0 = (int)g * 8;
+    if (!fixed_g) {
+      load_param8(scale, c0, sc, 1.f);
+      load_param8(shift, c0, sh, 0.f);
+    }
+    const int64_t p00 = ((int64_t)n * H + 2 * oy) * W + 2 * ox;
+    float v[4][8];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) load8<T>(x, p00 + (t >> 1) * (int64_t)W + (t & 1), c0, v[t]);
+    float m[8];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float z = fmaf(v[t][k], sc[k], sh[k]);
+        v[t][k] = z > 0.f ? z : 0.f;
+        m[k] = t == 0 ? v[t][k] : fmaxf(m[k], v[t][k]);
+      }
+      store8<T>(out1, p00 + (t >> 1) * (int64_t)W + (t & 1), c0, v[t]);
+    }
+    store8<T>(pooled, ((int64_t)n * OH + oy) * OW + ox, c0, m);
+  }
+}
+
 template <typename T, bool FAST, bool PERIMG = false>
 __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(
     PixView x, PixView dA1, PixView dA2, int64_t P, int C, const float* __restrict__ scale,
@@ -703,6 +761,30 @@ extern "C" int gsb_bn_act(const gsb_view* x, const float* scale, const float* sh
                                                                      drop_seed, drop_offset, drop_mask);
   }
   return check_launch("bn_act");
+}
+
+extern "C" int gsb_bn_act_pool(const gsb_view* x, const float* scale, const float* shift, const gsb_view* out1,
+                               const gsb_view* pooled, gsb_stream s) {
+  if (check_vec_view(x, "bn_act_pool.x") || check_vec_view(out1, "bn_act_pool.out1") || check_vec_view(pooled, "bn_act_pool.pooled"))
+    return -1;
+  GSB_REQUIRE(scale && shift, "bn_act_pool: scale / shift required");
+  GSB_REQUIRE(out1->dtype == x->dtype && out1->c == x->c && out1->n == x->n && out1->h == x->h && out1->w == x->w,
+              "bn_act_pool: out1 mismatch");
+  GSB_REQUIRE(x->h % 2 == 0 && x->w % 2 == 0 && x->h > 0 && x->w > 0, "bn_act_pool: even height and width required");
+  GSB_REQUIRE(pooled->dtype == x->dtype && pooled->c == x->c && pooled->n == x->n && pooled->h == x->h / 2 && pooled->w == x->w / 2,
+              "bn_act_pool: pooled mismatch");
+  const int64_t total = (int64_t)x->n * (x->h / 2) * (x->w / 2) * (x->c / 8);
+  int64_t blocks = (total + kThreads - 1) / kThreads;
+  const int64_t cap = (int64_t)num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  if (x->dtype == GSB_BF16)
+    gsb::launch(bn_act_pool_kernel<__nv_bfloat16>, gsb::LaunchCfg((int)blocks, kThreads, 0, to_stream(s)), pv(x), x->n, x->h, x->w, x->c,
+                scale, shift, pv(out1), pv(pooled));
+  else
+    gsb::launch(bn_act_pool_kernel<float>, gsb::LaunchCfg((int)blocks, kThreads, 0, to_stream(s)), pv(x), x->n, x->h, x->w, x->c, scale,
+                shift, pv(out1), pv(pooled));
+  return check_launch("bn_act_pool");
 }
 
 static int check_bwd_views(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2) {

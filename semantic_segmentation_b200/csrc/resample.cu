@@ -497,8 +497,9 @@ __global__ void __launch_bounds__(256) upsample2_fwd_blk_kernel(const T* __restr
   GSB_PDL_ENTRY();
   // one flat grid-stride loop over (image, row block, column block, channel group): no per-row tail (a row of the
   // production shape has 129 * 8 = 1032 items, 4.03 per thread of a row-owning block)
-  __shared__ float s_wx[kMaxUpW];
+  __shared__ float s_wx[kMaxUpW], s_wy[kMaxUpW];
   for (int v = threadIdx.x; v < 2 * w; v += blockDim.x) s_wx[v] = up_blk_w1(v, w);
+  for (int v = threadIdx.x; v < 2 * h; v += blockDim.x) s_wy[v] = up_blk_w1(v, h);
   __syncthreads();
   const unsigned G = (unsigned)C >> 3, per_row = (unsigned)(w + 1) * G;
   const unsigned H1 = (unsigned)h + 1;
@@ -517,7 +518,7 @@ __global__ void __launch_bounds__(256) upsample2_fwd_blk_kernel(const T* __restr
     const int bi = (int)(rb - n * H1) - 1;
     const int u0 = 2 * bi + 1, u1 = u0 + 1;
     const bool hasr0 = bi >= 0, hasr1 = bi < h - 1;
-    const float wy0 = hasr0 ? up_blk_w1(u0, h) : 0.f, wy1 = hasr1 ? up_blk_w1(u1, h) : 0.f;
+    const float wy0 = s_wy[hasr0 ? u0 : 0], wy1 = s_wy[hasr1 ? u1 : 0];   // rows outside the tensor are not stored
     const T* r0 = x + ((int64_t)n * h + max(bi, 0)) * w * xld;
     const T* r1 = x + ((int64_t)n * h + min(bi + 1, h - 1)) * w * xld;
     T* o0 = out + ((int64_t)n * 2 * h + u0) * OW * old;
@@ -614,6 +615,9 @@ __global__ void __launch_bounds__(256) upsample2_bwd_sep_kernel(const T* __restr
     for (int r = 0; r < 4; ++r) wy[r] = up_blk_wgt(2 * iy - 1 + r, iy, h);
     const T* base = dout + ((int64_t)n * 2 * h + (2 * iy - 1)) * OW * dld;
     const int64_t rstride = (int64_t)OW * dld;
+    int64_t roff[4];   // rows outside the tensor (block-uniform) weigh 0: they are read from the nearest row inside it
+#pragma unroll
+    for (int r = 0; r < 4; ++r) roff[r] = (int64_t)min(max(r, iy == 0 ? 1 : 0), iy == h - 1 ? 2 : 3) * rstride;
     __syncthreads();  // the previous row's phase 2 (and the weight table) is done
     // batches of U items per thread: the 4U row loads of a batch are independent and issued together (one memory round
     // trip per batch; one item at a time left the block latency-bound: 5 dependent round trips per row at 1040 items)
@@ -622,25 +626,24 @@ __global__ void __launch_bounds__(256) upsample2_bwd_sep_kernel(const T* __restr
     for (unsigned b0 = 0; b0 < items1; b0 += 256 * U) {
       Raw raw[U][4];
       bool ok[U];
+      unsigned cs[U], gs[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const unsigned it = b0 + u * 256 + threadIdx.x;
         const unsigned c = it / G, g = it - c * G;
+        cs[u] = c; gs[u] = g;
         const int v = vbase + (int)c;
         ok[u] = it < items1 && v >= 0 && v < OW;
         const T* p = base + (int64_t)(ok[u] ? v : 0) * dld + g * 8;
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-          // rows outside the tensor (block-uniform test) weigh 0: they are read from the nearest row inside it
-          const int rr = min(max(r, iy == 0 ? 1 : 0), iy == h - 1 ? 2 : 3);
-          if (ok[u]) raw[u][r] = RawVec8<T>::load(p + rr * rstride);
-        }
+        for (int r = 0; r < 4; ++r)
+          if (ok[u]) raw[u][r] = RawVec8<T>::load(p + roff[r]);
       }
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const unsigned it = b0 + u * 256 + threadIdx.x;
         if (it >= items1) continue;
-        const unsigned c = it / G, g = it - c * G;
+        const unsigned c = cs[u], g = gs[u];
         float2 acc[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) acc[k] = make_float2(0.f, 0.f);

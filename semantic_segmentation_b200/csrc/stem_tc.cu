@@ -82,7 +82,8 @@ __device__ __forceinline__ void gather_taps(const float* __restrict__ x, int H, 
 // forward: y[p][co] = sum_t x[p @ t] w[co][t], bf16 NHWC out, optional BatchNorm statistics of the STORED values
 // ---------------------------------------------------------------------------------------------------------------------
 template <int T, int K, int S>
-__global__ void __launch_bounds__(128) stem_tc_fwd_kernel(const float* __restrict__ x, int H, int W, const float* __restrict__ w,
+__global__ void __launch_bounds__(128, 6) stem_tc_fwd_kernel(const __grid_constant__ CUtensorMap ymap, int use_tma,
+                                                         const float* __restrict__ x, int H, int W, const float* __restrict__ w,
                                                          __nv_bfloat16* __restrict__ y, int64_t yld, int OH, int OW, int pad,
                                                          float* __restrict__ stats, int64_t P, int num_tiles) {
   GSB_PDL_ENTRY();
@@ -174,18 +175,28 @@ __global__ void __launch_bounds__(128) stem_tc_fwd_kernel(const float* __restric
       q[4 + j].z = pack_bf16(__uint_as_float(a1[8 * j + 4]), __uint_as_float(a1[8 * j + 5]));
       q[4 + j].w = pack_bf16(__uint_as_float(a1[8 * j + 6]), __uint_as_float(a1[8 * j + 7]));
     }
-    if (valid) {
+    if (valid && !use_tma) {   // strided output view: one 128-byte row per thread
       uint4* dst = reinterpret_cast<uint4*>(y + p * yld);
 #pragma unroll
       for (int j = 0; j < 8; ++j) dst[j] = q[j];
     }
-    if (stats != nullptr) {
-      // stage the stored tile (zero rows past the end) in the A buffer -- the MMAs are done with it -- and add it up by
-      // columns: thread (cp, rg) walks 32 rows of one 32-bit word column; the XOR swizzle keeps both sides conflict free
+    if (stats != nullptr || use_tma) {
+      // stage the stored tile (zero rows past the end) in the A buffer -- the MMAs are done with it -- in the 128-byte
+      // swizzle: that is the layout a TMA store reads (dense output: ONE bulk store of 16 KB per tile instead of 8
+      // row-strided 16-byte stores per thread, which kept the load / store unit queue full: ncu profiles/r02k, lg_throttle
+      // 3.9 of 11 stall cycles per issue), and it keeps the column sums below conflict free
 #pragma unroll
       for (int j = 0; j < 8; ++j)
         *reinterpret_cast<uint4*>(sA + tid * 128 + ((j ^ (tid & 7)) << 4)) = valid ? q[j] : make_uint4(0u, 0u, 0u, 0u);
+      if (use_tma) fence_proxy_async();
       __syncthreads();
+      if (use_tma && tid == 0) {
+        tma_store_2d(&ymap, sA, 0, tile * 128);     // rows past P are clipped by the tensor map
+        tma_store_commit();
+      }
+    }
+    if (stats != nullptr) {
+      // thread (cp, rg) walks 32 rows of one 32-bit word column of the staged tile
       const uint32_t* s32 = reinterpret_cast<const uint32_t*>(sA);
 #pragma unroll 8
       for (int i = 0; i < 32; ++i) {
@@ -196,6 +207,7 @@ __global__ void __launch_bounds__(128) stem_tc_fwd_kernel(const float* __restric
         s1 = __ffma2_rn(f, f, s1);
       }
     }
+    if (use_tma && tid == 0) tma_store_wait_read();   // the bulk store has read the staging tile
     tc_fence_before();
     __syncthreads();                // accumulator and staging tile are free for the next tile
     p = p_next;
@@ -333,12 +345,17 @@ int stem_tc_fwd(const float* x, int h, int w, const float* weight, const gsb_vie
   if (stats != nullptr && grid > max_rows) grid = max_rows;
   const int smem = 1024 + 16384 + 8192 + 64 + 4 * 2 * 64 * (int)sizeof(float);
   __nv_bfloat16* yp = reinterpret_cast<__nv_bfloat16*>(y->ptr);
+  static const bool tma_on = []() { const char* e = getenv("GSB_STEM_TMA_STORE"); return !(e && e[0] == '0'); }();
+  const int use_tma = (tma_on && y->sw == 64 && ((uintptr_t)y->ptr & 15) == 0 && P < ((int64_t)1 << 31)) ? 1 : 0;
+  CUtensorMap ymap;
+  memset(&ymap, 0, sizeof(ymap));
+  if (use_tma && make_w_map(&ymap, y->ptr, P, 64, 128)) return -1;
   if (k == 3)
-    gsb::launch(stem_tc_fwd_kernel<9, 3, 1>, gsb::LaunchCfg(grid, 128, smem, st), x, h, w, weight, yp, (int64_t)y->sw, y->h, y->w, pad,
-                stats, P, num_tiles);
+    gsb::launch(stem_tc_fwd_kernel<9, 3, 1>, gsb::LaunchCfg(grid, 128, smem, st), ymap, use_tma, x, h, w, weight, yp, (int64_t)y->sw,
+                y->h, y->w, pad, stats, P, num_tiles);
   else
-    gsb::launch(stem_tc_fwd_kernel<16, 4, 2>, gsb::LaunchCfg(grid, 128, smem, st), x, h, w, weight, yp, (int64_t)y->sw, y->h, y->w, pad,
-                stats, P, num_tiles);
+    gsb::launch(stem_tc_fwd_kernel<16, 4, 2>, gsb::LaunchCfg(grid, 128, smem, st), ymap, use_tma, x, h, w, weight, yp, (int64_t)y->sw,
+                y->h, y->w, pad, stats, P, num_tiles);
   if (rows) *rows = stats != nullptr ? grid : 0;
   return 0;
 }

@@ -178,6 +178,12 @@ class WeightPacks:
 _SIDE_STREAMS: Dict[int, "torch.cuda.Stream"] = {}
 
 
+def pool_fusion_enabled() -> bool:
+    """BatchNorm + ReLU + MaxPool2d(2) in one kernel at the encoder's DoubleConv -> Down seam (``GSB_POOL_FUSION=0``: off)."""
+    import os
+    return os.environ.get("GSB_POOL_FUSION", "1") != "0"
+
+
 def wgrad_stream_enabled() -> bool:
     """Weight-gradient kernels on a second stream (default on; ``GSB_WGRAD_STREAM=0`` switches it off): see BackwardBatch.side."""
     import os
@@ -395,7 +401,10 @@ class ConvBNAct:
     # x_view: GsbView of the input (NHWC act buffer or the NCHW fp32 network input)
     def forward(self, x_view: GsbView, x_keep, n: int, h: int, w: int, device, weight, bias, bn, training: bool,
                 out1: Optional[torch.Tensor] = None, out2: Optional[torch.Tensor] = None, save: bool = True,
-                drop_seed: int = 0, drop_mask: Optional[torch.Tensor] = None, packed=None):
+                drop_seed: int = 0, drop_mask: Optional[torch.Tensor] = None, packed=None,
+                pool_out: Optional[torch.Tensor] = None):
+        """pool_out: optional [n, oh/2, ow/2, cout] tensor that receives MaxPool2d(2) of out1 in the same pass when the
+        layer is the plain BatchNorm + ReLU form (``sv.extra['pooled']`` tells the caller whether it was written)."""
         s = self.spec
         oh, ow = s.out_hw(h, w)
         y = _nhwc_empty(n, oh, ow, s.cout, device)
@@ -460,9 +469,15 @@ class ConvBNAct:
             out1 = _nhwc_empty(n, oh, ow, s.cout, device)
         use_drop = self.dropout and training
         center = mean if (centered and self.has_bn) else None
-        ops.bn_act(y, scale, shift, self.act1, out1, self.act2 if self.act2 is not None else ACT_NONE,
-                   out2 if self.act2 is not None else None, drop_seed if use_drop else 0,
-                   drop_mask if use_drop else None, center=center, drop_offset=drop_offset if use_drop else 0)
+        pooled = (pool_out is not None and pool_fusion_enabled() and self.has_bn and self.act1 == ACT_RELU and self.act2 is None
+                  and not use_drop and center is None and oh % 2 == 0 and ow % 2 == 0)
+        if pooled:      # BatchNorm + ReLU + MaxPool2d(2) in one pass: the pooling does not read the activation back
+            ops.bn_act_pool(y, scale, shift, out1, pool_out)
+        else:
+            ops.bn_act(y, scale, shift, self.act1, out1, self.act2 if self.act2 is not None else ACT_NONE,
+                       out2 if self.act2 is not None else None, drop_seed if use_drop else 0,
+                       drop_mask if use_drop else None, center=center, drop_offset=drop_offset if use_drop else 0)
+        sv.extra["pooled"] = pooled
         if save:
             sv.x_view, sv.x_keep, sv.y = x_view, x_keep, y
             sv.scale, sv.shift, sv.mean, sv.invstd, sv.count = scale, shift, mean, invstd, count

@@ -333,6 +333,12 @@ def bn_act(x: torch.Tensor, scale, shift, act1: int, out1: torch.Tensor, act2: i
                             int(drop_seed), int(drop_offset), ptr(drop_mask), int(per_image), _s(x)), "bn_act")
 
 
+def bn_act_pool(x: torch.Tensor, scale, shift, out1: torch.Tensor, pooled: torch.Tensor) -> None:
+    """out1 = relu(x * scale + shift), pooled = MaxPool2d(2)(out1) in one pass (even H and W)."""
+    check(load().gsb_bn_act_pool(_ref(view_nhwc(x)), ptr(scale), ptr(shift), _ref(view_nhwc(out1)), _ref(view_nhwc(pooled)), _s(x)),
+          "bn_act_pool")
+
+
 def bn_bwd_reduce(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, drop_seed=0, drop_mask=None, center=None,
                   drop_offset=0) -> torch.Tensor:
     v = view_nhwc(x)

@@ -56,14 +56,14 @@ class DoubleConvOps:
         p = self.prefix + ".double_conv"
         return [(p + ".0.weight", self.c0.spec), (p + ".3.weight", self.c1.spec)]
 
-    def forward(self, x_view, x_keep, n, h, w, device, P, B, training, save, out=None, packs=None):
+    def forward(self, x_view, x_keep, n, h, w, device, P, B, training, save, out=None, packs=None, pool_out=None):
         p = self.prefix + ".double_conv"
         pk0 = packs.get(p + ".0.weight") if packs is not None else None
         pk1 = packs.get(p + ".3.weight") if packs is not None else None
         a0, s0 = self.c0.forward(x_view, x_keep, n, h, w, device, P[p + ".0.weight"], None, self._bn(P, B, 1),
                                  training, save=save, packed=pk0)
         a1, s1 = self.c1.forward(view_nhwc(a0), a0, n, h, w, device, P[p + ".3.weight"], None, self._bn(P, B, 4),
-                                 training, out1=out, save=save, packed=pk1)
+                                 training, out1=out, save=save, packed=pk1, pool_out=pool_out)
         return a1, (s0, s1)
 
     def backward(self, saved, dA, G: Dict[str, torch.Tensor], need: Dict[str, bool], need_dx: bool,
@@ -144,16 +144,25 @@ class UNetProgram:
                     packs.add(key, spec, P[key], need_bwd=save)
         packs.run()
         # encoder
-        x1, sv = self.inc.forward(view_nchw(x), x, n, h, w, dev, P, B, training, save, out=cats[0][..., :64], packs=packs)
+        # the block in front of a Down writes its max-pooled activation in the same pass as the activation itself
+        def pool_buffer(level):
+            return _nhwc_empty(n, sizes[level + 1][0], sizes[level + 1][1], self.chans[level], dev)
+
+        pooled = pool_buffer(0)
+        x1, sv = self.inc.forward(view_nchw(x), x, n, h, w, dev, P, B, training, save, out=cats[0][..., :64], packs=packs,
+                                  pool_out=pooled)
         tape["inc"] = sv
         skips = [x1]
         cur = x1
         for i in range(4):
-            pooled = ops.maxpool2_fwd(cur)
+            if not sv[1].extra.get("pooled"):           # odd size, fp32 validation mode, ...: separate pooling pass
+                pooled = ops.maxpool2_fwd(cur)
             hh, ww = sizes[i + 1]
             out = cats[i + 1][..., :self.chans[i + 1]] if i < 3 else None
+            nxt = pool_buffer(i + 1) if i < 3 else None
             cur, sv = self.downs[i].forward(view_nhwc(pooled), pooled, n, hh, ww, dev, P, B, training, save, out=out,
-                                            packs=packs)
+                                            packs=packs, pool_out=nxt)
+            pooled = nxt
             tape[f"down{i + 1}"] = sv
             skips.append(cur)
         tape["skips"] = skips if save else None
