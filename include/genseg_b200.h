@@ -194,6 +194,13 @@ int gsb_bn_bwd_partial(const gsb_view* x, const gsb_view* dA1, const gsb_view* d
                        const float* center, const float* mean, const float* invstd, int act1, int act2, uint64_t drop_seed,
                        int64_t drop_offset, const uint8_t* drop_mask, void* workspace, size_t workspace_bytes, int* rows,
                        int per_image, gsb_stream s);
+/* gsb_bn_bwd_partial for the BatchNorm + ReLU layer in front of a MaxPool2d(2) (unet_parts.py:34), with the pooling
+ * backward folded in: dA (in / out, the skip half of the concat gradient) += the pooled gradient dpool routed to the
+ * first maximum of each 2x2 window of relu(scale*x+shift), then the rows of [sum dy, sum dy*xhat] as above.  Replaces
+ * gsb_maxpool2_bwd(accumulate) + gsb_bn_bwd_partial (same dA, bit for bit).  bf16, even h and w. */
+int gsb_bn_bwd_partial_pool(const gsb_view* x, const gsb_view* dA, const gsb_view* dpool, const float* scale, const float* shift,
+                            const float* mean, const float* invstd, void* workspace, size_t workspace_bytes, int* rows,
+                            gsb_stream s);
 int gsb_bn_bwd_stats(const float* partial, int rows, int c, void* const* regions, int rank, int world, float* dgamma,
                      float* dbeta, int accumulate, double* sums, gsb_stream s);
 

@@ -71,6 +71,7 @@ SIGNATURES = {
     "gsb_bn_param_grad": (_i, [_p, _i, _p, _p, _i, _p]),
     "gsb_bn_stats_finalize": (_i, [_p, _i, _i, _d, _p, _i, _i, _p, _p, _p, _p, _p, _f, _f, _p, _p, _p, _p, _i, _p]),
     "gsb_bn_bwd_partial": (_i, [_VP, _VP, _VP, _p, _p, _p, _p, _p, _i, _i, _u64, _i64, _p, _p, _sz, _p, _i, _p]),
+    "gsb_bn_bwd_partial_pool": (_i, [_VP, _VP, _VP, _p, _p, _p, _p, _p, _sz, _p, _p]),
     "gsb_bn_bwd_stats": (_i, [_p, _i, _i, _p, _i, _i, _p, _p, _i, _p, _p]),
     "gsb_maxpool2_fwd": (_i, [_VP, _VP, _p]),
     "gsb_maxpool2_bwd": (_i, [_VP, _VP, _VP, _i, _p]),

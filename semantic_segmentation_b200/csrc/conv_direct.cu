@@ -302,6 +302,44 @@ __global__ void bias_grad_kernel(DView d, float* __restrict__ db) {
   }
 }
 
+// Any other view (the 1..3-channel fp32 NCHW network outputs): grid = (pixel chunks, channels); a CTA adds a strided
+// pixel range of one channel in fp64 and writes TWO partial rows (hi + lo floats); gsb::sum_slices adds the rows in row
+// order.  (One CTA per channel took 1.3 ms for the generator's 8 x 1 x 256 x 256 output: profiles/r02m_p2p_launch_summary.)
+__global__ void __launch_bounds__(256) bias_grad_rows_kernel(DView d, float* __restrict__ partial) {
+  GSB_PDL_ENTRY();
+  const int c = blockIdx.y, C = gridDim.y;
+  const int64_t P = (int64_t)d.N * d.H * d.W;
+  double acc = 0.0;
+  for (int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x; p < P; p += (int64_t)gridDim.x * 256) {
+    int x, y, n;
+    if ((p >> 31) == 0) {
+      const unsigned u = (unsigned)p, r = u / (unsigned)d.W;
+      x = (int)(u - r * (unsigned)d.W);
+      n = (int)(r / (unsigned)d.H);
+      y = (int)(r - (unsigned)n * (unsigned)d.H);
+    } else {
+      x = (int)(p % d.W);
+      const int64_t r = p / d.W;
+      y = (int)(r % d.H);
+      n = (int)(r / d.H);
+    }
+    acc += ld_elem(d.ptr, (int64_t)n * d.sn + (int64_t)y * d.sh + (int64_t)x * d.sw + (int64_t)c * d.sc, d.dtype);
+  }
+  __shared__ double red[8];
+  acc = warp_sum_d(acc);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    double v = threadIdx.x < 8 ? red[threadIdx.x] : 0.0;
+    v = warp_sum_d(v);
+    if (threadIdx.x == 0) {
+      const float hi = (float)v;
+      partial[((int64_t)blockIdx.x * 2) * C + c] = hi;
+      partial[((int64_t)blockIdx.x * 2 + 1) * C + c] = (float)(v - (double)hi);
+    }
+  }
+}
+
 // NHWC views with C % 8 == 0: 16-byte loads, every CTA covers a pixel range and writes TWO partial rows (its fp64 sums
 // split into hi + lo floats); gsb::sum_slices adds the rows in row order.
 template <typename T>
@@ -432,6 +470,18 @@ extern "C" int gsb_bias_grad(const gsb_view* dout, float* db, void* workspace, s
         gsb::launch(bias_grad_vec_kernel<float>, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), (const float*)dout->ptr, (int64_t)dout->sw, P, C,
                     partial);
       gsb::sum_slices(partial, 2 * grid, C, C, db, 0, to_stream(s));
+      return check_launch("bias_grad", 2);
+    }
+  }
+  if (workspace != nullptr && C >= 1 && C <= 65535 && P >= 4096) {
+    int64_t want = (P + 2047) / 2048;
+    int64_t cap = (int64_t)(workspace_bytes / (2 * (size_t)C * sizeof(float)));
+    if (cap > (int64_t)num_sms() * 4) cap = (int64_t)num_sms() * 4;
+    const int gx = (int)(want > cap ? cap : want);
+    if (gx >= 1) {
+      float* partial = reinterpret_cast<float*>(workspace);
+      gsb::launch(bias_grad_rows_kernel, gsb::LaunchCfg(dim3((unsigned)gx, (unsigned)C), 256, 0, to_stream(s)), dv(dout), partial);
+      gsb::sum_slices(partial, 2 * gx, C, C, db, 0, to_stream(s));
       return check_launch("bias_grad", 2);
     }
   }

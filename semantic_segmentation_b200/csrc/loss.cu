@@ -27,17 +27,22 @@ __device__ __forceinline__ double block_sum_d(double v, double* sh) {
   return r;  // valid in thread 0
 }
 
+// CT > 0: compile-time class count (the per-class arrays stay in registers: with a run-time bound they were indexed
+// dynamically, i.e. lived in local memory); CT == 0: any C <= kMaxC.
+template <int CT>
 __global__ void __launch_bounds__(256) seg_loss_reduce_kernel(const float* __restrict__ logits,
                                                              const int64_t* __restrict__ labels, int64_t P, int64_t HW,
                                                              int C, double* __restrict__ partial) {
   GSB_PDL_ENTRY();
   __shared__ double sh[8];
+  const int Cc = CT > 0 ? CT : C;
+  constexpr int CB = CT > 0 ? CT : kMaxC;
   float ce = 0.f, inter = 0.f, sp = 0.f, st = 0.f;
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P; p += (int64_t)gridDim.x * blockDim.x) {
     int64_t n = p / HW, r = p - n * HW;
-    const float* z = logits + n * C * HW + r;
+    const float* z = logits + n * Cc * HW + r;
     int t = (int)labels[p];
-    if (C == 1) {
+    if (Cc == 1) {
       float x = z[0];
       float pr = 1.f / (1.f + expf(-x));
       ce += fmaxf(x, 0.f) - x * (float)t + log1pf(expf(-fabsf(x)));
@@ -46,12 +51,16 @@ __global__ void __launch_bounds__(256) seg_loss_reduce_kernel(const float* __res
       st += (float)t;
     } else {
       float v[kMaxC], m = -INFINITY;
-      for (int c = 0; c < C; ++c) {
+#pragma unroll
+      for (int c = 0; c < CB; ++c) {
+        if (CT == 0 && c >= Cc) break;
         v[c] = z[(int64_t)c * HW];
         m = fmaxf(m, v[c]);
       }
       float se = 0.f, zt = 0.f, et = 0.f;
-      for (int c = 0; c < C; ++c) {
+#pragma unroll
+      for (int c = 0; c < CB; ++c) {
+        if (CT == 0 && c >= Cc) break;
         float e = expf(v[c] - m);
         se += e;
         if (c == t) { zt = v[c]; et = e; }
@@ -60,7 +69,11 @@ __global__ void __launch_bounds__(256) seg_loss_reduce_kernel(const float* __res
       ce += (m + logf(se)) - zt;
       inter += et * inv;
       float s = 0.f;
-      for (int c = 0; c < C; ++c) s += expf(v[c] - m) * inv;
+#pragma unroll
+      for (int c = 0; c < CB; ++c) {
+        if (CT == 0 && c >= Cc) break;
+        s += expf(v[c] - m) * inv;
+      }
       sp += s;
       st += 1.f;
     }
@@ -112,43 +125,54 @@ __global__ void seg_loss_finalize_kernel(const double* __restrict__ sums, double
   out[0] = (float)ce + (float)(1.0 - dice);
 }
 
+template <int CT>
 __global__ void __launch_bounds__(256) seg_loss_bwd_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels,
                                                           int64_t P, int64_t HW, int C, const double* __restrict__ sums,
                                                           double count, const float* __restrict__ gscale,
                                                           float* __restrict__ dlogits) {
   GSB_PDL_ENTRY();
+  const int Cc = CT > 0 ? CT : C;
+  constexpr int CB = CT > 0 ? CT : kMaxC;
   double dice, ad, bd;
   dice_terms(sums, dice, ad, bd);
   const float gs = gscale ? *gscale : 1.f;
   const float a = (float)ad, b = (float)bd, invn = (float)(1.0 / count);
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < P; p += (int64_t)gridDim.x * blockDim.x) {
     int64_t n = p / HW, r = p - n * HW;
-    const float* z = logits + n * C * HW + r;
-    float* dz = dlogits + n * C * HW + r;
+    const float* z = logits + n * Cc * HW + r;
+    float* dz = dlogits + n * Cc * HW + r;
     int t = (int)labels[p];
-    if (C == 1) {
+    if (Cc == 1) {
       float x = z[0];
       float pr = 1.f / (1.f + expf(-x));
       float g = -(a * (float)t - b);  // d(1-dice)/dp
       dz[0] = gs * ((pr - (float)t) * invn + g * pr * (1.f - pr));
     } else {
       float v[kMaxC], m = -INFINITY;
-      for (int c = 0; c < C; ++c) {
+#pragma unroll
+      for (int c = 0; c < CB; ++c) {
+        if (CT == 0 && c >= Cc) break;
         v[c] = z[(int64_t)c * HW];
         m = fmaxf(m, v[c]);
       }
       float se = 0.f;
-      for (int c = 0; c < C; ++c) {
+#pragma unroll
+      for (int c = 0; c < CB; ++c) {
+        if (CT == 0 && c >= Cc) break;
         v[c] = expf(v[c] - m);
         se += v[c];
       }
       float inv = 1.f / se, dot = 0.f;
-      for (int c = 0; c < C; ++c) {
+#pragma unroll
+      for (int c = 0; c < CB; ++c) {
+        if (CT == 0 && c >= Cc) break;
         v[c] *= inv;
         float g = -(a * (c == t ? 1.f : 0.f) - b);
         dot += v[c] * g;
       }
-      for (int c = 0; c < C; ++c) {
+#pragma unroll
+      for (int c = 0; c < CB; ++c) {
+        if (CT == 0 && c >= Cc) break;
         float g = -(a * (c == t ? 1.f : 0.f) - b);
         dz[(int64_t)c * HW] = gs * ((v[c] - (c == t ? 1.f : 0.f)) * invn + v[c] * (g - dot));
       }
@@ -327,7 +351,9 @@ extern "C" int gsb_seg_loss_reduce(const float* logits, const int64_t* labels, i
   int grid = grid1d(P);
   GSB_REQUIRE(workspace_bytes >= (size_t)grid * 4 * sizeof(double), "seg_loss_reduce: workspace too small");
   double* partial = reinterpret_cast<double*>(workspace);
-  gsb::launch(seg_loss_reduce_kernel, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), logits, labels, P, HW, c, partial);
+  if (c == 2) gsb::launch(seg_loss_reduce_kernel<2>, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), logits, labels, P, HW, c, partial);
+  else if (c == 1) gsb::launch(seg_loss_reduce_kernel<1>, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), logits, labels, P, HW, c, partial);
+  else gsb::launch(seg_loss_reduce_kernel<0>, gsb::LaunchCfg(grid, 256, 0, to_stream(s)), logits, labels, P, HW, c, partial);
   gsb::launch(sum_rows4_kernel, gsb::LaunchCfg(1, 256, 0, to_stream(s)), partial, grid, sums);
   return check_launch("seg_loss_reduce", 2);
 }
@@ -343,7 +369,10 @@ extern "C" int gsb_seg_loss_bwd(const float* logits, const int64_t* labels, int 
   GSB_REQUIRE(logits && labels && sums && dlogits && count > 0, "seg_loss_bwd: bad argument");
   GSB_REQUIRE(c >= 1 && c <= kMaxC, "seg_loss: n_classes %d unsupported (max %d)", c, kMaxC);
   int64_t HW = (int64_t)h * w, P = (int64_t)n * HW;
-  gsb::launch(seg_loss_bwd_kernel, gsb::LaunchCfg(grid1d(P, 16), 256, 0, to_stream(s)), logits, labels, P, HW, c, sums, count, gscale, dlogits);
+  const gsb::LaunchCfg lc(grid1d(P, 16), 256, 0, to_stream(s));
+  if (c == 2) gsb::launch(seg_loss_bwd_kernel<2>, lc, logits, labels, P, HW, c, sums, count, gscale, dlogits);
+  else if (c == 1) gsb::launch(seg_loss_bwd_kernel<1>, lc, logits, labels, P, HW, c, sums, count, gscale, dlogits);
+  else gsb::launch(seg_loss_bwd_kernel<0>, lc, logits, labels, P, HW, c, sums, count, gscale, dlogits);
   return check_launch("seg_loss_bwd");
 }
 

@@ -253,6 +253,119 @@ __global__ void __launch_bounds__(kThreads, 4) bn_bwd_reduce_relu_bf16_kernel(
   }
 }
 
+// The same statistics with the MaxPool2d(2) backward folded in (the encoder's Down -> DoubleConv seam in the backward
+// direction): the gradient of the block's output is  dA = dskip + route(dpool)  where dskip already sits in the concat
+// gradient (written by the decoder's data gradient) and route() sends each pooled gradient to the FIRST maximum of its
+// 2x2 window.  A thread owns one window of 8 channels: it recomputes the stored activations a = bf16(relu(scale*y+shift))
+// (exactly what bn_act wrote, so the argmax is the one maxpool2_bwd finds), adds the routed gradient, WRITES dA back
+// (rounded to bf16 as maxpool2_bwd's accumulate does: bn_bwd_apply reads it next) and accumulates sum dy, sum dy*y.
+// Replaces maxpool2_bwd (reads a, dpool, dskip; writes dskip) + this kernel's two reads by one pass: 2 tensor reads
+// less per encoder level.  H, W even, kThreads % (C/8) == 0.
+__global__ void __launch_bounds__(kThreads, 2) bn_bwd_reduce_relu_pool_bf16_kernel(
+    const __nv_bfloat16* __restrict__ x, int64_t xld, __nv_bfloat16* __restrict__ dA, int64_t dld,
+    const __nv_bfloat16* __restrict__ dpool, int64_t pld, int N, int H, int W, int C, const float* __restrict__ scale,
+    const float* __restrict__ shift, const float* __restrict__ mean, const float* __restrict__ invstd,
+    float* __restrict__ partial) {
+  GSB_PDL_ENTRY();
+  extern __shared__ float red[];  // [lanes][2][C]
+  const int G = C >> 3;
+  const int lanes = kThreads / G;
+  const int g = threadIdx.x % G, lane = threadIdx.x / G;
+  const int c0 = g * 8;
+  float s0[8], s1[8], sc[8], sh[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) s0[i] = s1[i] = 0.f;
+  load_param8(scale, c0, sc, 1.f);
+  load_param8(shift, c0, sh, 0.f);
+  const unsigned OW = (unsigned)W >> 1, OH = (unsigned)H >> 1;
+  const int64_t windows = (int64_t)N * OH * OW;
+  const int64_t step = (int64_t)gridDim.x * lanes;
+  for (int64_t wi = (int64_t)blockIdx.x * lanes + lane; wi < windows; wi += step) {
+    unsigned ox, oy, n;
+    if ((wi >> 32) == 0) {
+      const unsigned u = (unsigned)wi, row = u / OW;
+      ox = u - row * OW;
+      n = row / OH;
+      oy = row - n * OH;
+    } else {
+      const int64_t row = wi / OW;
+      ox = (unsigned)(wi - row * OW);
+      n = (unsigned)(row / OH);
+      oy = (unsigned)(row - (int64_t)n * OH);
+    }
+    const int64_t p00 = ((int64_t)n * H + 2 * oy) * W + 2 * ox;
+    uint4 rv[4], ra[4];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int64_t p = p00 + (t >> 1) * (int64_t)W + (t & 1);
+      rv[t] = *reinterpret_cast<const uint4*>(x + p * xld + c0);
+      ra[t] = *reinterpret_cast<const uint4*>(dA + p * dld + c0);
+    }
+    const uint4 rp = *reinterpret_cast<const uint4*>(dpool + wi * pld + c0);
+    const uint32_t* wp = reinterpret_cast<const uint32_t*>(&rp);
+    uint32_t outw[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float v0[4], v1[4], a0[4], a1[4];
+      int arg0 = 0, arg1 = 0;
+      float m0 = 0.f, m1 = 0.f;
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const uint32_t wv = reinterpret_cast<const uint32_t*>(&rv[t])[i];
+        v0[t] = __uint_as_float(wv << 16);
+        v1[t] = __uint_as_float(wv & 0xffff0000u);
+        // stored activation (bf16, round to nearest even) as bn_act_kernel<bf16, true> writes it
+        const float z0 = fmaf(v0[t], sc[2 * i], sh[2 * i]), z1 = fmaf(v1[t], sc[2 * i + 1], sh[2 * i + 1]);
+        a0[t] = __bfloat162float(__float2bfloat16_rn(z0 > 0.f ? z0 : 0.f));
+        a1[t] = __bfloat162float(__float2bfloat16_rn(z1 > 0.f ? z1 : 0.f));
+        if (t == 0) { m0 = a0[0]; m1 = a1[0]; }
+        else {
+          if (a0[t] > m0) { m0 = a0[t]; arg0 = t; }   // first maximum wins (maxpool2_bwd_kernel; no NaN after the ReLU)
+          if (a1[t] > m1) { m1 = a1[t]; arg1 = t; }
+        }
+      }
+      const float g0 = __uint_as_float(wp[i] << 16), g1 = __uint_as_float(wp[i] & 0xffff0000u);
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const uint32_t wa = reinterpret_cast<const uint32_t*>(&ra[t])[i];
+        float d0 = __uint_as_float(wa << 16), d1 = __uint_as_float(wa & 0xffff0000u);
+        d0 += arg0 == t ? g0 : 0.f;
+        d1 += arg1 == t ? g1 : 0.f;
+        const __nv_bfloat162 h = __floats2bfloat162_rn(d0, d1);
+        outw[t][i] = *reinterpret_cast<const uint32_t*>(&h);
+        d0 = __low2float(h);
+        d1 = __high2float(h);
+        const float e0 = a0[t] > 0.f ? d0 : 0.f, e1 = a1[t] > 0.f ? d1 : 0.f;   // z > 0 <=> stored a > 0
+        s0[2 * i] += e0;
+        s0[2 * i + 1] += e1;
+        s1[2 * i] = fmaf(e0, v0[t], s1[2 * i]);
+        s1[2 * i + 1] = fmaf(e1, v1[t], s1[2 * i + 1]);
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int64_t p = p00 + (t >> 1) * (int64_t)W + (t & 1);
+      *reinterpret_cast<uint4*>(dA + p * dld + c0) = make_uint4(outw[t][0], outw[t][1], outw[t][2], outw[t][3]);
+    }
+  }
+  {
+    float mu[8], is[8];
+    load_param8(mean, c0, mu, 0.f);
+    load_param8(invstd, c0, is, 1.f);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      red[(lane * 2 + 0) * C + c0 + i] = s0[i];
+      red[(lane * 2 + 1) * C + c0 + i] = is[i] * fmaf(-mu[i], s0[i], s1[i]);
+    }
+  }
+  __syncthreads();
+  for (int j = threadIdx.x; j < 2 * C; j += kThreads) {
+    float acc = 0.f;
+    for (int l = 0; l < lanes; ++l) acc += red[l * 2 * C + j];
+    partial[(int64_t)blockIdx.x * 2 * C + j] = acc;
+  }
+}
+
 // partial[rows][n] fp32 -> sums[n] fp64.  Block = 32 columns x 32 row lanes: coalesced 128-byte row segments,
 // four independent loads in flight per thread, fp64 accumulation, fixed summation order (deterministic).
 __global__ void __launch_bounds__(1024) reduce_partials_kernel(const float* __restrict__ partial, int rows, int n,
@@ -865,6 +978,31 @@ extern "C" int gsb_bn_bwd_partial(const gsb_view* x, const gsb_view* dA1, const 
                             workspace_bytes, rows, per_image, s))
     return -1;
   return check_launch("bn_bwd_partial");
+}
+
+// Stage 1 of the backward statistics with the MaxPool2d(2) backward folded in: dA (in / out) += route(dpool), rows of
+// [sum dy, sum dy*xhat] into `workspace`.  bf16, BatchNorm + ReLU, even h and w (the caller falls back to
+// gsb_maxpool2_bwd + gsb_bn_bwd_partial otherwise).
+extern "C" int gsb_bn_bwd_partial_pool(const gsb_view* x, const gsb_view* dA, const gsb_view* dpool, const float* scale,
+                                       const float* shift, const float* mean, const float* invstd, void* workspace,
+                                       size_t workspace_bytes, int* rows, gsb_stream s) {
+  GSB_REQUIRE(rows != nullptr && workspace != nullptr, "bn_bwd_partial_pool: null argument");
+  if (check_vec_view(x, "bn_bwd_pool.x") || check_vec_view(dA, "bn_bwd_pool.dA") || check_vec_view(dpool, "bn_bwd_pool.dpool")) return -1;
+  GSB_REQUIRE(x->dtype == GSB_BF16 && dA->dtype == GSB_BF16 && dpool->dtype == GSB_BF16, "bn_bwd_partial_pool: bf16 only");
+  GSB_REQUIRE(scale && shift && mean && invstd, "bn_bwd_partial_pool: BatchNorm parameters required");
+  GSB_REQUIRE(dA->n == x->n && dA->h == x->h && dA->w == x->w && dA->c == x->c, "bn_bwd_partial_pool: dA mismatch");
+  GSB_REQUIRE(x->h % 2 == 0 && x->w % 2 == 0 && x->h > 0 && x->w > 0, "bn_bwd_partial_pool: even height and width required");
+  GSB_REQUIRE(dpool->n == x->n && dpool->h == x->h / 2 && dpool->w == x->w / 2 && dpool->c == x->c, "bn_bwd_partial_pool: dpool mismatch");
+  const int C = x->c, lanes = kThreads / (C / 8);
+  const int64_t windows = num_pixels(dpool);
+  const int gx = grid_for(windows, lanes);
+  GSB_REQUIRE(workspace_bytes >= (size_t)gx * 2 * C * sizeof(float), "bn_bwd_partial_pool: workspace too small");
+  const size_t smem = (size_t)lanes * 2 * C * sizeof(float);
+  gsb::launch(bn_bwd_reduce_relu_pool_bf16_kernel, gsb::LaunchCfg(gx, kThreads, smem, to_stream(s)), (const __nv_bfloat16*)x->ptr, x->sw,
+              (__nv_bfloat16*)dA->ptr, dA->sw, (const __nv_bfloat16*)dpool->ptr, dpool->sw, x->n, x->h, x->w, C, scale, shift, mean,
+              invstd, reinterpret_cast<float*>(workspace));
+  *rows = gx;
+  return check_launch("bn_bwd_partial_pool");
 }
 
 static int fill_regions(PeerRegions& regs, void* const* regions, int rank, int world, int c, const char* who) {

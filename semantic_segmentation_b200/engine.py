@@ -493,13 +493,26 @@ class ConvBNAct:
 
     def backward(self, sv: Saved, dA1: torch.Tensor, dA2: Optional[torch.Tensor], need_dx: bool, need_dw: bool,
                  need_bn: bool, need_db: bool, dx_out: Optional[torch.Tensor] = None, dx_view: Optional[GsbView] = None,
-                 batch: Optional["BackwardBatch"] = None, key: Optional[str] = None):
-        """Returns (dx, dweight, dbias, dgamma, dbeta).  dx is written to dx_out / dx_view when given."""
+                 batch: Optional["BackwardBatch"] = None, key: Optional[str] = None, pool=None):
+        """Returns (dx, dweight, dbias, dgamma, dbeta).  dx is written to dx_out / dx_view when given.
+        pool = (a, dpooled): this layer's activation ``a`` feeds a MaxPool2d(2) whose gradient ``dpooled`` still has to be
+        routed into dA1 (in place): folded into the statistics pass where the layer has the plain BatchNorm + ReLU form,
+        else done by the separate max-pool backward kernel first."""
         s = self.spec
         y = sv.y
         n, oh, ow, _ = y.shape
         device = y.device
         train_bn = bool(sv.extra.get("train_bn"))
+        pool_grad = None
+        if pool is not None:
+            fusable = (pool_fusion_enabled() and train_bn and _fused_stats_mode()[0] and sv.extra.get("instance") is None
+                       and self.act1 == ACT_RELU and dA2 is None and not sv.drop_seed and sv.drop_mask is None
+                       and sv.center is None and y.dtype == torch.bfloat16 and oh % 2 == 0 and ow % 2 == 0
+                       and 256 % (s.cout // 8) == 0)
+            if fusable:
+                pool_grad = pool[1]
+            else:
+                ops.maxpool2_bwd(pool[0], pool[1], dA1, accumulate=True)
         dY = torch.empty_like(y)
         dgamma = dbeta = None
         act2 = self.act2 if self.act2 is not None else ACT_NONE
@@ -515,7 +528,7 @@ class ConvBNAct:
         elif train_bn and fused_ok:
             sums, dgamma, dbeta = ops.bn_bwd_stats(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2,
                                                    sv.drop_seed, sv.drop_mask, need_bn, peer, center=sv.center,
-                                                   drop_offset=sv.drop_offset)
+                                                   drop_offset=sv.drop_offset, pool_grad=pool_grad)
             mean, invstd = sv.mean, sv.invstd
         elif train_bn:
             sums = ops.bn_bwd_reduce(y, dA1, dA2, sv.scale, sv.shift, sv.mean, sv.invstd, self.act1, act2,

@@ -390,16 +390,22 @@ def bn_stats_finalize(partial: torch.Tensor, rows: int, c: int, count: float, ga
 
 
 def bn_bwd_stats(x, dA1, dA2, scale, shift, mean, invstd, act1, act2, drop_seed=0, drop_mask=None, want_param_grads=True,
-                 peer=None, center=None, drop_offset=0, per_image=False):
+                 peer=None, center=None, drop_offset=0, per_image=False, pool_grad=None):
     """[sum dy, sum dy*xhat] in two launches: per-block rows, then totals + dgamma / dbeta (local) + cross-rank sum.
-    -> (global sums fp64 [2c], dgamma, dbeta)."""
+    -> (global sums fp64 [2c], dgamma, dbeta).  pool_grad (BatchNorm + ReLU layers in front of a MaxPool2d(2), bf16, even
+    sizes): the pooled gradient is first routed into dA1 IN PLACE by the same pass (the max-pool backward)."""
     v = view_nhwc(x)
     ws = _bn_ws(v, x.device)
     rows = C.c_int(0)
     v2 = view_nhwc(dA2) if dA2 is not None else None
-    check(load().gsb_bn_bwd_partial(_ref(v), _ref(view_nhwc(dA1)), _ref(v2), ptr(scale), ptr(shift), ptr(center), ptr(mean),
-                                    ptr(invstd), act1, act2, int(drop_seed), int(drop_offset), ptr(drop_mask), ptr(ws),
-                                    ws.numel() * 4, C.byref(rows), int(per_image), _s(x)), "bn_bwd_partial")
+    if pool_grad is not None:
+        check(load().gsb_bn_bwd_partial_pool(_ref(v), _ref(view_nhwc(dA1)), _ref(view_nhwc(pool_grad)), ptr(scale), ptr(shift),
+                                             ptr(mean), ptr(invstd), ptr(ws), ws.numel() * 4, C.byref(rows), _s(x)),
+              "bn_bwd_partial_pool")
+    else:
+        check(load().gsb_bn_bwd_partial(_ref(v), _ref(view_nhwc(dA1)), _ref(v2), ptr(scale), ptr(shift), ptr(center), ptr(mean),
+                                        ptr(invstd), act1, act2, int(drop_seed), int(drop_offset), ptr(drop_mask), ptr(ws),
+                                        ws.numel() * 4, C.byref(rows), int(per_image), _s(x)), "bn_bwd_partial")
     cc = v.c * (v.n if per_image else 1)          # per_image: one "channel" per (image, channel)
     sums = torch.empty(2 * cc, device=x.device, dtype=torch.float64)
     dgamma = torch.empty(cc, device=x.device, dtype=torch.float32) if want_param_grads else None

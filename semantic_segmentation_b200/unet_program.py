@@ -67,11 +67,11 @@ class DoubleConvOps:
         return a1, (s0, s1)
 
     def backward(self, saved, dA, G: Dict[str, torch.Tensor], need: Dict[str, bool], need_dx: bool,
-                 dx_out=None, dx_view=None, batch=None):
+                 dx_out=None, dx_view=None, batch=None, pool=None):
         s0, s1 = saved
         p = self.prefix + ".double_conv"
         nw1, nb1 = need.get(p + ".3.weight", False), need.get(p + ".4.weight", False) or need.get(p + ".4.bias", False)
-        d0, dw, _, dg, db = self.c1.backward(s1, dA, None, True, nw1, nb1, False, batch=batch, key=p + ".3.weight")
+        d0, dw, _, dg, db = self.c1.backward(s1, dA, None, True, nw1, nb1, False, batch=batch, key=p + ".3.weight", pool=pool)
         _put(G, p + ".3.weight", dw)
         _put(G, p + ".4.weight", dg)
         _put(G, p + ".4.bias", db)
@@ -244,10 +244,12 @@ class UNetProgram:
                 _put(G, name + ".bias", db)
             dcur = dprev
         # encoder: dcur = d x5
+        pool = None
         for i in range(3, -1, -1):
-            dpooled = self.downs[i].backward(tape[f"down{i + 1}"], dcur, G, need, True, batch=batch)
-            # route through the 2x2 max-pool into the skip gradient already holding the concat part
-            ops.maxpool2_bwd(skips[i], dpooled, dskip[i], accumulate=True)
+            dpooled = self.downs[i].backward(tape[f"down{i + 1}"], dcur, G, need, True, batch=batch, pool=pool)
+            # the pooled gradient still has to go through the 2x2 max-pool into the skip gradient that already holds the
+            # concat part: the next block's BatchNorm backward statistics pass does it on the way (engine.ConvBNAct.backward)
+            pool = (skips[i], dpooled)
             dcur = dskip[i]
             if i >= 2:
                 # i == 3: decoder + bottleneck weight gradients (72 % of the parameters) are final: start their all-reduce
@@ -259,7 +261,7 @@ class UNetProgram:
         if need_dx:
             dx = torch.empty_like(tape["x"])
             dxv = view_nchw(dx)
-        self.inc.backward(tape["inc"], dcur, G, need, need_dx, dx_view=dxv, dx_out=dx, batch=batch)
+        self.inc.backward(tape["inc"], dcur, G, need, need_dx, dx_view=dxv, dx_out=dx, batch=batch, pool=pool)
         gbase = batch.gflat.untyped_storage().data_ptr()
         small = [g for g in G.values() if g is not None and g.untyped_storage().data_ptr() != gbase]
         if batch.reduce_finish(small):

@@ -304,7 +304,7 @@ def test_maxpool(dtype, hw):
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
-@pytest.mark.parametrize("shape", [(2, 64, 32, 48), (3, 24, 6, 10), (1, 512, 2, 2)])
+@pytest.mark.parametrize("shape", [(2, 64, 32, 48), (3, 32, 6, 10), (1, 512, 2, 2)])
 def test_bn_act_pool_fused(shape, dtype):
     """BatchNorm apply + ReLU + MaxPool2d(2) in one pass (unet_parts.py:21 -> :34) == the two separate kernels, bit for
     bit, with the activation written into a channel slice of a concat buffer."""
@@ -325,6 +325,39 @@ def test_bn_act_pool_fused(shape, dtype):
     assert rel(pooled_b.float(), ref) < (1e-6 if dtype == torch.float32 else 5e-3)
     with pytest.raises(RuntimeError):
         ops.bn_act_pool(y[:, :h - 1], scale, shift, cat_b[:, :h - 1, :, :c], pooled_b)
+
+
+@pytest.mark.parametrize("shape", [(2, 64, 32, 48), (3, 128, 6, 10), (1, 512, 2, 2), (8, 64, 64, 64)])
+def test_bn_bwd_stats_pool_fused(shape):
+    """MaxPool2d(2) backward folded into the BatchNorm backward statistics pass == gsb_maxpool2_bwd(accumulate) followed by
+    the plain statistics pass: the routed gradient dA bit for bit (incl. ties: ReLU zeros, first maximum wins), the sums
+    to fp32 summation order."""
+    g = torch.Generator().manual_seed(33)
+    n, c, h, w = shape
+    y = torch.randn(n, h, w, c, generator=g).to(DEV, torch.bfloat16)
+    scale = (torch.rand(c, generator=g) + 0.5).to(DEV)
+    shift = (torch.randn(c, generator=g) * 0.3).to(DEV)
+    mean = (torch.randn(c, generator=g) * 0.1).to(DEV)
+    invstd = (torch.rand(c, generator=g) + 0.5).to(DEV)
+    a = torch.empty_like(y)
+    ops.bn_act(y, scale, shift, ACT_RELU, a)
+    dcat = torch.randn(n, h, w, 2 * c, generator=g).to(DEV, torch.bfloat16)
+    dpool = torch.randn(n, h // 2, w // 2, c, generator=g).to(DEV, torch.bfloat16)
+    d_ref = dcat.clone()
+    ops.maxpool2_bwd(a, dpool, d_ref[..., :c], accumulate=True)
+    s_ref, dg_ref, db_ref = ops.bn_bwd_stats(y, d_ref[..., :c], None, scale, shift, mean, invstd, ACT_RELU, ACT_NONE)
+    d_fused = dcat.clone()
+    s_fused, dg, db = ops.bn_bwd_stats(y, d_fused[..., :c], None, scale, shift, mean, invstd, ACT_RELU, ACT_NONE, pool_grad=dpool)
+    assert torch.equal(d_ref, d_fused)
+    assert rel(s_fused, s_ref) < 2e-6 and rel(dg, dg_ref) < 2e-6 and rel(db, db_ref) < 2e-6
+    # against torch: the gradient that reaches the BatchNorm output through relu and max_pool2d
+    yt = (y.float() * scale + shift).permute(0, 3, 1, 2).clone().requires_grad_(True)
+    at = torch.relu(yt).bfloat16().float()       # argmax on the stored (bf16) activations
+    at.retain_grad()
+    F.max_pool2d(at, 2).backward(dpool.float().permute(0, 3, 1, 2))
+    routed = at.grad.permute(0, 2, 3, 1)
+    want = (dcat[..., :c].float() + routed).bfloat16()
+    assert torch.equal(d_fused[..., :c], want)
 
 
 @pytest.mark.parametrize("hw,out_hw", [((4, 4), (8, 8)), ((4, 5), (9, 11)), ((1, 3), (2, 6)), ((16, 16), (32, 32))])
@@ -607,6 +640,22 @@ def test_conv_kernels_are_deterministic(geom):
     for r in runs[1:]:
         assert torch.equal(r[0], runs[0][0]) and torch.equal(r[1], runs[0][1]) and torch.equal(r[2], runs[0][2])
     assert rel(runs[0][2], dy.double().sum((0, 1, 2))) < (1e-6 if dtype == torch.float32 else 1e-5)
+
+
+@pytest.mark.parametrize("shape", [(8, 1, 256, 256), (2, 3, 70, 90), (2, 1, 30, 30)])
+def test_bias_grad_planar_views(shape):
+    """Bias gradient of the 1..3-channel fp32 NCHW network outputs (generator's outermost ConvTranspose2d, the PatchGAN's last
+    convolution: networks.py:590,660): parallel over pixel chunks, partial rows added in order -> deterministic."""
+    from semantic_segmentation_b200._lib import view_nchw
+    g = torch.Generator().manual_seed(17)
+    d = torch.randn(shape, generator=g).to(DEV)
+    outs = []
+    for _ in range(2):
+        db = torch.full((shape[1],), 9.0, device=DEV)
+        ops.bias_grad(view_nchw(d), db)
+        outs.append(db.clone())
+    assert torch.equal(outs[0], outs[1])
+    assert rel(outs[0], d.double().sum((0, 2, 3))) < 1e-6
 
 
 THIN = [  # kind, k, stride, pad, cin, cout, n, h, w : 1..4 channels on one side (thin_conv.cu)
