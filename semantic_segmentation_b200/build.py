@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 BUILD = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libgenseg_b200.so")
-SOURCES = ["base.cu", "layout.cu", "norm.cu", "resample.cu", "loss.cu", "optim.cu", "conv_direct.cu", "thin_conv.cu", "peer.cu", "augment.cu", "edge.cu", "stem_tc.cu", "conv_tc.cu", "conv_tc_halo.cu",
+SOURCES = ["base.cu", "layout.cu", "norm.cu", "resample.cu", "loss.cu", "optim.cu", "conv_direct.cu", "thin_conv.cu", "peer.cu", "augment.cu", "edge.cu", "stem_tc.cu", "thin_tc.cu", "conv_tc.cu", "conv_tc_halo.cu",
            "conv_api.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
               "--expt-relaxed-constexpr"]

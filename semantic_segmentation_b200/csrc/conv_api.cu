@@ -4,6 +4,10 @@
 namespace gsb {
 int conv_gather_direct(const gsb_view* in, const void* wp, int wdtype, const float* bias, const gsb_view* out,
                        const gsb_conv_geom* g, int act, int accumulate, cudaStream_t st);
+int thin_tc_gather_try(const gsb_view* in, const void* wp, const float* bias, const gsb_view* out, const gsb_conv_geom* g, int act,
+                       void* scratch, size_t scratch_bytes, cudaStream_t st);
+int thin_tc_wgrad_try(const gsb_view* in, const gsb_view* dout, float* ws, int max_slices, int* used, const gsb_conv_geom* g,
+                      cudaStream_t st);
 int conv_wgrad_direct(const gsb_view* in, const gsb_view* dout, float* ws, int max_slices, int* used, const gsb_conv_geom* g,
                       cudaStream_t st);
 bool conv_tc_supported(const gsb_view* in, const gsb_view* out, const gsb_conv_geom* g);
@@ -56,6 +60,10 @@ extern "C" int gsb_conv_gather(const gsb_view* in, const void* wp, int wdtype, c
     return conv_gather_tc(in, wp, bias, out, g, act, stats_partial, stats_rows, reinterpret_cast<float*>(scratch), scratch_bytes,
                           gsb::to_stream(s));
   GSB_REQUIRE(stats_partial == nullptr || use_tc != 1, "conv_gather: stats need the tcgen05 path");
+  if (use_tc != 0 && wdtype == GSB_BF16 && !accumulate && gsb_tc_available()) {   // CW -> 1 transposed 8x8 cell (thin_tc.cu)
+    const int r = thin_tc_gather_try(in, wp, bias, out, g, act, scratch, scratch_bytes, gsb::to_stream(s));
+    if (r != 0) return r < 0 ? -1 : 0;
+  }
   return conv_gather_direct(in, wp, wdtype, bias, out, g, act, accumulate, gsb::to_stream(s));
 }
 
@@ -72,6 +80,10 @@ static int wgrad_dispatch(const gsb_view* in, const gsb_view* dout, float* ws, i
   bool tc_ok = gsb_tc_available() && conv_tc_supported(in, dout, g);
   if (use_tc == 1) GSB_REQUIRE(tc_ok, "conv_wgrad: tcgen05 path requested but shape/dtype unsupported");
   if (use_tc != 0 && tc_ok) return conv_wgrad_tc(in, dout, ws, max_slices, used, g, gsb::to_stream(s));
+  if (use_tc != 0 && gsb_tc_available()) {
+    const int r = thin_tc_wgrad_try(in, dout, ws, max_slices, used, g, gsb::to_stream(s));
+    if (r != 0) return r < 0 ? -1 : 0;
+  }
   return conv_wgrad_direct(in, dout, ws, max_slices, used, g, gsb::to_stream(s));
 }
 

@@ -59,14 +59,15 @@ parallel.shutdown()
 torch.manual_seed(77)
 G = networks.define_G(1, 1, 64, "unet_256", "batch", True, "normal", 0.02, []).to(dev).train()
 networks.upconv_arch = (1e-3 * torch.randn(8, 3, generator=torch.Generator().manual_seed(5))).to(dev).requires_grad_(True)
-m = torch.randint(0, 2, (4, 1, 256, 256), generator=torch.Generator().manual_seed(6)).float()
+GBD = max(4, int(os.environ.get("WORLD_SIZE", "1")))      # one image per rank at 8 ranks
+m = torch.randint(0, 2, (GBD, 1, 256, 256), generator=torch.Generator().manual_seed(6)).float()
 sd = {k: v.clone() for k, v in G.state_dict().items()}
 torch.manual_seed(99); G._program._calls = 0
 with torch.no_grad():
     full = G(m.to(dev))
 world = parallel.init_data_parallel(sync_bn=True)
 G.load_state_dict(sd)
-lo, hi = parallel.shard_batch(4)
+lo, hi = parallel.shard_batch(GBD)
 torch.manual_seed(99); G._program._calls = 0
 with torch.no_grad():
     part = G(m[lo:hi].to(dev))
