@@ -370,7 +370,7 @@ __global__ void __launch_bounds__(256) thin_tc_col2im_kernel(const float* __rest
 
 static bool thin_tc_enabled() {   // read per call: tests and A/B runs switch it inside one process
   const char* e = getenv("GSB_THIN_TC");
-  return e != nullptr && e[0] == '1';      // opt-in until the GPU tests of this path are green
+  return !(e != nullptr && e[0] == '0');   // on by default (GPU tests: test_thin_tc_outermost_cell, the Pix2Pix suites)
 }
 static bool thin_side_ok(const gsb_view* v) { return v->c == 1 && v->dtype == GSB_F32 && v->ptr != nullptr; }
 static bool wide_side_ok(const gsb_view* v) {   // dense pixel-linear bf16 NHWC with 64 or 128 channels

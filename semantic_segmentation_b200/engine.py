@@ -577,6 +577,12 @@ class ConvBNAct:
         return dx, dweight, dbias, dgamma, dbeta
 
 
+def _edge_tc() -> int:
+    """use_tc of the network-edge convolutions: 2 (tensor cores where a kernel exists for the shape -- the generator's CW -> 1
+    transposed 8x8 cell, thin_tc.cu -- else the thin SIMT kernels) unless the tensor-core mode is switched off."""
+    return 2 if _CONFIG["use_tc"] else 0
+
+
 class EdgeConv:
     """conv (+bias) -> act, written straight to an NCHW fp32 tensor (network outputs with 1..3
     channels: OutConv unet_parts.py:71-77, the discriminator's last conv networks.py:660, the
@@ -596,7 +602,7 @@ class EdgeConv:
             out = torch.empty((n, s.cout, oh, ow), device=x.device, dtype=torch.float32)
             wp = s.pack_fwd(weight)
             ops.conv_gather(view_nhwc(x), wp, bias, view_nchw(out), s.fwd_mode, s.k, s.stride, s.pad, act=self.act,
-                            use_tc=0)
+                            use_tc=_edge_tc())
         sv = Saved()
         if save:
             sv.x_view, sv.x_keep, sv.weight = view_nhwc(x), x, weight
@@ -624,7 +630,7 @@ class EdgeConv:
         if sv.extra.get("head") and dx_out is None:
             return ops.head_conv_bwd(sv.x_keep, sv.weight.detach().contiguous(), dout, need_dx, need_dw, need_db)
         if need_dw:
-            dweight = conv_weight_grad(s, sv.x_view, dv, device, 0)
+            dweight = conv_weight_grad(s, sv.x_view, dv, device, _edge_tc())
         if need_db:
             dbias = torch.empty(s.cout, device=device, dtype=torch.float32)
             ops.bias_grad(dv, dbias)
@@ -633,6 +639,6 @@ class EdgeConv:
             if dx_out is None:
                 dx_out = _nhwc_empty(xv.n, xv.h, xv.w, xv.c, device)
             wpb = s.pack_bwd(sv.weight)
-            ops.conv_gather(dv, wpb, None, view_nhwc(dx_out), s.bwd_mode, s.k, s.stride, s.pad, use_tc=0)
+            ops.conv_gather(dv, wpb, None, view_nhwc(dx_out), s.bwd_mode, s.k, s.stride, s.pad, use_tc=_edge_tc())
             dx = dx_out
         return dx, dweight, dbias

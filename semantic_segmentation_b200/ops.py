@@ -192,6 +192,12 @@ def conv_gather(inp: GsbView, wp: torch.Tensor, bias: Optional[torch.Tensor], ou
     if use_tc != 0 and wp.dtype == torch.bfloat16 and out.n * out.h * out.w <= 9472 and stream is None:
         # launches with a handful of tiles split their K loop over CTAs into fp32 slices of this buffer (<= 9.7 MB needed)
         scratch, sbytes = _scratch(wp.device, _SPLITK_BYTES), _SPLITK_BYTES
+    elif (use_tc != 0 and wp.dtype == torch.bfloat16 and mode == L.MODE_CONVT and k == 8 and stride == 2 and out.c == 1
+          and inp.c in (64, 128) and stream is None):
+        # the generator's CW -> 1 transposed 8x8 cell on the tensor cores (thin_tc.cu): Z[pixel][64 taps] fp32 between its
+        # GEMM and its col2im pass
+        sbytes = inp.n * inp.h * inp.w * 64 * 4
+        scratch = _scratch(wp.device, sbytes)
     check(lib.gsb_conv_gather(_ref(inp), ptr(wp), L.dtype_code(wp.dtype), ptr(bias), _ref(out), C.byref(g), act,
                               int(accumulate), use_tc, ptr(stats), C.byref(rows), ptr(scratch), sbytes,
                               stream if stream is not None else _s(wp)), "conv_gather")

@@ -675,6 +675,47 @@ def test_thin_convolutions(geom, dtype):
     assert res["fwd"] < tol and res["dgrad"] < tol and res["wgrad"] < (2e-5 if dtype == torch.float32 else 1e-4), res
 
 
+@pytest.mark.parametrize("shape", [(2, 128, 12, 10), (1, 64, 9, 17), (8, 128, 128, 128)])
+def test_thin_tc_outermost_cell(shape, monkeypatch):
+    """The generator's outermost up-cell, ConvTranspose2d(CW -> 1, 8x8 s2 p3) (networks.py:590 with the merged cell of
+    operations.py:14-39), on the tensor cores (thin_tc.cu): forward (GEMM over the 64 taps + col2im + bias + tanh), data
+    gradient and weight gradient against torch on bf16-representable operands, with the fp32 NCHW one-channel tensors the
+    engine uses, and against the SIMT thin kernels."""
+    from semantic_segmentation_b200._lib import view_nchw
+    n, cw, h, w = shape
+    g = torch.Generator().manual_seed(n * 1000 + cw + h)
+    x = torch.randn(n, cw, h, w, generator=g).bfloat16().float()
+    wt = (torch.randn(cw, 1, 8, 8, generator=g) / math.sqrt(cw * 16)).bfloat16().float()
+    bias = torch.randn(1, generator=g) * 0.1
+    x.requires_grad_(True)
+    wt.requires_grad_(True)
+    y = torch.tanh(F.conv_transpose2d(x, wt, bias, stride=2, padding=3))
+    dz = torch.randn(y.shape, generator=g).bfloat16().float()          # gradient w.r.t. the pre-activation, bf16-representable
+    F.conv_transpose2d(x, wt, bias, stride=2, padding=3).backward(dz)
+    xd = nhwc(x.detach(), torch.bfloat16)
+    wd = wt.detach().to(DEV)
+    wp, wpb = ops.pack_weight(wd, False, torch.bfloat16), ops.pack_weight(wd, True, torch.bfloat16)
+    bd = bias.to(DEV)
+    dzd = dz.to(DEV).contiguous()
+    out = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("GSB_THIN_TC", flag)
+        yd = torch.full((n, 1, 2 * h, 2 * w), 7.0, device=DEV)
+        ops.conv_gather(view_nhwc(xd), wp, bd, view_nchw(yd), MODE_CONVT, 8, 2, 3, act=ACT_TANH)
+        dxd = torch.full_like(xd, 3.0)
+        ops.conv_gather(view_nchw(dzd), wpb, None, view_nhwc(dxd), MODE_CONV, 8, 2, 3)
+        dwp = torch.zeros((64, 1, cw), device=DEV, dtype=torch.float32)
+        ops.conv_wgrad_into(view_nhwc(xd), view_nchw(dzd), dwp, MODE_CONVT, 8, 2, 3)
+        dw = ops.unpack_wgrad(dwp, (cw, 1, 8, 8), False)
+        torch.cuda.synchronize()
+        out[flag] = (yd.cpu(), from_nhwc(dxd), dw.cpu())
+    for flag in ("1", "0"):
+        yd, dx, dw = out[flag]
+        res = dict(fwd=rel(yd, y), dgrad=rel(dx, x.grad), wgrad=rel(dw, wt.grad))
+        assert res["fwd"] < 1e-5 and res["dgrad"] < 6e-3 and res["wgrad"] < 1e-4, (flag, res)
+    assert rel(out["1"][0], out["0"][0]) < 1e-5 and rel(out["1"][2], out["0"][2]) < 1e-4
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_instance_norm_batched_kernels(dtype):
     """InstanceNorm2d(affine=False) (networks.py:34-35) at batch 8 through the per-image mode of the BatchNorm kernels:
