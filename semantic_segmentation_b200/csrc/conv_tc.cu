@@ -406,13 +406,20 @@ conv_tc_wgrad_kernel(const __grid_constant__ TcMaps maps, const __grid_constant_
     for (int ch = 0; ch < BN / 32; ++ch) {
       uint32_t v[32];
       tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + ch * 32, v);
-      if (rvalid) {
+      if (rvalid && !p.a_is_in) {
+        // transposed convolutions: the thread's 32 accumulator columns are 128 contiguous bytes of its own row
+        // [tap][a_ch][nt * BN + 32 ch ..]: eight 16-byte stores (scalar stores wrote 4 bytes of every 32-byte sector per
+        // instruction: the deep generator levels ran at 0.7 TB/s of slice writes, profiles/r02p_p2p_launch_summary.txt)
+        float4* dst = reinterpret_cast<float4*>(slice + ((int64_t)tap * p.cout + a_ch) * p.cin + nt * BN + ch * 32);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
+        for (int j = 0; j < 8; ++j)
+          dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]),
+                               __uint_as_float(v[4 * j + 3]));
+      } else if (rvalid) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {   // lanes = consecutive a_ch: coalesced 128-byte rows per column
           const int b_ch = nt * BN + ch * 32 + j;
-          const int64_t idx = p.a_is_in ? ((int64_t)tap * p.cout + b_ch) * p.cin + a_ch
-                                        : ((int64_t)tap * p.cout + a_ch) * p.cin + b_ch;
-          slice[idx] = __uint_as_float(v[j]);
+          slice[((int64_t)tap * p.cout + b_ch) * p.cin + a_ch] = __uint_as_float(v[j]);
         }
       }
     }

@@ -588,13 +588,17 @@ conv_tc_wgrad_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_cons
       for (int ch = 0; ch < BN / 32; ++ch) {
         uint32_t v[32];
         tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + j * BN + ch * 32, v);
-        if (rvalid) {
+        if (rvalid && !p.a_is_in) {   // transposed convolutions: 128 contiguous bytes per thread (see conv_tc_wgrad_kernel)
+          float4* dst = reinterpret_cast<float4*>(slice + ((int64_t)tap * p.cout + a_ch) * p.cin + nt * BN + ch * 32);
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            dst[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]), __uint_as_float(v[4 * i + 2]),
+                                 __uint_as_float(v[4 * i + 3]));
+        } else if (rvalid) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
             const int b_ch = nt * BN + ch * 32 + i;
-            const int64_t idx = p.a_is_in ? ((int64_t)tap * p.cout + b_ch) * p.cin + a_ch
-                                          : ((int64_t)tap * p.cout + a_ch) * p.cin + b_ch;
-            slice[idx] = __uint_as_float(v[i]);
+            slice[((int64_t)tap * p.cout + b_ch) * p.cin + a_ch] = __uint_as_float(v[i]);
           }
         }
       }

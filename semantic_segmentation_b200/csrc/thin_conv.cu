@@ -483,12 +483,14 @@ int thin_gather_try(const gsb_view* in, const void* wp, int wdtype, const float*
     const int ppb = 256 / L;
     TView vi = tv(in), vo = tv(out);
     static const bool px_on = []() { const char* e = getenv("GSB_THIN_PX"); return !(e && e[0] == '0'); }();
-    if (px_on) {
+    constexpr int PXB = 4;
+    const int spacing = g->mode == GSB_MODE_CONV ? 1 : g->stride;
+    const int64_t wq = (out->w + spacing - 1) / spacing, xb = (wq + PXB - 1) / PXB;
+    const int64_t items = (int64_t)out->n * out->h * spacing * xb;
+    // small outputs (the PatchGAN head: 8 x 30 x 30 pixels = 120 CTAs of the blocked kernel, 81 us of latency): one pixel per
+    // lane group fills the GPU four times better
+    if (px_on && (items + ppb - 1) / ppb >= num_sms()) {
       // register-blocked kernel: 4 pixels of one row and phase per lane group
-      constexpr int PXB = 4;
-      const int spacing = g->mode == GSB_MODE_CONV ? 1 : g->stride;
-      const int64_t wq = (out->w + spacing - 1) / spacing, xb = (wq + PXB - 1) / PXB;
-      const int64_t items = (int64_t)out->n * out->h * spacing * xb;
       const int pgrid = grid_sm((items + ppb - 1) / ppb, 8);
 #define GSB_THIN_GP(T, C)                                                                                             \
   do {                                                                                                                \
@@ -576,6 +578,7 @@ int thin_wgrad_try(const gsb_view* in, const gsb_view* dout, float* dwp, int max
   const int taps = g->kh * g->kw, passes = (taps + TPr - 1) / TPr;
   const int G = in->c / 8, lanes = 256 / G;
   int grid = grid_sm((P + lanes * 16 - 1) / (lanes * 16), 2);
+  if (grid < num_sms()) grid = grid_sm((P + lanes * 4 - 1) / (lanes * 4), 2);   // small inputs: shorter pixel loops, more CTAs
   if (dwp != nullptr && grid > max_slices) grid = max_slices;
   *used = grid;
   if (dwp == nullptr) return 1;

@@ -17,7 +17,7 @@ for line in txt.splitlines():
     m = re.search(r"Function : (\S+)", line)
     if m:
         idx += 1
-        kern = re.sub(r"\(.*", "", names[idx]).replace("void gsb::", "").replace("(anonymous namespace)::", "")
+        kern = re.sub(r"\(.*", "", names[idx].replace("(anonymous namespace)::", "")).replace("void gsb::", "")
         hist.setdefault(kern, collections.Counter())
         continue
     m = re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", line)
