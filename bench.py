@@ -246,20 +246,47 @@ def run_secondary(args):
 
         for _ in range(max(args.warmup, 3)):
             wl["step"](static)
+        # Workloads whose step holds its per-step state on the device (capturable Adam, device-side dropout call count) are
+        # captured into ONE CUDA graph and replayed: the eager Pix2Pix step issues ~425 launches through ctypes and is
+        # host-bound on a slow host (13.0 against 8.4 ms of kernels, profiles/r02r_run.log).
+        graph, static_out, launches_per_step = None, None, None
+        if wl.get("graphable") and not args.no_graph and world == 1:
+            try:
+                barrier()
+                graph = torch.cuda.CUDAGraph()
+                c0 = lib.gsb_launch_count()
+                with torch.cuda.graph(graph):
+                    static_out = wl["step"](static)
+                launches_per_step = int(lib.gsb_launch_count() - c0)
+                graph.replay()
+                torch.cuda.synchronize()
+            except Exception as exc:  # pragma: no cover - reported on stderr, the run goes on eagerly
+                graph = None
+                sys.stderr.write('bench.py: CUDA graph capture failed, running eagerly: %r\n' % (exc,))
+                torch.cuda.synchronize()
+
+        def run_step():
+            if graph is not None:
+                graph.replay()
+                return static_out
+            return wl["step"](static)
+
+        for _ in range(3):
+            run_step()
         sampler = ClockSampler(local_rank)
         if rank == 0:
             sampler.start()
         l0 = lib.gsb_launch_count()
         torch.cuda.profiler.start()
-        t_dev = timed(lambda: wl["step"](static), args.steps)
+        t_dev = timed(run_step, args.steps)
         torch.cuda.profiler.stop()
-        launches = int(lib.gsb_launch_count() - l0)
+        launches = launches_per_step * args.steps if graph is not None else int(lib.gsb_launch_count() - l0)
         clocks = sampler.stop() if rank == 0 else None
 
         def e2e_step():
             for d, h in zip(static, host):
                 d.copy_(h, non_blocking=True)             # this step's inputs from pinned host memory
-            return float(wl["step"](static).item())       # and its result back to the host
+            return float(run_step().item())               # and its result back to the host
 
         e2e_step()
         t_e2e = timed(e2e_step, args.steps)
@@ -274,7 +301,7 @@ def run_secondary(args):
                            "parallelism": "dp%d" % world if args.workload != "eval" else "replicas x%d" % world,
                            "sync_bn": bool(world > 1 and not args.no_sync_bn and args.workload != "eval"),
                            "grad_comm_dtype": args.grad_comm_dtype if world > 1 and args.workload != "eval" else None,
-                           "cuda_graph": False, "l2": "per-step working set exceeds the 126 MB L2; no flush needed"},
+                           "cuda_graph": graph is not None, "l2": "per-step working set exceeds the 126 MB L2; no flush needed"},
                 "e2e": {"value": units / t_e2e, "unit": "images/s",
                         "h2d_bytes_per_step": int(sum(t.numel() * t.element_size() for t in host)) * world, "d2h_bytes_per_step": 4 * world},
                 "gpu_launches": launches, "clocks": clocks}

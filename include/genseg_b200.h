@@ -166,6 +166,12 @@ int gsb_bn_act(const gsb_view* x, const float* scale, const float* shift, const 
  * DoubleConv -> Down seam); bit-identical to gsb_bn_act(ReLU) followed by gsb_maxpool2_fwd.  Even h and w. */
 int gsb_bn_act_pool(const gsb_view* x, const float* scale, const float* shift, const gsb_view* out1, const gsb_view* pooled,
                     gsb_stream s);
+/* Explicit Dropout(0.5) keep mask (uint8 dense NHWC, the drop_mask argument of gsb_bn_act / gsb_bn_bwd_*) with the bits the
+ * fused Philox path draws for seed = (seed_k + *calls) mod 2^62 + 1 + layer_term (networks.py:604 nn.Dropout(0.5); the
+ * per-call seed rule of the generator program) -- the call count is read from device memory, so a captured CUDA graph draws a
+ * new mask at every replay.  numel, drop_offset: multiples of 8. */
+int gsb_dropout_mask(uint8_t* mask, int64_t numel, uint64_t seed_k, const int64_t* calls, uint64_t layer_term,
+                     int64_t drop_offset, gsb_stream s);
 /* Backward.  dy = act1'(z)*drop*dA1 + act2'(z)*dA2 (dA2 nullable), z as above.
  * reduce: sums[2][c] fp64 <- sum dy, sum dy*xhat.   apply (has_bn): dx = scale*(dy - s0/cnt - xhat*s1/cnt);
  * (no bn: pass mean = NULL -> dx = dy).  dgamma/dbeta accumulate (nullable). */
@@ -274,6 +280,13 @@ int gsb_rmsprop_step_multi(int n, float* const* p, const float* const* g, float*
 int gsb_adam_step_multi(int n, float* const* p, const float* const* g, float* const* exp_avg, float* const* exp_avg_sq,
                         const int64_t* numel, float lr, float beta1, float beta2, float eps, float weight_decay, int64_t step,
                         float grad_scale, gsb_stream s);
+/* Adam with the step count in DEVICE memory, for training steps replayed as a CUDA graph (torch.optim.Adam(capturable=True)
+ * semantics, pix2pix_model.py:75-78): *step_dev is the count of THIS step, advanced by gsb_counter_add before the call. */
+int gsb_adam_step_multi_dev(int n, float* const* p, const float* const* g, float* const* exp_avg, float* const* exp_avg_sq,
+                            const int64_t* numel, float lr, float beta1, float beta2, float eps, float weight_decay,
+                            const int64_t* step_dev, float grad_scale, gsb_stream s);
+/* *ctr += delta on the stream (device-side step / call counters of captured training steps). */
+int gsb_counter_add(int64_t* ctr, int64_t delta, gsb_stream s);
 
 /* ---- Device-side image chain of the GenSeg end-to-end step (running_files/train_end2end_jsrt.py:186-200).
  * gsb_minmax_f32      : ordered keys of (min, max) over the whole batch tensor (:197), keys = 2 x uint32 on the device.

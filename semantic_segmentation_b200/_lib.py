@@ -92,6 +92,9 @@ SIGNATURES = {
     "gsb_adam_step": (_i, [_p, _p, _p, _p, _i64, _f, _f, _f, _f, _f, _i64, _f, _p]),
     "gsb_rmsprop_step_multi": (_i, [_i, _p, _p, _p, _p, _p, _f, _f, _f, _f, _f, _f, _p]),
     "gsb_adam_step_multi": (_i, [_i, _p, _p, _p, _p, _p, _f, _f, _f, _f, _f, _i64, _f, _p]),
+    "gsb_adam_step_multi_dev": (_i, [_i, _p, _p, _p, _p, _p, _f, _f, _f, _f, _f, _p, _f, _p]),
+    "gsb_counter_add": (_i, [_p, _i64, _p]),
+    "gsb_dropout_mask": (_i, [_p, _i64, _u64, _p, _u64, _i64, _p]),
     "gsb_minmax_f32": (_i, [_p, _i64, _p, _p]),
     "gsb_quantize_hist": (_i, [_p, _p, _p, _p, _i, _i, _p]),
     "gsb_equalize_lut": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _p]),

@@ -900,6 +900,37 @@ extern "C" int gsb_bn_act_pool(const gsb_view* x, const float* scale, const floa
   return check_launch("bn_act_pool");
 }
 
+// Explicit Dropout(0.5) keep mask (uint8, dense NHWC, local indexing) holding exactly the bits the fused Philox path draws
+// for seed = (seed_k + *calls) mod 2^62 + 1 + layer_term -- the per-call seed rule of the generator program
+// (gan_program.py) with the CALL COUNT IN DEVICE MEMORY, so that a captured CUDA graph of the training step draws a new
+// mask at every replay (a host-side count would freeze the capture step's masks into the graph).
+namespace gsb {
+__global__ void __launch_bounds__(256) dropout_mask_kernel(uint8_t* __restrict__ mask, int64_t numel, uint64_t seed_k,
+                                                          const int64_t* __restrict__ calls, uint64_t layer_term,
+                                                          int64_t drop_offset) {
+  GSB_PDL_ENTRY();
+  const uint64_t seed = ((seed_k + (uint64_t)*calls) & ((1ull << 62) - 1)) + 1ull + layer_term;
+  const int64_t groups = numel >> 3;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < groups; i += (int64_t)gridDim.x * 256) {
+    const uint32_t bits = dropout_keep8(seed, (uint64_t)drop_offset + (uint64_t)i * 8ull);
+    uint2 r;
+    r.x = ((bits >> 0) & 1u) | (((bits >> 1) & 1u) << 8) | (((bits >> 2) & 1u) << 16) | (((bits >> 3) & 1u) << 24);
+    r.y = ((bits >> 4) & 1u) | (((bits >> 5) & 1u) << 8) | (((bits >> 6) & 1u) << 16) | (((bits >> 7) & 1u) << 24);
+    *reinterpret_cast<uint2*>(mask + i * 8) = r;
+  }
+}
+}  // namespace gsb
+
+extern "C" int gsb_dropout_mask(uint8_t* mask, int64_t numel, uint64_t seed_k, const int64_t* calls, uint64_t layer_term,
+                                int64_t drop_offset, gsb_stream s) {
+  GSB_REQUIRE(mask && calls && numel > 0 && numel % 8 == 0 && ((uintptr_t)mask & 7) == 0 && drop_offset % 8 == 0,
+              "dropout_mask: bad argument (numel and drop_offset must be multiples of 8)");
+  int64_t blocks = (numel / 8 + 255) / 256;
+  if (blocks > (int64_t)num_sms() * 8) blocks = (int64_t)num_sms() * 8;
+  gsb::launch(gsb::dropout_mask_kernel, gsb::LaunchCfg((int)blocks, 256, 0, to_stream(s)), mask, numel, seed_k, calls, layer_term, drop_offset);
+  return check_launch("dropout_mask");
+}
+
 static int check_bwd_views(const gsb_view* x, const gsb_view* dA1, const gsb_view* dA2) {
   if (check_vec_view(x, "bn_bwd.x") || check_vec_view(dA1, "bn_bwd.dA1")) return -1;
   GSB_REQUIRE(dA1->dtype == x->dtype && dA1->c == x->c && num_pixels(dA1) == num_pixels(x), "bn_bwd: dA1 mismatch");

@@ -130,9 +130,26 @@ __global__ void __launch_bounds__(256) rmsprop_multi_kernel(const __grid_constan
   }
 }
 
+// DEV: the step count lives in device memory (`step_dev`, already incremented for this step) and the bias corrections are
+// formed here -- a captured CUDA graph of the training step then advances like the eager loop (with a host-side count the
+// corrections of the capture step would be frozen into the graph).  step_size carries lr in that case.
+template <bool DEV>
 __global__ void __launch_bounds__(256) adam_multi_kernel(const __grid_constant__ OptJobs J, float step_size, float beta1,
-                                                        float beta2, float eps, float wd, float inv_sqrt_bc2, float gscale) {
+                                                        float beta2, float eps, float wd, float inv_sqrt_bc2, float gscale,
+                                                        const int64_t* __restrict__ step_dev) {
   GSB_PDL_ENTRY();
+  if (DEV) {
+    __shared__ float s_bc[2];
+    if (threadIdx.x == 0) {
+      const double t = (double)*step_dev;
+      const double bc1 = 1.0 - pow((double)beta1, t), bc2 = 1.0 - pow((double)beta2, t);
+      s_bc[0] = (float)((double)step_size / bc1);
+      s_bc[1] = (float)(1.0 / sqrt(bc2));
+    }
+    __syncthreads();
+    step_size = s_bc[0];
+    inv_sqrt_bc2 = s_bc[1];
+  }
   const int j = opt_find_job(J.blk0, J.count, blockIdx.x);
   float* __restrict__ p = J.p[j];
   const float* __restrict__ g = J.g[j];
@@ -203,6 +220,35 @@ extern "C" int gsb_adam_step_multi(int n, float* const* p, const float* const* g
   cudaStream_t st = gsb::to_stream(s);
   const float step_size = (float)(lr / bc1), isb = (float)(1.0 / sqrt(bc2));
   return gsb::run_opt_multi(n, p, g, exp_avg, exp_avg_sq, numel, true, "adam_step_multi", [&](const gsb::OptJobs& J, int blocks) {
-    gsb::launch(gsb::adam_multi_kernel, gsb::LaunchCfg(blocks, 256, 0, st), J, step_size, beta1, beta2, eps, weight_decay, isb, grad_scale);
+    gsb::launch(gsb::adam_multi_kernel<false>, gsb::LaunchCfg(blocks, 256, 0, st), J, step_size, beta1, beta2, eps, weight_decay, isb,
+                grad_scale, (const int64_t*)nullptr);
   });
+}
+
+// Adam with the step count in device memory (CUDA-graph capturable training steps): *step_dev = the count of THIS step
+// (>= 1; the caller advances it with gsb_counter_add before the call, once per optimiser step).
+extern "C" int gsb_adam_step_multi_dev(int n, float* const* p, const float* const* g, float* const* exp_avg, float* const* exp_avg_sq,
+                                       const int64_t* numel, float lr, float beta1, float beta2, float eps, float weight_decay,
+                                       const int64_t* step_dev, float grad_scale, gsb_stream s) {
+  if (n <= 0) return 0;
+  GSB_REQUIRE(p && g && exp_avg && exp_avg_sq && numel && step_dev, "adam_step_multi_dev: bad argument");
+  cudaStream_t st = gsb::to_stream(s);
+  return gsb::run_opt_multi(n, p, g, exp_avg, exp_avg_sq, numel, true, "adam_step_multi_dev", [&](const gsb::OptJobs& J, int blocks) {
+    gsb::launch(gsb::adam_multi_kernel<true>, gsb::LaunchCfg(blocks, 256, 0, st), J, lr, beta1, beta2, eps, weight_decay, 1.f, grad_scale,
+                step_dev);
+  });
+}
+
+namespace gsb {
+__global__ void counter_add_kernel(int64_t* ctr, int64_t delta) {
+  GSB_PDL_ENTRY();
+  if (threadIdx.x == 0 && blockIdx.x == 0) *ctr += delta;
+}
+}  // namespace gsb
+
+// *ctr += delta on the stream (device-side step / call counters of captured training steps)
+extern "C" int gsb_counter_add(int64_t* ctr, int64_t delta, gsb_stream s) {
+  GSB_REQUIRE(ctr != nullptr, "counter_add: null counter");
+  gsb::launch(gsb::counter_add_kernel, gsb::LaunchCfg(1, 32, 0, gsb::to_stream(s)), ctr, delta);
+  return check_launch("counter_add");
 }

@@ -28,6 +28,22 @@ def _block_prefix(level: int) -> str:
     return "model.model" if level == 1 else "model.model.1" + ".model.3" * (level - 2)
 
 
+_CAPTURABLE = {"on": None}
+
+
+def set_capturable(flag: bool) -> None:
+    """Capturable training steps (torch.cuda.graph over ``optimize_parameters``): the generator's dropout masks are drawn from
+    a call count kept in device memory (same masks as the eager path, call for call).  Also ``GSB_CAPTURABLE=1``."""
+    _CAPTURABLE["on"] = bool(flag)
+
+
+def capturable() -> bool:
+    if _CAPTURABLE["on"] is None:
+        import os
+        return os.environ.get("GSB_CAPTURABLE", "0") == "1"
+    return _CAPTURABLE["on"]
+
+
 class GeneratorProgram:
     def __init__(self, input_nc: int, output_nc: int, ngf: int = 64, use_dropout: bool = False, instance_norm: bool = False,
                  num_downs: int = 8):
@@ -77,6 +93,8 @@ class GeneratorProgram:
         names.append(ARCH_KEY)
         self.param_names = names
         self._calls = 0
+        self._calls_dev = None        # capturable mode: the call count in device memory (int64 scalar)
+        self._calls_mirror = None     # the host count the device counter was last known to equal
 
     @staticmethod
     def _bn(P, B, p: str):
@@ -117,6 +135,28 @@ class GeneratorProgram:
         # one seed per forward call, the same on every rank (same torch seed, same call count); the masks are indexed by the
         # GLOBAL element index (engine.first_global_sample), so a batch sharded over N ranks draws the one-rank masks
         base_seed = int((extra or {}).get("drop_seed", 0)) or (torch.initial_seed() * 1000003 + self._calls) % (1 << 62) + 1
+        if (capturable() and training and masks is None and not int((extra or {}).get("drop_seed", 0))
+                and any(self.up[L].dropout for L in range(1, D))):
+            # CUDA-graph capturable dropout: the call count lives in device memory and explicit keep masks holding exactly
+            # the bits of the seed rule above are drawn from it by a kernel, so every REPLAY of a captured step draws new
+            # masks (with the host-side count the capture step's masks would be frozen into the graph)
+            if self._calls_dev is None or self._calls_dev.device != dev:
+                self._calls_dev = torch.zeros((), device=dev, dtype=torch.int64)
+                self._calls_mirror = None
+            if self._calls_mirror is None or self._calls != self._calls_mirror + 1:
+                self._calls_dev.fill_(self._calls - 1)          # first use, or somebody re-seeded the host count
+            ops.counter_add(self._calls_dev, 1)
+            self._calls_mirror = self._calls
+            seed_k = (torch.initial_seed() * 1000003) % (1 << 62)
+            from .engine import first_global_sample
+            masks = []
+            for L in range(4, D):                               # masks[L - 4] belongs to level L (levels without dropout: None)
+                if L < D and self.up[L].dropout:
+                    oh, ow = h >> L, w >> L                      # output of up-cell L = spatial size of level L
+                    masks.append(ops.dropout_mask((n, oh, ow, self.c[L]), dev, seed_k, self._calls_dev, 7919 * L,
+                                                  first_global_sample(n) * oh * ow * self.c[L]))
+                else:
+                    masks.append(None)
         tape: Dict[str, object] = {"x": x, "arch": arch}
         c = self.c
         sizes = [(h, w)] + [(h >> L, w >> L) for L in range(1, D + 1)]      # sizes[L] = spatial of e_L

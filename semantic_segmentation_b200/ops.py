@@ -561,6 +561,30 @@ def adam_step_multi(ps, gs, ms, vs, lr, beta1, beta2, eps, weight_decay, step, g
                                      beta2, eps, weight_decay, int(step), grad_scale, _s(ps[0])), "adam_step_multi")
 
 
+def adam_step_multi_dev(ps, gs, ms, vs, lr, beta1, beta2, eps, weight_decay, step_dev: torch.Tensor, grad_scale=1.0) -> None:
+    """Adam with the step count in device memory (int64 scalar tensor, already advanced for this step): capturable."""
+    if not ps:
+        return
+    n = _atype(C.c_int64, len(ps))(*[p.numel() for p in ps])
+    check(load().gsb_adam_step_multi_dev(len(ps), _ptr_array(ps), _ptr_array(gs), _ptr_array(ms), _ptr_array(vs), n, lr, beta1,
+                                         beta2, eps, weight_decay, ptr(step_dev), grad_scale, _s(ps[0])), "adam_step_multi_dev")
+
+
+def counter_add(ctr: torch.Tensor, delta: int = 1) -> None:
+    """ctr (int64 scalar on the device) += delta, on the stream."""
+    assert ctr.dtype == torch.int64 and ctr.is_cuda
+    check(load().gsb_counter_add(ptr(ctr), int(delta), _s(ctr)), "counter_add")
+
+
+def dropout_mask(shape, device, seed_k: int, calls: torch.Tensor, layer_term: int, drop_offset: int) -> torch.Tensor:
+    """uint8 keep mask [n, h, w, c] with the Philox bits of seed (seed_k + calls) mod 2^62 + 1 + layer_term (calls: int64
+    device scalar)."""
+    mask = torch.empty(tuple(shape), device=device, dtype=torch.uint8)
+    check(load().gsb_dropout_mask(ptr(mask), mask.numel(), int(seed_k) & ((1 << 64) - 1), ptr(calls), int(layer_term),
+                                  int(drop_offset), _s(mask)), "dropout_mask")
+    return mask
+
+
 # --- device-side image chain of the end-to-end step (csrc/augment.cu) -----------------------------------
 def minmax_f32(x: torch.Tensor) -> torch.Tensor:
     """Ordered keys of (min, max) over a contiguous fp32 CUDA tensor -> int32[2] on the device (opaque; feed to quantize_hist)."""

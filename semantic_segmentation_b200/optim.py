@@ -72,13 +72,42 @@ class RMSprop(Optimizer):
 
 
 class Adam(Optimizer):
-    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, amsgrad=False, foreach=None):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, amsgrad=False, foreach=None,
+                 capturable=False):
         if amsgrad:
             raise NotImplementedError("genseg_b200: amsgrad is not on the B200 path (the reference does not use it)")
         if lr < 0.0 or eps < 0.0 or not 0.0 <= betas[0] < 1.0 or not 0.0 <= betas[1] < 1.0 or weight_decay < 0.0:
             raise ValueError("invalid Adam hyper-parameter")
         super().__init__(params, dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=weight_decay))
         self.grad_scale = 1.0
+        # capturable (torch.optim.Adam's flag): the step count lives in device memory (one int64 scalar per parameter
+        # group, state["step"] of every parameter refers to it) and the kernel forms the bias corrections from it, so a
+        # training step captured into a CUDA graph advances at every replay
+        self.capturable = bool(capturable)
+        self._step_dev = {}
+
+    def _step_capturable(self, gi: int, group) -> None:
+        params = [p for p in group["params"] if p.grad is not None]
+        if not params:
+            return
+        ctr = self._step_dev.get(gi)
+        if ctr is None:
+            t0 = max([int(self.state[p].get("step", 0)) for p in params if "exp_avg" in self.state[p]] or [0])
+            ctr = self._step_dev[gi] = torch.full((), t0, device=params[0].device, dtype=torch.int64)
+        ps, gs, ms, vs = [], [], [], []
+        for p in params:
+            st = self.state[p]
+            if "exp_avg" not in st:
+                st["exp_avg"] = torch.zeros_like(p)
+                st["exp_avg_sq"] = torch.zeros_like(p)
+            st["step"] = ctr
+            ps.append(p.data)
+            gs.append(_grad(p))
+            ms.append(st["exp_avg"])
+            vs.append(st["exp_avg_sq"])
+        ops.counter_add(ctr, 1)
+        ops.adam_step_multi_dev(ps, gs, ms, vs, float(group["lr"]), group["betas"][0], group["betas"][1], group["eps"],
+                                group["weight_decay"], ctr, self.grad_scale)
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -87,6 +116,10 @@ class Adam(Optimizer):
             with torch.enable_grad():
                 loss = closure()
         _require_cuda(self.param_groups)
+        if self.capturable:
+            for gi, group in enumerate(self.param_groups):
+                self._step_capturable(gi, group)
+            return loss
         for group in self.param_groups:
             by_step = {}                                   # bias correction depends on the step count: one launch per count
             for p in group["params"]:

@@ -279,3 +279,80 @@ def run_pix2pix_raw(name, golden_dir):
     finally:
         networks.upconv_arch = old_arch
         S.set_precision("bf16")
+
+
+def _p2p_trainer(capturable):
+    """Pix2Pix optimize_parameters (pix2pix_model.py:132-143) on a seeded unet_256 generator WITH dropout + PatchGAN, Adam
+    (lr 2e-4, beta1 0.5) -- `capturable`: Adam's step count and the generator's dropout call count in device memory."""
+    from semantic_segmentation_b200 import gan_program, optim
+    gan_program.set_capturable(capturable)
+    torch.manual_seed(4242)
+    G = networks.define_G(1, 1, 64, "unet_256", "batch", True, "normal", 0.02, [])
+    D = networks.define_D(2, 64, "basic", 3, "batch", "normal", 0.02, [])
+    G.load_state_dict(O.seeded_state(O.generator_state_spec(1, 1, 64, 8), 11, conv_std=0.02), strict=True)
+    D.load_state_dict(O.seeded_state(O.discriminator_state_spec(2, 64, 3), 12, conv_std=0.02), strict=True)
+    G, D = G.to(DEV).train(), D.to(DEV).train()
+    crit = networks.GANLoss("vanilla").to(DEV)
+    optG = optim.Adam(list(G.parameters()), lr=2e-4, betas=(0.5, 0.999), capturable=capturable)
+    optD = optim.Adam(list(D.parameters()), lr=2e-4, betas=(0.5, 0.999), capturable=capturable)
+    g = torch.Generator().manual_seed(14)
+    mask = torch.randint(0, 2, (1, 1, 256, 256), generator=g).float().to(DEV)
+    image = torch.rand(1, 1, 256, 256, generator=g).to(DEV)
+    pD = list(D.parameters())
+
+    def step():
+        fake = G(mask)
+        for p in pD:
+            p.requires_grad_(True)
+        optD.zero_grad()
+        loss_D = 0.5 * (crit(D(torch.cat([mask, fake], 1).detach()), False) + crit(D(torch.cat([mask, image], 1)), True))
+        loss_D.backward()
+        optD.step()
+        for p in pD:
+            p.requires_grad_(False)
+        optG.zero_grad()
+        loss_G = crit(D(torch.cat([mask, fake], 1)), True) + networks.l1_loss(fake, image) * 100.0
+        loss_G.backward()
+        optG.step()
+        return loss_G.detach()
+
+    return G, D, step
+
+
+def test_pix2pix_step_replays_as_cuda_graph():
+    """The whole optimize_parameters step captured into ONE CUDA graph (capturable Adam: step count in device memory;
+    dropout: call count in device memory, explicit masks with the bits of the eager seed rule) and replayed three times
+    == five eager steps of the non-capturable path: same dropout masks call for call, same bias corrections."""
+    S.set_precision("bf16")
+    old_arch = networks.upconv_arch
+    from semantic_segmentation_b200 import gan_program
+    try:
+        networks.upconv_arch = (1e-3 * torch.randn(8, 3, generator=torch.Generator().manual_seed(5))).to(DEV).requires_grad_(True)
+        Ga, Da, step_a = _p2p_trainer(False)
+        la = [float(step_a()) for _ in range(5)]
+        ref = {k: v.detach().clone() for k, v in list(Ga.state_dict().items()) + [("D." + k, v) for k, v in Da.state_dict().items()]}
+        networks.upconv_arch = (1e-3 * torch.randn(8, 3, generator=torch.Generator().manual_seed(5))).to(DEV).requires_grad_(True)
+        Gb, Db, step_b = _p2p_trainer(True)
+        lb = [float(step_b()) for _ in range(2)]                 # eager steps 1, 2 (capturable path)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            out = step_b()                                       # captured, not executed
+        for _ in range(3):                                       # steps 3, 4, 5
+            graph.replay()
+            lb.append(float(out))
+        torch.cuda.synchronize()
+        got = {k: v.detach().clone() for k, v in list(Gb.state_dict().items()) + [("D." + k, v) for k, v in Db.state_dict().items()]}
+        assert la[0] == lb[0], (la, lb)                          # the capturable path draws the very same dropout masks
+        for a, b in zip(la, lb):
+            assert abs(a - b) <= 1e-4 * max(1.0, abs(a)), (la, lb)
+        for k, v in ref.items():
+            if v.dtype.is_floating_point:
+                err = float((got[k].double() - v.double()).norm() / v.double().norm().clamp_min(1e-30))
+                assert err < 1e-5, (k, err)                      # host pow vs device pow in the bias correction: <= 1 ulp of lr
+            else:
+                assert torch.equal(got[k], v), k                 # num_batches_tracked: 5 forward passes on both sides
+    finally:
+        gan_program.set_capturable(False)
+        networks.upconv_arch = old_arch
+        S.set_precision("bf16")

@@ -28,26 +28,27 @@ def _lung_masks(batch):
     return lungs.float()[None, None].repeat(batch, 1, 1, 1).contiguous()
 
 
-def _gan_models(dev, world):
+def _gan_models(dev, world, capturable=False):
     import semantic_segmentation_b200 as S
-    from semantic_segmentation_b200 import parallel
+    from semantic_segmentation_b200 import gan_program, parallel
     from semantic_segmentation_b200.models_pix2pix import networks
     from semantic_segmentation_b200.optim import Adam
     S.set_precision("bf16")
+    gan_program.set_capturable(capturable)      # dropout call count in device memory: the step can be replayed as a CUDA graph
     torch.manual_seed(1234)                      # init_weights draws N(0, 0.02) from torch's generator: same on every rank
     G = networks.define_G(1, 1, 64, "unet_256", "batch", True, "normal", 0.02, [])
     D = networks.define_D(2, 64, "basic", 3, "batch", "normal", 0.02, [])
     G, D = G.to(dev).train(), D.to(dev).train()
     networks.upconv_arch = (1e-3 * torch.randn(8, 3, generator=torch.Generator().manual_seed(5))).to(dev).requires_grad_(True)
     crit = networks.GANLoss("vanilla").to(dev)
-    optG = Adam(list(G.parameters()), lr=2e-5, betas=(0.5, 0.999))
-    optD = Adam(list(D.parameters()), lr=2e-5, betas=(0.5, 0.999))
+    optG = Adam(list(G.parameters()), lr=2e-5, betas=(0.5, 0.999), capturable=capturable)
+    optD = Adam(list(D.parameters()), lr=2e-5, betas=(0.5, 0.999), capturable=capturable)
     optG.grad_scale = optD.grad_scale = 1.0 / world      # GANLoss / L1 are means over the rank's shard
     return networks, parallel, G, D, crit, optG, optD
 
 
 def pix2pix(dev, per, rank, world):
-    networks, parallel, G, D, crit, optG, optD = _gan_models(dev, world)
+    networks, parallel, G, D, crit, optG, optD = _gan_models(dev, world, capturable=True)
     g = torch.Generator().manual_seed(14 + rank)
     host = (torch.randint(0, 2, (per, 1, 256, 256), generator=g).float().pin_memory(),
             torch.rand(per, 1, 256, 256, generator=g).pin_memory())
@@ -72,7 +73,7 @@ def pix2pix(dev, per, rank, world):
         optG.step()
         return loss_G.detach()
 
-    return dict(step=step, host_batch=host, units=per, graphable=False,
+    return dict(step=step, host_batch=host, units=per, graphable=True,
                 metric="Pix2Pix optimize_parameters images/sec @256^2 (unet_256 G + 70x70 PatchGAN D, GANLoss + 100*L1, Adam, bf16)",
                 workload="Pix2Pix optimize_parameters (models_pix2pix/pix2pix_model.py:132-143): G fwd, D step, G step; "
                          "define_G(1,1,64,'unet_256','batch',dropout) + define_D(2,64,'basic'), %d images per GPU" % per,
