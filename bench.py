@@ -250,7 +250,7 @@ def run_secondary(args):
         # captured into ONE CUDA graph and replayed: the eager Pix2Pix step issues ~425 launches through ctypes and is
         # host-bound on a slow host (13.0 against 8.4 ms of kernels, profiles/r02r_run.log).
         graph, static_out, launches_per_step = None, None, None
-        if wl.get("graphable") and not args.no_graph and world == 1:
+        if wl.get("graphable") and not args.no_graph:
             try:
                 barrier()
                 graph = torch.cuda.CUDAGraph()

@@ -89,21 +89,22 @@ def genseg(dev, per, rank, world):
     from semantic_segmentation_b200.unet import UNet
     from semantic_segmentation_b200.util import augment
     from semantic_segmentation_b200.util.dice_score import seg_loss
-    networks, parallel, G, D, crit, optG, optD = _gan_models(dev, world)
+    networks, parallel, G, D, crit, optG, optD = _gan_models(dev, world, capturable=True)
     torch.manual_seed(4321)
     net = UNet(1, 1, False).to(dev).train()          # --classes 1, ConvTranspose2d U-Net (scripts/train_end2end_jsrt.sh)
     pU = list(net.parameters())
     optU = RMSprop(pU, lr=1e-5, weight_decay=1e-8, momentum=0.9)       # seg_loss is a global-batch mean: grad_scale 1
     g = torch.Generator().manual_seed(14 + rank)
     mask = _lung_masks(per)
+    # the affine matrices of the mask augmentation are part of the batch (drawn on the host like the images), so the whole
+    # iteration reads only device-resident inputs and can be replayed as one CUDA graph
     host = (mask.pin_memory(), torch.rand(per, 1, 256, 256, generator=g).pin_memory(),
-            torch.rand(per, 1, 256, 256, generator=g).pin_memory())
-    mats = [augment.draw_affine(per, 256, 256, torch.Generator().manual_seed(100 + 8 * rank + i)).to(dev) for i in range(8)]
-    state = {"i": 0}
+            torch.rand(per, 1, 256, 256, generator=g).pin_memory(),
+            augment.draw_affine(per, 256, 256, torch.Generator().manual_seed(100 + 8 * rank)).pin_memory())
     pG, pD = list(G.parameters()), list(D.parameters())
 
     def step(batch):
-        mask, image, val_image = batch
+        mask, image, val_image, mat = batch
         for p in pD:                                   # Generator problem (train_end2end_jsrt.py:141-155)
             p.requires_grad_(False)
         optG.zero_grad()
@@ -123,8 +124,7 @@ def genseg(dev, per, rank, world):
         optD.step()
         optU.zero_grad()                               # Unet problem (:177-232): real batch + generated batch
         loss = seg_loss(net(image), mask.long())
-        fake_mask = augment.augment_masks(mask, mats[state["i"] % len(mats)])
-        state["i"] += 1
+        fake_mask = augment.augment_masks(mask, mat)
         with torch.no_grad():
             fake_image = augment.synth_image_postprocess(G(fake_mask))
         fake_loss = seg_loss(net(fake_image), fake_mask.long())
@@ -135,7 +135,7 @@ def genseg(dev, per, rank, world):
         seg_loss(net(vi), mask.long()).backward()
         return loss_G.detach()
 
-    return dict(step=step, host_batch=host, units=per, graphable=False,
+    return dict(step=step, host_batch=host, units=per, graphable=True,
                 metric="GenSeg end-to-end iteration, real images/sec @256^2 (G step + D step + U-Net step on real + generated batch "
                        "+ Arch training_step, bf16)",
                 workload="GenSeg end-to-end iteration (running_files/train_end2end_jsrt.py:141-236), %d real images per GPU; the "
