@@ -104,6 +104,12 @@ int gsb_unmerge_upconv(const float* dw_merged, const float* db_merged, const flo
 int gsb_conv_gather(const gsb_view* in, const void* wp, int wdtype, const float* bias, const gsb_view* out,
                     const gsb_conv_geom* g, int act, int accumulate, int use_tc, float* stats_partial,
                     int* stats_rows, void* scratch, size_t scratch_bytes, gsb_stream s);
+/* Convolution with a per-channel affine epilogue, out = act(conv(in) * scale[co] + shift[co]): eval-mode Conv2d -> BatchNorm2d
+ * (running statistics) -> ReLU of unet_parts.py:16-21 as ONE pass.  0 = launched, 1 = not applicable for this shape (the
+ * caller then runs gsb_conv_gather + gsb_bn_act), -1 = error.  bf16 packed weights, forward convolutions on the tcgen05
+ * halo kernel (tiled space >= 16 x 16) only; out may be a channel slice of a wider NHWC buffer. */
+int gsb_conv_gather_affine(const gsb_view* in, const void* wp, int wdtype, const float* scale, const float* shift,
+                           const gsb_view* out, const gsb_conv_geom* g, int act, gsb_stream s);
 size_t gsb_conv_stats_rows(const gsb_view* out, const gsb_conv_geom* g);
 /* Weight gradient: sum_pixels dout[pix][cout] * in[pix@tap][cin], with the forward op's gather mode.  The pixel range is
  * split over CTAs; split i STORES its partial sums into slice i of ws[max_slices][kh*kw][cout][cin] (fp32, every used slice

@@ -49,6 +49,7 @@ SIGNATURES = {
     "gsb_merge_upconv": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _i, _p, _p, _p]),
     "gsb_unmerge_upconv": (_i, [_p] * 9 + [_i, _i] + [_p] * 7 + [_p, _sz, _p]),
     "gsb_conv_gather": (_i, [_VP, _p, _i, _p, _VP, _GP, _i, _i, _i, _p, _p, _p, _sz, _p]),
+    "gsb_conv_gather_affine": (_i, [_VP, _p, _i, _p, _p, _VP, _GP, _i, _p]),
     "gsb_conv_stats_rows": (_sz, [_VP, _GP]),
     "gsb_conv_wgrad_plan": (_i, [_VP, _VP, _GP, _i]),
     "gsb_conv_wgrad": (_i, [_VP, _VP, _p, _i, _p, _GP, _i, _p]),

@@ -12,7 +12,7 @@ int conv_wgrad_direct(const gsb_view* in, const gsb_view* dout, float* ws, int m
                       cudaStream_t st);
 bool conv_tc_supported(const gsb_view* in, const gsb_view* out, const gsb_conv_geom* g);
 int conv_gather_tc(const gsb_view* in, const void* wp, const float* bias, const gsb_view* out, const gsb_conv_geom* g, int act,
-                   float* stats, int* stats_rows, float* scratch, size_t scratch_bytes, cudaStream_t st);
+                   float* stats, int* stats_rows, float* scratch, size_t scratch_bytes, cudaStream_t st, const float* scale = nullptr);
 int conv_wgrad_tc(const gsb_view* in, const gsb_view* dout, float* ws, int max_slices, int* used, const gsb_conv_geom* g,
                   cudaStream_t st);
 int conv_tc_m_tiles(const gsb_view* out);
@@ -65,6 +65,22 @@ extern "C" int gsb_conv_gather(const gsb_view* in, const void* wp, int wdtype, c
     if (r != 0) return r < 0 ? -1 : 0;
   }
   return conv_gather_direct(in, wp, wdtype, bias, out, g, act, accumulate, gsb::to_stream(s));
+}
+
+// Convolution with a per-channel affine epilogue: out = act(conv(in) * scale[co] + shift[co]) -- inference with the BatchNorm
+// of running statistics folded into the producing kernel (unet_parts.py:16-21 in eval mode: Conv -> BN -> ReLU is one pass,
+// the normalised activation is never read back).  Returns 0 = launched, 1 = not applicable for this shape (the caller runs
+// gsb_conv_gather + gsb_bn_act), -1 = error.  bf16 weights, tcgen05 halo kernel only (mode CONV, tiled space >= 16 x 16).
+extern "C" int gsb_conv_gather_affine(const gsb_view* in, const void* wp, int wdtype, const float* scale, const float* shift,
+                                      const gsb_view* out, const gsb_conv_geom* g, int act, gsb_stream s) {
+  if (check_geom(g)) return -1;
+  GSB_REQUIRE(in && out && wp && scale && in->ptr && out->ptr, "conv_gather_affine: null argument");
+  GSB_REQUIRE(in->n == out->n, "conv_gather_affine: batch mismatch");
+  if (g->mode != GSB_MODE_CONV || wdtype != GSB_BF16 || !gsb_tc_available() || !conv_tc_supported(in, out, g)) return 1;
+  GSB_REQUIRE(out->h == out_extent(GSB_MODE_CONV, in->h, g->kh, g->stride, g->pad) &&
+                  out->w == out_extent(GSB_MODE_CONV, in->w, g->kw, g->stride, g->pad),
+              "conv_gather_affine: output extent %dx%d does not match conv of %dx%d", out->h, out->w, in->h, in->w);
+  return conv_gather_tc(in, wp, shift, out, g, act, nullptr, nullptr, nullptr, 0, gsb::to_stream(s), scale);
 }
 
 // Weight gradient, deterministic split reduction: the launch writes `*used_slices` complete fp32 slices

@@ -438,7 +438,8 @@ conv_tc_wgrad_kernel(const __grid_constant__ TcMaps maps, const __grid_constant_
 bool conv_halo_applicable(const SubView& outv);
 int conv_halo_m_tiles(int w, int h, int n);
 int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, const TcTaps& taps, const void* wp, int taps_total,
-                    int cin, int cout, const float* bias, int act, float* stats, int* stats_rows, cudaStream_t st);
+                    int cin, int cout, const float* bias, int act, float* stats, int* stats_rows, cudaStream_t st,
+                    const float* scale = nullptr);
 int conv_halo_wgrad(const SubView& tiled, const SubView* shifted, int nmaps, const TcTaps& taps, int shifted_c, int a_is_in,
                     int cin, int cout, int taps_total, float* ws, int max_slices, int* used, cudaStream_t st);
 
@@ -499,11 +500,12 @@ static int launch_tc(Kern kern, int grid_x, int grid_y, int smem, const TcMaps& 
 // One fprop-style launch over a tiled output (sub)view.
 static int fprop_launch(const SubView& outv, const SubView* shifted, int nmaps, const TcTaps& taps, const void* wp, int taps_total,
                         int cin, int cout, const float* bias, int act, float* stats, int* stats_rows, float* scratch,
-                        size_t scratch_bytes, cudaStream_t st) {
+                        size_t scratch_bytes, cudaStream_t st, const float* scale = nullptr) {
   {  // halo-stationary kernel first (16x16 tiles, operand reuse across vertical taps); falls through when not applicable
-    int r = conv_halo_fprop(outv, shifted, nmaps, taps, wp, taps_total, cin, cout, bias, act, stats, stats_rows, st);
+    int r = conv_halo_fprop(outv, shifted, nmaps, taps, wp, taps_total, cin, cout, bias, act, stats, stats_rows, st, scale);
     if (r != 0) return r < 0 ? -1 : 0;
   }
+  if (scale != nullptr) return 1;   // the per-channel factor exists in the halo kernel's epilogue only: not applicable
   TcMaps maps;
   memset(&maps, 0, sizeof(maps));
   int tw, th, tn;
@@ -564,8 +566,9 @@ static int fprop_launch(const SubView& outv, const SubView* shifted, int nmaps, 
 static int floor_div(int a, int b) { return (a >= 0) ? a / b : -((-a + b - 1) / b); }
 
 int conv_gather_tc(const gsb_view* in, const void* wp, const float* bias, const gsb_view* out, const gsb_conv_geom* g, int act,
-                   float* stats, int* stats_rows, float* scratch, size_t scratch_bytes, cudaStream_t st) {
+                   float* stats, int* stats_rows, float* scratch, size_t scratch_bytes, cudaStream_t st, const float* scale) {
   const int s = g->stride, taps_total = g->kh * g->kw;
+  if (scale != nullptr && g->mode != GSB_MODE_CONV) return 1;   // (returns 1 = "scaled epilogue not applicable")
   GSB_REQUIRE(stats == nullptr || !(g->mode == GSB_MODE_CONVT && s > 1), "conv_tc: fused BN statistics unsupported for strided transposed conv");
   if (g->mode == GSB_MODE_CONV) {
     // iy = oy*s - pad + ky = s*(oy + a) + par
@@ -590,7 +593,8 @@ int conv_gather_tc(const gsb_view* in, const void* wp, const float* bias, const 
       }
     GSB_REQUIRE(taps.ntaps > 0, "conv_tc: no taps");
     SubView ov = subview(out, 1, 0, 0);
-    return fprop_launch(ov, subs, nmaps, taps, wp, taps_total, in->c, out->c, bias, act, stats, stats_rows, scratch, scratch_bytes, st);
+    return fprop_launch(ov, subs, nmaps, taps, wp, taps_total, in->c, out->c, bias, act, stats, stats_rows, scratch, scratch_bytes, st,
+                        scale);
   }
   // transposed-conv gather: one launch per output parity
   for (int py = 0; py < s; ++py)

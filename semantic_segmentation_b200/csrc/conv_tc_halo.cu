@@ -44,6 +44,7 @@ struct HaloParams {
   int pw, full;          // box width in pixels; full = 1: ONE box per 64-channel block serves every (dx, dy) tap
   int act;
   const float* bias;
+  const float* scale;    // optional per-channel factor applied before the bias (inference: BatchNorm folded into the epilogue)
   float* stats;          // [2*spatial_tiles][2][cout] or null
 };
 
@@ -328,7 +329,7 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
     constexpr int CPW = OUT_COLS / 64;   // 32-column chunks per warp and staging pass
     const float slope = p.act == GSB_ACT_RELU ? 0.f : (p.act == GSB_ACT_LRELU ? 0.2f : 1.f);
     const bool is_tanh = p.act == GSB_ACT_TANH;
-    const bool simple = p.bias == nullptr && p.act == GSB_ACT_NONE;
+    const bool simple = p.bias == nullptr && p.scale == nullptr && p.act == GSB_ACT_NONE;
     const uint32_t so = smem_u32(s_out), sr = smem_u32(s_red), sacc = smem_u32(s_acc);
     uint32_t acc = 0, acc_phase = 0;
     if (p.stats != nullptr) {
@@ -376,6 +377,10 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
                 float f0 = __uint_as_float(v[g * 8 + 2 * e]), f1 = __uint_as_float(v[g * 8 + 2 * e + 1]);
+                if (p.scale != nullptr) {
+                  f0 *= __ldg(p.scale + cbase + g * 8 + 2 * e);
+                  f1 *= __ldg(p.scale + cbase + g * 8 + 2 * e + 1);
+                }
                 if (p.bias != nullptr) {
                   f0 += __ldg(p.bias + cbase + g * 8 + 2 * e);
                   f1 += __ldg(p.bias + cbase + g * 8 + 2 * e + 1);
@@ -713,7 +718,8 @@ int conv_halo_m_tiles(int w, int h, int n) {  // upper bound on the statistics r
 
 // Returns 1 when the launch was issued, 0 when the tap structure does not fit (caller falls back), -1 on error.
 int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, const TcTaps& taps, const void* wp, int taps_total,
-                    int cin, int cout, const float* bias, int act, float* stats, int* stats_rows, cudaStream_t st) {
+                    int cin, int cout, const float* bias, int act, float* stats, int* stats_rows, cudaStream_t st,
+                    const float* scale) {
   if (!conv_halo_applicable(outv)) return 0;
   HaloPlan plan;
   int max_ndy;
@@ -796,7 +802,7 @@ int conv_halo_fprop(const SubView& outv, const SubView* shifted, int nmaps, cons
   }
   p.nA = nA > 4 ? 4 : nA;
   GSB_REQUIRE(p.nA >= 2, "conv_halo: shared memory budget");
-  p.act = act; p.bias = bias; p.stats = stats;
+  p.act = act; p.bias = bias; p.scale = scale; p.stats = stats;
   const int smem = fixed + p.nA * p.a_stride + p.nB * p.tb * b_bytes;
   const int max_clusters = num_sms_avail() / CL;
   const int grid = (p.num_tiles < max_clusters ? p.num_tiles : max_clusters) * CL;

@@ -184,6 +184,12 @@ def pool_fusion_enabled() -> bool:
     return os.environ.get("GSB_POOL_FUSION", "1") != "0"
 
 
+def eval_fold_enabled() -> bool:
+    """Inference: BatchNorm (running statistics) + activation folded into the convolution's epilogue (``GSB_EVAL_FOLD=0``: off)."""
+    import os
+    return os.environ.get("GSB_EVAL_FOLD", "1") != "0"
+
+
 def wgrad_stream_enabled() -> bool:
     """Weight-gradient kernels on a second stream (default on; ``GSB_WGRAD_STREAM=0`` switches it off): see BackwardBatch.side."""
     import os
@@ -407,8 +413,22 @@ class ConvBNAct:
         layer is the plain BatchNorm + ReLU form (``sv.extra['pooled']`` tells the caller whether it was written)."""
         s = self.spec
         oh, ow = s.out_hw(h, w)
-        y = _nhwc_empty(n, oh, ow, s.cout, device)
         stem = _is_stem(s, x_view, x_keep)
+        if (not training and not save and self.has_bn and not self.instance and self.act2 is None and bias is None
+                and not stem and s.kind == "conv" and _CONFIG["use_tc"] and act_dtype() == torch.bfloat16
+                and not centered_bn() and eval_fold_enabled()):
+            # inference: BatchNorm of the running statistics folded into the convolution's epilogue -- Conv -> BN -> act is ONE
+            # pass, the pre-normalisation tensor is never written (nothing is saved: no backward through this call)
+            gamma, beta, rm, rv, nbt = bn
+            scale, shift, _m, _i = ops.bn_finalize(None, float(n * oh * ow), gamma, beta, rm, rv, None, BN_MOMENTUM, BN_EPS,
+                                                   s.cout, device, centered=False)
+            dst = out1 if out1 is not None else _nhwc_empty(n, oh, ow, s.cout, device)
+            wp = packed[0] if packed is not None and packed[0] is not None else s.pack_fwd(weight)
+            if ops.conv_gather_affine(x_view, wp, scale, shift, view_nhwc(dst), s.fwd_mode, s.k, s.stride, s.pad, self.act1):
+                sv = Saved()
+                sv.extra["pooled"] = False
+                return dst, sv
+        y = _nhwc_empty(n, oh, ow, s.cout, device)
         if stem:   # fp32 NCHW network input with 1..4 channels: bandwidth kernel, torch-layout fp32 weights
             stats, rows = ops.stem_conv_fwd(x_keep, weight.detach().contiguous(), bias, y, s.k, s.stride, s.pad,
                                             want_stats=self.has_bn and training and _CONFIG["fused_stats"] and not self.instance)

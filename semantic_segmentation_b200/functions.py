@@ -1,6 +1,6 @@
 """torch.autograd glue: ONE autograd node per network call.
 
-``ProgramFunction.apply(program, module_buffers, training, x, *params)`` runs the program's explicit
+``ProgramFunction.apply(program, module_buffers, training, extra, n_in, grad_mode, *inputs, *params)`` runs the program's explicit
 forward on the CUDA kernels and keeps its tape; backward runs the explicit backward.  It supports
 loss.backward(), torch.autograd.grad(..., allow_unused=True), retain_graph=True (the tape is never
 mutated by backward), torch.no_grad() (nothing saved) and requires_grad_(False) parameters (their
@@ -17,7 +17,7 @@ from ._lib import require_cuda
 
 class ProgramFunction(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, program, buffers: Dict[str, torch.Tensor], training: bool, extra, n_in: int, *tensors):
+    def forward(ctx, program, buffers: Dict[str, torch.Tensor], training: bool, extra, n_in: int, grad_mode: bool, *tensors):
         xs, params = tensors[:n_in], tensors[n_in:]
         for x in xs:
             require_cuda(x, "input")
@@ -27,7 +27,10 @@ class ProgramFunction(torch.autograd.Function):
         P = {k: v.detach() for k, v in zip(names, params)}
         for k, v in P.items():
             require_cuda(v, k)
-        need_any = any(ctx.needs_input_grad)
+        # ctx.needs_input_grad reflects requires_grad only -- it stays True under torch.no_grad() -- so the caller's grad mode
+        # travels as an argument: without it nothing is saved, no backward weight layout is packed and, in eval mode, the
+        # BatchNorm folds into the convolution epilogues (engine.ConvBNAct.forward)
+        need_any = bool(grad_mode) and any(ctx.needs_input_grad)
         xin = xs[0].detach() if n_in == 1 else tuple(x.detach() for x in xs)
         out, tape = program.forward(xin, P, buffers, training, need_any, extra)
         # The tape may hold the output tensor itself (e.g. the generator's tanh output, needed by its backward).  The
@@ -47,9 +50,9 @@ class ProgramFunction(torch.autograd.Function):
         if ctx.tape is None:
             raise RuntimeError("genseg_b200: backward called but no tape was saved")
         n_in = ctx.n_in
-        need_in = ctx.needs_input_grad  # (program, buffers, training, extra, n_in, *inputs, *params)
-        need = {k: bool(need_in[5 + n_in + i]) for i, k in enumerate(ctx.names)}
-        need_x = [bool(need_in[5 + i]) for i in range(n_in)]
+        need_in = ctx.needs_input_grad  # (program, buffers, training, extra, n_in, grad_mode, *inputs, *params)
+        need = {k: bool(need_in[6 + n_in + i]) for i, k in enumerate(ctx.names)}
+        need_x = [bool(need_in[6 + i]) for i in range(n_in)]
         dx, G = ctx.program.backward(ctx.tape, dout, need, need_x[0] if n_in == 1 else need_x)
         dxs = (dx,) if n_in == 1 else tuple(dx)
         dxs = tuple(d if nx else None for d, nx in zip(dxs, need_x))
@@ -59,7 +62,7 @@ class ProgramFunction(torch.autograd.Function):
             for p_, g_ in zip(ctx.param_refs, grads):
                 if g_ is not None:
                     p_._gsb_grad_reduced = True
-        return (None, None, None, None, None, *dxs, *grads)
+        return (None, None, None, None, None, None, *dxs, *grads)
 
 
 def run_program(program, module: torch.nn.Module, x, extra=None):
@@ -72,4 +75,4 @@ def run_program(program, module: torch.nn.Module, x, extra=None):
     pd = dict(module.named_parameters())
     bd = dict(module.named_buffers())
     params = [pd[k] for k in program.param_names]
-    return ProgramFunction.apply(program, bd, module.training, extra, len(xs), *xs, *params)
+    return ProgramFunction.apply(program, bd, module.training, extra, len(xs), torch.is_grad_enabled(), *xs, *params)

@@ -308,7 +308,7 @@ class UnetGenerator(nn.Module):
         bd = dict(self.named_buffers())
         params = [pd[k] for k in self._program.param_names if k != ARCH_KEY] + [arch]
         extra = {"drop_masks": self._dropout_masks} if self._dropout_masks is not None else None
-        return ProgramFunction.apply(self._program, bd, self.training, extra, 1, input, *params)
+        return ProgramFunction.apply(self._program, bd, self.training, extra, 1, torch.is_grad_enabled(), input, *params)
 
 
 class NLayerDiscriminator(nn.Module):

@@ -209,6 +209,19 @@ def conv_gather(inp: GsbView, wp: torch.Tensor, bias: Optional[torch.Tensor], ou
 _SPLITK_BYTES = 16 << 20
 
 
+def conv_gather_affine(inp: GsbView, wp: torch.Tensor, scale: torch.Tensor, shift: torch.Tensor, out: GsbView, mode: int, k: int,
+                       stride: int, pad: int, act: int) -> bool:
+    """out = act(conv(inp) * scale + shift) in one pass (inference: BatchNorm folded into the convolution's epilogue).
+    False when the shape has no such kernel (the caller then runs conv_gather + bn_act)."""
+    g = GsbConvGeom(mode, k, k, stride, pad)
+    rc = load().gsb_conv_gather_affine(_ref(inp), ptr(wp), L.dtype_code(wp.dtype), ptr(scale), ptr(shift), _ref(out), C.byref(g), act,
+                                       _s(wp))
+    if rc == 1:
+        return False
+    check(rc, "conv_gather_affine")
+    return True
+
+
 def conv_wgrad_plan(inp: GsbView, dout: GsbView, mode: int, k: int, stride: int, pad: int, use_tc: int = 2) -> int:
     """Number of partial-sum slices gsb_conv_wgrad will write for this geometry (host-side, no launch)."""
     g = GsbConvGeom(mode, k, k, stride, pad)

@@ -344,3 +344,44 @@ def test_pool_fusion_matches_separate_kernels(monkeypatch):
         ref = out["0"][1][k]
         err = float((gr.double() - ref.double()).norm() / ref.double().norm().clamp_min(1e-30))
         assert err < 2e-2, (k, err)     # bf16 step: the statistics differ in fp32 summation order only (measured ~1e-3)
+
+
+def test_eval_forward_folds_batchnorm_into_the_convolution(monkeypatch):
+    """Inference (net.eval(), no_grad): Conv -> BatchNorm(running statistics) -> ReLU runs as ONE kernel (per-channel affine
+    epilogue of the tcgen05 kernel, GSB_EVAL_FOLD) -- against the separate kernels: logits within the bf16 rounding of one
+    stored intermediate, identical argmax masks up to ties, far fewer launches."""
+    import semantic_segmentation_b200 as S
+    from semantic_segmentation_b200._lib import load
+    from semantic_segmentation_b200.unet import UNet
+    S.set_precision("bf16")
+    torch.manual_seed(31)
+    net = UNet(1, 2, True).cuda()
+    g = torch.Generator().manual_seed(8)
+    with torch.no_grad():                       # non-trivial running statistics
+        for m in net.modules():
+            if isinstance(m, torch.nn.BatchNorm2d):
+                m.running_mean.copy_(torch.randn(m.num_features, generator=g).cuda() * 0.1)
+                m.running_var.copy_((torch.rand(m.num_features, generator=g) + 0.5).cuda())
+    net.eval()
+    x = torch.rand(4, 1, 128, 128, generator=g).cuda()
+    out, launches = {}, {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("GSB_EVAL_FOLD", flag)
+        with torch.no_grad():
+            net(x)
+            l0 = load().gsb_launch_count()
+            out[flag] = net(x).float()
+            launches[flag] = load().gsb_launch_count() - l0
+    err = float((out["1"] - out["0"]).norm() / out["0"].norm())
+    assert err < 1e-2, err
+    agree = (out["1"].argmax(1) == out["0"].argmax(1)).float().mean().item()
+    assert agree > 0.995, agree
+    assert launches["1"] <= launches["0"] - 8, launches       # the BatchNorm passes of the >= 16 x 16 levels are gone (62 -> 53)
+    # and against the fp32 validation mode (separate kernels, centred BatchNorm): the production-dtype bound
+    S.set_precision("fp32")
+    try:
+        with torch.no_grad():
+            ref = net(x).float()
+    finally:
+        S.set_precision("bf16")
+    assert float((out["1"] - ref).norm() / ref.norm()) < 6e-2
