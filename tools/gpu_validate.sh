@@ -6,7 +6,7 @@ timeout 600 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')
 timeout 2400 python -m pytest tests -m gpu -q -x > gpurun_out/${TAG}_suite.log 2>&1; echo "suite rc=$?"; tail -4 gpurun_out/${TAG}_suite.log | cut -c1-300
 timeout 600 python bench.py > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err; echo "bench rc=$?"; tail -2 gpurun_out/${TAG}_bench.err | cut -c1-300
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${TAG}_bench_reference.json 2> gpurun_out/${TAG}_bench_reference.err; echo "reference arm rc=$?"; cat gpurun_out/${TAG}_bench_reference.json | cut -c1-600
-python - <<'PY'
+python - <<PY
 import json
 d=json.loads(open('gpurun_out/${TAG}_bench.json').read().strip().splitlines()[-1])
 print('bench ms', round(d['ms_per_step'],3), 'value', round(d['value'],1), 'e2e', round(d['e2e']['value'],1), d['clocks'], 'launches', d['gpu_launches'], 'roofline', round(d['roofline']['achieved']), round(d['roofline']['frac'],3), d['cpu_baseline'])
