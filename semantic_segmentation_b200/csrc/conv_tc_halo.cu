@@ -878,7 +878,9 @@ int conv_halo_wgrad(const SubView& tiled, const SubView* shifted, int nmaps, con
   const int base = m_tiles * p.n_tiles;
   // split-K over the pixel boxes: fill whole waves of SMs, keep >= 2 boxes per CTA
   const int sms = num_sms_avail();
-  static const bool one_wave = env_flag("GSB_WGRAD_ONE_WAVE", true);
+  // GSB_WGRAD_ONE_WAVE: 0 = off, 1 = every layer, 2 = only the 128-column kernel (A/B runs)
+  static const int one_wave_mode = []() { const char* e = getenv("GSB_WGRAD_ONE_WAVE"); return (e && e[0]) ? atoi(e) : 1; }();
+  const bool one_wave = one_wave_mode == 1 || (one_wave_mode == 2 && BN == 128);
   int max_split = p.boxes / 2 > 0 ? p.boxes / 2 : 1;
   if (ws != nullptr && max_split > max_slices) max_split = max_slices;
   int best = 1;
