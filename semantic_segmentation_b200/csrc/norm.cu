@@ -272,11 +272,9 @@ __global__ void __launch_bounds__(kThreads, 2) bn_bwd_reduce_relu_pool_bf16_kern
   const int lanes = kThreads / G;
   const int g = threadIdx.x % G, lane = threadIdx.x / G;
   const int c0 = g * 8;
-  float s0[8], s1[8], sc[8], sh[8];
+  float s0[8], s1[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) s0[i] = s1[i] = 0.f;
-  load_param8(scale, c0, sc, 1.f);
-  load_param8(shift, c0, sh, 0.f);
   const unsigned OW = (unsigned)W >> 1, OH = (unsigned)H >> 1;
   const int64_t windows = (int64_t)N * OH * OW;
   const int64_t step = (int64_t)gridDim.x * lanes;
@@ -302,10 +300,17 @@ __global__ void __launch_bounds__(kThreads, 2) bn_bwd_reduce_relu_pool_bf16_kern
       ra[t] = *reinterpret_cast<const uint4*>(dA + p * dld + c0);
     }
     const uint4 rp = *reinterpret_cast<const uint4*>(dpool + wi * pld + c0);
-    const uint32_t* wp = reinterpret_cast<const uint32_t*>(&rp);
-    uint32_t outw[4][4];
+    const uint32_t wp[4] = {rp.x, rp.y, rp.z, rp.w};
+    // the routed gradient replaces the loaded one IN PLACE (ra[t] word i), so no second set of 16 registers is live:
+    // (3 blocks per SM at 80 registers + spills measured the same 0.61 of the HBM roofline as 2 blocks: r02z_full_new.raw.csv)
+    uint32_t aw[4][4];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) { aw[t][0] = ra[t].x; aw[t][1] = ra[t].y; aw[t][2] = ra[t].z; aw[t][3] = ra[t].w; }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
+      // scale / shift of this channel pair from L1 (16 registers less than keeping all eight pairs)
+      const float2 sc2 = __ldg(reinterpret_cast<const float2*>(scale + c0 + 2 * i));
+      const float2 sh2 = __ldg(reinterpret_cast<const float2*>(shift + c0 + 2 * i));
       float v0[4], v1[4], a0[4], a1[4];
       int arg0 = 0, arg1 = 0;
       float m0 = 0.f, m1 = 0.f;
@@ -315,7 +320,7 @@ __global__ void __launch_bounds__(kThreads, 2) bn_bwd_reduce_relu_pool_bf16_kern
         v0[t] = __uint_as_float(wv << 16);
         v1[t] = __uint_as_float(wv & 0xffff0000u);
         // stored activation (bf16, round to nearest even) as bn_act_kernel<bf16, true> writes it
-        const float z0 = fmaf(v0[t], sc[2 * i], sh[2 * i]), z1 = fmaf(v1[t], sc[2 * i + 1], sh[2 * i + 1]);
+        const float z0 = fmaf(v0[t], sc2.x, sh2.x), z1 = fmaf(v1[t], sc2.y, sh2.y);
         a0[t] = __bfloat162float(__float2bfloat16_rn(z0 > 0.f ? z0 : 0.f));
         a1[t] = __bfloat162float(__float2bfloat16_rn(z1 > 0.f ? z1 : 0.f));
         if (t == 0) { m0 = a0[0]; m1 = a1[0]; }
@@ -327,12 +332,12 @@ __global__ void __launch_bounds__(kThreads, 2) bn_bwd_reduce_relu_pool_bf16_kern
       const float g0 = __uint_as_float(wp[i] << 16), g1 = __uint_as_float(wp[i] & 0xffff0000u);
 #pragma unroll
       for (int t = 0; t < 4; ++t) {
-        const uint32_t wa = reinterpret_cast<const uint32_t*>(&ra[t])[i];
+        const uint32_t wa = aw[t][i];
         float d0 = __uint_as_float(wa << 16), d1 = __uint_as_float(wa & 0xffff0000u);
         d0 += arg0 == t ? g0 : 0.f;
         d1 += arg1 == t ? g1 : 0.f;
         const __nv_bfloat162 h = __floats2bfloat162_rn(d0, d1);
-        outw[t][i] = *reinterpret_cast<const uint32_t*>(&h);
+        aw[t][i] = *reinterpret_cast<const uint32_t*>(&h);
         d0 = __low2float(h);
         d1 = __high2float(h);
         const float e0 = a0[t] > 0.f ? d0 : 0.f, e1 = a1[t] > 0.f ? d1 : 0.f;   // z > 0 <=> stored a > 0
@@ -345,7 +350,7 @@ __global__ void __launch_bounds__(kThreads, 2) bn_bwd_reduce_relu_pool_bf16_kern
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
       const int64_t p = p00 + (t >> 1) * (int64_t)W + (t & 1);
-      *reinterpret_cast<uint4*>(dA + p * dld + c0) = make_uint4(outw[t][0], outw[t][1], outw[t][2], outw[t][3]);
+      *reinterpret_cast<uint4*>(dA + p * dld + c0) = make_uint4(aw[t][0], aw[t][1], aw[t][2], aw[t][3]);
     }
   }
   {
