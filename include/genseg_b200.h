@@ -131,6 +131,10 @@ int gsb_stem_stats_rows(void);
 int gsb_stem_conv_fwd(const float* x, int n, int cin, int h, int w, const float* weight, const float* bias,
                       const gsb_view* y, int k, int stride, int pad, int act, float* stats_partial, int* stats_rows,
                       gsb_stream s);
+/* Inference form: out = act(conv(x) * scale[co] + shift[co]) in one pass (eval-mode Conv -> BatchNorm -> ReLU of
+ * unet_parts.py:16-18 on the network input).  0 = launched, 1 = not applicable (run gsb_stem_conv_fwd + gsb_bn_act), -1 = error. */
+int gsb_stem_conv_fwd_affine(const float* x, int n, int cin, int h, int w, const float* weight, const float* scale,
+                             const float* shift, const gsb_view* y, int k, int stride, int pad, int act, gsb_stream s);
 int gsb_edge_rows(void);
 int gsb_stem_conv_wgrad(const float* x, int n, int cin, int h, int w, const gsb_view* dy, int k, int stride, int pad,
                         float* dweight, void* workspace, size_t workspace_bytes, gsb_stream s);

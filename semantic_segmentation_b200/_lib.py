@@ -56,6 +56,7 @@ SIGNATURES = {
     "gsb_edge_rows": (_i, []),
     "gsb_stem_stats_rows": (_i, []),
     "gsb_stem_conv_fwd": (_i, [_p, _i, _i, _i, _i, _p, _p, _VP, _i, _i, _i, _i, _p, _p, _p]),
+    "gsb_stem_conv_fwd_affine": (_i, [_p, _i, _i, _i, _i, _p, _p, _p, _VP, _i, _i, _i, _i, _p]),
     "gsb_stem_conv_wgrad": (_i, [_p, _i, _i, _i, _i, _VP, _i, _i, _i, _p, _p, _sz, _p]),
     "gsb_head_conv_fwd": (_i, [_VP, _p, _p, _i, _p, _p]),
     "gsb_head_conv_bwd": (_i, [_VP, _p, _i, _p, _VP, _p, _p, _p, _sz, _p]),

@@ -557,7 +557,8 @@ __global__ void __launch_bounds__(256, 4) head_bwd_kernel(const T* __restrict__ 
 // tensor-core stem (stem_tc.cu)
 bool stem_tc_applicable(int cin, int cout, int k, int stride, int dtype, int64_t pixels);
 int stem_tc_fwd(const float* x, int h, int w, const float* weight, const gsb_view* y, int k, int stride, int pad, float* stats,
-                int max_rows, int* rows, cudaStream_t st);
+                int max_rows, int* rows, cudaStream_t st, const float* aff_scale = nullptr, const float* aff_shift = nullptr,
+                int aff_relu = 0);
 int stem_tc_wgrad(const float* x, int h, int w, const gsb_view* dy, int k, int stride, int pad, float* partial, int max_rows,
                   int* rows, cudaStream_t st);
 
@@ -587,6 +588,22 @@ static int stem_check(const float* x, const gsb_view* y, int cin, int k) {
 }
 
 extern "C" int gsb_stem_stats_rows(void) { return num_sms() * 8; }
+
+// Inference form of the stem: out = act(conv(x) * scale[co] + shift[co]) in one pass (eval-mode Conv -> BatchNorm -> ReLU of
+// unet_parts.py:16-18 on the 1-channel network input).  0 = launched, 1 = not applicable (the caller runs gsb_stem_conv_fwd +
+// gsb_bn_act), -1 = error.  act: GSB_ACT_NONE or GSB_ACT_RELU; tensor-core stem shapes only.
+extern "C" int gsb_stem_conv_fwd_affine(const float* x, int n, int cin, int h, int w, const float* weight, const float* scale,
+                                        const float* shift, const gsb_view* y, int k, int stride, int pad, int act, gsb_stream s) {
+  if (stem_check(x, y, cin, k)) return -1;
+  GSB_REQUIRE(weight && scale && y->n == n && y->h == (h + 2 * pad - k) / stride + 1 && y->w == (w + 2 * pad - k) / stride + 1,
+              "stem_conv_fwd_affine: shape mismatch");
+  if ((act != GSB_ACT_NONE && act != GSB_ACT_RELU) || !stem_tc_applicable(cin, y->c, k, stride, y->dtype, num_pixels(y))) return 1;
+  int rows = 0;
+  if (stem_tc_fwd(x, h, w, weight, y, k, stride, pad, nullptr, gsb_stem_stats_rows(), &rows, to_stream(s), scale, shift,
+                  act == GSB_ACT_RELU ? 1 : 0))
+    return -1;
+  return check_launch("stem_conv_fwd_affine");
+}
 
 extern "C" int gsb_stem_conv_fwd(const float* x, int n, int cin, int h, int w, const float* weight, const float* bias,
                                  const gsb_view* y, int k, int stride, int pad, int act, float* stats_partial, int* stats_rows,

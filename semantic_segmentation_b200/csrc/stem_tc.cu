@@ -85,7 +85,9 @@ template <int T, int K, int S>
 __global__ void __launch_bounds__(128, 6) stem_tc_fwd_kernel(const __grid_constant__ CUtensorMap ymap, int use_tma,
                                                          const float* __restrict__ x, int H, int W, const float* __restrict__ w,
                                                          __nv_bfloat16* __restrict__ y, int64_t yld, int OH, int OW, int pad,
-                                                         float* __restrict__ stats, int64_t P, int num_tiles) {
+                                                         float* __restrict__ stats, int64_t P, int num_tiles,
+                                                         const float* __restrict__ aff_scale, const float* __restrict__ aff_shift,
+                                                         int aff_relu) {
   GSB_PDL_ENTRY();
   constexpr int KS = (3 * T + 15) / 16;       // K = 16 steps that hold non-zero columns
   constexpr int NCH = 2 * KS;                 // 16-byte chunks per row that the MMAs read
@@ -95,7 +97,7 @@ __global__ void __launch_bounds__(128, 6) stem_tc_fwd_kernel(const __grid_consta
   uint8_t* sB = smem + 16384;                 // [64 co][64 columns]
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 16384 + 8192);
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(bar + 1);
-  float* red = reinterpret_cast<float*>(bar + 2);   // [4 row groups][2][64]
+  float* red = reinterpret_cast<float*>(bar + 2);   // [4 row groups][2][64]; with an affine epilogue: [scale 64 | shift 64]
   const int tid = threadIdx.x, warp = tid >> 5;
   if (tid == 0) {
     mbar_init(bar, 1);
@@ -126,6 +128,12 @@ __global__ void __launch_bounds__(128, 6) stem_tc_fwd_kernel(const __grid_consta
       q.w = pack_bf16(e[8 * j + 6], e[8 * j + 7]);
       *reinterpret_cast<uint4*>(sB + swz_off(tid, j)) = q;
     }
+  }
+  // inference: out = act(acc * scale[co] + shift[co]) (BatchNorm of the running statistics folded in; no statistics then)
+  const bool affine = aff_scale != nullptr;
+  if (affine && tid < 64) {
+    red[tid] = __ldg(aff_scale + tid);
+    red[64 + tid] = aff_shift ? __ldg(aff_shift + tid) : 0.f;
   }
   fence_proxy_async();
   tc_fence_before();
@@ -163,6 +171,16 @@ __global__ void __launch_bounds__(128, 6) stem_tc_fwd_kernel(const __grid_consta
     uint32_t a0[32], a1[32];
     tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16), a0);
     tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + 32, a1);
+    if (affine) {
+#pragma unroll
+      for (int c = 0; c < 32; ++c) {
+        float f0 = fmaf(__uint_as_float(a0[c]), red[c], red[64 + c]);
+        float f1 = fmaf(__uint_as_float(a1[c]), red[32 + c], red[96 + c]);
+        if (aff_relu) { f0 = fmaxf(f0, 0.f); f1 = fmaxf(f1, 0.f); }
+        a0[c] = __float_as_uint(f0);
+        a1[c] = __float_as_uint(f1);
+      }
+    }
     uint4 q[8];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -337,7 +355,7 @@ bool stem_tc_applicable(int cin, int cout, int k, int stride, int dtype, int64_t
 
 // Returns the number of statistic rows written (= CTAs) through *rows; 0 on success.
 int stem_tc_fwd(const float* x, int h, int w, const float* weight, const gsb_view* y, int k, int stride, int pad, float* stats,
-                int max_rows, int* rows, cudaStream_t st) {
+                int max_rows, int* rows, cudaStream_t st, const float* aff_scale, const float* aff_shift, int aff_relu) {
   const int64_t P = num_pixels(y);
   const int num_tiles = (int)((P + 127) / 128);
   int grid = num_sms() * 8;
@@ -352,10 +370,10 @@ int stem_tc_fwd(const float* x, int h, int w, const float* weight, const gsb_vie
   if (use_tma && make_w_map(&ymap, y->ptr, P, 64, 128)) return -1;
   if (k == 3)
     gsb::launch(stem_tc_fwd_kernel<9, 3, 1>, gsb::LaunchCfg(grid, 128, smem, st), ymap, use_tma, x, h, w, weight, yp, (int64_t)y->sw,
-                y->h, y->w, pad, stats, P, num_tiles);
+                y->h, y->w, pad, stats, P, num_tiles, aff_scale, aff_shift, aff_relu);
   else
     gsb::launch(stem_tc_fwd_kernel<16, 4, 2>, gsb::LaunchCfg(grid, 128, smem, st), ymap, use_tma, x, h, w, weight, yp, (int64_t)y->sw,
-                y->h, y->w, pad, stats, P, num_tiles);
+                y->h, y->w, pad, stats, P, num_tiles, aff_scale, aff_shift, aff_relu);
   if (rows) *rows = stats != nullptr ? grid : 0;
   return 0;
 }

@@ -415,7 +415,7 @@ class ConvBNAct:
         oh, ow = s.out_hw(h, w)
         stem = _is_stem(s, x_view, x_keep)
         if (not training and not save and self.has_bn and not self.instance and self.act2 is None and bias is None
-                and not stem and s.kind == "conv" and _CONFIG["use_tc"] and act_dtype() == torch.bfloat16
+                and s.kind == "conv" and _CONFIG["use_tc"] and act_dtype() == torch.bfloat16
                 and not centered_bn() and eval_fold_enabled()):
             # inference: BatchNorm of the running statistics folded into the convolution's epilogue -- Conv -> BN -> act is ONE
             # pass, the pre-normalisation tensor is never written (nothing is saved: no backward through this call)
@@ -423,8 +423,14 @@ class ConvBNAct:
             scale, shift, _m, _i = ops.bn_finalize(None, float(n * oh * ow), gamma, beta, rm, rv, None, BN_MOMENTUM, BN_EPS,
                                                    s.cout, device, centered=False)
             dst = out1 if out1 is not None else _nhwc_empty(n, oh, ow, s.cout, device)
-            wp = packed[0] if packed is not None and packed[0] is not None else s.pack_fwd(weight)
-            if ops.conv_gather_affine(x_view, wp, scale, shift, view_nhwc(dst), s.fwd_mode, s.k, s.stride, s.pad, self.act1):
+            if stem:
+                folded = ops.stem_conv_fwd_affine(x_keep, weight.detach().contiguous(), scale, shift, dst, s.k, s.stride, s.pad,
+                                                  self.act1)
+            else:
+                wp = packed[0] if packed is not None and packed[0] is not None else s.pack_fwd(weight)
+                folded = ops.conv_gather_affine(x_view, wp, scale, shift, view_nhwc(dst), s.fwd_mode, s.k, s.stride, s.pad,
+                                                self.act1)
+            if folded:
                 sv = Saved()
                 sv.extra["pooled"] = False
                 return dst, sv

@@ -209,6 +209,18 @@ def conv_gather(inp: GsbView, wp: torch.Tensor, bias: Optional[torch.Tensor], ou
 _SPLITK_BYTES = 16 << 20
 
 
+def stem_conv_fwd_affine(x: torch.Tensor, weight: torch.Tensor, scale: torch.Tensor, shift: torch.Tensor, y: torch.Tensor, k: int,
+                         stride: int, pad: int, act: int) -> bool:
+    """y = act(conv(x) * scale + shift) on the fp32 NCHW network input in one pass (inference); False = not applicable."""
+    n, cin, h, w = x.shape
+    rc = load().gsb_stem_conv_fwd_affine(ptr(x), n, cin, h, w, ptr(weight), ptr(scale), ptr(shift), _ref(view_nhwc(y)), k, stride, pad,
+                                         act, _s(x))
+    if rc == 1:
+        return False
+    check(rc, "stem_conv_fwd_affine")
+    return True
+
+
 def conv_gather_affine(inp: GsbView, wp: torch.Tensor, scale: torch.Tensor, shift: torch.Tensor, out: GsbView, mode: int, k: int,
                        stride: int, pad: int, act: int) -> bool:
     """out = act(conv(inp) * scale + shift) in one pass (inference: BatchNorm folded into the convolution's epilogue).
