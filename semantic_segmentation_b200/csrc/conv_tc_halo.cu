@@ -374,16 +374,30 @@ conv_tc_halo_kernel(const __grid_constant__ TcMaps maps, const __grid_constant__
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
               uint32_t pk[4];
+              // per-channel factor / offset of these 8 columns: four 16-byte loads (warp-uniform addresses) instead of 32
+              // scalar ones -- the scalar form made the inference epilogue of the 64-column kernel 27 % slower than the
+              // training one (profiles/r02zz_eval_launch_summary.txt)
+              float sc8[8], bi8[8];
+              if (p.scale != nullptr) {
+                const float4 a = __ldg(reinterpret_cast<const float4*>(p.scale + cbase + g * 8));
+                const float4 b = __ldg(reinterpret_cast<const float4*>(p.scale + cbase + g * 8 + 4));
+                sc8[0] = a.x; sc8[1] = a.y; sc8[2] = a.z; sc8[3] = a.w; sc8[4] = b.x; sc8[5] = b.y; sc8[6] = b.z; sc8[7] = b.w;
+              }
+              if (p.bias != nullptr) {
+                const float4 a = __ldg(reinterpret_cast<const float4*>(p.bias + cbase + g * 8));
+                const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + cbase + g * 8 + 4));
+                bi8[0] = a.x; bi8[1] = a.y; bi8[2] = a.z; bi8[3] = a.w; bi8[4] = b.x; bi8[5] = b.y; bi8[6] = b.z; bi8[7] = b.w;
+              }
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
                 float f0 = __uint_as_float(v[g * 8 + 2 * e]), f1 = __uint_as_float(v[g * 8 + 2 * e + 1]);
                 if (p.scale != nullptr) {
-                  f0 *= __ldg(p.scale + cbase + g * 8 + 2 * e);
-                  f1 *= __ldg(p.scale + cbase + g * 8 + 2 * e + 1);
+                  f0 *= sc8[2 * e];
+                  f1 *= sc8[2 * e + 1];
                 }
                 if (p.bias != nullptr) {
-                  f0 += __ldg(p.bias + cbase + g * 8 + 2 * e);
-                  f1 += __ldg(p.bias + cbase + g * 8 + 2 * e + 1);
+                  f0 += bi8[2 * e];
+                  f1 += bi8[2 * e + 1];
                 }
                 if (is_tanh) {
                   f0 = tanhf(f0);

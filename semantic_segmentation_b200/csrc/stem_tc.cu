@@ -172,13 +172,20 @@ __global__ void __launch_bounds__(128, 6) stem_tc_fwd_kernel(const __grid_consta
     tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16), a0);
     tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + 32, a1);
     if (affine) {
+      const float4* r4 = reinterpret_cast<const float4*>(red);   // 16-byte broadcast reads: [scale 64 | shift 64]
 #pragma unroll
-      for (int c = 0; c < 32; ++c) {
-        float f0 = fmaf(__uint_as_float(a0[c]), red[c], red[64 + c]);
-        float f1 = fmaf(__uint_as_float(a1[c]), red[32 + c], red[96 + c]);
-        if (aff_relu) { f0 = fmaxf(f0, 0.f); f1 = fmaxf(f1, 0.f); }
-        a0[c] = __float_as_uint(f0);
-        a1[c] = __float_as_uint(f1);
+      for (int c4 = 0; c4 < 8; ++c4) {
+        const float4 s0 = r4[c4], s1 = r4[8 + c4], h0 = r4[16 + c4], h1 = r4[24 + c4];
+        const float sa[4] = {s0.x, s0.y, s0.z, s0.w}, sb[4] = {s1.x, s1.y, s1.z, s1.w};
+        const float ha[4] = {h0.x, h0.y, h0.z, h0.w}, hb[4] = {h1.x, h1.y, h1.z, h1.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          float f0 = fmaf(__uint_as_float(a0[4 * c4 + k]), sa[k], ha[k]);
+          float f1 = fmaf(__uint_as_float(a1[4 * c4 + k]), sb[k], hb[k]);
+          if (aff_relu) { f0 = fmaxf(f0, 0.f); f1 = fmaxf(f1, 0.f); }
+          a0[4 * c4 + k] = __float_as_uint(f0);
+          a1[4 * c4 + k] = __float_as_uint(f1);
+        }
       }
     }
     uint4 q[8];

@@ -160,7 +160,7 @@ def evaluate(dev, n, hw):
             counts, _ = predict_counts(net, x, y)
             return dice_from_counts(counts)
 
-    return dict(step=step, host_batch=host, units=n, graphable=False,
+    return dict(step=step, host_batch=host, units=n, graphable=True,
                 metric="U-Net inference images/sec (eval forward + fused argmax / Dice counts, bf16)",
                 workload="UNet(1,2,bilinear) evaluate path (unet/evaluate.py:10-43): %d x 1 x %d x %d per batch" % (n, hw, hw),
                 flops_per_unit=79.818e9 * (hw / 256.0) ** 2, flops_note="forward only", weight_bytes_note=None)
